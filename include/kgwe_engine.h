@@ -1,0 +1,247 @@
+/*
+ * kgwe_engine.h — C ABI of the B200 scoring engine for KGWE's scheduler hot path.
+ *
+ * This is the drop-in boundary for ONE path of asklokesh/k8s-gpu-workload-enhancer:
+ * the per-pod x per-node x per-GPU-subset Filter/Prioritize scoring done today by
+ * (*TopologyAwareScheduler).scoreNodes and the argmax/commit around it in Schedule
+ * (reference: src/scheduler/scheduler.go:114-179, 182-707).  A cgo shim in the
+ * reference's src/scheduler package binds exactly these entry points (see
+ * INTEGRATION.md); tests and bench.py bind the same symbols through ctypes.
+ *
+ * Conventions
+ *  - Every function returns KGWE_OK (0) or a negative kgwe_status; nothing throws or
+ *    aborts across this boundary.  kgwe_last_error() gives the message of the last
+ *    failing call on that engine.
+ *  - All structs are plain old data with fixed-width fields.  Buffers are owned by
+ *    the caller; the engine keeps no caller pointer after a call returns (cgo rule).
+ *  - The engine owns its device memory and pinned staging.  One mutex per engine
+ *    (mirrors `s.mu`, scheduler.go:17) makes every entry point callable from any
+ *    thread; each call selects the engine's CUDA device first.
+ *  - There is no CPU fallback: if CUDA is unavailable, kgwe_engine_create fails.
+ *  - Canonical order: nodes are visited in ascending node index and
+ *    ties on TotalScore resolve to the LOWEST node index; NUMA groups in ascending
+ *    numa[] value; PCIe groups in ascending pcie_switch[] id.  Each is one of the
+ *    outcomes Go's map iteration / unstable sort can produce.
+ */
+#ifndef KGWE_ENGINE_H
+#define KGWE_ENGINE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KGWE_MAX_GPUS      8     /* GPUs per node record (all BASELINE configs use 8) */
+#define KGWE_MIG_PROFILES  10    /* CRD whitelist, src/sharing/mig_controller.go:273-284 */
+#define KGWE_MAX_TOPK      16
+#define KGWE_NO_NODE       0xFFFFFFFFu
+#define KGWE_MAX_BW_GBPS   100000.0   /* upsert rejects bandwidths outside [0, this] or non-finite */
+
+typedef enum kgwe_status {
+    KGWE_OK                =  0,
+    KGWE_ERR_INVALID_ARG   = -1,
+    KGWE_ERR_CUDA          = -2,
+    KGWE_ERR_NO_DEVICE     = -3,
+    KGWE_ERR_OUT_OF_RANGE  = -4,
+    KGWE_ERR_NOT_FOUND     = -5,   /* "allocation not found for workload", scheduler.go:715 */
+    KGWE_ERR_CONFLICT      = -6,   /* commit names a GPU that is already allocated, scheduler.go:634-640 */
+    KGWE_ERR_NO_MEMORY     = -7,
+    KGWE_ERR_TOO_LARGE     = -8
+} kgwe_status;
+
+/* TopologyPreference, src/scheduler/types.go:60-77.  Any other string maps to NONE
+ * (the `default:` arm, scheduler.go:325-331). */
+enum {
+    KGWE_TOPO_NONE = 0,
+    KGWE_TOPO_NVLINK_OPTIMAL = 1,
+    KGWE_TOPO_NVLINK_REQUIRED = 2,   /* treated exactly like OPTIMAL, scheduler.go:319-320 */
+    KGWE_TOPO_SAME_NUMA = 3,
+    KGWE_TOPO_SAME_PCIE_SWITCH = 4
+};
+
+/* GPUArchitecture, src/discovery/types.go:50-59.  0 = "" (no requirement / unknown). */
+enum {
+    KGWE_ARCH_ANY = 0, KGWE_ARCH_VOLTA = 1, KGWE_ARCH_TURING = 2, KGWE_ARCH_AMPERE = 3,
+    KGWE_ARCH_HOPPER = 4, KGWE_ARCH_ADA = 5, KGWE_ARCH_BLACKWELL = 6
+    /* 7..254: host-interned other strings; 255 = a requested string no GPU carries */
+};
+
+/* MIG profile ids: index+1 into the CRD whitelist in this order
+ * (deploy/helm/kgwe/crds/gpuworkload-crd.yaml:94-104):
+ * 1g.5gb 1g.10gb 2g.10gb 2g.20gb 3g.20gb 3g.40gb 4g.20gb 4g.40gb 7g.40gb 7g.80gb */
+#define KGWE_MIG_NONE     0      /* MIGRequirements == nil */
+#define KGWE_MIG_UNKNOWN  255    /* a profile name outside the table: availability is 0 */
+
+/* Engine configuration.  Mirrors the fields of SchedulerConfig that the path reads
+ * (src/scheduler/types.go:346-392; weights used at scheduler.go:282-284). */
+typedef struct kgwe_config {
+    uint32_t struct_size;        /* sizeof(kgwe_config), for forward compatibility */
+    int32_t  device;             /* CUDA device ordinal */
+    uint32_t max_nodes;          /* capacity of the cluster image (records) */
+    uint32_t node_base;          /* global index of local record 0 (node sharding; 0 on one GPU) */
+    int32_t  topology_weight;    /* 40  (types.go:385) */
+    int32_t  resource_weight;    /* 35  (types.go:386) */
+    int32_t  balance_weight;     /* 25  (types.go:387) */
+    int32_t  hint_bonus;         /* 10  (scheduler.go:274) */
+    double   nvlink_norm_gbps;   /* 900.0 (scheduler.go:368) */
+    uint32_t flags;              /* reserved, 0 */
+    uint32_t reserved;
+} kgwe_config;
+
+/* One node of the topology snapshot: exactly the fields of NodeTopology / GPUDevice the
+ * scorer reads (src/discovery/types.go:11-47,116-164,336-366).
+ * 768 bytes.  GPU order = order of node.GPUs.  Entries at index >= n_gpus are ignored. */
+typedef struct kgwe_node_image {
+    double   nvl_bw[KGWE_MAX_GPUS][KGWE_MAX_GPUS]; /* [i][j] = GPU i's NVLinkConnections[uuid_j].BandwidthGBps; 0 if no entry */
+    double   pcie_bw[KGWE_MAX_GPUS];               /* Topology.PCIeInfo.BandwidthGBps */
+    uint64_t free_bytes[KGWE_MAX_GPUS];            /* Memory.FreeBytes */
+    double   util[KGWE_MAX_GPUS];                  /* Utilization.GPUPercent */
+    uint8_t  nvl_present[KGWE_MAX_GPUS];           /* bit j: GPU i has a NVLinkConnections entry for GPU j */
+    uint8_t  nvl_active[KGWE_MAX_GPUS];            /* bit j: that entry has IsActive (subset of nvl_present) */
+    int8_t   numa[KGWE_MAX_GPUS];                  /* Topology.NUMANode, order-preserving (packer rank-compresses) */
+    uint8_t  pcie_switch[KGWE_MAX_GPUS];           /* PCIeInfo.SwitchID interned in first-appearance order, ""->"default" */
+    uint8_t  arch[KGWE_MAX_GPUS];                  /* KGWE_ARCH_* */
+    uint8_t  mig_free[KGWE_MIG_PROFILES];          /* per profile: # of !InUse instances on MIG-enabled GPUs (scheduler.go:606-622) */
+    uint8_t  n_gpus;                               /* len(node.GPUs), 0..8 */
+    uint8_t  healthy_mask;                         /* bit i: Health.Status == "Healthy" (scheduler.go:597) */
+    uint8_t  allocated_mask;                       /* ENGINE-OWNED: GPUs named by ledger entries on this node; ignored on upsert */
+    uint8_t  flags;                                /* bit0: record present (ENGINE-OWNED) */
+    uint8_t  pad0[2];
+    uint32_t n_allocs;                             /* ENGINE-OWNED: ledger entries (workloads) on this node (scheduler.go:561-566) */
+    uint32_t pad1;
+} kgwe_node_image;
+
+/* One pending workload: the fields of GPUWorkload.Requirements the path reads
+ * (src/scheduler/types.go:36-57,80-89).  32 bytes. */
+typedef struct kgwe_pod_req {
+    uint64_t wl_id;               /* host-interned GPUWorkload.UID (ledger key) */
+    int32_t  gpu_count;           /* Requirements.GPUCount, >= 0 */
+    int32_t  min_memory_gb;       /* Requirements.MinMemoryGB, 0..2^20 */
+    double   min_bandwidth_gbps;  /* EXTENSION E3 (field unused by the reference); 0 = off = reference behaviour */
+    uint8_t  topology_pref;       /* KGWE_TOPO_* */
+    uint8_t  arch;                /* KGWE_ARCH_ANY or the required architecture */
+    uint8_t  mig_profile;         /* KGWE_MIG_NONE, 1..10, or KGWE_MIG_UNKNOWN */
+    uint8_t  flags;               /* KGWE_POD_* */
+    int32_t  mig_count;           /* MIGRequirements.Count */
+} kgwe_pod_req;
+
+#define KGWE_POD_EXHAUSTIVE  0x01  /* EXTENSION E1: score all C(A,k) subsets instead of the greedy (NVLink modes) */
+
+/* Result flags */
+#define KGWE_F_ELIGIBLE   0x01   /* isNodeEligible passed (Filter) */
+#define KGWE_F_KEPT       0x02   /* eligible and TotalScore > 0 (scheduler.go:196) => in scoreNodes' result */
+#define KGWE_F_HINT       0x04   /* hint bonus applied */
+#define KGWE_F_FALLBACK   0x08   /* topology fallback arm taken (30 / 50 / 40) */
+#define KGWE_F_MINBW      0x10   /* filtered by E3 min-bandwidth */
+
+/* NodeScore for one (pod, node) evaluation (src/scheduler/types.go:295-319).  16 bytes.
+ * Scores are the reference's unclamped integers.  `order` is SelectedGPUs in the
+ * reference's order: GPU index at position p in bits [3p, 3p+3), count in bits [24,28). */
+typedef struct kgwe_node_score {
+    int32_t  total;        /* TotalScore */
+    int16_t  topology;     /* TopologyScore */
+    int16_t  resource;     /* ResourceScore */
+    int16_t  balance;      /* BalanceScore */
+    uint8_t  gpu_mask;     /* SelectedGPUs as a set */
+    uint8_t  flags;        /* KGWE_F_* */
+    uint32_t order;        /* SelectedGPUs as an ordered list */
+} kgwe_node_score;
+
+/* A ranked placement / a SchedulingDecision (src/scheduler/types.go:253-277).  32 bytes. */
+typedef struct kgwe_placement {
+    uint32_t node_idx;           /* global node index, KGWE_NO_NODE when there is none */
+    int32_t  total;
+    int16_t  topology;
+    int16_t  resource;
+    int16_t  balance;
+    uint8_t  gpu_mask;
+    uint8_t  flags;
+    uint32_t order;
+    uint32_t reserved;
+    double   est_bandwidth_gbps; /* EstimatedBandwidth, scheduler.go:656-692 */
+} kgwe_placement;
+
+typedef struct kgwe_stats {
+    uint64_t evaluations;        /* (pod,node) pairs scored since create */
+    uint64_t candidates;         /* GPU subsets scored (counting rule: SURVEY.md 8d) */
+    uint64_t scheduled;          /* SchedulerMetrics.TotalScheduled */
+    uint64_t failed;             /* SchedulerMetrics.TotalFailed */
+    uint64_t topology_optimal;   /* TopologyOptimalPlacements (TopologyScore >= 80, scheduler.go:154) */
+    uint64_t kernel_launches;    /* engine kernels launched since create */
+    uint64_t h2d_bytes;
+    uint64_t d2h_bytes;
+    double   last_call_gpu_ms;   /* device time of the last scoring call (CUDA events) */
+    uint32_t n_nodes;            /* records in use (highest present local index + 1) */
+    uint32_t n_allocations;      /* ledger size */
+} kgwe_stats;
+
+typedef struct kgwe_engine kgwe_engine;
+
+/* Replaces NewTopologyAwareScheduler's state set-up (scheduler.go:97-111): device
+ * image, ledger, staging.  Fails with KGWE_ERR_NO_DEVICE when CUDA is unusable. */
+int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out);
+int kgwe_engine_destroy(kgwe_engine* e);
+
+/* Fill *cfg with DefaultSchedulerConfig() values (src/scheduler/types.go:379-392). */
+void kgwe_config_default(kgwe_config* cfg);
+
+/* Topology snapshot ingestion.  Replaces the full rebuild per informer event in
+ * DiscoveryService.RefreshTopology / watchNodes (src/discovery/discovery.go:290-319,
+ * 589-600) by one record update; `local_idx` is the index inside this engine's shard.
+ * Ledger-owned fields of *img are ignored and re-derived. */
+int kgwe_node_upsert(kgwe_engine* e, uint32_t local_idx, const kgwe_node_image* img);
+int kgwe_nodes_upsert(kgwe_engine* e, uint32_t first_local_idx, uint32_t count, const kgwe_node_image* imgs);
+int kgwe_node_remove(kgwe_engine* e, uint32_t local_idx);
+
+/* Ledger.  Replaces recordAllocation (scheduler.go:695-707; same wl_id overwrites) and
+ * ReleaseAllocation (scheduler.go:710-727; unknown id -> KGWE_ERR_NOT_FOUND). */
+int kgwe_alloc_commit(kgwe_engine* e, uint64_t wl_id, uint32_t local_idx, uint8_t gpu_mask);
+int kgwe_alloc_release(kgwe_engine* e, uint64_t wl_id);
+
+/* Stateless Filter + Prioritize for P workloads over every node of the image.
+ * Replaces scoreNodes (scheduler.go:182-203) and everything it calls, plus the
+ * descending sort at scheduler.go:144-146 in canonical order.
+ *   hint_bitmap  nullable; P rows of ceil(n_nodes/8) bytes; bit n of row p set when node n
+ *                is in pod p's PlacementHint.PreferredNodes (scheduler.go:270-279)
+ *   out_scores   nullable; P x n_nodes records, row-major by pod
+ *   topk         0..KGWE_MAX_TOPK; out_topk gets P x topk placements, best first,
+ *                unused slots have node_idx == KGWE_NO_NODE
+ * Host pointers; copies are done by the engine inside the call. */
+int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods,
+                     const uint8_t* hint_bitmap, kgwe_node_score* out_scores,
+                     uint32_t topk, kgwe_placement* out_topk);
+
+/* Same computation with every buffer already in device memory of the engine's GPU,
+ * enqueued on `cuda_stream` (a cudaStream_t; NULL = the engine's own stream) without a
+ * host synchronisation.  Used for device-resident pipelines (node-sharded multi-GPU
+ * merge over NCCL) and for kernel-only timing. */
+int kgwe_score_batch_device(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods,
+                            const uint8_t* d_hint_bitmap, kgwe_node_score* d_out_scores,
+                            uint32_t topk, kgwe_placement* d_out_topk, void* cuda_stream);
+
+/* Merge R ranked lists per pod (layout [r][p][topk], device memory) into one
+ * [p][topk] list in canonical order (score desc, node index asc).  This is the merge
+ * every rank runs after the all-gather of local top-k lists. */
+int kgwe_topk_merge_device(kgwe_engine* e, const kgwe_placement* d_lists, uint32_t n_lists,
+                           uint32_t n_pods, uint32_t topk, kgwe_placement* d_out, void* cuda_stream);
+
+/* Stateful Schedule for a queue of workloads, in order: score, pick the best node
+ * (lowest index on ties), EstimatedBandwidth, commit to the ledger, next workload.
+ * Replaces Schedule + tryScheduleOnNode + recordAllocation (scheduler.go:114-179,
+ * 625-653, 695-707) called once per workload.  out[i].node_idx == KGWE_NO_NODE means
+ * "no eligible nodes found for workload" (scheduler.go:140). */
+int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods,
+                        const uint8_t* hint_bitmap, kgwe_placement* out);
+
+/* Read one record back (device -> host) in ABI layout, ledger fields included. */
+int kgwe_node_read(kgwe_engine* e, uint32_t local_idx, kgwe_node_image* out);
+
+int kgwe_get_stats(kgwe_engine* e, kgwe_stats* out);
+const char* kgwe_last_error(kgwe_engine* e);
+const char* kgwe_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KGWE_ENGINE_H */

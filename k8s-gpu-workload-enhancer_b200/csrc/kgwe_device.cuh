@@ -1,0 +1,343 @@
+// kgwe_device.cuh — device-side record layout and the per-(pod,node) evaluation shared by
+// every kernel of the engine (stateless batch, stateful queue, finalisation).
+//
+// Execution shape: one (pod,node) evaluation is done by a group of 8 lanes, 4 groups per
+// warp.  Lane j of a group owns GPU j of the node: it is the START GPU of one greedy
+// NVLink chain (reference src/scheduler/scheduler.go:389), so the 8 chains of
+// findBestNVLinkGroup run side by side and a 3-step segmented shuffle picks the winner
+// with the reference's strict-greater / first-start rule.  Everything else in an
+// evaluation is group-uniform integer work.
+//
+// Arithmetic: FP64 with explicit round-to-nearest intrinsics (__dadd_rn, __dmul_rn,
+// __ddiv_rn) and truncating conversion, compiled with --fmad=false, because Go on amd64
+// never contracts a*b+c and the integer scores must match bit for bit.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/kgwe_engine.h"
+
+namespace kgwe {
+
+// Device image of one node: same 768 bytes as kgwe_node_image, with the NVLink matrix
+// stored the way the greedy reads it.  bw_in[m] is the 64-byte row "bandwidth of GPU c's
+// link to GPU m, for c = 0..7" (what a candidate c adds when m has joined the group);
+// inside the row the 16-byte chunk holding c = 2q, 2q+1 sits at chunk position
+// q ^ (m >> 1), so the 8 lanes of a group, each reading a different row m at the same
+// logical chunk q, hit 8 distinct 4-bank groups of shared memory (conflict-free LDS.128).
+struct __align__(16) DevNode {
+    double   bw_in[8][8];
+    double   pcie_bw[8];
+    uint64_t free_bytes[8];
+    double   util[8];
+    uint8_t  act_in[8];      // act_in[m] bit c: GPU c has an ACTIVE link entry to GPU m
+    uint8_t  present[8];     // present[i] bit j: GPU i has a link entry for GPU j (active or not)
+    int8_t   numa[8];
+    uint8_t  pcie_switch[8];
+    uint8_t  arch[8];
+    uint8_t  mig_free[KGWE_MIG_PROFILES];
+    uint8_t  n_gpus, healthy_mask, allocated_mask, flags;
+    uint8_t  pad0[2];
+    uint32_t n_allocs;
+    uint32_t pad1;
+};
+static_assert(sizeof(DevNode) == 768, "device record must stay 768 bytes");
+static_assert(sizeof(kgwe_node_image) == 768, "ABI record must stay 768 bytes");
+static_assert(sizeof(kgwe_pod_req) == 32 && sizeof(kgwe_node_score) == 16 && sizeof(kgwe_placement) == 32, "ABI sizes");
+
+__host__ __device__ inline int bw_slot(int m, int c) { return (((c >> 1) ^ (m >> 1)) << 1) | (c & 1); }
+
+struct Params {          // kgwe_config, device copy
+    int32_t wt, wr, wb, bonus;
+    double  norm;
+    uint32_t node_base;
+};
+
+// Pod-independent facts about one node, recomputed only when its ledger fields change.
+struct NodeCtx {
+    uint32_t avail;        // healthy & ~allocated & (n_gpus bits)        scheduler.go:581-603
+    int      A;
+    uint64_t colact;       // byte m = act_in[m]
+    uint64_t sum_free;     // sum of FreeBytes over available GPUs          scheduler.go:528-531
+    int      util_bonus;   // 25 / 10 / 0 from the ordered mean of GPUPercent scheduler.go:540-550
+    int      balance;      // calculateBalanceScore                          scheduler.go:556-578
+    uint64_t arch8;        // arch[0..7]
+    uint64_t numa_pick, pcie_pick;    // byte k-1: first group (ascending key) with >= k members, else 0
+    uint32_t numa_order, pcie_order;  // available GPUs in (key asc, index asc) order, 3 bits each
+    bool     valid;
+};
+
+struct EvalOut {
+    int32_t  total, topo, res, bal;
+    uint32_t mask, order, flags;   // order: packed list + count in bits 24..27
+    uint32_t candidates;
+};
+
+__device__ __forceinline__ uint64_t ld_u64(const void* p) { return *reinterpret_cast<const uint64_t*>(p); }
+
+// Groups of available GPUs by an 8-bit key, visited in ascending key (canonical order of
+// scoreNUMATopology / scorePCIeTopology, scheduler.go:438-513).
+__device__ inline void group_tables(uint64_t keys8, bool is_signed, uint32_t avail, uint64_t& pick, uint32_t& order) {
+    pick = 0; order = 0;
+    uint32_t remaining = avail; int pos = 0;
+    while (remaining) {
+        int minkey = 1 << 30;
+        for (int g = 0; g < 8; ++g)
+            if (remaining >> g & 1) {
+                int kb = (int)((keys8 >> (8 * g)) & 0xff);
+                int key = is_signed ? (int)(int8_t)kb : kb;
+                minkey = key < minkey ? key : minkey;
+            }
+        uint32_t grp = 0;
+        for (int g = 0; g < 8; ++g)
+            if (remaining >> g & 1) {
+                int kb = (int)((keys8 >> (8 * g)) & 0xff);
+                int key = is_signed ? (int)(int8_t)kb : kb;
+                if (key == minkey) { grp |= 1u << g; order |= (uint32_t)g << (3 * pos); ++pos; }
+            }
+        int sz = __popc(grp);
+        for (int k = 1; k <= sz; ++k)
+            if (((pick >> (8 * (k - 1))) & 0xff) == 0) pick |= (uint64_t)grp << (8 * (k - 1));
+        remaining &= ~grp;
+    }
+}
+
+__device__ inline void node_ctx_init(NodeCtx& c, const DevNode* rec, bool in_range) {
+    c.valid = in_range && (rec->flags & 1);
+    uint32_t ng = c.valid ? rec->n_gpus : 0;
+    ng = ng > 8 ? 8 : ng;
+    uint32_t avail = c.valid ? ((uint32_t)rec->healthy_mask & ~(uint32_t)rec->allocated_mask & ((1u << ng) - 1u)) : 0;
+    c.avail = avail; c.A = __popc(avail);
+    c.colact = c.valid ? ld_u64(rec->act_in) : 0;
+    c.arch8 = c.valid ? ld_u64(rec->arch) : 0;
+    uint64_t sum = 0; double usum = 0.0;
+    for (int g = 0; g < 8; ++g)
+        if (avail >> g & 1) { sum += rec->free_bytes[g]; usum = __dadd_rn(usum, rec->util[g]); }
+    c.sum_free = sum;
+    c.util_bonus = 0;
+    if (c.A > 0) {
+        double avg = __ddiv_rn(usum, (double)c.A);
+        c.util_bonus = avg < 30.0 ? 25 : (avg < 60.0 ? 10 : 0);
+    }
+    c.balance = 0;
+    if (ng > 0) {
+        double usage = __ddiv_rn((double)rec->n_allocs, (double)ng);
+        int s = __double2int_rz(__dmul_rn(100.0, __dsub_rn(1.0, usage)));
+        c.balance = s > 0 ? s : 0;
+    }
+    if (c.valid) {
+        group_tables(ld_u64(rec->numa), true, avail, c.numa_pick, c.numa_order);
+        group_tables(ld_u64(rec->pcie_switch), false, avail, c.pcie_pick, c.pcie_order);
+    } else { c.numa_pick = c.pcie_pick = 0; c.numa_order = c.pcie_order = 0; }
+}
+
+// First k set bits of `m` in index order -> (mask, packed list).
+__device__ __forceinline__ void take_first_k(uint32_t m, int k, uint32_t& sel, uint32_t& order) {
+    sel = 0; order = 0;
+    for (int i = 0; i < k && m; ++i) {
+        int b = __ffs(m) - 1;
+        sel |= 1u << b; order |= (uint32_t)b << (3 * i);
+        m &= m - 1;
+    }
+}
+__device__ __forceinline__ uint32_t mask_of_order(uint32_t order, int k) {
+    uint32_t sel = 0;
+    for (int i = 0; i < k; ++i) sel |= 1u << ((order >> (3 * i)) & 7);
+    return sel;
+}
+
+// estimateBandwidth, scheduler.go:656-692: mean over pairs i<j (SelectedGPUs order) of GPU
+// i's link entry to GPU j when one exists (IsActive is NOT checked there), else GPU i's
+// PCIe bandwidth.  Ordered FP64 sum.
+__device__ inline double est_bandwidth(const DevNode* rec, uint32_t order, int n) {
+    if (n <= 1) return 0.0;
+    double total = 0.0; int pairs = 0;
+    for (int i = 0; i < n; ++i) {
+        int a = (order >> (3 * i)) & 7;
+        for (int j = i + 1; j < n; ++j) {
+            int b = (order >> (3 * j)) & 7;
+            double x = (rec->present[a] >> b & 1) ? rec->bw_in[b][bw_slot(b, a)] : rec->pcie_bw[a];
+            total = __dadd_rn(total, x); ++pairs;
+        }
+    }
+    return pairs ? __ddiv_rn(total, (double)pairs) : 0.0;
+}
+
+// One greedy chain of findBestNVLinkGroup (scheduler.go:389-426) from start GPU `s`.
+// agg[c] is carried across steps: the reference recomputes the candidate's sum over the
+// members in join order from 0.0 at every step, which is exactly this running prefix sum
+// (same operands, same order), so the results are bit-identical.
+__device__ __forceinline__ void greedy_chain(const DevNode* rec, const NodeCtx& nc, int s, int k,
+                                             bool& ok, double& total, uint32_t& order, uint32_t& members) {
+    ok = (nc.avail >> s) & 1;
+    total = 0.0; order = (uint32_t)s; members = 1u << s;
+    if (!ok) return;
+    double agg[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) agg[c] = 0.0;
+    uint32_t conn = nc.avail & ~members;
+    int m = s;
+    for (int step = 1; step < k; ++step) {
+        conn &= (uint32_t)(nc.colact >> (8 * m)) & 0xffu;
+        const double2* row = reinterpret_cast<const double2*>(rec->bw_in[m]);
+        int f = m >> 1;
+        double best = 0.0; int bc = -1;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            double2 v = row[q ^ f];
+            agg[2 * q] = __dadd_rn(agg[2 * q], v.x);
+            agg[2 * q + 1] = __dadd_rn(agg[2 * q + 1], v.y);
+            if ((conn >> (2 * q) & 1) && agg[2 * q] > best) { best = agg[2 * q]; bc = 2 * q; }
+            if ((conn >> (2 * q + 1) & 1) && agg[2 * q + 1] > best) { best = agg[2 * q + 1]; bc = 2 * q + 1; }
+        }
+        if (bc < 0) { ok = false; return; }
+        members |= 1u << bc; conn &= ~(1u << bc);
+        order |= (uint32_t)bc << (3 * step);
+        total = __dadd_rn(total, best);
+        m = bc;
+    }
+}
+
+// EXTENSION E1: lane j scores the subsets whose mask value is congruent to j mod 8.
+__device__ inline void exhaustive_lane(const DevNode* rec, const NodeCtx& nc, int j, int k, double& best, uint32_t& bestmask) {
+    best = 0.0; bestmask = 0;
+    for (uint32_t sub = (uint32_t)j; sub < 256u; sub += 8u) {
+        if ((sub & ~nc.avail) || __popc(sub) != k) continue;
+        bool ok = true;
+        for (int m = 0; m < 8; ++m)
+            if ((sub >> m & 1) && (sub & ~(1u << m) & ~(uint32_t)((nc.colact >> (8 * m)) & 0xff))) ok = false;
+        if (!ok) continue;
+        double total = 0.0; bool first = true;
+        for (int jj = 0; jj < 8; ++jj) {
+            if (!(sub >> jj & 1)) continue;
+            double agg = 0.0;
+            for (int i = 0; i < jj; ++i)
+                if (sub >> i & 1) agg = __dadd_rn(agg, rec->bw_in[i][bw_slot(i, jj)]);
+            if (!first) total = __dadd_rn(total, agg);
+            first = false;
+        }
+        if (total > best) { best = total; bestmask = sub; }
+    }
+}
+
+__device__ __forceinline__ int nvlink_score(double total, int k, double norm) {   // scheduler.go:368-370
+    double maxbw = __dmul_rn(norm, (double)(k * (k - 1) / 2));
+    double ratio = __ddiv_rn(total, maxbw);
+    return __double2int_rz(__dadd_rn(50.0, __dmul_rn(50.0, ratio)));
+}
+
+// isNodeEligible + scoreNode for one (pod,node), executed by the 8 lanes of a group
+// (lane j = `lane & 7`); the result is identical on all 8 lanes.  All 32 lanes of the warp
+// must call it together (segmented shuffles inside).
+__device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, const kgwe_pod_req& pod, const Params& P,
+                                         bool hinted, int lane, EvalOut& o) {
+    const int j = lane & 7;
+    // k > 8 can never be eligible (A <= 8); clamp so no loop below depends on a huge count
+    const int k = pod.gpu_count > 9 ? 9 : pod.gpu_count;
+    o.total = o.topo = o.res = o.bal = 0; o.mask = o.order = o.flags = 0; o.candidates = 1;
+    // --- Filter: isNodeEligible, scheduler.go:206-241 ---
+    bool eligible = nc.valid && k >= 0 && nc.A >= k;
+    if (pod.arch != KGWE_ARCH_ANY) {
+        uint32_t match = 0;
+        for (int g = 0; g < 8; ++g) if ((uint8_t)(nc.arch8 >> (8 * g)) == pod.arch) match |= 1u << g;
+        eligible = eligible && (match & nc.avail);
+    }
+    if (pod.mig_profile != KGWE_MIG_NONE) {
+        int have = (pod.mig_profile >= 1 && pod.mig_profile <= KGWE_MIG_PROFILES && nc.valid) ? rec->mig_free[pod.mig_profile - 1] : 0;
+        eligible = eligible && have >= pod.mig_count;
+    }
+    // --- Prioritize: calculateTopologyScore, scheduler.go:303-333 ---
+    int topo = 0; uint32_t sel = 0, order = 0; int nsel = 0; bool fallback = false;
+    const bool nvl = pod.topology_pref == KGWE_TOPO_NVLINK_OPTIMAL || pod.topology_pref == KGWE_TOPO_NVLINK_REQUIRED;
+    if (k <= 1) {
+        if (nc.A > 0) { topo = 100; take_first_k(nc.avail, 1, sel, order); nsel = 1; }
+    } else if (nvl) {
+        // scoreNVLinkTopology, scheduler.go:336-373 (warp-uniform branch: one pod per warp pass)
+        uint64_t key; uint32_t pay;
+        const bool run = eligible;       // ineligible groups idle through the shuffles
+        if (!(pod.flags & KGWE_POD_EXHAUSTIVE)) {
+            bool ok = false; double total = 0.0; uint32_t ord = 0, mem = 0;
+            if (run) greedy_chain(rec, nc, j, k, ok, total, ord, mem);
+            key = (ok && total > 0.0) ? (uint64_t)__double_as_longlong(total) : 0ull;
+            pay = ord;
+            o.candidates = (uint32_t)nc.A;
+        } else {
+            double best = 0.0; uint32_t bm = 0;
+            if (run) exhaustive_lane(rec, nc, j, k, best, bm);
+            key = best > 0.0 ? (uint64_t)__double_as_longlong(best) : 0ull;
+            pay = bm;
+            uint32_t c = 1; for (int i = 1; i <= k; ++i) c = c * (uint32_t)(nc.A - k + i) / (uint32_t)i;
+            o.candidates = nc.A >= k ? c : 0;
+        }
+        // winner over the 8 lanes: strictly largest total, then lowest start index / lowest mask
+        // (greedy: first start in available order, scheduler.go:428-431)
+        uint32_t tie = (pod.flags & KGWE_POD_EXHAUSTIVE) ? pay : (uint32_t)j;
+#pragma unroll
+        for (int off = 4; off >= 1; off >>= 1) {
+            uint64_t okey = __shfl_xor_sync(0xffffffffu, key, off, 8);
+            uint32_t otie = __shfl_xor_sync(0xffffffffu, tie, off, 8);
+            uint32_t opay = __shfl_xor_sync(0xffffffffu, pay, off, 8);
+            if (okey > key || (okey == key && otie < tie)) { key = okey; tie = otie; pay = opay; }
+        }
+        if (key == 0ull) {               // no fully connected group: scheduler.go:358-365
+            topo = 30; fallback = true; take_first_k(nc.avail, k, sel, order); nsel = k;
+        } else {
+            topo = nvlink_score(__longlong_as_double((long long)key), k, P.norm);
+            if (pod.flags & KGWE_POD_EXHAUSTIVE) take_first_k(pay, k, sel, order);
+            else { order = pay; sel = mask_of_order(order, k); }
+            nsel = k;
+        }
+    } else if (pod.topology_pref == KGWE_TOPO_SAME_NUMA || pod.topology_pref == KGWE_TOPO_SAME_PCIE_SWITCH) {
+        const bool numa = pod.topology_pref == KGWE_TOPO_SAME_NUMA;
+        uint64_t pick = numa ? nc.numa_pick : nc.pcie_pick;
+        uint32_t gorder = numa ? nc.numa_order : nc.pcie_order;
+        uint32_t grp = k <= 8 ? (uint32_t)((pick >> (8 * (k - 1))) & 0xff) : 0;
+        if (grp) { topo = numa ? 90 : 80; take_first_k(grp, k, sel, order); nsel = k; }
+        else if (nc.A >= k) {
+            topo = numa ? 50 : 40; fallback = true;
+            order = gorder & ((k >= 8) ? 0xffffffu : ((1u << (3 * k)) - 1u));
+            sel = mask_of_order(order, k); nsel = k;
+        }
+    } else {
+        topo = 50;
+        int n = k < nc.A ? k : nc.A;
+        take_first_k(nc.avail, n, sel, order); nsel = n;
+    }
+    if (!eligible) { o.candidates = 1; return; }
+    // --- calculateResourceScore, scheduler.go:516-553 ---
+    int res = 0;
+    if (nc.A > 0) {
+        uint64_t required = (uint64_t)(uint32_t)pod.min_memory_gb * 1073741824ull * (uint64_t)(uint32_t)k;
+        res = 50 + (nc.sum_free >= required * 2 ? 25 : (nc.sum_free >= required ? 10 : 0)) + nc.util_bonus;
+        res = res > 100 ? 100 : res;
+    }
+    // --- weighted total, scheduler.go:282-286 ---
+    int total = (topo * P.wt + res * P.wr + nc.balance * P.wb) / 100;
+    uint32_t flags = KGWE_F_ELIGIBLE;
+    if (hinted) { total += P.bonus; flags |= KGWE_F_HINT; }
+    bool kept = total > 0;                                   // scheduler.go:196
+    if (fallback) flags |= KGWE_F_FALLBACK;
+    // EXTENSION E3: minimum inter-GPU bandwidth (field declared at types.go:44, unused by the reference)
+    if (kept && pod.min_bandwidth_gbps > 0.0 && k >= 2 && est_bandwidth(rec, order, nsel) < pod.min_bandwidth_gbps) {
+        kept = false; flags |= KGWE_F_MINBW;
+    }
+    if (kept) flags |= KGWE_F_KEPT;
+    o.total = total; o.topo = topo; o.res = res; o.bal = nc.balance;
+    o.mask = sel; o.order = order | ((uint32_t)nsel << 24); o.flags = flags;
+}
+
+__device__ __forceinline__ kgwe_node_score to_record(const EvalOut& o) {
+    kgwe_node_score r;
+    r.total = o.total; r.topology = (int16_t)o.topo; r.resource = (int16_t)o.res; r.balance = (int16_t)o.bal;
+    r.gpu_mask = (uint8_t)o.mask; r.flags = (uint8_t)o.flags; r.order = o.order;
+    return r;
+}
+
+// Ranking key: TotalScore descending, then node index ascending (canonical tie-break).
+// Only kept evaluations rank (total > 0), so 0 means "none".
+__device__ __forceinline__ uint64_t rank_key(int32_t total, uint32_t global_node) {
+    return ((uint64_t)(uint32_t)total << 32) | (uint64_t)(0xFFFFFFFFu - global_node);
+}
+__device__ __forceinline__ uint32_t key_node(uint64_t key) { return 0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFu); }
+
+}  // namespace kgwe

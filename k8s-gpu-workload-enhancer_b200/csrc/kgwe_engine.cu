@@ -1,0 +1,604 @@
+// kgwe_engine.cu — host side of the engine and the C ABI of include/kgwe_engine.h.
+//
+// State (replaces TopologyAwareScheduler's fields, reference src/scheduler/scheduler.go:16-39):
+//   * cluster image: DevNode[max_nodes] in HBM + a pinned host mirror; upserts touch the mirror
+//     and a dirty list, and are flushed as coalesced H2D copies before the next scoring call
+//     (incremental, instead of discovery.go:290-319's full rebuild);
+//   * ledger: wl_id -> (node, gpu mask) on the host; its per-node projection
+//     (allocated_mask, n_allocs) lives inside the node records, which is all the kernels need
+//     (replaces the three full ledger scans per (pod,node) at scheduler.go:587-593, 562-566);
+//   * scratch: arg-max key table, pod/hint/top-k staging, an optional score-matrix chunk.
+// No CPU fallback: every scoring entry point launches the CUDA kernels or fails.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "kgwe_kernels.cuh"
+
+using namespace kgwe;
+
+namespace {
+
+struct LedgerEntry { uint32_t node; uint8_t mask; };
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr; size_t cap = 0;
+    cudaError_t ensure(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        size_t want = std::max(n, cap * 2);
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+template <typename T>
+struct PinBuf {
+    T* p = nullptr; size_t cap = 0;
+    cudaError_t ensure(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        cudaError_t e = cudaMallocHost(&p, n * sizeof(T));
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+constexpr size_t kScoreScratchBytes = 1ull << 30;   // internal score-matrix chunk (top-k > 1 without out_scores, host copies)
+
+}  // namespace
+
+struct kgwe_engine {
+    std::mutex mu;
+    kgwe_config cfg;
+    Params params;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int sm_count = 148;
+    int sched_blocks_per_sm = 1;
+
+    DevNode* d_nodes = nullptr;       // cluster image in HBM
+    DevNode* h_nodes = nullptr;       // pinned mirror (device layout)
+    std::vector<uint8_t> dirty_flag;
+    std::vector<uint32_t> dirty;
+    uint32_t n_nodes = 0;             // high-water mark of present records
+    uint32_t n_present = 0;
+    std::unordered_map<uint64_t, LedgerEntry> ledger;
+
+    DevBuf<kgwe_pod_req> d_pods;
+    DevBuf<uint8_t> d_hint;
+    DevBuf<unsigned long long> d_best;      // arg-max keys, kept all-zero between calls
+    DevBuf<kgwe_placement> d_topk;
+    DevBuf<kgwe_node_score> d_scores;
+    unsigned long long* d_counters = nullptr;   // [0] evaluations (K3), [1] candidates
+    PinBuf<kgwe_pod_req> h_pods;
+    PinBuf<kgwe_placement> h_topk;
+    PinBuf<uint8_t> h_hint;
+    unsigned long long* h_counters = nullptr;
+
+    kgwe_stats stats;
+    std::string err;
+};
+
+namespace {
+
+int fail(kgwe_engine* e, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    if (e) e->err = buf;
+    return code;
+}
+#define CU(e, call) do { cudaError_t _c = (call); if (_c != cudaSuccess) return fail(e, KGWE_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(_c)); } while (0)
+
+// ABI record -> device record: transpose + chunk-swizzle the NVLink matrix (kgwe_device.cuh),
+// transpose the active masks, normalise masks to n_gpus.
+int to_device_record(kgwe_engine* e, const kgwe_node_image& in, DevNode& out) {
+    if (in.n_gpus > KGWE_MAX_GPUS) return fail(e, KGWE_ERR_INVALID_ARG, "n_gpus %u > %d", in.n_gpus, KGWE_MAX_GPUS);
+    const int ng = in.n_gpus;
+    const uint8_t gm = (uint8_t)((1u << ng) - 1u);
+    memset(&out, 0, sizeof out);
+    for (int i = 0; i < ng; ++i) {
+        const uint8_t present = in.nvl_present[i] & gm & (uint8_t)~(1u << i);
+        const uint8_t active = in.nvl_active[i] & present;
+        out.present[i] = present;
+        for (int j = 0; j < ng; ++j) {
+            double bw = (present >> j & 1) ? in.nvl_bw[i][j] : 0.0;
+            if (!(bw >= 0.0) || !(bw <= KGWE_MAX_BW_GBPS)) return fail(e, KGWE_ERR_INVALID_ARG, "nvl_bw[%d][%d]=%g outside [0,%g]", i, j, bw, KGWE_MAX_BW_GBPS);
+            if (bw == 0.0) bw = 0.0;                              // -0.0 -> +0.0
+            out.bw_in[j][bw_slot(j, i)] = bw;                     // i's link to j
+            if (active >> j & 1) out.act_in[j] |= (uint8_t)(1u << i);
+        }
+        const double pb = in.pcie_bw[i], ut = in.util[i];
+        if (!(pb >= 0.0) || !(pb <= KGWE_MAX_BW_GBPS)) return fail(e, KGWE_ERR_INVALID_ARG, "pcie_bw[%d]=%g outside [0,%g]", i, pb, KGWE_MAX_BW_GBPS);
+        if (!std::isfinite(ut)) return fail(e, KGWE_ERR_INVALID_ARG, "util[%d] is not finite", i);
+        out.pcie_bw[i] = pb; out.util[i] = ut; out.free_bytes[i] = in.free_bytes[i];
+        out.numa[i] = in.numa[i]; out.pcie_switch[i] = in.pcie_switch[i]; out.arch[i] = in.arch[i];
+    }
+    memcpy(out.mig_free, in.mig_free, sizeof out.mig_free);
+    out.n_gpus = (uint8_t)ng; out.healthy_mask = in.healthy_mask & gm; out.flags = 1;
+    return KGWE_OK;
+}
+
+void to_abi_record(const DevNode& in, kgwe_node_image& out) {
+    memset(&out, 0, sizeof out);
+    const int ng = in.n_gpus;
+    for (int i = 0; i < ng; ++i) {
+        out.nvl_present[i] = in.present[i];
+        for (int j = 0; j < ng; ++j) {
+            out.nvl_bw[i][j] = in.bw_in[j][bw_slot(j, i)];
+            if (in.act_in[j] >> i & 1) out.nvl_active[i] |= (uint8_t)(1u << j);
+        }
+        out.pcie_bw[i] = in.pcie_bw[i]; out.util[i] = in.util[i]; out.free_bytes[i] = in.free_bytes[i];
+        out.numa[i] = in.numa[i]; out.pcie_switch[i] = in.pcie_switch[i]; out.arch[i] = in.arch[i];
+    }
+    memcpy(out.mig_free, in.mig_free, sizeof out.mig_free);
+    out.n_gpus = in.n_gpus; out.healthy_mask = in.healthy_mask; out.allocated_mask = in.allocated_mask;
+    out.flags = in.flags; out.n_allocs = in.n_allocs;
+}
+
+void mark_dirty(kgwe_engine* e, uint32_t idx) {
+    if (!e->dirty_flag[idx]) { e->dirty_flag[idx] = 1; e->dirty.push_back(idx); }
+}
+
+// Coalesce dirty records into runs and copy them to the device image.
+int flush_dirty(kgwe_engine* e, cudaStream_t s) {
+    if (e->dirty.empty()) return KGWE_OK;
+    std::sort(e->dirty.begin(), e->dirty.end());
+    size_t i = 0;
+    while (i < e->dirty.size()) {
+        size_t j = i + 1;
+        while (j < e->dirty.size() && e->dirty[j] == e->dirty[j - 1] + 1) ++j;
+        const uint32_t first = e->dirty[i], count = (uint32_t)(j - i);
+        CU(e, cudaMemcpyAsync(e->d_nodes + first, e->h_nodes + first, (size_t)count * sizeof(DevNode), cudaMemcpyHostToDevice, s));
+        e->stats.h2d_bytes += (uint64_t)count * sizeof(DevNode);
+        i = j;
+    }
+    for (uint32_t idx : e->dirty) e->dirty_flag[idx] = 0;
+    e->dirty.clear();
+    // the copies read the pinned mirror; finish them before any later upsert can touch it
+    CU(e, cudaStreamSynchronize(s));
+    return KGWE_OK;
+}
+
+int validate_pods(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n) {
+    for (uint32_t i = 0; i < n; ++i) {
+        if (pods[i].gpu_count < 0) return fail(e, KGWE_ERR_INVALID_ARG, "pod %u: gpu_count %d < 0", i, pods[i].gpu_count);
+        if (pods[i].min_memory_gb < 0 || pods[i].min_memory_gb > (1 << 20)) return fail(e, KGWE_ERR_INVALID_ARG, "pod %u: min_memory_gb %d outside [0, 2^20]", i, pods[i].min_memory_gb);
+        if (!(pods[i].min_bandwidth_gbps >= 0.0)) return fail(e, KGWE_ERR_INVALID_ARG, "pod %u: min_bandwidth_gbps must be >= 0", i);
+    }
+    return KGWE_OK;
+}
+
+uint32_t hint_row_bytes(const kgwe_engine* e) { return (e->n_nodes + 7) / 8; }
+
+size_t score_smem_bytes(uint32_t pods_per_chunk) { return (size_t)TILE_NODES * sizeof(DevNode) + (size_t)pods_per_chunk * 8 + 16; }
+
+// Launch K1 (+K1b / K2) for n_pods pods whose descriptors, hint rows and outputs are in
+// device memory.  d_scores may be null unless topk > 1.
+int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const uint8_t* d_hint,
+                 kgwe_node_score* d_scores, uint32_t topk, kgwe_placement* d_topk, cudaStream_t s) {
+    if (n_pods == 0 || e->n_nodes == 0) return KGWE_OK;
+    const uint32_t n_tiles = (e->n_nodes + TILE_NODES - 1) / TILE_NODES;
+    // pod chunks: enough CTAs to fill the GPU a few times over, table size bounded
+    uint32_t want_ctas = (uint32_t)e->sm_count * 2u * 4u;
+    uint32_t chunks = std::max(1u, (want_ctas + n_tiles - 1) / n_tiles);
+    chunks = std::min(chunks, n_pods);
+    uint32_t ppc = (n_pods + chunks - 1) / chunks;
+    if (ppc > MAX_PODS_PER_CHUNK) ppc = MAX_PODS_PER_CHUNK;
+    chunks = (n_pods + ppc - 1) / ppc;
+    if (chunks > 65535u) return fail(e, KGWE_ERR_TOO_LARGE, "too many pods in one launch (%u)", n_pods);
+    unsigned long long* best = nullptr;
+    if (topk == 1) {
+        const size_t had = e->d_best.cap;
+        CU(e, e->d_best.ensure(n_pods));
+        if (e->d_best.cap != had) CU(e, cudaMemsetAsync(e->d_best.p, 0, e->d_best.cap * sizeof(unsigned long long), s));
+        best = e->d_best.p;
+    }
+    dim3 grid(n_tiles, chunks);
+    score_kernel<<<grid, SCORE_THREADS, score_smem_bytes(ppc), s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e),
+                                                                   d_scores, best, e->params, e->d_counters);
+    CU(e, cudaGetLastError());
+    e->stats.kernel_launches++;
+    if (topk == 1) {
+        const uint32_t threads = 256, pods_per_block = threads / 8;
+        finalize_top1_kernel<<<(n_pods + pods_per_block - 1) / pods_per_block, threads, 0, s>>>(
+            e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), best, d_topk, 1, e->params);
+        CU(e, cudaGetLastError());
+        e->stats.kernel_launches++;
+    } else if (topk > 1) {
+        topk_select_kernel<<<n_pods, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_scores, topk, d_topk, e->params);
+        CU(e, cudaGetLastError());
+        e->stats.kernel_launches++;
+    }
+    e->stats.evaluations += (uint64_t)n_pods * e->n_present;
+    return KGWE_OK;
+}
+
+int pull_counters(kgwe_engine* e, cudaStream_t s) {
+    CU(e, cudaMemcpyAsync(e->h_counters, e->d_counters, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    CU(e, cudaMemsetAsync(e->d_counters, 0, 2 * sizeof(unsigned long long), s));
+    return KGWE_OK;
+}
+
+int ledger_apply(kgwe_engine* e, uint64_t wl_id, uint32_t idx, uint8_t mask, bool touch_device) {
+    // recordAllocation: the same UID overwrites its previous entry (scheduler.go:699)
+    auto it = e->ledger.find(wl_id);
+    if (it != e->ledger.end()) {
+        const uint32_t old_node = it->second.node;
+        e->ledger.erase(it);
+        uint8_t m = 0; uint32_t n = 0;
+        for (auto& kv : e->ledger) if (kv.second.node == old_node) { m |= kv.second.mask; n++; }
+        e->h_nodes[old_node].allocated_mask = m; e->h_nodes[old_node].n_allocs = n;
+        mark_dirty(e, old_node);
+    }
+    DevNode& rec = e->h_nodes[idx];
+    rec.allocated_mask |= mask; rec.n_allocs++;
+    e->ledger[wl_id] = LedgerEntry{idx, mask};
+    if (touch_device) mark_dirty(e, idx);
+    return KGWE_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* kgwe_version(void) { return "kgwe-b200 0.1 (sm_100a)"; }
+
+void kgwe_config_default(kgwe_config* c) {
+    if (!c) return;
+    memset(c, 0, sizeof *c);
+    c->struct_size = sizeof *c; c->device = 0; c->max_nodes = 16384; c->node_base = 0;
+    c->topology_weight = 40; c->resource_weight = 35; c->balance_weight = 25; c->hint_bonus = 10;
+    c->nvlink_norm_gbps = 900.0;
+}
+
+int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
+    if (!cfg || !out || cfg->struct_size != sizeof(kgwe_config) || cfg->max_nodes == 0) return KGWE_ERR_INVALID_ARG;
+    auto bad_w = [](int w) { return w < -1000 || w > 1000; };
+    if (bad_w(cfg->topology_weight) || bad_w(cfg->resource_weight) || bad_w(cfg->balance_weight) || bad_w(cfg->hint_bonus)) return KGWE_ERR_INVALID_ARG;
+    if (!(cfg->nvlink_norm_gbps >= 400.0) || !(cfg->nvlink_norm_gbps <= 1e6)) return KGWE_ERR_INVALID_ARG;   // keeps TopologyScore inside int16
+    *out = nullptr;
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0 || cfg->device < 0 || cfg->device >= n_dev) return KGWE_ERR_NO_DEVICE;
+    if (cudaSetDevice(cfg->device) != cudaSuccess) return KGWE_ERR_NO_DEVICE;
+    kgwe_engine* e = new (std::nothrow) kgwe_engine();
+    if (!e) return KGWE_ERR_NO_MEMORY;
+    e->cfg = *cfg;
+    e->params = Params{cfg->topology_weight, cfg->resource_weight, cfg->balance_weight, cfg->hint_bonus, cfg->nvlink_norm_gbps, cfg->node_base};
+    memset(&e->stats, 0, sizeof e->stats);
+    bool ok = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess
+           && cudaEventCreate(&e->ev0) == cudaSuccess && cudaEventCreate(&e->ev1) == cudaSuccess
+           && cudaMalloc(&e->d_nodes, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
+           && cudaMallocHost(&e->h_nodes, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
+           && cudaMalloc(&e->d_counters, 2 * sizeof(unsigned long long)) == cudaSuccess
+           && cudaMallocHost(&e->h_counters, 2 * sizeof(unsigned long long)) == cudaSuccess
+           && cudaMemset(e->d_nodes, 0, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
+           && cudaMemset(e->d_counters, 0, 2 * sizeof(unsigned long long)) == cudaSuccess;
+    if (ok) {
+        memset(e->h_nodes, 0, (size_t)cfg->max_nodes * sizeof(DevNode));
+        e->h_counters[0] = e->h_counters[1] = 0;
+        e->dirty_flag.assign(cfg->max_nodes, 0);
+        cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, cfg->device);
+        ok = cudaFuncSetAttribute(score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK)) == cudaSuccess;
+        int bps = 0;
+        if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, schedule_kernel, SCORE_THREADS, 0) == cudaSuccess && bps > 0) e->sched_blocks_per_sm = bps;
+    }
+    if (!ok) { cudaGetLastError(); kgwe_engine_destroy(e); return KGWE_ERR_CUDA; }
+    *out = e;
+    return KGWE_OK;
+}
+
+int kgwe_engine_destroy(kgwe_engine* e) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    cudaSetDevice(e->cfg.device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    e->d_pods.release(); e->d_hint.release(); e->d_best.release(); e->d_topk.release(); e->d_scores.release();
+    e->h_pods.release(); e->h_topk.release(); e->h_hint.release();
+    if (e->d_nodes) cudaFree(e->d_nodes);
+    if (e->h_nodes) cudaFreeHost(e->h_nodes);
+    if (e->d_counters) cudaFree(e->d_counters);
+    if (e->h_counters) cudaFreeHost(e->h_counters);
+    if (e->ev0) cudaEventDestroy(e->ev0);
+    if (e->ev1) cudaEventDestroy(e->ev1);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+    return KGWE_OK;
+}
+
+int kgwe_nodes_upsert(kgwe_engine* e, uint32_t first, uint32_t count, const kgwe_node_image* imgs) {
+    if (!e || (!imgs && count)) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if ((uint64_t)first + count > e->cfg.max_nodes) return fail(e, KGWE_ERR_OUT_OF_RANGE, "nodes [%u,%u) exceed max_nodes %u", first, first + count, e->cfg.max_nodes);
+    for (uint32_t i = 0; i < count; ++i) {
+        DevNode rec;
+        int rc = to_device_record(e, imgs[i], rec);
+        if (rc != KGWE_OK) return rc;
+        DevNode& dst = e->h_nodes[first + i];
+        const bool was = dst.flags & 1;
+        rec.allocated_mask = was ? dst.allocated_mask : 0;      // ledger-owned fields survive a refresh
+        rec.n_allocs = was ? dst.n_allocs : 0;
+        dst = rec;
+        if (!was) e->n_present++;
+        mark_dirty(e, first + i);
+        e->n_nodes = std::max(e->n_nodes, first + i + 1);
+    }
+    return KGWE_OK;
+}
+
+int kgwe_node_upsert(kgwe_engine* e, uint32_t idx, const kgwe_node_image* img) { return kgwe_nodes_upsert(e, idx, 1, img); }
+
+int kgwe_node_remove(kgwe_engine* e, uint32_t idx) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (idx >= e->cfg.max_nodes) return fail(e, KGWE_ERR_OUT_OF_RANGE, "node %u out of range", idx);
+    DevNode& dst = e->h_nodes[idx];
+    if (!(dst.flags & 1)) return fail(e, KGWE_ERR_NOT_FOUND, "node %u not present", idx);
+    // the reference deletes the map entry (discovery.go:597-600); ledger entries naming the node stay
+    // in the ledger (they are keyed by node name there) and simply stop matching any node.
+    const uint8_t keep_mask = dst.allocated_mask; const uint32_t keep_allocs = dst.n_allocs;
+    memset(&dst, 0, sizeof dst);
+    dst.allocated_mask = keep_mask; dst.n_allocs = keep_allocs;
+    e->n_present--;
+    mark_dirty(e, idx);
+    while (e->n_nodes > 0 && !(e->h_nodes[e->n_nodes - 1].flags & 1)) e->n_nodes--;
+    return KGWE_OK;
+}
+
+int kgwe_alloc_commit(kgwe_engine* e, uint64_t wl_id, uint32_t idx, uint8_t gpu_mask) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (idx >= e->cfg.max_nodes) return fail(e, KGWE_ERR_OUT_OF_RANGE, "node %u out of range", idx);
+    return ledger_apply(e, wl_id, idx, gpu_mask, true);
+}
+
+int kgwe_alloc_release(kgwe_engine* e, uint64_t wl_id) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    auto it = e->ledger.find(wl_id);
+    if (it == e->ledger.end()) return fail(e, KGWE_ERR_NOT_FOUND, "allocation not found for workload %llu", (unsigned long long)wl_id);
+    const uint32_t node = it->second.node;
+    e->ledger.erase(it);
+    DevNode& rec = e->h_nodes[node];
+    uint8_t m = 0; uint32_t n = 0;
+    for (auto& kv : e->ledger) if (kv.second.node == node) { m |= kv.second.mask; n++; }
+    rec.allocated_mask = m; rec.n_allocs = n;
+    mark_dirty(e, node);
+    return KGWE_OK;
+}
+
+int kgwe_score_batch_device(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const uint8_t* d_hint,
+                            kgwe_node_score* d_out, uint32_t topk, kgwe_placement* d_topk, void* cuda_stream) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (topk > KGWE_MAX_TOPK || (topk && !d_topk) || (n_pods && !d_pods)) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    CU(e, cudaSetDevice(e->cfg.device));
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : e->stream;
+    int rc = flush_dirty(e, s);
+    if (rc != KGWE_OK) return rc;
+    kgwe_node_score* scores = d_out;
+    if (topk > 1 && !scores) {
+        if ((size_t)n_pods * e->n_nodes * sizeof(kgwe_node_score) > 8 * kScoreScratchBytes) return fail(e, KGWE_ERR_TOO_LARGE, "top-k > 1 without d_out_scores needs a %zu-byte scratch matrix; pass d_out_scores or split the batch", (size_t)n_pods * e->n_nodes * sizeof(kgwe_node_score));
+        CU(e, e->d_scores.ensure((size_t)n_pods * e->n_nodes));
+        scores = e->d_scores.p;
+    }
+    return launch_score(e, d_pods, n_pods, d_hint, scores, topk, d_topk, s);
+}
+
+int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, const uint8_t* hint,
+                     kgwe_node_score* out_scores, uint32_t topk, kgwe_placement* out_topk) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (topk > KGWE_MAX_TOPK || (topk && !out_topk) || (n_pods && !pods)) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    int rc = validate_pods(e, pods, n_pods);
+    if (rc != KGWE_OK) return rc;
+    CU(e, cudaSetDevice(e->cfg.device));
+    cudaStream_t s = e->stream;
+    rc = flush_dirty(e, s);
+    if (rc != KGWE_OK) return rc;
+    if (n_pods == 0) return KGWE_OK;
+    const uint32_t N = e->n_nodes;
+    if (N == 0) {
+        for (size_t i = 0; i < (size_t)n_pods * topk; ++i) { memset(&out_topk[i], 0, sizeof(kgwe_placement)); out_topk[i].node_idx = KGWE_NO_NODE; }
+        return KGWE_OK;
+    }
+    const uint32_t row = hint_row_bytes(e);
+    const bool need_matrix = out_scores || topk > 1;
+    // pods per pass bounded by the score-matrix scratch
+    uint32_t pass = n_pods;
+    if (need_matrix) pass = (uint32_t)std::max<size_t>(1, std::min<size_t>(n_pods, kScoreScratchBytes / ((size_t)N * sizeof(kgwe_node_score))));
+    CU(e, e->d_pods.ensure(pass)); CU(e, e->h_pods.ensure(pass));
+    if (hint) { CU(e, e->d_hint.ensure((size_t)pass * row)); CU(e, e->h_hint.ensure((size_t)pass * row)); }
+    if (topk) { CU(e, e->d_topk.ensure((size_t)pass * topk)); CU(e, e->h_topk.ensure((size_t)pass * topk)); }
+    if (need_matrix) CU(e, e->d_scores.ensure((size_t)pass * N));
+    double gpu_ms = 0.0;
+    for (uint32_t p0 = 0; p0 < n_pods; p0 += pass) {
+        const uint32_t np = std::min(pass, n_pods - p0);
+        memcpy(e->h_pods.p, pods + p0, (size_t)np * sizeof(kgwe_pod_req));
+        CU(e, cudaMemcpyAsync(e->d_pods.p, e->h_pods.p, (size_t)np * sizeof(kgwe_pod_req), cudaMemcpyHostToDevice, s));
+        e->stats.h2d_bytes += (uint64_t)np * sizeof(kgwe_pod_req);
+        if (hint) {
+            memcpy(e->h_hint.p, hint + (size_t)p0 * row, (size_t)np * row);
+            CU(e, cudaMemcpyAsync(e->d_hint.p, e->h_hint.p, (size_t)np * row, cudaMemcpyHostToDevice, s));
+            e->stats.h2d_bytes += (uint64_t)np * row;
+        }
+        CU(e, cudaEventRecord(e->ev0, s));
+        rc = launch_score(e, e->d_pods.p, np, hint ? e->d_hint.p : nullptr, need_matrix ? e->d_scores.p : nullptr, topk, topk ? e->d_topk.p : nullptr, s);
+        if (rc != KGWE_OK) return rc;
+        CU(e, cudaEventRecord(e->ev1, s));
+        if (topk) {
+            CU(e, cudaMemcpyAsync(e->h_topk.p, e->d_topk.p, (size_t)np * topk * sizeof(kgwe_placement), cudaMemcpyDeviceToHost, s));
+            e->stats.d2h_bytes += (uint64_t)np * topk * sizeof(kgwe_placement);
+        }
+        if (out_scores) {
+            CU(e, cudaMemcpyAsync(out_scores + (size_t)p0 * N, e->d_scores.p, (size_t)np * N * sizeof(kgwe_node_score), cudaMemcpyDeviceToHost, s));
+            e->stats.d2h_bytes += (uint64_t)np * N * sizeof(kgwe_node_score);
+        }
+        rc = pull_counters(e, s);
+        if (rc != KGWE_OK) return rc;
+        CU(e, cudaStreamSynchronize(s));
+        if (topk) memcpy(out_topk + (size_t)p0 * topk, e->h_topk.p, (size_t)np * topk * sizeof(kgwe_placement));
+        e->stats.candidates += e->h_counters[1];
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) == cudaSuccess) gpu_ms += ms;
+    }
+    e->stats.last_call_gpu_ms = gpu_ms;
+    return KGWE_OK;
+}
+
+int kgwe_topk_merge_device(kgwe_engine* e, const kgwe_placement* d_lists, uint32_t n_lists, uint32_t n_pods, uint32_t topk,
+                           kgwe_placement* d_out, void* cuda_stream) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (!d_lists || !d_out || topk == 0 || topk > KGWE_MAX_TOPK || n_lists == 0 || n_lists > 32) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    if (n_pods == 0) return KGWE_OK;
+    CU(e, cudaSetDevice(e->cfg.device));
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : e->stream;
+    topk_merge_kernel<<<(n_pods + 127) / 128, 128, 0, s>>>(d_lists, n_lists, n_pods, topk, d_out);
+    CU(e, cudaGetLastError());
+    e->stats.kernel_launches++;
+    return KGWE_OK;
+}
+
+int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, const uint8_t* hint, kgwe_placement* out) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if ((n_pods && !pods) || (n_pods && !out)) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    int rc = validate_pods(e, pods, n_pods);
+    if (rc != KGWE_OK) return rc;
+    CU(e, cudaSetDevice(e->cfg.device));
+    cudaStream_t s = e->stream;
+    if (n_pods == 0) return KGWE_OK;
+    const uint32_t N = e->n_nodes;
+    if (N == 0) {
+        for (uint32_t i = 0; i < n_pods; ++i) { memset(&out[i], 0, sizeof(kgwe_placement)); out[i].node_idx = KGWE_NO_NODE; e->stats.failed++; }
+        return KGWE_OK;
+    }
+    const uint32_t row = hint_row_bytes(e);
+    // A workload whose UID is already in the ledger (or repeats inside the queue) overwrites its
+    // old entry AFTER it has been scored against it (scheduler.go:699).  Such a pod ends a
+    // segment: the kernel runs up to and including it, then the host drops the old entry.
+    double gpu_ms = 0.0;
+    uint32_t p0 = 0;
+    while (p0 < n_pods) {
+        uint32_t p1 = p0; bool overwrite = false;
+        {
+            std::unordered_map<uint64_t, int> seen;
+            while (p1 < n_pods) {
+                const uint64_t id = pods[p1].wl_id;
+                if (e->ledger.count(id) || seen.count(id)) { overwrite = true; ++p1; break; }
+                seen[id] = 1; ++p1;
+            }
+        }
+        const uint32_t np = p1 - p0;
+        rc = flush_dirty(e, s);
+        if (rc != KGWE_OK) return rc;
+        CU(e, e->d_pods.ensure(np)); CU(e, e->h_pods.ensure(np));
+        CU(e, e->d_topk.ensure(np)); CU(e, e->h_topk.ensure(np));
+        {
+            const size_t had = e->d_best.cap;
+            CU(e, e->d_best.ensure(np));
+            if (e->d_best.cap != had) CU(e, cudaMemsetAsync(e->d_best.p, 0, e->d_best.cap * sizeof(unsigned long long), s));
+        }
+        memcpy(e->h_pods.p, pods + p0, (size_t)np * sizeof(kgwe_pod_req));
+        CU(e, cudaMemcpyAsync(e->d_pods.p, e->h_pods.p, (size_t)np * sizeof(kgwe_pod_req), cudaMemcpyHostToDevice, s));
+        e->stats.h2d_bytes += (uint64_t)np * sizeof(kgwe_pod_req);
+        const uint8_t* d_hint = nullptr;
+        if (hint) {
+            CU(e, e->d_hint.ensure((size_t)np * row)); CU(e, e->h_hint.ensure((size_t)np * row));
+            memcpy(e->h_hint.p, hint + (size_t)p0 * row, (size_t)np * row);
+            CU(e, cudaMemcpyAsync(e->d_hint.p, e->h_hint.p, (size_t)np * row, cudaMemcpyHostToDevice, s));
+            e->stats.h2d_bytes += (uint64_t)np * row;
+            d_hint = e->d_hint.p;
+        }
+        // persistent grid: as many CTAs as can be co-resident, no more than there are node tiles
+        uint32_t grid = std::min<uint32_t>((uint32_t)(e->sm_count * e->sched_blocks_per_sm), (N + TILE_NODES - 1) / TILE_NODES);
+        grid = std::max(grid, 1u);
+        DevNode* d_nodes = e->d_nodes; uint32_t n_nodes = N; const kgwe_pod_req* d_pods = e->d_pods.p; uint32_t npods = np; uint32_t rowb = row;
+        unsigned long long* best = e->d_best.p; kgwe_placement* d_out = e->d_topk.p; Params prm = e->params; unsigned long long* ctr = e->d_counters;
+        void* args[] = {&d_nodes, &n_nodes, &d_pods, &npods, &d_hint, &rowb, &best, &d_out, &prm, &ctr};
+        CU(e, cudaEventRecord(e->ev0, s));
+        CU(e, cudaLaunchCooperativeKernel((const void*)schedule_kernel, dim3(grid), dim3(SCORE_THREADS), args, 0, s));
+        e->stats.kernel_launches++;
+        CU(e, cudaMemsetAsync(e->d_best.p, 0, (size_t)np * sizeof(unsigned long long), s));
+        CU(e, cudaEventRecord(e->ev1, s));
+        CU(e, cudaMemcpyAsync(e->h_topk.p, e->d_topk.p, (size_t)np * sizeof(kgwe_placement), cudaMemcpyDeviceToHost, s));
+        e->stats.d2h_bytes += (uint64_t)np * sizeof(kgwe_placement);
+        rc = pull_counters(e, s);
+        if (rc != KGWE_OK) return rc;
+        CU(e, cudaStreamSynchronize(s));
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) == cudaSuccess) gpu_ms += ms;
+        e->stats.evaluations += e->h_counters[0];
+        e->stats.candidates += e->h_counters[1];
+        // mirror the device-side commits into the host ledger and the pinned image
+        for (uint32_t i = 0; i < np; ++i) {
+            const kgwe_placement& d = e->h_topk.p[i];
+            out[p0 + i] = d;
+            if (d.node_idx == KGWE_NO_NODE) { e->stats.failed++; continue; }
+            e->stats.scheduled++;
+            if (d.topology >= 80) e->stats.topology_optimal++;
+            const uint32_t local = d.node_idx - e->cfg.node_base;
+            const bool last_overwrites = overwrite && i == np - 1;
+            if (!last_overwrites) {
+                DevNode& rec = e->h_nodes[local];
+                rec.allocated_mask |= d.gpu_mask; rec.n_allocs++;
+                e->ledger[pods[p0 + i].wl_id] = LedgerEntry{local, d.gpu_mask};
+            } else {
+                // device already holds the new commit; bring the mirror level, then drop the old entry
+                DevNode& rec = e->h_nodes[local];
+                rec.allocated_mask |= d.gpu_mask; rec.n_allocs++;
+                auto it = e->ledger.find(pods[p0 + i].wl_id);
+                const uint32_t old_node = it->second.node;
+                e->ledger.erase(it);
+                e->ledger[pods[p0 + i].wl_id] = LedgerEntry{local, d.gpu_mask};
+                for (uint32_t nd : {old_node, local}) {
+                    uint8_t m = 0; uint32_t n = 0;
+                    for (auto& kv : e->ledger) if (kv.second.node == nd) { m |= kv.second.mask; n++; }
+                    e->h_nodes[nd].allocated_mask = m; e->h_nodes[nd].n_allocs = n;
+                    mark_dirty(e, nd);
+                }
+            }
+        }
+        p0 = p1;
+    }
+    e->stats.last_call_gpu_ms = gpu_ms;
+    return KGWE_OK;
+}
+
+int kgwe_node_read(kgwe_engine* e, uint32_t idx, kgwe_node_image* out) {
+    if (!e || !out) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (idx >= e->cfg.max_nodes) return fail(e, KGWE_ERR_OUT_OF_RANGE, "node %u out of range", idx);
+    CU(e, cudaSetDevice(e->cfg.device));
+    int rc = flush_dirty(e, e->stream);
+    if (rc != KGWE_OK) return rc;
+    DevNode rec;
+    CU(e, cudaMemcpyAsync(&rec, e->d_nodes + idx, sizeof rec, cudaMemcpyDeviceToHost, e->stream));
+    CU(e, cudaStreamSynchronize(e->stream));
+    to_abi_record(rec, *out);
+    return KGWE_OK;
+}
+
+int kgwe_get_stats(kgwe_engine* e, kgwe_stats* out) {
+    if (!e || !out) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    *out = e->stats;
+    out->n_nodes = e->n_nodes;
+    out->n_allocations = (uint32_t)e->ledger.size();
+    return KGWE_OK;
+}
+
+const char* kgwe_last_error(kgwe_engine* e) { return e ? e->err.c_str() : "null engine"; }
+
+}  // extern "C"

@@ -1,0 +1,300 @@
+// kgwe_kernels.cuh — the engine's kernels (sm_100a).
+//
+//  score_kernel      K1  stateless Filter+Prioritize: grid = node tiles x pod chunks.  A CTA
+//                        stages one tile of 64 node records (48 KB) into shared memory with a
+//                        single TMA bulk copy (cp.async.bulk + mbarrier), derives the
+//                        pod-independent NodeCtx of its nodes once, then streams its pod chunk:
+//                        8 lanes per (pod,node), 16-byte score records out, per-pod arg-max
+//                        through a shared-memory key table flushed with one atomicMax per pod.
+//  finalize_top1     K1b turns the arg-max keys into placements (+ EstimatedBandwidth).
+//  topk_select       K2  ranked top-k per pod from the score matrix (canonical order).
+//  topk_merge        K2b merges per-shard ranked lists (multi-GPU, after the all-gather).
+//  schedule_kernel   K3  stateful queue: persistent cooperative kernel, one grid-wide arg-max
+//                        and an owner-side commit per pod.
+#pragma once
+#include <cooperative_groups.h>
+
+#include "kgwe_device.cuh"
+
+namespace kgwe {
+namespace cg = cooperative_groups;
+
+constexpr int TILE_NODES = 64;                 // nodes per CTA tile
+constexpr int SCORE_THREADS = TILE_NODES * 8;  // 8 lanes per node
+constexpr int MAX_PODS_PER_CHUNK = 1024;       // size of the per-CTA arg-max table
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
+    uint32_t done = 0;
+    while (!done) {
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(smem_u32(bar)), "r"(phase) : "memory");
+    }
+}
+
+__device__ __forceinline__ kgwe_pod_req load_pod(const kgwe_pod_req* pods, uint32_t p) {
+    const uint4* src = reinterpret_cast<const uint4*>(pods + p);
+    union { uint4 v[2]; kgwe_pod_req r; } u;
+    u.v[0] = __ldg(src); u.v[1] = __ldg(src + 1);
+    return u.r;
+}
+
+__device__ __forceinline__ bool hint_bit(const uint8_t* hint, uint32_t row_bytes, uint32_t p, uint32_t n) {
+    return hint && ((__ldg(hint + (size_t)p * row_bytes + (n >> 3)) >> (n & 7)) & 1);
+}
+
+__device__ __forceinline__ void store_placement(kgwe_placement* dst, uint32_t node, const EvalOut& o, double est) {
+    kgwe_placement pl;
+    pl.node_idx = node; pl.total = o.total; pl.topology = (int16_t)o.topo; pl.resource = (int16_t)o.res;
+    pl.balance = (int16_t)o.bal; pl.gpu_mask = (uint8_t)o.mask; pl.flags = (uint8_t)o.flags; pl.order = o.order;
+    pl.reserved = 0; pl.est_bandwidth_gbps = est;
+    *dst = pl;
+}
+__device__ __forceinline__ void store_no_placement(kgwe_placement* dst) {
+    kgwe_placement pl;
+    pl.node_idx = KGWE_NO_NODE; pl.total = 0; pl.topology = pl.resource = pl.balance = 0; pl.gpu_mask = 0; pl.flags = 0;
+    pl.order = 0; pl.reserved = 0; pl.est_bandwidth_gbps = 0.0;
+    *dst = pl;
+}
+
+// ---------------------------------------------------------------------------------------
+// K1.  dynamic smem: [tile: TILE_NODES x 768 B][keys: pods_per_chunk x 8 B][mbarrier 8 B]
+__global__ void __launch_bounds__(SCORE_THREADS, 2)
+score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
+             const kgwe_pod_req* __restrict__ pods, uint32_t n_pods, uint32_t pods_per_chunk,
+             const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
+             kgwe_node_score* __restrict__ out, unsigned long long* __restrict__ best,
+             Params P, unsigned long long* __restrict__ counters) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    DevNode* tile = reinterpret_cast<DevNode*>(smem);
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem + TILE_NODES * sizeof(DevNode));
+    uint64_t* bar = reinterpret_cast<uint64_t*>(keys + pods_per_chunk);
+
+    const int tid = threadIdx.x, lane = tid & 31, grp = tid >> 3;
+    const uint32_t tile_first = blockIdx.x * TILE_NODES;
+    const uint32_t tile_count = min((uint32_t)TILE_NODES, n_nodes - tile_first);
+    const uint32_t p_begin = blockIdx.y * pods_per_chunk;
+    const uint32_t p_end = min(n_pods, p_begin + pods_per_chunk);
+
+    if (tid == 0) mbar_init(bar, 1);
+    __syncthreads();
+    if (tid == 0) {
+        const uint32_t bytes = tile_count * (uint32_t)sizeof(DevNode);
+        mbar_expect_tx(bar, bytes);
+        tma_bulk_g2s(tile, nodes + tile_first, bytes, bar);
+    }
+    if (best) for (uint32_t i = tid; i < pods_per_chunk; i += SCORE_THREADS) keys[i] = 0ull;
+    mbar_wait(bar, 0);
+    __syncthreads();
+
+    const uint32_t node = tile_first + grp;
+    const DevNode* rec = tile + grp;
+    NodeCtx nc;
+    node_ctx_init(nc, rec, grp < (int)tile_count);
+    const uint32_t gnode = P.node_base + node;
+    unsigned long long cand = 0;
+
+    for (uint32_t p = p_begin; p < p_end; ++p) {
+        const kgwe_pod_req pod = load_pod(pods, p);
+        EvalOut o;
+        evaluate(rec, nc, pod, P, hint_bit(hint, hint_row_bytes, p, node), lane, o);
+        if ((lane & 7) == 0 && grp < (int)tile_count) {
+            cand += o.candidates;
+            if (out) {
+                const kgwe_node_score r = to_record(o);
+                *reinterpret_cast<int4*>(out + (size_t)p * n_nodes + node) = *reinterpret_cast<const int4*>(&r);
+            }
+        }
+        if (best) {
+            unsigned long long key = (o.flags & KGWE_F_KEPT) ? rank_key(o.total, gnode) : 0ull;
+            unsigned long long k2 = __shfl_xor_sync(0xffffffffu, key, 8);  key = k2 > key ? k2 : key;
+            k2 = __shfl_xor_sync(0xffffffffu, key, 16);                    key = k2 > key ? k2 : key;
+            if (lane == 0 && key) atomicMax(&keys[p - p_begin], key);
+        }
+    }
+    // candidates counter: one atomic per warp
+    cand += __shfl_xor_sync(0xffffffffu, cand, 8);
+    cand += __shfl_xor_sync(0xffffffffu, cand, 16);
+    if (lane == 0 && counters && cand) atomicAdd(&counters[1], cand);
+    if (best) {
+        __syncthreads();
+        for (uint32_t i = tid; i < p_end - p_begin; i += SCORE_THREADS)
+            if (keys[i]) atomicMax(&best[p_begin + i], keys[i]);
+    }
+}
+
+// K1b: one 8-lane group per pod.  Re-evaluates the winning (pod,node) to recover its GPU
+// list, adds EstimatedBandwidth, and clears the key slot for the next call.
+__global__ void __launch_bounds__(256)
+finalize_top1_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
+                     const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
+                     unsigned long long* __restrict__ best, kgwe_placement* __restrict__ out, uint32_t out_stride, Params P) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t p = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+    const bool live = p < n_pods;
+    unsigned long long key = live ? best[p] : 0ull;
+    const uint32_t node = key ? key_node(key) - P.node_base : 0;
+    kgwe_pod_req pod;
+    if (live) pod = load_pod(pods, p); else { pod = kgwe_pod_req{}; }
+    const DevNode* rec = nodes + node;
+    NodeCtx nc;
+    node_ctx_init(nc, rec, live && key != 0ull && node < n_nodes);
+    EvalOut o;
+    evaluate(rec, nc, pod, P, live && hint_bit(hint, hint_row_bytes, p, node), lane, o);
+    if (live && (lane & 7) == 0) {
+        if (key == 0ull) store_no_placement(out + (size_t)p * out_stride);
+        else store_placement(out + (size_t)p * out_stride, P.node_base + node, o, est_bandwidth(rec, o.order, (int)((o.order >> 24) & 15)));
+        best[p] = 0ull;
+    }
+}
+
+// K2: one CTA per pod over that pod's row of the score matrix.
+__global__ void __launch_bounds__(256)
+topk_select_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, const kgwe_node_score* __restrict__ scores,
+                   uint32_t topk, kgwe_placement* __restrict__ out, Params P) {
+    __shared__ unsigned long long wmax[8];
+    __shared__ unsigned long long sel[KGWE_MAX_TOPK];
+    const uint32_t p = blockIdx.x;
+    const kgwe_node_score* row = scores + (size_t)p * n_nodes;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned long long bound = ~0ull;
+    for (uint32_t r = 0; r < topk; ++r) {
+        unsigned long long local = 0ull;
+        for (uint32_t n = tid; n < n_nodes; n += 256) {
+            const int4 v = __ldg(reinterpret_cast<const int4*>(row + n));
+            const uint32_t flags = ((uint32_t)v.z >> 24) & 0xff;
+            if (flags & KGWE_F_KEPT) {
+                const unsigned long long key = rank_key(v.x, P.node_base + n);
+                if (key < bound && key > local) local = key;
+            }
+        }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) { unsigned long long o2 = __shfl_xor_sync(0xffffffffu, local, off); local = o2 > local ? o2 : local; }
+        if (lane == 0) wmax[warp] = local;
+        __syncthreads();
+        unsigned long long m = wmax[0];
+#pragma unroll
+        for (int w = 1; w < 8; ++w) m = wmax[w] > m ? wmax[w] : m;
+        if (tid == 0) sel[r] = m;
+        bound = m;
+        __syncthreads();
+        if (m == 0ull) { for (uint32_t r2 = r + 1 + tid; r2 < topk; r2 += 256) sel[r2] = 0ull; break; }
+    }
+    __syncthreads();
+    if (tid < (int)topk) {
+        const unsigned long long key = sel[tid];
+        kgwe_placement* dst = out + (size_t)p * topk + tid;
+        if (key == 0ull) store_no_placement(dst);
+        else {
+            const uint32_t n = key_node(key) - P.node_base;
+            const kgwe_node_score s = row[n];
+            EvalOut o; o.total = s.total; o.topo = s.topology; o.res = s.resource; o.bal = s.balance;
+            o.mask = s.gpu_mask; o.flags = s.flags; o.order = s.order; o.candidates = 0;
+            store_placement(dst, P.node_base + n, o, est_bandwidth(nodes + n, s.order, (int)((s.order >> 24) & 15)));
+        }
+    }
+}
+
+// K2b: thread per pod; lists[r][p][topk] are each ranked; emit the ranked union's first topk.
+__global__ void __launch_bounds__(128)
+topk_merge_kernel(const kgwe_placement* __restrict__ lists, uint32_t n_lists, uint32_t n_pods, uint32_t topk,
+                  kgwe_placement* __restrict__ out) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pods) return;
+    uint8_t head[32];
+    for (uint32_t r = 0; r < n_lists && r < 32; ++r) head[r] = 0;
+    for (uint32_t j = 0; j < topk; ++j) {
+        int br = -1; int32_t bt = 0; uint32_t bn = 0;
+        for (uint32_t r = 0; r < n_lists && r < 32; ++r) {
+            if (head[r] >= topk) continue;
+            const kgwe_placement* c = lists + ((size_t)r * n_pods + p) * topk + head[r];
+            const uint32_t cn = c->node_idx;
+            if (cn == KGWE_NO_NODE) continue;
+            const int32_t ct = c->total;
+            if (br < 0 || ct > bt || (ct == bt && cn < bn)) { br = (int)r; bt = ct; bn = cn; }
+        }
+        kgwe_placement* dst = out + (size_t)p * topk + j;
+        if (br < 0) store_no_placement(dst);
+        else { *dst = lists[((size_t)br * n_pods + p) * topk + head[br]]; head[br]++; }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// K3.  Cooperative launch; grid * 64 lane groups; group g owns nodes g, g + G, g + 2G, ...
+// Ownership is static, so a commit only has to be seen by the group that made it: ONE grid
+// barrier per workload (for the arg-max), none for the commit.
+__global__ void __launch_bounds__(SCORE_THREADS, 2)
+schedule_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
+                const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
+                unsigned long long* __restrict__ best, kgwe_placement* __restrict__ out,
+                Params P, unsigned long long* __restrict__ counters) {
+    cg::grid_group grid = cg::this_grid();
+    __shared__ unsigned long long wmax[SCORE_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t n_groups = gridDim.x * (SCORE_THREADS / 8);
+    const uint32_t g = blockIdx.x * (SCORE_THREADS / 8) + (tid >> 3);
+    const uint32_t iters = (n_nodes + n_groups - 1) / n_groups;
+    const bool single = iters <= 1;
+    NodeCtx nc;
+    if (single) node_ctx_init(nc, nodes + g, g < n_nodes);
+    unsigned long long cand = 0, evals = 0;
+
+    for (uint32_t p = 0; p < n_pods; ++p) {
+        const kgwe_pod_req pod = load_pod(pods, p);
+        unsigned long long mykey = 0ull; EvalOut keep; uint32_t keepnode = 0;
+        keep.total = keep.topo = keep.res = keep.bal = 0; keep.mask = keep.order = keep.flags = 0; keep.candidates = 0;
+        for (uint32_t it = 0; it < iters; ++it) {
+            const uint32_t node = g + it * n_groups;
+            const DevNode* rec = nodes + node;
+            if (!single) node_ctx_init(nc, rec, node < n_nodes);
+            EvalOut o;
+            evaluate(rec, nc, pod, P, node < n_nodes && hint_bit(hint, hint_row_bytes, p, node), lane, o);
+            if (node < n_nodes) { cand += o.candidates; evals += 1; }
+            const unsigned long long key = (o.flags & KGWE_F_KEPT) ? rank_key(o.total, P.node_base + node) : 0ull;
+            if (key > mykey) { mykey = key; keep = o; keepnode = node; }
+        }
+        unsigned long long m = mykey;
+#pragma unroll
+        for (int off = 16; off >= 8; off >>= 1) { unsigned long long o2 = __shfl_xor_sync(0xffffffffu, m, off); m = o2 > m ? o2 : m; }
+        if (lane == 0) wmax[warp] = m;
+        __syncthreads();
+        if (tid == 0) {
+            unsigned long long b = wmax[0];
+            for (int w = 1; w < SCORE_THREADS / 32; ++w) b = wmax[w] > b ? wmax[w] : b;
+            if (b) atomicMax(&best[p], b);
+        }
+        grid.sync();
+        const unsigned long long win = *reinterpret_cast<volatile unsigned long long*>(&best[p]);
+        if (win == 0ull) {
+            if (g == 0 && (lane & 7) == 0) store_no_placement(out + p);      // "no eligible nodes found", scheduler.go:138-141
+        } else if (win == mykey) {
+            // this group owns the winner: tryScheduleOnNode + recordAllocation (scheduler.go:625-653, 695-707)
+            DevNode* rec = nodes + keepnode;
+            if ((lane & 7) == 0) {
+                store_placement(out + p, P.node_base + keepnode, keep, est_bandwidth(rec, keep.order, (int)((keep.order >> 24) & 15)));
+                rec->allocated_mask = (uint8_t)(rec->allocated_mask | keep.mask);
+                rec->n_allocs = rec->n_allocs + 1;
+            }
+            __syncwarp(0xffu << (lane & 24));
+            if (single) node_ctx_init(nc, rec, true);
+        }
+    }
+    if ((lane & 7) != 0) { cand = 0; evals = 0; }
+#pragma unroll
+    for (int off = 16; off >= 8; off >>= 1) { cand += __shfl_xor_sync(0xffffffffu, cand, off); evals += __shfl_xor_sync(0xffffffffu, evals, off); }
+    if (lane == 0 && counters) { if (evals) atomicAdd(&counters[0], evals); if (cand) atomicAdd(&counters[1], cand); }
+}
+
+}  // namespace kgwe

@@ -1,0 +1,109 @@
+"""Thin ctypes wrapper over the C ABI (include/kgwe_engine.h).  One method per entry
+point, numpy arrays in the ABI's layouts in and out.  Mirrors what the cgo shim in the
+reference's src/scheduler package does; no scoring logic here."""
+import ctypes as C
+
+import numpy as np
+
+from . import abi
+
+
+class EngineError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"kgwe error {code}: {msg}")
+        self.code = code
+
+
+class Engine:
+    """Owns one kgwe_engine (one CUDA device, one node shard)."""
+
+    def __init__(self, max_nodes, device=0, node_base=0, config=None):
+        self.lib = abi.load_engine_lib()
+        self.cfg = config if config is not None else abi.default_config(max_nodes, device, node_base)
+        self.h = C.c_void_p()
+        rc = self.lib.kgwe_engine_create(C.byref(self.cfg), C.byref(self.h))
+        if rc != 0:
+            raise EngineError(rc, "kgwe_engine_create failed (no usable CUDA device? there is no CPU fallback)")
+
+    def close(self):
+        if self.h:
+            self.lib.kgwe_engine_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc != 0:
+            msg = self.lib.kgwe_last_error(self.h)
+            raise EngineError(rc, msg.decode() if msg else "")
+
+    # --- snapshot ingestion (replaces discovery.go:290-319 full rebuilds) ---
+    def upsert_nodes(self, images, first=0):
+        images = np.ascontiguousarray(images, dtype=abi.NODE_IMAGE)
+        self._check(self.lib.kgwe_nodes_upsert(self.h, first, len(images), abi.ptr(images)))
+
+    def upsert_node(self, idx, image):
+        img = np.ascontiguousarray(image, dtype=abi.NODE_IMAGE).reshape(1)
+        self._check(self.lib.kgwe_node_upsert(self.h, idx, abi.ptr(img)))
+
+    def remove_node(self, idx):
+        self._check(self.lib.kgwe_node_remove(self.h, idx))
+
+    def read_node(self, idx):
+        out = np.zeros(1, dtype=abi.NODE_IMAGE)
+        self._check(self.lib.kgwe_node_read(self.h, idx, abi.ptr(out)))
+        return out[0]
+
+    # --- ledger (scheduler.go:695-727) ---
+    def commit(self, wl_id, node_idx, gpu_mask):
+        self._check(self.lib.kgwe_alloc_commit(self.h, int(wl_id), int(node_idx), int(gpu_mask)))
+
+    def release(self, wl_id):
+        self._check(self.lib.kgwe_alloc_release(self.h, int(wl_id)))
+
+    def seed_ledger(self, ledger):
+        for a in ledger:
+            self.commit(a["wl_id"], a["node_idx"], a["gpu_mask"])
+
+    # --- scoring ---
+    def score_batch(self, pods, n_nodes, hint=None, want_scores=True, topk=0):
+        """scoreNodes for every pod (scheduler.go:182-203).  Returns (scores[P,N] | None, topk[P,topk] | None)."""
+        pods = np.ascontiguousarray(pods, dtype=abi.POD_REQ)
+        P = len(pods)
+        scores = np.zeros((P, n_nodes), dtype=abi.NODE_SCORE) if want_scores else None
+        top = np.zeros((P, topk), dtype=abi.PLACEMENT) if topk else None
+        if hint is not None:
+            hint = np.ascontiguousarray(hint, dtype=np.uint8)
+        self._check(self.lib.kgwe_score_batch(self.h, abi.ptr(pods), P, abi.ptr(hint), abi.ptr(scores), topk, abi.ptr(top)))
+        return scores, top
+
+    def score_batch_device(self, d_pods, n_pods, d_hint, d_scores, topk, d_topk, stream=None):
+        """All arguments are raw device addresses (ints) on this engine's GPU; asynchronous."""
+        self._check(self.lib.kgwe_score_batch_device(self.h, d_pods, n_pods, d_hint, d_scores, topk, d_topk, stream))
+
+    def topk_merge_device(self, d_lists, n_lists, n_pods, topk, d_out, stream=None):
+        self._check(self.lib.kgwe_topk_merge_device(self.h, d_lists, n_lists, n_pods, topk, d_out, stream))
+
+    def schedule_queue(self, pods, hint=None):
+        """Schedule() per pod in order with commits (scheduler.go:114-179)."""
+        pods = np.ascontiguousarray(pods, dtype=abi.POD_REQ)
+        out = np.zeros(len(pods), dtype=abi.PLACEMENT)
+        if hint is not None:
+            hint = np.ascontiguousarray(hint, dtype=np.uint8)
+        self._check(self.lib.kgwe_schedule_queue(self.h, abi.ptr(pods), len(pods), abi.ptr(hint), abi.ptr(out)))
+        return out
+
+    def stats(self):
+        s = abi.Stats()
+        self._check(self.lib.kgwe_get_stats(self.h, C.byref(s)))
+        return {name: getattr(s, name) for name, _ in abi.Stats._fields_}
+
+
+def unpack_order(order):
+    """SelectedGPUs (ordered) from the packed `order` field."""
+    n = (int(order) >> 24) & 15
+    return [(int(order) >> (3 * p)) & 7 for p in range(n)]

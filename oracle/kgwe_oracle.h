@@ -1,0 +1,65 @@
+/*
+ * kgwe_oracle.h — C API of the CPU oracle.  TEST INFRASTRUCTURE ONLY.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+ * legs may load this library, and only as the checker or the timed CPU baseline —
+ * never as part of the product path (the CUDA engine has no CPU fallback).
+ *
+ * PARITY UNPINNED BY REFERENCE TESTS: the reference ships no tests, golden vectors or
+ * fixtures for this path and its Go toolchain is absent here, so this restatement is
+ * pinned by source reading plus the hand-derived known-answer vectors of SURVEY.md 8c
+ * (tests/golden/kats.json), not by outputs of the reference itself.
+ */
+#ifndef KGWE_ORACLE_H
+#define KGWE_ORACLE_H
+
+#include "../include/kgwe_engine.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* A ledger entry (GPUAllocation, src/scheduler/scheduler.go:68-75) in index form. */
+typedef struct kgwe_oracle_alloc {
+    uint64_t wl_id;
+    uint32_t node_idx;
+    uint8_t  gpu_mask;
+    uint8_t  pad[3];
+} kgwe_oracle_alloc;
+
+enum { KGWE_ORACLE_FAITHFUL = 0, KGWE_ORACLE_INDEXED = 1 };
+
+typedef struct kgwe_oracle_counters {
+    uint64_t evaluations;
+    uint64_t candidates;
+    double   seconds;          /* wall time of the scoring work only (structures already built) */
+} kgwe_oracle_counters;
+
+/* scoreNodes for each pod over all nodes (stateless w.r.t. the ledger passed in).
+ * mode FAITHFUL keeps the reference's data structures (string UUIDs, hash-map ledger
+ * scanned per node, per-call adjacency maps); INDEXED computes the same results on
+ * dense arrays.  `threads` > 1 splits pods over std::threads. */
+int kgwe_oracle_score_batch(const kgwe_config* cfg,
+                            const kgwe_node_image* nodes, uint32_t n_nodes,
+                            const kgwe_oracle_alloc* ledger, uint32_t n_ledger,
+                            const kgwe_pod_req* pods, uint32_t n_pods,
+                            const uint8_t* hint_bitmap,
+                            kgwe_node_score* out_scores,
+                            uint32_t topk, kgwe_placement* out_topk,
+                            int mode, int threads, kgwe_oracle_counters* counters);
+
+/* Schedule() for each pod in order, committing as it goes.  ledger_out (capacity
+ * n_ledger + n_pods) receives the final ledger; *n_ledger_out its size. */
+int kgwe_oracle_schedule_queue(const kgwe_config* cfg,
+                               const kgwe_node_image* nodes, uint32_t n_nodes,
+                               const kgwe_oracle_alloc* ledger, uint32_t n_ledger,
+                               const kgwe_pod_req* pods, uint32_t n_pods,
+                               const uint8_t* hint_bitmap,
+                               kgwe_placement* out,
+                               kgwe_oracle_alloc* ledger_out, uint32_t* n_ledger_out,
+                               int mode, kgwe_oracle_counters* counters);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

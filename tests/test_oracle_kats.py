@@ -1,0 +1,128 @@
+"""Pins the CPU oracle (both builds) against hand-derived known-answer vectors.
+The reference has no tests/golden vectors of its own: parity is
+pinned by source reading, and these are the vectors that reading produced."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from helpers import CUBE_EDGES, ledger_of, make_node, make_pod, order_list
+
+KATS = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "kats.json")))
+
+
+def _node(abi, kw):
+    kw = dict(kw)
+    if kw.get("links") == "cube":
+        kw["links"] = CUBE_EDGES
+    elif isinstance(kw.get("links"), list):
+        kw["links"] = [tuple(e) for e in kw["links"]]
+    if "inactive" in kw:
+        kw["inactive"] = [tuple(e) for e in kw["inactive"]]
+    return make_node(abi, **kw)
+
+
+def check_expect(abi, rec, top, exp):
+    assert rec["flags"] & abi.F_ELIGIBLE
+    for f in ("topology", "resource", "balance", "total"):
+        if f in exp:
+            assert int(rec[f]) == exp[f], f
+    if "gpus" in exp:
+        assert order_list(rec["order"]) == exp["gpus"]
+        assert int(rec["gpu_mask"]) == sum(1 << g for g in exp["gpus"])
+    assert bool(rec["flags"] & abi.F_FALLBACK) == bool(exp.get("fallback", False))
+    if "est_bw" in exp:
+        assert float(top["est_bandwidth_gbps"]) == exp["est_bw"]
+
+
+@pytest.mark.parametrize("mode", [0, 1], ids=["faithful", "indexed"])
+@pytest.mark.parametrize("case", KATS["cases"], ids=[c["name"].split(" ")[0] + f"-{i}" for i, c in enumerate(KATS["cases"])])
+def test_kat(kg, orc, case, mode):
+    abi = kg.abi
+    nodes = np.array([_node(abi, case["node"])], dtype=abi.NODE_IMAGE)
+    pods = np.array([make_pod(abi, **case["pod"])], dtype=abi.POD_REQ)
+    led = ledger_of(abi, [tuple(x) for x in case["ledger"]])
+    scores, top, _ = orc.score_batch(abi, nodes, led, pods, want_scores=True, topk=1, mode=mode)
+    check_expect(abi, scores[0, 0], top[0, 0], case["expect"])
+
+
+@pytest.mark.parametrize("mode", [0, 1], ids=["faithful", "indexed"])
+def test_balance_table(kg, orc, mode):
+    abi = kg.abi
+    for G, table in ((8, KATS["balance_table"]["8"]), (6, KATS["balance_table"]["6"])):
+        nodes = np.array([make_node(abi, n_gpus=G)], dtype=abi.NODE_IMAGE)
+        pods = np.array([make_pod(abi, 0, pref="None")], dtype=abi.POD_REQ)   # k=0 keeps every state eligible
+        for a, want in enumerate(table):
+            led = ledger_of(abi, [(100 + i, 0, 0) for i in range(a)])        # a workloads holding no GPU
+            scores, _, _ = orc.score_batch(abi, nodes, led, pods, mode=mode)
+            assert int(scores[0, 0]["balance"]) == want, (G, a)
+
+
+def test_weighted_totals_and_hint(kg, orc):
+    abi = kg.abi
+    # (83,85,62)->78 is KAT-8a's node; with the hint bit set the total gains +10
+    case = [c for c in KATS["cases"] if c["name"].startswith("KAT-8a")][0]
+    nodes = np.array([_node(abi, case["node"])], dtype=abi.NODE_IMAGE)
+    pods = np.array([make_pod(abi, **case["pod"])], dtype=abi.POD_REQ)
+    led = ledger_of(abi, [tuple(x) for x in case["ledger"]])
+    hint = np.array([[1]], dtype=np.uint8)
+    for mode in (0, 1):
+        s, _, _ = orc.score_batch(abi, nodes, led, pods, hint=hint, mode=mode)
+        assert int(s[0, 0]["total"]) == 88 and s[0, 0]["flags"] & abi.F_HINT
+    for t, r, b, tot in KATS["weighted_totals"]["cases"]:
+        assert (t * 40 + r * 35 + b * 25) // 100 == tot
+
+
+def test_kat12_arch_filter_one_match_suffices(kg, orc):
+    abi = kg.abi
+    arch = [abi.ARCH_AMPERE] * 7 + [abi.ARCH_HOPPER]
+    nodes = np.array([make_node(abi, arch=arch), make_node(abi, arch=arch, unhealthy=(7,))], dtype=abi.NODE_IMAGE)
+    pods = np.array([make_pod(abi, 4, arch=abi.ARCH_HOPPER, mem=16)], dtype=abi.POD_REQ)
+    for mode in (0, 1):
+        s, _, _ = orc.score_batch(abi, nodes, None, pods, mode=mode)
+        assert s[0, 0]["flags"] & abi.F_ELIGIBLE            # one available Hopper GPU is enough (scheduler.go:221-226)
+        assert order_list(s[0, 0]["order"]) == [0, 1, 2, 3]  # ... and it need not be among the selected GPUs
+        assert s[0, 1]["flags"] == 0                        # the only Hopper GPU is unhealthy -> filtered
+
+
+def test_mig_filter(kg, orc):
+    abi = kg.abi
+    nodes = np.array([make_node(abi, mig_free={2: 3}), make_node(abi)], dtype=abi.NODE_IMAGE)
+    for mode in (0, 1):
+        for count, want0 in ((3, True), (4, False)):
+            pods = np.array([make_pod(abi, 1, mig=(2, count))], dtype=abi.POD_REQ)
+            s, _, _ = orc.score_batch(abi, nodes, None, pods, mode=mode)
+            assert bool(s[0, 0]["flags"] & abi.F_ELIGIBLE) == want0
+            assert s[0, 1]["flags"] == 0
+        pods = np.array([make_pod(abi, 1, mig=(abi.MIG_UNKNOWN, 1))], dtype=abi.POD_REQ)
+        s, _, _ = orc.score_batch(abi, nodes, None, pods, mode=mode)
+        assert s[0, 0]["flags"] == 0
+
+
+def test_schedule_sequence_kat1_then_kat2(kg, orc):
+    abi = kg.abi
+    nodes = np.array([make_node(abi)], dtype=abi.NODE_IMAGE)
+    pods = np.array([make_pod(abi, 4, wl_id=1), make_pod(abi, 4, wl_id=2), make_pod(abi, 4, wl_id=3)], dtype=abi.POD_REQ)
+    for mode in (0, 1):
+        dec, led, _ = orc.schedule_queue(abi, nodes, None, pods, mode=mode)
+        assert order_list(dec[0]["order"]) == [0, 1, 2, 3] and int(dec[0]["total"]) == 100
+        assert order_list(dec[1]["order"]) == [4, 5, 6, 7] and int(dec[1]["total"]) == 96 and int(dec[1]["balance"]) == 87
+        assert dec[2]["node_idx"] == abi.NO_NODE          # "no eligible nodes found" (scheduler.go:138-141)
+        assert len(led) == 2
+
+
+def test_faithful_equals_indexed_on_synthetic(kg, orc):
+    abi, synth = kg.abi, kg.synth
+    for num, scale in ((1, 1.0), (2, 0.06), (3, 0.006)):
+        nodes, pods, led = synth.config(num, scale)
+        pods = pods[:60]
+        hint = synth.make_hint(len(pods), len(nodes), 0.05)
+        a = orc.score_batch(abi, nodes, led, pods, hint=hint, want_scores=True, topk=4, mode=0)
+        b = orc.score_batch(abi, nodes, led, pods, hint=hint, want_scores=True, topk=4, mode=1, threads=2)
+        assert a[0].tobytes() == b[0].tobytes() and a[1].tobytes() == b[1].tobytes()
+        assert a[2]["candidates"] == b[2]["candidates"] and a[2]["evaluations"] == len(pods) * len(nodes)
+        da = orc.schedule_queue(abi, nodes, led, pods, hint=hint, mode=0)
+        db = orc.schedule_queue(abi, nodes, led, pods, hint=hint, mode=1)
+        assert da[0].tobytes() == db[0].tobytes()
+        assert da[1].tobytes() == db[1].tobytes()
