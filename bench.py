@@ -1,0 +1,346 @@
+#!/usr/bin/env python
+"""bench.py — placement candidates scored / s on BASELINE.json's headline config.
+
+Workload (config.workload): configs[2], the 10,000-node x 8-GPU mixed cluster with a
+10,000-pod burst, reference greedy subset scoring (NVLinkOptimal, k ~ U{1..8}), 30% of the
+nodes pre-allocated.  One "step" = one stateless Filter+Prioritize pass of ALL pods over
+ALL nodes (scoreNodes per pod, reference src/scheduler/scheduler.go:182-203) producing the
+full P x N NodeScore matrix in HBM plus the best placement per pod.
+
+  value     device-resident: pods and outputs already in HBM (kgwe_score_batch_device).
+  e2e       the reference-facing C-ABI call kgwe_score_batch with HOST buffers: pod
+            descriptors copied host->device and the per-pod best placement copied
+            device->host inside the timed region, every step.
+  roofline  the scoring kernel (K1) alone: algorithmic bytes (784 B per (pod,node)
+            evaluation) / its CUDA-event duration, vs the measured HBM peak.
+  cpu_baseline / --impl reference
+            the faithful CPU restatement of the reference scorer (oracle/, the Go
+            toolchain is absent) on a bounded sample of the same workload, all host cores.
+
+N > 1 (torchrun): nodes are sharded by contiguous index range over the ranks (SURVEY.md
+8e), each rank scores all pods against its shard, local top-1 lists are all-gathered over
+NCCL and merged on every rank.  Total work is fixed => "scaling": "strong".
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as entry  # noqa: E402
+
+BYTES_PER_EVAL = 784            # 768 B node record read + 16 B NodeScore written
+METRIC = "placement_candidates_scored_per_sec"
+UNIT = "candidates/s"
+WORKLOAD = "BASELINE configs[2]: 10,000-node x 8-GPU mixed H100/A100/B200 cluster, 10,000-pod burst, greedy k-of-8 subset scoring (NVLinkOptimal, k~U{1..8}), 30% nodes pre-allocated"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="kgwe", choices=["kgwe", "reference"])
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink N and P (testing only; the default is the full config)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the bounded cpu_baseline sample")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(gpu_index)],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 8:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.f.name)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_reference_rate(kg, nodes, ledger, pods, seconds, cores):
+    """Faithful CPU restatement on a bounded sample: `cores` threads, whole-node sweep per pod."""
+    from oracle import binding as orc
+    t0 = time.time()
+    _, _, c = orc.score_batch(kg.abi, nodes, ledger, pods[:cores], want_scores=False, topk=1, mode=orc.FAITHFUL, threads=cores)
+    per_pod = max(c["seconds"], 1e-3)               # one pod per thread took this long
+    n = int(max(1, min(len(pods) // cores, seconds / per_pod))) * cores
+    _, _, c = orc.score_batch(kg.abi, nodes, ledger, pods[:n], want_scores=False, topk=1, mode=orc.FAITHFUL, threads=cores)
+    return {"value": c["candidates"] / c["seconds"], "evals_per_s": c["evaluations"] / c["seconds"], "pods": n,
+            "seconds": c["seconds"], "wall": time.time() - t0}
+
+
+def run_reference(args):
+    """--impl reference: the reference's own algorithm on host cores (faithful C++ restatement;
+    Go is not installed on this image).  Each step = a bounded sample of the workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    kg = entry.load_package()
+    entry.build_oracle()
+    from oracle import binding as orc
+    nodes, pods, ledger = kg.synth.config(3, args.scale)
+    cores = host_cores()
+    # calibrate: one pod per thread, then size a step so that (steps+warmup) steps fit ~150 s
+    _, _, c = orc.score_batch(kg.abi, nodes, ledger, pods[:cores], want_scores=False, topk=1, mode=orc.FAITHFUL, threads=cores)
+    per_round = max(c["seconds"], 1e-3)
+    rounds = int(max(1, min(len(pods) // cores, 150.0 / (args.steps + args.warmup) / per_round)))
+    n = rounds * cores
+    for w in range(args.warmup):
+        orc.score_batch(kg.abi, nodes, ledger, pods[w * n % len(pods):][:n], want_scores=False, topk=1, mode=orc.FAITHFUL, threads=cores)
+    cand = ev = 0
+    secs = 0.0
+    t0 = time.time()
+    for s in range(args.steps):
+        off = (s * n) % max(1, len(pods) - n + 1)
+        _, _, c = orc.score_batch(kg.abi, nodes, ledger, pods[off:off + n], want_scores=False, topk=1, mode=orc.FAITHFUL, threads=cores)
+        cand += c["candidates"]; ev += c["evaluations"]; secs += c["seconds"]
+    wall = time.time() - t0
+    v = cand / wall
+    sample = f"{n} pods x {len(nodes)} nodes per step ({n * len(nodes)} evaluations), ledger {len(ledger)} entries, {cores} threads"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": wall / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": {"workload": WORKLOAD, "n_nodes": len(nodes), "n_pods": len(pods), "sample_per_step": sample},
+        "evaluations_per_sec": ev / wall,
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "note": "faithful C++ restatement of scheduler.go:182-707 (Go toolchain absent); likely faster than Go"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def run_kgwe(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    kg = entry.build() if rank == 0 else None
+    if world > 1:
+        dist.barrier()
+    kg = kg or entry.load_package()
+    abi = kg.abi
+
+    nodes, pods, ledger = kg.synth.config(3, args.scale)
+    N, P = len(nodes), len(pods)
+    lo, hi = rank * N // world, (rank + 1) * N // world        # contiguous node shard of this rank
+    eng = kg.Engine(max_nodes=hi - lo, device=local_rank, node_base=lo)
+    eng.upsert_nodes(nodes[lo:hi])
+    for a in ledger:
+        if lo <= a["node_idx"] < hi:
+            eng.commit(a["wl_id"], a["node_idx"] - lo, a["gpu_mask"])
+    n_local = hi - lo
+
+    stream = torch.cuda.current_stream()
+    sptr = stream.cuda_stream
+    d_pods = torch.from_numpy(pods.view(np.uint8).reshape(P, abi.POD_REQ.itemsize)).to(dev)
+    d_scores = torch.empty((P, n_local, abi.NODE_SCORE.itemsize), dtype=torch.uint8, device=dev)
+    d_top = torch.empty((P, abi.PLACEMENT.itemsize), dtype=torch.uint8, device=dev)
+    d_gather = torch.empty((world, P, abi.PLACEMENT.itemsize), dtype=torch.uint8, device=dev) if world > 1 else None
+    d_merged = torch.empty((P, abi.PLACEMENT.itemsize), dtype=torch.uint8, device=dev) if world > 1 else None
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
+
+    def step_device():
+        flush.zero_()                                                    # L2 flush between steps
+        eng.score_batch_device(d_pods.data_ptr(), P, None, d_scores.data_ptr(), 1, d_top.data_ptr(), sptr)
+        if world > 1:
+            dist.all_gather_into_tensor(d_gather, d_top)
+            eng.topk_merge_device(d_gather.data_ptr(), world, P, 1, d_merged.data_ptr(), sptr)
+
+    def fence():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        step_device()
+    fence()
+    st0 = eng.stats()
+    clocks = ClockSampler(local_rank)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    fence()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(stream)
+    fence()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop()
+    st1 = eng.stats()
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+
+    # whole-job units: every rank scored P pods x its shard
+    cand_local = st1["candidates"] - st0["candidates"]
+    ev_local = st1["evaluations"] - st0["evaluations"]
+    tot = torch.tensor([cand_local, ev_local, st1["kernel_launches"] - st0["kernel_launches"]], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    cand_total, ev_total, launches = (float(x) for x in tot.tolist())
+    # K1 alone (events recorded by the engine on the launching stream, rank 0's shard)
+    k1_ms = (st1["score_kernel_ms"] - st0["score_kernel_ms"]) / max(1, st1["score_kernel_timed"] - st0["score_kernel_timed"])
+    k1_evals = P * n_local
+
+    # ---- e2e through the host-buffer C ABI: H2D pods + D2H best placement per pod, every step ----
+    h2d = P * abi.POD_REQ.itemsize
+    d2h = P * abi.PLACEMENT.itemsize
+    for _ in range(2):
+        eng.score_batch(pods, n_local, want_scores=False, topk=1)
+    fence()
+    c0 = eng.stats()["candidates"]
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        _, top = eng.score_batch(pods, n_local, want_scores=False, topk=1)
+        if world > 1:
+            g = torch.from_numpy(top.view(np.uint8).reshape(P, abi.PLACEMENT.itemsize)).to(dev, non_blocking=True)
+            dist.all_gather_into_tensor(d_gather, g)
+            eng.topk_merge_device(d_gather.data_ptr(), world, P, 1, d_merged.data_ptr(), sptr)
+            _ = d_merged.cpu()
+    fence()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    c = torch.tensor([eng.stats()["candidates"] - c0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+    e2e_value = float(c.item()) / float(t.item())
+
+    # ---- per-pod Prioritize latency: one kgwe_score_batch(P=1) C-ABI call per pod (N=1 only) ----
+    lat = None
+    if world == 1:
+        one = pods[:1].copy()
+        for i in range(200):
+            eng.score_batch(pods[i:i + 1], n_local, want_scores=False, topk=1)
+        xs = []
+        for i in range(2000):
+            q = pods[i % P:i % P + 1]
+            a = time.perf_counter()
+            eng.score_batch(q, n_local, want_scores=False, topk=1)
+            xs.append((time.perf_counter() - a) * 1e6)
+        xs = np.array(xs)
+        lat = {"n_nodes": N, "calls": len(xs), "p50_us": float(np.percentile(xs, 50)), "p99_us": float(np.percentile(xs, 99)), "max_us": float(xs.max())}
+        del one
+
+    # ---- stateful Schedule() queue throughput (reported beside the headline; N=1 only) ----
+    sched = None
+    if world == 1:
+        eng2 = kg.Engine(max_nodes=N, device=local_rank)
+        eng2.upsert_nodes(nodes)
+        eng2.seed_ledger(ledger)
+        q = pods[: min(P, 4000)]
+        a = time.perf_counter()
+        dec = eng2.schedule_queue(q)
+        w = time.perf_counter() - a
+        s2 = eng2.stats()
+        sched = {"pods": len(q), "wall_ms": w * 1e3, "gpu_ms": s2["last_call_gpu_ms"], "us_per_pod": s2["last_call_gpu_ms"] * 1e3 / len(q),
+                 "placed": int((dec["node_idx"] != abi.NO_NODE).sum()), "candidates_per_sec": s2["candidates"] / w}
+        eng2.close()
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        achieved = k1_evals * BYTES_PER_EVAL / (k1_ms * 1e-3) / 1e9
+        out = {
+            "metric": METRIC, "value": cand_total / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "n_nodes": N, "n_pods": P, "ledger_entries": int(len(ledger)), "mode": "greedy (reference parity)",
+                       "sharding": f"nodes by contiguous range over {world} rank(s)",
+                       "l2": "256 MiB buffer written between steps (inside the timed region); each step also writes a 1.6 GB score matrix (> L2)"},
+            "evaluations_per_sec": ev_total / (ms_total * 1e-3),
+            "candidates_per_step": cand_total / args.steps,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "call": "kgwe_score_batch(host pods, topk=1 -> host placements)"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "kernel": "kgwe::score_kernel", "ms_per_launch": k1_ms, "evaluations_per_launch": k1_evals,
+                         "bytes_per_evaluation": BYTES_PER_EVAL, "peak_source": peak_src,
+                         "note": "algorithmic bytes; the node image is L2-resident across pods so DRAM traffic is far lower (see profiles/)"},
+            "clocks": clk,
+        }
+        if lat:
+            out["prioritize_latency"] = lat
+        if sched:
+            out["stateful_queue"] = sched
+        if not args.no_cpu_baseline and world == 1:
+            entry.build_oracle()
+            cores = host_cores()
+            r = cpu_reference_rate(kg, nodes, ledger, pods, args.cpu_seconds, cores)
+            out["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": cores, "kind": "port",
+                                   "sample": f"{r['pods']} pods x {N} nodes ({r['pods'] * N} evaluations, {r['seconds']:.1f} s), ledger {len(ledger)} entries",
+                                   "evaluations_per_sec": r["evals_per_s"],
+                                   "note": "faithful C++ restatement of scheduler.go:182-707 (Go toolchain absent); likely faster than Go"}
+        print(json.dumps(out))
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_kgwe(args)
+
+
+if __name__ == "__main__":
+    main()

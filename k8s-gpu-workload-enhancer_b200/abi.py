@@ -59,7 +59,8 @@ class Stats(C.Structure):
     _fields_ = [("evaluations", C.c_uint64), ("candidates", C.c_uint64), ("scheduled", C.c_uint64),
                 ("failed", C.c_uint64), ("topology_optimal", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("last_call_gpu_ms", C.c_double),
-                ("n_nodes", C.c_uint32), ("n_allocations", C.c_uint32)]
+                ("n_nodes", C.c_uint32), ("n_allocations", C.c_uint32),
+                ("score_kernel_ms", C.c_double), ("score_kernel_timed", C.c_uint64)]
 
 
 def default_config(max_nodes, device=0, node_base=0):

@@ -87,6 +87,11 @@ struct kgwe_engine {
     PinBuf<uint8_t> h_hint;
     unsigned long long* h_counters = nullptr;
 
+    // K1 timing: event pairs recorded around each score_kernel launch, harvested by get_stats
+    static constexpr int kTimers = 64;
+    cudaEvent_t t0[kTimers] = {}, t1[kTimers] = {};
+    int timers_pending = 0;
+
     kgwe_stats stats;
     std::string err;
 };
@@ -206,9 +211,12 @@ int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, co
         best = e->d_best.p;
     }
     dim3 grid(n_tiles, chunks);
+    const bool timed = e->timers_pending < kgwe_engine::kTimers;
+    if (timed) CU(e, cudaEventRecord(e->t0[e->timers_pending], s));
     score_kernel<<<grid, SCORE_THREADS, score_smem_bytes(ppc), s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e),
                                                                    d_scores, best, e->params, e->d_counters);
     CU(e, cudaGetLastError());
+    if (timed) { CU(e, cudaEventRecord(e->t1[e->timers_pending], s)); e->timers_pending++; }
     e->stats.kernel_launches++;
     if (topk == 1) {
         const uint32_t threads = 256, pods_per_block = threads / 8;
@@ -290,7 +298,8 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
         e->h_counters[0] = e->h_counters[1] = 0;
         e->dirty_flag.assign(cfg->max_nodes, 0);
         cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, cfg->device);
-        ok = cudaFuncSetAttribute(score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK)) == cudaSuccess;
+        for (int i = 0; i < kgwe_engine::kTimers && ok; ++i) ok = cudaEventCreate(&e->t0[i]) == cudaSuccess && cudaEventCreate(&e->t1[i]) == cudaSuccess;
+        ok = ok && cudaFuncSetAttribute(score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK)) == cudaSuccess;
         int bps = 0;
         if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, schedule_kernel, SCORE_THREADS, 0) == cudaSuccess && bps > 0) e->sched_blocks_per_sm = bps;
     }
@@ -309,6 +318,7 @@ int kgwe_engine_destroy(kgwe_engine* e) {
     if (e->h_nodes) cudaFreeHost(e->h_nodes);
     if (e->d_counters) cudaFree(e->d_counters);
     if (e->h_counters) cudaFreeHost(e->h_counters);
+    for (int i = 0; i < kgwe_engine::kTimers; ++i) { if (e->t0[i]) cudaEventDestroy(e->t0[i]); if (e->t1[i]) cudaEventDestroy(e->t1[i]); }
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
     if (e->stream) cudaStreamDestroy(e->stream);
@@ -593,6 +603,13 @@ int kgwe_node_read(kgwe_engine* e, uint32_t idx, kgwe_node_image* out) {
 int kgwe_get_stats(kgwe_engine* e, kgwe_stats* out) {
     if (!e || !out) return KGWE_ERR_INVALID_ARG;
     std::lock_guard<std::mutex> lk(e->mu);
+    for (int i = 0; i < e->timers_pending; ++i) {       // harvest K1 timings (waits for those launches)
+        float ms = 0.f;
+        if (cudaEventSynchronize(e->t1[i]) == cudaSuccess && cudaEventElapsedTime(&ms, e->t0[i], e->t1[i]) == cudaSuccess) {
+            e->stats.score_kernel_ms += ms; e->stats.score_kernel_timed++;
+        }
+    }
+    e->timers_pending = 0;
     *out = e->stats;
     out->n_nodes = e->n_nodes;
     out->n_allocations = (uint32_t)e->ledger.size();

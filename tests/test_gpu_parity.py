@@ -1,0 +1,267 @@
+"""Parity tests proper: the CUDA engine, called through the C ABI, against the CPU oracle
+on the same inputs.  Bar: every integer/byte field bit-exact; EstimatedBandwidth (the only
+float output) must also be bit-exact here, tolerance 1e-6 relative is the stated ceiling."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from helpers import CUBE_EDGES, ledger_of, make_node, make_pod, order_list
+from test_oracle_kats import KATS, _node, check_expect
+
+pytestmark = pytest.mark.gpu
+REL_TOL = 1e-6
+
+
+def assert_same_placements(a, b):
+    for f in a.dtype.names:
+        if f == "est_bandwidth_gbps":
+            np.testing.assert_allclose(a[f], b[f], rtol=REL_TOL, atol=0)
+        else:
+            assert np.array_equal(a[f], b[f]), f
+    assert a.tobytes() == b.tobytes()      # and in fact bit-identical
+
+
+def engine_for(kg, nodes, ledger=None, **kw):
+    eng = kg.Engine(max_nodes=max(1, len(nodes)), **kw)
+    if len(nodes):
+        eng.upsert_nodes(nodes)
+    if ledger is not None:
+        eng.seed_ledger(ledger)
+    return eng
+
+
+@pytest.mark.parametrize("case", KATS["cases"], ids=[c["name"].split(" ")[0] + f"-{i}" for i, c in enumerate(KATS["cases"])])
+def test_kat_through_engine(kg, case):
+    abi = kg.abi
+    nodes = np.array([_node(abi, case["node"])], dtype=abi.NODE_IMAGE)
+    pods = np.array([make_pod(abi, **case["pod"])], dtype=abi.POD_REQ)
+    eng = engine_for(kg, nodes, ledger_of(abi, [tuple(x) for x in case["ledger"]]))
+    scores, top = eng.score_batch(pods, 1, want_scores=True, topk=1)
+    check_expect(abi, scores[0, 0], top[0, 0], case["expect"])
+    eng.close()
+
+
+@pytest.mark.parametrize("num,scale,npods", [(1, 1.0, 100), (2, 0.2, 200), (3, 0.03, 300), (5, 0.02, 160)])
+@pytest.mark.parametrize("with_hint", [False, True])
+def test_stateless_matrix_and_topk(kg, orc, num, scale, npods, with_hint):
+    abi, synth = kg.abi, kg.synth
+    nodes, pods, led = synth.config(num, scale)
+    pods = pods[:npods]
+    hint = synth.make_hint(len(pods), len(nodes), 0.03) if with_hint else None
+    eng = engine_for(kg, nodes, led)
+    for topk in (1, 5, 16):
+        scores, top = eng.score_batch(pods, len(nodes), hint=hint, want_scores=True, topk=topk)
+        o_scores, o_top, ctr = orc.score_batch(abi, nodes, led, pods, hint=hint, want_scores=True, topk=topk, threads=4)
+        assert scores.tobytes() == o_scores.tobytes()
+        assert_same_placements(top, o_top)
+    # top-k without the matrix (fused arg-max path for k=1, internal scratch for k>1)
+    for topk in (1, 3):
+        _, top = eng.score_batch(pods, len(nodes), hint=hint, want_scores=False, topk=topk)
+        _, o_top, _ = orc.score_batch(abi, nodes, led, pods, hint=hint, want_scores=False, topk=topk, threads=4)
+        assert_same_placements(top, o_top)
+    st = eng.stats()
+    assert st["evaluations"] == 5 * len(pods) * len(nodes)
+    assert st["candidates"] == 5 * ctr["candidates"]
+    eng.close()
+
+
+@pytest.mark.parametrize("num,scale,npods", [(1, 1.0, 100), (2, 0.1, 150), (3, 0.02, 400), (5, 0.01, 96)])
+def test_stateful_queue(kg, orc, num, scale, npods):
+    abi, synth = kg.abi, kg.synth
+    nodes, pods, led = synth.config(num, scale)
+    pods = pods[:npods]
+    eng = engine_for(kg, nodes, led)
+    dec = eng.schedule_queue(pods)
+    o_dec, o_led, _ = orc.schedule_queue(abi, nodes, led, pods)
+    assert_same_placements(dec, o_dec)
+    # the device image now carries the oracle's final ledger projection
+    alloc = np.zeros(len(nodes), np.uint8)
+    cnt = np.zeros(len(nodes), np.uint32)
+    for a in o_led:
+        alloc[a["node_idx"]] |= a["gpu_mask"]
+        cnt[a["node_idx"]] += 1
+    for n in range(len(nodes)):
+        rec = eng.read_node(n)
+        assert rec["allocated_mask"] == alloc[n] and rec["n_allocs"] == cnt[n]
+    st = eng.stats()
+    assert st["scheduled"] == int((o_dec["node_idx"] != abi.NO_NODE).sum())
+    assert st["failed"] == int((o_dec["node_idx"] == abi.NO_NODE).sum())
+    assert st["n_allocations"] == len(o_led)
+    # scoring after the queue sees the commits
+    s2, _ = eng.score_batch(pods[:20], len(nodes), want_scores=True)
+    o2, _, _ = orc.score_batch(abi, nodes, o_led, pods[:20], want_scores=True)
+    assert s2.tobytes() == o2.tobytes()
+    eng.close()
+
+
+def test_stateful_with_hint_and_multi_node_groups(kg, orc):
+    """More nodes than resident lane groups forces the multi-node-per-group path of the queue kernel."""
+    abi, synth = kg.abi, kg.synth
+    nodes = synth.make_cluster(24000, "mixed", seed=99)
+    pods = synth.make_pods(40, seed=99)
+    led = synth.make_ledger(nodes, 0.2, seed=99)
+    hint = synth.make_hint(len(pods), len(nodes), 0.001, seed=99)
+    eng = engine_for(kg, nodes, led)
+    dec = eng.schedule_queue(pods, hint=hint)
+    o_dec, _, _ = orc.schedule_queue(abi, nodes, led, pods, hint=hint)
+    assert_same_placements(dec, o_dec)
+    eng.close()
+
+
+def test_exhaustive_extension(kg, orc):
+    abi, synth = kg.abi, kg.synth
+    nodes, pods, led = synth.config(3, 0.02)
+    pods = pods[:200].copy()
+    eng = engine_for(kg, nodes, led)
+    g_scores, _ = eng.score_batch(pods, len(nodes), want_scores=True)
+    pods["flags"] = abi.POD_EXHAUSTIVE
+    scores, top = eng.score_batch(pods, len(nodes), want_scores=True, topk=2)
+    o_scores, o_top, _ = orc.score_batch(abi, nodes, led, pods, want_scores=True, topk=2, threads=4)
+    assert scores.tobytes() == o_scores.tobytes()
+    assert_same_placements(top, o_top)
+    # property: on symmetric bandwidth matrices the exhaustive topology score is >= the greedy one
+    assert (scores["topology"] >= g_scores["topology"]).all()
+    eng.close()
+
+
+def test_edge_cases(kg, orc):
+    abi = kg.abi
+    # empty cluster, empty pod list
+    eng = kg.Engine(max_nodes=4)
+    pods = np.array([make_pod(abi, 2)], dtype=abi.POD_REQ)
+    _, top = eng.score_batch(pods, 0, want_scores=False, topk=2)
+    assert (top["node_idx"] == abi.NO_NODE).all()
+    dec = eng.schedule_queue(pods)
+    assert dec[0]["node_idx"] == abi.NO_NODE
+    s, t = eng.score_batch(pods[:0], 0, want_scores=True, topk=1)
+    assert s.shape == (0, 0)
+    # ragged nodes: 0..8 GPUs, all-unhealthy, no links
+    nodes = np.array([make_node(abi, n_gpus=g) for g in range(9)] + [make_node(abi, unhealthy=range(8)), make_node(abi, links="none")],
+                     dtype=abi.NODE_IMAGE)
+    eng2 = engine_for(kg, nodes)
+    pods = np.array([make_pod(abi, k, pref=p, mem=m) for k in (0, 1, 2, 5, 8, 9, 100) for p in ("None", "NVLinkOptimal", "SameNUMA", "SamePCIeSwitch")
+                     for m in (0, 16, 2000)], dtype=abi.POD_REQ)
+    scores, top = eng2.score_batch(pods, len(nodes), want_scores=True, topk=16)
+    o_scores, o_top, _ = orc.score_batch(abi, nodes, None, pods, want_scores=True, topk=16)
+    assert scores.tobytes() == o_scores.tobytes()
+    assert_same_placements(top, o_top)
+    # invalid arguments are rejected, not computed
+    bad = pods[:1].copy(); bad["gpu_count"] = -1
+    with pytest.raises(kg.EngineError):
+        eng2.score_batch(bad, len(nodes))
+    nan_node = make_node(abi); nan_node["nvl_bw"][0][1] = np.nan
+    with pytest.raises(kg.EngineError):
+        eng2.upsert_node(0, nan_node)
+    with pytest.raises(kg.EngineError):
+        eng2.upsert_node(10_000, make_node(abi))
+    eng.close(); eng2.close()
+
+
+def test_incremental_updates_and_ledger(kg, orc):
+    abi, synth = kg.abi, kg.synth
+    nodes, pods, led = synth.config(2, 0.05)
+    pods = pods[:50]
+    eng = engine_for(kg, nodes, led)
+    # informer event: one node changes (a GPU goes unhealthy, memory drops)
+    nodes = nodes.copy()
+    nodes[7]["healthy_mask"] &= 0xF0
+    nodes[7]["free_bytes"][:] = 1 << 30
+    eng.upsert_node(7, nodes[7])
+    # node 3 deleted (discovery.go:597-600): the oracle sees it as an absent record
+    eng.remove_node(3)
+    o_nodes = nodes.copy(); o_nodes[3]["n_gpus"] = 0; o_nodes[3]["healthy_mask"] = 0
+    s, _ = eng.score_batch(pods, len(nodes), want_scores=True)
+    o, _, _ = orc.score_batch(abi, o_nodes, led, pods, want_scores=True)
+    keep = np.arange(len(nodes)) != 3
+    assert s[:, keep].tobytes() == o[:, keep].tobytes()
+    assert (s[:, 3]["flags"] == 0).all()
+    # ledger: release / unknown release / same wl_id overwrites (scheduler.go:699, 710-716)
+    first = led[0]
+    eng.release(first["wl_id"])
+    with pytest.raises(kg.EngineError) as ei:
+        eng.release(first["wl_id"])
+    assert ei.value.code == -5 and "allocation not found" in str(ei.value)
+    led2 = led[1:].copy()
+    eng.commit(led2[0]["wl_id"], 5, 0x81)                      # overwrite: moves to node 5
+    led2[0]["node_idx"], led2[0]["gpu_mask"] = 5, 0x81
+    s, _ = eng.score_batch(pods, len(nodes), want_scores=True)
+    o, _, _ = orc.score_batch(abi, o_nodes, led2, pods, want_scores=True)
+    assert s[:, keep].tobytes() == o[:, keep].tobytes()
+    # a queue that re-schedules a workload already in the ledger
+    again = pods[:6].copy()
+    again["wl_id"][2] = led2[3]["wl_id"]
+    again["wl_id"][4] = again["wl_id"][1]
+    dec = eng.schedule_queue(again)
+    o_dec, o_led, _ = orc.schedule_queue(abi, o_nodes, led2, again)
+    assert_same_placements(dec, o_dec)
+    assert eng.stats()["n_allocations"] == len(o_led)
+    s, _ = eng.score_batch(pods, len(nodes), want_scores=True)
+    o, _, _ = orc.score_batch(abi, o_nodes, o_led, pods, want_scores=True)
+    assert s[:, keep].tobytes() == o[:, keep].tobytes()
+    eng.close()
+
+
+def test_node_read_roundtrip(kg):
+    abi, synth = kg.abi, kg.synth
+    nodes = synth.make_cluster(40, "mixed", seed=5, partial_node_frac=0.3, mig_frac=0.5)
+    eng = engine_for(kg, nodes)
+    for n in (0, 13, 39):
+        rec = eng.read_node(n)
+        for f in ("pcie_bw", "free_bytes", "util", "nvl_present", "nvl_active", "numa", "pcie_switch", "arch", "mig_free", "n_gpus", "healthy_mask"):
+            assert np.array_equal(rec[f], nodes[n][f]), f
+        assert np.array_equal(rec["nvl_bw"], nodes[n]["nvl_bw"])
+    eng.close()
+
+
+def test_mig_and_arch_filters_synthetic(kg, orc):
+    abi, synth = kg.abi, kg.synth
+    nodes = synth.make_cluster(300, "mixed", seed=11, partial_node_frac=0.2, mig_frac=0.6, unhealthy_frac=0.1, inactive_link_frac=0.05)
+    pods = synth.make_pods(300, seed=11, arch_frac=0.5, mig_frac=0.5, minbw_choices=(0.0, 300.0, 700.0, 1000.0))
+    led = synth.make_ledger(nodes, 0.5, seed=11)
+    eng = engine_for(kg, nodes, led)
+    s, top = eng.score_batch(pods, len(nodes), want_scores=True, topk=8)
+    o, o_top, _ = orc.score_batch(abi, nodes, led, pods, want_scores=True, topk=8, threads=4)
+    assert s.tobytes() == o.tobytes()
+    assert_same_placements(top, o_top)
+    assert (s["flags"] & abi.F_MINBW).any() and (s["flags"] & abi.F_FALLBACK).any()
+    dec = eng.schedule_queue(pods)
+    o_dec, _, _ = orc.schedule_queue(abi, nodes, led, pods)
+    assert_same_placements(dec, o_dec)
+    eng.close()
+
+
+def test_full_size_properties(kg, orc):
+    """BASELINE config 3 at full size (10k nodes x 10k pods): oracle spot-checks plus
+    size-independent properties (arg-max of the matrix row == fused top-1, idempotence,
+    no GPU handed out twice by the stateful queue)."""
+    abi, synth = kg.abi, kg.synth
+    nodes, pods, led = synth.config(3)
+    eng = engine_for(kg, nodes, led)
+    N = len(nodes)
+    _, top_a = eng.score_batch(pods, N, want_scores=False, topk=1)
+    _, top_b = eng.score_batch(pods, N, want_scores=False, topk=1)
+    assert top_a.tobytes() == top_b.tobytes()
+    sample = np.arange(0, len(pods), 97)
+    s, top = eng.score_batch(pods[sample], N, want_scores=True, topk=1)
+    o, o_top, _ = orc.score_batch(abi, nodes, led, pods[sample], want_scores=True, topk=1, threads=8)
+    assert s.tobytes() == o.tobytes()
+    assert_same_placements(top, o_top)
+    assert top.tobytes() == top_a[sample].tobytes()
+    kept = (s["flags"] & abi.F_KEPT) != 0
+    best = np.where(kept, s["total"], -1).argmax(axis=1)        # first max = lowest index
+    assert np.array_equal(best.astype(np.uint32), top[:, 0]["node_idx"])
+    dec = eng.schedule_queue(pods[:3000])
+    o_dec, _, _ = orc.schedule_queue(abi, nodes, led, pods[:3000])
+    assert_same_placements(dec, o_dec)
+    used = {}
+    for a in led:
+        used[int(a["node_idx"])] = used.get(int(a["node_idx"]), 0) | int(a["gpu_mask"])
+    for d in dec:
+        if d["node_idx"] == abi.NO_NODE:
+            continue
+        n = int(d["node_idx"])
+        assert used.get(n, 0) & int(d["gpu_mask"]) == 0
+        used[n] = used.get(n, 0) | int(d["gpu_mask"])
+    eng.close()
