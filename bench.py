@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--impl", default="kgwe", choices=["kgwe", "reference"])
     ap.add_argument("--scale", type=float, default=1.0, help="shrink N and P (testing only; the default is the full config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernel-only", action="store_true", help="only the device-resident steps (for ncu runs; prints no bench value)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the bounded cpu_baseline sample")
     return ap.parse_args()
 
@@ -188,8 +189,10 @@ def run_kgwe(args):
             eng.commit(a["wl_id"], a["node_idx"] - lo, a["gpu_mask"])
     n_local = hi - lo
 
-    stream = torch.cuda.current_stream()
+    stream = torch.cuda.Stream(device=dev)        # a real (non-NULL) stream: kernels, NCCL and the timing events all go here
+    torch.cuda.set_stream(stream)
     sptr = stream.cuda_stream
+    assert sptr != 0
     d_pods = torch.from_numpy(pods.view(np.uint8).reshape(P, abi.POD_REQ.itemsize)).to(dev)
     d_scores = torch.empty((P, n_local, abi.NODE_SCORE.itemsize), dtype=torch.uint8, device=dev)
     d_top = torch.empty((P, abi.PLACEMENT.itemsize), dtype=torch.uint8, device=dev)
@@ -239,6 +242,11 @@ def run_kgwe(args):
     # K1 alone (events recorded by the engine on the launching stream, rank 0's shard)
     k1_ms = (st1["score_kernel_ms"] - st0["score_kernel_ms"]) / max(1, st1["score_kernel_timed"] - st0["score_kernel_timed"])
     k1_evals = P * n_local
+    if args.kernel_only:
+        if rank == 0:
+            print(json.dumps({"kernel_only": True, "ms_per_step": ms_total / args.steps, "k1_ms": k1_ms, "launches": launches}))
+        eng.close()
+        return
 
     # ---- e2e through the host-buffer C ABI: H2D pods + D2H best placement per pod, every step ----
     h2d = P * abi.POD_REQ.itemsize

@@ -610,6 +610,12 @@ int kgwe_get_stats(kgwe_engine* e, kgwe_stats* out) {
         }
     }
     e->timers_pending = 0;
+    // fold in candidates counted by asynchronous (device-pointer) calls since the last pull
+    if (cudaSetDevice(e->cfg.device) == cudaSuccess && cudaDeviceSynchronize() == cudaSuccess &&
+        cudaMemcpy(e->h_counters, e->d_counters, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost) == cudaSuccess &&
+        cudaMemset(e->d_counters, 0, 2 * sizeof(unsigned long long)) == cudaSuccess) {
+        e->stats.candidates += e->h_counters[1];
+    }
     *out = e->stats;
     out->n_nodes = e->n_nodes;
     out->n_allocations = (uint32_t)e->ledger.size();
