@@ -222,6 +222,35 @@ int kgwe_score_batch_device(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t
                             const uint8_t* d_hint_bitmap, kgwe_node_score* d_out_scores,
                             uint32_t topk, kgwe_placement* d_out_topk, void* cuda_stream);
 
+/* Best placement per pod WITHOUT any allocation inside the call.  No counterpart in the
+ * reference: this entry point exists for hosts of this library, not for a function of KGWE.
+ *
+ * kgwe_score_batch_device may grow the engine's arg-max key table with cudaMalloc when a
+ * batch is larger than any before it.  Some callers must never reach cudaMalloc once they
+ * are serving: a scheduler extender answering Prioritize under a deadline (cudaMalloc
+ * takes the driver's allocation lock and synchronises the whole device, so every other
+ * engine / shard in the process stalls behind it), and processes that handed all free
+ * device memory to another owner at start-up (a late cudaMalloc there can simply fail).
+ * This variant computes the same result as kgwe_score_batch_device(..., topk = 1, ...)
+ * with the key table in a fixed array that is part of the library image:
+ * KGWE_NOALLOC_MAX_PODS keys of 8 bytes = 128 KiB, held by every GPU that loads the
+ * library until the process exits.
+ *
+ *   - inputs and outputs are the caller's device buffers, as for kgwe_score_batch_device;
+ *     d_out_scores is optional, d_out_top1 gets n_pods placements;
+ *   - n_pods > KGWE_NOALLOC_MAX_PODS is refused with KGWE_ERR_TOO_LARGE (split the batch);
+ *   - the call makes no cudaMalloc / cudaFree / cudaMallocHost and uses no allocating
+ *     library routine; pending node upserts are still copied to the image first;
+ *   - the FIRST call on a device looks up the array's device address; make that first
+ *     call before starting any stream capture on that device;
+ *   - all calls on one GPU share the one array (it keeps whatever the previous call left,
+ *     so each call clears the slots it uses first): two calls that overlap on the same
+ *     GPU - different engines or different streams - race on it.  Serialise them. */
+#define KGWE_NOALLOC_MAX_PODS 16384u
+int kgwe_score_top1_noalloc(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods,
+                            const uint8_t* d_hint_bitmap, kgwe_node_score* d_out_scores,
+                            kgwe_placement* d_out_top1, void* cuda_stream);
+
 /* Merge R ranked lists per pod (layout [r][p][topk], device memory) into one
  * [p][topk] list in canonical order (score desc, node index asc).  This is the merge
  * every rank runs after the all-gather of local top-k lists. */

@@ -625,3 +625,67 @@ int kgwe_get_stats(kgwe_engine* e, kgwe_stats* out) {
 const char* kgwe_last_error(kgwe_engine* e) { return e ? e->err.c_str() : "null engine"; }
 
 }  // extern "C"
+
+// =======================================================================================
+// kgwe_score_top1_noalloc — see include/kgwe_engine.h.  Same kernels as the top-1 path of
+// kgwe_score_batch_device, but the arg-max key table is this fixed array instead of the
+// engine's growable cudaMalloc'd buffer, so nothing in the call can allocate.
+//
+// g_noalloc_keys is a device array: in host code its name is only a handle for the
+// runtime, not an address a kernel can use.  The usable device address is looked up once
+// per device (with that device current) via cudaGetSymbolAddress and cached.
+static __device__ __align__(256) unsigned long long g_noalloc_keys[KGWE_NOALLOC_MAX_PODS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+unsigned long long* g_noalloc_ptr[kMaxDevices] = {};
+
+// Called with the engine's device current.  First call per device resolves the address.
+int noalloc_table(kgwe_engine* e, unsigned long long** out) {
+    const int dev = e->cfg.device;
+    if (dev < 0 || dev >= kMaxDevices) return fail(e, KGWE_ERR_INVALID_ARG, "device ordinal %d not supported by the no-alloc path", dev);
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        void* p = nullptr;
+        cudaError_t rc = cudaGetSymbolAddress(&p, g_noalloc_keys);
+        if (rc != cudaSuccess || !p) return fail(e, KGWE_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_keys) on device %d: %s", dev, cudaGetErrorString(rc));
+        g_noalloc_ptr[dev] = static_cast<unsigned long long*>(p);
+    }
+    *out = g_noalloc_ptr[dev];
+    return KGWE_OK;
+}
+}  // namespace
+
+extern "C" int kgwe_score_top1_noalloc(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const uint8_t* d_hint,
+                                       kgwe_node_score* d_out, kgwe_placement* d_top1, void* cuda_stream) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if ((n_pods && !d_pods) || (n_pods && !d_top1)) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    if (n_pods > KGWE_NOALLOC_MAX_PODS)
+        return fail(e, KGWE_ERR_TOO_LARGE, "kgwe_score_top1_noalloc: %u pods exceed the fixed key table of %u (KGWE_NOALLOC_MAX_PODS); split the batch", n_pods, KGWE_NOALLOC_MAX_PODS);
+    CU(e, cudaSetDevice(e->cfg.device));
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : e->stream;
+    unsigned long long* keys = nullptr;
+    int rc = noalloc_table(e, &keys);
+    if (rc != KGWE_OK) return rc;
+    rc = flush_dirty(e, s);                 // H2D copies of pending upserts only; allocates nothing
+    if (rc != KGWE_OK) return rc;
+    if (n_pods == 0) return KGWE_OK;
+    if (e->n_nodes == 0) return fail(e, KGWE_ERR_INVALID_ARG, "kgwe_score_top1_noalloc: the cluster image is empty");
+    // the table still holds whatever an earlier (possibly failed) call left: clear our slots
+    CU(e, cudaMemsetAsync(keys, 0, (size_t)n_pods * sizeof(unsigned long long), s));
+    const uint32_t n_tiles = (e->n_nodes + TILE_NODES - 1) / TILE_NODES;
+    uint32_t chunks = std::max(1u, ((uint32_t)e->sm_count * 8u + n_tiles - 1) / n_tiles);
+    chunks = std::min(chunks, n_pods);
+    uint32_t ppc = std::min<uint32_t>((n_pods + chunks - 1) / chunks, MAX_PODS_PER_CHUNK);
+    chunks = (n_pods + ppc - 1) / ppc;
+    score_kernel<<<dim3(n_tiles, chunks), SCORE_THREADS, score_smem_bytes(ppc), s>>>(
+        e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e), d_out, keys, e->params, e->d_counters);
+    CU(e, cudaGetLastError());
+    finalize_top1_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), keys, d_top1, 1, e->params);
+    CU(e, cudaGetLastError());
+    e->stats.kernel_launches += 2;
+    e->stats.evaluations += (uint64_t)n_pods * e->n_present;
+    return KGWE_OK;
+}

@@ -85,6 +85,11 @@ class Engine:
         """All arguments are raw device addresses (ints) on this engine's GPU; asynchronous."""
         self._check(self.lib.kgwe_score_batch_device(self.h, d_pods, n_pods, d_hint, d_scores, topk, d_topk, stream))
 
+    def score_top1_noalloc(self, d_pods, n_pods, d_hint, d_scores, d_top1, stream=None):
+        """kgwe_score_top1_noalloc: best placement per pod with the key table in the library's
+        fixed device array (no allocation inside the call; at most abi.NOALLOC_MAX_PODS pods)."""
+        self._check(self.lib.kgwe_score_top1_noalloc(self.h, d_pods, n_pods, d_hint, d_scores, d_top1, stream))
+
     def topk_merge_device(self, d_lists, n_lists, n_pods, topk, d_out, stream=None):
         self._check(self.lib.kgwe_topk_merge_device(self.h, d_lists, n_lists, n_pods, topk, d_out, stream))
 
