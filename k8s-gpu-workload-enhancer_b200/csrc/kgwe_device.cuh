@@ -47,6 +47,25 @@ static_assert(sizeof(kgwe_pod_req) == 32 && sizeof(kgwe_node_score) == 16 && siz
 
 __host__ __device__ inline int bw_slot(int m, int c) { return (((c >> 1) ^ (m >> 1)) << 1) | (c & 1); }
 
+// DevNode.flags
+constexpr uint8_t NODE_PRESENT = 0x01;
+constexpr uint8_t NODE_INTEGRAL = 0x02;   // every link bandwidth is a whole number of GB/s (set by the host packer)
+
+// Integer form of one node's greedy inputs, built in shared memory by the scoring kernel for
+// nodes whose bandwidths are whole numbers (<= KGWE_MAX_BW_GBPS < 2^17).  Sums of such doubles
+// are exact in FP64, so int32 arithmetic yields the very same totals and the same comparisons
+// as the reference's float64 code.  Values are pre-scaled by 8 and the candidate's tie-break
+// code (7 - c) is folded into the low 3 bits through init[], so `max` over the eight running
+// sums IS the reference's "largest aggregate, first candidate on ties" rule:
+//   row[m][c]  = 8 * bw(c -> m) when that link is active, FAST_NEG otherwise (and on the diagonal,
+//                which retires a GPU from the candidates the step after it joins);
+//   init[c]    = 7 - c for an available GPU, FAST_NEG otherwise.
+// A running sum that ever met FAST_NEG stays negative (at most 8 of them: no int32 overflow).
+// Row chunks of 16 bytes are swizzled by (m >> 2) so 8 lanes on 8 rows are bank-conflict free.
+constexpr int32_t FAST_NEG = -(1 << 27);
+struct __align__(16) NodeFast { int32_t row[8][8]; int32_t init[8]; };
+__host__ __device__ inline int fast_slot(int m, int c) { return ((((c >> 2) ^ (m >> 2)) & 1) << 2) | (c & 3); }
+
 struct Params {          // kgwe_config, device copy
     int32_t wt, wr, wb, bonus;
     double  norm;
@@ -64,7 +83,9 @@ struct NodeCtx {
     uint64_t arch8;        // arch[0..7]
     uint64_t numa_pick, pcie_pick;    // byte k-1: first group (ascending key) with >= k members, else 0
     uint32_t numa_order, pcie_order;  // available GPUs in (key asc, index asc) order, 3 bits each
-    bool     valid;
+    uint64_t avail_prefix;            // byte k-1: the first k available GPUs (index order) as a mask
+    uint32_t avail_order;             // available GPUs in index order, 3 bits each
+    bool     valid, integral;
 };
 
 struct EvalOut {
@@ -103,7 +124,8 @@ __device__ inline void group_tables(uint64_t keys8, bool is_signed, uint32_t ava
 }
 
 __device__ inline void node_ctx_init(NodeCtx& c, const DevNode* rec, bool in_range) {
-    c.valid = in_range && (rec->flags & 1);
+    c.valid = in_range && (rec->flags & NODE_PRESENT);
+    c.integral = c.valid && (rec->flags & NODE_INTEGRAL);
     uint32_t ng = c.valid ? rec->n_gpus : 0;
     ng = ng > 8 ? 8 : ng;
     uint32_t avail = c.valid ? ((uint32_t)rec->healthy_mask & ~(uint32_t)rec->allocated_mask & ((1u << ng) - 1u)) : 0;
@@ -125,6 +147,15 @@ __device__ inline void node_ctx_init(NodeCtx& c, const DevNode* rec, bool in_ran
         int s = __double2int_rz(__dmul_rn(100.0, __dsub_rn(1.0, usage)));
         c.balance = s > 0 ? s : 0;
     }
+    c.avail_prefix = 0; c.avail_order = 0;
+    {
+        uint32_t m = avail, acc = 0; int i = 0;
+        while (m) {
+            const int b = __ffs(m) - 1;
+            acc |= 1u << b; c.avail_order |= (uint32_t)b << (3 * i); c.avail_prefix |= (uint64_t)acc << (8 * i);
+            m &= m - 1; ++i;
+        }
+    }
     if (c.valid) {
         group_tables(ld_u64(rec->numa), true, avail, c.numa_pick, c.numa_order);
         group_tables(ld_u64(rec->pcie_switch), false, avail, c.pcie_pick, c.pcie_order);
@@ -144,6 +175,49 @@ __device__ __forceinline__ uint32_t mask_of_order(uint32_t order, int k) {
     uint32_t sel = 0;
     for (int i = 0; i < k; ++i) sel |= 1u << ((order >> (3 * i)) & 7);
     return sel;
+}
+
+// First min(k, A) available GPUs in index order, from the per-node tables.
+__device__ __forceinline__ void first_k_avail(const NodeCtx& nc, int k, uint32_t& sel, uint32_t& order, int& n) {
+    n = k < nc.A ? k : nc.A;
+    if (n <= 0) { sel = 0; order = 0; n = 0; return; }
+    sel = (uint32_t)(nc.avail_prefix >> (8 * (n - 1))) & 0xffu;
+    order = nc.avail_order & (n >= 8 ? 0xffffffu : ((1u << (3 * n)) - 1u));
+}
+
+// Lane j's build step of NodeFast: row j (what each candidate gains when GPU j joins).
+__device__ __forceinline__ void node_fast_build(NodeFast* nf, const DevNode* rec, const NodeCtx& nc, int j) {
+    const uint32_t act = (uint32_t)(nc.colact >> (8 * j)) & 0xffu;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const double v = rec->bw_in[j][bw_slot(j, c)];
+        nf->row[j][fast_slot(j, c)] = ((act >> c & 1) && c != j) ? __double2int_rz(__dmul_rn(v, 8.0)) : FAST_NEG;
+    }
+    nf->init[j] = (nc.avail >> j & 1) ? (7 - j) : FAST_NEG;
+}
+
+// Integer twin of greedy_chain (see NodeFast).  Returns key = (total << 3) | (7 - s) when the
+// chain from start s reaches size k with total > 0, else 0; pay = join order | members << 24.
+__device__ __forceinline__ void greedy_chain_fast(const NodeFast* nf, int s, int k, int32_t& key, uint32_t& pay) {
+    key = 0; pay = 0;
+    const int4* ip = reinterpret_cast<const int4*>(nf->init);
+    int4 a = ip[0], b = ip[1];
+    if (nf->init[s] < 0) return;                       // start GPU not available
+    int32_t total = 0; uint32_t order = (uint32_t)s, members = 1u << s; int m = s;
+    for (int step = 1; step < k; ++step) {
+        const int4* rp = reinterpret_cast<const int4*>(nf->row[m]);
+        const int f = (m >> 2) & 1;
+        const int4 r0 = rp[f], r1 = rp[f ^ 1];
+        a.x += r0.x; a.y += r0.y; a.z += r0.z; a.w += r0.w;
+        b.x += r1.x; b.y += r1.y; b.z += r1.z; b.w += r1.w;
+        const int32_t best = __vimax3_s32(__vimax3_s32(a.x, a.y, a.z), __vimax3_s32(a.w, b.x, b.y), max(b.z, b.w));
+        if (best <= 7) return;                          // nobody fully connected with a positive aggregate
+        const int bc = 7 - (best & 7);
+        total += best >> 3;
+        order |= (uint32_t)bc << (3 * step); members |= 1u << bc;
+        m = bc;
+    }
+    if (total > 0) { key = (total << 3) | (7 - s); pay = order | (members << 24); }
 }
 
 // estimateBandwidth, scheduler.go:656-692: mean over pairs i<j (SelectedGPUs order) of GPU
@@ -229,8 +303,9 @@ __device__ __forceinline__ int nvlink_score(double total, int k, double norm) { 
 // isNodeEligible + scoreNode for one (pod,node), executed by the 8 lanes of a group
 // (lane j = `lane & 7`); the result is identical on all 8 lanes.  All 32 lanes of the warp
 // must call it together (segmented shuffles inside).
+template <bool FAST>
 __device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, const kgwe_pod_req& pod, const Params& P,
-                                         bool hinted, int lane, EvalOut& o) {
+                                         bool hinted, int lane, EvalOut& o, const NodeFast* nf = nullptr, bool warp_fast = false) {
     const int j = lane & 7;
     // k > 8 can never be eligible (A <= 8); clamp so no loop below depends on a huge count
     const int k = pod.gpu_count > 9 ? 9 : pod.gpu_count;
@@ -250,41 +325,55 @@ __device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, 
     int topo = 0; uint32_t sel = 0, order = 0; int nsel = 0; bool fallback = false;
     const bool nvl = pod.topology_pref == KGWE_TOPO_NVLINK_OPTIMAL || pod.topology_pref == KGWE_TOPO_NVLINK_REQUIRED;
     if (k <= 1) {
-        if (nc.A > 0) { topo = 100; take_first_k(nc.avail, 1, sel, order); nsel = 1; }
+        if (nc.A > 0) { topo = 100; first_k_avail(nc, 1, sel, order, nsel); }
     } else if (nvl) {
         // scoreNVLinkTopology, scheduler.go:336-373 (warp-uniform branch: one pod per warp pass)
-        uint64_t key; uint32_t pay;
-        const bool run = eligible;       // ineligible groups idle through the shuffles
-        if (!(pod.flags & KGWE_POD_EXHAUSTIVE)) {
-            bool ok = false; double total = 0.0; uint32_t ord = 0, mem = 0;
-            if (run) greedy_chain(rec, nc, j, k, ok, total, ord, mem);
-            key = (ok && total > 0.0) ? (uint64_t)__double_as_longlong(total) : 0ull;
-            pay = ord;
+        const bool exhaustive = pod.flags & KGWE_POD_EXHAUSTIVE;
+        bool found; double win_total;
+        if (FAST && warp_fast && !exhaustive) {
+            // all four nodes of this warp have whole-number bandwidths: integer chains, 32-bit winner
+            int32_t key = 0; uint32_t pay = 0;
+            if (eligible) greedy_chain_fast(nf, j, k, key, pay);
+#pragma unroll
+            for (int off = 4; off >= 1; off >>= 1) key = max(key, __shfl_xor_sync(0xffffffffu, key, off, 8));
+            pay = __shfl_sync(0xffffffffu, pay, 7 - (key & 7), 8);
+            found = key > 0; win_total = (double)(key >> 3);
+            order = pay & 0xffffffu; sel = pay >> 24;
             o.candidates = (uint32_t)nc.A;
         } else {
-            double best = 0.0; uint32_t bm = 0;
-            if (run) exhaustive_lane(rec, nc, j, k, best, bm);
-            key = best > 0.0 ? (uint64_t)__double_as_longlong(best) : 0ull;
-            pay = bm;
-            uint32_t c = 1; for (int i = 1; i <= k; ++i) c = c * (uint32_t)(nc.A - k + i) / (uint32_t)i;
-            o.candidates = nc.A >= k ? c : 0;
-        }
-        // winner over the 8 lanes: strictly largest total, then lowest start index / lowest mask
-        // (greedy: first start in available order, scheduler.go:428-431)
-        uint32_t tie = (pod.flags & KGWE_POD_EXHAUSTIVE) ? pay : (uint32_t)j;
+            uint64_t key; uint32_t pay;
+            if (!exhaustive) {
+                bool ok = false; double total = 0.0; uint32_t ord = 0, mem = 0;
+                if (eligible) greedy_chain(rec, nc, j, k, ok, total, ord, mem);
+                key = (ok && total > 0.0) ? (uint64_t)__double_as_longlong(total) : 0ull;
+                pay = ord | (mem << 24);
+                o.candidates = (uint32_t)nc.A;
+            } else {
+                double best = 0.0; uint32_t bm = 0;
+                if (eligible) exhaustive_lane(rec, nc, j, k, best, bm);
+                key = best > 0.0 ? (uint64_t)__double_as_longlong(best) : 0ull;
+                pay = bm;
+                uint32_t c = 1; for (int i = 1; i <= k; ++i) c = c * (uint32_t)(nc.A - k + i) / (uint32_t)i;
+                o.candidates = nc.A >= k ? c : 0;
+            }
+            // winner over the 8 lanes: strictly largest total, then lowest start index / lowest mask
+            // (greedy: first start in available order, scheduler.go:428-431)
+            uint32_t tie = exhaustive ? pay : (uint32_t)j;
 #pragma unroll
-        for (int off = 4; off >= 1; off >>= 1) {
-            uint64_t okey = __shfl_xor_sync(0xffffffffu, key, off, 8);
-            uint32_t otie = __shfl_xor_sync(0xffffffffu, tie, off, 8);
-            uint32_t opay = __shfl_xor_sync(0xffffffffu, pay, off, 8);
-            if (okey > key || (okey == key && otie < tie)) { key = okey; tie = otie; pay = opay; }
+            for (int off = 4; off >= 1; off >>= 1) {
+                uint64_t okey = __shfl_xor_sync(0xffffffffu, key, off, 8);
+                uint32_t otie = __shfl_xor_sync(0xffffffffu, tie, off, 8);
+                uint32_t opay = __shfl_xor_sync(0xffffffffu, pay, off, 8);
+                if (okey > key || (okey == key && otie < tie)) { key = okey; tie = otie; pay = opay; }
+            }
+            found = key != 0ull; win_total = __longlong_as_double((long long)key);
+            if (exhaustive) take_first_k(pay, k, sel, order);
+            else { order = pay & 0xffffffu; sel = pay >> 24; }
         }
-        if (key == 0ull) {               // no fully connected group: scheduler.go:358-365
-            topo = 30; fallback = true; take_first_k(nc.avail, k, sel, order); nsel = k;
+        if (!found) {                    // no fully connected group: scheduler.go:358-365
+            topo = 30; fallback = true; first_k_avail(nc, k, sel, order, nsel);
         } else {
-            topo = nvlink_score(__longlong_as_double((long long)key), k, P.norm);
-            if (pod.flags & KGWE_POD_EXHAUSTIVE) take_first_k(pay, k, sel, order);
-            else { order = pay; sel = mask_of_order(order, k); }
+            topo = nvlink_score(win_total, k, P.norm);
             nsel = k;
         }
     } else if (pod.topology_pref == KGWE_TOPO_SAME_NUMA || pod.topology_pref == KGWE_TOPO_SAME_PCIE_SWITCH) {
@@ -300,8 +389,7 @@ __device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, 
         }
     } else {
         topo = 50;
-        int n = k < nc.A ? k : nc.A;
-        take_first_k(nc.avail, n, sel, order); nsel = n;
+        first_k_avail(nc, k, sel, order, nsel);
     }
     if (!eligible) { o.candidates = 1; return; }
     // --- calculateResourceScore, scheduler.go:516-553 ---

@@ -113,6 +113,7 @@ int to_device_record(kgwe_engine* e, const kgwe_node_image& in, DevNode& out) {
     const int ng = in.n_gpus;
     const uint8_t gm = (uint8_t)((1u << ng) - 1u);
     memset(&out, 0, sizeof out);
+    bool integral = true;
     for (int i = 0; i < ng; ++i) {
         const uint8_t present = in.nvl_present[i] & gm & (uint8_t)~(1u << i);
         const uint8_t active = in.nvl_active[i] & present;
@@ -121,6 +122,7 @@ int to_device_record(kgwe_engine* e, const kgwe_node_image& in, DevNode& out) {
             double bw = (present >> j & 1) ? in.nvl_bw[i][j] : 0.0;
             if (!(bw >= 0.0) || !(bw <= KGWE_MAX_BW_GBPS)) return fail(e, KGWE_ERR_INVALID_ARG, "nvl_bw[%d][%d]=%g outside [0,%g]", i, j, bw, KGWE_MAX_BW_GBPS);
             if (bw == 0.0) bw = 0.0;                              // -0.0 -> +0.0
+            if (bw != std::floor(bw)) integral = false;
             out.bw_in[j][bw_slot(j, i)] = bw;                     // i's link to j
             if (active >> j & 1) out.act_in[j] |= (uint8_t)(1u << i);
         }
@@ -131,7 +133,8 @@ int to_device_record(kgwe_engine* e, const kgwe_node_image& in, DevNode& out) {
         out.numa[i] = in.numa[i]; out.pcie_switch[i] = in.pcie_switch[i]; out.arch[i] = in.arch[i];
     }
     memcpy(out.mig_free, in.mig_free, sizeof out.mig_free);
-    out.n_gpus = (uint8_t)ng; out.healthy_mask = in.healthy_mask & gm; out.flags = 1;
+    out.n_gpus = (uint8_t)ng; out.healthy_mask = in.healthy_mask & gm;
+    out.flags = NODE_PRESENT | (integral ? NODE_INTEGRAL : 0);
     return KGWE_OK;
 }
 
@@ -149,7 +152,7 @@ void to_abi_record(const DevNode& in, kgwe_node_image& out) {
     }
     memcpy(out.mig_free, in.mig_free, sizeof out.mig_free);
     out.n_gpus = in.n_gpus; out.healthy_mask = in.healthy_mask; out.allocated_mask = in.allocated_mask;
-    out.flags = in.flags; out.n_allocs = in.n_allocs;
+    out.flags = in.flags & NODE_PRESENT; out.n_allocs = in.n_allocs;
 }
 
 void mark_dirty(kgwe_engine* e, uint32_t idx) {
@@ -187,7 +190,7 @@ int validate_pods(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n) {
 
 uint32_t hint_row_bytes(const kgwe_engine* e) { return (e->n_nodes + 7) / 8; }
 
-size_t score_smem_bytes(uint32_t pods_per_chunk) { return (size_t)TILE_NODES * sizeof(DevNode) + (size_t)pods_per_chunk * 8 + 16; }
+size_t score_smem_bytes(uint32_t pods_per_chunk) { return (size_t)TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast)) + (size_t)pods_per_chunk * 8 + 16; }
 
 // Launch K1 (+K1b / K2) for n_pods pods whose descriptors, hint rows and outputs are in
 // device memory.  d_scores may be null unless topk > 1.

@@ -70,7 +70,7 @@ __device__ __forceinline__ void store_no_placement(kgwe_placement* dst) {
 }
 
 // ---------------------------------------------------------------------------------------
-// K1.  dynamic smem: [tile: TILE_NODES x 768 B][keys: pods_per_chunk x 8 B][mbarrier 8 B]
+// K1.  dynamic smem: [tile: TILE_NODES x 768 B][fast: TILE_NODES x 288 B][keys: pods_per_chunk x 8 B][mbarrier 8 B]
 __global__ void __launch_bounds__(SCORE_THREADS, 2)
 score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
              const kgwe_pod_req* __restrict__ pods, uint32_t n_pods, uint32_t pods_per_chunk,
@@ -79,7 +79,8 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
              Params P, unsigned long long* __restrict__ counters) {
     extern __shared__ __align__(128) unsigned char smem[];
     DevNode* tile = reinterpret_cast<DevNode*>(smem);
-    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem + TILE_NODES * sizeof(DevNode));
+    NodeFast* fast = reinterpret_cast<NodeFast*>(smem + TILE_NODES * sizeof(DevNode));
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem + TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast)));
     uint64_t* bar = reinterpret_cast<uint64_t*>(keys + pods_per_chunk);
 
     const int tid = threadIdx.x, lane = tid & 31, grp = tid >> 3;
@@ -103,13 +104,19 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     const DevNode* rec = tile + grp;
     NodeCtx nc;
     node_ctx_init(nc, rec, grp < (int)tile_count);
+    // integer form of the greedy inputs; usable when all four nodes of the warp are whole-number
+    NodeFast* nf = fast + grp;
+    const bool warp_fast = __all_sync(0xffffffffu, nc.integral || !nc.valid);
+    if (nc.integral) node_fast_build(nf, rec, nc, lane & 7);
+    else nf->init[lane & 7] = FAST_NEG;
+    __syncwarp();
     const uint32_t gnode = P.node_base + node;
     unsigned long long cand = 0;
 
     for (uint32_t p = p_begin; p < p_end; ++p) {
         const kgwe_pod_req pod = load_pod(pods, p);
         EvalOut o;
-        evaluate(rec, nc, pod, P, hint_bit(hint, hint_row_bytes, p, node), lane, o);
+        evaluate<true>(rec, nc, pod, P, hint_bit(hint, hint_row_bytes, p, node), lane, o, nf, warp_fast);
         if ((lane & 7) == 0 && grp < (int)tile_count) {
             cand += o.candidates;
             if (out) {
@@ -152,7 +159,7 @@ finalize_top1_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, const 
     NodeCtx nc;
     node_ctx_init(nc, rec, live && key != 0ull && node < n_nodes);
     EvalOut o;
-    evaluate(rec, nc, pod, P, live && hint_bit(hint, hint_row_bytes, p, node), lane, o);
+    evaluate<false>(rec, nc, pod, P, live && hint_bit(hint, hint_row_bytes, p, node), lane, o);
     if (live && (lane & 7) == 0) {
         if (key == 0ull) store_no_placement(out + (size_t)p * out_stride);
         else store_placement(out + (size_t)p * out_stride, P.node_base + node, o, est_bandwidth(rec, o.order, (int)((o.order >> 24) & 15)));
@@ -260,7 +267,7 @@ schedule_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict
             const DevNode* rec = nodes + node;
             if (!single) node_ctx_init(nc, rec, node < n_nodes);
             EvalOut o;
-            evaluate(rec, nc, pod, P, node < n_nodes && hint_bit(hint, hint_row_bytes, p, node), lane, o);
+            evaluate<false>(rec, nc, pod, P, node < n_nodes && hint_bit(hint, hint_row_bytes, p, node), lane, o);
             if (node < n_nodes) { cand += o.candidates; evals += 1; }
             const unsigned long long key = (o.flags & KGWE_F_KEPT) ? rank_key(o.total, P.node_base + node) : 0ull;
             if (key > mykey) { mykey = key; keep = o; keepnode = node; }
