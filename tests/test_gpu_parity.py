@@ -265,3 +265,27 @@ def test_full_size_properties(kg, orc):
         assert used.get(n, 0) & int(d["gpu_mask"]) == 0
         used[n] = used.get(n, 0) | int(d["gpu_mask"])
     eng.close()
+
+
+def test_fractional_bandwidths_take_the_fp64_path(kg, orc):
+    """Whole-number bandwidths use the integer chains; anything else must fall back to the
+    FP64 chains, also when both kinds of node share a warp.  Random doubles make the order of
+    the float64 additions matter, so this also pins the summation order."""
+    abi, synth = kg.abi, kg.synth
+    nodes = synth.make_cluster(700, "mixed", seed=21, unhealthy_frac=0.05, inactive_link_frac=0.03)
+    rng = synth.SplitMix64(77)
+    frac = rng.uniform(len(nodes)) < 0.5
+    jitter = 0.5 + rng.uniform(len(nodes) * 64).reshape(len(nodes), 8, 8)     # asymmetric, irrational-looking
+    nodes["nvl_bw"] = np.where(frac[:, None, None], nodes["nvl_bw"] * jitter, nodes["nvl_bw"])
+    nodes["nvl_bw"][5] *= 0.0                       # active links of zero bandwidth never extend a group
+    pods = synth.make_pods(257, seed=21, k_lo=2, pref_probs=(0, 0.8, 0.2, 0, 0), minbw_choices=(0.0, 500.0))
+    led = synth.make_ledger(nodes, 0.3, seed=21)
+    eng = engine_for(kg, nodes, led)
+    s, top = eng.score_batch(pods, len(nodes), want_scores=True, topk=4)
+    o, o_top, _ = orc.score_batch(abi, nodes, led, pods, want_scores=True, topk=4, threads=4)
+    assert s.tobytes() == o.tobytes()
+    assert_same_placements(top, o_top)
+    dec = eng.schedule_queue(pods)
+    o_dec, _, _ = orc.schedule_queue(abi, nodes, led, pods)
+    assert_same_placements(dec, o_dec)
+    eng.close()
