@@ -300,17 +300,22 @@ __device__ __forceinline__ int nvlink_score(double total, int k, double norm) { 
     return __double2int_rz(__dadd_rn(50.0, __dmul_rn(50.0, ratio)));
 }
 
-// isNodeEligible + scoreNode for one (pod,node), executed by the 8 lanes of a group
-// (lane j = `lane & 7`); the result is identical on all 8 lanes.  All 32 lanes of the warp
-// must call it together (segmented shuffles inside).
-template <bool FAST>
-__device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, const kgwe_pod_req& pod, const Params& P,
-                                         bool hinted, int lane, EvalOut& o, const NodeFast* nf = nullptr, bool warp_fast = false) {
-    const int j = lane & 7;
-    // k > 8 can never be eligible (A <= 8); clamp so no loop below depends on a huge count
-    const int k = pod.gpu_count > 9 ? 9 : pod.gpu_count;
-    o.total = o.topo = o.res = o.bal = 0; o.mask = o.order = o.flags = 0; o.candidates = 1;
-    // --- Filter: isNodeEligible, scheduler.go:206-241 ---
+// ---- one evaluation, in three parts ----------------------------------------------------
+// eval_filter : isNodeEligible (Filter)                                   scheduler.go:206-241
+// NVLink group search (greedy chains / exhaustive), only for NVLink preferences with k >= 2
+// eval_finish : the rest of calculateTopologyScore + resource/balance/total scheduler.go:244-333, 516-578
+// `evaluate` strings them together for one pod per 8-lane group; the scoring kernel's octet
+// path calls the parts itself so that each lane finishes a different pod.
+
+__device__ __forceinline__ int clamp_k(int gpu_count) {
+    // k > 8 can never be eligible (A <= 8); clamp so no loop depends on a huge count
+    return gpu_count > 9 ? 9 : gpu_count;
+}
+__device__ __forceinline__ bool is_nvlink_pref(const kgwe_pod_req& pod) {
+    return pod.topology_pref == KGWE_TOPO_NVLINK_OPTIMAL || pod.topology_pref == KGWE_TOPO_NVLINK_REQUIRED;
+}
+
+__device__ __forceinline__ bool eval_filter(const DevNode* rec, const NodeCtx& nc, const kgwe_pod_req& pod, int k) {
     bool eligible = nc.valid && k >= 0 && nc.A >= k;
     if (pod.arch != KGWE_ARCH_ANY) {
         uint32_t match = 0;
@@ -321,55 +326,23 @@ __device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, 
         int have = (pod.mig_profile >= 1 && pod.mig_profile <= KGWE_MIG_PROFILES && nc.valid) ? rec->mig_free[pod.mig_profile - 1] : 0;
         eligible = eligible && have >= pod.mig_count;
     }
-    // --- Prioritize: calculateTopologyScore, scheduler.go:303-333 ---
-    int topo = 0; uint32_t sel = 0, order = 0; int nsel = 0; bool fallback = false;
-    const bool nvl = pod.topology_pref == KGWE_TOPO_NVLINK_OPTIMAL || pod.topology_pref == KGWE_TOPO_NVLINK_REQUIRED;
+    return eligible;
+}
+
+// For NVLink preferences with k >= 2 the caller passes the group search's outcome:
+// found / win_total / sel / order (SelectedGPUs) and the candidate count.
+__device__ __forceinline__ void eval_finish(const DevNode* rec, const NodeCtx& nc, const kgwe_pod_req& pod, const Params& P,
+                                            bool hinted, bool eligible, int k,
+                                            bool found, double win_total, uint32_t sel, uint32_t order, uint32_t candidates,
+                                            EvalOut& o) {
+    o.total = o.topo = o.res = o.bal = 0; o.mask = o.order = o.flags = 0; o.candidates = 1;
+    if (!eligible) return;
+    int topo = 0; int nsel = 0; bool fallback = false;
     if (k <= 1) {
+        sel = 0; order = 0;
         if (nc.A > 0) { topo = 100; first_k_avail(nc, 1, sel, order, nsel); }
-    } else if (nvl) {
-        // scoreNVLinkTopology, scheduler.go:336-373 (warp-uniform branch: one pod per warp pass)
-        const bool exhaustive = pod.flags & KGWE_POD_EXHAUSTIVE;
-        bool found; double win_total;
-        if (FAST && warp_fast && !exhaustive) {
-            // all four nodes of this warp have whole-number bandwidths: integer chains, 32-bit winner
-            int32_t key = 0; uint32_t pay = 0;
-            if (eligible) greedy_chain_fast(nf, j, k, key, pay);
-#pragma unroll
-            for (int off = 4; off >= 1; off >>= 1) key = max(key, __shfl_xor_sync(0xffffffffu, key, off, 8));
-            pay = __shfl_sync(0xffffffffu, pay, 7 - (key & 7), 8);
-            found = key > 0; win_total = (double)(key >> 3);
-            order = pay & 0xffffffu; sel = pay >> 24;
-            o.candidates = (uint32_t)nc.A;
-        } else {
-            uint64_t key; uint32_t pay;
-            if (!exhaustive) {
-                bool ok = false; double total = 0.0; uint32_t ord = 0, mem = 0;
-                if (eligible) greedy_chain(rec, nc, j, k, ok, total, ord, mem);
-                key = (ok && total > 0.0) ? (uint64_t)__double_as_longlong(total) : 0ull;
-                pay = ord | (mem << 24);
-                o.candidates = (uint32_t)nc.A;
-            } else {
-                double best = 0.0; uint32_t bm = 0;
-                if (eligible) exhaustive_lane(rec, nc, j, k, best, bm);
-                key = best > 0.0 ? (uint64_t)__double_as_longlong(best) : 0ull;
-                pay = bm;
-                uint32_t c = 1; for (int i = 1; i <= k; ++i) c = c * (uint32_t)(nc.A - k + i) / (uint32_t)i;
-                o.candidates = nc.A >= k ? c : 0;
-            }
-            // winner over the 8 lanes: strictly largest total, then lowest start index / lowest mask
-            // (greedy: first start in available order, scheduler.go:428-431)
-            uint32_t tie = exhaustive ? pay : (uint32_t)j;
-#pragma unroll
-            for (int off = 4; off >= 1; off >>= 1) {
-                uint64_t okey = __shfl_xor_sync(0xffffffffu, key, off, 8);
-                uint32_t otie = __shfl_xor_sync(0xffffffffu, tie, off, 8);
-                uint32_t opay = __shfl_xor_sync(0xffffffffu, pay, off, 8);
-                if (okey > key || (okey == key && otie < tie)) { key = okey; tie = otie; pay = opay; }
-            }
-            found = key != 0ull; win_total = __longlong_as_double((long long)key);
-            if (exhaustive) take_first_k(pay, k, sel, order);
-            else { order = pay & 0xffffffu; sel = pay >> 24; }
-        }
+    } else if (is_nvlink_pref(pod)) {
+        o.candidates = candidates;
         if (!found) {                    // no fully connected group: scheduler.go:358-365
             topo = 30; fallback = true; first_k_avail(nc, k, sel, order, nsel);
         } else {
@@ -378,11 +351,12 @@ __device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, 
         }
     } else if (pod.topology_pref == KGWE_TOPO_SAME_NUMA || pod.topology_pref == KGWE_TOPO_SAME_PCIE_SWITCH) {
         const bool numa = pod.topology_pref == KGWE_TOPO_SAME_NUMA;
-        uint64_t pick = numa ? nc.numa_pick : nc.pcie_pick;
-        uint32_t gorder = numa ? nc.numa_order : nc.pcie_order;
-        uint32_t grp = k <= 8 ? (uint32_t)((pick >> (8 * (k - 1))) & 0xff) : 0;
+        const uint64_t pick = numa ? nc.numa_pick : nc.pcie_pick;
+        const uint32_t gorder = numa ? nc.numa_order : nc.pcie_order;
+        const uint32_t grp = (uint32_t)((pick >> (8 * (k - 1))) & 0xff);      // 2 <= k <= A <= 8 here
+        sel = 0; order = 0;
         if (grp) { topo = numa ? 90 : 80; take_first_k(grp, k, sel, order); nsel = k; }
-        else if (nc.A >= k) {
+        else {
             topo = numa ? 50 : 40; fallback = true;
             order = gorder & ((k >= 8) ? 0xffffffu : ((1u << (3 * k)) - 1u));
             sel = mask_of_order(order, k); nsel = k;
@@ -391,11 +365,10 @@ __device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, 
         topo = 50;
         first_k_avail(nc, k, sel, order, nsel);
     }
-    if (!eligible) { o.candidates = 1; return; }
     // --- calculateResourceScore, scheduler.go:516-553 ---
     int res = 0;
     if (nc.A > 0) {
-        uint64_t required = (uint64_t)(uint32_t)pod.min_memory_gb * 1073741824ull * (uint64_t)(uint32_t)k;
+        const uint64_t required = (uint64_t)(uint32_t)pod.min_memory_gb * 1073741824ull * (uint64_t)(uint32_t)k;
         res = 50 + (nc.sum_free >= required * 2 ? 25 : (nc.sum_free >= required ? 10 : 0)) + nc.util_bonus;
         res = res > 100 ? 100 : res;
     }
@@ -412,6 +385,68 @@ __device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, 
     if (kept) flags |= KGWE_F_KEPT;
     o.total = total; o.topo = topo; o.res = res; o.bal = nc.balance;
     o.mask = sel; o.order = order | ((uint32_t)nsel << 24); o.flags = flags;
+}
+
+// Winner of the 8 integer chains of a group: key = (total << 3) | (7 - start).
+__device__ __forceinline__ void fast_group_winner(int32_t& key, uint32_t& pay) {
+#pragma unroll
+    for (int off = 4; off >= 1; off >>= 1) key = max(key, __shfl_xor_sync(0xffffffffu, key, off, 8));
+    pay = __shfl_sync(0xffffffffu, pay, 7 - (key & 7), 8);
+}
+
+// isNodeEligible + scoreNode for one (pod,node), executed by the 8 lanes of a group
+// (lane j = `lane & 7`); the result is identical on all 8 lanes.  All 32 lanes of the warp
+// must call it together (segmented shuffles inside) with the same pod.
+template <bool FAST>
+__device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, const kgwe_pod_req& pod, const Params& P,
+                                         bool hinted, int lane, EvalOut& o, const NodeFast* nf = nullptr, bool warp_fast = false) {
+    const int j = lane & 7;
+    const int k = clamp_k(pod.gpu_count);
+    const bool eligible = eval_filter(rec, nc, pod, k);
+    bool found = false; double win_total = 0.0; uint32_t sel = 0, order = 0, candidates = 1;
+    if (k >= 2 && is_nvlink_pref(pod)) {
+        // scoreNVLinkTopology, scheduler.go:336-373 (warp-uniform branch: one pod per warp pass)
+        const bool exhaustive = pod.flags & KGWE_POD_EXHAUSTIVE;
+        if (FAST && warp_fast && !exhaustive) {
+            // all four nodes of this warp have whole-number bandwidths: integer chains, 32-bit winner
+            int32_t key = 0; uint32_t pay = 0;
+            if (eligible) greedy_chain_fast(nf, j, k, key, pay);
+            fast_group_winner(key, pay);
+            found = key > 0; win_total = (double)(key >> 3);
+            order = pay & 0xffffffu; sel = pay >> 24;
+            candidates = (uint32_t)nc.A;
+        } else {
+            uint64_t key; uint32_t pay;
+            if (!exhaustive) {
+                bool ok = false; double total = 0.0; uint32_t ord = 0, mem = 0;
+                if (eligible) greedy_chain(rec, nc, j, k, ok, total, ord, mem);
+                key = (ok && total > 0.0) ? (uint64_t)__double_as_longlong(total) : 0ull;
+                pay = ord | (mem << 24);
+                candidates = (uint32_t)nc.A;
+            } else {
+                double best = 0.0; uint32_t bm = 0;
+                if (eligible) exhaustive_lane(rec, nc, j, k, best, bm);
+                key = best > 0.0 ? (uint64_t)__double_as_longlong(best) : 0ull;
+                pay = bm;
+                uint32_t c = 1; for (int i = 1; i <= k; ++i) c = c * (uint32_t)(nc.A - k + i) / (uint32_t)i;
+                candidates = nc.A >= k ? c : 0;
+            }
+            // winner over the 8 lanes: strictly largest total, then lowest start index / lowest mask
+            // (greedy: first start in available order, scheduler.go:428-431)
+            uint32_t tie = exhaustive ? pay : (uint32_t)j;
+#pragma unroll
+            for (int off = 4; off >= 1; off >>= 1) {
+                uint64_t okey = __shfl_xor_sync(0xffffffffu, key, off, 8);
+                uint32_t otie = __shfl_xor_sync(0xffffffffu, tie, off, 8);
+                uint32_t opay = __shfl_xor_sync(0xffffffffu, pay, off, 8);
+                if (okey > key || (okey == key && otie < tie)) { key = okey; tie = otie; pay = opay; }
+            }
+            found = key != 0ull; win_total = __longlong_as_double((long long)key);
+            if (exhaustive) take_first_k(pay, k, sel, order);
+            else { order = pay & 0xffffffu; sel = pay >> 24; }
+        }
+    }
+    eval_finish(rec, nc, pod, P, hinted, eligible, k, found, win_total, sel, order, candidates, o);
 }
 
 __device__ __forceinline__ kgwe_node_score to_record(const EvalOut& o) {

@@ -190,7 +190,7 @@ int validate_pods(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n) {
 
 uint32_t hint_row_bytes(const kgwe_engine* e) { return (e->n_nodes + 7) / 8; }
 
-size_t score_smem_bytes(uint32_t pods_per_chunk) { return (size_t)TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast)) + (size_t)pods_per_chunk * 8 + 16; }
+size_t score_smem_bytes(uint32_t pods_per_chunk) { return (size_t)TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx)) + (size_t)pods_per_chunk * 8 + 16; }
 
 // Launch K1 (+K1b / K2) for n_pods pods whose descriptors, hint rows and outputs are in
 // device memory.  d_scores may be null unless topk > 1.

@@ -70,7 +70,19 @@ __device__ __forceinline__ void store_no_placement(kgwe_placement* dst) {
 }
 
 // ---------------------------------------------------------------------------------------
-// K1.  dynamic smem: [tile: TILE_NODES x 768 B][fast: TILE_NODES x 288 B][keys: pods_per_chunk x 8 B][mbarrier 8 B]
+// K1.  dynamic smem: [tile: 64 x 768 B][fast: 64 x 288 B][ctx: 64 x NodeCtx][keys: pods_per_chunk x 8 B][mbarrier]
+//
+// Pod loop, "octet" form: the 8 lanes of a group take 8 consecutive pods at a time.
+//   phase 0  lane i loads pod i and runs the Filter for (pod i, this node);
+//   phase A  for each of the 8 pods that needs an NVLink group on this node, the 8 lanes run
+//            the 8 greedy chains (lane = start GPU) and reduce to the winner; lane i keeps pod i's;
+//   phase B  lane i finishes pod i (topology score, resource, total, flags), stores its 16-byte
+//            NodeScore and joins the per-pod arg-max.
+// So the group search is 8-wide per evaluation while the scalar part of an evaluation is done by
+// one lane instead of redundantly by eight.  Stores of one warp instruction: for each i, the 4
+// groups' lanes i write 4 consecutive nodes of pod i = 64 contiguous bytes.
+// Warps with a node whose bandwidths are not whole numbers, and octets containing an
+// exhaustive-mode pod, take the one-pod-per-pass generic path instead.
 __global__ void __launch_bounds__(SCORE_THREADS, 2)
 score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
              const kgwe_pod_req* __restrict__ pods, uint32_t n_pods, uint32_t pods_per_chunk,
@@ -80,10 +92,11 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     extern __shared__ __align__(128) unsigned char smem[];
     DevNode* tile = reinterpret_cast<DevNode*>(smem);
     NodeFast* fast = reinterpret_cast<NodeFast*>(smem + TILE_NODES * sizeof(DevNode));
-    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem + TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast)));
+    NodeCtx* ctxs = reinterpret_cast<NodeCtx*>(smem + TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast)));
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem + TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx)));
     uint64_t* bar = reinterpret_cast<uint64_t*>(keys + pods_per_chunk);
 
-    const int tid = threadIdx.x, lane = tid & 31, grp = tid >> 3;
+    const int tid = threadIdx.x, lane = tid & 31, grp = tid >> 3, j = tid & 7;
     const uint32_t tile_first = blockIdx.x * TILE_NODES;
     const uint32_t tile_count = min((uint32_t)TILE_NODES, n_nodes - tile_first);
     const uint32_t p_begin = blockIdx.y * pods_per_chunk;
@@ -101,39 +114,90 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     __syncthreads();
 
     const uint32_t node = tile_first + grp;
+    const bool node_ok = grp < (int)tile_count;
     const DevNode* rec = tile + grp;
-    NodeCtx nc;
-    node_ctx_init(nc, rec, grp < (int)tile_count);
-    // integer form of the greedy inputs; usable when all four nodes of the warp are whole-number
     NodeFast* nf = fast + grp;
-    const bool warp_fast = __all_sync(0xffffffffu, nc.integral || !nc.valid);
-    if (nc.integral) node_fast_build(nf, rec, nc, lane & 7);
-    else nf->init[lane & 7] = FAST_NEG;
-    __syncwarp();
+    bool warp_fast;
+    {
+        NodeCtx c;
+        node_ctx_init(c, rec, node_ok);
+        // integer form of the greedy inputs; usable when all four nodes of the warp are whole-number
+        warp_fast = __all_sync(0xffffffffu, c.integral || !c.valid);
+        if (c.integral) node_fast_build(nf, rec, c, j);
+        else nf->init[j] = FAST_NEG;
+        if (j == 0) ctxs[grp] = c;
+        __syncwarp();
+    }
+    const NodeCtx& nc = ctxs[grp];
     const uint32_t gnode = P.node_base + node;
     unsigned long long cand = 0;
 
-    for (uint32_t p = p_begin; p < p_end; ++p) {
-        const kgwe_pod_req pod = load_pod(pods, p);
+    for (uint32_t p0 = p_begin; p0 < p_end; p0 += 8) {
+        // ---- phase 0: lane j owns pod p0 + j ----
+        const uint32_t p = p0 + j;
+        const bool live = p < p_end;
+        kgwe_pod_req pod = load_pod(pods, live ? p : p0);
+        const int k = clamp_k(pod.gpu_count);
+        const bool eligible = live && eval_filter(rec, nc, pod, k);
+        const bool wants_group = k >= 2 && is_nvlink_pref(pod);
+        const bool octet = warp_fast && !__any_sync(0xffffffffu, live && wants_group && (pod.flags & KGWE_POD_EXHAUSTIVE));
         EvalOut o;
-        evaluate<true>(rec, nc, pod, P, hint_bit(hint, hint_row_bytes, p, node), lane, o, nf, warp_fast);
-        if ((lane & 7) == 0 && grp < (int)tile_count) {
-            cand += o.candidates;
-            if (out) {
-                const kgwe_node_score r = to_record(o);
-                *reinterpret_cast<int4*>(out + (size_t)p * n_nodes + node) = *reinterpret_cast<const int4*>(&r);
+        if (octet) {
+            // ---- phase A: the group searches, one pod slot at a time ----
+            int32_t mykey = 0; uint32_t mypay = 0;
+            const int chain_k = (eligible && wants_group) ? k : 0;
+#pragma unroll 1
+            for (int t = 0; t < 8; ++t) {
+                const int kt = __shfl_sync(0xffffffffu, chain_k, t, 8);
+                if (!__any_sync(0xffffffffu, kt != 0)) continue;       // warp-uniform
+                int32_t key = 0; uint32_t pay = 0;
+                if (kt) greedy_chain_fast(nf, j, kt, key, pay);
+                fast_group_winner(key, pay);
+                if (j == t) { mykey = key; mypay = pay; }
             }
-        }
-        if (best) {
-            unsigned long long key = (o.flags & KGWE_F_KEPT) ? rank_key(o.total, gnode) : 0ull;
-            unsigned long long k2 = __shfl_xor_sync(0xffffffffu, key, 8);  key = k2 > key ? k2 : key;
-            k2 = __shfl_xor_sync(0xffffffffu, key, 16);                    key = k2 > key ? k2 : key;
-            if (lane == 0 && key) atomicMax(&keys[p - p_begin], key);
+            // ---- phase B: lane j finishes pod p0 + j ----
+            eval_finish(rec, nc, pod, P, live && hint_bit(hint, hint_row_bytes, p, node), eligible, k,
+                        mykey > 0, (double)(mykey >> 3), mypay >> 24, mypay & 0xffffffu, (uint32_t)nc.A, o);
+            if (live && node_ok) {
+                cand += o.candidates;
+                if (out) {
+                    const kgwe_node_score r = to_record(o);
+                    *reinterpret_cast<int4*>(out + (size_t)p * n_nodes + node) = *reinterpret_cast<const int4*>(&r);
+                }
+            }
+            if (best) {
+                unsigned long long key = (live && (o.flags & KGWE_F_KEPT)) ? rank_key(o.total, gnode) : 0ull;
+                unsigned long long k2 = __shfl_xor_sync(0xffffffffu, key, 8);  key = k2 > key ? k2 : key;
+                k2 = __shfl_xor_sync(0xffffffffu, key, 16);                    key = k2 > key ? k2 : key;
+                if (lane < 8 && key) atomicMax(&keys[p - p_begin], key);
+            }
+        } else {
+            // generic path: one pod per pass, all 8 lanes of a group on the same pod
+            const uint32_t n_here = min(8u, p_end - p0);
+#pragma unroll 1
+            for (uint32_t t = 0; t < n_here; ++t) {
+                const uint32_t pt = p0 + t;
+                const kgwe_pod_req podt = load_pod(pods, pt);
+                evaluate<true>(rec, nc, podt, P, hint_bit(hint, hint_row_bytes, pt, node), lane, o, nf, warp_fast);
+                if (j == 0 && node_ok) {
+                    cand += o.candidates;
+                    if (out) {
+                        const kgwe_node_score r = to_record(o);
+                        *reinterpret_cast<int4*>(out + (size_t)pt * n_nodes + node) = *reinterpret_cast<const int4*>(&r);
+                    }
+                }
+                if (best) {
+                    unsigned long long key = (o.flags & KGWE_F_KEPT) ? rank_key(o.total, gnode) : 0ull;
+                    unsigned long long k2 = __shfl_xor_sync(0xffffffffu, key, 8);  key = k2 > key ? k2 : key;
+                    k2 = __shfl_xor_sync(0xffffffffu, key, 16);                    key = k2 > key ? k2 : key;
+                    if (lane == 0 && key) atomicMax(&keys[pt - p_begin], key);
+                }
+            }
         }
     }
     // candidates counter: one atomic per warp
-    cand += __shfl_xor_sync(0xffffffffu, cand, 8);
-    cand += __shfl_xor_sync(0xffffffffu, cand, 16);
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) cand += __shfl_xor_sync(0xffffffffu, cand, off);
     if (lane == 0 && counters && cand) atomicAdd(&counters[1], cand);
     if (best) {
         __syncthreads();
