@@ -194,18 +194,14 @@ def run_kgwe(args):
     sptr = stream.cuda_stream
     assert sptr != 0
     d_pods = torch.from_numpy(pods.view(np.uint8).reshape(P, abi.POD_REQ.itemsize)).to(dev)
-    d_scores = torch.empty((P, n_local, abi.NODE_SCORE.itemsize), dtype=torch.uint8, device=dev)
-    d_top = torch.empty((P, abi.PLACEMENT.itemsize), dtype=torch.uint8, device=dev)
-    d_gather = torch.empty((world, P, abi.PLACEMENT.itemsize), dtype=torch.uint8, device=dev) if world > 1 else None
-    d_merged = torch.empty((P, abi.PLACEMENT.itemsize), dtype=torch.uint8, device=dev) if world > 1 else None
+    scorer = kg.sharded.ShardedScorer(eng, n_local, world, dist if world > 1 else None, sptr)
+    scorer.alloc(torch, dev, P, 1, with_matrix=True)
+    d_gather, d_merged = scorer.d_gather, scorer.d_merged
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
 
     def step_device():
         flush.zero_()                                                    # L2 flush between steps
-        eng.score_batch_device(d_pods.data_ptr(), P, None, d_scores.data_ptr(), 1, d_top.data_ptr(), sptr)
-        if world > 1:
-            dist.all_gather_into_tensor(d_gather, d_top)
-            eng.topk_merge_device(d_gather.data_ptr(), world, P, 1, d_merged.data_ptr(), sptr)
+        scorer.step(d_pods)
 
     def fence():
         if world > 1:
@@ -259,7 +255,7 @@ def run_kgwe(args):
     for _ in range(args.steps):
         _, top = eng.score_batch(pods, n_local, want_scores=False, topk=1)
         if world > 1:
-            g = torch.from_numpy(top.view(np.uint8).reshape(P, abi.PLACEMENT.itemsize)).to(dev, non_blocking=True)
+            g = torch.from_numpy(top.view(np.uint8).reshape(P, 1, abi.PLACEMENT.itemsize)).to(dev, non_blocking=True)
             dist.all_gather_into_tensor(d_gather, g)
             eng.topk_merge_device(d_gather.data_ptr(), world, P, 1, d_merged.data_ptr(), sptr)
             _ = d_merged.cpu()

@@ -257,6 +257,11 @@ int kgwe_score_top1_noalloc(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t
 int kgwe_topk_merge_device(kgwe_engine* e, const kgwe_placement* d_lists, uint32_t n_lists,
                            uint32_t n_pods, uint32_t topk, kgwe_placement* d_out, void* cuda_stream);
 
+/* The same merge on host memory, for hosts that gather the per-shard lists themselves (gRPC,
+ * gloo, one process driving several engines).  Pure host code, needs no engine and no GPU. */
+int kgwe_topk_merge_host(const kgwe_placement* lists, uint32_t n_lists, uint32_t n_pods, uint32_t topk,
+                         kgwe_placement* out);
+
 /* Stateful Schedule for a queue of workloads, in order: score, pick the best node
  * (lowest index on ties), EstimatedBandwidth, commit to the ledger, next workload.
  * Replaces Schedule + tryScheduleOnNode + recordAllocation (scheduler.go:114-179,

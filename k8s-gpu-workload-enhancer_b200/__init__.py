@@ -6,5 +6,5 @@ mirror of the reference's TopologyAwareScheduler interface over that ABI), and t
 plumbing used by tests and bench.py.  The directory name carries a hyphen, so import it
 through `__graft_entry__.load_package()`, which registers it as `kgwe_b200`.
 """
-from . import abi, synth  # noqa: F401
+from . import abi, sharded, synth  # noqa: F401
 from .engine import Engine, EngineError, unpack_order  # noqa: F401

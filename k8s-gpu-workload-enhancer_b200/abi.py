@@ -73,7 +73,7 @@ ENGINE_SYMBOLS = [
     "kgwe_engine_create", "kgwe_engine_destroy", "kgwe_config_default", "kgwe_node_upsert", "kgwe_nodes_upsert",
     "kgwe_node_remove", "kgwe_alloc_commit", "kgwe_alloc_release", "kgwe_score_batch", "kgwe_score_batch_device",
     "kgwe_topk_merge_device", "kgwe_schedule_queue", "kgwe_node_read", "kgwe_get_stats", "kgwe_last_error",
-    "kgwe_version", "kgwe_score_top1_noalloc",
+    "kgwe_version", "kgwe_score_top1_noalloc", "kgwe_topk_merge_host",
 ]
 NOALLOC_MAX_PODS = 16384
 
@@ -103,6 +103,7 @@ def load_engine_lib():
     lib.kgwe_score_batch.argtypes = [vp, vp, u32, vp, vp, u32, vp]
     lib.kgwe_score_batch_device.argtypes = [vp, vp, u32, vp, vp, u32, vp, vp]
     lib.kgwe_score_top1_noalloc.argtypes = [vp, vp, u32, vp, vp, vp, vp]
+    lib.kgwe_topk_merge_host.argtypes = [vp, u32, u32, u32, vp]
     lib.kgwe_topk_merge_device.argtypes = [vp, vp, u32, u32, u32, vp, vp]
     lib.kgwe_schedule_queue.argtypes = [vp, vp, u32, vp, vp]
     lib.kgwe_node_read.argtypes = [vp, u32, vp]

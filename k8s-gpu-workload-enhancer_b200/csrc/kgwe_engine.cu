@@ -483,6 +483,26 @@ int kgwe_topk_merge_device(kgwe_engine* e, const kgwe_placement* d_lists, uint32
     return KGWE_OK;
 }
 
+int kgwe_topk_merge_host(const kgwe_placement* lists, uint32_t n_lists, uint32_t n_pods, uint32_t topk, kgwe_placement* out) {
+    if (!lists || !out || topk == 0 || topk > KGWE_MAX_TOPK || n_lists == 0 || n_lists > 32) return KGWE_ERR_INVALID_ARG;
+    for (uint32_t p = 0; p < n_pods; ++p) {
+        uint32_t head[32] = {0};
+        for (uint32_t j = 0; j < topk; ++j) {
+            int br = -1; int32_t bt = 0; uint32_t bn = 0;
+            for (uint32_t r = 0; r < n_lists; ++r) {
+                if (head[r] >= topk) continue;
+                const kgwe_placement& c = lists[((size_t)r * n_pods + p) * topk + head[r]];
+                if (c.node_idx == KGWE_NO_NODE) continue;
+                if (br < 0 || c.total > bt || (c.total == bt && c.node_idx < bn)) { br = (int)r; bt = c.total; bn = c.node_idx; }
+            }
+            kgwe_placement& dst = out[(size_t)p * topk + j];
+            if (br < 0) { memset(&dst, 0, sizeof dst); dst.node_idx = KGWE_NO_NODE; }
+            else { dst = lists[((size_t)br * n_pods + p) * topk + head[br]]; head[br]++; }
+        }
+    }
+    return KGWE_OK;
+}
+
 int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, const uint8_t* hint, kgwe_placement* out) {
     if (!e) return KGWE_ERR_INVALID_ARG;
     std::lock_guard<std::mutex> lk(e->mu);

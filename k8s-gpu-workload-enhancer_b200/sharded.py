@@ -1,0 +1,50 @@
+"""Node-sharded scoring over several GPUs: one process per GPU, rank r owns the
+contiguous node range [r*N/R, (r+1)*N/R), scores every pod against its shard, and the ranked
+local top-k lists (32-byte placements with GLOBAL node indices) are all-gathered once per batch
+and merged identically on every rank (score desc, node index asc).  torch.distributed is the
+plumbing (NCCL over NVLink on GPUs; gloo in the CPU tests of the protocol)."""
+import numpy as np
+
+from . import abi
+
+
+def shard_range(n_nodes, rank, world):
+    """Contiguous node range of `rank`; keeps the lowest-index tie-break a pure key comparison."""
+    return rank * n_nodes // world, (rank + 1) * n_nodes // world
+
+
+def merge_host(lists, topk):
+    """lists: [R, P, topk] placements (numpy) -> [P, topk], via kgwe_topk_merge_host."""
+    lists = np.ascontiguousarray(lists, dtype=abi.PLACEMENT)
+    R, P = lists.shape[0], lists.shape[1]
+    out = np.zeros((P, topk), dtype=abi.PLACEMENT)
+    rc = abi.load_engine_lib().kgwe_topk_merge_host(abi.ptr(lists), R, P, topk, abi.ptr(out))
+    if rc != 0:
+        raise RuntimeError(f"kgwe_topk_merge_host: {rc}")
+    return out
+
+
+class ShardedScorer:
+    """Device-resident sharded batch scorer.  `engine` holds this rank's shard (created with
+    node_base = shard start).  Buffers are torch uint8 tensors on the engine's GPU."""
+
+    def __init__(self, engine, n_local, world, dist=None, stream_ptr=None):
+        self.eng, self.n_local, self.world, self.dist, self.sptr = engine, n_local, world, dist, stream_ptr
+
+    def alloc(self, torch, dev, n_pods, topk, with_matrix=True):
+        it = abi.PLACEMENT.itemsize
+        self.P, self.topk = n_pods, topk
+        self.d_scores = torch.empty((n_pods, self.n_local, abi.NODE_SCORE.itemsize), dtype=torch.uint8, device=dev) if with_matrix else None
+        self.d_top = torch.empty((n_pods, topk, it), dtype=torch.uint8, device=dev)
+        self.d_gather = torch.empty((self.world, n_pods, topk, it), dtype=torch.uint8, device=dev) if self.world > 1 else None
+        self.d_merged = torch.empty((n_pods, topk, it), dtype=torch.uint8, device=dev) if self.world > 1 else self.d_top
+
+    def step(self, d_pods, d_hint=None):
+        """One batch: local scoring (+ matrix), all-gather of local top-k, merge.  Asynchronous."""
+        sc = self.d_scores.data_ptr() if self.d_scores is not None else None
+        self.eng.score_batch_device(d_pods.data_ptr(), self.P, d_hint.data_ptr() if d_hint is not None else None,
+                                    sc, self.topk, self.d_top.data_ptr(), self.sptr)
+        if self.world > 1:
+            self.dist.all_gather_into_tensor(self.d_gather, self.d_top)
+            self.eng.topk_merge_device(self.d_gather.data_ptr(), self.world, self.P, self.topk, self.d_merged.data_ptr(), self.sptr)
+        return self.d_merged

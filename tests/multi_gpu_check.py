@@ -1,0 +1,54 @@
+"""Run under torchrun on N GPUs: node-sharded scoring (NCCL all-gather + merge) must equal the
+oracle's ranking over the whole cluster.  `python -m torch.distributed.run --nproc-per-node N
+tests/multi_gpu_check.py`.  Exit code 0 = parity on every rank."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as entry  # noqa: E402
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    world, rank, local = int(os.environ["WORLD_SIZE"]), int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    kg = entry.load_package()
+    from oracle import binding as orc
+    abi, synth = kg.abi, kg.synth
+    nodes, pods, led = synth.config(3, 0.1)
+    pods = pods[:500]
+    N, P, topk = len(nodes), len(pods), 4
+    lo, hi = kg.sharded.shard_range(N, rank, world)
+    eng = kg.Engine(max_nodes=hi - lo, device=local, node_base=lo)
+    eng.upsert_nodes(nodes[lo:hi])
+    for a in led:
+        if lo <= a["node_idx"] < hi:
+            eng.commit(a["wl_id"], a["node_idx"] - lo, a["gpu_mask"])
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    sc = kg.sharded.ShardedScorer(eng, hi - lo, world, dist, stream.cuda_stream)
+    sc.alloc(torch, dev, P, topk, with_matrix=True)
+    d_pods = torch.from_numpy(pods.view(np.uint8).reshape(P, abi.POD_REQ.itemsize)).to(dev)
+    merged = sc.step(d_pods)
+    torch.cuda.synchronize()
+    got = merged.cpu().numpy().view(abi.PLACEMENT).reshape(P, topk)
+    local_scores = sc.d_scores.cpu().numpy().view(abi.NODE_SCORE).reshape(P, hi - lo)
+    o_scores, want, _ = orc.score_batch(abi, nodes, led, pods, want_scores=True, topk=topk, threads=4)
+    ok = got.tobytes() == want.tobytes() and local_scores.tobytes() == np.ascontiguousarray(o_scores[:, lo:hi]).tobytes()
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print(f"multi_gpu_check world={world}: {'PARITY OK' if flag.item() else 'MISMATCH'} ({P} pods x {N} nodes, top-{topk})")
+    eng.close()
+    dist.destroy_process_group()
+    sys.exit(0 if flag.item() else 1)
+
+
+if __name__ == "__main__":
+    main()
