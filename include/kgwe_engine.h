@@ -134,6 +134,7 @@ typedef struct kgwe_pod_req {
 #define KGWE_F_HINT       0x04   /* hint bonus applied */
 #define KGWE_F_FALLBACK   0x08   /* topology fallback arm taken (30 / 50 / 40) */
 #define KGWE_F_MINBW      0x10   /* filtered by E3 min-bandwidth */
+#define KGWE_F_GANG_ROLLBACK 0x20 /* E5: this member was placeable but its gang was not; nothing was committed */
 
 /* NodeScore for one (pod, node) evaluation (src/scheduler/types.go:295-319).  16 bytes.
  * Scores are the reference's unclamped integers.  `order` is SelectedGPUs in the
@@ -269,6 +270,31 @@ int kgwe_topk_merge_host(const kgwe_placement* lists, uint32_t n_lists, uint32_t
  * "no eligible nodes found for workload" (scheduler.go:140). */
 int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods,
                         const uint8_t* hint_bitmap, kgwe_placement* out);
+
+/* EXTENSION E5 - gang scheduling (GangSchedulingGroup exists only as a type in the reference,
+ * src/scheduler/types.go:415-444; Schedule places a workload's GPUs on ONE node, so an FSDP
+ * worldSize=64 job is 8 member workloads x 8 GPUs).  Members of a gang are consecutive in
+ * `pods`; gang_of[i] is the (non-decreasing) gang number of pod i.  Each gang is scheduled with
+ * the kgwe_schedule_queue semantic member by member and is all-or-nothing: if any member finds
+ * no node, every commit of that gang is rolled back, all its members get node_idx ==
+ * KGWE_NO_NODE (members that had a node carry KGWE_F_GANG_ROLLBACK) and the queue continues
+ * with the next gang.  Workload ids must be unique and not yet in the ledger. */
+int kgwe_schedule_gangs(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, const uint32_t* gang_of,
+                        const uint8_t* hint_bitmap, kgwe_placement* out);
+
+/* EXTENSION E4 - side terms of a placement (absent from the reference): for the GPU set of each
+ * placement, with pair weight w(a,b) = min over both directions of the ACTIVE link bandwidth
+ * (0 when either direction has none):
+ *   bisection_gbps       min over all splits of the set into floor(k/2) and the rest of the summed
+ *                        w across the split (35 distinct cuts at k = 8); 0 for k <= 1
+ *   ring_bottleneck_gbps max over all cyclic orders of the set of the smallest w along the ring
+ *                        ((k-1)! orders with the first GPU fixed); w(a,b) for k = 2; 0 for k <= 1
+ * Reported only; they do not enter TotalScore.  Host buffers. */
+typedef struct kgwe_side_terms {
+    double bisection_gbps;
+    double ring_bottleneck_gbps;
+} kgwe_side_terms;
+int kgwe_placement_terms(kgwe_engine* e, const kgwe_placement* placements, uint32_t n, kgwe_side_terms* out);
 
 /* Read one record back (device -> host) in ABI layout, ledger fields included. */
 int kgwe_node_read(kgwe_engine* e, uint32_t local_idx, kgwe_node_image* out);

@@ -503,6 +503,66 @@ int kgwe_topk_merge_host(const kgwe_placement* lists, uint32_t n_lists, uint32_t
     return KGWE_OK;
 }
 
+// Launch the stateful queue kernel (K3) for np pods and wait.  Decisions land in e->h_topk; the
+// DEVICE image then carries every commit of the segment, the host mirror none yet.
+static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t np, const uint8_t* hint_rows, double* gpu_ms) {
+    cudaStream_t s = e->stream;
+    const uint32_t N = e->n_nodes, row = hint_row_bytes(e);
+    int rc = flush_dirty(e, s);
+    if (rc != KGWE_OK) return rc;
+    CU(e, e->d_pods.ensure(np)); CU(e, e->h_pods.ensure(np));
+    CU(e, e->d_topk.ensure(np)); CU(e, e->h_topk.ensure(np));
+    {
+        const size_t had = e->d_best.cap;
+        CU(e, e->d_best.ensure(np));
+        if (e->d_best.cap != had) CU(e, cudaMemsetAsync(e->d_best.p, 0, e->d_best.cap * sizeof(unsigned long long), s));
+    }
+    memcpy(e->h_pods.p, pods, (size_t)np * sizeof(kgwe_pod_req));
+    CU(e, cudaMemcpyAsync(e->d_pods.p, e->h_pods.p, (size_t)np * sizeof(kgwe_pod_req), cudaMemcpyHostToDevice, s));
+    e->stats.h2d_bytes += (uint64_t)np * sizeof(kgwe_pod_req);
+    const uint8_t* d_hint = nullptr;
+    if (hint_rows) {
+        CU(e, e->d_hint.ensure((size_t)np * row)); CU(e, e->h_hint.ensure((size_t)np * row));
+        memcpy(e->h_hint.p, hint_rows, (size_t)np * row);
+        CU(e, cudaMemcpyAsync(e->d_hint.p, e->h_hint.p, (size_t)np * row, cudaMemcpyHostToDevice, s));
+        e->stats.h2d_bytes += (uint64_t)np * row;
+        d_hint = e->d_hint.p;
+    }
+    // persistent grid: as many CTAs as can be co-resident, no more than there are node tiles
+    uint32_t grid = std::min<uint32_t>((uint32_t)(e->sm_count * e->sched_blocks_per_sm), (N + TILE_NODES - 1) / TILE_NODES);
+    grid = std::max(grid, 1u);
+    DevNode* d_nodes = e->d_nodes; uint32_t n_nodes = N; const kgwe_pod_req* d_pods = e->d_pods.p; uint32_t npods = np; uint32_t rowb = row;
+    unsigned long long* best = e->d_best.p; kgwe_placement* d_out = e->d_topk.p; Params prm = e->params; unsigned long long* ctr = e->d_counters;
+    void* args[] = {&d_nodes, &n_nodes, &d_pods, &npods, &d_hint, &rowb, &best, &d_out, &prm, &ctr};
+    CU(e, cudaEventRecord(e->ev0, s));
+    CU(e, cudaLaunchCooperativeKernel((const void*)schedule_kernel, dim3(grid), dim3(SCORE_THREADS), args, 0, s));
+    e->stats.kernel_launches++;
+    CU(e, cudaMemsetAsync(e->d_best.p, 0, (size_t)np * sizeof(unsigned long long), s));
+    CU(e, cudaEventRecord(e->ev1, s));
+    CU(e, cudaMemcpyAsync(e->h_topk.p, e->d_topk.p, (size_t)np * sizeof(kgwe_placement), cudaMemcpyDeviceToHost, s));
+    e->stats.d2h_bytes += (uint64_t)np * sizeof(kgwe_placement);
+    rc = pull_counters(e, s);
+    if (rc != KGWE_OK) return rc;
+    CU(e, cudaStreamSynchronize(s));
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) == cudaSuccess) *gpu_ms += ms;
+    e->stats.evaluations += e->h_counters[0];
+    e->stats.candidates += e->h_counters[1];
+    return KGWE_OK;
+}
+
+// Mirror one device-side commit into the host ledger and the pinned image (no device traffic).
+static void apply_commit(kgwe_engine* e, uint64_t wl_id, const kgwe_placement& d) {
+    e->stats.scheduled++;
+    if (d.topology >= 80) e->stats.topology_optimal++;
+    const uint32_t local = d.node_idx - e->cfg.node_base;
+    DevNode& rec = e->h_nodes[local];
+    rec.allocated_mask |= d.gpu_mask; rec.n_allocs++;
+    e->ledger[wl_id] = LedgerEntry{local, d.gpu_mask};
+}
+
+static void no_node(kgwe_placement& p, uint8_t flags) { memset(&p, 0, sizeof p); p.node_idx = KGWE_NO_NODE; p.flags = flags; }
+
 int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, const uint8_t* hint, kgwe_placement* out) {
     if (!e) return KGWE_ERR_INVALID_ARG;
     std::lock_guard<std::mutex> lk(e->mu);
@@ -510,11 +570,9 @@ int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pod
     int rc = validate_pods(e, pods, n_pods);
     if (rc != KGWE_OK) return rc;
     CU(e, cudaSetDevice(e->cfg.device));
-    cudaStream_t s = e->stream;
     if (n_pods == 0) return KGWE_OK;
-    const uint32_t N = e->n_nodes;
-    if (N == 0) {
-        for (uint32_t i = 0; i < n_pods; ++i) { memset(&out[i], 0, sizeof(kgwe_placement)); out[i].node_idx = KGWE_NO_NODE; e->stats.failed++; }
+    if (e->n_nodes == 0) {
+        for (uint32_t i = 0; i < n_pods; ++i) { no_node(out[i], 0); e->stats.failed++; }
         return KGWE_OK;
     }
     const uint32_t row = hint_row_bytes(e);
@@ -534,78 +592,107 @@ int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pod
             }
         }
         const uint32_t np = p1 - p0;
-        rc = flush_dirty(e, s);
+        rc = run_queue_segment(e, pods + p0, np, hint ? hint + (size_t)p0 * row : nullptr, &gpu_ms);
         if (rc != KGWE_OK) return rc;
-        CU(e, e->d_pods.ensure(np)); CU(e, e->h_pods.ensure(np));
-        CU(e, e->d_topk.ensure(np)); CU(e, e->h_topk.ensure(np));
-        {
-            const size_t had = e->d_best.cap;
-            CU(e, e->d_best.ensure(np));
-            if (e->d_best.cap != had) CU(e, cudaMemsetAsync(e->d_best.p, 0, e->d_best.cap * sizeof(unsigned long long), s));
-        }
-        memcpy(e->h_pods.p, pods + p0, (size_t)np * sizeof(kgwe_pod_req));
-        CU(e, cudaMemcpyAsync(e->d_pods.p, e->h_pods.p, (size_t)np * sizeof(kgwe_pod_req), cudaMemcpyHostToDevice, s));
-        e->stats.h2d_bytes += (uint64_t)np * sizeof(kgwe_pod_req);
-        const uint8_t* d_hint = nullptr;
-        if (hint) {
-            CU(e, e->d_hint.ensure((size_t)np * row)); CU(e, e->h_hint.ensure((size_t)np * row));
-            memcpy(e->h_hint.p, hint + (size_t)p0 * row, (size_t)np * row);
-            CU(e, cudaMemcpyAsync(e->d_hint.p, e->h_hint.p, (size_t)np * row, cudaMemcpyHostToDevice, s));
-            e->stats.h2d_bytes += (uint64_t)np * row;
-            d_hint = e->d_hint.p;
-        }
-        // persistent grid: as many CTAs as can be co-resident, no more than there are node tiles
-        uint32_t grid = std::min<uint32_t>((uint32_t)(e->sm_count * e->sched_blocks_per_sm), (N + TILE_NODES - 1) / TILE_NODES);
-        grid = std::max(grid, 1u);
-        DevNode* d_nodes = e->d_nodes; uint32_t n_nodes = N; const kgwe_pod_req* d_pods = e->d_pods.p; uint32_t npods = np; uint32_t rowb = row;
-        unsigned long long* best = e->d_best.p; kgwe_placement* d_out = e->d_topk.p; Params prm = e->params; unsigned long long* ctr = e->d_counters;
-        void* args[] = {&d_nodes, &n_nodes, &d_pods, &npods, &d_hint, &rowb, &best, &d_out, &prm, &ctr};
-        CU(e, cudaEventRecord(e->ev0, s));
-        CU(e, cudaLaunchCooperativeKernel((const void*)schedule_kernel, dim3(grid), dim3(SCORE_THREADS), args, 0, s));
-        e->stats.kernel_launches++;
-        CU(e, cudaMemsetAsync(e->d_best.p, 0, (size_t)np * sizeof(unsigned long long), s));
-        CU(e, cudaEventRecord(e->ev1, s));
-        CU(e, cudaMemcpyAsync(e->h_topk.p, e->d_topk.p, (size_t)np * sizeof(kgwe_placement), cudaMemcpyDeviceToHost, s));
-        e->stats.d2h_bytes += (uint64_t)np * sizeof(kgwe_placement);
-        rc = pull_counters(e, s);
-        if (rc != KGWE_OK) return rc;
-        CU(e, cudaStreamSynchronize(s));
-        float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) == cudaSuccess) gpu_ms += ms;
-        e->stats.evaluations += e->h_counters[0];
-        e->stats.candidates += e->h_counters[1];
-        // mirror the device-side commits into the host ledger and the pinned image
         for (uint32_t i = 0; i < np; ++i) {
             const kgwe_placement& d = e->h_topk.p[i];
             out[p0 + i] = d;
             if (d.node_idx == KGWE_NO_NODE) { e->stats.failed++; continue; }
-            e->stats.scheduled++;
-            if (d.topology >= 80) e->stats.topology_optimal++;
-            const uint32_t local = d.node_idx - e->cfg.node_base;
             const bool last_overwrites = overwrite && i == np - 1;
-            if (!last_overwrites) {
-                DevNode& rec = e->h_nodes[local];
-                rec.allocated_mask |= d.gpu_mask; rec.n_allocs++;
-                e->ledger[pods[p0 + i].wl_id] = LedgerEntry{local, d.gpu_mask};
-            } else {
-                // device already holds the new commit; bring the mirror level, then drop the old entry
-                DevNode& rec = e->h_nodes[local];
-                rec.allocated_mask |= d.gpu_mask; rec.n_allocs++;
-                auto it = e->ledger.find(pods[p0 + i].wl_id);
-                const uint32_t old_node = it->second.node;
-                e->ledger.erase(it);
-                e->ledger[pods[p0 + i].wl_id] = LedgerEntry{local, d.gpu_mask};
-                for (uint32_t nd : {old_node, local}) {
-                    uint8_t m = 0; uint32_t n = 0;
-                    for (auto& kv : e->ledger) if (kv.second.node == nd) { m |= kv.second.mask; n++; }
-                    e->h_nodes[nd].allocated_mask = m; e->h_nodes[nd].n_allocs = n;
-                    mark_dirty(e, nd);
-                }
+            if (!last_overwrites) { apply_commit(e, pods[p0 + i].wl_id, d); continue; }
+            // device already holds the new commit; bring the mirror level, then drop the old entry
+            const uint32_t old_node = e->ledger.find(pods[p0 + i].wl_id)->second.node;
+            e->ledger.erase(pods[p0 + i].wl_id);
+            apply_commit(e, pods[p0 + i].wl_id, d);
+            const uint32_t local = d.node_idx - e->cfg.node_base;
+            for (uint32_t nd : {old_node, local}) {
+                uint8_t m = 0; uint32_t n = 0;
+                for (auto& kv : e->ledger) if (kv.second.node == nd) { m |= kv.second.mask; n++; }
+                e->h_nodes[nd].allocated_mask = m; e->h_nodes[nd].n_allocs = n;
+                mark_dirty(e, nd);
             }
         }
         p0 = p1;
     }
     e->stats.last_call_gpu_ms = gpu_ms;
+    return KGWE_OK;
+}
+
+// E5.  Speculative: run a window of the queue in one kernel; everything before the first gang
+// with a failed member is final.  That gang is rejected, the device records touched from there
+// on are restored from the host mirror (which never saw them), and the queue resumes after it.
+int kgwe_schedule_gangs(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, const uint32_t* gang_of,
+                        const uint8_t* hint, kgwe_placement* out) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (n_pods && (!pods || !out || !gang_of)) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    int rc = validate_pods(e, pods, n_pods);
+    if (rc != KGWE_OK) return rc;
+    {
+        std::unordered_map<uint64_t, int> seen;
+        for (uint32_t i = 0; i < n_pods; ++i) {
+            if (i && gang_of[i] < gang_of[i - 1]) return fail(e, KGWE_ERR_INVALID_ARG, "gang_of must be non-decreasing (pod %u)", i);
+            if (e->ledger.count(pods[i].wl_id) || seen.count(pods[i].wl_id)) return fail(e, KGWE_ERR_INVALID_ARG, "pod %u: workload id already scheduled", i);
+            seen[pods[i].wl_id] = 1;
+        }
+    }
+    CU(e, cudaSetDevice(e->cfg.device));
+    if (n_pods == 0) return KGWE_OK;
+    if (e->n_nodes == 0) {
+        for (uint32_t i = 0; i < n_pods; ++i) { no_node(out[i], 0); e->stats.failed++; }
+        return KGWE_OK;
+    }
+    const uint32_t row = hint_row_bytes(e);
+    const uint32_t kWindow = 4096;
+    double gpu_ms = 0.0;
+    uint32_t p0 = 0;
+    while (p0 < n_pods) {
+        // window = whole gangs, at least one
+        uint32_t p1 = std::min(n_pods, p0 + kWindow);
+        while (p1 < n_pods && gang_of[p1] == gang_of[p1 - 1]) ++p1;
+        const uint32_t np = p1 - p0;
+        rc = run_queue_segment(e, pods + p0, np, hint ? hint + (size_t)p0 * row : nullptr, &gpu_ms);
+        if (rc != KGWE_OK) return rc;
+        uint32_t bad = np;                                   // first pod of the first failing gang
+        for (uint32_t i = 0; i < np; ++i)
+            if (e->h_topk.p[i].node_idx == KGWE_NO_NODE) { bad = i; while (bad > 0 && gang_of[p0 + bad - 1] == gang_of[p0 + i]) --bad; break; }
+        for (uint32_t i = 0; i < bad; ++i) { out[p0 + i] = e->h_topk.p[i]; apply_commit(e, pods[p0 + i].wl_id, e->h_topk.p[i]); }
+        if (bad == np) { p0 = p1; continue; }
+        uint32_t gend = bad;
+        while (gend < np && gang_of[p0 + gend] == gang_of[p0 + bad]) ++gend;
+        for (uint32_t i = bad; i < np; ++i) {                // undo on the device whatever the kernel committed from here on
+            const kgwe_placement& d = e->h_topk.p[i];
+            if (d.node_idx != KGWE_NO_NODE) mark_dirty(e, d.node_idx - e->cfg.node_base);
+            if (i < gend) { no_node(out[p0 + i], d.node_idx != KGWE_NO_NODE ? KGWE_F_GANG_ROLLBACK : 0); e->stats.failed++; }
+        }
+        p0 += gend;
+    }
+    e->stats.last_call_gpu_ms = gpu_ms;
+    return KGWE_OK;
+}
+
+int kgwe_placement_terms(kgwe_engine* e, const kgwe_placement* placements, uint32_t n, kgwe_side_terms* out) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (n && (!placements || !out)) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    if (n == 0) return KGWE_OK;
+    CU(e, cudaSetDevice(e->cfg.device));
+    cudaStream_t s = e->stream;
+    int rc = flush_dirty(e, s);
+    if (rc != KGWE_OK) return rc;
+    CU(e, e->d_topk.ensure(n)); CU(e, e->h_topk.ensure(n));
+    static_assert(sizeof(kgwe_side_terms) <= sizeof(kgwe_placement), "terms are staged in the placement buffers");
+    CU(e, e->d_scores.ensure(((size_t)n * sizeof(kgwe_side_terms) + sizeof(kgwe_node_score) - 1) / sizeof(kgwe_node_score)));
+    memcpy(e->h_topk.p, placements, (size_t)n * sizeof(kgwe_placement));
+    CU(e, cudaMemcpyAsync(e->d_topk.p, e->h_topk.p, (size_t)n * sizeof(kgwe_placement), cudaMemcpyHostToDevice, s));
+    kgwe_side_terms* d_terms = reinterpret_cast<kgwe_side_terms*>(e->d_scores.p);
+    side_terms_kernel<<<(n + 3) / 4, 128, 0, s>>>(e->d_nodes, e->n_nodes, e->cfg.node_base, e->d_topk.p, n, d_terms);
+    CU(e, cudaGetLastError());
+    e->stats.kernel_launches++;
+    CU(e, cudaMemcpyAsync(e->h_topk.p, d_terms, (size_t)n * sizeof(kgwe_side_terms), cudaMemcpyDeviceToHost, s));
+    CU(e, cudaStreamSynchronize(s));
+    memcpy(out, e->h_topk.p, (size_t)n * sizeof(kgwe_side_terms));
+    e->stats.h2d_bytes += (uint64_t)n * sizeof(kgwe_placement); e->stats.d2h_bytes += (uint64_t)n * sizeof(kgwe_side_terms);
     return KGWE_OK;
 }
 

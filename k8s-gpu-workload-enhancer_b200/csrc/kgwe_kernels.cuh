@@ -368,4 +368,67 @@ schedule_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict
     if (lane == 0 && counters) { if (evals) atomicAdd(&counters[0], evals); if (cand) atomicAdd(&counters[1], cand); }
 }
 
+// ---------------------------------------------------------------------------------------
+// E4 side terms: one warp per placement.  Lanes split the 2^k subsets (bisection) and the
+// (k-1)! cyclic orders (ring); warp-shuffle min / max at the end.  Cut sums are accumulated
+// per lane in ascending (a, b) order, so the result does not depend on the lane split.
+__device__ __forceinline__ double pair_w(const DevNode* rec, int a, int b) {
+    const bool ab = rec->act_in[b] >> a & 1, ba = rec->act_in[a] >> b & 1;
+    if (!ab || !ba) return 0.0;
+    const double x = rec->bw_in[b][bw_slot(b, a)], y = rec->bw_in[a][bw_slot(a, b)];
+    return x < y ? x : y;
+}
+
+__global__ void __launch_bounds__(128)
+side_terms_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, uint32_t node_base,
+                  const kgwe_placement* __restrict__ pls, uint32_t n, kgwe_side_terms* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (i >= n) return;
+    const kgwe_placement pl = pls[i];
+    const uint32_t local = pl.node_idx - node_base;
+    double bis = 0.0, ring = 0.0;
+    int g[8]; int k = 0;
+    if (pl.node_idx != KGWE_NO_NODE && local < n_nodes)
+        for (int b = 0; b < 8; ++b) if (pl.gpu_mask >> b & 1) g[k++] = b;
+    if (k >= 2) {
+        const DevNode* rec = nodes + local;
+        double w[8][8];
+        for (int a = 0; a < k; ++a) for (int b = 0; b < k; ++b) w[a][b] = a == b ? 0.0 : pair_w(rec, g[a], g[b]);
+        // bisection: subsets T of positions with |T| = k/2
+        const int h = k / 2;
+        double best = 1e300;
+        for (uint32_t t = (uint32_t)lane; t < (1u << k); t += 32) {
+            if (__popc(t) != h) continue;
+            double cut = 0.0;
+            for (int a = 0; a < k; ++a) if (t >> a & 1)
+                for (int b = 0; b < k; ++b) if (!(t >> b & 1)) cut = __dadd_rn(cut, w[a][b]);
+            best = cut < best ? cut : best;
+        }
+        // ring: position 0 fixed, the other k-1 permuted (factoradic decode of the order index)
+        int nperm = 1; for (int f = 2; f < k; ++f) nperm *= f;
+        double rbest = -1.0;
+        for (int idx = lane; idx < nperm; idx += 32) {
+            int rest[7]; for (int q = 0; q < k - 1; ++q) rest[q] = q + 1;
+            int code = idx, prev = 0; double mn = 1e300;
+            for (int q = k - 1; q >= 1; --q) {
+                const int c = code % q; code /= q;
+                const int cur = rest[c];
+                for (int z = c; z < q - 1; ++z) rest[z] = rest[z + 1];
+                const double e = w[prev][cur]; mn = e < mn ? e : mn;
+                prev = cur;
+            }
+            const double e = w[prev][0]; mn = e < mn ? e : mn;
+            rbest = mn > rbest ? mn : rbest;
+        }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) {
+            const double ob = __shfl_xor_sync(0xffffffffu, best, off), orr = __shfl_xor_sync(0xffffffffu, rbest, off);
+            best = ob < best ? ob : best; rbest = orr > rbest ? orr : rbest;
+        }
+        bis = best; ring = rbest;
+    }
+    if (lane == 0) { out[i].bisection_gbps = bis; out[i].ring_bottleneck_gbps = ring; }
+}
+
 }  // namespace kgwe

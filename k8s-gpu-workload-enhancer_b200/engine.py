@@ -102,6 +102,23 @@ class Engine:
         self._check(self.lib.kgwe_schedule_queue(self.h, abi.ptr(pods), len(pods), abi.ptr(hint), abi.ptr(out)))
         return out
 
+    def schedule_gangs(self, pods, gang_of, hint=None):
+        """E5: all-or-nothing gangs (members consecutive, gang_of non-decreasing)."""
+        pods = np.ascontiguousarray(pods, dtype=abi.POD_REQ)
+        gang_of = np.ascontiguousarray(gang_of, dtype=np.uint32)
+        out = np.zeros(len(pods), dtype=abi.PLACEMENT)
+        if hint is not None:
+            hint = np.ascontiguousarray(hint, dtype=np.uint8)
+        self._check(self.lib.kgwe_schedule_gangs(self.h, abi.ptr(pods), len(pods), abi.ptr(gang_of), abi.ptr(hint), abi.ptr(out)))
+        return out
+
+    def placement_terms(self, placements):
+        """E4: bisection bandwidth and ring bottleneck of each placement's GPU set."""
+        pl = np.ascontiguousarray(placements, dtype=abi.PLACEMENT).reshape(-1)
+        out = np.zeros(len(pl), dtype=abi.SIDE_TERMS)
+        self._check(self.lib.kgwe_placement_terms(self.h, abi.ptr(pl), len(pl), abi.ptr(out)))
+        return out
+
     def stats(self):
         s = abi.Stats()
         self._check(self.lib.kgwe_get_stats(self.h, C.byref(s)))

@@ -28,6 +28,8 @@ def lib():
         _lib = C.CDLL(LIB_PATH)
         vp, u32 = C.c_void_p, C.c_uint32
         _lib.kgwe_oracle_score_batch.argtypes = [vp, vp, u32, vp, u32, vp, u32, vp, vp, u32, vp, C.c_int, C.c_int, C.POINTER(Counters)]
+        _lib.kgwe_oracle_schedule_gangs.argtypes = [vp, vp, u32, vp, u32, vp, u32, vp, vp, vp, vp, C.POINTER(u32), C.c_int]
+        _lib.kgwe_oracle_placement_terms.argtypes = [vp, vp, u32, vp, u32, vp]
         _lib.kgwe_oracle_schedule_queue.argtypes = [vp, vp, u32, vp, u32, vp, u32, vp, vp, vp, C.POINTER(u32), C.c_int, C.POINTER(Counters)]
     return _lib
 
@@ -73,3 +75,35 @@ def schedule_queue(abi, nodes, ledger, pods, hint=None, mode=INDEXED, cfg=None):
     if rc != 0:
         raise RuntimeError(f"oracle error {rc}")
     return out, led_out[: n_out.value].copy(), {"evaluations": c.evaluations, "candidates": c.candidates, "seconds": c.seconds}
+
+
+def schedule_gangs(abi, nodes, ledger, pods, gang_of, hint=None, mode=INDEXED, cfg=None):
+    """E5 all-or-nothing gangs.  Returns (decisions[P], final ledger)."""
+    nodes = np.ascontiguousarray(nodes, dtype=abi.NODE_IMAGE)
+    pods = np.ascontiguousarray(pods, dtype=abi.POD_REQ)
+    gang_of = np.ascontiguousarray(gang_of, dtype=np.uint32)
+    ledger = np.ascontiguousarray(ledger if ledger is not None else np.zeros(0, abi.ALLOC), dtype=abi.ALLOC)
+    P, N = len(pods), len(nodes)
+    out = np.zeros(P, dtype=abi.PLACEMENT)
+    led_out = np.zeros(len(ledger) + P, dtype=abi.ALLOC)
+    n_out = C.c_uint32(0)
+    cfg = cfg if cfg is not None else abi.default_config(N)
+    if hint is not None:
+        hint = np.ascontiguousarray(hint, dtype=np.uint8)
+    rc = lib().kgwe_oracle_schedule_gangs(C.addressof(cfg), _p(nodes), N, _p(ledger), len(ledger), _p(pods), P, _p(gang_of), _p(hint),
+                                          _p(out), _p(led_out), C.byref(n_out), mode)
+    if rc != 0:
+        raise RuntimeError(f"oracle error {rc}")
+    return out, led_out[: n_out.value].copy()
+
+
+def placement_terms(abi, nodes, placements, cfg=None):
+    """E4 side terms by brute force."""
+    nodes = np.ascontiguousarray(nodes, dtype=abi.NODE_IMAGE)
+    pl = np.ascontiguousarray(placements, dtype=abi.PLACEMENT).reshape(-1)
+    out = np.zeros(len(pl), dtype=abi.SIDE_TERMS)
+    cfg = cfg if cfg is not None else abi.default_config(len(nodes))
+    rc = lib().kgwe_oracle_placement_terms(C.addressof(cfg), _p(nodes), len(nodes), _p(pl), len(pl), _p(out))
+    if rc != 0:
+        raise RuntimeError(f"oracle error {rc}")
+    return out

@@ -830,3 +830,73 @@ extern "C" int kgwe_oracle_schedule_queue(const kgwe_config* cfg, const kgwe_nod
     delete world;
     return KGWE_OK;
 }
+
+// EXTENSION E5 (no reference counterpart beyond the GangSchedulingGroup type, types.go:415-444)
+extern "C" int kgwe_oracle_schedule_gangs(const kgwe_config* cfg, const kgwe_node_image* nodes, uint32_t n_nodes,
+                                          const kgwe_oracle_alloc* ledger, uint32_t n_ledger,
+                                          const kgwe_pod_req* pods, uint32_t n_pods, const uint32_t* gang_of, const uint8_t* hint,
+                                          kgwe_placement* out, kgwe_oracle_alloc* ledger_out, uint32_t* n_ledger_out, int mode) {
+    if (!nodes || !pods || !out || !gang_of) return KGWE_ERR_INVALID_ARG;
+    std::vector<kgwe_oracle_alloc> led(ledger, ledger + n_ledger);
+    const size_t row = (n_nodes + 7) / 8;
+    uint32_t p0 = 0;
+    while (p0 < n_pods) {
+        uint32_t p1 = p0 + 1;
+        while (p1 < n_pods && gang_of[p1] == gang_of[p0]) ++p1;
+        const uint32_t np = p1 - p0;
+        std::vector<kgwe_oracle_alloc> next(led.size() + np);
+        uint32_t n_next = 0;
+        int rc = kgwe_oracle_schedule_queue(cfg, nodes, n_nodes, led.data(), (uint32_t)led.size(), pods + p0, np,
+                                            hint ? hint + (size_t)p0 * row : nullptr, out + p0, next.data(), &n_next, mode, nullptr);
+        if (rc != KGWE_OK) return rc;
+        bool all = true;
+        for (uint32_t i = 0; i < np; ++i) if (out[p0 + i].node_idx == KGWE_NO_NODE) all = false;
+        if (all) { next.resize(n_next); led.swap(next); }
+        else for (uint32_t i = 0; i < np; ++i) {            // roll the whole gang back
+            const bool had = out[p0 + i].node_idx != KGWE_NO_NODE;
+            out[p0 + i] = no_placement();
+            out[p0 + i].flags = had ? KGWE_F_GANG_ROLLBACK : 0;
+        }
+        p0 = p1;
+    }
+    if (ledger_out && n_ledger_out) { memcpy(ledger_out, led.data(), led.size() * sizeof(kgwe_oracle_alloc)); *n_ledger_out = (uint32_t)led.size(); }
+    return KGWE_OK;
+}
+
+// EXTENSION E4
+extern "C" int kgwe_oracle_placement_terms(const kgwe_config* cfg, const kgwe_node_image* nodes, uint32_t n_nodes,
+                                           const kgwe_placement* pls, uint32_t n, kgwe_side_terms* out) {
+    if (!nodes || !pls || !out) return KGWE_ERR_INVALID_ARG;
+    const uint32_t base = cfg ? cfg->node_base : 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        out[i].bisection_gbps = 0.0; out[i].ring_bottleneck_gbps = 0.0;
+        if (pls[i].node_idx == KGWE_NO_NODE || pls[i].node_idx - base >= n_nodes) continue;
+        const kgwe_node_image& im = nodes[pls[i].node_idx - base];
+        std::vector<int> g;
+        for (int b = 0; b < KGWE_MAX_GPUS; ++b) if (pls[i].gpu_mask >> b & 1) g.push_back(b);
+        const int k = (int)g.size();
+        if (k < 2) continue;
+        auto w = [&](int a, int b) -> double {
+            if (!indexed::link_active(im, g[a], g[b]) || !indexed::link_active(im, g[b], g[a])) return 0.0;
+            return std::min(im.nvl_bw[g[a]][g[b]], im.nvl_bw[g[b]][g[a]]);
+        };
+        double best = 1e300;
+        for (unsigned t = 0; t < (1u << k); ++t) {
+            if (__builtin_popcount(t) != k / 2) continue;
+            double cut = 0.0;
+            for (int a = 0; a < k; ++a) if (t >> a & 1) for (int b = 0; b < k; ++b) if (!(t >> b & 1)) cut += w(a, b);
+            best = std::min(best, cut);
+        }
+        std::vector<int> perm;
+        for (int q = 1; q < k; ++q) perm.push_back(q);
+        double ring = -1.0;
+        do {
+            double mn = w(0, perm[0]);
+            for (int q = 0; q + 1 < k - 1; ++q) mn = std::min(mn, w(perm[q], perm[q + 1]));
+            mn = std::min(mn, w(perm[k - 2], 0));
+            ring = std::max(ring, mn);
+        } while (std::next_permutation(perm.begin(), perm.end()));
+        out[i].bisection_gbps = best; out[i].ring_bottleneck_gbps = ring;
+    }
+    return KGWE_OK;
+}

@@ -59,6 +59,20 @@ int kgwe_oracle_schedule_queue(const kgwe_config* cfg,
                                kgwe_oracle_alloc* ledger_out, uint32_t* n_ledger_out,
                                int mode, kgwe_oracle_counters* counters);
 
+/* EXTENSION E5: all-or-nothing gangs over Schedule() (see kgwe_schedule_gangs). */
+int kgwe_oracle_schedule_gangs(const kgwe_config* cfg,
+                               const kgwe_node_image* nodes, uint32_t n_nodes,
+                               const kgwe_oracle_alloc* ledger, uint32_t n_ledger,
+                               const kgwe_pod_req* pods, uint32_t n_pods, const uint32_t* gang_of,
+                               const uint8_t* hint_bitmap,
+                               kgwe_placement* out,
+                               kgwe_oracle_alloc* ledger_out, uint32_t* n_ledger_out, int mode);
+
+/* EXTENSION E4: bisection bandwidth / ring bottleneck of each placement (see kgwe_placement_terms).
+ * Plain loops: every subset, every permutation (std::next_permutation). */
+int kgwe_oracle_placement_terms(const kgwe_config* cfg, const kgwe_node_image* nodes, uint32_t n_nodes,
+                                const kgwe_placement* placements, uint32_t n, kgwe_side_terms* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -289,3 +289,57 @@ def test_fractional_bandwidths_take_the_fp64_path(kg, orc):
     o_dec, _, _ = orc.schedule_queue(abi, nodes, led, pods)
     assert_same_placements(dec, o_dec)
     eng.close()
+
+
+def test_gang_scheduling_extension(kg, orc):
+    """E5: config 5 shape (8 members x 8 GPUs per gang) on a cluster too small for all gangs, so
+    some gangs roll back in the middle of the queue; plus hand-built mixed gangs."""
+    abi, synth = kg.abi, kg.synth
+    nodes, pods, led = synth.config(5, 0.012)            # 120 nodes, 15 gangs of 8 x 8 GPUs
+    gang_of = (np.arange(len(pods)) // 8).astype(np.uint32)
+    eng = engine_for(kg, nodes, led)
+    dec = eng.schedule_gangs(pods, gang_of)
+    o_dec, o_led = orc.schedule_gangs(abi, nodes, led, pods, gang_of)
+    assert_same_placements(dec, o_dec)
+    assert eng.stats()["n_allocations"] == len(o_led)
+    assert (dec["node_idx"] == abi.NO_NODE).any() and (dec["node_idx"] != abi.NO_NODE).any()
+    # the image must match the oracle's final ledger (rolled-back commits really gone)
+    s, _ = eng.score_batch(pods[:16], len(nodes), want_scores=True)
+    o, _, _ = orc.score_batch(abi, nodes, o_led, pods[:16], want_scores=True)
+    assert s.tobytes() == o.tobytes()
+    eng.close()
+    # ragged gangs with mixed sizes and preferences, several failures in a row
+    nodes = synth.make_cluster(40, "mixed", seed=3)
+    pods = synth.make_pods(300, seed=3, k_lo=3, k_hi=8)
+    sizes = synth.SplitMix64(5).randint(1, 9, 100)
+    gang_of = np.repeat(np.arange(100), sizes)[:300].astype(np.uint32)
+    eng = engine_for(kg, nodes)
+    dec = eng.schedule_gangs(pods, gang_of)
+    o_dec, o_led = orc.schedule_gangs(abi, nodes, None, pods, gang_of)
+    assert_same_placements(dec, o_dec)
+    assert (dec["flags"] & abi.F_GANG_ROLLBACK).any()
+    eng.close()
+
+
+def test_side_terms_extension(kg, orc):
+    """E4: bisection bandwidth / ring bottleneck of placements, GPU vs brute force (the only
+    floating-point accumulation is the cut sum, in a fixed order: bit-exact expected)."""
+    abi, synth = kg.abi, kg.synth
+    nodes = synth.make_cluster(300, "mixed", seed=8, inactive_link_frac=0.08)
+    rng = synth.SplitMix64(9)
+    jitter = 0.5 + rng.uniform(len(nodes) * 64).reshape(len(nodes), 8, 8)
+    nodes["nvl_bw"] = nodes["nvl_bw"] * jitter                     # asymmetric, non-integral
+    pods = synth.make_pods(400, seed=8)
+    eng = engine_for(kg, nodes)
+    dec = eng.schedule_queue(pods)
+    extra = np.zeros(3, dtype=abi.PLACEMENT)
+    extra["node_idx"] = [abi.NO_NODE, 0, 5]
+    extra["gpu_mask"] = [0, 0xFF, 0x00]
+    pls = np.concatenate([dec, extra])
+    t = eng.placement_terms(pls)
+    o = orc.placement_terms(abi, nodes, pls)
+    np.testing.assert_allclose(t["bisection_gbps"], o["bisection_gbps"], rtol=REL_TOL, atol=0)
+    np.testing.assert_allclose(t["ring_bottleneck_gbps"], o["ring_bottleneck_gbps"], rtol=REL_TOL, atol=0)
+    assert t.tobytes() == o.tobytes()
+    assert (t["bisection_gbps"] > 0).any() and (t["ring_bottleneck_gbps"] > 0).any()
+    eng.close()
