@@ -296,6 +296,40 @@ typedef struct kgwe_side_terms {
 } kgwe_side_terms;
 int kgwe_placement_terms(kgwe_engine* e, const kgwe_placement* placements, uint32_t n, kgwe_side_terms* out);
 
+/* EXTENSION E2 - MIG slice bin-packing and rebalancing.  The reference only has stubs here
+ * (findAvailableInstance / findGPUWithCapacity always fail, Rebalance is empty:
+ * src/sharing/mig_controller.go:340-348, 407-415, 480-504); its data are the profile table
+ * (src/discovery/types.go:233-239: max 7/3/2/1/1 instances of 1g/2g/3g/4g/7g) and the 10-name
+ * whitelist.  Own spec:
+ *   - a GPU has 8 memory slices; `occ` is the occupancy bitmask.  A profile (ids 1..10, whitelist
+ *     order) has a class (odd id = 40 GB parts: 1g.5gb 2g.10gb 3g.20gb 4g.20gb 7g.40gb; even id =
+ *     80 GB parts) and a geometry with fixed legal placements (NVIDIA's MIG placement rules):
+ *     1g: 1 slice at 0..6; 2g: 2 slices at 0,2,4; 3g: 4 slices at 0,4; 4g: 4 slices at 0; 7g: all 8.
+ *   - a request fits placement m on a MIG-enabled GPU of its class when (occ & m) == 0.  Among all
+ *     fits in the cluster choose the one that destroys the fewest still-free legal placements of
+ *     that GPU (the 14 placements above, itself included); ties -> lowest GPU index, then lowest
+ *     start.  Requests are served in order, each commit (occ |= m) is seen by the next. */
+typedef struct kgwe_mig_gpu { uint8_t occ; uint8_t cls; uint8_t enabled; uint8_t pad; } kgwe_mig_gpu;
+typedef struct kgwe_mig_assignment {
+    uint32_t gpu_idx;      /* KGWE_NO_NODE when nothing fits */
+    uint8_t  start, size, cost, profile;
+} kgwe_mig_assignment;
+/* gpus: in/out (occupancy after all commits); profiles: n_reqs profile ids; host buffers. */
+int kgwe_mig_pack(kgwe_engine* e, kgwe_mig_gpu* gpus, uint32_t n_gpus, const uint8_t* profiles, uint32_t n_reqs,
+                  kgwe_mig_assignment* out);
+
+/*   - rebalancing pass: idle GPUs (enabled, occ == 0) of each class are split among that class's
+ *     profiles in proportion to target[profile-1] (MIGStrategy.ProfileDistribution, mig_controller.go
+ *     :263-270): profile p gets floor(share_p * idle) GPUs in profile order, the remainder goes to the
+ *     largest fractional parts (ties: lowest profile id); idle GPUs are handed out in index order and
+ *     each is filled with as many instances of its profile as fit (7/3/2/1/1).  Emits one create op
+ *     per instance - 40 GB-class GPUs first, then 80 GB-class, each by profile, GPU index, start -
+ *     and the resulting free-instance supply per profile.  *n_ops is the number of ops the plan
+ *     has; only the first ops_cap are written. */
+typedef struct kgwe_mig_op { uint32_t gpu_idx; uint8_t profile, start, size, pad; } kgwe_mig_op;
+int kgwe_mig_rebalance(kgwe_engine* e, const kgwe_mig_gpu* gpus, uint32_t n_gpus, const double* target /*[10]*/,
+                       kgwe_mig_op* ops, uint32_t ops_cap, uint32_t* n_ops, uint32_t* supply /*[10]*/);
+
 /* Read one record back (device -> host) in ABI layout, ledger fields included. */
 int kgwe_node_read(kgwe_engine* e, uint32_t local_idx, kgwe_node_image* out);
 

@@ -21,6 +21,9 @@ MIG_NONE, MIG_UNKNOWN = 0, 255
 MIG_NAMES = ["1g.5gb", "1g.10gb", "2g.10gb", "2g.20gb", "3g.20gb", "3g.40gb", "4g.20gb", "4g.40gb", "7g.40gb", "7g.80gb"]
 POD_EXHAUSTIVE = 0x01
 F_ELIGIBLE, F_KEPT, F_HINT, F_FALLBACK, F_MINBW, F_GANG_ROLLBACK = 0x01, 0x02, 0x04, 0x08, 0x10, 0x20
+MIG_GPU = np.dtype([("occ", "u1"), ("cls", "u1"), ("enabled", "u1"), ("pad", "u1")])
+MIG_ASSIGNMENT = np.dtype([("gpu_idx", "<u4"), ("start", "u1"), ("size", "u1"), ("cost", "u1"), ("profile", "u1")])
+MIG_OP = np.dtype([("gpu_idx", "<u4"), ("profile", "u1"), ("start", "u1"), ("size", "u1"), ("pad", "u1")])
 SIDE_TERMS = np.dtype([("bisection_gbps", "<f8"), ("ring_bottleneck_gbps", "<f8")])
 
 NODE_IMAGE = np.dtype([
@@ -75,7 +78,7 @@ ENGINE_SYMBOLS = [
     "kgwe_node_remove", "kgwe_alloc_commit", "kgwe_alloc_release", "kgwe_score_batch", "kgwe_score_batch_device",
     "kgwe_topk_merge_device", "kgwe_schedule_queue", "kgwe_node_read", "kgwe_get_stats", "kgwe_last_error",
     "kgwe_version", "kgwe_score_top1_noalloc", "kgwe_topk_merge_host",
-    "kgwe_schedule_gangs", "kgwe_placement_terms",
+    "kgwe_schedule_gangs", "kgwe_placement_terms", "kgwe_mig_pack", "kgwe_mig_rebalance",
 ]
 NOALLOC_MAX_PODS = 16384
 
@@ -105,6 +108,8 @@ def load_engine_lib():
     lib.kgwe_score_batch.argtypes = [vp, vp, u32, vp, vp, u32, vp]
     lib.kgwe_score_batch_device.argtypes = [vp, vp, u32, vp, vp, u32, vp, vp]
     lib.kgwe_score_top1_noalloc.argtypes = [vp, vp, u32, vp, vp, vp, vp]
+    lib.kgwe_mig_pack.argtypes = [vp, vp, u32, vp, u32, vp]
+    lib.kgwe_mig_rebalance.argtypes = [vp, vp, u32, vp, vp, u32, C.POINTER(u32), vp]
     lib.kgwe_schedule_gangs.argtypes = [vp, vp, u32, vp, vp, vp]
     lib.kgwe_placement_terms.argtypes = [vp, vp, u32, vp]
     lib.kgwe_topk_merge_host.argtypes = [vp, u32, u32, u32, vp]

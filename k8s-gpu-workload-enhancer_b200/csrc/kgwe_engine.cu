@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "kgwe_kernels.cuh"
+#include "kgwe_mig.cuh"
 
 using namespace kgwe;
 
@@ -693,6 +694,84 @@ int kgwe_placement_terms(kgwe_engine* e, const kgwe_placement* placements, uint3
     CU(e, cudaStreamSynchronize(s));
     memcpy(out, e->h_topk.p, (size_t)n * sizeof(kgwe_side_terms));
     e->stats.h2d_bytes += (uint64_t)n * sizeof(kgwe_placement); e->stats.d2h_bytes += (uint64_t)n * sizeof(kgwe_side_terms);
+    return KGWE_OK;
+}
+
+// E2.  The MIG table is the caller's; the engine lends its device, stream and scratch.
+int kgwe_mig_pack(kgwe_engine* e, kgwe_mig_gpu* gpus, uint32_t n_gpus, const uint8_t* profiles, uint32_t n_reqs, kgwe_mig_assignment* out) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if ((n_gpus && !gpus) || (n_reqs && (!profiles || !out))) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    if (n_reqs == 0 || n_gpus == 0) {
+        for (uint32_t i = 0; i < n_reqs; ++i) { memset(&out[i], 0, sizeof out[i]); out[i].gpu_idx = KGWE_NO_NODE; out[i].profile = profiles[i]; }
+        return KGWE_OK;
+    }
+    const size_t smem = (size_t)MIG_GEOS * 256 + 33 * 4 + 2 * (size_t)n_gpus;
+    if (smem > 200 * 1024 || n_gpus >= (1u << 24)) return fail(e, KGWE_ERR_TOO_LARGE, "kgwe_mig_pack: %u GPUs exceed the single-CTA table (max ~100k per call; shard by GPU)", n_gpus);
+    CU(e, cudaSetDevice(e->cfg.device));
+    cudaStream_t s = e->stream;
+    static_assert(sizeof(kgwe_mig_gpu) == 4 && sizeof(kgwe_mig_assignment) == 8 && sizeof(kgwe_mig_op) == 8, "MIG ABI sizes");
+    const size_t bytes_g = (size_t)n_gpus * sizeof(kgwe_mig_gpu), bytes_o = (size_t)n_reqs * sizeof(kgwe_mig_assignment);
+    // scratch carved from the byte buffers: [gpus][profiles][assignments]
+    const size_t off_p = (bytes_g + 255) & ~(size_t)255, off_o = (off_p + n_reqs + 255) & ~(size_t)255, total = off_o + bytes_o;
+    CU(e, e->d_hint.ensure(total)); CU(e, e->h_hint.ensure(total));
+    memcpy(e->h_hint.p, gpus, bytes_g); memcpy(e->h_hint.p + off_p, profiles, n_reqs);
+    CU(e, cudaMemcpyAsync(e->d_hint.p, e->h_hint.p, off_p + n_reqs, cudaMemcpyHostToDevice, s));
+    CU(e, cudaFuncSetAttribute(mig_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(e, cudaEventRecord(e->ev0, s));
+    mig_pack_kernel<<<1, MIG_THREADS, smem, s>>>(reinterpret_cast<kgwe_mig_gpu*>(e->d_hint.p), n_gpus, e->d_hint.p + off_p, n_reqs,
+                                                 reinterpret_cast<kgwe_mig_assignment*>(e->d_hint.p + off_o));
+    CU(e, cudaGetLastError());
+    CU(e, cudaEventRecord(e->ev1, s));
+    e->stats.kernel_launches++;
+    CU(e, cudaMemcpyAsync(e->h_hint.p, e->d_hint.p, bytes_g, cudaMemcpyDeviceToHost, s));
+    CU(e, cudaMemcpyAsync(e->h_hint.p + off_o, e->d_hint.p + off_o, bytes_o, cudaMemcpyDeviceToHost, s));
+    CU(e, cudaStreamSynchronize(s));
+    memcpy(gpus, e->h_hint.p, bytes_g); memcpy(out, e->h_hint.p + off_o, bytes_o);
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) == cudaSuccess) e->stats.last_call_gpu_ms = ms;
+    e->stats.h2d_bytes += off_p + n_reqs; e->stats.d2h_bytes += bytes_g + bytes_o;
+    return KGWE_OK;
+}
+
+int kgwe_mig_rebalance(kgwe_engine* e, const kgwe_mig_gpu* gpus, uint32_t n_gpus, const double* target,
+                       kgwe_mig_op* ops, uint32_t ops_cap, uint32_t* n_ops, uint32_t* supply) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if ((n_gpus && !gpus) || !target || !n_ops || !supply || (ops_cap && !ops)) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    double sum = 0.0;
+    for (int p = 0; p < KGWE_MIG_PROFILES; ++p) { if (!(target[p] >= 0.0)) return fail(e, KGWE_ERR_INVALID_ARG, "target[%d] must be >= 0", p); sum += target[p]; }
+    if (sum > 1.01) return fail(e, KGWE_ERR_INVALID_ARG, "profile distribution exceeds 100%%");      // mig_controller.go:263-270
+    *n_ops = 0; for (int p = 0; p < KGWE_MIG_PROFILES; ++p) supply[p] = 0;
+    if (n_gpus == 0) return KGWE_OK;
+    CU(e, cudaSetDevice(e->cfg.device));
+    cudaStream_t s = e->stream;
+    const size_t bytes_g = (size_t)n_gpus * sizeof(kgwe_mig_gpu);
+    const size_t off_r = (bytes_g + 255) & ~(size_t)255, off_c = off_r + (size_t)n_gpus * 4, off_o = (off_c + 8 + 255) & ~(size_t)255;
+    const size_t total = off_o + (size_t)ops_cap * sizeof(kgwe_mig_op);
+    CU(e, e->d_hint.ensure(total)); CU(e, e->h_hint.ensure(total));
+    memcpy(e->h_hint.p, gpus, bytes_g);
+    CU(e, cudaMemcpyAsync(e->d_hint.p, e->h_hint.p, bytes_g, cudaMemcpyHostToDevice, s));
+    uint32_t* d_rank = reinterpret_cast<uint32_t*>(e->d_hint.p + off_r);
+    uint32_t* d_cnt = reinterpret_cast<uint32_t*>(e->d_hint.p + off_c);
+    mig_rank_kernel<<<1, 1024, 0, s>>>(reinterpret_cast<const kgwe_mig_gpu*>(e->d_hint.p), n_gpus, d_rank, d_cnt);
+    CU(e, cudaGetLastError());
+    uint32_t idle[2] = {0, 0};
+    CU(e, cudaMemcpyAsync(e->h_hint.p + off_c, d_cnt, 8, cudaMemcpyDeviceToHost, s));
+    CU(e, cudaStreamSynchronize(s));
+    memcpy(idle, e->h_hint.p + off_c, 8);
+    MigPlan plan;
+    mig_make_plan(idle, target, plan, n_ops, supply);
+    const uint32_t n_write = std::min(*n_ops, ops_cap);
+    if (n_write) {
+        mig_emit_kernel<<<(n_gpus + 255) / 256, 256, 0, s>>>(reinterpret_cast<const kgwe_mig_gpu*>(e->d_hint.p), n_gpus, d_rank, plan,
+                                                            reinterpret_cast<kgwe_mig_op*>(e->d_hint.p + off_o), ops_cap);
+        CU(e, cudaGetLastError());
+        CU(e, cudaMemcpyAsync(e->h_hint.p + off_o, e->d_hint.p + off_o, (size_t)n_write * sizeof(kgwe_mig_op), cudaMemcpyDeviceToHost, s));
+        CU(e, cudaStreamSynchronize(s));
+        memcpy(ops, e->h_hint.p + off_o, (size_t)n_write * sizeof(kgwe_mig_op));
+    }
+    e->stats.kernel_launches += 2;
     return KGWE_OK;
 }
 

@@ -119,6 +119,25 @@ class Engine:
         self._check(self.lib.kgwe_placement_terms(self.h, abi.ptr(pl), len(pl), abi.ptr(out)))
         return out
 
+    def mig_pack(self, gpus, profiles):
+        """E2: serve MIG slice requests in order (best-fit).  Returns (assignments, gpus after)."""
+        gpus = np.ascontiguousarray(gpus, dtype=abi.MIG_GPU).copy()
+        profiles = np.ascontiguousarray(profiles, dtype=np.uint8)
+        out = np.zeros(len(profiles), dtype=abi.MIG_ASSIGNMENT)
+        self._check(self.lib.kgwe_mig_pack(self.h, abi.ptr(gpus), len(gpus), abi.ptr(profiles), len(profiles), abi.ptr(out)))
+        return out, gpus
+
+    def mig_rebalance(self, gpus, target, ops_cap=None):
+        """E2: repartition idle GPUs toward `target` (10 fractions).  Returns (ops, supply[10])."""
+        gpus = np.ascontiguousarray(gpus, dtype=abi.MIG_GPU)
+        target = np.ascontiguousarray(target, dtype=np.float64)
+        cap = ops_cap if ops_cap is not None else 7 * len(gpus)
+        ops = np.zeros(cap, dtype=abi.MIG_OP)
+        supply = np.zeros(10, dtype=np.uint32)
+        n = C.c_uint32(0)
+        self._check(self.lib.kgwe_mig_rebalance(self.h, abi.ptr(gpus), len(gpus), abi.ptr(target), abi.ptr(ops), cap, C.byref(n), abi.ptr(supply)))
+        return ops[: min(n.value, cap)].copy(), supply, n.value
+
     def stats(self):
         s = abi.Stats()
         self._check(self.lib.kgwe_get_stats(self.h, C.byref(s)))

@@ -156,6 +156,30 @@ def make_hint(n_pods, n_nodes, frac, seed=SEED_BASE):
     return np.packbits(bits, axis=1, bitorder="little")
 
 
+def make_mig(n_gpus, n_reqs, seed=SEED_BASE ^ 4, occupancy=0.4):
+    """BASELINE configs[3]: MIG-enabled GPUs (half 40 GB-class, half 80 GB-class, 3% MIG-disabled) with
+    a random VALID initial occupancy (~`occupancy` of the GPUs carry instances), and a request stream
+    with the example ProfileDistribution 70/20/10 % for 1g/2g/3g (reference
+    examples/distributed-training.yaml:183-186) plus 5 % 4g/7g.  Returns (gpus, profiles)."""
+    rng = SplitMix64(seed)
+    gpus = np.zeros(n_gpus, dtype=abi.MIG_GPU)
+    gpus["cls"] = rng.randint(0, 1, n_gpus)
+    gpus["enabled"] = (rng.uniform(n_gpus) >= 0.03).astype(np.uint8)
+    # valid occupancies = unions of disjoint legal placements: pick a few random placements per busy GPU
+    masks = np.array([1 << s for s in range(7)] + [3, 12, 48] + [15, 240] + [15] + [255], dtype=np.uint16)
+    busy = rng.uniform(n_gpus) < occupancy
+    occ = np.zeros(n_gpus, dtype=np.uint16)
+    for _ in range(3):
+        pick = masks[rng.randint(0, len(masks) - 1, n_gpus)]
+        ok = busy & ((occ & pick) == 0) & (rng.uniform(n_gpus) < 0.7)
+        occ = np.where(ok, occ | pick, occ)
+    gpus["occ"] = occ.astype(np.uint8)
+    geo = rng.choice([0.665, 0.19, 0.095, 0.025, 0.025], n_reqs)      # 70/20/10 scaled to 95 % + 2.5 % 4g + 2.5 % 7g
+    cls = rng.randint(0, 1, n_reqs)
+    profiles = (2 * geo + 1 + cls).astype(np.uint8)
+    return gpus, profiles
+
+
 def config(num, scale=1.0):
     """(nodes, pods, ledger) for BASELINE.json configs[num-1]; `scale` shrinks N and P for tests."""
     seed = SEED_BASE ^ num

@@ -28,6 +28,8 @@ def lib():
         _lib = C.CDLL(LIB_PATH)
         vp, u32 = C.c_void_p, C.c_uint32
         _lib.kgwe_oracle_score_batch.argtypes = [vp, vp, u32, vp, u32, vp, u32, vp, vp, u32, vp, C.c_int, C.c_int, C.POINTER(Counters)]
+        _lib.kgwe_oracle_mig_pack.argtypes = [vp, u32, vp, u32, vp]
+        _lib.kgwe_oracle_mig_rebalance.argtypes = [vp, u32, vp, vp, u32, C.POINTER(u32), vp]
         _lib.kgwe_oracle_schedule_gangs.argtypes = [vp, vp, u32, vp, u32, vp, u32, vp, vp, vp, vp, C.POINTER(u32), C.c_int]
         _lib.kgwe_oracle_placement_terms.argtypes = [vp, vp, u32, vp, u32, vp]
         _lib.kgwe_oracle_schedule_queue.argtypes = [vp, vp, u32, vp, u32, vp, u32, vp, vp, vp, C.POINTER(u32), C.c_int, C.POINTER(Counters)]
@@ -107,3 +109,26 @@ def placement_terms(abi, nodes, placements, cfg=None):
     if rc != 0:
         raise RuntimeError(f"oracle error {rc}")
     return out
+
+
+def mig_pack(abi, gpus, profiles):
+    gpus = np.ascontiguousarray(gpus, dtype=abi.MIG_GPU).copy()
+    profiles = np.ascontiguousarray(profiles, dtype=np.uint8)
+    out = np.zeros(len(profiles), dtype=abi.MIG_ASSIGNMENT)
+    rc = lib().kgwe_oracle_mig_pack(_p(gpus), len(gpus), _p(profiles), len(profiles), _p(out))
+    if rc != 0:
+        raise RuntimeError(f"oracle error {rc}")
+    return out, gpus
+
+
+def mig_rebalance(abi, gpus, target, ops_cap=None):
+    gpus = np.ascontiguousarray(gpus, dtype=abi.MIG_GPU)
+    target = np.ascontiguousarray(target, dtype=np.float64)
+    cap = ops_cap if ops_cap is not None else 7 * len(gpus)
+    ops = np.zeros(cap, dtype=abi.MIG_OP)
+    supply = np.zeros(10, dtype=np.uint32)
+    n = C.c_uint32(0)
+    rc = lib().kgwe_oracle_mig_rebalance(_p(gpus), len(gpus), _p(target), _p(ops), cap, C.byref(n), _p(supply))
+    if rc != 0:
+        raise RuntimeError(f"oracle error {rc}")
+    return ops[: min(n.value, cap)].copy(), supply, n.value

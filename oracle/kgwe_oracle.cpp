@@ -900,3 +900,83 @@ extern "C" int kgwe_oracle_placement_terms(const kgwe_config* cfg, const kgwe_no
     }
     return KGWE_OK;
 }
+
+// EXTENSION E2 — MIG placement tables (NVIDIA MIG placement rules; instance maxima agree with
+// the reference's profile table, src/discovery/types.go:233-239: 7 / 3 / 2 / 1 / 1).
+namespace mig {
+struct Placement { int geo, start, size; unsigned mask; };
+const int kSize[5] = {1, 2, 4, 4, 8};
+std::vector<Placement> legal() {
+    std::vector<Placement> v;
+    for (int s = 0; s <= 6; ++s) v.push_back({0, s, 1, 1u << s});
+    for (int s = 0; s <= 4; s += 2) v.push_back({1, s, 2, 3u << s});
+    for (int s = 0; s <= 4; s += 4) v.push_back({2, s, 4, 15u << s});
+    v.push_back({3, 0, 4, 15u});
+    v.push_back({4, 0, 8, 255u});
+    return v;
+}
+}  // namespace mig
+
+extern "C" int kgwe_oracle_mig_pack(kgwe_mig_gpu* gpus, uint32_t n_gpus, const uint8_t* profiles, uint32_t n_reqs, kgwe_mig_assignment* out) {
+    if ((n_gpus && !gpus) || (n_reqs && (!profiles || !out))) return KGWE_ERR_INVALID_ARG;
+    const std::vector<mig::Placement> all = mig::legal();
+    for (uint32_t r = 0; r < n_reqs; ++r) {
+        const int p = profiles[r];
+        kgwe_mig_assignment a; memset(&a, 0, sizeof a); a.gpu_idx = KGWE_NO_NODE; a.profile = (uint8_t)p;
+        if (p >= 1 && p <= KGWE_MIG_PROFILES) {
+            const int geo = (p - 1) / 2, cls = (p - 1) % 2;
+            int bestCost = 1 << 30;
+            for (uint32_t g = 0; g < n_gpus; ++g) {
+                if (!gpus[g].enabled || (gpus[g].cls & 1) != cls) continue;
+                for (const auto& pl : all) {
+                    if (pl.geo != geo || (gpus[g].occ & pl.mask)) continue;
+                    int cost = 0;
+                    for (const auto& q : all) if (!(gpus[g].occ & q.mask) && (q.mask & pl.mask)) ++cost;
+                    if (cost < bestCost) { bestCost = cost; a.gpu_idx = g; a.start = (uint8_t)pl.start; a.size = (uint8_t)pl.size; a.cost = (uint8_t)cost; }
+                }
+            }
+            if (a.gpu_idx != KGWE_NO_NODE) gpus[a.gpu_idx].occ |= (uint8_t)(((1u << a.size) - 1u) << a.start);
+        }
+        out[r] = a;
+    }
+    return KGWE_OK;
+}
+
+extern "C" int kgwe_oracle_mig_rebalance(const kgwe_mig_gpu* gpus, uint32_t n_gpus, const double* target,
+                                         kgwe_mig_op* ops, uint32_t ops_cap, uint32_t* n_ops, uint32_t* supply) {
+    if ((n_gpus && !gpus) || !target || !n_ops || !supply) return KGWE_ERR_INVALID_ARG;
+    const int kStarts[5] = {7, 3, 2, 1, 1}, kStride[5] = {1, 2, 4, 0, 0};
+    std::vector<kgwe_mig_op> all;
+    for (int p = 0; p < KGWE_MIG_PROFILES; ++p) supply[p] = 0;
+    for (int c = 0; c < 2; ++c) {
+        std::vector<uint32_t> idle;
+        for (uint32_t g = 0; g < n_gpus; ++g) if (gpus[g].enabled && gpus[g].occ == 0 && (gpus[g].cls & 1) == c) idle.push_back(g);
+        double S = 0.0;
+        for (int q = 0; q < 5; ++q) if (target[2 * q + c] > 0.0) S += target[2 * q + c];
+        if (!(S > 0.0) || idle.empty()) continue;
+        uint32_t n[5] = {0, 0, 0, 0, 0}; double frac[5] = {0, 0, 0, 0, 0}; uint32_t used = 0;
+        for (int q = 0; q < 5; ++q) {
+            const double t = target[2 * q + c];
+            if (!(t > 0.0)) continue;
+            const double share = (t / S) * (double)idle.size();
+            n[q] = (uint32_t)share; frac[q] = share - (double)n[q]; used += n[q];
+        }
+        for (uint32_t left = (uint32_t)idle.size() - used; left > 0; --left) {
+            int bq = -1;
+            for (int q = 0; q < 5; ++q) if (target[2 * q + c] > 0.0 && (bq < 0 || frac[q] > frac[bq])) bq = q;
+            if (bq < 0) break;
+            n[bq]++; frac[bq] = -1.0;
+        }
+        size_t at = 0;
+        for (int q = 0; q < 5; ++q)
+            for (uint32_t i = 0; i < n[q]; ++i, ++at)
+                for (int sidx = 0; sidx < kStarts[q]; ++sidx) {
+                    kgwe_mig_op op; memset(&op, 0, sizeof op);
+                    op.gpu_idx = idle[at]; op.profile = (uint8_t)(2 * q + 1 + c); op.start = (uint8_t)(sidx * kStride[q]); op.size = (uint8_t)mig::kSize[q];
+                    all.push_back(op); supply[2 * q + c]++;
+                }
+    }
+    *n_ops = (uint32_t)all.size();
+    for (uint32_t i = 0; i < all.size() && i < ops_cap; ++i) ops[i] = all[i];
+    return KGWE_OK;
+}

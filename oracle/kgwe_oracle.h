@@ -73,6 +73,11 @@ int kgwe_oracle_schedule_gangs(const kgwe_config* cfg,
 int kgwe_oracle_placement_terms(const kgwe_config* cfg, const kgwe_node_image* nodes, uint32_t n_nodes,
                                 const kgwe_placement* placements, uint32_t n, kgwe_side_terms* out);
 
+/* EXTENSION E2: MIG bin-packing and rebalancing by plain loops (spec in include/kgwe_engine.h). */
+int kgwe_oracle_mig_pack(kgwe_mig_gpu* gpus, uint32_t n_gpus, const uint8_t* profiles, uint32_t n_reqs, kgwe_mig_assignment* out);
+int kgwe_oracle_mig_rebalance(const kgwe_mig_gpu* gpus, uint32_t n_gpus, const double* target,
+                              kgwe_mig_op* ops, uint32_t ops_cap, uint32_t* n_ops, uint32_t* supply);
+
 #ifdef __cplusplus
 }
 #endif

@@ -48,3 +48,50 @@ def test_gang_rollback(kg, orc):
         assert (dec[2:5]["node_idx"] == abi.NO_NODE).all()
         assert [int(f) for f in dec[2:5]["flags"]] == [abi.F_GANG_ROLLBACK, abi.F_GANG_ROLLBACK, 0]
         assert dec[5]["node_idx"] == 0 and dec[5]["gpu_mask"] == 0xF0 and len(led) == 3
+
+
+def test_mig_pack_known_answers(kg, orc):
+    """Hand-derived best-fit cases on one 80 GB-class GPU (profile ids: 2=1g.10gb 4=2g.20gb 6=3g.40gb 8=4g.40gb 10=7g.80gb)."""
+    abi = kg.abi
+    def gpus(*occ, cls=1, enabled=1):
+        g = np.zeros(len(occ), dtype=abi.MIG_GPU)
+        g["occ"], g["cls"], g["enabled"] = occ, cls, enabled
+        return g
+    # empty GPU, 1g: start s overlaps {1g@s, the 2g covering s (none for s=6), the 3g covering s, 4g if s<4, 7g}:
+    #   s=0..3 -> 5, s=4,5 -> 4, s=6 -> 3  => best-fit takes start 6 (cost 3)
+    a, g = orc.mig_pack(abi, gpus(0), [2])
+    assert (a[0]["gpu_idx"], a[0]["start"], a[0]["size"], a[0]["cost"]) == (0, 6, 1, 3) and g[0]["occ"] == 0x40
+    # then a 3g: start 0 overlaps 1g x4 + 2g x2 + 3g@0 + 4g + (7g already dead) = 8; start 4 is blocked by slice 6 -> start 0
+    a, g = orc.mig_pack(abi, g, [6])
+    assert (a[0]["start"], a[0]["cost"]) == (0, 8) and g[0]["occ"] == 0x4F
+    # 4g no longer fits (slices 0-3 taken), 7g neither; 2g fits only at start 4 (1g@4, 1g@5, 2g@4 -> cost 3)
+    a, g = orc.mig_pack(abi, g, [8, 10, 4])
+    assert a[0]["gpu_idx"] == abi.NO_NODE and a[1]["gpu_idx"] == abi.NO_NODE
+    assert (a[2]["gpu_idx"], a[2]["start"], a[2]["cost"]) == (0, 4, 3) and g[0]["occ"] == 0x7F
+    # class and enable filters; ties -> lowest GPU index; the fuller GPU wins when it destroys less
+    a, g = orc.mig_pack(abi, gpus(0, 0, cls=[0, 1]), [1, 2, 3])          # 1g.5gb -> GPU0, 1g.10gb -> GPU1, 2g.10gb -> GPU0
+    assert a["gpu_idx"].tolist() == [0, 1, 0]
+    a, g = orc.mig_pack(abi, gpus(0, 0, enabled=[0, 1]), [2])
+    assert a[0]["gpu_idx"] == 1
+    a, g = orc.mig_pack(abi, gpus(0x00, 0x0F), [4])     # empty GPU: cheapest 2g is start 4 (cost 5); GPU with 0-3 taken: start 4 costs 4 -> GPU 1
+    assert (a[0]["gpu_idx"], a[0]["start"], a[0]["cost"]) == (1, 4, 4)
+    a, _ = orc.mig_pack(abi, gpus(0), [0, 11])          # invalid profile ids never fit
+    assert (a["gpu_idx"] == abi.NO_NODE).all()
+
+
+def test_mig_rebalance_known_answers(kg, orc):
+    abi = kg.abi
+    g = np.zeros(12, dtype=abi.MIG_GPU)
+    g["enabled"] = 1
+    g["cls"] = [1] * 10 + [0] * 2
+    g["occ"][3] = 1                                     # busy -> not idle; 9 idle 80 GB GPUs, 2 idle 40 GB GPUs
+    target = np.zeros(10)
+    target[1], target[3], target[5] = 0.7, 0.2, 0.1    # 1g.10gb / 2g.20gb / 3g.40gb (the example strategy)
+    ops, supply, n = orc.mig_rebalance(abi, g, target)
+    # shares of 9: 6.3 / 1.8 / 0.9 -> floors 6,1,0; the 2 left go to the largest fractions .9 (3g) then .8 (2g) -> 6,2,1
+    assert supply.tolist() == [0, 42, 0, 6, 0, 2, 0, 0, 0, 0] and n == 50 and len(ops) == 50
+    assert ops["gpu_idx"][:7].tolist() == [0] * 7 and ops["start"][:7].tolist() == list(range(7))
+    assert ops["gpu_idx"][42:48].tolist() == [7, 7, 7, 8, 8, 8] and ops["start"][42:48].tolist() == [0, 2, 4, 0, 2, 4]   # idle order skips GPU 3
+    assert ops["gpu_idx"][48:].tolist() == [9, 9] and ops["start"][48:].tolist() == [0, 4] and ops["profile"][48] == 6
+    # the 40 GB class has no target -> untouched
+    assert not (ops["gpu_idx"] >= 10).any()
