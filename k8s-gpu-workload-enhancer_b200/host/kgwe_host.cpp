@@ -1,0 +1,253 @@
+// kgwe_host.cpp — see kgwe_host.hpp.  Everything numeric happens behind the C ABI on the GPU;
+// this file packs structs into the ABI's records, keeps the string tables, and rebuilds the
+// reference's result types (names, UUIDs, reasons, error strings) from the ABI's indices.
+#include "kgwe_host.hpp"
+
+#include <algorithm>
+#include <chrono>
+#include <cstring>
+#include <mutex>
+#include <set>
+
+namespace kgwe_host {
+
+namespace {
+const char* kArch[] = {"", "Volta", "Turing", "Ampere", "Hopper", "Ada", "Blackwell"};
+const char* kMig[KGWE_MIG_PROFILES] = {"1g.5gb", "1g.10gb", "2g.10gb", "2g.20gb", "3g.20gb", "3g.40gb", "4g.20gb", "4g.40gb", "7g.40gb", "7g.80gb"};
+std::mutex g_arch_mu;
+std::unordered_map<std::string, uint8_t> g_arch_extra;
+
+std::vector<int> order_list(uint32_t order) {
+    std::vector<int> v; const int n = (order >> 24) & 15;
+    for (int p = 0; p < n; ++p) v.push_back((order >> (3 * p)) & 7);
+    return v;
+}
+}  // namespace
+
+uint8_t ArchCode(const std::string& arch) {
+    for (int i = 0; i < 7; ++i) if (arch == kArch[i]) return (uint8_t)i;
+    std::lock_guard<std::mutex> lk(g_arch_mu);
+    auto it = g_arch_extra.find(arch);
+    if (it != g_arch_extra.end()) return it->second;
+    if (g_arch_extra.size() >= 247) return 255;
+    const uint8_t code = (uint8_t)(7 + g_arch_extra.size());
+    g_arch_extra[arch] = code;
+    return code;
+}
+
+uint8_t MIGProfileCode(const std::string& name) {
+    for (int i = 0; i < KGWE_MIG_PROFILES; ++i) if (name == kMig[i]) return (uint8_t)(i + 1);
+    return KGWE_MIG_UNKNOWN;
+}
+
+uint8_t TopologyPreferenceCode(const std::string& p) {
+    if (p == "NVLinkOptimal") return KGWE_TOPO_NVLINK_OPTIMAL;
+    if (p == "NVLinkRequired") return KGWE_TOPO_NVLINK_REQUIRED;
+    if (p == "SameNUMA") return KGWE_TOPO_SAME_NUMA;
+    if (p == "SamePCIeSwitch") return KGWE_TOPO_SAME_PCIE_SWITCH;
+    return KGWE_TOPO_NONE;          // "None" and anything else: the default arm, scheduler.go:325-331
+}
+
+std::string PackNode(const NodeTopology& node, PackedNode* out) {
+    if (node.GPUs.size() > KGWE_MAX_GPUS) return "node " + node.NodeName + ": more than 8 GPUs";
+    kgwe_node_image& im = out->image;
+    memset(&im, 0, sizeof im);
+    out->uuids.clear();
+    std::unordered_map<std::string, int> gpu_of;
+    for (size_t i = 0; i < node.GPUs.size(); ++i) { gpu_of[node.GPUs[i].UUID] = (int)i; out->uuids.push_back(node.GPUs[i].UUID); }
+    // NUMA: order-preserving rank compression (only order and equality matter to scoreNUMATopology)
+    std::set<int> numa_vals;
+    for (auto& g : node.GPUs) numa_vals.insert(g.Topology.NUMANode);
+    std::map<int, int> numa_rank; { int r = 0; for (int v : numa_vals) numa_rank[v] = r++; }
+    // PCIe switch: interned in first-appearance order over node.GPUs, "" -> "default" (scheduler.go:484-486)
+    std::unordered_map<std::string, uint8_t> sw;
+    unsigned mig_free[KGWE_MIG_PROFILES] = {0};
+    im.n_gpus = (uint8_t)node.GPUs.size();
+    for (size_t i = 0; i < node.GPUs.size(); ++i) {
+        const GPUDevice& g = node.GPUs[i];
+        for (auto& kv : g.Topology.NVLinkConnections) {
+            auto it = gpu_of.find(kv.first);
+            if (it == gpu_of.end() || it->second == (int)i) continue;    // peers outside the node never reach the scorer
+            im.nvl_bw[i][it->second] = kv.second.BandwidthGBps;
+            im.nvl_present[i] |= (uint8_t)(1u << it->second);
+            if (kv.second.IsActive) im.nvl_active[i] |= (uint8_t)(1u << it->second);
+        }
+        im.pcie_bw[i] = g.Topology.PCIeInfo.BandwidthGBps;
+        im.free_bytes[i] = g.MemoryFreeBytes;
+        im.util[i] = g.UtilizationGPUPercent;
+        std::string s = g.Topology.PCIeInfo.SwitchID.empty() ? "default" : g.Topology.PCIeInfo.SwitchID;
+        if (!sw.count(s)) sw[s] = (uint8_t)sw.size();
+        im.pcie_switch[i] = sw[s];
+        im.numa[i] = (int8_t)numa_rank[g.Topology.NUMANode];
+        im.arch[i] = ArchCode(g.Architecture);
+        if (g.HealthStatus == "Healthy") im.healthy_mask |= (uint8_t)(1u << i);
+        if (g.MIGConfig && g.MIGConfig->Enabled)
+            for (auto& inst : g.MIGConfig->CurrentInstances) {
+                const uint8_t p = MIGProfileCode(inst.Profile.Name);
+                if (!inst.InUse && p >= 1 && p <= KGWE_MIG_PROFILES) mig_free[p - 1]++;
+            }
+    }
+    for (int p = 0; p < KGWE_MIG_PROFILES; ++p) {
+        if (mig_free[p] > 255) return "node " + node.NodeName + ": more than 255 free MIG instances of one profile";
+        im.mig_free[p] = (uint8_t)mig_free[p];
+    }
+    return "";
+}
+
+Result<std::unique_ptr<TopologyAwareScheduler>> TopologyAwareScheduler::New(const SchedulerConfig& cfg, uint32_t maxNodes, int device) {
+    Result<std::unique_ptr<TopologyAwareScheduler>> r;
+    kgwe_config c;
+    kgwe_config_default(&c);
+    c.device = device; c.max_nodes = maxNodes;
+    c.topology_weight = cfg.TopologyWeight; c.resource_weight = cfg.ResourceWeight; c.balance_weight = cfg.BalanceWeight;
+    kgwe_engine* e = nullptr;
+    const int rc = kgwe_engine_create(&c, &e);
+    if (rc != KGWE_OK) { r.error = "kgwe_engine_create failed (" + std::to_string(rc) + "): no usable CUDA device; the engine has no CPU fallback"; return r; }
+    r.value.reset(new TopologyAwareScheduler());
+    r.value->cfg_ = cfg; r.value->engine_ = e; r.value->max_nodes_ = maxNodes;
+    return r;
+}
+
+TopologyAwareScheduler::~TopologyAwareScheduler() { if (engine_) kgwe_engine_destroy(engine_); }
+
+uint32_t TopologyAwareScheduler::NodeIndex(const std::string& name) const {
+    auto it = node_index_.find(name);
+    return it == node_index_.end() ? KGWE_NO_NODE : it->second;
+}
+
+std::string TopologyAwareScheduler::UpsertNode(const NodeTopology& node) {
+    PackedNode pk;
+    std::string err = PackNode(node, &pk);
+    if (!err.empty()) return err;
+    uint32_t idx = NodeIndex(node.NodeName);
+    if (idx == KGWE_NO_NODE) {
+        if (node_names_.size() >= max_nodes_) return "cluster image is full";
+        idx = (uint32_t)node_names_.size();
+        node_index_[node.NodeName] = idx; node_names_.push_back(node.NodeName); node_uuids_.emplace_back();
+    }
+    node_uuids_[idx] = pk.uuids;
+    if (kgwe_node_upsert(engine_, idx, &pk.image) != KGWE_OK) return kgwe_last_error(engine_);
+    return "";
+}
+
+std::string TopologyAwareScheduler::RemoveNode(const std::string& name) {
+    const uint32_t idx = NodeIndex(name);
+    if (idx == KGWE_NO_NODE) return "node " + name + " not found";
+    if (kgwe_node_remove(engine_, idx) != KGWE_OK) return kgwe_last_error(engine_);
+    node_index_.erase(name);          // the index stays retired; a re-added node gets a fresh one
+    node_names_[idx].clear();
+    return "";
+}
+
+kgwe_pod_req TopologyAwareScheduler::PodReq(const GPUWorkload& w) {
+    kgwe_pod_req p; memset(&p, 0, sizeof p);
+    auto it = wl_id_.find(w.UID);
+    if (it == wl_id_.end()) it = wl_id_.emplace(w.UID, next_wl_++).first;
+    p.wl_id = it->second;
+    p.gpu_count = w.Requirements.GPUCount; p.min_memory_gb = w.Requirements.MinMemoryGB;
+    p.min_bandwidth_gbps = cfg_.EnableMinBandwidthFilter ? w.Requirements.MinBandwidthGBps : 0.0;
+    p.topology_pref = TopologyPreferenceCode(w.Requirements.TopologyPreference);
+    p.arch = w.Requirements.GPUArchitecture.empty() ? (uint8_t)KGWE_ARCH_ANY : ArchCode(w.Requirements.GPUArchitecture);
+    if (w.Requirements.MIGReq) { p.mig_profile = MIGProfileCode(w.Requirements.MIGReq->Profile); p.mig_count = w.Requirements.MIGReq->Count; }
+    return p;
+}
+
+std::vector<uint8_t> TopologyAwareScheduler::HintBitmap(const PlacementHint* hint) const {
+    std::vector<uint8_t> bm;
+    if (!hint) return bm;
+    bm.assign((node_names_.size() + 7) / 8, 0);
+    for (auto& n : hint->PreferredNodes) { const uint32_t i = NodeIndex(n); if (i != KGWE_NO_NODE) bm[i / 8] |= (uint8_t)(1u << (i & 7)); }
+    return bm;
+}
+
+NodeScore TopologyAwareScheduler::NodeScoreOf(const kgwe_placement& pl) const {
+    NodeScore s;
+    s.NodeName = node_names_[pl.node_idx];
+    s.TotalScore = pl.total; s.TopologyScore = pl.topology; s.ResourceScore = pl.resource; s.BalanceScore = pl.balance;
+    for (int g : order_list(pl.order)) s.SelectedGPUs.push_back(node_uuids_[pl.node_idx][g]);
+    // scheduler.go:270-297
+    if (pl.flags & KGWE_F_HINT) s.Reasons.push_back("ML optimizer preferred this node");
+    if (pl.topology >= 80) s.Reasons.push_back("Optimal NVLink connectivity available");
+    if (pl.resource >= 80) s.Reasons.push_back("Sufficient resources with headroom");
+    if (pl.balance >= 80) s.Reasons.push_back("Good load distribution");
+    return s;
+}
+
+SchedulingDecision TopologyAwareScheduler::DecisionOf(const GPUWorkload& w, const kgwe_placement& pl) const {
+    const NodeScore s = NodeScoreOf(pl);
+    SchedulingDecision d;
+    d.WorkloadUID = w.UID; d.SelectedNode = s.NodeName; d.SelectedGPUs = s.SelectedGPUs; d.Score = s.TotalScore;
+    d.Reasons = s.Reasons; d.EstimatedBandwidth = pl.est_bandwidth_gbps;
+    return d;
+}
+
+void TopologyAwareScheduler::UpdateLatency(double ms) {   // scheduler.go:805-819 ("P99" is the max there too)
+    const double total = (double)(metrics_.TotalScheduled + metrics_.TotalFailed);
+    metrics_.AverageLatencyMs = total == 0 ? ms : (metrics_.AverageLatencyMs * total + ms) / (total + 1);
+    metrics_.P99LatencyMs = std::max(metrics_.P99LatencyMs, ms);
+}
+
+Result<std::vector<NodeScore>> TopologyAwareScheduler::ScoreNodes(const GPUWorkload& w, const PlacementHint* hint, uint32_t topk) {
+    Result<std::vector<NodeScore>> r;
+    if (!HasTopology()) { r.error = "cluster topology not available"; return r; }
+    topk = std::min<uint32_t>(topk, KGWE_MAX_TOPK);
+    const kgwe_pod_req p = PodReq(w);
+    std::vector<uint8_t> bm = HintBitmap(hint);
+    std::vector<kgwe_placement> out(topk);
+    if (kgwe_score_batch(engine_, &p, 1, hint ? bm.data() : nullptr, nullptr, topk, out.data()) != KGWE_OK) { r.error = kgwe_last_error(engine_); return r; }
+    for (auto& pl : out) { if (pl.node_idx == KGWE_NO_NODE) break; r.value.push_back(NodeScoreOf(pl)); }
+    return r;
+}
+
+Result<SchedulingDecision> TopologyAwareScheduler::Schedule(const GPUWorkload& w, const PlacementHint* hint) {
+    const auto t0 = std::chrono::steady_clock::now();
+    Result<SchedulingDecision> r;
+    if (!HasTopology()) { r.error = "cluster topology not available"; return r; }            // scheduler.go:124
+    const kgwe_pod_req p = PodReq(w);
+    std::vector<uint8_t> bm = HintBitmap(hint);
+    kgwe_placement pl;
+    const int rc = kgwe_schedule_queue(engine_, &p, 1, hint ? bm.data() : nullptr, &pl);
+    const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    if (rc != KGWE_OK) { r.error = kgwe_last_error(engine_); return r; }
+    if (pl.node_idx == KGWE_NO_NODE) {
+        UpdateLatency(ms); metrics_.TotalFailed++;
+        r.error = "no eligible nodes found for workload " + w.Name;                            // scheduler.go:140
+        return r;
+    }
+    r.value = DecisionOf(w, pl);
+    UpdateLatency(ms); metrics_.TotalScheduled++;
+    if (pl.topology >= 80) metrics_.TopologyOptimalPlacements++;                               // scheduler.go:154
+    events_.push_back(SchedulingEvent{"Scheduled", w.UID, std::make_shared<SchedulingDecision>(r.value), ""});
+    return r;
+}
+
+std::vector<Result<SchedulingDecision>> TopologyAwareScheduler::ScheduleBurst(const std::vector<GPUWorkload>& ws) {
+    std::vector<Result<SchedulingDecision>> out(ws.size());
+    if (ws.empty()) return out;
+    if (!HasTopology()) { for (auto& r : out) r.error = "cluster topology not available"; return out; }
+    std::vector<kgwe_pod_req> pods; pods.reserve(ws.size());
+    for (auto& w : ws) pods.push_back(PodReq(w));
+    std::vector<kgwe_placement> pls(ws.size());
+    if (kgwe_schedule_queue(engine_, pods.data(), (uint32_t)pods.size(), nullptr, pls.data()) != KGWE_OK) {
+        for (auto& r : out) r.error = kgwe_last_error(engine_);
+        return out;
+    }
+    for (size_t i = 0; i < ws.size(); ++i) {
+        if (pls[i].node_idx == KGWE_NO_NODE) { metrics_.TotalFailed++; out[i].error = "no eligible nodes found for workload " + ws[i].Name; continue; }
+        out[i].value = DecisionOf(ws[i], pls[i]);
+        metrics_.TotalScheduled++;
+        if (pls[i].topology >= 80) metrics_.TopologyOptimalPlacements++;
+        events_.push_back(SchedulingEvent{"Scheduled", ws[i].UID, std::make_shared<SchedulingDecision>(out[i].value), ""});
+    }
+    return out;
+}
+
+std::string TopologyAwareScheduler::ReleaseAllocation(const std::string& uid) {
+    auto it = wl_id_.find(uid);
+    if (it == wl_id_.end() || kgwe_alloc_release(engine_, it->second) != KGWE_OK)
+        return "allocation not found for workload " + uid;                                      // scheduler.go:715
+    events_.push_back(SchedulingEvent{"Released", uid, nullptr, ""});
+    return "";
+}
+
+}  // namespace kgwe_host

@@ -1,0 +1,105 @@
+// GPU: the C++ mirror of TopologyAwareScheduler (Schedule / ScoreNodes / ReleaseAllocation / metrics /
+// events) on a struct-form cluster, checked against the CPU oracle run on the packed images.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "../../oracle/kgwe_oracle.h"
+#include "cluster_fixture.hpp"
+
+#define CHECK(c) do { if (!(c)) { fprintf(stderr, "FAIL %s:%d: %s\n", __FILE__, __LINE__, #c); exit(1); } } while (0)
+
+using namespace kgwe_host;
+
+static kgwe_pod_req pod_of(const GPUWorkload& w, uint64_t id) {
+    kgwe_pod_req p; memset(&p, 0, sizeof p);
+    p.wl_id = id; p.gpu_count = w.Requirements.GPUCount; p.min_memory_gb = w.Requirements.MinMemoryGB;
+    p.topology_pref = TopologyPreferenceCode(w.Requirements.TopologyPreference);
+    p.arch = w.Requirements.GPUArchitecture.empty() ? (uint8_t)KGWE_ARCH_ANY : ArchCode(w.Requirements.GPUArchitecture);
+    if (w.Requirements.MIGReq) { p.mig_profile = MIGProfileCode(w.Requirements.MIGReq->Profile); p.mig_count = w.Requirements.MIGReq->Count; }
+    return p;
+}
+
+int main() {
+    const int N = 48, P = 160;
+    auto cluster = fixture::make_cluster(N);
+    auto jobs = fixture::make_workloads(P);
+    auto made = TopologyAwareScheduler::New(SchedulerConfig{}, 64);
+    CHECK(made.ok());
+    auto& S = *made.value;
+    GPUWorkload early = jobs[0];
+    CHECK(S.Schedule(early).error == "cluster topology not available");                 // scheduler.go:124
+    std::vector<kgwe_node_image> images;
+    for (auto& n : cluster) { CHECK(S.UpsertNode(n).empty()); PackedNode pk; CHECK(PackNode(n, &pk).empty()); images.push_back(pk.image); }
+
+    // oracle on the same packed images, same order of workloads
+    std::vector<kgwe_pod_req> pods;
+    for (int i = 0; i < P; ++i) pods.push_back(pod_of(jobs[i], (uint64_t)i + 1));
+    std::vector<kgwe_placement> want(P);
+    std::vector<kgwe_oracle_alloc> led(P); uint32_t n_led = 0;
+    CHECK(kgwe_oracle_schedule_queue(nullptr, images.data(), N, nullptr, 0, pods.data(), P, nullptr, want.data(), led.data(), &n_led, KGWE_ORACLE_FAITHFUL, nullptr) == 0);
+
+    // Prioritize before anything is placed: ranked NodeScores for job 5 against the oracle's top-4
+    {
+        std::vector<kgwe_placement> top(4);
+        CHECK(kgwe_oracle_score_batch(nullptr, images.data(), N, nullptr, 0, &pods[5], 1, nullptr, nullptr, 4, top.data(), KGWE_ORACLE_INDEXED, 1, nullptr) == 0);
+        auto ranked = S.ScoreNodes(jobs[5], nullptr, 4);
+        CHECK(ranked.ok());
+        size_t n_valid = 0; for (auto& t : top) if (t.node_idx != KGWE_NO_NODE) ++n_valid;
+        CHECK(ranked.value.size() == n_valid);
+        for (size_t i = 0; i < n_valid; ++i) {
+            CHECK(ranked.value[i].NodeName == cluster[top[i].node_idx].NodeName && ranked.value[i].TotalScore == top[i].total);
+            CHECK(ranked.value[i].TopologyScore == top[i].topology && ranked.value[i].BalanceScore == top[i].balance);
+        }
+    }
+    // first half one Schedule() call per workload, second half as one burst
+    int placed = 0, failed = 0, optimal = 0;
+    std::vector<Result<SchedulingDecision>> got;
+    for (int i = 0; i < P / 2; ++i) got.push_back(S.Schedule(jobs[i]));
+    { std::vector<GPUWorkload> rest(jobs.begin() + P / 2, jobs.end()); for (auto& r : S.ScheduleBurst(rest)) got.push_back(r); }
+    for (int i = 0; i < P; ++i) {
+        if (want[i].node_idx == KGWE_NO_NODE) {
+            CHECK(!got[i].ok() && got[i].error == "no eligible nodes found for workload " + jobs[i].Name);   // scheduler.go:140
+            ++failed; continue;
+        }
+        CHECK(got[i].ok());
+        const SchedulingDecision& d = got[i].value;
+        CHECK(d.WorkloadUID == jobs[i].UID && d.SelectedNode == cluster[want[i].node_idx].NodeName && d.Score == want[i].total);
+        const int n = (want[i].order >> 24) & 15;
+        CHECK((int)d.SelectedGPUs.size() == n);
+        for (int q = 0; q < n; ++q) CHECK(d.SelectedGPUs[q] == fixture::uuid((int)want[i].node_idx, (want[i].order >> (3 * q)) & 7));
+        CHECK(d.EstimatedBandwidth == want[i].est_bandwidth_gbps);
+        const bool top80 = want[i].topology >= 80;
+        bool has = false; for (auto& r : d.Reasons) if (r == "Optimal NVLink connectivity available") has = true;
+        CHECK(has == top80);
+        ++placed; if (top80) ++optimal;
+    }
+    CHECK(placed > 20 && failed > 0);
+    SchedulerMetrics m = S.GetMetrics();
+    CHECK(m.TotalScheduled == placed && m.TotalFailed == failed && m.TopologyOptimalPlacements == optimal);
+    CHECK((int)S.Events().size() == placed && S.Events().front().Type == "Scheduled");
+    // release: the GPUs come back; unknown / repeated release -> the reference's error string
+    int first_placed = 0; while (want[first_placed].node_idx == KGWE_NO_NODE) ++first_placed;
+    CHECK(S.ReleaseAllocation(jobs[first_placed].UID).empty());
+    CHECK(S.ReleaseAllocation(jobs[first_placed].UID) == "allocation not found for workload " + jobs[first_placed].UID);   // scheduler.go:715
+    CHECK(S.ReleaseAllocation("never-seen") == "allocation not found for workload never-seen");
+    CHECK(S.Events().back().Type == "Released");
+    // a hint turns into +10 and a reason (scheduler.go:270-279)
+    {
+        GPUWorkload w = jobs[1]; w.UID = "uid-hinted"; w.Name = "hinted"; w.Requirements.GPUCount = 1; w.Requirements.TopologyPreference = "None";
+        w.Requirements.GPUArchitecture.clear(); w.Requirements.MIGReq.reset();
+        auto plain = S.ScoreNodes(w, nullptr, 16);
+        CHECK(plain.ok() && plain.value.size() >= 2);
+        PlacementHint h; h.PreferredNodes = {plain.value.back().NodeName, "no-such-node"};
+        auto hinted = S.ScoreNodes(w, &h, 16);
+        CHECK(hinted.ok());
+        bool seen = false;
+        for (auto& s : hinted.value) if (s.NodeName == plain.value.back().NodeName) { seen = true; CHECK(s.TotalScore == plain.value.back().TotalScore + 10); CHECK(s.Reasons[0] == "ML optimizer preferred this node"); }
+        CHECK(seen);
+    }
+    // node delete event
+    CHECK(S.RemoveNode(cluster[0].NodeName).empty() && S.NodeIndex(cluster[0].NodeName) == KGWE_NO_NODE);
+    CHECK(!S.RemoveNode(cluster[0].NodeName).empty());
+    printf("host_scheduler_test OK: %d placed, %d failed, %d topology-optimal, %zu events\n", placed, failed, optimal, S.Events().size());
+    return 0;
+}
