@@ -44,7 +44,7 @@ WORKLOAD = "BASELINE configs[2]: 10,000-node x 8-GPU mixed H100/A100/B200 cluste
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="kgwe", choices=["kgwe", "reference"])
     ap.add_argument("--scale", type=float, default=1.0, help="shrink N and P (testing only; the default is the full config)")
@@ -268,21 +268,26 @@ def run_kgwe(args):
         dist.all_reduce(c, op=dist.ReduceOp.SUM)
     e2e_value = float(c.item()) / float(t.item())
 
-    # ---- per-pod Prioritize latency: one kgwe_score_batch(P=1) C-ABI call per pod (N=1 only) ----
+    # ---- per-pod Prioritize latency vs node count: one kgwe_score_batch(P=1) C-ABI call per pod (N=1 only) ----
     lat = None
     if world == 1:
-        one = pods[:1].copy()
-        for i in range(200):
-            eng.score_batch(pods[i:i + 1], n_local, want_scores=False, topk=1)
-        xs = []
-        for i in range(2000):
-            q = pods[i % P:i % P + 1]
-            a = time.perf_counter()
-            eng.score_batch(q, n_local, want_scores=False, topk=1)
-            xs.append((time.perf_counter() - a) * 1e6)
-        xs = np.array(xs)
-        lat = {"n_nodes": N, "calls": len(xs), "p50_us": float(np.percentile(xs, 50)), "p99_us": float(np.percentile(xs, 99)), "max_us": float(xs.max())}
-        del one
+        def measure(engine, n_here, calls=3000, warm=300):
+            for i in range(warm):
+                engine.score_batch(pods[i % P:i % P + 1], n_here, want_scores=False, topk=1)
+            xs = np.empty(calls)
+            for i in range(calls):
+                q = pods[i % P:i % P + 1]
+                a = time.perf_counter()
+                engine.score_batch(q, n_here, want_scores=False, topk=1)
+                xs[i] = (time.perf_counter() - a) * 1e6
+            return {"n_nodes": n_here, "calls": calls, "p50_us": float(np.percentile(xs, 50)), "p99_us": float(np.percentile(xs, 99)), "max_us": float(xs.max())}
+        lat = [measure(eng, n_local)]
+        for n_small in (1000, 16):
+            if n_small < N:
+                e3 = kg.Engine(max_nodes=n_small, device=local_rank)
+                e3.upsert_nodes(nodes[:n_small])
+                lat.append(measure(e3, n_small))
+                e3.close()
 
     # ---- stateful Schedule() queue throughput (reported beside the headline; N=1 only) ----
     sched = None

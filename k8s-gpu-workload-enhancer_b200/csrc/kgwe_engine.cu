@@ -428,6 +428,22 @@ int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, 
     }
     const uint32_t row = hint_row_bytes(e);
     const bool need_matrix = out_scores || topk > 1;
+    if (!need_matrix && topk == 1 && n_pods <= 32) {
+        // Latency path (per-pod Prioritize): no copy operations at all.  Pod descriptors, hint rows and
+        // placements live in pinned host memory, which the kernels read and write directly over PCIe
+        // (unified addressing): two launches and one stream synchronisation per call.
+        CU(e, e->h_pods.ensure(32)); CU(e, e->h_topk.ensure(32));
+        if (hint) CU(e, e->h_hint.ensure((size_t)32 * row));
+        memcpy(e->h_pods.p, pods, (size_t)n_pods * sizeof(kgwe_pod_req));
+        if (hint) memcpy(e->h_hint.p, hint, (size_t)n_pods * row);
+        rc = launch_score(e, e->h_pods.p, n_pods, hint ? e->h_hint.p : nullptr, nullptr, 1, e->h_topk.p, s);
+        if (rc != KGWE_OK) return rc;
+        CU(e, cudaStreamSynchronize(s));
+        memcpy(out_topk, e->h_topk.p, (size_t)n_pods * sizeof(kgwe_placement));
+        e->stats.h2d_bytes += (uint64_t)n_pods * sizeof(kgwe_pod_req) + (hint ? (uint64_t)n_pods * row : 0);
+        e->stats.d2h_bytes += (uint64_t)n_pods * sizeof(kgwe_placement);
+        return KGWE_OK;
+    }
     // pods per pass bounded by the score-matrix scratch
     uint32_t pass = n_pods;
     if (need_matrix) pass = (uint32_t)std::max<size_t>(1, std::min<size_t>(n_pods, kScoreScratchBytes / ((size_t)N * sizeof(kgwe_node_score))));
