@@ -85,9 +85,15 @@ typedef struct kgwe_config {
     int32_t  balance_weight;     /* 25  (types.go:387) */
     int32_t  hint_bonus;         /* 10  (scheduler.go:274) */
     double   nvlink_norm_gbps;   /* 900.0 (scheduler.go:368) */
-    uint32_t flags;              /* reserved, 0 */
+    uint32_t flags;              /* KGWE_CFG_* */
     uint32_t reserved;
 } kgwe_config;
+
+/* kgwe_score_batch_device cannot look at the pods before launching: set this when device-resident
+ * batches may contain KGWE_POD_EXHAUSTIVE pods, so the scoring kernel is launched with its per-node
+ * subset tables (one CTA per SM instead of two).  Without it such pods are still scored correctly,
+ * on a slower path.  kgwe_score_batch (host pods) picks the right kernel by itself. */
+#define KGWE_CFG_SUBSET_TABLES 0x1u
 
 /* One node of the topology snapshot: exactly the fields of NodeTopology / GPUDevice the
  * scorer reads (src/discovery/types.go:11-47,116-164,336-366).

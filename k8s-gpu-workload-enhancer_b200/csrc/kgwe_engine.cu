@@ -191,12 +191,15 @@ int validate_pods(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n) {
 
 uint32_t hint_row_bytes(const kgwe_engine* e) { return (e->n_nodes + 7) / 8; }
 
-size_t score_smem_bytes(uint32_t pods_per_chunk) { return (size_t)TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx)) + (size_t)pods_per_chunk * 8 + 16; }
+size_t score_smem_bytes(uint32_t pods_per_chunk, bool tables = false) {
+    return (size_t)TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx)) + (tables ? SUBSET_SMEM_BYTES : 0) + (size_t)pods_per_chunk * 8 + 16;
+}
 
 // Launch K1 (+K1b / K2) for n_pods pods whose descriptors, hint rows and outputs are in
 // device memory.  d_scores may be null unless topk > 1.
 int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const uint8_t* d_hint,
-                 kgwe_node_score* d_scores, uint32_t topk, kgwe_placement* d_topk, cudaStream_t s) {
+                 kgwe_node_score* d_scores, uint32_t topk, kgwe_placement* d_topk, cudaStream_t s, bool tables = false) {
+    tables = tables || (e->cfg.flags & KGWE_CFG_SUBSET_TABLES);
     if (n_pods == 0 || e->n_nodes == 0) return KGWE_OK;
     const uint32_t n_tiles = (e->n_nodes + TILE_NODES - 1) / TILE_NODES;
     // pod chunks: enough CTAs to fill the GPU a few times over, table size bounded
@@ -217,8 +220,12 @@ int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, co
     dim3 grid(n_tiles, chunks);
     const bool timed = e->timers_pending < kgwe_engine::kTimers;
     if (timed) CU(e, cudaEventRecord(e->t0[e->timers_pending], s));
-    score_kernel<<<grid, SCORE_THREADS, score_smem_bytes(ppc), s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e),
-                                                                   d_scores, best, e->params, e->d_counters);
+    if (tables)
+        score_kernel<true><<<grid, SCORE_THREADS, score_smem_bytes(ppc, true), s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e),
+                                                                                   d_scores, best, e->params, e->d_counters);
+    else
+        score_kernel<false><<<grid, SCORE_THREADS, score_smem_bytes(ppc), s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e),
+                                                                              d_scores, best, e->params, e->d_counters);
     CU(e, cudaGetLastError());
     if (timed) { CU(e, cudaEventRecord(e->t1[e->timers_pending], s)); e->timers_pending++; }
     e->stats.kernel_launches++;
@@ -303,7 +310,8 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
         e->dirty_flag.assign(cfg->max_nodes, 0);
         cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, cfg->device);
         for (int i = 0; i < kgwe_engine::kTimers && ok; ++i) ok = cudaEventCreate(&e->t0[i]) == cudaSuccess && cudaEventCreate(&e->t1[i]) == cudaSuccess;
-        ok = ok && cudaFuncSetAttribute(score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK)) == cudaSuccess;
+        ok = ok && cudaFuncSetAttribute(score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK)) == cudaSuccess
+                && cudaFuncSetAttribute(score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK, true)) == cudaSuccess;
         int bps = 0;
         if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, schedule_kernel, SCORE_THREADS, 0) == cudaSuccess && bps > 0) e->sched_blocks_per_sm = bps;
     }
@@ -463,7 +471,9 @@ int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, 
             e->stats.h2d_bytes += (uint64_t)np * row;
         }
         CU(e, cudaEventRecord(e->ev0, s));
-        rc = launch_score(e, e->d_pods.p, np, hint ? e->d_hint.p : nullptr, need_matrix ? e->d_scores.p : nullptr, topk, topk ? e->d_topk.p : nullptr, s);
+        bool any_exh = false;
+        for (uint32_t i = 0; i < np && !any_exh; ++i) any_exh = pods[p0 + i].flags & KGWE_POD_EXHAUSTIVE;
+        rc = launch_score(e, e->d_pods.p, np, hint ? e->d_hint.p : nullptr, need_matrix ? e->d_scores.p : nullptr, topk, topk ? e->d_topk.p : nullptr, s, any_exh);
         if (rc != KGWE_OK) return rc;
         CU(e, cudaEventRecord(e->ev1, s));
         if (topk) {
@@ -885,7 +895,7 @@ extern "C" int kgwe_score_top1_noalloc(kgwe_engine* e, const kgwe_pod_req* d_pod
     chunks = std::min(chunks, n_pods);
     uint32_t ppc = std::min<uint32_t>((n_pods + chunks - 1) / chunks, MAX_PODS_PER_CHUNK);
     chunks = (n_pods + ppc - 1) / ppc;
-    score_kernel<<<dim3(n_tiles, chunks), SCORE_THREADS, score_smem_bytes(ppc), s>>>(
+    score_kernel<false><<<dim3(n_tiles, chunks), SCORE_THREADS, score_smem_bytes(ppc), s>>>(
         e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e), d_out, keys, e->params, e->d_counters);
     CU(e, cudaGetLastError());
     finalize_top1_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), keys, d_top1, 1, e->params);

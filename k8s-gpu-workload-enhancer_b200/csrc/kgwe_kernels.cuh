@@ -81,9 +81,20 @@ __device__ __forceinline__ void store_no_placement(kgwe_placement* dst) {
 // So the group search is 8-wide per evaluation while the scalar part of an evaluation is done by
 // one lane instead of redundantly by eight.  Stores of one warp instruction: for each i, the 4
 // groups' lanes i write 4 consecutive nodes of pod i = 64 contiguous bytes.
-// Warps with a node whose bandwidths are not whole numbers, and octets containing an
-// exhaustive-mode pod, take the one-pod-per-pass generic path instead.
-__global__ void __launch_bounds__(SCORE_THREADS, 2)
+// Warps with a node whose bandwidths are not whole numbers take the one-pod-per-pass generic path
+// instead, and so do octets containing an exhaustive-mode pod unless the kernel was launched with
+// subset tables (TABLES): then each node also gets, once per tile, the score key of every one of
+// its 256 GPU subsets (E1: total << 8 | 255 - mask, 0 when the subset is not an available active
+// clique), laid out by popcount, and an exhaustive evaluation is the max over the C(8,k) keys of
+// its k - 8 lanes x <= 9 entries - with the same lowest-mask tie-break.
+//   extra smem with TABLES: [subset keys: 64 x 256 x 4 B][mask-by-popcount order: 256 B]
+constexpr int SUBSET_SMEM_BYTES = TILE_NODES * 256 * 4 + 256;
+__device__ __forceinline__ int subset_off(int k) {      // first table slot of popcount k: sum_{i<k} C(8,i)
+    return k <= 0 ? 0 : k == 1 ? 1 : k == 2 ? 9 : k == 3 ? 37 : k == 4 ? 93 : k == 5 ? 163 : k == 6 ? 219 : k == 7 ? 247 : k == 8 ? 255 : 256;
+}
+
+template <bool TABLES>
+__global__ void __launch_bounds__(SCORE_THREADS, TABLES ? 1 : 2)
 score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
              const kgwe_pod_req* __restrict__ pods, uint32_t n_pods, uint32_t pods_per_chunk,
              const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
@@ -93,7 +104,10 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     DevNode* tile = reinterpret_cast<DevNode*>(smem);
     NodeFast* fast = reinterpret_cast<NodeFast*>(smem + TILE_NODES * sizeof(DevNode));
     NodeCtx* ctxs = reinterpret_cast<NodeCtx*>(smem + TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast)));
-    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem + TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx)));
+    constexpr size_t kBase = TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx));
+    uint32_t* subset = reinterpret_cast<uint32_t*>(smem + kBase);                       // TABLES only
+    uint8_t* smask = smem + kBase + TILE_NODES * 256 * 4;                               // TABLES only
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem + kBase + (TABLES ? SUBSET_SMEM_BYTES : 0));
     uint64_t* bar = reinterpret_cast<uint64_t*>(keys + pods_per_chunk);
 
     const int tid = threadIdx.x, lane = tid & 31, grp = tid >> 3, j = tid & 7;
@@ -110,6 +124,11 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         tma_bulk_g2s(tile, nodes + tile_first, bytes, bar);
     }
     if (best) for (uint32_t i = tid; i < pods_per_chunk; i += SCORE_THREADS) keys[i] = 0ull;
+    if (TABLES && tid < 256) {          // slot of mask `tid` in (popcount, value) order
+        int rank = 0;
+        for (int m = 0; m < tid; ++m) rank += __popc(m) == __popc(tid);
+        smask[subset_off(__popc(tid)) + rank] = (uint8_t)tid;
+    }
     mbar_wait(bar, 0);
     __syncthreads();
 
@@ -126,6 +145,24 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         if (c.integral) node_fast_build(nf, rec, c, j);
         else nf->init[j] = FAST_NEG;
         if (j == 0) ctxs[grp] = c;
+        if (TABLES) {
+            // E1 subset keys of this node: lane j fills slots j, j+8, ...
+            uint32_t* tab = subset + grp * 256;
+            for (int r = j; r < 256; r += 8) {
+                const uint32_t mask = smask[r];
+                uint32_t key = 0;
+                if (c.integral && mask && !(mask & ~c.avail)) {
+                    bool ok = true; int total = 0;
+                    for (int m = 0; m < 8; ++m) {
+                        if (!(mask >> m & 1)) continue;
+                        if (mask & ~(1u << m) & ~(uint32_t)((c.colact >> (8 * m)) & 0xff)) ok = false;
+                        for (int i = 0; i < m; ++i) if (mask >> i & 1) total += __double2int_rz(rec->bw_in[i][bw_slot(i, m)]);
+                    }
+                    if (ok && total > 0) key = ((uint32_t)total << 8) | (255u - mask);
+                }
+                tab[r] = key;
+            }
+        }
         __syncwarp();
     }
     const NodeCtx& nc = ctxs[grp];
@@ -140,24 +177,49 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         const int k = clamp_k(pod.gpu_count);
         const bool eligible = live && eval_filter(rec, nc, pod, k);
         const bool wants_group = k >= 2 && is_nvlink_pref(pod);
-        const bool octet = warp_fast && !__any_sync(0xffffffffu, live && wants_group && (pod.flags & KGWE_POD_EXHAUSTIVE));
+        const bool exhaustive = wants_group && (pod.flags & KGWE_POD_EXHAUSTIVE);
+        const bool octet = warp_fast && (TABLES || !__any_sync(0xffffffffu, live && exhaustive));
         EvalOut o;
         if (octet) {
             // ---- phase A: the group searches, one pod slot at a time ----
             int32_t mykey = 0; uint32_t mypay = 0;
-            const int chain_k = (eligible && wants_group) ? k : 0;
+            const int chain_k = (eligible && wants_group) ? (k | (exhaustive ? 16 : 0)) : 0;
 #pragma unroll 1
             for (int t = 0; t < 8; ++t) {
-                const int kt = __shfl_sync(0xffffffffu, chain_k, t, 8);
-                if (!__any_sync(0xffffffffu, kt != 0)) continue;       // warp-uniform
+                const int ct = __shfl_sync(0xffffffffu, chain_k, t, 8);
+                if (!__any_sync(0xffffffffu, ct != 0)) continue;       // warp-uniform
+                const int kt = ct & 15;
                 int32_t key = 0; uint32_t pay = 0;
-                if (kt) greedy_chain_fast(nf, j, kt, key, pay);
-                fast_group_winner(key, pay);
+                if (TABLES && __any_sync(0xffffffffu, ct & 16)) {      // some group has an exhaustive pod in this slot
+                    if (ct & 16) {
+                        const uint32_t* tab = subset + grp * 256;
+                        uint32_t b = 0;
+                        for (int r = subset_off(kt) + j; r < subset_off(kt + 1); r += 8) b = max(b, tab[r]);
+#pragma unroll
+                        for (int off = 4; off >= 1; off >>= 1) b = max(b, __shfl_xor_sync(0xffu << (lane & 24), b, off, 8));
+                        key = (int32_t)b;
+                    } else if (kt) {
+                        greedy_chain_fast(nf, j, kt, key, pay);
+#pragma unroll
+                        for (int off = 4; off >= 1; off >>= 1) key = max(key, __shfl_xor_sync(0xffu << (lane & 24), key, off, 8));
+                        pay = __shfl_sync(0xffu << (lane & 24), pay, 7 - (key & 7), 8);
+                    }
+                } else {
+                    if (kt) greedy_chain_fast(nf, j, kt, key, pay);
+                    fast_group_winner(key, pay);
+                }
                 if (j == t) { mykey = key; mypay = pay; }
             }
             // ---- phase B: lane j finishes pod p0 + j ----
+            bool found = mykey > 0; double win_total = (double)(mykey >> 3);
+            uint32_t sel = mypay >> 24, ord = mypay & 0xffffffu, ncand = (uint32_t)nc.A;
+            if (TABLES && exhaustive) {
+                win_total = (double)(mykey >> 8);
+                take_first_k(255u - ((uint32_t)mykey & 255u), k, sel, ord);
+                ncand = 1; for (int i = 1; i <= k; ++i) ncand = ncand * (uint32_t)(nc.A - k + i) / (uint32_t)i;
+            }
             eval_finish(rec, nc, pod, P, live && hint_bit(hint, hint_row_bytes, p, node), eligible, k,
-                        mykey > 0, (double)(mykey >> 3), mypay >> 24, mypay & 0xffffffu, (uint32_t)nc.A, o);
+                        found, win_total, sel, ord, ncand, o);
             if (live && node_ok) {
                 cand += o.candidates;
                 if (out) {

@@ -17,9 +17,10 @@ class EngineError(RuntimeError):
 class Engine:
     """Owns one kgwe_engine (one CUDA device, one node shard)."""
 
-    def __init__(self, max_nodes, device=0, node_base=0, config=None):
+    def __init__(self, max_nodes, device=0, node_base=0, config=None, flags=0):
         self.lib = abi.load_engine_lib()
         self.cfg = config if config is not None else abi.default_config(max_nodes, device, node_base)
+        self.cfg.flags |= flags
         self.h = C.c_void_p()
         rc = self.lib.kgwe_engine_create(C.byref(self.cfg), C.byref(self.h))
         if rc != 0:

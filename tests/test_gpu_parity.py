@@ -123,6 +123,29 @@ def test_exhaustive_extension(kg, orc):
     assert_same_placements(top, o_top)
     # property: on symmetric bandwidth matrices the exhaustive topology score is >= the greedy one
     assert (scores["topology"] >= g_scores["topology"]).all()
+    # greedy and exhaustive pods interleaved inside the same 8-pod octets, a few nodes with fractional
+    # bandwidths (generic FP64 path), through the host API and through the device API of an engine
+    # created with KGWE_CFG_SUBSET_TABLES - and of one without it (slow path, same answers)
+    import torch
+    mixed = pods.copy()
+    mixed["flags"] = np.where(np.arange(len(mixed)) % 3 == 0, 0, abi.POD_EXHAUSTIVE).astype(np.uint8)
+    mixed["topology_pref"][::5] = abi.TOPO_SAME_NUMA
+    nodes2 = nodes.copy()
+    nodes2["nvl_bw"][::7] *= 1.03125
+    o_scores, o_top, _ = orc.score_batch(abi, nodes2, led, mixed, want_scores=True, topk=1, threads=4)
+    for flags in (abi.CFG_SUBSET_TABLES, 0):
+        e2 = engine_for(kg, nodes2, led, flags=flags)
+        s2, t2 = e2.score_batch(mixed, len(nodes2), want_scores=True, topk=1)
+        assert s2.tobytes() == o_scores.tobytes()
+        assert_same_placements(t2, o_top)
+        d_pods = torch.from_numpy(mixed.view(np.uint8).reshape(len(mixed), abi.POD_REQ.itemsize)).cuda()
+        d_sc = torch.zeros((len(mixed), len(nodes2), abi.NODE_SCORE.itemsize), dtype=torch.uint8, device="cuda")
+        d_top = torch.zeros((len(mixed), abi.PLACEMENT.itemsize), dtype=torch.uint8, device="cuda")
+        e2.score_batch_device(d_pods.data_ptr(), len(mixed), None, d_sc.data_ptr(), 1, d_top.data_ptr())
+        torch.cuda.synchronize()
+        assert d_sc.cpu().numpy().tobytes() == o_scores.tobytes()
+        assert d_top.cpu().numpy().tobytes() == o_top.tobytes()
+        e2.close()
     eng.close()
 
 
