@@ -54,17 +54,19 @@ constexpr uint8_t NODE_INTEGRAL = 0x02;   // every link bandwidth is a whole num
 // Integer form of one node's greedy inputs, built in shared memory by the scoring kernel for
 // nodes whose bandwidths are whole numbers (<= KGWE_MAX_BW_GBPS < 2^17).  Sums of such doubles
 // are exact in FP64, so int32 arithmetic yields the very same totals and the same comparisons
-// as the reference's float64 code.  Values are pre-scaled by 8 and the candidate's tie-break
-// code (7 - c) is folded into the low 3 bits through init[], so `max` over the eight running
-// sums IS the reference's "largest aggregate, first candidate on ties" rule:
-//   row[m][c]  = 8 * bw(c -> m) when that link is active, FAST_NEG otherwise (and on the diagonal,
+// as the reference's float64 code.  Values are pre-scaled by 64 and the candidate's tie-break
+// code (7 - c) is folded into the low bits through init[], so `max` over the eight running
+// sums IS the reference's "largest aggregate, first candidate on ties" rule, and the sum of the
+// per-step maxima is 64 * total + (at most 7 * 7 of tie codes), i.e. total = sum >> 6:
+//   row[m][c]  = 64 * bw(c -> m) when that link is active, FAST_NEG otherwise (and on the diagonal,
 //                which retires a GPU from the candidates the step after it joins);
 //   init[c]    = 7 - c for an available GPU, FAST_NEG otherwise.
-// A running sum that ever met FAST_NEG stays negative (at most 8 of them: no int32 overflow).
-// Row chunks of 16 bytes are swizzled by (m >> 2) so 8 lanes on 8 rows are bank-conflict free.
+// A running sum that ever met FAST_NEG stays negative (at most 8 of them: no int32 overflow;
+// positive parts stay below 7 * 64 * 1e5 < 2^26).  Rows are 32 bytes at a 48-byte stride, which
+// puts the 8 rows' 16-byte chunks on 8 distinct bank groups: 8 lanes on 8 rows never conflict.
 constexpr int32_t FAST_NEG = -(1 << 27);
-struct __align__(16) NodeFast { int32_t row[8][8]; int32_t init[8]; };
-__host__ __device__ inline int fast_slot(int m, int c) { return ((((c >> 2) ^ (m >> 2)) & 1) << 2) | (c & 3); }
+constexpr int FAST_SHIFT = 6;
+struct __align__(16) NodeFast { int32_t row[8][12]; int32_t init[8]; };
 
 struct Params {          // kgwe_config, device copy
     int32_t wt, wr, wb, bonus;
@@ -191,33 +193,48 @@ __device__ __forceinline__ void node_fast_build(NodeFast* nf, const DevNode* rec
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
         const double v = rec->bw_in[j][bw_slot(j, c)];
-        nf->row[j][fast_slot(j, c)] = ((act >> c & 1) && c != j) ? __double2int_rz(__dmul_rn(v, 8.0)) : FAST_NEG;
+        nf->row[j][c] = ((act >> c & 1) && c != j) ? (__double2int_rz(v) << FAST_SHIFT) : FAST_NEG;
     }
     nf->init[j] = (nc.avail >> j & 1) ? (7 - j) : FAST_NEG;
 }
 
-// Integer twin of greedy_chain (see NodeFast).  Returns key = (total << 3) | (7 - s) when the
-// chain from start s reaches size k with total > 0, else 0; pay = join order | members << 24.
-__device__ __forceinline__ void greedy_chain_fast(const NodeFast* nf, int s, int k, int32_t& key, uint32_t& pay) {
+// Integer twin of greedy_chain (see NodeFast), fully unrolled for a group size K.  Returns
+// key = (total << 3) | (7 - s) when the chain from start s reaches size K with total > 0, else 0;
+// pay = join order (3 bits per position).
+template <int K>
+__device__ __forceinline__ void greedy_chain_fast_k(const NodeFast* nf, int s, int32_t& key, uint32_t& pay) {
     key = 0; pay = 0;
     const int4* ip = reinterpret_cast<const int4*>(nf->init);
     int4 a = ip[0], b = ip[1];
     if (nf->init[s] < 0) return;                       // start GPU not available
-    int32_t total = 0; uint32_t order = (uint32_t)s, members = 1u << s; int m = s;
-    for (int step = 1; step < k; ++step) {
+    int32_t sum = 0; uint32_t order = (uint32_t)s; int m = s;
+#pragma unroll
+    for (int step = 1; step < K; ++step) {
         const int4* rp = reinterpret_cast<const int4*>(nf->row[m]);
-        const int f = (m >> 2) & 1;
-        const int4 r0 = rp[f], r1 = rp[f ^ 1];
+        const int4 r0 = rp[0], r1 = rp[1];
         a.x += r0.x; a.y += r0.y; a.z += r0.z; a.w += r0.w;
         b.x += r1.x; b.y += r1.y; b.z += r1.z; b.w += r1.w;
         const int32_t best = __vimax3_s32(__vimax3_s32(a.x, a.y, a.z), __vimax3_s32(a.w, b.x, b.y), max(b.z, b.w));
         if (best <= 7) return;                          // nobody fully connected with a positive aggregate
-        const int bc = 7 - (best & 7);
-        total += best >> 3;
-        order |= (uint32_t)bc << (3 * step); members |= 1u << bc;
-        m = bc;
+        m = ~best & 7;                                  // 7 - (best & 7)
+        sum += best;
+        order |= (uint32_t)m << (3 * step);
     }
-    if (total > 0) { key = (total << 3) | (7 - s); pay = order | (members << 24); }
+    const int32_t total = sum >> FAST_SHIFT;
+    if (total > 0) { key = (total << 3) | (7 - s); pay = order; }
+}
+
+__device__ __forceinline__ void greedy_chain_fast(const NodeFast* nf, int s, int k, int32_t& key, uint32_t& pay) {
+    switch (k) {
+        case 2: greedy_chain_fast_k<2>(nf, s, key, pay); break;
+        case 3: greedy_chain_fast_k<3>(nf, s, key, pay); break;
+        case 4: greedy_chain_fast_k<4>(nf, s, key, pay); break;
+        case 5: greedy_chain_fast_k<5>(nf, s, key, pay); break;
+        case 6: greedy_chain_fast_k<6>(nf, s, key, pay); break;
+        case 7: greedy_chain_fast_k<7>(nf, s, key, pay); break;
+        case 8: greedy_chain_fast_k<8>(nf, s, key, pay); break;
+        default: key = 0; pay = 0;
+    }
 }
 
 // estimateBandwidth, scheduler.go:656-692: mean over pairs i<j (SelectedGPUs order) of GPU
@@ -413,7 +430,7 @@ __device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, 
             if (eligible) greedy_chain_fast(nf, j, k, key, pay);
             fast_group_winner(key, pay);
             found = key > 0; win_total = (double)(key >> 3);
-            order = pay & 0xffffffu; sel = pay >> 24;
+            order = pay; sel = mask_of_order(order, k);
             candidates = (uint32_t)nc.A;
         } else {
             uint64_t key; uint32_t pay;

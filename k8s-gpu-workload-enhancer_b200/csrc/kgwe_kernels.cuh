@@ -212,7 +212,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
             }
             // ---- phase B: lane j finishes pod p0 + j ----
             bool found = mykey > 0; double win_total = (double)(mykey >> 3);
-            uint32_t sel = mypay >> 24, ord = mypay & 0xffffffu, ncand = (uint32_t)nc.A;
+            uint32_t ord = mypay, sel = found ? mask_of_order(mypay, k) : 0u, ncand = (uint32_t)nc.A;
             if (TABLES && exhaustive) {
                 win_total = (double)(mykey >> 8);
                 take_first_k(255u - ((uint32_t)mykey & 255u), k, sel, ord);
