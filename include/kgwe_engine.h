@@ -94,6 +94,11 @@ typedef struct kgwe_config {
  * subset tables (one CTA per SM instead of two).  Without it such pods are still scored correctly,
  * on a slower path.  kgwe_score_batch (host pods) picks the right kernel by itself. */
 #define KGWE_CFG_SUBSET_TABLES 0x1u
+/* The greedy group of a node depends only on the node's state and on GPUCount, not on the pod:
+ * with this flag the scoring kernel finds it once per node tile for each count 2..8 and every
+ * (pod,node) evaluation looks it up.  Results are identical; throughput figures obtained with it
+ * are reported separately from the brute-force rate (the group search is shared between pods). */
+#define KGWE_CFG_MEMOISE_GROUPS 0x2u
 
 /* One node of the topology snapshot: exactly the fields of NodeTopology / GPUDevice the
  * scorer reads (src/discovery/types.go:11-47,116-164,336-366).

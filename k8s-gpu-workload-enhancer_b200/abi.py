@@ -21,6 +21,7 @@ MIG_NONE, MIG_UNKNOWN = 0, 255
 MIG_NAMES = ["1g.5gb", "1g.10gb", "2g.10gb", "2g.20gb", "3g.20gb", "3g.40gb", "4g.20gb", "4g.40gb", "7g.40gb", "7g.80gb"]
 POD_EXHAUSTIVE = 0x01
 CFG_SUBSET_TABLES = 0x1
+CFG_MEMOISE_GROUPS = 0x2
 F_ELIGIBLE, F_KEPT, F_HINT, F_FALLBACK, F_MINBW, F_GANG_ROLLBACK = 0x01, 0x02, 0x04, 0x08, 0x10, 0x20
 MIG_GPU = np.dtype([("occ", "u1"), ("cls", "u1"), ("enabled", "u1"), ("pad", "u1")])
 MIG_ASSIGNMENT = np.dtype([("gpu_idx", "<u4"), ("start", "u1"), ("size", "u1"), ("cost", "u1"), ("profile", "u1")])

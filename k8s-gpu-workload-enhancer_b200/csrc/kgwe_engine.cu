@@ -191,8 +191,9 @@ int validate_pods(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n) {
 
 uint32_t hint_row_bytes(const kgwe_engine* e) { return (e->n_nodes + 7) / 8; }
 
-size_t score_smem_bytes(uint32_t pods_per_chunk, bool tables = false) {
-    return (size_t)TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx)) + (tables ? SUBSET_SMEM_BYTES : 0) + (size_t)pods_per_chunk * 8 + 16;
+size_t score_smem_bytes(uint32_t pods_per_chunk, bool tables = false, bool memo = false) {
+    return (size_t)TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx)) + (tables ? SUBSET_SMEM_BYTES : 0) + (memo ? MEMO_SMEM_BYTES : 0) +
+           (size_t)pods_per_chunk * 8 + 16;
 }
 
 // Launch K1 (+K1b / K2) for n_pods pods whose descriptors, hint rows and outputs are in
@@ -220,12 +221,13 @@ int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, co
     dim3 grid(n_tiles, chunks);
     const bool timed = e->timers_pending < kgwe_engine::kTimers;
     if (timed) CU(e, cudaEventRecord(e->t0[e->timers_pending], s));
-    if (tables)
-        score_kernel<true><<<grid, SCORE_THREADS, score_smem_bytes(ppc, true), s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e),
-                                                                                   d_scores, best, e->params, e->d_counters);
-    else
-        score_kernel<false><<<grid, SCORE_THREADS, score_smem_bytes(ppc), s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e),
-                                                                              d_scores, best, e->params, e->d_counters);
+    const bool memo = e->cfg.flags & KGWE_CFG_MEMOISE_GROUPS;
+    const size_t smem = score_smem_bytes(ppc, tables, memo);
+#define KGWE_LAUNCH_SCORE(T, M) score_kernel<T, M><<<grid, SCORE_THREADS, smem, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e), \
+                                                                                     d_scores, best, e->params, e->d_counters)
+    if (tables) { if (memo) KGWE_LAUNCH_SCORE(true, true); else KGWE_LAUNCH_SCORE(true, false); }
+    else        { if (memo) KGWE_LAUNCH_SCORE(false, true); else KGWE_LAUNCH_SCORE(false, false); }
+#undef KGWE_LAUNCH_SCORE
     CU(e, cudaGetLastError());
     if (timed) { CU(e, cudaEventRecord(e->t1[e->timers_pending], s)); e->timers_pending++; }
     e->stats.kernel_launches++;
@@ -310,8 +312,10 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
         e->dirty_flag.assign(cfg->max_nodes, 0);
         cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, cfg->device);
         for (int i = 0; i < kgwe_engine::kTimers && ok; ++i) ok = cudaEventCreate(&e->t0[i]) == cudaSuccess && cudaEventCreate(&e->t1[i]) == cudaSuccess;
-        ok = ok && cudaFuncSetAttribute(score_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK)) == cudaSuccess
-                && cudaFuncSetAttribute(score_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK, true)) == cudaSuccess;
+        ok = ok && cudaFuncSetAttribute(score_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK, false, false)) == cudaSuccess
+                && cudaFuncSetAttribute(score_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK, true, false)) == cudaSuccess
+                && cudaFuncSetAttribute(score_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK, false, true)) == cudaSuccess
+                && cudaFuncSetAttribute(score_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK, true, true)) == cudaSuccess;
         int bps = 0;
         if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, schedule_kernel, SCORE_THREADS, 0) == cudaSuccess && bps > 0) e->sched_blocks_per_sm = bps;
     }
@@ -895,7 +899,7 @@ extern "C" int kgwe_score_top1_noalloc(kgwe_engine* e, const kgwe_pod_req* d_pod
     chunks = std::min(chunks, n_pods);
     uint32_t ppc = std::min<uint32_t>((n_pods + chunks - 1) / chunks, MAX_PODS_PER_CHUNK);
     chunks = (n_pods + ppc - 1) / ppc;
-    score_kernel<false><<<dim3(n_tiles, chunks), SCORE_THREADS, score_smem_bytes(ppc), s>>>(
+    score_kernel<false, false><<<dim3(n_tiles, chunks), SCORE_THREADS, score_smem_bytes(ppc), s>>>(
         e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e), d_out, keys, e->params, e->d_counters);
     CU(e, cudaGetLastError());
     finalize_top1_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), keys, d_top1, 1, e->params);

@@ -93,7 +93,13 @@ __device__ __forceinline__ int subset_off(int k) {      // first table slot of p
     return k <= 0 ? 0 : k == 1 ? 1 : k == 2 ? 9 : k == 3 ? 37 : k == 4 ? 93 : k == 5 ? 163 : k == 6 ? 219 : k == 7 ? 247 : k == 8 ? 255 : 256;
 }
 
-template <bool TABLES>
+// MEMO (engine flag KGWE_CFG_MEMOISE_GROUPS): the greedy winner of a node depends only on the
+// node and on k, so it is computed once per tile for k = 2..8 and every (pod,node) evaluation
+// looks it up instead of re-running the 8 chains.  Same results; reported separately from the
+// brute-force rate because the group search is then shared between pods.
+//   extra smem with MEMO: [winners: 64 nodes x 8 x (key, pay)] = 4 KB
+constexpr int MEMO_SMEM_BYTES = TILE_NODES * 8 * 8;
+template <bool TABLES, bool MEMO>
 __global__ void __launch_bounds__(SCORE_THREADS, TABLES ? 1 : 2)
 score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
              const kgwe_pod_req* __restrict__ pods, uint32_t n_pods, uint32_t pods_per_chunk,
@@ -107,7 +113,8 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     constexpr size_t kBase = TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx));
     uint32_t* subset = reinterpret_cast<uint32_t*>(smem + kBase);                       // TABLES only
     uint8_t* smask = smem + kBase + TILE_NODES * 256 * 4;                               // TABLES only
-    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem + kBase + (TABLES ? SUBSET_SMEM_BYTES : 0));
+    int2* memo = reinterpret_cast<int2*>(smem + kBase + (TABLES ? SUBSET_SMEM_BYTES : 0));   // MEMO only
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem + kBase + (TABLES ? SUBSET_SMEM_BYTES : 0) + (MEMO ? MEMO_SMEM_BYTES : 0));
     uint64_t* bar = reinterpret_cast<uint64_t*>(keys + pods_per_chunk);
 
     const int tid = threadIdx.x, lane = tid & 31, grp = tid >> 3, j = tid & 7;
@@ -164,6 +171,17 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
             }
         }
         __syncwarp();
+        if (MEMO) {
+            // greedy winners of this node for every group size (all 32 lanes: shuffles inside)
+#pragma unroll 1
+            for (int kk = 2; kk <= 8; ++kk) {
+                int32_t key = 0; uint32_t pay = 0;
+                if (c.integral && c.A >= kk) greedy_chain_fast(nf, j, kk, key, pay);
+                fast_group_winner(key, pay);
+                if (j == 0) memo[grp * 8 + (kk - 1)] = make_int2(key, (int)pay);
+            }
+            __syncwarp();
+        }
     }
     const NodeCtx& nc = ctxs[grp];
     const uint32_t gnode = P.node_base + node;
@@ -183,7 +201,11 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         if (octet) {
             // ---- phase A: the group searches, one pod slot at a time ----
             int32_t mykey = 0; uint32_t mypay = 0;
-            const int chain_k = (eligible && wants_group) ? (k | (exhaustive ? 16 : 0)) : 0;
+            int chain_k = (eligible && wants_group) ? (k | (exhaustive ? 16 : 0)) : 0;
+            if (MEMO && chain_k && !exhaustive) {        // look the greedy winner up instead of searching
+                const int2 w = memo[grp * 8 + (k - 1)];
+                mykey = w.x; mypay = (uint32_t)w.y; chain_k = 0;
+            }
 #pragma unroll 1
             for (int t = 0; t < 8; ++t) {
                 const int ct = __shfl_sync(0xffffffffu, chain_k, t, 8);

@@ -50,7 +50,7 @@ def test_stateless_matrix_and_topk(kg, orc, num, scale, npods, with_hint):
     nodes, pods, led = synth.config(num, scale)
     pods = pods[:npods]
     hint = synth.make_hint(len(pods), len(nodes), 0.03) if with_hint else None
-    eng = engine_for(kg, nodes, led)
+    eng = engine_for(kg, nodes, led, flags=abi.CFG_MEMOISE_GROUPS if with_hint else 0)     # both group-search modes
     for topk in (1, 5, 16):
         scores, top = eng.score_batch(pods, len(nodes), hint=hint, want_scores=True, topk=topk)
         o_scores, o_top, ctr = orc.score_batch(abi, nodes, led, pods, hint=hint, want_scores=True, topk=topk, threads=4)
@@ -133,7 +133,7 @@ def test_exhaustive_extension(kg, orc):
     nodes2 = nodes.copy()
     nodes2["nvl_bw"][::7] *= 1.03125
     o_scores, o_top, _ = orc.score_batch(abi, nodes2, led, mixed, want_scores=True, topk=1, threads=4)
-    for flags in (abi.CFG_SUBSET_TABLES, 0):
+    for flags in (abi.CFG_SUBSET_TABLES, 0, abi.CFG_MEMOISE_GROUPS, abi.CFG_MEMOISE_GROUPS | abi.CFG_SUBSET_TABLES):
         e2 = engine_for(kg, nodes2, led, flags=flags)
         s2, t2 = e2.score_batch(mixed, len(nodes2), want_scores=True, topk=1)
         assert s2.tobytes() == o_scores.tobytes()
