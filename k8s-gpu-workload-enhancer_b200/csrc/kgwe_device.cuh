@@ -87,7 +87,7 @@ struct NodeCtx {
     uint32_t numa_order, pcie_order;  // available GPUs in (key asc, index asc) order, 3 bits each
     uint64_t avail_prefix;            // byte k-1: the first k available GPUs (index order) as a mask
     uint32_t avail_order;             // available GPUs in index order, 3 bits each
-    bool     valid, integral;
+    bool     valid, integral, tables_valid;
 };
 
 struct EvalOut {
@@ -125,7 +125,16 @@ __device__ inline void group_tables(uint64_t keys8, bool is_signed, uint32_t ava
     }
 }
 
-__device__ inline void node_ctx_init(NodeCtx& c, const DevNode* rec, bool in_range) {
+__device__ inline void node_ctx_group_tables(NodeCtx& c, const DevNode* rec) {
+    if (c.valid) {
+        group_tables(ld_u64(rec->numa), true, c.avail, c.numa_pick, c.numa_order);
+        group_tables(ld_u64(rec->pcie_switch), false, c.avail, c.pcie_pick, c.pcie_order);
+    } else { c.numa_pick = c.pcie_pick = 0; c.numa_order = c.pcie_order = 0; }
+    c.tables_valid = true;
+}
+
+// Everything of NodeCtx except the NUMA / PCIe group tables (tables_valid = false).
+__device__ inline void node_ctx_core(NodeCtx& c, const DevNode* rec, bool in_range) {
     c.valid = in_range && (rec->flags & NODE_PRESENT);
     c.integral = c.valid && (rec->flags & NODE_INTEGRAL);
     uint32_t ng = c.valid ? rec->n_gpus : 0;
@@ -158,10 +167,12 @@ __device__ inline void node_ctx_init(NodeCtx& c, const DevNode* rec, bool in_ran
             m &= m - 1; ++i;
         }
     }
-    if (c.valid) {
-        group_tables(ld_u64(rec->numa), true, avail, c.numa_pick, c.numa_order);
-        group_tables(ld_u64(rec->pcie_switch), false, avail, c.pcie_pick, c.pcie_order);
-    } else { c.numa_pick = c.pcie_pick = 0; c.numa_order = c.pcie_order = 0; }
+    c.numa_pick = c.pcie_pick = 0; c.numa_order = c.pcie_order = 0; c.tables_valid = false;
+}
+
+__device__ inline void node_ctx_init(NodeCtx& c, const DevNode* rec, bool in_range) {
+    node_ctx_core(c, rec, in_range);
+    node_ctx_group_tables(c, rec);
 }
 
 // First k set bits of `m` in index order -> (mask, packed list).
@@ -222,6 +233,31 @@ __device__ __forceinline__ void greedy_chain_fast_k(const NodeFast* nf, int s, i
     }
     const int32_t total = sum >> FAST_SHIFT;
     if (total > 0) { key = (total << 3) | (7 - s); pay = order; }
+}
+
+// The chain from start s for group size k is the first k-1 steps of the chain for size 8, so one
+// run yields the outcome for every size: sums[t] = running sum of maxima after step t+1 (valid for
+// t < steps), order = join order of the longest chain.  Used where a node's winners for all sizes
+// are rebuilt at once (memo tables).
+__device__ __forceinline__ void greedy_chain_fast_all(const NodeFast* nf, int s, int32_t (&sums)[7], int& steps, uint32_t& order) {
+    steps = 0; order = (uint32_t)s;
+    const int4* ip = reinterpret_cast<const int4*>(nf->init);
+    int4 a = ip[0], b = ip[1];
+    if (nf->init[s] < 0) { steps = -1; return; }
+    int32_t sum = 0; int m = s;
+#pragma unroll
+    for (int step = 1; step < 8; ++step) {
+        const int4* rp = reinterpret_cast<const int4*>(nf->row[m]);
+        const int4 r0 = rp[0], r1 = rp[1];
+        a.x += r0.x; a.y += r0.y; a.z += r0.z; a.w += r0.w;
+        b.x += r1.x; b.y += r1.y; b.z += r1.z; b.w += r1.w;
+        const int32_t best = __vimax3_s32(__vimax3_s32(a.x, a.y, a.z), __vimax3_s32(a.w, b.x, b.y), max(b.z, b.w));
+        if (best <= 7) return;
+        m = ~best & 7;
+        sum += best;
+        sums[step - 1] = sum; steps = step;
+        order |= (uint32_t)m << (3 * step);
+    }
 }
 
 __device__ __forceinline__ void greedy_chain_fast(const NodeFast* nf, int s, int k, int32_t& key, uint32_t& pay) {

@@ -68,6 +68,7 @@ struct kgwe_engine {
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     int sm_count = 148;
     int sched_blocks_per_sm = 1;
+    int sched_tile_blocks_per_sm = 0;
 
     DevNode* d_nodes = nullptr;       // cluster image in HBM
     DevNode* h_nodes = nullptr;       // pinned mirror (device layout)
@@ -80,6 +81,7 @@ struct kgwe_engine {
     DevBuf<kgwe_pod_req> d_pods;
     DevBuf<uint8_t> d_hint;
     DevBuf<unsigned long long> d_best;      // arg-max keys, kept all-zero between calls
+    DevBuf<unsigned int> d_arrive;          // per-pod arrival counters of the queue kernel, kept all-zero between calls
     DevBuf<kgwe_placement> d_topk;
     DevBuf<kgwe_node_score> d_scores;
     unsigned long long* d_counters = nullptr;   // [0] evaluations (K3), [1] candidates
@@ -190,6 +192,7 @@ int validate_pods(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n) {
 }
 
 uint32_t hint_row_bytes(const kgwe_engine* e) { return (e->n_nodes + 7) / 8; }
+size_t sched_tile_smem_bytes() { return (size_t)TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx) + 64) + 16; }
 
 size_t score_smem_bytes(uint32_t pods_per_chunk, bool tables = false, bool memo = false) {
     return (size_t)TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx)) + (tables ? SUBSET_SMEM_BYTES : 0) + (memo ? MEMO_SMEM_BYTES : 0) +
@@ -318,6 +321,9 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
                 && cudaFuncSetAttribute(score_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK, true, true)) == cudaSuccess;
         int bps = 0;
         if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, schedule_kernel, SCORE_THREADS, 0) == cudaSuccess && bps > 0) e->sched_blocks_per_sm = bps;
+        ok = ok && cudaFuncSetAttribute(schedule_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sched_tile_smem_bytes()) == cudaSuccess;
+        bps = 0;
+        if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, schedule_tile_kernel, SCORE_THREADS, sched_tile_smem_bytes()) == cudaSuccess && bps > 0) e->sched_tile_blocks_per_sm = bps;
     }
     if (!ok) { cudaGetLastError(); kgwe_engine_destroy(e); return KGWE_ERR_CUDA; }
     *out = e;
@@ -328,7 +334,7 @@ int kgwe_engine_destroy(kgwe_engine* e) {
     if (!e) return KGWE_ERR_INVALID_ARG;
     cudaSetDevice(e->cfg.device);
     if (e->stream) cudaStreamSynchronize(e->stream);
-    e->d_pods.release(); e->d_hint.release(); e->d_best.release(); e->d_topk.release(); e->d_scores.release();
+    e->d_pods.release(); e->d_hint.release(); e->d_best.release(); e->d_arrive.release(); e->d_topk.release(); e->d_scores.release();
     e->h_pods.release(); e->h_topk.release(); e->h_hint.release();
     if (e->d_nodes) cudaFree(e->d_nodes);
     if (e->h_nodes) cudaFreeHost(e->h_nodes);
@@ -547,6 +553,9 @@ static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t 
         const size_t had = e->d_best.cap;
         CU(e, e->d_best.ensure(np));
         if (e->d_best.cap != had) CU(e, cudaMemsetAsync(e->d_best.p, 0, e->d_best.cap * sizeof(unsigned long long), s));
+        const size_t had2 = e->d_arrive.cap;
+        CU(e, e->d_arrive.ensure(np));
+        if (e->d_arrive.cap != had2) CU(e, cudaMemsetAsync(e->d_arrive.p, 0, e->d_arrive.cap * sizeof(unsigned int), s));
     }
     memcpy(e->h_pods.p, pods, (size_t)np * sizeof(kgwe_pod_req));
     CU(e, cudaMemcpyAsync(e->d_pods.p, e->h_pods.p, (size_t)np * sizeof(kgwe_pod_req), cudaMemcpyHostToDevice, s));
@@ -563,12 +572,18 @@ static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t 
     uint32_t grid = std::min<uint32_t>((uint32_t)(e->sm_count * e->sched_blocks_per_sm), (N + TILE_NODES - 1) / TILE_NODES);
     grid = std::max(grid, 1u);
     DevNode* d_nodes = e->d_nodes; uint32_t n_nodes = N; const kgwe_pod_req* d_pods = e->d_pods.p; uint32_t npods = np; uint32_t rowb = row;
-    unsigned long long* best = e->d_best.p; kgwe_placement* d_out = e->d_topk.p; Params prm = e->params; unsigned long long* ctr = e->d_counters;
-    void* args[] = {&d_nodes, &n_nodes, &d_pods, &npods, &d_hint, &rowb, &best, &d_out, &prm, &ctr};
+    unsigned long long* best = e->d_best.p; unsigned int* arrive = e->d_arrive.p; kgwe_placement* d_out = e->d_topk.p; Params prm = e->params; unsigned long long* ctr = e->d_counters;
+    void* args[] = {&d_nodes, &n_nodes, &d_pods, &npods, &d_hint, &rowb, &best, &arrive, &d_out, &prm, &ctr};
     CU(e, cudaEventRecord(e->ev0, s));
+    const uint32_t n_tiles = (N + TILE_NODES - 1) / TILE_NODES;
+    if (n_tiles <= (uint32_t)(e->sm_count * e->sched_tile_blocks_per_sm)) {
+        // every node gets its own lane group: tile form (shared-memory resident tables)
+        CU(e, cudaLaunchCooperativeKernel((const void*)schedule_tile_kernel, dim3(n_tiles), dim3(SCORE_THREADS), args, sched_tile_smem_bytes(), s));
+    } else
     CU(e, cudaLaunchCooperativeKernel((const void*)schedule_kernel, dim3(grid), dim3(SCORE_THREADS), args, 0, s));
     e->stats.kernel_launches++;
     CU(e, cudaMemsetAsync(e->d_best.p, 0, (size_t)np * sizeof(unsigned long long), s));
+    CU(e, cudaMemsetAsync(e->d_arrive.p, 0, (size_t)np * sizeof(unsigned int), s));
     CU(e, cudaEventRecord(e->ev1, s));
     CU(e, cudaMemcpyAsync(e->h_topk.p, e->d_topk.p, (size_t)np * sizeof(kgwe_placement), cudaMemcpyDeviceToHost, s));
     e->stats.d2h_bytes += (uint64_t)np * sizeof(kgwe_placement);

@@ -393,10 +393,10 @@ topk_merge_kernel(const kgwe_placement* __restrict__ lists, uint32_t n_lists, ui
 __global__ void __launch_bounds__(SCORE_THREADS, 2)
 schedule_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
                 const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
-                unsigned long long* __restrict__ best, kgwe_placement* __restrict__ out,
+                unsigned long long* __restrict__ best, unsigned int* __restrict__ arrive, kgwe_placement* __restrict__ out,
                 Params P, unsigned long long* __restrict__ counters) {
-    cg::grid_group grid = cg::this_grid();
     __shared__ unsigned long long wmax[SCORE_THREADS / 32];
+    __shared__ unsigned long long winner;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t n_groups = gridDim.x * (SCORE_THREADS / 8);
     const uint32_t g = blockIdx.x * (SCORE_THREADS / 8) + (tid >> 3);
@@ -425,13 +425,21 @@ schedule_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict
         for (int off = 16; off >= 8; off >>= 1) { unsigned long long o2 = __shfl_xor_sync(0xffffffffu, m, off); m = o2 > m ? o2 : m; }
         if (lane == 0) wmax[warp] = m;
         __syncthreads();
+        // grid-wide arg-max + barrier in one: every CTA folds its maximum into best[p], then bumps the
+        // pod's arrival counter; the pod is decided when all CTAs have arrived (all CTAs are co-resident:
+        // cooperative launch).  One counter per pod, so nothing has to be reset inside the kernel.
         if (tid == 0) {
             unsigned long long b = wmax[0];
             for (int w = 1; w < SCORE_THREADS / 32; ++w) b = wmax[w] > b ? wmax[w] : b;
             if (b) atomicMax(&best[p], b);
+            __threadfence();
+            atomicAdd(&arrive[p], 1u);
+            while (*reinterpret_cast<volatile unsigned int*>(&arrive[p]) < gridDim.x) { }
+            __threadfence();
+            winner = *reinterpret_cast<volatile unsigned long long*>(&best[p]);
         }
-        grid.sync();
-        const unsigned long long win = *reinterpret_cast<volatile unsigned long long*>(&best[p]);
+        __syncthreads();
+        const unsigned long long win = winner;
         if (win == 0ull) {
             if (g == 0 && (lane & 7) == 0) store_no_placement(out + p);      // "no eligible nodes found", scheduler.go:138-141
         } else if (win == mykey) {
@@ -447,6 +455,151 @@ schedule_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict
         }
     }
     if ((lane & 7) != 0) { cand = 0; evals = 0; }
+#pragma unroll
+    for (int off = 16; off >= 8; off >>= 1) { cand += __shfl_xor_sync(0xffffffffu, cand, off); evals += __shfl_xor_sync(0xffffffffu, evals, off); }
+    if (lane == 0 && counters) { if (evals) atomicAdd(&counters[0], evals); if (cand) atomicAdd(&counters[1], cand); }
+}
+
+// ---------------------------------------------------------------------------------------
+// K3 tile form (used when every node has its own lane group: n_nodes <= grid * 64).  CTA b owns
+// the node tile [64b, 64b+64) for the whole queue: the tile, its NodeCtx / NodeFast and a table of
+// greedy winners per group size live in shared memory and are rebuilt by the owning group only
+// when one of its commits changes the node.  Per workload: a filter + table look-up + finish per
+// node, block max, then the same arg-max + arrival-counter barrier as above.  The next workload's
+// descriptor is prefetched while the current one is decided.
+__device__ __forceinline__ void group_winner_masked(int32_t& key, uint32_t& pay, uint32_t gmask) {
+#pragma unroll
+    for (int off = 4; off >= 1; off >>= 1) key = max(key, __shfl_xor_sync(gmask, key, off, 8));
+    pay = __shfl_sync(gmask, pay, 7 - (key & 7), 8);
+}
+
+// (Re)build one node's tables by its 8 lanes.  `full` = first build (NVLink matrix rows too);
+// after a commit only availability-dependent parts change.  NUMA / PCIe group tables are left
+// stale (tables_valid = false) and filled on demand by ensure_group_tables.
+__device__ __forceinline__ void node_tables_build(const DevNode* rec, bool in_range, bool full, NodeCtx* ctx, NodeFast* nf, int2* memo, int j, uint32_t gmask) {
+    NodeCtx c;
+    node_ctx_core(c, rec, in_range);
+    if (c.integral) { if (full) node_fast_build(nf, rec, c, j); else nf->init[j] = (c.avail >> j & 1) ? (7 - j) : FAST_NEG; }
+    else nf->init[j] = FAST_NEG;
+    if (j == 0) *ctx = c;
+    __syncwarp(gmask);
+    int32_t sums[7]; int steps = -1; uint32_t order = 0;
+    if (c.integral) greedy_chain_fast_all(nf, j, sums, steps, order);
+#pragma unroll
+    for (int kk = 2; kk <= 8; ++kk) {
+        const int32_t total = steps >= kk - 1 ? (sums[kk - 2] >> FAST_SHIFT) : 0;
+        int32_t key = total > 0 ? ((total << 3) | (7 - j)) : 0;
+        uint32_t pay = order & ((kk >= 8) ? 0xffffffu : ((1u << (3 * kk)) - 1u));
+        group_winner_masked(key, pay, gmask);
+        if (j == 0) memo[kk - 1] = make_int2(key, (int)pay);
+    }
+    __syncwarp(gmask);
+}
+
+// NUMA / PCIe group tables of a node, computed the first time a workload asks for them after
+// the node changed.  Group-uniform scalar code, no shuffles: safe under divergence.
+__device__ __forceinline__ void ensure_group_tables(NodeCtx* ctx, const DevNode* rec, int j, uint32_t gmask) {
+    if (ctx->tables_valid) return;
+    NodeCtx c = *ctx;
+    node_ctx_group_tables(c, rec);
+    __syncwarp(gmask);
+    if (j == 0) *ctx = c;
+    __syncwarp(gmask);
+}
+
+__global__ void __launch_bounds__(SCORE_THREADS, 2)
+schedule_tile_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
+                     const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
+                     unsigned long long* __restrict__ best, unsigned int* __restrict__ arrive, kgwe_placement* __restrict__ out,
+                     Params P, unsigned long long* __restrict__ counters) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    DevNode* tile = reinterpret_cast<DevNode*>(smem);
+    NodeFast* fast = reinterpret_cast<NodeFast*>(smem + TILE_NODES * sizeof(DevNode));
+    NodeCtx* ctxs = reinterpret_cast<NodeCtx*>(smem + TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast)));
+    int2* memos = reinterpret_cast<int2*>(smem + TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx)));
+    uint64_t* bar = reinterpret_cast<uint64_t*>(memos + TILE_NODES * 8);
+    __shared__ unsigned long long wmax[SCORE_THREADS / 32];
+    __shared__ unsigned long long winner;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, grp = tid >> 3, j = tid & 7;
+    const uint32_t gmask = 0xffu << (lane & 24);
+    const uint32_t tile_first = blockIdx.x * TILE_NODES;
+    const uint32_t tile_count = tile_first < n_nodes ? min((uint32_t)TILE_NODES, n_nodes - tile_first) : 0;
+    if (tid == 0) mbar_init(bar, 1);
+    __syncthreads();
+    if (tid == 0 && tile_count) {
+        const uint32_t bytes = tile_count * (uint32_t)sizeof(DevNode);
+        mbar_expect_tx(bar, bytes);
+        tma_bulk_g2s(tile, nodes + tile_first, bytes, bar);
+    }
+    if (tile_count) mbar_wait(bar, 0);
+    __syncthreads();
+
+    const uint32_t node = tile_first + grp;
+    const bool node_ok = grp < (int)tile_count;
+    DevNode* rec = tile + grp;
+    NodeFast* nf = fast + grp;
+    int2* memo = memos + grp * 8;
+    node_tables_build(rec, node_ok, true, ctxs + grp, nf, memo, j, gmask);
+    const NodeCtx& nc = ctxs[grp];
+    bool warp_fast = __all_sync(0xffffffffu, nc.integral || !nc.valid);
+    unsigned long long cand = 0, evals = 0;
+    kgwe_pod_req pod = load_pod(pods, 0);
+
+    for (uint32_t p = 0; p < n_pods; ++p) {
+        const kgwe_pod_req next = load_pod(pods, p + 1 < n_pods ? p + 1 : p);      // prefetch
+        const int k = clamp_k(pod.gpu_count);
+        const bool hinted = node_ok && hint_bit(hint, hint_row_bytes, p, node);
+        EvalOut o;
+        if (pod.topology_pref == KGWE_TOPO_SAME_NUMA || pod.topology_pref == KGWE_TOPO_SAME_PCIE_SWITCH) ensure_group_tables(ctxs + grp, rec, j, gmask);
+        if (warp_fast && !(pod.flags & KGWE_POD_EXHAUSTIVE)) {      // warp-uniform
+            const bool eligible = eval_filter(rec, nc, pod, k);
+            bool found = false; double win_total = 0.0; uint32_t sel = 0, ord = 0;
+            if (eligible && k >= 2 && is_nvlink_pref(pod)) {
+                const int2 w = memo[k - 1];
+                found = w.x > 0; win_total = (double)(w.x >> 3); ord = (uint32_t)w.y; sel = found ? mask_of_order(ord, k) : 0u;
+            }
+            eval_finish(rec, nc, pod, P, hinted, eligible, k, found, win_total, sel, ord, (uint32_t)nc.A, o);
+        } else {
+            evaluate<false>(rec, nc, pod, P, hinted, lane, o);
+        }
+        if (node_ok && j == 0) { cand += o.candidates; evals += 1; }
+        const unsigned long long mykey = (o.flags & KGWE_F_KEPT) ? rank_key(o.total, P.node_base + node) : 0ull;
+        unsigned long long m = mykey;
+#pragma unroll
+        for (int off = 16; off >= 8; off >>= 1) { unsigned long long o2 = __shfl_xor_sync(0xffffffffu, m, off); m = o2 > m ? o2 : m; }
+        if (lane == 0) wmax[warp] = m;
+        __syncthreads();
+        if (tid == 0) {
+            unsigned long long b = wmax[0];
+            for (int w = 1; w < SCORE_THREADS / 32; ++w) b = wmax[w] > b ? wmax[w] : b;
+            if (b) atomicMax(&best[p], b);
+            __threadfence();
+            atomicAdd(&arrive[p], 1u);
+            while (*reinterpret_cast<volatile unsigned int*>(&arrive[p]) < gridDim.x) { }
+            __threadfence();
+            winner = *reinterpret_cast<volatile unsigned long long*>(&best[p]);
+        }
+        __syncthreads();
+        const unsigned long long win = winner;
+        if (win == 0ull) {
+            if (blockIdx.x == 0 && tid == 0) store_no_placement(out + p);
+        } else if (win == mykey) {
+            // this group owns the winner: tryScheduleOnNode + recordAllocation (scheduler.go:625-653, 695-707)
+            if (j == 0) {
+                store_placement(out + p, P.node_base + node, o, est_bandwidth(rec, o.order, (int)((o.order >> 24) & 15)));
+                rec->allocated_mask = (uint8_t)(rec->allocated_mask | o.mask);
+                rec->n_allocs = rec->n_allocs + 1;
+                nodes[node].allocated_mask = rec->allocated_mask;       // the image in HBM follows
+                nodes[node].n_allocs = rec->n_allocs;
+            }
+            __syncwarp(gmask);
+            node_tables_build(rec, true, false, ctxs + grp, nf, memo, j, gmask);
+        }
+        __syncwarp();
+        pod = next;
+    }
+    if (j != 0) { cand = 0; evals = 0; }
 #pragma unroll
     for (int off = 16; off >= 8; off >>= 1) { cand += __shfl_xor_sync(0xffffffffu, cand, off); evals += __shfl_xor_sync(0xffffffffu, evals, off); }
     if (lane == 0 && counters) { if (evals) atomicAdd(&counters[0], evals); if (cand) atomicAdd(&counters[1], cand); }
