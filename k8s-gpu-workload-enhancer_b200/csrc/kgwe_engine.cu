@@ -203,14 +203,19 @@ size_t score_smem_bytes(uint32_t pods_per_chunk, bool tables = false, bool memo 
 // device memory.  d_scores may be null unless topk > 1.
 int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const uint8_t* d_hint,
                  kgwe_node_score* d_scores, uint32_t topk, kgwe_placement* d_topk, cudaStream_t s, bool tables = false) {
-    tables = tables || (e->cfg.flags & KGWE_CFG_SUBSET_TABLES);
     if (n_pods == 0 || e->n_nodes == 0) return KGWE_OK;
     const uint32_t n_tiles = (e->n_nodes + TILE_NODES - 1) / TILE_NODES;
-    // pod chunks: enough CTAs to fill the GPU a few times over, table size bounded
-    uint32_t want_ctas = (uint32_t)e->sm_count * 2u * 4u;
-    uint32_t chunks = std::max(1u, (want_ctas + n_tiles - 1) / n_tiles);
-    chunks = std::min(chunks, n_pods);
-    uint32_t ppc = (n_pods + chunks - 1) / chunks;
+    // pod chunks: whole waves of co-resident CTAs (2 per SM; 1 with subset tables), as few waves as keep
+    // the per-CTA arg-max table within bounds - every CTA pays the tile set-up once, so fewer, longer
+    // CTAs amortise it better, and whole waves avoid a ragged tail (all CTAs do the same amount of work)
+    tables = tables || (e->cfg.flags & KGWE_CFG_SUBSET_TABLES);
+    const uint32_t slots = (uint32_t)e->sm_count * (tables ? 1u : 2u);
+    uint32_t chunks = 1, ppc = n_pods;
+    for (uint32_t waves = 1; waves <= 64; ++waves) {
+        chunks = std::max(1u, std::min(n_pods, slots * waves / n_tiles));
+        ppc = (n_pods + chunks - 1) / chunks;
+        if (ppc <= MAX_PODS_PER_CHUNK && (waves >= 2 || n_pods <= 64)) break;
+    }
     if (ppc > MAX_PODS_PER_CHUNK) ppc = MAX_PODS_PER_CHUNK;
     chunks = (n_pods + ppc - 1) / ppc;
     if (chunks > 65535u) return fail(e, KGWE_ERR_TOO_LARGE, "too many pods in one launch (%u)", n_pods);

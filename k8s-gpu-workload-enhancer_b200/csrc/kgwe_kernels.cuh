@@ -131,13 +131,19 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         tma_bulk_g2s(tile, nodes + tile_first, bytes, bar);
     }
     if (best) for (uint32_t i = tid; i < pods_per_chunk; i += SCORE_THREADS) keys[i] = 0ull;
+    // NUMA / PCIe group tables are only worth building when the chunk has a pod that asks for them
+    bool want_groups = false;
+    for (uint32_t p = p_begin + tid; p < p_end; p += SCORE_THREADS) {
+        const uint8_t pref = __ldg(&pods[p].topology_pref);
+        want_groups |= pref == KGWE_TOPO_SAME_NUMA || pref == KGWE_TOPO_SAME_PCIE_SWITCH;
+    }
     if (TABLES && tid < 256) {          // slot of mask `tid` in (popcount, value) order
         int rank = 0;
         for (int m = 0; m < tid; ++m) rank += __popc(m) == __popc(tid);
         smask[subset_off(__popc(tid)) + rank] = (uint8_t)tid;
     }
     mbar_wait(bar, 0);
-    __syncthreads();
+    want_groups = __syncthreads_or(want_groups);
 
     const uint32_t node = tile_first + grp;
     const bool node_ok = grp < (int)tile_count;
@@ -146,7 +152,8 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     bool warp_fast;
     {
         NodeCtx c;
-        node_ctx_init(c, rec, node_ok);
+        node_ctx_core(c, rec, node_ok);
+        if (want_groups) node_ctx_group_tables(c, rec);
         // integer form of the greedy inputs; usable when all four nodes of the warp are whole-number
         warp_fast = __all_sync(0xffffffffu, c.integral || !c.valid);
         if (c.integral) node_fast_build(nf, rec, c, j);
