@@ -440,20 +440,23 @@ __device__ __forceinline__ void eval_finish(const DevNode* rec, const NodeCtx& n
     o.mask = sel; o.order = order | ((uint32_t)nsel << 24); o.flags = flags;
 }
 
-// Winner of the 8 integer chains of a group: key = (total << 3) | (7 - start).
-__device__ __forceinline__ void fast_group_winner(int32_t& key, uint32_t& pay) {
+// Winner of the 8 integer chains of a group: key = (total << 3) | (7 - start).  `gmask` names the
+// 8 lanes of the group (or the whole warp when all four groups are known to be here together).
+__device__ __forceinline__ void fast_group_winner(int32_t& key, uint32_t& pay, uint32_t gmask = 0xffffffffu) {
 #pragma unroll
-    for (int off = 4; off >= 1; off >>= 1) key = max(key, __shfl_xor_sync(0xffffffffu, key, off, 8));
-    pay = __shfl_sync(0xffffffffu, pay, 7 - (key & 7), 8);
+    for (int off = 4; off >= 1; off >>= 1) key = max(key, __shfl_xor_sync(gmask, key, off, 8));
+    pay = __shfl_sync(gmask, pay, 7 - (key & 7), 8);
 }
 
 // isNodeEligible + scoreNode for one (pod,node), executed by the 8 lanes of a group
-// (lane j = `lane & 7`); the result is identical on all 8 lanes.  All 32 lanes of the warp
-// must call it together (segmented shuffles inside) with the same pod.
+// (lane j = `lane & 7`); the result is identical on all 8 lanes.  The 8 lanes of a group must call
+// it together; its shuffles name only the group's own lanes, so the four groups of a warp may be
+// on different pods (and so on different branches).
 template <bool FAST>
 __device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, const kgwe_pod_req& pod, const Params& P,
                                          bool hinted, int lane, EvalOut& o, const NodeFast* nf = nullptr, bool warp_fast = false) {
     const int j = lane & 7;
+    const uint32_t gmask = 0xffu << (lane & 24);
     const int k = clamp_k(pod.gpu_count);
     const bool eligible = eval_filter(rec, nc, pod, k);
     bool found = false; double win_total = 0.0; uint32_t sel = 0, order = 0, candidates = 1;
@@ -464,7 +467,7 @@ __device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, 
             // all four nodes of this warp have whole-number bandwidths: integer chains, 32-bit winner
             int32_t key = 0; uint32_t pay = 0;
             if (eligible) greedy_chain_fast(nf, j, k, key, pay);
-            fast_group_winner(key, pay);
+            fast_group_winner(key, pay, gmask);
             found = key > 0; win_total = (double)(key >> 3);
             order = pay; sel = mask_of_order(order, k);
             candidates = (uint32_t)nc.A;
@@ -489,9 +492,9 @@ __device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, 
             uint32_t tie = exhaustive ? pay : (uint32_t)j;
 #pragma unroll
             for (int off = 4; off >= 1; off >>= 1) {
-                uint64_t okey = __shfl_xor_sync(0xffffffffu, key, off, 8);
-                uint32_t otie = __shfl_xor_sync(0xffffffffu, tie, off, 8);
-                uint32_t opay = __shfl_xor_sync(0xffffffffu, pay, off, 8);
+                uint64_t okey = __shfl_xor_sync(gmask, key, off, 8);
+                uint32_t otie = __shfl_xor_sync(gmask, tie, off, 8);
+                uint32_t opay = __shfl_xor_sync(gmask, pay, off, 8);
                 if (okey > key || (okey == key && otie < tie)) { key = okey; tie = otie; pay = opay; }
             }
             found = key != 0ull; win_total = __longlong_as_double((long long)key);

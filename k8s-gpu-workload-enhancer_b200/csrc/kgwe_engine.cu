@@ -10,6 +10,7 @@
 //   * scratch: arg-max key table, pod/hint/top-k staging, an optional score-matrix chunk.
 // No CPU fallback: every scoring entry point launches the CUDA kernels or fails.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -89,6 +90,9 @@ struct kgwe_engine {
     PinBuf<kgwe_placement> h_topk;
     PinBuf<uint8_t> h_hint;
     unsigned long long* h_counters = nullptr;
+    unsigned int* d_done = nullptr;           // latency path: CTA completion ticket
+    unsigned int* h_flag = nullptr;           // latency path: pinned word the kernel sets to flag_seq when the placements are written
+    unsigned int flag_seq = 0;
 
     // K1 timing: event pairs recorded around each score_kernel launch, harvested by get_stats
     static constexpr int kTimers = 64;
@@ -202,7 +206,10 @@ size_t score_smem_bytes(uint32_t pods_per_chunk, bool tables = false, bool memo 
 // Launch K1 (+K1b / K2) for n_pods pods whose descriptors, hint rows and outputs are in
 // device memory.  d_scores may be null unless topk > 1.
 int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const uint8_t* d_hint,
-                 kgwe_node_score* d_scores, uint32_t topk, kgwe_placement* d_topk, cudaStream_t s, bool tables = false) {
+                 kgwe_node_score* d_scores, uint32_t topk, kgwe_placement* d_topk, cudaStream_t s, bool tables = false,
+                 bool fused_tail = false) {
+    FusedTail tail{nullptr, nullptr, nullptr, 0};
+    if (fused_tail) tail = FusedTail{d_topk, e->d_done, e->h_flag, ++e->flag_seq};
     if (n_pods == 0 || e->n_nodes == 0) return KGWE_OK;
     const uint32_t n_tiles = (e->n_nodes + TILE_NODES - 1) / TILE_NODES;
     // pod chunks: whole waves of co-resident CTAs (2 per SM; 1 with subset tables), as few waves as keep
@@ -227,18 +234,19 @@ int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, co
         best = e->d_best.p;
     }
     dim3 grid(n_tiles, chunks);
-    const bool timed = e->timers_pending < kgwe_engine::kTimers;
+    const bool timed = !fused_tail && e->timers_pending < kgwe_engine::kTimers;
     if (timed) CU(e, cudaEventRecord(e->t0[e->timers_pending], s));
     const bool memo = e->cfg.flags & KGWE_CFG_MEMOISE_GROUPS;
     const size_t smem = score_smem_bytes(ppc, tables, memo);
 #define KGWE_LAUNCH_SCORE(T, M) score_kernel<T, M><<<grid, SCORE_THREADS, smem, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e), \
-                                                                                     d_scores, best, e->params, e->d_counters)
+                                                                                     d_scores, best, e->params, e->d_counters, tail)
     if (tables) { if (memo) KGWE_LAUNCH_SCORE(true, true); else KGWE_LAUNCH_SCORE(true, false); }
     else        { if (memo) KGWE_LAUNCH_SCORE(false, true); else KGWE_LAUNCH_SCORE(false, false); }
 #undef KGWE_LAUNCH_SCORE
     CU(e, cudaGetLastError());
     if (timed) { CU(e, cudaEventRecord(e->t1[e->timers_pending], s)); e->timers_pending++; }
     e->stats.kernel_launches++;
+    if (fused_tail) { e->stats.evaluations += (uint64_t)n_pods * e->n_present; return KGWE_OK; }
     if (topk == 1) {
         const uint32_t threads = 256, pods_per_block = threads / 8;
         finalize_top1_kernel<<<(n_pods + pods_per_block - 1) / pods_per_block, threads, 0, s>>>(
@@ -312,11 +320,13 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
            && cudaMallocHost(&e->h_nodes, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
            && cudaMalloc(&e->d_counters, 2 * sizeof(unsigned long long)) == cudaSuccess
            && cudaMallocHost(&e->h_counters, 2 * sizeof(unsigned long long)) == cudaSuccess
+           && cudaMalloc(&e->d_done, sizeof(unsigned int)) == cudaSuccess && cudaMemset(e->d_done, 0, sizeof(unsigned int)) == cudaSuccess
+           && cudaMallocHost(&e->h_flag, sizeof(unsigned int)) == cudaSuccess
            && cudaMemset(e->d_nodes, 0, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
            && cudaMemset(e->d_counters, 0, 2 * sizeof(unsigned long long)) == cudaSuccess;
     if (ok) {
         memset(e->h_nodes, 0, (size_t)cfg->max_nodes * sizeof(DevNode));
-        e->h_counters[0] = e->h_counters[1] = 0;
+        e->h_counters[0] = e->h_counters[1] = 0; *e->h_flag = 0;
         e->dirty_flag.assign(cfg->max_nodes, 0);
         cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, cfg->device);
         for (int i = 0; i < kgwe_engine::kTimers && ok; ++i) ok = cudaEventCreate(&e->t0[i]) == cudaSuccess && cudaEventCreate(&e->t1[i]) == cudaSuccess;
@@ -345,6 +355,8 @@ int kgwe_engine_destroy(kgwe_engine* e) {
     if (e->h_nodes) cudaFreeHost(e->h_nodes);
     if (e->d_counters) cudaFree(e->d_counters);
     if (e->h_counters) cudaFreeHost(e->h_counters);
+    if (e->d_done) cudaFree(e->d_done);
+    if (e->h_flag) cudaFreeHost(e->h_flag);
     for (int i = 0; i < kgwe_engine::kTimers; ++i) { if (e->t0[i]) cudaEventDestroy(e->t0[i]); if (e->t1[i]) cudaEventDestroy(e->t1[i]); }
     if (e->ev0) cudaEventDestroy(e->ev0);
     if (e->ev1) cudaEventDestroy(e->ev1);
@@ -451,7 +463,7 @@ int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, 
     }
     const uint32_t row = hint_row_bytes(e);
     const bool need_matrix = out_scores || topk > 1;
-    if (!need_matrix && topk == 1 && n_pods <= 32) {
+    if (!need_matrix && topk == 1 && n_pods <= 32 && !(e->cfg.flags & KGWE_CFG_SUBSET_TABLES)) {
         // Latency path (per-pod Prioritize): no copy operations at all.  Pod descriptors, hint rows and
         // placements live in pinned host memory, which the kernels read and write directly over PCIe
         // (unified addressing): two launches and one stream synchronisation per call.
@@ -459,9 +471,21 @@ int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, 
         if (hint) CU(e, e->h_hint.ensure((size_t)32 * row));
         memcpy(e->h_pods.p, pods, (size_t)n_pods * sizeof(kgwe_pod_req));
         if (hint) memcpy(e->h_hint.p, hint, (size_t)n_pods * row);
-        rc = launch_score(e, e->h_pods.p, n_pods, hint ? e->h_hint.p : nullptr, nullptr, 1, e->h_topk.p, s);
+        rc = launch_score(e, e->h_pods.p, n_pods, hint ? e->h_hint.p : nullptr, nullptr, 1, e->h_topk.p, s, false, true);
         if (rc != KGWE_OK) return rc;
-        CU(e, cudaStreamSynchronize(s));
+        // wait for the kernel's flag in pinned memory instead of a stream synchronisation; look at the
+        // stream now and then so a failed launch cannot spin forever
+        volatile unsigned int* flag = e->h_flag;
+        const auto t0 = std::chrono::steady_clock::now();
+        for (uint32_t spins = 0; *flag != e->flag_seq; ++spins) {
+            if ((spins & 0x3fff) == 0x3fff) {
+                const cudaError_t q = cudaStreamQuery(s);
+                if (q == cudaSuccess) { if (*flag != e->flag_seq) return fail(e, KGWE_ERR_CUDA, "latency path: kernel finished without raising its flag (flag %u, expected %u)", *flag, e->flag_seq); break; }
+                if (q != cudaErrorNotReady) return fail(e, KGWE_ERR_CUDA, "latency path: %s", cudaGetErrorString(q));
+                if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > 5.0)
+                    return fail(e, KGWE_ERR_CUDA, "latency path: no answer from the GPU after 5 s (flag %u, expected %u)", *flag, e->flag_seq);
+            }
+        }
         memcpy(out_topk, e->h_topk.p, (size_t)n_pods * sizeof(kgwe_placement));
         e->stats.h2d_bytes += (uint64_t)n_pods * sizeof(kgwe_pod_req) + (hint ? (uint64_t)n_pods * row : 0);
         e->stats.d2h_bytes += (uint64_t)n_pods * sizeof(kgwe_placement);
@@ -920,7 +944,7 @@ extern "C" int kgwe_score_top1_noalloc(kgwe_engine* e, const kgwe_pod_req* d_pod
     uint32_t ppc = std::min<uint32_t>((n_pods + chunks - 1) / chunks, MAX_PODS_PER_CHUNK);
     chunks = (n_pods + ppc - 1) / ppc;
     score_kernel<false, false><<<dim3(n_tiles, chunks), SCORE_THREADS, score_smem_bytes(ppc), s>>>(
-        e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e), d_out, keys, e->params, e->d_counters);
+        e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e), d_out, keys, e->params, e->d_counters, FusedTail{nullptr, nullptr, nullptr, 0});
     CU(e, cudaGetLastError());
     finalize_top1_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), keys, d_top1, 1, e->params);
     CU(e, cudaGetLastError());

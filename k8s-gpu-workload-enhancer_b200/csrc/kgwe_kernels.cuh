@@ -69,6 +69,27 @@ __device__ __forceinline__ void store_no_placement(kgwe_placement* dst) {
     *dst = pl;
 }
 
+// K1b: one 8-lane group per pod.  Re-evaluates the winning (pod,node) to recover its GPU
+// list, adds EstimatedBandwidth, and clears the key slot for the next call.
+__device__ __forceinline__ void finalize_one(const DevNode* __restrict__ nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods,
+                                             uint32_t p, bool live, const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
+                                             unsigned long long* best, kgwe_placement* out, const Params& P, int lane) {
+    unsigned long long key = live ? *reinterpret_cast<volatile unsigned long long*>(&best[p]) : 0ull;
+    const uint32_t node = key ? key_node(key) - P.node_base : 0;
+    kgwe_pod_req pod;
+    if (live) pod = load_pod(pods, p); else { pod = kgwe_pod_req{}; }
+    const DevNode* rec = nodes + node;
+    NodeCtx nc;
+    node_ctx_init(nc, rec, live && key != 0ull && node < n_nodes);
+    EvalOut o;
+    evaluate<false>(rec, nc, pod, P, live && hint_bit(hint, hint_row_bytes, p, node), lane, o);
+    if (live && (lane & 7) == 0) {
+        if (key == 0ull) store_no_placement(out + p);
+        else store_placement(out + p, P.node_base + node, o, est_bandwidth(rec, o.order, (int)((o.order >> 24) & 15)));
+        best[p] = 0ull;
+    }
+}
+
 // ---------------------------------------------------------------------------------------
 // K1.  dynamic smem: [tile: 64 x 768 B][fast: 64 x 288 B][ctx: 64 x NodeCtx][keys: pods_per_chunk x 8 B][mbarrier]
 //
@@ -99,13 +120,15 @@ __device__ __forceinline__ int subset_off(int k) {      // first table slot of p
 // brute-force rate because the group search is then shared between pods.
 //   extra smem with MEMO: [winners: 64 nodes x 8 x (key, pay)] = 4 KB
 constexpr int MEMO_SMEM_BYTES = TILE_NODES * 8 * 8;
+// Optional fused finalisation for the latency path: out != nullptr enables it.
+struct FusedTail { kgwe_placement* out; unsigned int* done; unsigned int* flag; unsigned int seq; };
 template <bool TABLES, bool MEMO>
 __global__ void __launch_bounds__(SCORE_THREADS, TABLES ? 1 : 2)
 score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
              const kgwe_pod_req* __restrict__ pods, uint32_t n_pods, uint32_t pods_per_chunk,
              const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
              kgwe_node_score* __restrict__ out, unsigned long long* __restrict__ best,
-             Params P, unsigned long long* __restrict__ counters) {
+             Params P, unsigned long long* __restrict__ counters, FusedTail tail) {
     extern __shared__ __align__(128) unsigned char smem[];
     DevNode* tile = reinterpret_cast<DevNode*>(smem);
     NodeFast* fast = reinterpret_cast<NodeFast*>(smem + TILE_NODES * sizeof(DevNode));
@@ -295,31 +318,30 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         for (uint32_t i = tid; i < p_end - p_begin; i += SCORE_THREADS)
             if (keys[i]) atomicMax(&best[p_begin + i], keys[i]);
     }
+    if (tail.out) {
+        // latency path (n_pods <= 64): the last CTA to finish turns the keys into placements in the
+        // same launch and raises the host-visible flag (threadfence-reduction pattern)
+        __shared__ unsigned int ticket;
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) ticket = atomicAdd(tail.done, 1u);
+        __syncthreads();
+        if (ticket == gridDim.x * gridDim.y - 1) {
+            __threadfence();
+            finalize_one(nodes, n_nodes, pods, (uint32_t)grp, (uint32_t)grp < n_pods, hint, hint_row_bytes, best, tail.out, P, lane);
+            __threadfence_system();
+            __syncthreads();
+            if (tid == 0) { *tail.done = 0u; *reinterpret_cast<volatile unsigned int*>(tail.flag) = tail.seq; }
+        }
+    }
 }
 
-// K1b: one 8-lane group per pod.  Re-evaluates the winning (pod,node) to recover its GPU
-// list, adds EstimatedBandwidth, and clears the key slot for the next call.
 __global__ void __launch_bounds__(256)
 finalize_top1_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
                      const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
                      unsigned long long* __restrict__ best, kgwe_placement* __restrict__ out, uint32_t out_stride, Params P) {
-    const int lane = threadIdx.x & 31;
     const uint32_t p = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
-    const bool live = p < n_pods;
-    unsigned long long key = live ? best[p] : 0ull;
-    const uint32_t node = key ? key_node(key) - P.node_base : 0;
-    kgwe_pod_req pod;
-    if (live) pod = load_pod(pods, p); else { pod = kgwe_pod_req{}; }
-    const DevNode* rec = nodes + node;
-    NodeCtx nc;
-    node_ctx_init(nc, rec, live && key != 0ull && node < n_nodes);
-    EvalOut o;
-    evaluate<false>(rec, nc, pod, P, live && hint_bit(hint, hint_row_bytes, p, node), lane, o);
-    if (live && (lane & 7) == 0) {
-        if (key == 0ull) store_no_placement(out + (size_t)p * out_stride);
-        else store_placement(out + (size_t)p * out_stride, P.node_base + node, o, est_bandwidth(rec, o.order, (int)((o.order >> 24) & 15)));
-        best[p] = 0ull;
-    }
+    finalize_one(nodes, n_nodes, pods, p, p < n_pods, hint, hint_row_bytes, best, out, P, threadIdx.x & 31);
 }
 
 // K2: one CTA per pod over that pod's row of the score matrix.

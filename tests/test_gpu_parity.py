@@ -414,3 +414,32 @@ def test_mig_pack_and_rebalance_extension(kg, orc):
     assert np.array_equal(occ.astype(np.uint8), g_after["occ"])
     # a failed request really had no fit at that moment is covered by the oracle parity above
     eng.close()
+
+
+def test_latency_path_small_batches(kg, orc):
+    """Per-pod Prioritize calls (<= 32 pods, top-1 only) take the zero-copy single-launch path:
+    pods of different preferences side by side (lane groups of one warp on different branches),
+    with and without hints, after incremental updates, many calls in a row."""
+    abi, synth = kg.abi, kg.synth
+    for num, scale in ((1, 1.0), (2, 0.15), (3, 0.03)):
+        nodes, pods, led = synth.config(num, scale)
+        pods = pods[:96].copy()
+        pods["topology_pref"] = np.arange(len(pods)) % 5                   # every preference, interleaved
+        pods["gpu_count"] = 1 + (np.arange(len(pods)) * 7) % 9            # 1..9 (9 never fits)
+        hint = synth.make_hint(len(pods), len(nodes), 0.05)
+        eng = engine_for(kg, nodes, led)
+        _, want, _ = orc.score_batch(abi, nodes, led, pods, hint=hint, want_scores=False, topk=1)
+        _, want_nohint, _ = orc.score_batch(abi, nodes, led, pods, want_scores=False, topk=1)
+        for size in (1, 3, 8, 32):
+            for p0 in range(0, len(pods) - size + 1, size):
+                _, got = eng.score_batch(pods[p0:p0 + size], len(nodes), hint=hint[p0:p0 + size], want_scores=False, topk=1)
+                assert_same_placements(got, want[p0:p0 + size])
+        _, got = eng.score_batch(pods[:17], len(nodes), want_scores=False, topk=1)
+        assert_same_placements(got, want_nohint[:17])
+        # a commit between two calls is seen by the next call
+        eng.commit(999_999, 1, 0x0F)
+        led2 = np.concatenate([led, ledger_of(abi, [(999_999, 1, 0x0F)])])
+        _, got = eng.score_batch(pods[:9], len(nodes), want_scores=False, topk=1)
+        _, want2, _ = orc.score_batch(abi, nodes, led2, pods[:9], want_scores=False, topk=1)
+        assert_same_placements(got, want2)
+        eng.close()
