@@ -118,10 +118,15 @@ typedef struct kgwe_node_image {
     uint8_t  healthy_mask;                         /* bit i: Health.Status == "Healthy" (scheduler.go:597) */
     uint8_t  allocated_mask;                       /* ENGINE-OWNED: GPUs named by ledger entries on this node; ignored on upsert */
     uint8_t  flags;                                /* bit0: record present (ENGINE-OWNED) */
-    uint8_t  pad0[2];
+    uint8_t  mig_enabled_mask;                     /* bit i: GPU i has MIGConfig != nil && Enabled (discovery.go:442) */
+    uint8_t  mig_has_free_mask;                    /* bit i: ... and at least one instance with !InUse (discovery.go:444-449) */
     uint32_t n_allocs;                             /* ENGINE-OWNED: ledger entries (workloads) on this node (scheduler.go:561-566) */
-    uint32_t pad1;
+    uint8_t  node_flags;                           /* KGWE_NODE_* (read by the hint scorer / exporter gauge only) */
+    uint8_t  pad1[3];
 } kgwe_node_image;
+
+#define KGWE_NODE_NVSWITCH    0x01   /* NVSwitchInfo != nil && Present (prometheus_exporter.go:526) */
+#define KGWE_NODE_ANY_NVLINK  0x02   /* some GPU has at least one NVLinkConnections entry, on- or off-node (prometheus_exporter.go:531-536) */
 
 /* One pending workload: the fields of GPUWorkload.Requirements the path reads
  * (src/scheduler/types.go:36-57,80-89).  32 bytes. */
@@ -340,6 +345,38 @@ int kgwe_mig_pack(kgwe_engine* e, kgwe_mig_gpu* gpus, uint32_t n_gpus, const uin
 typedef struct kgwe_mig_op { uint32_t gpu_idx; uint8_t profile, start, size, pad; } kgwe_mig_op;
 int kgwe_mig_rebalance(kgwe_engine* e, const kgwe_mig_gpu* gpus, uint32_t n_gpus, const double* target /*[10]*/,
                        kgwe_mig_op* ops, uint32_t ops_cap, uint32_t* n_ops, uint32_t* supply /*[10]*/);
+
+/* DiscoveryService.GetTopologyHint (src/discovery/discovery.go:222-247) - the reference's second
+ * node-parallel scorer, over the same image ("next" row 8f.3).  Per request: every node is scored
+ * by scoreNodeForRequirements (discovery.go:378-434: availability rule :436-460 - healthy and
+ * either a free MIG instance or GPUPercent < 90 -, free-memory filter, base 50, +30 when
+ * findNVLinkGroups (:462-488) finds a GPU with Count-1 linked peers among the filtered GPUs, +10
+ * same NUMA, +5 per selected GPU of the wanted architecture) and the best node wins
+ * (score > best, :231).  Canonical order: lowest node index on ties, peers of a GPU in ascending
+ * GPU index (Go iterates a map there).  out[i].node_idx == KGWE_NO_NODE <=> "no suitable placement
+ * found for requirements" (:241).  The ledger is not consulted (the reference does not either). */
+typedef struct kgwe_hint_req {
+    int32_t count;             /* GPURequirements.Count */
+    int32_t min_memory_gb;     /* MinMemoryGB */
+    uint8_t prefer_nvlink;     /* PreferNVLink */
+    uint8_t prefer_same_numa;  /* PreferSameNUMA */
+    uint8_t arch;              /* Architecture, KGWE_ARCH_ANY = "" */
+    uint8_t pad[5];
+} kgwe_hint_req;
+typedef struct kgwe_topology_hint {
+    uint32_t node_idx;         /* PreferredNode */
+    int32_t  score;            /* Score */
+    uint32_t order;            /* PreferredGPUs, packed like kgwe_node_score.order */
+    uint8_t  gpu_mask;
+    uint8_t  pad[3];
+    double   bandwidth_estimate;   /* BandwidthEstimate, discovery.go:506-541 */
+} kgwe_topology_hint;
+int kgwe_topology_hint_batch(kgwe_engine* e, const kgwe_hint_req* reqs, uint32_t n_reqs, kgwe_topology_hint* out);
+
+/* PrometheusExporter.calculateTopologyScore per node (src/monitoring/prometheus_exporter.go:517-539,
+ * "next" row 8f.4): 0 without GPUs, else min(100, 50 + 30 NVSwitch + 20 any NVLink entry).
+ * out gets one int32 per record 0..n_nodes-1 (absent records: 0). */
+int kgwe_topology_gauges(kgwe_engine* e, int32_t* out, uint32_t n_nodes);
 
 /* Read one record back (device -> host) in ABI layout, ledger fields included. */
 int kgwe_node_read(kgwe_engine* e, uint32_t local_idx, kgwe_node_image* out);

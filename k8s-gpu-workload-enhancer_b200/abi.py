@@ -34,8 +34,12 @@ NODE_IMAGE = np.dtype([
     ("nvl_present", "u1", (MAX_GPUS,)), ("nvl_active", "u1", (MAX_GPUS,)),
     ("numa", "i1", (MAX_GPUS,)), ("pcie_switch", "u1", (MAX_GPUS,)), ("arch", "u1", (MAX_GPUS,)),
     ("mig_free", "u1", (MIG_PROFILES,)), ("n_gpus", "u1"), ("healthy_mask", "u1"),
-    ("allocated_mask", "u1"), ("flags", "u1"), ("pad0", "u1", (2,)), ("n_allocs", "<u4"), ("pad1", "<u4"),
+    ("allocated_mask", "u1"), ("flags", "u1"), ("mig_enabled_mask", "u1"), ("mig_has_free_mask", "u1"), ("n_allocs", "<u4"),
+    ("node_flags", "u1"), ("pad1", "u1", (3,)),
 ])
+NODE_NVSWITCH, NODE_ANY_NVLINK = 0x01, 0x02
+HINT_REQ = np.dtype([("count", "<i4"), ("min_memory_gb", "<i4"), ("prefer_nvlink", "u1"), ("prefer_same_numa", "u1"), ("arch", "u1"), ("pad", "u1", (5,))])
+TOPOLOGY_HINT = np.dtype([("node_idx", "<u4"), ("score", "<i4"), ("order", "<u4"), ("gpu_mask", "u1"), ("pad", "u1", (3,)), ("bandwidth_estimate", "<f8")])
 POD_REQ = np.dtype([
     ("wl_id", "<u8"), ("gpu_count", "<i4"), ("min_memory_gb", "<i4"), ("min_bandwidth_gbps", "<f8"),
     ("topology_pref", "u1"), ("arch", "u1"), ("mig_profile", "u1"), ("flags", "u1"), ("mig_count", "<i4"),
@@ -51,7 +55,7 @@ PLACEMENT = np.dtype([
 ALLOC = np.dtype([("wl_id", "<u8"), ("node_idx", "<u4"), ("gpu_mask", "u1"), ("pad", "u1", (3,))])
 
 assert NODE_IMAGE.itemsize == 768 and POD_REQ.itemsize == 32 and NODE_SCORE.itemsize == 16
-assert PLACEMENT.itemsize == 32 and ALLOC.itemsize == 16
+assert PLACEMENT.itemsize == 32 and ALLOC.itemsize == 16 and HINT_REQ.itemsize == 16 and TOPOLOGY_HINT.itemsize == 24
 
 
 class Config(C.Structure):
@@ -81,6 +85,7 @@ ENGINE_SYMBOLS = [
     "kgwe_topk_merge_device", "kgwe_schedule_queue", "kgwe_node_read", "kgwe_get_stats", "kgwe_last_error",
     "kgwe_version", "kgwe_score_top1_noalloc", "kgwe_topk_merge_host",
     "kgwe_schedule_gangs", "kgwe_placement_terms", "kgwe_mig_pack", "kgwe_mig_rebalance",
+    "kgwe_topology_hint_batch", "kgwe_topology_gauges",
 ]
 NOALLOC_MAX_PODS = 16384
 
@@ -110,6 +115,8 @@ def load_engine_lib():
     lib.kgwe_score_batch.argtypes = [vp, vp, u32, vp, vp, u32, vp]
     lib.kgwe_score_batch_device.argtypes = [vp, vp, u32, vp, vp, u32, vp, vp]
     lib.kgwe_score_top1_noalloc.argtypes = [vp, vp, u32, vp, vp, vp, vp]
+    lib.kgwe_topology_hint_batch.argtypes = [vp, vp, u32, vp]
+    lib.kgwe_topology_gauges.argtypes = [vp, vp, u32]
     lib.kgwe_mig_pack.argtypes = [vp, vp, u32, vp, u32, vp]
     lib.kgwe_mig_rebalance.argtypes = [vp, vp, u32, vp, vp, u32, C.POINTER(u32), vp]
     lib.kgwe_schedule_gangs.argtypes = [vp, vp, u32, vp, vp, vp]

@@ -37,9 +37,10 @@ struct __align__(16) DevNode {
     uint8_t  arch[8];
     uint8_t  mig_free[KGWE_MIG_PROFILES];
     uint8_t  n_gpus, healthy_mask, allocated_mask, flags;
-    uint8_t  pad0[2];
+    uint8_t  mig_enabled_mask, mig_has_free_mask;
     uint32_t n_allocs;
-    uint32_t pad1;
+    uint8_t  node_flags;
+    uint8_t  pad1[3];
 };
 static_assert(sizeof(DevNode) == 768, "device record must stay 768 bytes");
 static_assert(sizeof(kgwe_node_image) == 768, "ABI record must stay 768 bytes");

@@ -141,6 +141,8 @@ int to_device_record(kgwe_engine* e, const kgwe_node_image& in, DevNode& out) {
     }
     memcpy(out.mig_free, in.mig_free, sizeof out.mig_free);
     out.n_gpus = (uint8_t)ng; out.healthy_mask = in.healthy_mask & gm;
+    out.mig_enabled_mask = in.mig_enabled_mask & gm; out.mig_has_free_mask = in.mig_has_free_mask & in.mig_enabled_mask & gm;
+    out.node_flags = in.node_flags;
     out.flags = NODE_PRESENT | (integral ? NODE_INTEGRAL : 0);
     return KGWE_OK;
 }
@@ -160,6 +162,7 @@ void to_abi_record(const DevNode& in, kgwe_node_image& out) {
     memcpy(out.mig_free, in.mig_free, sizeof out.mig_free);
     out.n_gpus = in.n_gpus; out.healthy_mask = in.healthy_mask; out.allocated_mask = in.allocated_mask;
     out.flags = in.flags & NODE_PRESENT; out.n_allocs = in.n_allocs;
+    out.mig_enabled_mask = in.mig_enabled_mask; out.mig_has_free_mask = in.mig_has_free_mask; out.node_flags = in.node_flags;
 }
 
 void mark_dirty(kgwe_engine* e, uint32_t idx) {
@@ -768,6 +771,67 @@ int kgwe_placement_terms(kgwe_engine* e, const kgwe_placement* placements, uint3
     CU(e, cudaStreamSynchronize(s));
     memcpy(out, e->h_topk.p, (size_t)n * sizeof(kgwe_side_terms));
     e->stats.h2d_bytes += (uint64_t)n * sizeof(kgwe_placement); e->stats.d2h_bytes += (uint64_t)n * sizeof(kgwe_side_terms);
+    return KGWE_OK;
+}
+
+int kgwe_topology_hint_batch(kgwe_engine* e, const kgwe_hint_req* reqs, uint32_t n_reqs, kgwe_topology_hint* out) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (n_reqs && (!reqs || !out)) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    if (n_reqs > 65535u) return fail(e, KGWE_ERR_TOO_LARGE, "at most 65535 hint requests per call");
+    for (uint32_t i = 0; i < n_reqs; ++i)
+        if (reqs[i].min_memory_gb < 0) return fail(e, KGWE_ERR_INVALID_ARG, "request %u: min_memory_gb < 0", i);
+    if (n_reqs == 0) return KGWE_OK;
+    CU(e, cudaSetDevice(e->cfg.device));
+    cudaStream_t s = e->stream;
+    int rc = flush_dirty(e, s);
+    if (rc != KGWE_OK) return rc;
+    static_assert(sizeof(kgwe_hint_req) == 16 && sizeof(kgwe_topology_hint) == 24, "hint ABI sizes");
+    if (e->n_nodes == 0) {
+        for (uint32_t i = 0; i < n_reqs; ++i) { memset(&out[i], 0, sizeof out[i]); out[i].node_idx = KGWE_NO_NODE; }
+        return KGWE_OK;
+    }
+    const size_t bytes_in = (size_t)n_reqs * sizeof(kgwe_hint_req), off_out = (bytes_in + 255) & ~(size_t)255, bytes_out = (size_t)n_reqs * sizeof(kgwe_topology_hint);
+    CU(e, e->d_hint.ensure(off_out + bytes_out)); CU(e, e->h_hint.ensure(off_out + bytes_out));
+    {
+        const size_t had = e->d_best.cap;
+        CU(e, e->d_best.ensure(n_reqs));
+        if (e->d_best.cap != had) CU(e, cudaMemsetAsync(e->d_best.p, 0, e->d_best.cap * sizeof(unsigned long long), s));
+    }
+    memcpy(e->h_hint.p, reqs, bytes_in);
+    CU(e, cudaMemcpyAsync(e->d_hint.p, e->h_hint.p, bytes_in, cudaMemcpyHostToDevice, s));
+    const kgwe_hint_req* d_reqs = reinterpret_cast<const kgwe_hint_req*>(e->d_hint.p);
+    kgwe_topology_hint* d_out = reinterpret_cast<kgwe_topology_hint*>(e->d_hint.p + off_out);
+    hint_score_kernel<<<dim3((e->n_nodes + 255) / 256, n_reqs), 256, 0, s>>>(e->d_nodes, e->n_nodes, e->cfg.node_base, d_reqs, e->d_best.p);
+    CU(e, cudaGetLastError());
+    hint_finalize_kernel<<<(n_reqs + 127) / 128, 128, 0, s>>>(e->d_nodes, e->n_nodes, e->cfg.node_base, d_reqs, n_reqs, e->d_best.p, d_out);
+    CU(e, cudaGetLastError());
+    e->stats.kernel_launches += 2;
+    CU(e, cudaMemcpyAsync(e->h_hint.p + off_out, d_out, bytes_out, cudaMemcpyDeviceToHost, s));
+    CU(e, cudaStreamSynchronize(s));
+    memcpy(out, e->h_hint.p + off_out, bytes_out);
+    e->stats.h2d_bytes += bytes_in; e->stats.d2h_bytes += bytes_out;
+    return KGWE_OK;
+}
+
+int kgwe_topology_gauges(kgwe_engine* e, int32_t* out, uint32_t n_nodes) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (n_nodes && !out) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    if (n_nodes == 0) return KGWE_OK;
+    CU(e, cudaSetDevice(e->cfg.device));
+    cudaStream_t s = e->stream;
+    int rc = flush_dirty(e, s);
+    if (rc != KGWE_OK) return rc;
+    const size_t bytes = (size_t)n_nodes * sizeof(int32_t);
+    CU(e, e->d_hint.ensure(bytes)); CU(e, e->h_hint.ensure(bytes));
+    gauge_kernel<<<(n_nodes + 255) / 256, 256, 0, s>>>(e->d_nodes, std::min(e->n_nodes, e->cfg.max_nodes), reinterpret_cast<int32_t*>(e->d_hint.p), n_nodes);
+    CU(e, cudaGetLastError());
+    e->stats.kernel_launches++;
+    CU(e, cudaMemcpyAsync(e->h_hint.p, e->d_hint.p, bytes, cudaMemcpyDeviceToHost, s));
+    CU(e, cudaStreamSynchronize(s));
+    memcpy(out, e->h_hint.p, bytes);
+    e->stats.d2h_bytes += bytes;
     return KGWE_OK;
 }
 

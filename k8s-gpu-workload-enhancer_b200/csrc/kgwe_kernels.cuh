@@ -635,6 +635,110 @@ schedule_tile_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __res
 }
 
 // ---------------------------------------------------------------------------------------
+// K5: DiscoveryService.GetTopologyHint (discovery.go:222-247, 378-488).  One thread per
+// (request, node): a handful of mask operations; block max of score << 32 | ~node, one atomicMax
+// per request per block; the winners are turned into hints by hint_finalize_kernel.
+struct HintEval { int score; uint32_t mask, order; int n; };
+
+__device__ __forceinline__ HintEval hint_eval(const DevNode* rec, bool in_range, const kgwe_hint_req& rq) {
+    HintEval h{0, 0, 0, 0};
+    if (!in_range || !(rec->flags & NODE_PRESENT)) return h;
+    const uint32_t ng = rec->n_gpus > 8 ? 8 : rec->n_gpus;
+    const uint32_t all = (1u << ng) - 1u;
+    // getAvailableGPUs, discovery.go:436-460: healthy and (MIG enabled ? a free instance : GPUPercent < 90)
+    uint32_t avail = 0;
+    for (uint32_t g = 0; g < ng; ++g) {
+        if (!(rec->healthy_mask >> g & 1)) continue;
+        const bool ok = (rec->mig_enabled_mask >> g & 1) ? (rec->mig_has_free_mask >> g & 1) : (rec->util[g] < 90.0);
+        if (ok) avail |= 1u << g;
+    }
+    const int count = rq.count;
+    if ((int)__popc(avail) < count) return h;                                   // :380-382
+    uint32_t filt = 0;                                                           // :385-391
+    for (uint32_t g = 0; g < ng; ++g)
+        if ((avail >> g & 1) && (long long)(rec->free_bytes[g] >> 30) >= (long long)rq.min_memory_gb) filt |= 1u << g;
+    if ((int)__popc(filt) < count) return h;                                    // :393-395
+    int score = 50; uint32_t mask = 0, order = 0; int n = 0;
+    if (count > 1 && rq.prefer_nvlink) {                                         // :402-409 + findNVLinkGroups :462-488
+        uint32_t m = filt;
+        while (m) {
+            const int g = __ffs(m) - 1; m &= m - 1;
+            const uint32_t peers = rec->present[g] & filt & all & ~(1u << g);    // any link entry, active or not
+            if ((int)__popc(peers) >= count - 1) {
+                uint32_t s2, o2;
+                take_first_k(peers, count - 1, s2, o2);
+                mask = s2 | (1u << g); order = (uint32_t)g | (o2 << 3); n = count;
+                score += 30;
+                break;
+            }
+        }
+    }
+    if (n == 0) {                                                                // :411-415
+        const int want = count < 0 ? 0 : count;
+        take_first_k(filt, want > 8 ? 8 : want, mask, order); n = __popc(mask);
+    }
+    if (rq.prefer_same_numa) {                                                   // :418-420, areOnSameNUMA :490-504
+        bool same = true; int first = -1000;
+        for (uint32_t g = 0; g < ng; ++g) if (mask >> g & 1) { if (first == -1000) first = rec->numa[g]; else if (rec->numa[g] != first) same = false; }
+        if (same) score += 10;
+    }
+    if (rq.arch != KGWE_ARCH_ANY)                                                // :423-431
+        for (uint32_t g = 0; g < ng; ++g) if ((mask >> g & 1) && rec->arch[g] == rq.arch) score += 5;
+    h.score = score; h.mask = mask; h.order = order | ((uint32_t)n << 24); h.n = n;
+    return h;
+}
+
+__global__ void __launch_bounds__(256)
+hint_score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, uint32_t node_base, const kgwe_hint_req* __restrict__ reqs,
+                  unsigned long long* __restrict__ best) {
+    __shared__ unsigned long long wmax[8];
+    const uint32_t node = blockIdx.x * blockDim.x + threadIdx.x;
+    const kgwe_hint_req rq = reqs[blockIdx.y];
+    const HintEval h = hint_eval(nodes + node, node < n_nodes, rq);
+    unsigned long long key = h.score > 0 ? rank_key(h.score, node_base + node) : 0ull;   // score > hint.Score(0), lowest index on ties
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) { const unsigned long long o = __shfl_xor_sync(0xffffffffu, key, off); key = o > key ? o : key; }
+    if ((threadIdx.x & 31) == 0) wmax[threadIdx.x >> 5] = key;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long b = wmax[0];
+        for (int w = 1; w < 8; ++w) b = wmax[w] > b ? wmax[w] : b;
+        if (b) atomicMax(&best[blockIdx.y], b);
+    }
+}
+
+__global__ void __launch_bounds__(128)
+hint_finalize_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, uint32_t node_base, const kgwe_hint_req* __restrict__ reqs, uint32_t n_reqs,
+                     unsigned long long* __restrict__ best, kgwe_topology_hint* __restrict__ out) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_reqs) return;
+    const unsigned long long key = best[r];
+    best[r] = 0ull;
+    kgwe_topology_hint t;
+    t.node_idx = KGWE_NO_NODE; t.score = 0; t.order = 0; t.gpu_mask = 0; t.pad[0] = t.pad[1] = t.pad[2] = 0; t.bandwidth_estimate = 0.0;
+    if (key) {
+        const uint32_t node = key_node(key) - node_base;
+        const HintEval h = hint_eval(nodes + node, node < n_nodes, reqs[r]);
+        t.node_idx = node_base + node; t.score = h.score; t.order = h.order; t.gpu_mask = (uint8_t)h.mask;
+        t.bandwidth_estimate = est_bandwidth(nodes + node, h.order, h.n);          // discovery.go:506-541
+    }
+    out[r] = t;
+}
+
+// K6: the exporter's per-node topology gauge (prometheus_exporter.go:517-539).
+__global__ void __launch_bounds__(256)
+gauge_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, int32_t* __restrict__ out, uint32_t n_out) {
+    const uint32_t node = blockIdx.x * blockDim.x + threadIdx.x;
+    if (node >= n_out) return;
+    int score = 0;
+    if (node < n_nodes && (nodes[node].flags & NODE_PRESENT) && nodes[node].n_gpus > 0) {
+        score = 50 + ((nodes[node].node_flags & KGWE_NODE_NVSWITCH) ? 30 : 0) + ((nodes[node].node_flags & KGWE_NODE_ANY_NVLINK) ? 20 : 0);
+        score = score > 100 ? 100 : score;
+    }
+    out[node] = score;
+}
+
+// ---------------------------------------------------------------------------------------
 // E4 side terms: one warp per placement.  Lanes split the 2^k subsets (bisection) and the
 // (k-1)! cyclic orders (ring); warp-shuffle min / max at the end.  Cut sums are accumulated
 // per lane in ascending (a, b) order, so the result does not depend on the lane split.

@@ -139,6 +139,19 @@ class Engine:
         self._check(self.lib.kgwe_mig_rebalance(self.h, abi.ptr(gpus), len(gpus), abi.ptr(target), abi.ptr(ops), cap, C.byref(n), abi.ptr(supply)))
         return ops[: min(n.value, cap)].copy(), supply, n.value
 
+    def topology_hints(self, reqs):
+        """DiscoveryService.GetTopologyHint for each request (discovery.go:222-247)."""
+        reqs = np.ascontiguousarray(reqs, dtype=abi.HINT_REQ)
+        out = np.zeros(len(reqs), dtype=abi.TOPOLOGY_HINT)
+        self._check(self.lib.kgwe_topology_hint_batch(self.h, abi.ptr(reqs), len(reqs), abi.ptr(out)))
+        return out
+
+    def topology_gauges(self, n_nodes):
+        """PrometheusExporter.calculateTopologyScore per node (prometheus_exporter.go:517-539)."""
+        out = np.zeros(n_nodes, dtype=np.int32)
+        self._check(self.lib.kgwe_topology_gauges(self.h, abi.ptr(out), n_nodes))
+        return out
+
     def stats(self):
         s = abi.Stats()
         self._check(self.lib.kgwe_get_stats(self.h, C.byref(s)))

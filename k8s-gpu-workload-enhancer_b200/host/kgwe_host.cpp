@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdio>
 #include <cstring>
 #include <mutex>
 #include <set>
@@ -63,6 +64,7 @@ std::string PackNode(const NodeTopology& node, PackedNode* out) {
     std::unordered_map<std::string, uint8_t> sw;
     unsigned mig_free[KGWE_MIG_PROFILES] = {0};
     im.n_gpus = (uint8_t)node.GPUs.size();
+    if (node.NVSwitchPresent) im.node_flags |= KGWE_NODE_NVSWITCH;
     for (size_t i = 0; i < node.GPUs.size(); ++i) {
         const GPUDevice& g = node.GPUs[i];
         for (auto& kv : g.Topology.NVLinkConnections) {
@@ -81,6 +83,11 @@ std::string PackNode(const NodeTopology& node, PackedNode* out) {
         im.numa[i] = (int8_t)numa_rank[g.Topology.NUMANode];
         im.arch[i] = ArchCode(g.Architecture);
         if (g.HealthStatus == "Healthy") im.healthy_mask |= (uint8_t)(1u << i);
+        if (!g.Topology.NVLinkConnections.empty()) im.node_flags |= KGWE_NODE_ANY_NVLINK;
+        if (g.MIGConfig && g.MIGConfig->Enabled) {
+            im.mig_enabled_mask |= (uint8_t)(1u << i);
+            for (auto& inst : g.MIGConfig->CurrentInstances) if (!inst.InUse) im.mig_has_free_mask |= (uint8_t)(1u << i);
+        }
         if (g.MIGConfig && g.MIGConfig->Enabled)
             for (auto& inst : g.MIGConfig->CurrentInstances) {
                 const uint8_t p = MIGProfileCode(inst.Profile.Name);
@@ -240,6 +247,32 @@ std::vector<Result<SchedulingDecision>> TopologyAwareScheduler::ScheduleBurst(co
         events_.push_back(SchedulingEvent{"Scheduled", ws[i].UID, std::make_shared<SchedulingDecision>(out[i].value), ""});
     }
     return out;
+}
+
+Result<TopologyHint> TopologyAwareScheduler::GetTopologyHint(const HintRequirements& req) {
+    Result<TopologyHint> r;
+    kgwe_hint_req q; memset(&q, 0, sizeof q);
+    q.count = req.Count; q.min_memory_gb = req.MinMemoryGB; q.prefer_nvlink = req.PreferNVLink; q.prefer_same_numa = req.PreferSameNUMA;
+    q.arch = req.Architecture.empty() ? (uint8_t)KGWE_ARCH_ANY : ArchCode(req.Architecture);
+    kgwe_topology_hint t;
+    if (kgwe_topology_hint_batch(engine_, &q, 1, &t) != KGWE_OK) { r.error = kgwe_last_error(engine_); return r; }
+    if (t.node_idx == KGWE_NO_NODE) { r.error = "no suitable placement found for requirements"; return r; }     // discovery.go:241
+    r.value.PreferredNode = node_names_[t.node_idx]; r.value.Score = t.score; r.value.BandwidthEstimate = t.bandwidth_estimate;
+    for (int g : order_list(t.order)) r.value.PreferredGPUs.push_back(node_uuids_[t.node_idx][g]);
+    // explainPlacement, discovery.go:544-558
+    if (t.score >= 80) r.value.Reasons.push_back("Optimal NVLink connectivity between selected GPUs");
+    else if (t.score >= 60) r.value.Reasons.push_back("Good topology placement with partial NVLink connectivity");
+    else r.value.Reasons.push_back("PCIe-based connectivity (NVLink not available)");
+    if (t.bandwidth_estimate > 500) { char b[64]; snprintf(b, sizeof b, "High aggregate bandwidth: %.0f GB/s", t.bandwidth_estimate); r.value.Reasons.push_back(b); }
+    return r;
+}
+
+Result<std::map<std::string, int>> TopologyAwareScheduler::TopologyScores() {
+    Result<std::map<std::string, int>> r;
+    std::vector<int32_t> v(node_names_.size());
+    if (!v.empty() && kgwe_topology_gauges(engine_, v.data(), (uint32_t)v.size()) != KGWE_OK) { r.error = kgwe_last_error(engine_); return r; }
+    for (size_t i = 0; i < v.size(); ++i) if (!node_names_[i].empty()) r.value[node_names_[i]] = v[i];
+    return r;
 }
 
 std::string TopologyAwareScheduler::ReleaseAllocation(const std::string& uid) {

@@ -38,7 +38,7 @@ struct GPUDevice {
     DeviceTopology Topology;
     std::shared_ptr<MIGConfiguration> MIGConfig;   // nil-able, like the Go pointer
 };
-struct NodeTopology { std::string NodeName; std::vector<GPUDevice> GPUs; };
+struct NodeTopology { std::string NodeName; std::vector<GPUDevice> GPUs; bool NVSwitchPresent = false; /* NVSwitchInfo != nil && Present */ };
 
 // ---- scheduler types ----
 struct MIGRequirements { std::string Profile; int Count = 0; };
@@ -69,6 +69,11 @@ struct SchedulerConfig {     // DefaultSchedulerConfig(), types.go:379-392
 };
 struct SchedulingEvent { std::string Type, WorkloadUID; std::shared_ptr<SchedulingDecision> Decision; std::string Error; };
 
+// discovery.GPURequirements / TopologyHint (src/discovery/discovery.go:250-281, src/discovery/types.go TopologyHint):
+// the request and answer of DiscoveryService.GetTopologyHint (discovery.go:222-247).
+struct HintRequirements { int Count = 0; int MinMemoryGB = 0; bool PreferNVLink = false; bool PreferSameNUMA = false; std::string Architecture; };
+struct TopologyHint { std::string PreferredNode; std::vector<std::string> PreferredGPUs; int Score = 0; double BandwidthEstimate = 0; std::vector<std::string> Reasons; };
+
 // Go-style (value, error) result: ok() == (err == nil).
 template <typename T>
 struct Result { T value; std::string error; bool ok() const { return error.empty(); } };
@@ -98,6 +103,9 @@ public:
     // scoreNodes + descending sort (scheduler.go:137-146), best `topk` nodes.
     Result<std::vector<NodeScore>> ScoreNodes(const GPUWorkload& workload, const PlacementHint* hint, uint32_t topk);
     std::string ReleaseAllocation(const std::string& workloadUID);      // scheduler.go:710-727
+    // DiscoveryService.GetTopologyHint (discovery.go:222-247) and the exporter's per-node gauge (prometheus_exporter.go:517-539)
+    Result<TopologyHint> GetTopologyHint(const HintRequirements& req);
+    Result<std::map<std::string, int>> TopologyScores();
     SchedulerMetrics GetMetrics() const { return metrics_; }            // scheduler.go:793
     std::deque<SchedulingEvent>& Events() { return events_; }           // scheduler.go:800 (a queue instead of a channel)
 

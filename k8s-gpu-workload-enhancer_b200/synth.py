@@ -97,8 +97,25 @@ def make_cluster(n_nodes, kind="mixed", seed=SEED_BASE, unhealthy_frac=0.02, ina
         cnt = rng.randint(0, 7, N * abi.MIG_PROFILES).reshape(N, abi.MIG_PROFILES)
         sparse = rng.uniform(N * abi.MIG_PROFILES).reshape(N, abi.MIG_PROFILES) < 0.4
         nodes["mig_free"] = np.where(has[:, None] & sparse, cnt, 0).astype(np.uint8)
+        en = rng.uniform(N * 8).reshape(N, 8) < 0.3
+        fr = rng.uniform(N * 8).reshape(N, 8) < 0.6
+        nodes["mig_enabled_mask"] = _mask_bits(has[:, None] & en & gvalid)
+        nodes["mig_has_free_mask"] = _mask_bits(has[:, None] & en & fr & gvalid)
+    nodes["node_flags"] = (np.where(cube | (n_gpus < 8), 0, abi.NODE_NVSWITCH) | np.where(adj.any(axis=(1, 2)), abi.NODE_ANY_NVLINK, 0)).astype(np.uint8)
     nodes["flags"] = 1
     return nodes
+
+
+def make_hint_reqs(n, seed=SEED_BASE):
+    """discovery.GPURequirements for GetTopologyHint (discovery.go:250-281), the fields it reads."""
+    rng = SplitMix64(seed ^ 0x48494E54)
+    r = np.zeros(n, dtype=abi.HINT_REQ)
+    r["count"] = rng.randint(0, 9, n)
+    r["min_memory_gb"] = np.array([0, 16, 40, 80, 120])[rng.randint(0, 4, n)]
+    r["prefer_nvlink"] = rng.randint(0, 1, n)
+    r["prefer_same_numa"] = rng.randint(0, 1, n)
+    r["arch"] = np.array([abi.ARCH_ANY, abi.ARCH_HOPPER, abi.ARCH_AMPERE, abi.ARCH_BLACKWELL], dtype=np.uint8)[rng.randint(0, 3, n)]
+    return r
 
 
 def make_pods(n_pods, seed=SEED_BASE, k_lo=1, k_hi=8, pref_probs=(0.2, 0.5, 0.0, 0.2, 0.1), arch_frac=0.0,

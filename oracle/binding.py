@@ -28,6 +28,8 @@ def lib():
         _lib = C.CDLL(LIB_PATH)
         vp, u32 = C.c_void_p, C.c_uint32
         _lib.kgwe_oracle_score_batch.argtypes = [vp, vp, u32, vp, u32, vp, u32, vp, vp, u32, vp, C.c_int, C.c_int, C.POINTER(Counters)]
+        _lib.kgwe_oracle_topology_hints.argtypes = [vp, vp, u32, vp, u32, vp]
+        _lib.kgwe_oracle_topology_gauges.argtypes = [vp, u32, vp]
         _lib.kgwe_oracle_mig_pack.argtypes = [vp, u32, vp, u32, vp]
         _lib.kgwe_oracle_mig_rebalance.argtypes = [vp, u32, vp, vp, u32, C.POINTER(u32), vp]
         _lib.kgwe_oracle_schedule_gangs.argtypes = [vp, vp, u32, vp, u32, vp, u32, vp, vp, vp, vp, C.POINTER(u32), C.c_int]
@@ -132,3 +134,23 @@ def mig_rebalance(abi, gpus, target, ops_cap=None):
     if rc != 0:
         raise RuntimeError(f"oracle error {rc}")
     return ops[: min(n.value, cap)].copy(), supply, n.value
+
+
+def topology_hints(abi, nodes, reqs, cfg=None):
+    nodes = np.ascontiguousarray(nodes, dtype=abi.NODE_IMAGE)
+    reqs = np.ascontiguousarray(reqs, dtype=abi.HINT_REQ)
+    out = np.zeros(len(reqs), dtype=abi.TOPOLOGY_HINT)
+    cfg = cfg if cfg is not None else abi.default_config(max(1, len(nodes)))
+    rc = lib().kgwe_oracle_topology_hints(C.addressof(cfg), _p(nodes), len(nodes), _p(reqs), len(reqs), _p(out))
+    if rc != 0:
+        raise RuntimeError(f"oracle error {rc}")
+    return out
+
+
+def topology_gauges(abi, nodes):
+    nodes = np.ascontiguousarray(nodes, dtype=abi.NODE_IMAGE)
+    out = np.zeros(len(nodes), dtype=np.int32)
+    rc = lib().kgwe_oracle_topology_gauges(_p(nodes), len(nodes), _p(out))
+    if rc != 0:
+        raise RuntimeError(f"oracle error {rc}")
+    return out

@@ -980,3 +980,98 @@ extern "C" int kgwe_oracle_mig_rebalance(const kgwe_mig_gpu* gpus, uint32_t n_gp
     for (uint32_t i = 0; i < all.size() && i < ops_cap; ++i) ops[i] = all[i];
     return KGWE_OK;
 }
+
+// ---- DiscoveryService.GetTopologyHint, src/discovery/discovery.go:222-247 ----------------------
+namespace hint {
+struct Scored { goint score; std::vector<int> gpus; };
+
+// getAvailableGPUs, discovery.go:436-460
+std::vector<int> getAvailableGPUs(const kgwe_node_image& im) {
+    std::vector<int> available;
+    const int ng = std::min<int>(im.n_gpus, KGWE_MAX_GPUS);
+    for (int g = 0; g < ng; ++g) {
+        if (!(im.healthy_mask >> g & 1)) continue;
+        if (im.mig_enabled_mask >> g & 1) { if (im.mig_has_free_mask >> g & 1) available.push_back(g); }
+        else if (im.util[g] < 90) available.push_back(g);
+    }
+    return available;
+}
+
+// findNVLinkGroups, discovery.go:462-488 (peers of a GPU visited in ascending GPU index: canonical)
+std::vector<std::vector<int>> findNVLinkGroups(const kgwe_node_image& im, const std::vector<int>& gpus, goint size) {
+    std::vector<std::vector<int>> groups;
+    const int ng = std::min<int>(im.n_gpus, KGWE_MAX_GPUS);
+    for (int gpu : gpus) {
+        std::vector<int> group{gpu};
+        for (int peer = 0; peer < ng; ++peer) {
+            if (!(im.nvl_present[gpu] >> peer & 1) || peer == gpu) continue;
+            if ((goint)group.size() >= size) break;
+            if (std::find(gpus.begin(), gpus.end(), peer) != gpus.end()) group.push_back(peer);
+        }
+        if ((goint)group.size() >= size) { group.resize(size); groups.push_back(group); }
+    }
+    return groups;
+}
+
+// scoreNodeForRequirements, discovery.go:378-434
+Scored scoreNodeForRequirements(const kgwe_node_image& im, const kgwe_hint_req& req) {
+    std::vector<int> availableGPUs = getAvailableGPUs(im);
+    if ((goint)availableGPUs.size() < req.count) return {0, {}};
+    std::vector<int> filteredGPUs;
+    for (int g : availableGPUs) {
+        goint memGB = (goint)(im.free_bytes[g] / (1024ull * 1024 * 1024));
+        if (memGB >= req.min_memory_gb) filteredGPUs.push_back(g);
+    }
+    if ((goint)filteredGPUs.size() < req.count) return {0, {}};
+    goint score = 50;
+    std::vector<int> selected;
+    if (req.count > 1 && req.prefer_nvlink) {
+        auto groups = findNVLinkGroups(im, filteredGPUs, req.count);
+        if (!groups.empty()) { score += 30; selected = groups[0]; }
+    }
+    if (selected.empty())
+        for (goint i = 0; i < req.count && i < (goint)filteredGPUs.size(); ++i) selected.push_back(filteredGPUs[i]);
+    if (req.prefer_same_numa) {           // areOnSameNUMA, discovery.go:490-504
+        bool same = true; int numaNode = -1000;
+        for (int g : selected) { if (numaNode == -1000) numaNode = im.numa[g]; else if (numaNode != im.numa[g]) same = false; }
+        if (same) score += 10;
+    }
+    if (req.arch != KGWE_ARCH_ANY)
+        for (int g : selected) if (im.arch[g] == req.arch) score += 5;
+    return {score, selected};
+}
+}  // namespace hint
+
+extern "C" int kgwe_oracle_topology_hints(const kgwe_config* cfg, const kgwe_node_image* nodes, uint32_t n_nodes,
+                                          const kgwe_hint_req* reqs, uint32_t n_reqs, kgwe_topology_hint* out) {
+    if (!nodes || (n_reqs && (!reqs || !out))) return KGWE_ERR_INVALID_ARG;
+    const uint32_t base = cfg ? cfg->node_base : 0;
+    for (uint32_t r = 0; r < n_reqs; ++r) {
+        kgwe_topology_hint t; memset(&t, 0, sizeof t); t.node_idx = KGWE_NO_NODE;
+        goint bestScore = 0; std::vector<int> bestGpus; uint32_t bestNode = 0;
+        for (uint32_t n = 0; n < n_nodes; ++n) {                       // discovery.go:231-238, nodes in index order
+            hint::Scored s = hint::scoreNodeForRequirements(nodes[n], reqs[r]);
+            if (s.score > bestScore) { bestScore = s.score; bestGpus = s.gpus; bestNode = n; }
+        }
+        if (bestScore > 0) {
+            t.node_idx = base + bestNode; t.score = (int32_t)bestScore; t.order = pack_order(bestGpus);
+            for (int g : bestGpus) t.gpu_mask |= (uint8_t)(1u << g);
+            t.bandwidth_estimate = indexed::est_bandwidth(nodes[bestNode], bestGpus);     // discovery.go:506-541 (same formula as scheduler.go:656-692)
+        }
+        out[r] = t;
+    }
+    return KGWE_OK;
+}
+
+// PrometheusExporter.calculateTopologyScore, src/monitoring/prometheus_exporter.go:517-539
+extern "C" int kgwe_oracle_topology_gauges(const kgwe_node_image* nodes, uint32_t n_nodes, int32_t* out) {
+    if (n_nodes && (!nodes || !out)) return KGWE_ERR_INVALID_ARG;
+    for (uint32_t n = 0; n < n_nodes; ++n) {
+        if (nodes[n].n_gpus == 0) { out[n] = 0; continue; }
+        goint score = 50;
+        if (nodes[n].node_flags & KGWE_NODE_NVSWITCH) score += 30;
+        if (nodes[n].node_flags & KGWE_NODE_ANY_NVLINK) score += 20;
+        out[n] = (int32_t)std::min<goint>(100, score);
+    }
+    return KGWE_OK;
+}

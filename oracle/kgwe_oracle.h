@@ -73,6 +73,12 @@ int kgwe_oracle_schedule_gangs(const kgwe_config* cfg,
 int kgwe_oracle_placement_terms(const kgwe_config* cfg, const kgwe_node_image* nodes, uint32_t n_nodes,
                                 const kgwe_placement* placements, uint32_t n, kgwe_side_terms* out);
 
+/* DiscoveryService.GetTopologyHint (src/discovery/discovery.go:222-247, 378-541) and the exporter's
+ * per-node topology gauge (src/monitoring/prometheus_exporter.go:517-539), restated on the image. */
+int kgwe_oracle_topology_hints(const kgwe_config* cfg, const kgwe_node_image* nodes, uint32_t n_nodes,
+                               const kgwe_hint_req* reqs, uint32_t n_reqs, kgwe_topology_hint* out);
+int kgwe_oracle_topology_gauges(const kgwe_node_image* nodes, uint32_t n_nodes, int32_t* out);
+
 /* EXTENSION E2: MIG bin-packing and rebalancing by plain loops (spec in include/kgwe_engine.h). */
 int kgwe_oracle_mig_pack(kgwe_mig_gpu* gpus, uint32_t n_gpus, const uint8_t* profiles, uint32_t n_reqs, kgwe_mig_assignment* out);
 int kgwe_oracle_mig_rebalance(const kgwe_mig_gpu* gpus, uint32_t n_gpus, const double* target,

@@ -19,6 +19,7 @@ inline NodeTopology make_node(int idx, int kind, uint64_t& rng) {
     NodeTopology n;
     char name[32]; snprintf(name, sizeof name, "node-%03d", idx);
     n.NodeName = name;
+    n.NVSwitchPresent = kind != 3;
     const double bw = kind == 0 ? 900.0 : kind == 2 ? 1800.0 : 600.0;
     const char* arch = kind == 0 ? "Hopper" : kind == 2 ? "Blackwell" : "Ampere";
     const int total_gib = kind == 2 ? 180 : 80;

@@ -97,6 +97,26 @@ int main() {
         for (auto& s : hinted.value) if (s.NodeName == plain.value.back().NodeName) { seen = true; CHECK(s.TotalScore == plain.value.back().TotalScore + 10); CHECK(s.Reasons[0] == "ML optimizer preferred this node"); }
         CHECK(seen);
     }
+    // GetTopologyHint / exporter gauge through the mirror, against the oracle on the packed images
+    {
+        HintRequirements hr; hr.Count = 4; hr.MinMemoryGB = 40; hr.PreferNVLink = true; hr.PreferSameNUMA = true; hr.Architecture = "Blackwell";
+        kgwe_hint_req q; memset(&q, 0, sizeof q);
+        q.count = 4; q.min_memory_gb = 40; q.prefer_nvlink = 1; q.prefer_same_numa = 1; q.arch = KGWE_ARCH_BLACKWELL;
+        kgwe_topology_hint t;
+        CHECK(kgwe_oracle_topology_hints(nullptr, images.data(), N, &q, 1, &t) == 0);
+        auto h = S.GetTopologyHint(hr);
+        CHECK(t.node_idx != KGWE_NO_NODE && h.ok());
+        CHECK(h.value.PreferredNode == cluster[t.node_idx].NodeName && h.value.Score == t.score && h.value.BandwidthEstimate == t.bandwidth_estimate);
+        CHECK((int)h.value.PreferredGPUs.size() == 4 && h.value.PreferredGPUs[0] == fixture::uuid((int)t.node_idx, t.order & 7));
+        CHECK(h.value.Reasons[0] == (t.score >= 80 ? "Optimal NVLink connectivity between selected GPUs" : "Good topology placement with partial NVLink connectivity"));
+        hr.Count = 9;
+        CHECK(S.GetTopologyHint(hr).error == "no suitable placement found for requirements");
+        std::vector<int32_t> gauges(N);
+        CHECK(kgwe_oracle_topology_gauges(images.data(), N, gauges.data()) == 0);
+        auto ts = S.TopologyScores();
+        CHECK(ts.ok() && (int)ts.value.size() == N);
+        for (int i = 0; i < N; ++i) CHECK(ts.value[cluster[i].NodeName] == gauges[i]);
+    }
     // node delete event
     CHECK(S.RemoveNode(cluster[0].NodeName).empty() && S.NodeIndex(cluster[0].NodeName) == KGWE_NO_NODE);
     CHECK(!S.RemoveNode(cluster[0].NodeName).empty());

@@ -2,7 +2,7 @@
 values for E4 side terms and E5 gang roll-back."""
 import numpy as np
 
-from helpers import CUBE_EDGES, ledger_of, make_node, make_pod
+from helpers import CUBE_EDGES, ledger_of, make_node, make_pod, order_list
 
 
 def _pl(abi, node, mask):
@@ -95,3 +95,39 @@ def test_mig_rebalance_known_answers(kg, orc):
     assert ops["gpu_idx"][48:].tolist() == [9, 9] and ops["start"][48:].tolist() == [0, 4] and ops["profile"][48] == 6
     # the 40 GB class has no target -> untouched
     assert not (ops["gpu_idx"] >= 10).any()
+
+
+def test_topology_hint_known_answers(kg, orc):
+    """GetTopologyHint (discovery.go:222-247, 378-488), hand-derived: base 50, +30 linked group, +10 same NUMA,
+    +5 per selected GPU of the wanted architecture; availability = healthy and (free MIG instance | util < 90)."""
+    abi = kg.abi
+    busy = make_node(abi, util=[95.0] * 6 + [10.0, 10.0])                 # only GPUs 6,7 are under 90 %
+    cube = make_node(abi, links=CUBE_EDGES, arch=abi.ARCH_AMPERE)
+    small = make_node(abi, free_gib=20)
+    mig = make_node(abi, util=99.0)
+    mig["mig_enabled_mask"], mig["mig_has_free_mask"] = 0x0F, 0x05        # GPUs 0 and 2 have a free instance; 4-7 fail on util
+    nodes = np.array([busy, cube, small, mig], dtype=abi.NODE_IMAGE)
+    def req(count, mem=0, nvl=0, numa=0, arch=0):
+        r = np.zeros(1, dtype=abi.HINT_REQ)
+        r["count"], r["min_memory_gb"], r["prefer_nvlink"], r["prefer_same_numa"], r["arch"] = count, mem, nvl, numa, arch
+        return r
+    def ask(r, nn=nodes):
+        t = orc.topology_hints(abi, nn, r)[0]
+        return int(t["node_idx"]) if t["node_idx"] != abi.NO_NODE else None, int(t["score"]), order_list(t["order"]), float(t["bandwidth_estimate"])
+    # 2 GPUs with NVLink + same NUMA + Hopper: node 0 -> GPUs 6,7 linked, NUMA 1, both Hopper: 50+30+10+10 = 100
+    assert ask(req(2, 40, 1, 1, abi.ARCH_HOPPER)) == (0, 100, [6, 7], 900.0)
+    # 4 GPUs: node 0 has only 2 available; cube node: GPU 0 has 3 linked peers (1,2,4) -> [0,1,2,4], NUMA differs; Ampere wanted: 50+30+20 = 100
+    assert ask(req(4, 40, 1, 1, abi.ARCH_AMPERE)) == (1, 100, [0, 1, 2, 4], (900 * 3 + 64 * 3) / 6)
+    # 5 GPUs on the cube: no GPU has 4 peers -> first 5, no NVLink bonus; node 2 (full mesh, 20 GiB free) wins with 80 when memory allows
+    assert ask(req(5, 16, 1, 0, 0)) == (2, 80, [0, 1, 2, 3, 4], 900.0)
+    assert ask(req(5, 40, 1, 0, 0)) == (1, 50, [0, 1, 2, 3, 4], (900 * 5 + 64 * 5) / 10)     # cube edges among 0..4: 0-1 0-2 0-4 1-3 2-3
+    # MIG rule: node 3's only available GPUs are 0 and 2 (free instances), util does not matter for them
+    assert ask(req(2, 0, 0, 1, 0), nodes[3:]) == (0, 60, [0, 2], 900.0)
+    assert ask(req(3, 0, 0, 0, 0), nodes[3:]) == (None, 0, [], 0.0)       # "no suitable placement found for requirements"
+    # count 1 / 0: no group search; count 0 selects nothing and still scores 50 (+10: an empty set is "same NUMA")
+    assert ask(req(1, 0, 1, 0, 0)) == (0, 50, [6], 0.0)
+    assert ask(req(0, 0, 1, 1, 0)) == (0, 60, [], 0.0)
+    # exporter gauge: 50 base, +30 NVSwitch, +20 any NVLink entry, 0 without GPUs
+    g = np.array([make_node(abi), make_node(abi, links="none"), make_node(abi, n_gpus=0)], dtype=abi.NODE_IMAGE)
+    g["node_flags"] = [abi.NODE_NVSWITCH | abi.NODE_ANY_NVLINK, 0, abi.NODE_NVSWITCH]
+    assert orc.topology_gauges(abi, g).tolist() == [100, 50, 0]

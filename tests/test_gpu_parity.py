@@ -443,3 +443,35 @@ def test_latency_path_small_batches(kg, orc):
         _, want2, _ = orc.score_batch(abi, nodes, led2, pods[:9], want_scores=False, topk=1)
         assert_same_placements(got, want2)
         eng.close()
+
+
+def test_topology_hint_and_gauges(kg, orc):
+    """The reference's second node-parallel scorer (DiscoveryService.GetTopologyHint) and the
+    exporter's per-node gauge, GPU vs the restatement, incl. the hand-derived cases."""
+    abi, synth = kg.abi, kg.synth
+    nodes = synth.make_cluster(3000, "mixed", seed=31, unhealthy_frac=0.1, inactive_link_frac=0.05, partial_node_frac=0.2, mig_frac=0.4)
+    reqs = synth.make_hint_reqs(500, seed=31)
+    eng = engine_for(kg, nodes)
+    got = eng.topology_hints(reqs)
+    want = orc.topology_hints(abi, nodes, reqs)
+    for f in abi.TOPOLOGY_HINT.names:
+        if f == "bandwidth_estimate":
+            np.testing.assert_allclose(got[f], want[f], rtol=REL_TOL, atol=0)
+        else:
+            assert np.array_equal(got[f], want[f]), f
+    assert got.tobytes() == want.tobytes()
+    assert (got["node_idx"] == abi.NO_NODE).any() and (got["score"] >= 90).any()
+    assert np.array_equal(eng.topology_gauges(len(nodes)), orc.topology_gauges(abi, nodes))
+    # an informer update changes the answer
+    nodes2 = nodes.copy()
+    best = int(got[got["node_idx"] != abi.NO_NODE][0]["node_idx"])
+    nodes2[best]["healthy_mask"] = 0
+    eng.upsert_node(best, nodes2[best])
+    assert eng.topology_hints(reqs).tobytes() == orc.topology_hints(abi, nodes2, reqs).tobytes()
+    # sharded engine: global indices
+    e2 = kg.Engine(max_nodes=1000, node_base=2000)
+    e2.upsert_nodes(nodes[2000:])
+    cfg = abi.default_config(1000, node_base=2000)
+    assert e2.topology_hints(reqs[:50]).tobytes() == orc.topology_hints(abi, nodes[2000:], reqs[:50], cfg=cfg).tobytes()
+    assert eng.topology_hints(reqs[:0]).shape == (0,)
+    eng.close(); e2.close()
