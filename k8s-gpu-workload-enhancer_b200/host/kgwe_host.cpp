@@ -275,6 +275,48 @@ Result<std::map<std::string, int>> TopologyAwareScheduler::TopologyScores() {
     return r;
 }
 
+std::string TopologyAwareScheduler::ScoreAll(const GPUWorkload& w, std::vector<kgwe_node_score>* scores) {
+    if (!HasTopology()) return "cluster topology not available";
+    kgwe_stats st;
+    if (kgwe_get_stats(engine_, &st) != KGWE_OK) return kgwe_last_error(engine_);
+    scores->assign(st.n_nodes, kgwe_node_score{});
+    const kgwe_pod_req p = PodReq(w);
+    if (st.n_nodes && kgwe_score_batch(engine_, &p, 1, nullptr, scores->data(), 0, nullptr) != KGWE_OK) return kgwe_last_error(engine_);
+    return "";
+}
+
+ExtenderFilterResult TopologyAwareScheduler::Filter(const GPUWorkload& w, const std::vector<std::string>& names) {
+    ExtenderFilterResult r;
+    std::vector<kgwe_node_score> sc;
+    r.Error = ScoreAll(w, &sc);
+    if (!r.Error.empty()) return r;
+    for (auto& n : names) {
+        const uint32_t i = NodeIndex(n);
+        if (i == KGWE_NO_NODE || i >= sc.size()) { r.FailedNodes[n] = "node not in the GPU topology snapshot"; continue; }
+        if (sc[i].flags & KGWE_F_KEPT) r.NodeNames.push_back(n);
+        else if (sc[i].flags & KGWE_F_MINBW) r.FailedNodes[n] = "inter-GPU bandwidth below the requested minimum";
+        else if (sc[i].flags & KGWE_F_ELIGIBLE) r.FailedNodes[n] = "placement score is not positive";
+        else r.FailedNodes[n] = "not enough available GPUs of the required kind";
+    }
+    return r;
+}
+
+std::vector<HostPriority> TopologyAwareScheduler::Prioritize(const GPUWorkload& w, const std::vector<std::string>& names) {
+    std::vector<HostPriority> out;
+    std::vector<kgwe_node_score> sc;
+    const std::string err = ScoreAll(w, &sc);
+    for (auto& n : names) {
+        HostPriority hp; hp.Host = n;
+        const uint32_t i = NodeIndex(n);
+        if (err.empty() && i != KGWE_NO_NODE && i < sc.size() && (sc[i].flags & KGWE_F_KEPT)) {
+            const int64_t t = std::min<int64_t>(100, std::max<int64_t>(0, sc[i].total));
+            hp.Score = t * MaxExtenderPriority / 100;
+        }
+        out.push_back(hp);
+    }
+    return out;
+}
+
 std::string TopologyAwareScheduler::ReleaseAllocation(const std::string& uid) {
     auto it = wl_id_.find(uid);
     if (it == wl_id_.end() || kgwe_alloc_release(engine_, it->second) != KGWE_OK)

@@ -74,6 +74,14 @@ struct SchedulingEvent { std::string Type, WorkloadUID; std::shared_ptr<Scheduli
 struct HintRequirements { int Count = 0; int MinMemoryGB = 0; bool PreferNVLink = false; bool PreferSameNUMA = false; std::string Architecture; };
 struct TopologyHint { std::string PreferredNode; std::vector<std::string> PreferredGPUs; int Score = 0; double BandwidthEstimate = 0; std::vector<std::string> Reasons; };
 
+// kube-scheduler extender wire types (k8s.io/kube-scheduler/extender/v1: ExtenderFilterResult, HostPriority,
+// MaxExtenderPriority = 10).  The reference only CONFIGURES an extender (verbs filter / prioritize,
+// deploy/helm/kgwe/templates/scheduler-configmap.yaml:61-79) and ships no handler; these are the payloads
+// such handlers would fill from the engine ("next" row 8f.2), without the HTTP/JSON transport.
+struct ExtenderFilterResult { std::vector<std::string> NodeNames; std::map<std::string, std::string> FailedNodes; std::string Error; };
+struct HostPriority { std::string Host; int64_t Score = 0; };
+constexpr int64_t MaxExtenderPriority = 10;
+
 // Go-style (value, error) result: ok() == (err == nil).
 template <typename T>
 struct Result { T value; std::string error; bool ok() const { return error.empty(); } };
@@ -105,6 +113,11 @@ public:
     std::string ReleaseAllocation(const std::string& workloadUID);      // scheduler.go:710-727
     // DiscoveryService.GetTopologyHint (discovery.go:222-247) and the exporter's per-node gauge (prometheus_exporter.go:517-539)
     Result<TopologyHint> GetTopologyHint(const HintRequirements& req);
+    // Extender verbs for one pod over the candidate node names kube-scheduler sends (nodeCacheCapable: false).
+    // filter: keeps the nodes scoreNodes would keep (isNodeEligible and TotalScore > 0, scheduler.go:189-200);
+    // prioritize: TotalScore clamped to 0..100 and scaled to 0..MaxExtenderPriority.
+    ExtenderFilterResult Filter(const GPUWorkload& workload, const std::vector<std::string>& nodeNames);
+    std::vector<HostPriority> Prioritize(const GPUWorkload& workload, const std::vector<std::string>& nodeNames);
     Result<std::map<std::string, int>> TopologyScores();
     SchedulerMetrics GetMetrics() const { return metrics_; }            // scheduler.go:793
     std::deque<SchedulingEvent>& Events() { return events_; }           // scheduler.go:800 (a queue instead of a channel)
@@ -119,6 +132,7 @@ private:
     NodeScore NodeScoreOf(const kgwe_placement& pl) const;
     SchedulingDecision DecisionOf(const GPUWorkload& w, const kgwe_placement& pl) const;
     void UpdateLatency(double ms);
+    std::string ScoreAll(const GPUWorkload& w, std::vector<kgwe_node_score>* scores);
 
     SchedulerConfig cfg_;
     kgwe_engine* engine_ = nullptr;

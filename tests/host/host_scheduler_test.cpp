@@ -2,6 +2,7 @@
 // events) on a struct-form cluster, checked against the CPU oracle run on the packed images.
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <cstring>
 
 #include "../../oracle/kgwe_oracle.h"
@@ -116,6 +117,36 @@ int main() {
         auto ts = S.TopologyScores();
         CHECK(ts.ok() && (int)ts.value.size() == N);
         for (int i = 0; i < N; ++i) CHECK(ts.value[cluster[i].NodeName] == gauges[i]);
+    }
+    // extender verbs: payloads built from the score matrix of one pod
+    {
+        GPUWorkload w = jobs[7]; w.UID = "uid-ext"; w.Name = "ext";
+        kgwe_pod_req q = pod_of(w, 999999);
+        std::vector<kgwe_node_score> want_sc(N);
+        // current ledger = oracle's final ledger minus the released workload
+        std::vector<kgwe_oracle_alloc> cur;
+        for (uint32_t i = 0; i < n_led; ++i) if (led[i].wl_id != (uint64_t)first_placed + 1) cur.push_back(led[i]);
+        CHECK(kgwe_oracle_score_batch(nullptr, images.data(), N, cur.data(), (uint32_t)cur.size(), &q, 1, nullptr, want_sc.data(), 0, nullptr, KGWE_ORACLE_INDEXED, 1, nullptr) == 0);
+        std::vector<std::string> names;
+        for (int i = 0; i < N; i += 2) names.push_back(cluster[i].NodeName);
+        names.push_back("ghost-node");
+        ExtenderFilterResult fr = S.Filter(w, names);
+        CHECK(fr.Error.empty() && fr.FailedNodes.count("ghost-node") == 1);
+        size_t kept = 0;
+        for (int i = 0; i < N; i += 2) {
+            const bool k = want_sc[i].flags & KGWE_F_KEPT;
+            kept += k;
+            CHECK((std::find(fr.NodeNames.begin(), fr.NodeNames.end(), cluster[i].NodeName) != fr.NodeNames.end()) == k);
+            CHECK((fr.FailedNodes.count(cluster[i].NodeName) == 1) == !k);
+        }
+        CHECK(fr.NodeNames.size() == kept);
+        auto pr = S.Prioritize(w, names);
+        CHECK(pr.size() == names.size() && pr.back().Host == "ghost-node" && pr.back().Score == 0);
+        for (size_t x = 0; x + 1 < pr.size(); ++x) {
+            const kgwe_node_score& ws = want_sc[2 * x];
+            const int64_t exp = (ws.flags & KGWE_F_KEPT) ? std::min<int64_t>(100, std::max<int64_t>(0, ws.total)) * 10 / 100 : 0;
+            CHECK(pr[x].Host == cluster[2 * x].NodeName && pr[x].Score == exp && pr[x].Score <= MaxExtenderPriority);
+        }
     }
     // node delete event
     CHECK(S.RemoveNode(cluster[0].NodeName).empty() && S.NodeIndex(cluster[0].NodeName) == KGWE_NO_NODE);
