@@ -475,3 +475,67 @@ def test_topology_hint_and_gauges(kg, orc):
     assert e2.topology_hints(reqs[:50]).tobytes() == orc.topology_hints(abi, nodes[2000:], reqs[:50], cfg=cfg).tobytes()
     assert eng.topology_hints(reqs[:0]).shape == (0,)
     eng.close(); e2.close()
+
+
+def test_non_default_config(kg, orc):
+    """SchedulerConfig weights, hint bonus and the NVLink normalisation are engine parameters
+    (types.go:346-392, scheduler.go:282-286, 368): non-default values, incl. zero and negative weights."""
+    abi, synth = kg.abi, kg.synth
+    nodes, pods, led = synth.config(2, 0.1)
+    pods = synth.make_pods(120, seed=77, arch_frac=0.2)
+    hint = synth.make_hint(len(pods), len(nodes), 0.1)
+    for wt, wr, wb, bonus, norm in ((60, 30, 10, 25, 600.0), (0, 100, 0, 0, 900.0), (100, -20, 50, 7, 1800.0), (33, 33, 34, 1000, 450.5)):
+        cfg = abi.default_config(len(nodes))
+        cfg.topology_weight, cfg.resource_weight, cfg.balance_weight, cfg.hint_bonus, cfg.nvlink_norm_gbps = wt, wr, wb, bonus, norm
+        eng = kg.Engine(max_nodes=len(nodes), config=cfg)
+        eng.upsert_nodes(nodes)
+        eng.seed_ledger(led)
+        s, t = eng.score_batch(pods, len(nodes), hint=hint, want_scores=True, topk=3)
+        o, ot, _ = orc.score_batch(abi, nodes, led, pods, hint=hint, want_scores=True, topk=3, cfg=cfg)
+        assert s.tobytes() == o.tobytes()
+        assert_same_placements(t, ot)
+        d = eng.schedule_queue(pods, hint=hint)
+        od, _, _ = orc.schedule_queue(abi, nodes, led, pods, hint=hint, cfg=cfg)
+        assert_same_placements(d, od)
+        eng.close()
+
+
+def test_concurrent_callers_share_one_engine(kg, orc):
+    """Entry points take the engine's mutex (mirrors s.mu, scheduler.go:17): threads hammering
+    stateless scoring while another thread commits and releases must all get consistent answers."""
+    import threading
+    abi, synth = kg.abi, kg.synth
+    nodes, pods, led = synth.config(2, 0.05)
+    pods = pods[:40]
+    eng = engine_for(kg, nodes, led)
+    _, base, _ = orc.score_batch(abi, nodes, led, pods, want_scores=False, topk=1)
+    led2 = np.concatenate([led, ledger_of(abi, [(77_000_001, 0, 0xFF)])])
+    _, alt, _ = orc.score_batch(abi, nodes, led2, pods, want_scores=False, topk=1)
+    errors = []
+
+    def reader():
+        try:
+            for _ in range(60):
+                _, t = eng.score_batch(pods, len(nodes), want_scores=False, topk=1)
+                if t.tobytes() not in (base.tobytes(), alt.tobytes()):
+                    errors.append("torn read")
+        except Exception as ex:           # noqa: BLE001
+            errors.append(repr(ex))
+
+    def writer():
+        try:
+            for _ in range(60):
+                eng.commit(77_000_001, 0, 0xFF)
+                eng.release(77_000_001)
+        except Exception as ex:           # noqa: BLE001
+            errors.append(repr(ex))
+
+    threads = [threading.Thread(target=reader) for _ in range(3)] + [threading.Thread(target=writer)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors[:3]
+    _, t = eng.score_batch(pods, len(nodes), want_scores=False, topk=1)
+    assert t.tobytes() == base.tobytes()
+    eng.close()
