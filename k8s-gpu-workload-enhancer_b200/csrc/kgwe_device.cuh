@@ -217,8 +217,7 @@ template <int K>
 __device__ __forceinline__ void greedy_chain_fast_k(const NodeFast* nf, int s, int32_t& key, uint32_t& pay) {
     key = 0; pay = 0;
     const int4* ip = reinterpret_cast<const int4*>(nf->init);
-    int4 a = ip[0], b = ip[1];
-    if (nf->init[s] < 0) return;                       // start GPU not available
+    int4 a = ip[0], b = ip[1];                         // (the caller has checked that start s is available)
     int32_t sum = 0; uint32_t order = (uint32_t)s; int m = s;
 #pragma unroll
     for (int step = 1; step < K; ++step) {
@@ -261,6 +260,7 @@ __device__ __forceinline__ void greedy_chain_fast_all(const NodeFast* nf, int s,
     }
 }
 
+// Precondition for lane s: nf->init[s] >= 0 (start GPU available); callers test it once per node.
 __device__ __forceinline__ void greedy_chain_fast(const NodeFast* nf, int s, int k, int32_t& key, uint32_t& pay) {
     switch (k) {
         case 2: greedy_chain_fast_k<2>(nf, s, key, pay); break;
@@ -443,10 +443,9 @@ __device__ __forceinline__ void eval_finish(const DevNode* rec, const NodeCtx& n
 
 // Winner of the 8 integer chains of a group: key = (total << 3) | (7 - start).  `gmask` names the
 // 8 lanes of the group (or the whole warp when all four groups are known to be here together).
-__device__ __forceinline__ void fast_group_winner(int32_t& key, uint32_t& pay, uint32_t gmask = 0xffffffffu) {
-#pragma unroll
-    for (int off = 4; off >= 1; off >>= 1) key = max(key, __shfl_xor_sync(gmask, key, off, 8));
-    pay = __shfl_sync(gmask, pay, 7 - (key & 7), 8);
+__device__ __forceinline__ void fast_group_winner(int32_t& key, uint32_t& pay, uint32_t gmask) {
+    key = __reduce_max_sync(gmask, key);              // REDUX.MAX over the group's 8 lanes
+    pay = __shfl_sync(gmask, pay, ~key & 7, 8);       // 7 - (key & 7) = the winning start lane
 }
 
 // isNodeEligible + scoreNode for one (pod,node), executed by the 8 lanes of a group
@@ -467,7 +466,7 @@ __device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, 
         if (FAST && warp_fast && !exhaustive) {
             // all four nodes of this warp have whole-number bandwidths: integer chains, 32-bit winner
             int32_t key = 0; uint32_t pay = 0;
-            if (eligible) greedy_chain_fast(nf, j, k, key, pay);
+            if (eligible && nf->init[j] >= 0) greedy_chain_fast(nf, j, k, key, pay);
             fast_group_winner(key, pay, gmask);
             found = key > 0; win_total = (double)(key >> 3);
             order = pay; sel = mask_of_order(order, k);

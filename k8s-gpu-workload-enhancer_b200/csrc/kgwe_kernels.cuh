@@ -206,8 +206,8 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
 #pragma unroll 1
             for (int kk = 2; kk <= 8; ++kk) {
                 int32_t key = 0; uint32_t pay = 0;
-                if (c.integral && c.A >= kk) greedy_chain_fast(nf, j, kk, key, pay);
-                fast_group_winner(key, pay);
+                if (c.integral && c.A >= kk && (c.avail >> j & 1)) greedy_chain_fast(nf, j, kk, key, pay);
+                fast_group_winner(key, pay, 0xffu << (lane & 24));
                 if (j == 0) memo[grp * 8 + (kk - 1)] = make_int2(key, (int)pay);
             }
             __syncwarp();
@@ -215,6 +215,8 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     }
     const NodeCtx& nc = ctxs[grp];
     const uint32_t gnode = P.node_base + node;
+    const uint32_t gmask = 0xffu << (lane & 24);
+    const bool start_ok = nf->init[j] >= 0;             // this lane's start GPU is available
     unsigned long long cand = 0;
 
     for (uint32_t p0 = p_begin; p0 < p_end; p0 += 8) {
@@ -247,18 +249,14 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
                         const uint32_t* tab = subset + grp * 256;
                         uint32_t b = 0;
                         for (int r = subset_off(kt) + j; r < subset_off(kt + 1); r += 8) b = max(b, tab[r]);
-#pragma unroll
-                        for (int off = 4; off >= 1; off >>= 1) b = max(b, __shfl_xor_sync(0xffu << (lane & 24), b, off, 8));
-                        key = (int32_t)b;
+                        key = (int32_t)__reduce_max_sync(gmask, b);
                     } else if (kt) {
-                        greedy_chain_fast(nf, j, kt, key, pay);
-#pragma unroll
-                        for (int off = 4; off >= 1; off >>= 1) key = max(key, __shfl_xor_sync(0xffu << (lane & 24), key, off, 8));
-                        pay = __shfl_sync(0xffu << (lane & 24), pay, 7 - (key & 7), 8);
+                        if (start_ok) greedy_chain_fast(nf, j, kt, key, pay);
+                        fast_group_winner(key, pay, gmask);
                     }
                 } else {
-                    if (kt) greedy_chain_fast(nf, j, kt, key, pay);
-                    fast_group_winner(key, pay);
+                    if (kt && start_ok) greedy_chain_fast(nf, j, kt, key, pay);
+                    fast_group_winner(key, pay, gmask);
                 }
                 if (j == t) { mykey = key; mypay = pay; }
             }
@@ -496,11 +494,7 @@ schedule_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict
 // when one of its commits changes the node.  Per workload: a filter + table look-up + finish per
 // node, block max, then the same arg-max + arrival-counter barrier as above.  The next workload's
 // descriptor is prefetched while the current one is decided.
-__device__ __forceinline__ void group_winner_masked(int32_t& key, uint32_t& pay, uint32_t gmask) {
-#pragma unroll
-    for (int off = 4; off >= 1; off >>= 1) key = max(key, __shfl_xor_sync(gmask, key, off, 8));
-    pay = __shfl_sync(gmask, pay, 7 - (key & 7), 8);
-}
+__device__ __forceinline__ void group_winner_masked(int32_t& key, uint32_t& pay, uint32_t gmask) { fast_group_winner(key, pay, gmask); }
 
 // (Re)build one node's tables by its 8 lanes.  `full` = first build (NVLink matrix rows too);
 // after a commit only availability-dependent parts change.  NUMA / PCIe group tables are left
