@@ -249,7 +249,9 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
                         const uint32_t* tab = subset + grp * 256;
                         uint32_t b = 0;
                         for (int r = subset_off(kt) + j; r < subset_off(kt + 1); r += 8) b = max(b, tab[r]);
-                        key = (int32_t)__reduce_max_sync(gmask, b);
+#pragma unroll
+                        for (int off = 4; off >= 1; off >>= 1) b = max(b, __shfl_xor_sync(gmask, b, off, 8));
+                        key = (int32_t)b;
                     } else if (kt) {
                         if (start_ok) greedy_chain_fast(nf, j, kt, key, pay);
                         fast_group_winner(key, pay, gmask);
