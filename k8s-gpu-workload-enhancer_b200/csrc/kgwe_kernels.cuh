@@ -80,7 +80,8 @@ __device__ __forceinline__ void finalize_one(const DevNode* __restrict__ nodes, 
     if (live) pod = load_pod(pods, p); else { pod = kgwe_pod_req{}; }
     const DevNode* rec = nodes + node;
     NodeCtx nc;
-    node_ctx_init(nc, rec, live && key != 0ull && node < n_nodes);
+    node_ctx_core(nc, rec, live && key != 0ull && node < n_nodes);
+    if (pod.topology_pref == KGWE_TOPO_SAME_NUMA || pod.topology_pref == KGWE_TOPO_SAME_PCIE_SWITCH) node_ctx_group_tables(nc, rec);
     EvalOut o;
     evaluate<false>(rec, nc, pod, P, live && hint_bit(hint, hint_row_bytes, p, node), lane, o);
     if (live && (lane & 7) == 0) {
