@@ -215,8 +215,17 @@ def run_kgwe(args):
     sptr = stream.cuda_stream
     assert sptr != 0
     d_pods = torch.from_numpy(pods.view(np.uint8).reshape(P, abi.POD_REQ.itemsize)).to(dev)
-    scorer = kg.sharded.ShardedScorer(eng, n_local, world, dist if world > 1 else None, sptr)
+    scorer = kg.sharded.ShardedScorer(eng, n_local, world, dist if world > 1 else None, sptr, rank=rank)
     scorer.alloc(torch, dev, P, 1, with_matrix=True)
+    exchange = "none (1 GPU)"
+    if world > 1:
+        ok_p2p = scorer.enable_p2p(torch, dev, P) if os.environ.get("KGWE_EXCHANGE", "p2p") == "p2p" else False
+        agree = torch.tensor([1 if ok_p2p else 0], device=dev)
+        dist.all_reduce(agree, op=dist.ReduceOp.MIN)          # all ranks or none
+        if int(agree.item()) == 0:
+            scorer.p2p = None
+        exchange = ("P2P stores from the finalisation kernel into every rank's gather buffer (symmetric memory) + one cross-GPU barrier"
+                    if scorer.p2p is not None else "NCCL all_gather of the local top-1 lists")
     d_gather, d_merged = scorer.d_gather, scorer.d_merged
     flush = torch.empty(160 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
 
@@ -403,7 +412,7 @@ def run_kgwe(args):
             "warmup": max(3, args.warmup), "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": WORKLOAD, "n_nodes": N, "n_pods": P, "ledger_entries": int(len(ledger)), "mode": "greedy (reference parity)",
-                       "sharding": f"nodes by contiguous range over {world} rank(s)",
+                       "sharding": f"nodes by contiguous range over {world} rank(s)", "exchange": exchange,
                        "l2": "160 MiB buffer written between steps (inside the timed region); each step also writes its P x N_local x 16 B score matrix (1.6 GB at 1 GPU, 200 MB at 8), both larger than the 126 MB L2"},
             "evaluations_per_sec": ev_total / (ms_total * 1e-3),
             "candidates_per_step": cand_total / args.steps,

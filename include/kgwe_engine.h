@@ -268,6 +268,18 @@ int kgwe_score_top1_noalloc(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t
                             const uint8_t* d_hint_bitmap, kgwe_node_score* d_out_scores,
                             kgwe_placement* d_out_top1, void* cuda_stream);
 
+/* Node-sharded top-1 batches with the exchange fused into the finalisation kernel: instead of
+ * writing this rank's best placement per pod locally and all-gathering, the kernel stores it
+ * straight into EVERY rank's gather buffer (slot `my_rank` of a [n_ranks][n_pods] placement array)
+ * through peer-mapped device memory (NVLink / NVSwitch P2P stores).  peer_gather_bufs is a HOST
+ * array of n_ranks device addresses, one per rank (this rank's own buffer included), e.g. the
+ * buffer_ptrs of a torch symmetric-memory allocation.  The caller still has to order "all ranks
+ * have written" before reading its buffer (a cross-GPU barrier on the same stream) and then runs
+ * kgwe_topk_merge_device on it.  Otherwise identical to kgwe_score_batch_device(..., topk = 1). */
+int kgwe_score_batch_device_p2p(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods,
+                                const uint8_t* d_hint_bitmap, kgwe_node_score* d_out_scores,
+                                const uint64_t* peer_gather_bufs, uint32_t n_ranks, uint32_t my_rank, void* cuda_stream);
+
 /* Merge R ranked lists per pod (layout [r][p][topk], device memory) into one
  * [p][topk] list in canonical order (score desc, node index asc).  This is the merge
  * every rank runs after the all-gather of local top-k lists. */

@@ -85,7 +85,7 @@ ENGINE_SYMBOLS = [
     "kgwe_topk_merge_device", "kgwe_schedule_queue", "kgwe_node_read", "kgwe_get_stats", "kgwe_last_error",
     "kgwe_version", "kgwe_score_top1_noalloc", "kgwe_topk_merge_host",
     "kgwe_schedule_gangs", "kgwe_placement_terms", "kgwe_mig_pack", "kgwe_mig_rebalance",
-    "kgwe_topology_hint_batch", "kgwe_topology_gauges",
+    "kgwe_topology_hint_batch", "kgwe_topology_gauges", "kgwe_score_batch_device_p2p",
 ]
 NOALLOC_MAX_PODS = 16384
 
@@ -115,6 +115,7 @@ def load_engine_lib():
     lib.kgwe_score_batch.argtypes = [vp, vp, u32, vp, vp, u32, vp]
     lib.kgwe_score_batch_device.argtypes = [vp, vp, u32, vp, vp, u32, vp, vp]
     lib.kgwe_score_top1_noalloc.argtypes = [vp, vp, u32, vp, vp, vp, vp]
+    lib.kgwe_score_batch_device_p2p.argtypes = [vp, vp, u32, vp, vp, vp, u32, u32, vp]
     lib.kgwe_topology_hint_batch.argtypes = [vp, vp, u32, vp]
     lib.kgwe_topology_gauges.argtypes = [vp, vp, u32]
     lib.kgwe_mig_pack.argtypes = [vp, vp, u32, vp, u32, vp]

@@ -447,6 +447,57 @@ int kgwe_score_batch_device(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t
     return launch_score(e, d_pods, n_pods, d_hint, scores, topk, d_topk, s);
 }
 
+int kgwe_score_batch_device_p2p(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const uint8_t* d_hint,
+                                kgwe_node_score* d_out, const uint64_t* peer_bufs, uint32_t n_ranks, uint32_t my_rank, void* cuda_stream) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (!peer_bufs || n_ranks == 0 || n_ranks > 8 || my_rank >= n_ranks || (n_pods && !d_pods)) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments (1..8 ranks)");
+    CU(e, cudaSetDevice(e->cfg.device));
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : e->stream;
+    int rc = flush_dirty(e, s);
+    if (rc != KGWE_OK) return rc;
+    if (n_pods == 0) return KGWE_OK;
+    if (e->n_nodes == 0) return fail(e, KGWE_ERR_INVALID_ARG, "the cluster image of this shard is empty");
+    // K1 exactly as in launch_score(topk = 1), then the fused finalise + scatter
+    const uint32_t n_tiles = (e->n_nodes + TILE_NODES - 1) / TILE_NODES;
+    const bool tables = e->cfg.flags & KGWE_CFG_SUBSET_TABLES, memo = e->cfg.flags & KGWE_CFG_MEMOISE_GROUPS;
+    const uint32_t slots = (uint32_t)e->sm_count * (tables ? 1u : 2u);
+    uint32_t chunks = 1, ppc = n_pods;
+    for (uint32_t waves = 1; waves <= 64; ++waves) {
+        chunks = std::max(1u, std::min(n_pods, slots * waves / n_tiles));
+        ppc = (n_pods + chunks - 1) / chunks;
+        if (ppc <= MAX_PODS_PER_CHUNK && (waves >= 2 || n_pods <= 64)) break;
+    }
+    if (ppc > MAX_PODS_PER_CHUNK) ppc = MAX_PODS_PER_CHUNK;
+    chunks = (n_pods + ppc - 1) / ppc;
+    if (chunks > 65535u) return fail(e, KGWE_ERR_TOO_LARGE, "too many pods in one launch (%u)", n_pods);
+    {
+        const size_t had = e->d_best.cap;
+        CU(e, e->d_best.ensure(n_pods));
+        if (e->d_best.cap != had) CU(e, cudaMemsetAsync(e->d_best.p, 0, e->d_best.cap * sizeof(unsigned long long), s));
+    }
+    unsigned long long* best = e->d_best.p;
+    const dim3 grid(n_tiles, chunks);
+    const size_t smem = score_smem_bytes(ppc, tables, memo);
+    const FusedTail tail{nullptr, nullptr, nullptr, 0};
+    const bool timed = e->timers_pending < kgwe_engine::kTimers;
+    if (timed) CU(e, cudaEventRecord(e->t0[e->timers_pending], s));
+#define KGWE_LAUNCH_SCORE(T, M) score_kernel<T, M><<<grid, SCORE_THREADS, smem, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e), \
+                                                                                     d_out, best, e->params, e->d_counters, tail)
+    if (tables) { if (memo) KGWE_LAUNCH_SCORE(true, true); else KGWE_LAUNCH_SCORE(true, false); }
+    else        { if (memo) KGWE_LAUNCH_SCORE(false, true); else KGWE_LAUNCH_SCORE(false, false); }
+#undef KGWE_LAUNCH_SCORE
+    CU(e, cudaGetLastError());
+    if (timed) { CU(e, cudaEventRecord(e->t1[e->timers_pending], s)); e->timers_pending++; }
+    PeerBufs peers;
+    for (uint32_t r = 0; r < 8; ++r) peers.p[r] = r < n_ranks ? reinterpret_cast<kgwe_placement*>(peer_bufs[r]) : nullptr;
+    finalize_top1_p2p_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), best, peers, n_ranks, my_rank, e->params);
+    CU(e, cudaGetLastError());
+    e->stats.kernel_launches += 2;
+    e->stats.evaluations += (uint64_t)n_pods * e->n_present;
+    return KGWE_OK;
+}
+
 int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, const uint8_t* hint,
                      kgwe_node_score* out_scores, uint32_t topk, kgwe_placement* out_topk) {
     if (!e) return KGWE_ERR_INVALID_ARG;

@@ -337,6 +337,29 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     }
 }
 
+// K1b with the exchange fused in: the placement of (this rank, pod p) is stored into slot `my_rank`
+// of every rank's gather buffer over peer-mapped memory (NVLink P2P stores), replacing the all-gather.
+struct PeerBufs { kgwe_placement* p[8]; };
+__global__ void __launch_bounds__(256)
+finalize_top1_p2p_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
+                         const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
+                         unsigned long long* __restrict__ best, PeerBufs peers, uint32_t n_ranks, uint32_t my_rank, Params P) {
+    const uint32_t p = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+    const bool live = p < n_pods;
+    // compute into this rank's own buffer first, then replicate the 32-byte record to the peers
+    kgwe_placement* mine = peers.p[my_rank] + (size_t)my_rank * n_pods;
+    finalize_one(nodes, n_nodes, pods, p, live, hint, hint_row_bytes, best, mine, P, threadIdx.x & 31);
+    if (live && (threadIdx.x & 7) == 0) {
+        const int4* src = reinterpret_cast<const int4*>(mine + p);
+        const int4 a = src[0], b = src[1];
+        for (uint32_t r = 0; r < n_ranks; ++r) {
+            if (r == my_rank) continue;
+            int4* dst = reinterpret_cast<int4*>(peers.p[r] + (size_t)my_rank * n_pods + p);
+            dst[0] = a; dst[1] = b;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256)
 finalize_top1_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
                      const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,

@@ -91,6 +91,12 @@ class Engine:
         fixed device array (no allocation inside the call; at most abi.NOALLOC_MAX_PODS pods)."""
         self._check(self.lib.kgwe_score_top1_noalloc(self.h, d_pods, n_pods, d_hint, d_scores, d_top1, stream))
 
+    def score_batch_device_p2p(self, d_pods, n_pods, d_hint, d_scores, peer_ptrs, my_rank, stream=None):
+        """Top-1 scoring whose finalisation kernel writes this rank's placements into every rank's gather
+        buffer (peer_ptrs: one device address per rank) over NVLink, replacing the all-gather."""
+        arr = (C.c_uint64 * len(peer_ptrs))(*[int(x) for x in peer_ptrs])
+        self._check(self.lib.kgwe_score_batch_device_p2p(self.h, d_pods, n_pods, d_hint, d_scores, arr, len(peer_ptrs), my_rank, stream))
+
     def topk_merge_device(self, d_lists, n_lists, n_pods, topk, d_out, stream=None):
         self._check(self.lib.kgwe_topk_merge_device(self.h, d_lists, n_lists, n_pods, topk, d_out, stream))
 

@@ -28,8 +28,28 @@ class ShardedScorer:
     """Device-resident sharded batch scorer.  `engine` holds this rank's shard (created with
     node_base = shard start).  Buffers are torch uint8 tensors on the engine's GPU."""
 
-    def __init__(self, engine, n_local, world, dist=None, stream_ptr=None):
-        self.eng, self.n_local, self.world, self.dist, self.sptr = engine, n_local, world, dist, stream_ptr
+    def __init__(self, engine, n_local, world, dist=None, stream_ptr=None, rank=0):
+        self.eng, self.n_local, self.world, self.dist, self.sptr, self.rank = engine, n_local, world, dist, stream_ptr, rank
+        self.p2p = None            # (symmetric-memory tensor [2, world, P, 32], handle) when the fused exchange is on
+        self.step_no = 0
+
+    def enable_p2p(self, torch, dev, n_pods):
+        """Fused exchange for top-1 batches: the finalisation kernel stores straight into every rank's
+        gather buffer (torch symmetric memory = peer-mapped allocations), double-buffered, one cross-GPU
+        barrier per batch instead of an NCCL all-gather.  Returns False (and stays on NCCL) if
+        symmetric memory cannot be set up on this box."""
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            buf = symm_mem.empty((2, self.world, n_pods, abi.PLACEMENT.itemsize), dtype=torch.uint8, device=dev)
+            hdl = symm_mem.rendezvous(buf, self.dist.group.WORLD)
+            ptrs = [int(p) for p in hdl.buffer_ptrs]
+            if len(ptrs) != self.world:
+                return False
+            self.p2p = (buf, hdl, ptrs)
+            return True
+        except Exception:          # noqa: BLE001 - any failure: keep the NCCL path
+            self.p2p = None
+            return False
 
     def alloc(self, torch, dev, n_pods, topk, with_matrix=True):
         it = abi.PLACEMENT.itemsize
@@ -42,6 +62,16 @@ class ShardedScorer:
     def step(self, d_pods, d_hint=None):
         """One batch: local scoring (+ matrix), all-gather of local top-k, merge.  Asynchronous."""
         sc = self.d_scores.data_ptr() if self.d_scores is not None else None
+        if self.p2p is not None and self.topk == 1 and self.world > 1:
+            buf, hdl, ptrs = self.p2p
+            slot = self.step_no & 1
+            self.step_no += 1
+            off = slot * self.world * self.P * abi.PLACEMENT.itemsize
+            self.eng.score_batch_device_p2p(d_pods.data_ptr(), self.P, d_hint.data_ptr() if d_hint is not None else None, sc,
+                                            [p + off for p in ptrs], self.rank, self.sptr)
+            hdl.barrier(channel=slot)          # every rank's stores have landed before anyone merges
+            self.eng.topk_merge_device(buf[slot].data_ptr(), self.world, self.P, 1, self.d_merged.data_ptr(), self.sptr)
+            return self.d_merged
         self.eng.score_batch_device(d_pods.data_ptr(), self.P, d_hint.data_ptr() if d_hint is not None else None,
                                     sc, self.topk, self.d_top.data_ptr(), self.sptr)
         if self.world > 1:

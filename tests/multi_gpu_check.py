@@ -41,6 +41,18 @@ def main():
     local_scores = sc.d_scores.cpu().numpy().view(abi.NODE_SCORE).reshape(P, hi - lo)
     o_scores, want, _ = orc.score_batch(abi, nodes, led, pods, want_scores=True, topk=topk, threads=4)
     ok = got.tobytes() == want.tobytes() and local_scores.tobytes() == np.ascontiguousarray(o_scores[:, lo:hi]).tobytes()
+    # the same batch with the exchange fused into the finalisation kernel (P2P stores), top-1, several steps in a row
+    sc1 = kg.sharded.ShardedScorer(eng, hi - lo, world, dist, stream.cuda_stream, rank=rank)
+    sc1.alloc(torch, dev, P, 1, with_matrix=False)
+    p2p_on = sc1.enable_p2p(torch, dev, P)
+    _, want1, _ = orc.score_batch(abi, nodes, led, pods, want_scores=False, topk=1, threads=4)
+    for it in range(5):
+        m = sc1.step(d_pods)
+        torch.cuda.synchronize()
+        got1 = m.cpu().numpy().view(abi.PLACEMENT).reshape(P, 1)
+        ok = ok and got1.tobytes() == want1.tobytes()
+    if rank == 0:
+        print(f"fused P2P exchange: {'on' if p2p_on else 'unavailable (NCCL path used)'}")
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
