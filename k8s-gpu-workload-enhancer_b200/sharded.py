@@ -78,3 +78,32 @@ class ShardedScorer:
             self.dist.all_gather_into_tensor(self.d_gather, self.d_top)
             self.eng.topk_merge_device(self.d_gather.data_ptr(), self.world, self.P, self.topk, self.d_merged.data_ptr(), self.sptr)
         return self.d_merged
+
+
+def schedule_queue_sharded(dist, rank, world, shard, pods, score_top1, commit, hint=None, device=None, torch=None):
+    """Stateful Schedule() over a node-sharded cluster: per workload every rank scores its
+    shard (top-1, global node index), ONE small all-gather of the 32-byte placements, the identical merge on
+    every rank (score desc, node index asc), and the rank that owns the winning node commits it.
+      score_top1(pod_array_of_1, hint_row_or_None) -> PLACEMENT record of this shard's best node
+      commit(wl_id, local_node_idx, gpu_mask)
+    `shard` = (lo, hi) node range of this rank.  Exact, but it pays a collective per workload: for clusters
+    that fit one GPU (10k nodes = 7.68 MB) kgwe_schedule_queue on one engine is the fast path."""
+    lo, hi = shard
+    out = np.zeros(len(pods), dtype=abi.PLACEMENT)
+    it = abi.PLACEMENT.itemsize
+    for i in range(len(pods)):
+        local = np.ascontiguousarray(score_top1(pods[i:i + 1], None if hint is None else hint[i:i + 1]), dtype=abi.PLACEMENT).reshape(1)
+        if world > 1:
+            mine = torch.from_numpy(local.view(np.uint8).reshape(it).copy())
+            if device is not None:
+                mine = mine.to(device)
+            gathered = torch.empty(world * it, dtype=torch.uint8, device=mine.device)
+            dist.all_gather_into_tensor(gathered, mine)
+            lists = gathered.cpu().numpy().view(abi.PLACEMENT).reshape(world, 1, 1)
+        else:
+            lists = local.reshape(1, 1, 1)
+        best = merge_host(lists, 1)[0, 0]
+        out[i] = best
+        if best["node_idx"] != abi.NO_NODE and lo <= int(best["node_idx"]) < hi:
+            commit(int(pods[i]["wl_id"]), int(best["node_idx"]) - lo, int(best["gpu_mask"]))
+    return out

@@ -53,6 +53,14 @@ def main():
         ok = ok and got1.tobytes() == want1.tobytes()
     if rank == 0:
         print(f"fused P2P exchange: {'on' if p2p_on else 'unavailable (NCCL path used)'}")
+    # stateful queue over the sharded cluster: per-workload all-gather, owner rank commits
+    qpods = pods[:120]
+    got_q = kg.sharded.schedule_queue_sharded(
+        dist, rank, world, (lo, hi), qpods,
+        lambda pod, h: eng.score_batch(pod, hi - lo, want_scores=False, topk=1)[1][0, 0],
+        lambda wl, n, m: eng.commit(wl, n, m), device=dev, torch=torch)
+    want_q, _, _ = orc.schedule_queue(abi, nodes, led, qpods)
+    ok = ok and got_q.tobytes() == want_q.tobytes()
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:

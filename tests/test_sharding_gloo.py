@@ -42,6 +42,56 @@ def _worker(rank, world, port, q):
     q.put((rank, ok, int((want["node_idx"] >= hi - lo).sum()) if rank == 0 else 0))
 
 
+def _queue_worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    import __graft_entry__ as entry
+    kg = entry.load_package()
+    from oracle import binding as orc
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    abi, synth = kg.abi, kg.synth
+    nodes, pods, led = synth.config(1)                     # 16 nodes: pods compete for the same nodes across shards
+    pods = pods[:60]
+    lo, hi = kg.sharded.shard_range(len(nodes), rank, world)
+    state = {"led": [tuple(x) for x in led[(led["node_idx"] >= lo) & (led["node_idx"] < hi)][["wl_id", "node_idx", "gpu_mask"]].tolist()]}
+    cfg = abi.default_config(hi - lo, node_base=lo)
+
+    def score_top1(pod, hint_row):                         # the oracle stands in for this rank's GPU engine
+        ledger = np.zeros(len(state["led"]), dtype=abi.ALLOC)
+        for i, (w, n, m) in enumerate(state["led"]):
+            ledger[i]["wl_id"], ledger[i]["node_idx"], ledger[i]["gpu_mask"] = w, n, m
+        _, top, _ = orc.score_batch(abi, nodes[lo:hi], ledger, pod, want_scores=False, topk=1, cfg=cfg)
+        return top[0, 0]
+
+    def commit(wl, local_node, mask):
+        state["led"].append((wl, local_node, mask))
+
+    got = kg.sharded.schedule_queue_sharded(dist, rank, world, (lo, hi), pods, score_top1, commit, torch=torch)
+    want, _, _ = orc.schedule_queue(abi, nodes, led, pods)
+    ok = got.tobytes() == want.tobytes()
+    dist.barrier()
+    dist.destroy_process_group()
+    q.put((rank, ok, len(state["led"])))
+
+
+def test_two_rank_sharded_stateful_queue_matches_single_scheduler(kg, engine_lib):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29700 + os.getpid() % 1000
+    procs = [ctx.Process(target=_queue_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(ok for _, ok, _ in res), res
+    assert all(n > 0 for _, _, n in res)                   # both shards received commits
+
+
 def test_two_rank_sharded_topk_merge_matches_global_ranking(kg, engine_lib):
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
