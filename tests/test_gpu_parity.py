@@ -539,3 +539,41 @@ def test_concurrent_callers_share_one_engine(kg, orc):
     _, t = eng.score_batch(pods, len(nodes), want_scores=False, topk=1)
     assert t.tobytes() == base.tobytes()
     eng.close()
+
+
+def test_topk_merge_device_equals_host_merge(kg):
+    """The merge every rank runs after the exchange: device kernel vs kgwe_topk_merge_host on random ranked lists
+    (ties on score across shards, short lists, empty shards)."""
+    import torch
+    abi, synth = kg.abi, kg.synth
+    rng = synth.SplitMix64(404)
+    R, P, K = 5, 300, 6
+    lists = np.zeros((R, P, K), dtype=abi.PLACEMENT)
+    lists["node_idx"] = abi.NO_NODE
+    for r in range(R):
+        n_valid = rng.randint(0, K, P)
+        totals = np.sort(rng.randint(1, 12, P * K).reshape(P, K), axis=1)[:, ::-1]          # few distinct scores -> many ties
+        nodes_ = np.sort(rng.randint(0, 199, P * K).reshape(P, K), axis=1) + 1000 * r       # ascending inside a shard, disjoint across shards
+        # canonical order inside a list: score desc, node asc -> sort node ascending within equal scores
+        for p in range(P):
+            order = np.lexsort((nodes_[p], -totals[p]))
+            t, n = totals[p][order], nodes_[p][order]
+            v = int(n_valid[p])
+            lists[r, p, :v]["total"] = t[:v]
+            lists[r, p, :v]["node_idx"] = n[:v]
+            lists[r, p, :v]["gpu_mask"] = (n[:v] % 255).astype(np.uint8)
+    want = kg.sharded.merge_host(lists, K)
+    eng = kg.Engine(max_nodes=1)
+    d_lists = torch.from_numpy(lists.view(np.uint8).reshape(R, P, K, abi.PLACEMENT.itemsize)).cuda()
+    d_out = torch.zeros((P, K, abi.PLACEMENT.itemsize), dtype=torch.uint8, device="cuda")
+    eng.topk_merge_device(d_lists.data_ptr(), R, P, K, d_out.data_ptr())
+    torch.cuda.synchronize()
+    got = d_out.cpu().numpy().view(abi.PLACEMENT).reshape(P, K)
+    assert got.tobytes() == want.tobytes()
+    # reference semantics of the merge itself: global (score desc, node asc) order of the union
+    for p in (0, 17, 299):
+        union = [(int(x["total"]), int(x["node_idx"])) for r in range(R) for x in lists[r, p] if x["node_idx"] != abi.NO_NODE]
+        union.sort(key=lambda x: (-x[0], x[1]))
+        exp = union[:K]
+        assert [(int(x["total"]), int(x["node_idx"])) for x in want[p] if x["node_idx"] != abi.NO_NODE] == exp
+    eng.close()
