@@ -336,6 +336,26 @@ def run_kgwe(args):
                 lat.append(measure(e3, n_small))
                 e3.close()
 
+    # ---- the same per-pod Prioritize over the node shards (N > 1): local top-1 on every rank, one 32-byte
+    #      all-gather, identical merge; SURVEY 8e asks whether this beats the 1-GPU latency (it does not at 10k nodes)
+    lat_sharded = None
+    if world > 1:
+        itp = abi.PLACEMENT.itemsize
+        gathered = torch.empty(world * itp, dtype=torch.uint8, device=dev)
+        xs = np.empty(600)
+        for i in range(700):
+            dist.barrier()
+            a = time.perf_counter()
+            _, t1 = eng.score_batch(pods[i % P:i % P + 1], n_local, want_scores=False, topk=1)
+            mine = torch.from_numpy(t1.view(np.uint8).reshape(itp)).to(dev)
+            dist.all_gather_into_tensor(gathered, mine)
+            lists = gathered.cpu().numpy().view(abi.PLACEMENT).reshape(world, 1, 1)
+            kg.sharded.merge_host(lists, 1)
+            if i >= 100:
+                xs[i - 100] = (time.perf_counter() - a) * 1e6
+        lat_sharded = {"n_nodes": N, "ranks": world, "calls": len(xs), "p50_us": float(np.percentile(xs, 50)), "p99_us": float(np.percentile(xs, 99)),
+                       "path": "kgwe_score_batch(P=1) per shard + NCCL all_gather(32 B) + kgwe_topk_merge_host"}
+
     # ---- stateful Schedule() queue throughput (reported beside the headline; N=1 only) ----
     sched = None
     if world == 1:
@@ -428,6 +448,8 @@ def run_kgwe(args):
         }
         if lat:
             out["prioritize_latency"] = lat
+        if lat_sharded:
+            out["prioritize_latency_sharded"] = lat_sharded
         if sched:
             out["stateful_queue"] = sched
         if exh:
