@@ -14,6 +14,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -58,6 +59,11 @@ struct PinBuf {
 };
 
 constexpr size_t kScoreScratchBytes = 1ull << 30;   // internal score-matrix chunk (top-k > 1 without out_scores, host copies)
+// Testing knob: KGWE_SCORE_SCRATCH_BYTES shrinks the chunk so the multi-pass path of kgwe_score_batch can be exercised on small inputs.
+size_t score_scratch_bytes() {
+    static const size_t v = [] { const char* s = getenv("KGWE_SCORE_SCRATCH_BYTES"); const long long x = s ? atoll(s) : 0; return x > 0 ? (size_t)x : kScoreScratchBytes; }();
+    return v;
+}
 
 }  // namespace
 
@@ -547,7 +553,7 @@ int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, 
     }
     // pods per pass bounded by the score-matrix scratch
     uint32_t pass = n_pods;
-    if (need_matrix) pass = (uint32_t)std::max<size_t>(1, std::min<size_t>(n_pods, kScoreScratchBytes / ((size_t)N * sizeof(kgwe_node_score))));
+    if (need_matrix) pass = (uint32_t)std::max<size_t>(1, std::min<size_t>(n_pods, score_scratch_bytes() / ((size_t)N * sizeof(kgwe_node_score))));
     CU(e, e->d_pods.ensure(pass)); CU(e, e->h_pods.ensure(pass));
     if (hint) { CU(e, e->d_hint.ensure((size_t)pass * row)); CU(e, e->h_hint.ensure((size_t)pass * row)); }
     if (topk) { CU(e, e->d_topk.ensure((size_t)pass * topk)); CU(e, e->h_topk.ensure((size_t)pass * topk)); }
