@@ -217,8 +217,11 @@ size_t score_smem_bytes(uint32_t pods_per_chunk, bool tables = false, bool memo 
 int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const uint8_t* d_hint,
                  kgwe_node_score* d_scores, uint32_t topk, kgwe_placement* d_topk, cudaStream_t s, bool tables = false,
                  bool fused_tail = false) {
-    FusedTail tail{nullptr, nullptr, nullptr, 0};
-    if (fused_tail) tail = FusedTail{d_topk, e->d_done, e->h_flag, ++e->flag_seq};
+    FusedTail tail{};
+    if (fused_tail) {
+        tail.out = d_topk; tail.done = e->d_done; tail.flag = e->h_flag; tail.seq = ++e->flag_seq;
+        if (n_pods <= 4) { tail.n_inline = n_pods; memcpy(tail.inline_pods, d_pods, (size_t)n_pods * sizeof(kgwe_pod_req)); }   // d_pods is the pinned HOST copy on this path
+    }
     if (n_pods == 0 || e->n_nodes == 0) return KGWE_OK;
     const uint32_t n_tiles = (e->n_nodes + TILE_NODES - 1) / TILE_NODES;
     // pod chunks: whole waves of co-resident CTAs (2 per SM; 1 with subset tables), as few waves as keep
@@ -485,7 +488,7 @@ int kgwe_score_batch_device_p2p(kgwe_engine* e, const kgwe_pod_req* d_pods, uint
     unsigned long long* best = e->d_best.p;
     const dim3 grid(n_tiles, chunks);
     const size_t smem = score_smem_bytes(ppc, tables, memo);
-    const FusedTail tail{nullptr, nullptr, nullptr, 0};
+    const FusedTail tail{};
     const bool timed = e->timers_pending < kgwe_engine::kTimers;
     if (timed) CU(e, cudaEventRecord(e->t0[e->timers_pending], s));
 #define KGWE_LAUNCH_SCORE(T, M) score_kernel<T, M><<<grid, SCORE_THREADS, smem, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e), \
@@ -1065,7 +1068,7 @@ extern "C" int kgwe_score_top1_noalloc(kgwe_engine* e, const kgwe_pod_req* d_pod
     uint32_t ppc = std::min<uint32_t>((n_pods + chunks - 1) / chunks, MAX_PODS_PER_CHUNK);
     chunks = (n_pods + ppc - 1) / ppc;
     score_kernel<false, false><<<dim3(n_tiles, chunks), SCORE_THREADS, score_smem_bytes(ppc), s>>>(
-        e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e), d_out, keys, e->params, e->d_counters, FusedTail{nullptr, nullptr, nullptr, 0});
+        e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e), d_out, keys, e->params, e->d_counters, FusedTail{});
     CU(e, cudaGetLastError());
     finalize_top1_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), keys, d_top1, 1, e->params);
     CU(e, cudaGetLastError());

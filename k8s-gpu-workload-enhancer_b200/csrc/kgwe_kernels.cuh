@@ -51,6 +51,11 @@ __device__ __forceinline__ kgwe_pod_req load_pod(const kgwe_pod_req* pods, uint3
     return u.r;
 }
 
+// Pod descriptor p from the shared-memory copy of the inline descriptors when there is one, else from global memory.
+__device__ __forceinline__ kgwe_pod_req load_pod2(const kgwe_pod_req* pods, const kgwe_pod_req* spods, uint32_t p) {
+    return spods ? spods[p] : load_pod(pods, p);
+}
+
 __device__ __forceinline__ bool hint_bit(const uint8_t* hint, uint32_t row_bytes, uint32_t p, uint32_t n) {
     return hint && ((__ldg(hint + (size_t)p * row_bytes + (n >> 3)) >> (n & 7)) & 1);
 }
@@ -73,11 +78,12 @@ __device__ __forceinline__ void store_no_placement(kgwe_placement* dst) {
 // list, adds EstimatedBandwidth, and clears the key slot for the next call.
 __device__ __forceinline__ void finalize_one(const DevNode* __restrict__ nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods,
                                              uint32_t p, bool live, const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
-                                             unsigned long long* best, kgwe_placement* out, const Params& P, int lane) {
+                                             unsigned long long* best, kgwe_placement* out, const Params& P, int lane,
+                                             const kgwe_pod_req* spods = nullptr) {
     unsigned long long key = live ? *reinterpret_cast<volatile unsigned long long*>(&best[p]) : 0ull;
     const uint32_t node = key ? key_node(key) - P.node_base : 0;
     kgwe_pod_req pod;
-    if (live) pod = load_pod(pods, p); else { pod = kgwe_pod_req{}; }
+    if (live) pod = load_pod2(pods, spods, p); else { pod = kgwe_pod_req{}; }
     const DevNode* rec = nodes + node;
     NodeCtx nc;
     node_ctx_core(nc, rec, live && key != 0ull && node < n_nodes);
@@ -122,7 +128,10 @@ __device__ __forceinline__ int subset_off(int k) {      // first table slot of p
 //   extra smem with MEMO: [winners: 64 nodes x 8 x (key, pay)] = 4 KB
 constexpr int MEMO_SMEM_BYTES = TILE_NODES * 8 * 8;
 // Optional fused finalisation for the latency path: out != nullptr enables it.
-struct FusedTail { kgwe_placement* out; unsigned int* done; unsigned int* flag; unsigned int seq; };
+// Up to 4 pod descriptors can travel inside the kernel parameters (n_inline > 0): the kernel then never
+// reads the descriptors over PCIe from pinned host memory, which removes three dependent host-memory
+// round trips from a single-pod call.
+struct FusedTail { kgwe_placement* out; unsigned int* done; unsigned int* flag; unsigned int seq; unsigned int n_inline; kgwe_pod_req inline_pods[4]; };
 template <bool TABLES, bool MEMO>
 __global__ void __launch_bounds__(SCORE_THREADS, TABLES ? 1 : 2)
 score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
@@ -147,6 +156,9 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     const uint32_t p_begin = blockIdx.y * pods_per_chunk;
     const uint32_t p_end = min(n_pods, p_begin + pods_per_chunk);
 
+    __shared__ kgwe_pod_req inline_copy[4];
+    if (tid < (int)tail.n_inline) inline_copy[tid] = tail.inline_pods[tid];
+    const kgwe_pod_req* spods = tail.n_inline ? inline_copy : nullptr;
     if (tid == 0) mbar_init(bar, 1);
     __syncthreads();
     if (tid == 0) {
@@ -158,7 +170,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     // NUMA / PCIe group tables are only worth building when the chunk has a pod that asks for them
     bool want_groups = false;
     for (uint32_t p = p_begin + tid; p < p_end; p += SCORE_THREADS) {
-        const uint8_t pref = __ldg(&pods[p].topology_pref);
+        const uint8_t pref = spods ? spods[p].topology_pref : __ldg(&pods[p].topology_pref);
         want_groups |= pref == KGWE_TOPO_SAME_NUMA || pref == KGWE_TOPO_SAME_PCIE_SWITCH;
     }
     if (TABLES && tid < 256) {          // slot of mask `tid` in (popcount, value) order
@@ -224,7 +236,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         // ---- phase 0: lane j owns pod p0 + j ----
         const uint32_t p = p0 + j;
         const bool live = p < p_end;
-        kgwe_pod_req pod = load_pod(pods, live ? p : p0);
+        kgwe_pod_req pod = load_pod2(pods, spods, live ? p : p0);
         const int k = clamp_k(pod.gpu_count);
         const bool eligible = live && eval_filter(rec, nc, pod, k);
         const bool wants_group = k >= 2 && is_nvlink_pref(pod);
@@ -292,7 +304,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
 #pragma unroll 1
             for (uint32_t t = 0; t < n_here; ++t) {
                 const uint32_t pt = p0 + t;
-                const kgwe_pod_req podt = load_pod(pods, pt);
+                const kgwe_pod_req podt = load_pod2(pods, spods, pt);
                 evaluate<true>(rec, nc, podt, P, hint_bit(hint, hint_row_bytes, pt, node), lane, o, nf, warp_fast);
                 if (j == 0 && node_ok) {
                     cand += o.candidates;
@@ -329,7 +341,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         __syncthreads();
         if (ticket == gridDim.x * gridDim.y - 1) {
             __threadfence();
-            finalize_one(nodes, n_nodes, pods, (uint32_t)grp, (uint32_t)grp < n_pods, hint, hint_row_bytes, best, tail.out, P, lane);
+            finalize_one(nodes, n_nodes, pods, (uint32_t)grp, (uint32_t)grp < n_pods, hint, hint_row_bytes, best, tail.out, P, lane, spods);
             __threadfence_system();
             __syncthreads();
             if (tid == 0) { *tail.done = 0u; *reinterpret_cast<volatile unsigned int*>(tail.flag) = tail.seq; }
