@@ -189,7 +189,7 @@ typedef struct kgwe_stats {
     uint64_t h2d_bytes;
     uint64_t d2h_bytes;
     double   last_call_gpu_ms;   /* device time of the last scoring call (CUDA events) */
-    uint32_t n_nodes;            /* records in use (highest present local index + 1) */
+    uint32_t n_nodes;            /* highest local index ever upserted + 1 (high-water mark; removed records score as absent) */
     uint32_t n_allocations;      /* ledger size */
     double   score_kernel_ms;    /* summed device time of the scoring kernel (K1) launches timed so far (CUDA events on the launching stream) */
     uint64_t score_kernel_timed; /* how many K1 launches that sum covers */

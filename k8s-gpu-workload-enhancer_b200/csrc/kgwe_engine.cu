@@ -387,8 +387,14 @@ int kgwe_nodes_upsert(kgwe_engine* e, uint32_t first, uint32_t count, const kgwe
         if (rc != KGWE_OK) return rc;
         DevNode& dst = e->h_nodes[first + i];
         const bool was = dst.flags & 1;
-        rec.allocated_mask = was ? dst.allocated_mask : 0;      // ledger-owned fields survive a refresh
-        rec.n_allocs = was ? dst.n_allocs : 0;
+        if (was) { rec.allocated_mask = dst.allocated_mask; rec.n_allocs = dst.n_allocs; }     // ledger-owned fields survive a refresh
+        else {
+            // a node (re)appearing under an index the ledger still names gets its allocations back, as the
+            // reference's name-keyed ledger would match them again (scheduler.go:587-593)
+            uint8_t m = 0; uint32_t n = 0;
+            for (auto& kv : e->ledger) if (kv.second.node == first + i) { m |= kv.second.mask; n++; }
+            rec.allocated_mask = m; rec.n_allocs = n;
+        }
         dst = rec;
         if (!was) e->n_present++;
         mark_dirty(e, first + i);
@@ -406,13 +412,12 @@ int kgwe_node_remove(kgwe_engine* e, uint32_t idx) {
     DevNode& dst = e->h_nodes[idx];
     if (!(dst.flags & 1)) return fail(e, KGWE_ERR_NOT_FOUND, "node %u not present", idx);
     // the reference deletes the map entry (discovery.go:597-600); ledger entries naming the node stay
-    // in the ledger (they are keyed by node name there) and simply stop matching any node.
-    const uint8_t keep_mask = dst.allocated_mask; const uint32_t keep_allocs = dst.n_allocs;
+    // in the ledger (they are keyed by node name there) and simply stop matching any node - until a
+    // node comes back under the same index (see kgwe_nodes_upsert).  n_nodes is a high-water mark and
+    // does not shrink, so the stride of score matrices and hint rows stays what the host knows.
     memset(&dst, 0, sizeof dst);
-    dst.allocated_mask = keep_mask; dst.n_allocs = keep_allocs;
     e->n_present--;
     mark_dirty(e, idx);
-    while (e->n_nodes > 0 && !(e->h_nodes[e->n_nodes - 1].flags & 1)) e->n_nodes--;
     return KGWE_OK;
 }
 

@@ -119,19 +119,20 @@ TopologyAwareScheduler::~TopologyAwareScheduler() { if (engine_) kgwe_engine_des
 
 uint32_t TopologyAwareScheduler::NodeIndex(const std::string& name) const {
     auto it = node_index_.find(name);
-    return it == node_index_.end() ? KGWE_NO_NODE : it->second;
+    return (it == node_index_.end() || node_names_[it->second].empty()) ? KGWE_NO_NODE : it->second;     // "" = currently removed
 }
 
 std::string TopologyAwareScheduler::UpsertNode(const NodeTopology& node) {
     PackedNode pk;
     std::string err = PackNode(node, &pk);
     if (!err.empty()) return err;
-    uint32_t idx = NodeIndex(node.NodeName);
-    if (idx == KGWE_NO_NODE) {
+    auto known = node_index_.find(node.NodeName);       // a node that comes back keeps its index (and so its ledger entries, as in the reference)
+    uint32_t idx;
+    if (known == node_index_.end()) {
         if (node_names_.size() >= max_nodes_) return "cluster image is full";
         idx = (uint32_t)node_names_.size();
         node_index_[node.NodeName] = idx; node_names_.push_back(node.NodeName); node_uuids_.emplace_back();
-    }
+    } else { idx = known->second; node_names_[idx] = node.NodeName; }
     node_uuids_[idx] = pk.uuids;
     if (kgwe_node_upsert(engine_, idx, &pk.image) != KGWE_OK) return kgwe_last_error(engine_);
     return "";
@@ -141,8 +142,7 @@ std::string TopologyAwareScheduler::RemoveNode(const std::string& name) {
     const uint32_t idx = NodeIndex(name);
     if (idx == KGWE_NO_NODE) return "node " + name + " not found";
     if (kgwe_node_remove(engine_, idx) != KGWE_OK) return kgwe_last_error(engine_);
-    node_index_.erase(name);          // the index stays retired; a re-added node gets a fresh one
-    node_names_[idx].clear();
+    node_names_[idx].clear();         // the name keeps its index for when the node comes back
     return "";
 }
 

@@ -200,6 +200,13 @@ def test_incremental_updates_and_ledger(kg, orc):
     keep = np.arange(len(nodes)) != 3
     assert s[:, keep].tobytes() == o[:, keep].tobytes()
     assert (s[:, 3]["flags"] == 0).all()
+    # node 3 comes back: the ledger entries that name it match again (name-keyed ledger, scheduler.go:587-593)
+    eng.upsert_node(3, nodes[3])
+    s_back, _ = eng.score_batch(pods, len(nodes), want_scores=True)
+    o_back, _, _ = orc.score_batch(abi, nodes, led, pods, want_scores=True)
+    assert s_back.tobytes() == o_back.tobytes()
+    eng.remove_node(3)
+    assert eng.stats()["n_nodes"] == len(nodes)
     # ledger: release / unknown release / same wl_id overwrites (scheduler.go:699, 710-716)
     first = led[0]
     eng.release(first["wl_id"])
