@@ -44,6 +44,7 @@ mig_pack_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uint8_t*
     uint32_t* wmin = reinterpret_cast<uint32_t*>(msm + MIG_GEOS * 256);   // [32] + [1] winner
     uint8_t* occ = msm + MIG_GEOS * 256 + 33 * 4;     // [n_gpus]
     uint8_t* meta = occ + n_gpus;                     // [n_gpus]: bit0 enabled, bit1 class
+    __shared__ uint8_t req_stage[MIG_THREADS];        // the next 1024 request profiles (no global-memory latency per request)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int i = tid; i < MIG_GEOS * 256; i += MIG_THREADS) lut[i] = (uint8_t)mig_best((uint32_t)(i & 255), i >> 8);
     for (uint32_t g = tid; g < n_gpus; g += MIG_THREADS) {
@@ -52,7 +53,11 @@ mig_pack_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uint8_t*
     }
     __syncthreads();
     for (uint32_t r = 0; r < n_reqs; ++r) {
-        const int profile = profiles[r];
+        if ((r & (MIG_THREADS - 1)) == 0) {           // refill the staged profiles (the loop's trailing barrier orders this)
+            if (r + tid < n_reqs) req_stage[tid] = profiles[r + tid];
+            __syncthreads();
+        }
+        const int profile = req_stage[r & (MIG_THREADS - 1)];
         uint32_t key = 0xFFFFFFFFu;
         if (profile >= 1 && profile <= KGWE_MIG_PROFILES) {
             const int geo = mig_geo(profile);
