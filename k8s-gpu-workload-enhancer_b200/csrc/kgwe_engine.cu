@@ -909,8 +909,8 @@ int kgwe_mig_pack(kgwe_engine* e, kgwe_mig_gpu* gpus, uint32_t n_gpus, const uin
         for (uint32_t i = 0; i < n_reqs; ++i) { memset(&out[i], 0, sizeof out[i]); out[i].gpu_idx = KGWE_NO_NODE; out[i].profile = profiles[i]; }
         return KGWE_OK;
     }
-    const size_t smem = (size_t)MIG_GEOS * 256 + 33 * 4 + 2 * (size_t)n_gpus;
-    if (smem > 200 * 1024 || n_gpus >= (1u << 24)) return fail(e, KGWE_ERR_TOO_LARGE, "kgwe_mig_pack: %u GPUs exceed the single-CTA table (max ~100k per call; shard by GPU)", n_gpus);
+    const size_t smem = (size_t)MIG_GEOS * 256 + 36 * 4 + 10 * (size_t)MIG_THREADS * 4 + (size_t)MIG_THREADS * 2 + 2 * (size_t)n_gpus;
+    if (smem > 220 * 1024 || n_gpus >= (1u << 24)) return fail(e, KGWE_ERR_TOO_LARGE, "kgwe_mig_pack: %u GPUs exceed the single-CTA table (max ~85k per call; shard by GPU)", n_gpus);
     CU(e, cudaSetDevice(e->cfg.device));
     cudaStream_t s = e->stream;
     static_assert(sizeof(kgwe_mig_gpu) == 4 && sizeof(kgwe_mig_assignment) == 8 && sizeof(kgwe_mig_op) == 8, "MIG ABI sizes");

@@ -32,25 +32,29 @@ __host__ __device__ inline uint32_t mig_best(uint32_t occ, int geo) {
     return best;
 }
 
-// K4: one persistent CTA.  Occupancy bytes and the (geometry, occupancy) -> best-placement table
-// live in shared memory; per request every thread scans its GPUs (stride = block size), a block-wide
-// min picks (cost, gpu, start), the owner commits.  Key = cost << 27 | gpu << 3 | start.
+// K4: one persistent CTA.  Per-GPU state words (enabled/class << 8 | occupancy) and the
+// (geometry, occupancy) -> best-placement table live in shared memory.  Thread t owns GPUs t, t+1024, ...
+// and caches, per (class, geometry), the best key among them; a commit only invalidates the owner thread's
+// five cached keys of that class, so a request costs one cached read per thread (plus a 10-GPU rescan by
+// the few threads whose cache is stale), a block-wide min of cost << 27 | gpu << 3 | start, and the commit.
 constexpr int MIG_THREADS = 1024;
 __global__ void __launch_bounds__(MIG_THREADS, 1)
 mig_pack_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uint8_t* __restrict__ profiles, uint32_t n_reqs,
                 kgwe_mig_assignment* __restrict__ out) {
     extern __shared__ unsigned char msm[];
-    uint8_t* lut = msm;                               // [5][256]
-    uint32_t* wmin = reinterpret_cast<uint32_t*>(msm + MIG_GEOS * 256);   // [32] + [1] winner
-    uint8_t* occ = msm + MIG_GEOS * 256 + 33 * 4;     // [n_gpus]
-    uint8_t* meta = occ + n_gpus;                     // [n_gpus]: bit0 enabled, bit1 class
-    __shared__ uint8_t req_stage[MIG_THREADS];        // the next 1024 request profiles (no global-memory latency per request)
+    uint8_t* lut = msm;                                                             // [5][256]
+    uint32_t* wmin = reinterpret_cast<uint32_t*>(msm + MIG_GEOS * 256);             // [32] + [1] winner
+    uint32_t* cache = wmin + 36;                                                    // [10][1024] best key per (class*5 + geometry, thread)
+    uint16_t* stale = reinterpret_cast<uint16_t*>(cache + 10 * MIG_THREADS);        // [1024] bit ci: cache[ci][t] must be recomputed
+    uint16_t* state = stale + MIG_THREADS;                                          // [n_gpus]
+    __shared__ uint8_t req_stage[MIG_THREADS];        // the next 1024 request profiles
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int i = tid; i < MIG_GEOS * 256; i += MIG_THREADS) lut[i] = (uint8_t)mig_best((uint32_t)(i & 255), i >> 8);
     for (uint32_t g = tid; g < n_gpus; g += MIG_THREADS) {
         const kgwe_mig_gpu v = gpus[g];
-        occ[g] = v.occ; meta[g] = (uint8_t)((v.enabled ? 1 : 0) | ((v.cls & 1) << 1));
+        state[g] = (uint16_t)(((v.enabled ? 1 : 0) | ((v.cls & 1) << 1)) << 8 | v.occ);
     }
+    stale[tid] = 0x3FF;
     __syncthreads();
     for (uint32_t r = 0; r < n_reqs; ++r) {
         if ((r & (MIG_THREADS - 1)) == 0) {           // refill the staged profiles (the loop's trailing barrier orders this)
@@ -60,16 +64,21 @@ mig_pack_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uint8_t*
         const int profile = req_stage[r & (MIG_THREADS - 1)];
         uint32_t key = 0xFFFFFFFFu;
         if (profile >= 1 && profile <= KGWE_MIG_PROFILES) {
-            const int geo = mig_geo(profile);
-            const uint8_t want = (uint8_t)(1 | (mig_cls(profile) << 1));
-            const uint8_t* row = lut + geo * 256;
-            for (uint32_t g = tid; g < n_gpus; g += MIG_THREADS) {
-                if (meta[g] != want) continue;
-                const uint32_t b = row[occ[g]];
-                if (b == 0xFF) continue;
-                const uint32_t k2 = ((b >> 3) << 27) | (g << 3) | (b & 7);
-                key = k2 < key ? k2 : key;
+            const int geo = mig_geo(profile), ci = mig_cls(profile) * MIG_GEOS + geo;
+            if (stale[tid] >> ci & 1) {
+                const uint32_t want = 1u | ((uint32_t)mig_cls(profile) << 1);
+                const uint8_t* row = lut + geo * 256;
+                uint32_t k1 = 0xFFFFFFFFu;
+                for (uint32_t g = tid; g < n_gpus; g += MIG_THREADS) {
+                    const uint32_t st = state[g];
+                    const uint32_t b = row[st & 0xff];
+                    const uint32_t k2 = ((b >> 3) << 27) | (g << 3) | (b & 7);
+                    if ((st >> 8) == want && b != 0xFF && k2 < k1) k1 = k2;
+                }
+                cache[ci * MIG_THREADS + tid] = k1;
+                stale[tid] = (uint16_t)(stale[tid] & ~(1u << ci));
             }
+            key = cache[ci * MIG_THREADS + tid];
         }
 #pragma unroll
         for (int off = 16; off >= 1; off >>= 1) { const uint32_t o = __shfl_xor_sync(0xffffffffu, key, off); key = o < key ? o : key; }
@@ -80,20 +89,21 @@ mig_pack_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uint8_t*
 #pragma unroll
             for (int off = 16; off >= 1; off >>= 1) { const uint32_t o = __shfl_xor_sync(0xffffffffu, k2, off); k2 = o < k2 ? o : k2; }
             if (lane == 0) {
-                wmin[32] = k2;
                 kgwe_mig_assignment a;
                 if (k2 == 0xFFFFFFFFu) { a.gpu_idx = KGWE_NO_NODE; a.start = a.size = a.cost = 0; a.profile = (uint8_t)profile; }
                 else {
                     const uint32_t g = (k2 >> 3) & 0xFFFFFFu; const int geo = mig_geo(profile);
                     a.gpu_idx = g; a.start = (uint8_t)(k2 & 7); a.size = (uint8_t)mig_size(geo); a.cost = (uint8_t)(k2 >> 27); a.profile = (uint8_t)profile;
-                    occ[g] = (uint8_t)(occ[g] | (((1u << a.size) - 1u) << a.start));
+                    state[g] = (uint16_t)(state[g] | (((1u << a.size) - 1u) << a.start));
+                    const uint32_t owner = g & (MIG_THREADS - 1);
+                    stale[owner] = (uint16_t)(stale[owner] | (0x1Fu << (mig_cls(profile) * MIG_GEOS)));    // that class's five geometries
                 }
                 out[r] = a;
             }
         }
         __syncthreads();
     }
-    for (uint32_t g = tid; g < n_gpus; g += MIG_THREADS) gpus[g].occ = occ[g];
+    for (uint32_t g = tid; g < n_gpus; g += MIG_THREADS) gpus[g].occ = (uint8_t)(state[g] & 0xff);
 }
 
 // Rebalance, device part 1: exclusive rank of every idle GPU (enabled, occ == 0) within its class,
