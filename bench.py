@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--impl", default="kgwe", choices=["kgwe", "reference"])
     ap.add_argument("--scale", type=float, default=1.0, help="shrink N and P (testing only; the default is the full config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--weak", action="store_true", help="weak scaling: 10,000 nodes PER GPU (a larger cluster than the named config; not the default)")
     ap.add_argument("--kernel-only", action="store_true", help="only the device-resident steps (for ncu runs; prints no bench value)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the bounded cpu_baseline sample")
     return ap.parse_args()
@@ -201,6 +202,8 @@ def run_kgwe(args):
     abi = kg.abi
 
     nodes, pods, ledger = kg.synth.config(3, args.scale)
+    if args.weak and world > 1:
+        nodes, _, ledger = kg.synth.config(3, args.scale * world)   # same pod burst, `world` times the nodes
     N, P = len(nodes), len(pods)
     lo, hi = rank * N // world, (rank + 1) * N // world        # contiguous node shard of this rank
     eng = kg.Engine(max_nodes=hi - lo, device=local_rank, node_base=lo)
@@ -429,7 +432,7 @@ def run_kgwe(args):
         achieved = k1_evals * BYTES_PER_EVAL / (k1_ms * 1e-3) / 1e9
         out = {
             "metric": METRIC, "value": cand_total / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(3, args.warmup), "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong",
+            "warmup": max(3, args.warmup), "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak" if (args.weak and world > 1) else "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": WORKLOAD, "n_nodes": N, "n_pods": P, "ledger_entries": int(len(ledger)), "mode": "greedy (reference parity)",
                        "sharding": f"nodes by contiguous range over {world} rank(s)", "exchange": exchange,
