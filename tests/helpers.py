@@ -6,7 +6,7 @@ CUBE_EDGES = [(0, 1), (0, 2), (0, 4), (1, 3), (1, 5), (2, 3), (2, 6), (3, 7), (4
 
 
 def make_node(abi, n_gpus=8, links="full", bw=900.0, free_gib=80, util=0.0, arch=None, numa=None, switch=None,
-              unhealthy=(), inactive=(), pcie_bw=64.0, mig_free=None):
+              unhealthy=(), inactive=(), pcie_bw=64.0, mig_free=None, bw_matrix=None):
     """links: 'full', 'none', or a list of undirected (i, j) edges.  inactive: edges present but IsActive=false."""
     arch = abi.ARCH_HOPPER if arch is None else arch
     n = np.zeros(1, dtype=abi.NODE_IMAGE)[0]
@@ -22,6 +22,11 @@ def make_node(abi, n_gpus=8, links="full", bw=900.0, free_gib=80, util=0.0, arch
             n["nvl_present"][a] |= 1 << b
             if (i, j) not in inactive and (j, i) not in inactive:
                 n["nvl_active"][a] |= 1 << b
+    if bw_matrix is not None:          # directed overrides: bw_matrix[i][j] = GPU i's entry for GPU j (None keeps the default)
+        for i, row in enumerate(bw_matrix):
+            for j, v in enumerate(row):
+                if v is not None and i != j:
+                    n["nvl_bw"][i][j] = v
     for g in range(n_gpus):
         n["pcie_bw"][g] = pcie_bw
         n["free_bytes"][g] = (free_gib[g] if isinstance(free_gib, (list, tuple)) else free_gib) * GIB
