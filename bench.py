@@ -55,6 +55,17 @@ def parse():
     return ap.parse_args()
 
 
+def measured_limits(n_gpus, scale):
+    """What actually bounds K1 according to the committed ncu capture (single-GPU full-size workload only)."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["score_kernel"]
+        if n_gpus == t["n_gpus"] and scale == 1.0:
+            return {k: t[k] for k in ("warp_instructions_per_evaluation", "issue_active_pct", "shared_data_pipe_pct", "alu_pipe_pct", "note")}
+    except Exception:
+        pass
+    return None
+
+
 def measured_traffic(n_gpus, scale):
     """DRAM bytes per score_kernel launch from the committed ncu --set full capture (profiles/traffic.json),
     valid for the full-size single-GPU workload only."""
@@ -444,7 +455,7 @@ def run_kgwe(args):
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(world, args.scale),
                          "kernel": "kgwe::score_kernel", "ms_per_launch": k1_ms, "evaluations_per_launch": k1_evals,
-                         "bytes_per_evaluation": BYTES_PER_EVAL, "peak_source": peak_src,
+                         "bytes_per_evaluation": BYTES_PER_EVAL, "peak_source": peak_src, "actual_limits": measured_limits(world, args.scale),
                          "traffic_unit": "bytes of DRAM read+write per launch (ncu, profiles/traffic.json)",
                          "note": "achieved = algorithmic bytes (SURVEY 8d); the 7.68 MB node image is L2-resident across the pods of a launch, so real DRAM traffic is ~1.6 GB (the score matrix) and frac > 1 is expected: the kernel is instruction-issue bound (profiles/README.md)"},
             "clocks": clk,
