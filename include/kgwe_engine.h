@@ -390,6 +390,15 @@ int kgwe_topology_hint_batch(kgwe_engine* e, const kgwe_hint_req* reqs, uint32_t
  * out gets one int32 per record 0..n_nodes-1 (absent records: 0). */
 int kgwe_topology_gauges(kgwe_engine* e, int32_t* out, uint32_t n_nodes);
 
+/* Checkpoint / resume of the engine state (cluster image + ledger).  The reference keeps its ledger
+ * in memory only (scheduler.go:29) and rebuilds topology from NVML/Kubernetes; a scheduler that
+ * restarts can use these to come back without replaying every event.  The blob is opaque,
+ * versioned and self-describing; kgwe_snapshot_load replaces image and ledger of an engine whose
+ * max_nodes is large enough (weights / normalisation stay those of the loading engine). */
+int kgwe_snapshot_size(kgwe_engine* e, uint64_t* bytes);
+int kgwe_snapshot_save(kgwe_engine* e, void* buf, uint64_t capacity, uint64_t* written);
+int kgwe_snapshot_load(kgwe_engine* e, const void* buf, uint64_t len);
+
 /* Read one record back (device -> host) in ABI layout, ledger fields included. */
 int kgwe_node_read(kgwe_engine* e, uint32_t local_idx, kgwe_node_image* out);
 

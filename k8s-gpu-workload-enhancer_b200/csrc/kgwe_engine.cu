@@ -978,6 +978,64 @@ int kgwe_mig_rebalance(kgwe_engine* e, const kgwe_mig_gpu* gpus, uint32_t n_gpus
     return KGWE_OK;
 }
 
+namespace {
+struct SnapHeader { uint32_t magic, version, n_nodes, n_present; uint64_t n_ledger; uint32_t record_bytes, entry_bytes; };
+struct SnapEntry { uint64_t wl_id; uint32_t node; uint32_t mask; };
+constexpr uint32_t kSnapMagic = 0x4B475745u, kSnapVersion = 1;
+uint64_t snapshot_bytes(const kgwe_engine* e) { return sizeof(SnapHeader) + (uint64_t)e->n_nodes * sizeof(DevNode) + (uint64_t)e->ledger.size() * sizeof(SnapEntry); }
+}  // namespace
+
+int kgwe_snapshot_size(kgwe_engine* e, uint64_t* bytes) {
+    if (!e || !bytes) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    *bytes = snapshot_bytes(e);
+    return KGWE_OK;
+}
+
+int kgwe_snapshot_save(kgwe_engine* e, void* buf, uint64_t capacity, uint64_t* written) {
+    if (!e || !buf || !written) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    const uint64_t need = snapshot_bytes(e);
+    if (capacity < need) return fail(e, KGWE_ERR_TOO_LARGE, "snapshot needs %llu bytes, buffer has %llu", (unsigned long long)need, (unsigned long long)capacity);
+    // the pinned mirror is authoritative: every commit of the queue kernels is mirrored before a call returns
+    unsigned char* p = static_cast<unsigned char*>(buf);
+    SnapHeader h{kSnapMagic, kSnapVersion, e->n_nodes, e->n_present, (uint64_t)e->ledger.size(), (uint32_t)sizeof(DevNode), (uint32_t)sizeof(SnapEntry)};
+    memcpy(p, &h, sizeof h); p += sizeof h;
+    memcpy(p, e->h_nodes, (size_t)e->n_nodes * sizeof(DevNode)); p += (size_t)e->n_nodes * sizeof(DevNode);
+    std::vector<SnapEntry> entries; entries.reserve(e->ledger.size());
+    for (auto& kv : e->ledger) entries.push_back(SnapEntry{kv.first, kv.second.node, kv.second.mask});
+    std::sort(entries.begin(), entries.end(), [](const SnapEntry& a, const SnapEntry& b) { return a.wl_id < b.wl_id; });   // deterministic blob
+    memcpy(p, entries.data(), entries.size() * sizeof(SnapEntry));
+    *written = need;
+    return KGWE_OK;
+}
+
+int kgwe_snapshot_load(kgwe_engine* e, const void* buf, uint64_t len) {
+    if (!e || !buf) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    SnapHeader h;
+    if (len < sizeof h) return fail(e, KGWE_ERR_INVALID_ARG, "snapshot too short");
+    memcpy(&h, buf, sizeof h);
+    if (h.magic != kSnapMagic || h.version != kSnapVersion || h.record_bytes != sizeof(DevNode) || h.entry_bytes != sizeof(SnapEntry))
+        return fail(e, KGWE_ERR_INVALID_ARG, "not a kgwe snapshot of this version");
+    if (h.n_nodes > e->cfg.max_nodes) return fail(e, KGWE_ERR_OUT_OF_RANGE, "snapshot has %u nodes, engine holds %u", h.n_nodes, e->cfg.max_nodes);
+    if (len != sizeof h + (uint64_t)h.n_nodes * sizeof(DevNode) + h.n_ledger * sizeof(SnapEntry)) return fail(e, KGWE_ERR_INVALID_ARG, "snapshot length mismatch");
+    const unsigned char* p = static_cast<const unsigned char*>(buf) + sizeof h;
+    const uint32_t old_n = e->n_nodes;
+    memcpy(e->h_nodes, p, (size_t)h.n_nodes * sizeof(DevNode)); p += (size_t)h.n_nodes * sizeof(DevNode);
+    for (uint32_t i = h.n_nodes; i < old_n; ++i) memset(&e->h_nodes[i], 0, sizeof(DevNode));
+    e->ledger.clear();
+    for (uint64_t i = 0; i < h.n_ledger; ++i) {
+        SnapEntry en; memcpy(&en, p + i * sizeof(SnapEntry), sizeof en);
+        if (en.node >= e->cfg.max_nodes) return fail(e, KGWE_ERR_INVALID_ARG, "snapshot ledger entry names node %u", en.node);
+        e->ledger[en.wl_id] = LedgerEntry{en.node, (uint8_t)en.mask};
+    }
+    e->n_nodes = std::max(h.n_nodes, old_n);          // high-water mark never shrinks (absent records score as absent)
+    e->n_present = 0;
+    for (uint32_t i = 0; i < e->n_nodes; ++i) { if (e->h_nodes[i].flags & NODE_PRESENT) e->n_present++; mark_dirty(e, i); }
+    return KGWE_OK;
+}
+
 int kgwe_node_read(kgwe_engine* e, uint32_t idx, kgwe_node_image* out) {
     if (!e || !out) return KGWE_ERR_INVALID_ARG;
     std::lock_guard<std::mutex> lk(e->mu);

@@ -158,6 +158,19 @@ class Engine:
         self._check(self.lib.kgwe_topology_gauges(self.h, abi.ptr(out), n_nodes))
         return out
 
+    def snapshot(self):
+        """Checkpoint: cluster image + ledger as an opaque blob (bytes)."""
+        n = C.c_uint64(0)
+        self._check(self.lib.kgwe_snapshot_size(self.h, C.byref(n)))
+        buf = np.zeros(n.value, dtype=np.uint8)
+        w = C.c_uint64(0)
+        self._check(self.lib.kgwe_snapshot_save(self.h, abi.ptr(buf), n.value, C.byref(w)))
+        return buf[: w.value].tobytes()
+
+    def restore(self, blob):
+        buf = np.frombuffer(blob, dtype=np.uint8).copy()
+        self._check(self.lib.kgwe_snapshot_load(self.h, abi.ptr(buf), len(buf)))
+
     def stats(self):
         s = abi.Stats()
         self._check(self.lib.kgwe_get_stats(self.h, C.byref(s)))

@@ -584,3 +584,35 @@ def test_topk_merge_device_equals_host_merge(kg):
         exp = union[:K]
         assert [(int(x["total"]), int(x["node_idx"])) for x in want[p] if x["node_idx"] != abi.NO_NODE] == exp
     eng.close()
+
+
+def test_snapshot_and_restore(kg, orc):
+    """Checkpoint / resume: image + ledger saved after a queue has run, loaded into a fresh engine, and both
+    engines must keep answering identically (stateless scores, further scheduling, releases)."""
+    abi, synth = kg.abi, kg.synth
+    nodes, pods, led = synth.config(2, 0.08)
+    eng = engine_for(kg, nodes, led)
+    eng.schedule_queue(pods[:40])
+    eng.remove_node(5)
+    blob = eng.snapshot()
+    assert blob == eng.snapshot()                                   # deterministic
+    fresh = kg.Engine(max_nodes=len(nodes) + 10)
+    fresh.restore(blob)
+    assert fresh.stats()["n_allocations"] == eng.stats()["n_allocations"] and fresh.stats()["n_nodes"] == eng.stats()["n_nodes"]
+    a, ta = eng.score_batch(pods[40:70], len(nodes), want_scores=True, topk=3)
+    b, tb = fresh.score_batch(pods[40:70], len(nodes), want_scores=True, topk=3)
+    assert a.tobytes() == b.tobytes() and ta.tobytes() == tb.tobytes()
+    da, db = eng.schedule_queue(pods[40:70]), fresh.schedule_queue(pods[40:70])
+    assert da.tobytes() == db.tobytes()
+    wl = int(pods[41]["wl_id"])
+    if da[1]["node_idx"] != abi.NO_NODE:
+        eng.release(wl); fresh.release(wl)
+    a, _ = eng.score_batch(pods[:10], len(nodes), want_scores=True)
+    b, _ = fresh.score_batch(pods[:10], len(nodes), want_scores=True)
+    assert a.tobytes() == b.tobytes()
+    small = kg.Engine(max_nodes=4)
+    with pytest.raises(kg.EngineError):
+        small.restore(blob)                                         # too many nodes for this engine
+    with pytest.raises(kg.EngineError):
+        fresh.restore(blob[:100])
+    eng.close(); fresh.close(); small.close()
