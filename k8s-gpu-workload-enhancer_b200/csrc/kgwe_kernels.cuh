@@ -511,7 +511,7 @@ schedule_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict
             // this group owns the winner: tryScheduleOnNode + recordAllocation (scheduler.go:625-653, 695-707)
             DevNode* rec = nodes + keepnode;
             if ((lane & 7) == 0) {
-                store_placement(out + p, P.node_base + keepnode, keep, est_bandwidth(rec, keep.order, (int)((keep.order >> 24) & 15)));
+                store_placement(out + p, P.node_base + keepnode, keep, 0.0);     // EstimatedBandwidth: est_bandwidth_kernel, after the queue
                 rec->allocated_mask = (uint8_t)(rec->allocated_mask | keep.mask);
                 rec->n_allocs = rec->n_allocs + 1;
             }
@@ -648,7 +648,7 @@ schedule_tile_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __res
         } else if (win == mykey) {
             // this group owns the winner: tryScheduleOnNode + recordAllocation (scheduler.go:625-653, 695-707)
             if (j == 0) {
-                store_placement(out + p, P.node_base + node, o, est_bandwidth(rec, o.order, (int)((o.order >> 24) & 15)));
+                store_placement(out + p, P.node_base + node, o, 0.0);     // EstimatedBandwidth is filled in after the queue (est_bandwidth_kernel)
                 rec->allocated_mask = (uint8_t)(rec->allocated_mask | o.mask);
                 rec->n_allocs = rec->n_allocs + 1;
                 nodes[node].allocated_mask = rec->allocated_mask;       // the image in HBM follows
@@ -664,6 +664,19 @@ schedule_tile_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __res
 #pragma unroll
     for (int off = 16; off >= 8; off >>= 1) { cand += __shfl_xor_sync(0xffffffffu, cand, off); evals += __shfl_xor_sync(0xffffffffu, evals, off); }
     if (lane == 0 && counters) { if (evals) atomicAdd(&counters[0], evals); if (cand) atomicAdd(&counters[1], cand); }
+}
+
+// EstimatedBandwidth of the queue's decisions (scheduler.go:656-692), one thread per decision.  It
+// depends only on link data that commits never change, so it is taken off the per-workload critical
+// path of the queue kernels and computed for all decisions at once afterwards.
+__global__ void __launch_bounds__(128)
+est_bandwidth_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, uint32_t node_base, kgwe_placement* __restrict__ pls, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t node = pls[i].node_idx;
+    if (node == KGWE_NO_NODE || node - node_base >= n_nodes) return;
+    const uint32_t order = pls[i].order;
+    pls[i].est_bandwidth_gbps = est_bandwidth(nodes + (node - node_base), order, (int)((order >> 24) & 15));
 }
 
 // ---------------------------------------------------------------------------------------
