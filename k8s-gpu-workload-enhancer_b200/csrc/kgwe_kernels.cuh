@@ -44,6 +44,17 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t phase) {
     }
 }
 
+// Arrival counter of the queue kernels' grid-wide step: release on the increment, acquire on the poll,
+// instead of two full __threadfence()s around relaxed accesses.
+__device__ __forceinline__ void arrive_release(unsigned int* ctr) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(ctr) : "memory");
+}
+__device__ __forceinline__ unsigned int load_acquire(const unsigned int* ctr) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+    return v;
+}
+
 __device__ __forceinline__ kgwe_pod_req load_pod(const kgwe_pod_req* pods, uint32_t p) {
     const uint4* src = reinterpret_cast<const uint4*>(pods + p);
     union { uint4 v[2]; kgwe_pod_req r; } u;
@@ -497,10 +508,8 @@ schedule_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict
             unsigned long long b = wmax[0];
             for (int w = 1; w < SCORE_THREADS / 32; ++w) b = wmax[w] > b ? wmax[w] : b;
             if (b) atomicMax(&best[p], b);
-            __threadfence();
-            atomicAdd(&arrive[p], 1u);
-            while (*reinterpret_cast<volatile unsigned int*>(&arrive[p]) < gridDim.x) { }
-            __threadfence();
+            arrive_release(&arrive[p]);                       // orders the max before the arrival (release)
+            while (load_acquire(&arrive[p]) < gridDim.x) { }   // ... and the winner read after it (acquire)
             winner = *reinterpret_cast<volatile unsigned long long*>(&best[p]);
         }
         __syncthreads();
@@ -635,10 +644,8 @@ schedule_tile_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __res
             unsigned long long b = wmax[0];
             for (int w = 1; w < SCORE_THREADS / 32; ++w) b = wmax[w] > b ? wmax[w] : b;
             if (b) atomicMax(&best[p], b);
-            __threadfence();
-            atomicAdd(&arrive[p], 1u);
-            while (*reinterpret_cast<volatile unsigned int*>(&arrive[p]) < gridDim.x) { }
-            __threadfence();
+            arrive_release(&arrive[p]);                       // orders the max before the arrival (release)
+            while (load_acquire(&arrive[p]) < gridDim.x) { }   // ... and the winner read after it (acquire)
             winner = *reinterpret_cast<volatile unsigned long long*>(&best[p]);
         }
         __syncthreads();
