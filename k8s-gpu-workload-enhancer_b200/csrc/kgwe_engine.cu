@@ -212,6 +212,22 @@ size_t score_smem_bytes(uint32_t pods_per_chunk, bool tables = false, bool memo 
            (size_t)pods_per_chunk * 8 + 16;
 }
 
+// Pod chunks of a K1 launch: whole waves of co-resident CTAs (2 per SM; 1 with subset tables), as few waves
+// as keep the per-CTA arg-max table within bounds - every CTA pays the tile set-up once, so fewer, longer
+// CTAs amortise it better, and whole waves avoid a ragged tail (all CTAs do the same amount of work).
+void plan_pod_chunks(const kgwe_engine* e, uint32_t n_pods, uint32_t n_tiles, bool tables, uint32_t* chunks_out, uint32_t* ppc_out) {
+    const uint32_t slots = (uint32_t)e->sm_count * (tables ? 1u : 2u);
+    uint32_t chunks = 1, ppc = n_pods;
+    for (uint32_t waves = 1; waves <= 64; ++waves) {
+        chunks = std::max(1u, std::min(n_pods, slots * waves / n_tiles));
+        ppc = (n_pods + chunks - 1) / chunks;
+        if (ppc <= MAX_PODS_PER_CHUNK && (waves >= 2 || n_pods <= 64)) break;
+    }
+    if (ppc > MAX_PODS_PER_CHUNK) ppc = MAX_PODS_PER_CHUNK;
+    *ppc_out = ppc;
+    *chunks_out = (n_pods + ppc - 1) / ppc;
+}
+
 // Launch K1 (+K1b / K2) for n_pods pods whose descriptors, hint rows and outputs are in
 // device memory.  d_scores may be null unless topk > 1.
 int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const uint8_t* d_hint,
@@ -224,19 +240,9 @@ int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, co
     }
     if (n_pods == 0 || e->n_nodes == 0) return KGWE_OK;
     const uint32_t n_tiles = (e->n_nodes + TILE_NODES - 1) / TILE_NODES;
-    // pod chunks: whole waves of co-resident CTAs (2 per SM; 1 with subset tables), as few waves as keep
-    // the per-CTA arg-max table within bounds - every CTA pays the tile set-up once, so fewer, longer
-    // CTAs amortise it better, and whole waves avoid a ragged tail (all CTAs do the same amount of work)
     tables = tables || (e->cfg.flags & KGWE_CFG_SUBSET_TABLES);
-    const uint32_t slots = (uint32_t)e->sm_count * (tables ? 1u : 2u);
-    uint32_t chunks = 1, ppc = n_pods;
-    for (uint32_t waves = 1; waves <= 64; ++waves) {
-        chunks = std::max(1u, std::min(n_pods, slots * waves / n_tiles));
-        ppc = (n_pods + chunks - 1) / chunks;
-        if (ppc <= MAX_PODS_PER_CHUNK && (waves >= 2 || n_pods <= 64)) break;
-    }
-    if (ppc > MAX_PODS_PER_CHUNK) ppc = MAX_PODS_PER_CHUNK;
-    chunks = (n_pods + ppc - 1) / ppc;
+    uint32_t chunks, ppc;
+    plan_pod_chunks(e, n_pods, n_tiles, tables, &chunks, &ppc);
     if (chunks > 65535u) return fail(e, KGWE_ERR_TOO_LARGE, "too many pods in one launch (%u)", n_pods);
     unsigned long long* best = nullptr;
     if (topk == 1) {
@@ -475,15 +481,8 @@ int kgwe_score_batch_device_p2p(kgwe_engine* e, const kgwe_pod_req* d_pods, uint
     // K1 exactly as in launch_score(topk = 1), then the fused finalise + scatter
     const uint32_t n_tiles = (e->n_nodes + TILE_NODES - 1) / TILE_NODES;
     const bool tables = e->cfg.flags & KGWE_CFG_SUBSET_TABLES, memo = e->cfg.flags & KGWE_CFG_MEMOISE_GROUPS;
-    const uint32_t slots = (uint32_t)e->sm_count * (tables ? 1u : 2u);
-    uint32_t chunks = 1, ppc = n_pods;
-    for (uint32_t waves = 1; waves <= 64; ++waves) {
-        chunks = std::max(1u, std::min(n_pods, slots * waves / n_tiles));
-        ppc = (n_pods + chunks - 1) / chunks;
-        if (ppc <= MAX_PODS_PER_CHUNK && (waves >= 2 || n_pods <= 64)) break;
-    }
-    if (ppc > MAX_PODS_PER_CHUNK) ppc = MAX_PODS_PER_CHUNK;
-    chunks = (n_pods + ppc - 1) / ppc;
+    uint32_t chunks, ppc;
+    plan_pod_chunks(e, n_pods, n_tiles, tables, &chunks, &ppc);
     if (chunks > 65535u) return fail(e, KGWE_ERR_TOO_LARGE, "too many pods in one launch (%u)", n_pods);
     {
         const size_t had = e->d_best.cap;
