@@ -146,7 +146,7 @@ mig_rank_kernel(const kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, uint32_t
     if (tid < 2) idle_count[tid] = carry[tid];
 }
 
-// Plan computed on the host from the idle counts and the targets (same code in the oracle).
+// Plan computed on the host from the idle counts and the targets (the CPU checker restates the same rule independently).
 struct MigPlan {
     uint32_t first_rank[2][MIG_GEOS + 1];   // class c: ranks [first_rank[c][q], first_rank[c][q+1]) get geometry q
     uint32_t op_base[2][MIG_GEOS];          // op index of the first GPU of (class, geometry)
@@ -174,7 +174,7 @@ mig_emit_kernel(const kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const ui
     }
 }
 
-// Host side of the plan (shared by engine and oracle through this header): GPUs per profile from
+// Host side of the plan: GPUs per profile from
 // the targets, largest-remainder rounding, ties to the lowest profile id.
 inline void mig_make_plan(const uint32_t idle[2], const double* target, MigPlan& plan, uint32_t* n_ops, uint32_t* supply) {
     uint32_t ops = 0;
