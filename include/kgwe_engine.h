@@ -226,7 +226,10 @@ int kgwe_alloc_release(kgwe_engine* e, uint64_t wl_id);
  *   out_scores   nullable; P x n_nodes records, row-major by pod
  *   topk         0..KGWE_MAX_TOPK; out_topk gets P x topk placements, best first,
  *                unused slots have node_idx == KGWE_NO_NODE
- * Host pointers; copies are done by the engine inside the call. */
+ * Host pointers; copies are done by the engine inside the call.  n_nodes here is kgwe_stats.n_nodes
+ * (highest index ever upserted + 1); removed records give all-zero score records.  Calls with at
+ * most 32 pods that ask only for the best placement (no matrix, topk == 1) take a single-launch,
+ * copy-free path meant for per-pod Prioritize latency. */
 int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods,
                      const uint8_t* hint_bitmap, kgwe_node_score* out_scores,
                      uint32_t topk, kgwe_placement* out_topk);
