@@ -126,3 +126,17 @@ def test_faithful_equals_indexed_on_synthetic(kg, orc):
         db = orc.schedule_queue(abi, nodes, led, pods, hint=hint, mode=1)
         assert da[0].tobytes() == db[0].tobytes()
         assert da[1].tobytes() == db[1].tobytes()
+
+
+def test_contributing_md_snippet_expectation(kg, orc):
+    """The only expected value the reference itself writes down for this path: CONTRIBUTING.md:291-322 sketches
+    a test 'optimal NVLink placement' - a node with 8 NVLink-connected GPUs, GPUCount 4, NVLinkOptimal - and
+    requires score >= 80.  (It calls functions that do not exist in the reference; the inequality is what pins.)"""
+    abi = kg.abi
+    nodes = np.array([make_node(abi)], dtype=abi.NODE_IMAGE)                      # createTestNode(8, true)
+    pods = np.array([make_pod(abi, 4, pref="NVLinkOptimal", mem=0)], dtype=abi.POD_REQ)
+    for mode in (0, 1):
+        s, _, _ = orc.score_batch(abi, nodes, None, pods, mode=mode)
+        assert int(s[0, 0]["topology"]) >= 80 and int(s[0, 0]["total"]) >= 80
+    # docs/architecture.md:353-358 quotes ranges "NVLink 50-100, NUMA 50-90, PCIe 50-80"; the code's fallbacks are
+    # 30 / 50 / 40 and NVLink exceeds 100 above 900 GB/s (KAT-3) - the code, not the prose, is what is restated.
