@@ -1,0 +1,71 @@
+"""Differential fuzzing: random clusters / pod queues with every feature switched on at random, engine vs
+oracle (indexed build), stateless matrix + top-k and the stateful queue, over many seeds.
+  python tools/fuzz_parity.py [n_seeds] [first_seed]"""
+import os, sys
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import __graft_entry__ as entry
+
+
+def one_seed(kg, orc, seed):
+    abi, synth = kg.abi, kg.synth
+    rng = synth.SplitMix64(seed * 7919 + 13)
+    u = rng.uniform(16)
+    N = int(40 + u[0] * 400)
+    P = int(40 + u[1] * 200)
+    nodes = synth.make_cluster(N, "mixed" if u[2] < 0.8 else "dgx", seed=seed, unhealthy_frac=u[3] * 0.3, inactive_link_frac=u[4] * 0.2,
+                               partial_node_frac=u[5] * 0.5, mig_frac=u[6])
+    kind = int(u[7] * 4)
+    if kind == 1:      # fractional, asymmetric bandwidths on some nodes (FP64 path)
+        frac = rng.uniform(N) < 0.4
+        jit = 0.5 + rng.uniform(N * 64).reshape(N, 8, 8)
+        nodes["nvl_bw"] = np.where(frac[:, None, None], nodes["nvl_bw"] * jit, nodes["nvl_bw"])
+    elif kind == 2:    # whole-number but irregular, asymmetric bandwidths (integer path, no common unit)
+        jit = rng.randint(1, 2000, N * 64).reshape(N, 8, 8).astype(np.float64)
+        nodes["nvl_bw"] = np.where(nodes["nvl_bw"] > 0, jit, 0.0)
+    elif kind == 3:    # zero-bandwidth links here and there
+        z = rng.uniform(N * 64).reshape(N, 8, 8) < 0.15
+        nodes["nvl_bw"] = np.where(z, 0.0, nodes["nvl_bw"])
+    nodes["numa"] = rng.randint(-2, 2, N * 8).reshape(N, 8).astype(np.int8)
+    nodes["pcie_switch"] = rng.randint(0, 3, N * 8).reshape(N, 8).astype(np.uint8)
+    nodes["util"] = np.floor(rng.uniform(N * 8).reshape(N, 8) * 400) / 4.0
+    prefs = rng.uniform(5) + 0.05
+    pods = synth.make_pods(P, seed=seed, k_lo=0, k_hi=9, pref_probs=tuple(prefs / prefs.sum()), arch_frac=u[8] * 0.6,
+                           minbw_choices=(0.0, 0.0, 200.0, 650.0, 1000.0), mig_frac=u[9] * 0.5)
+    pods["min_memory_gb"] = rng.randint(0, 200, P)
+    exh = rng.uniform(P) < u[10] * 0.5
+    pods["flags"] = np.where(exh, abi.POD_EXHAUSTIVE, 0).astype(np.uint8)
+    led = synth.make_ledger(nodes, u[11] * 0.8, seed=seed)
+    hint = synth.make_hint(P, N, u[12] * 0.1, seed=seed) if u[13] < 0.5 else None
+    flags = [0, abi.CFG_MEMOISE_GROUPS, abi.CFG_SUBSET_TABLES, abi.CFG_MEMOISE_GROUPS | abi.CFG_SUBSET_TABLES][int(u[14] * 4)]
+    eng = kg.Engine(max_nodes=N, flags=flags)
+    eng.upsert_nodes(nodes)
+    eng.seed_ledger(led)
+    topk = [1, 2, 5, 16][int(u[15] * 4)]
+    s, t = eng.score_batch(pods, N, hint=hint, want_scores=True, topk=topk)
+    o, ot, _ = orc.score_batch(abi, nodes, led, pods, hint=hint, want_scores=True, topk=topk, threads=4)
+    assert s.tobytes() == o.tobytes(), f"seed {seed}: score matrix differs"
+    assert t.tobytes() == ot.tobytes(), f"seed {seed}: top-{topk} differs"
+    for p0 in range(0, min(P, 24), 3):       # latency path
+        _, t1 = eng.score_batch(pods[p0:p0 + 3], N, hint=None if hint is None else hint[p0:p0 + 3], want_scores=False, topk=1)
+        _, o1, _ = orc.score_batch(abi, nodes, led, pods[p0:p0 + 3], hint=None if hint is None else hint[p0:p0 + 3], want_scores=False, topk=1)
+        assert t1.tobytes() == o1.tobytes(), f"seed {seed}: latency path differs at pod {p0}"
+    d = eng.schedule_queue(pods, hint=hint)
+    od, oled, _ = orc.schedule_queue(abi, nodes, led, pods, hint=hint)
+    assert d.tobytes() == od.tobytes(), f"seed {seed}: queue decisions differ"
+    s2, _ = eng.score_batch(pods[:8], N, want_scores=True)
+    o2, _, _ = orc.score_batch(abi, nodes, oled, pods[:8], want_scores=True)
+    assert s2.tobytes() == o2.tobytes(), f"seed {seed}: image after the queue differs"
+    eng.close()
+    return N, P, kind, flags
+
+
+if __name__ == "__main__":
+    n = int(sys.argv[1]) if len(sys.argv) > 1 else 40
+    first = int(sys.argv[2]) if len(sys.argv) > 2 else 1
+    kg = entry.load_package()
+    from oracle import binding as orc
+    for seed in range(first, first + n):
+        N, P, kind, flags = one_seed(kg, orc, seed)
+        print(f"seed {seed}: ok ({N} nodes, {P} pods, bandwidth kind {kind}, engine flags {flags})", flush=True)
+    print(f"fuzz_parity: {n} seeds bit-exact")
