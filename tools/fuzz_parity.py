@@ -56,6 +56,23 @@ def one_seed(kg, orc, seed):
     s2, _ = eng.score_batch(pods[:8], N, want_scores=True)
     o2, _, _ = orc.score_batch(abi, nodes, oled, pods[:8], want_scores=True)
     assert s2.tobytes() == o2.tobytes(), f"seed {seed}: image after the queue differs"
+    t = eng.placement_terms(d)
+    ot = orc.placement_terms(abi, nodes, d)
+    assert t.tobytes() == ot.tobytes(), f"seed {seed}: side terms differ"
+    reqs = synth.make_hint_reqs(64, seed=seed)
+    assert eng.topology_hints(reqs).tobytes() == orc.topology_hints(abi, nodes, reqs).tobytes(), f"seed {seed}: topology hints differ"
+    assert np.array_equal(eng.topology_gauges(N), orc.topology_gauges(abi, nodes)), f"seed {seed}: gauges differ"
+    eng.close()
+    # gangs on a fresh engine: ragged gang sizes, all-or-nothing with rollbacks
+    eng = kg.Engine(max_nodes=N, flags=flags)
+    eng.upsert_nodes(nodes)
+    eng.seed_ledger(led)
+    sizes = rng.randint(1, 9, P)
+    gang_of = np.repeat(np.arange(P), sizes)[:P].astype(np.uint32)
+    g = eng.schedule_gangs(pods, gang_of, hint=hint)
+    og, ogl = orc.schedule_gangs(abi, nodes, led, pods, gang_of, hint=hint)
+    assert g.tobytes() == og.tobytes(), f"seed {seed}: gang decisions differ"
+    assert eng.stats()["n_allocations"] == len(ogl), f"seed {seed}: ledger size after gangs differs"
     eng.close()
     return N, P, kind, flags
 
