@@ -238,7 +238,17 @@ int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, co
         tail.out = d_topk; tail.done = e->d_done; tail.flag = e->h_flag; tail.seq = ++e->flag_seq;
         if (n_pods <= 4) { tail.n_inline = n_pods; memcpy(tail.inline_pods, d_pods, (size_t)n_pods * sizeof(kgwe_pod_req)); }   // d_pods is the pinned HOST copy on this path
     }
-    if (n_pods == 0 || e->n_nodes == 0) return KGWE_OK;
+    if (n_pods == 0) return KGWE_OK;
+    if (e->n_nodes == 0) {
+        // empty image (host entry points answer this themselves): every placement is "no node"
+        if (topk && d_topk && !fused_tail) {
+            const size_t n = (size_t)n_pods * topk;
+            no_node_fill_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(d_topk, n);
+            CU(e, cudaGetLastError());
+            e->stats.kernel_launches++;
+        }
+        return KGWE_OK;
+    }
     const uint32_t n_tiles = (e->n_nodes + TILE_NODES - 1) / TILE_NODES;
     tables = tables || (e->cfg.flags & KGWE_CFG_SUBSET_TABLES);
     uint32_t chunks, ppc;
@@ -743,9 +753,11 @@ int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pod
             out[p0 + i] = d;
             if (d.node_idx == KGWE_NO_NODE) { e->stats.failed++; continue; }
             const bool last_overwrites = overwrite && i == np - 1;
-            if (!last_overwrites) { apply_commit(e, pods[p0 + i].wl_id, d); continue; }
+            const auto prev = last_overwrites ? e->ledger.find(pods[p0 + i].wl_id) : e->ledger.end();
+            // (a repeated id whose earlier occurrence found no node has nothing to overwrite)
+            if (prev == e->ledger.end()) { apply_commit(e, pods[p0 + i].wl_id, d); continue; }
             // device already holds the new commit; bring the mirror level, then drop the old entry
-            const uint32_t old_node = e->ledger.find(pods[p0 + i].wl_id)->second.node;
+            const uint32_t old_node = prev->second.node;
             e->ledger.erase(pods[p0 + i].wl_id);
             apply_commit(e, pods[p0 + i].wl_id, d);
             const uint32_t local = d.node_idx - e->cfg.node_base;
@@ -1022,13 +1034,27 @@ int kgwe_snapshot_load(kgwe_engine* e, const void* buf, uint64_t len) {
     if (h.n_nodes > e->cfg.max_nodes) return fail(e, KGWE_ERR_OUT_OF_RANGE, "snapshot has %u nodes, engine holds %u", h.n_nodes, e->cfg.max_nodes);
     if (len != sizeof h + (uint64_t)h.n_nodes * sizeof(DevNode) + h.n_ledger * sizeof(SnapEntry)) return fail(e, KGWE_ERR_INVALID_ARG, "snapshot length mismatch");
     const unsigned char* p = static_cast<const unsigned char*>(buf) + sizeof h;
+    const unsigned char* pl = p + (size_t)h.n_nodes * sizeof(DevNode);
+    // check the whole blob before touching the engine: a rejected snapshot leaves the state as it was
+    for (uint32_t i = 0; i < h.n_nodes; ++i) {
+        DevNode rec; memcpy(&rec, p + (size_t)i * sizeof(DevNode), sizeof rec);
+        if (rec.n_gpus > KGWE_MAX_GPUS) return fail(e, KGWE_ERR_INVALID_ARG, "snapshot record %u: n_gpus %u", i, rec.n_gpus);
+        for (int g = 0; g < KGWE_MAX_GPUS; ++g) {
+            if (!(rec.pcie_bw[g] >= 0.0) || !(rec.pcie_bw[g] <= KGWE_MAX_BW_GBPS) || !std::isfinite(rec.util[g])) return fail(e, KGWE_ERR_INVALID_ARG, "snapshot record %u: GPU %d out of range", i, g);
+            for (int c = 0; c < KGWE_MAX_GPUS; ++c)
+                if (!(rec.bw_in[g][c] >= 0.0) || !(rec.bw_in[g][c] <= KGWE_MAX_BW_GBPS)) return fail(e, KGWE_ERR_INVALID_ARG, "snapshot record %u: link bandwidth out of range", i);
+        }
+    }
+    for (uint64_t i = 0; i < h.n_ledger; ++i) {
+        SnapEntry en; memcpy(&en, pl + i * sizeof(SnapEntry), sizeof en);
+        if (en.node >= e->cfg.max_nodes) return fail(e, KGWE_ERR_INVALID_ARG, "snapshot ledger entry names node %u", en.node);
+    }
     const uint32_t old_n = e->n_nodes;
-    memcpy(e->h_nodes, p, (size_t)h.n_nodes * sizeof(DevNode)); p += (size_t)h.n_nodes * sizeof(DevNode);
+    memcpy(e->h_nodes, p, (size_t)h.n_nodes * sizeof(DevNode));
     for (uint32_t i = h.n_nodes; i < old_n; ++i) memset(&e->h_nodes[i], 0, sizeof(DevNode));
     e->ledger.clear();
     for (uint64_t i = 0; i < h.n_ledger; ++i) {
-        SnapEntry en; memcpy(&en, p + i * sizeof(SnapEntry), sizeof en);
-        if (en.node >= e->cfg.max_nodes) return fail(e, KGWE_ERR_INVALID_ARG, "snapshot ledger entry names node %u", en.node);
+        SnapEntry en; memcpy(&en, pl + i * sizeof(SnapEntry), sizeof en);
         e->ledger[en.wl_id] = LedgerEntry{en.node, (uint8_t)en.mask};
     }
     e->n_nodes = std::max(h.n_nodes, old_n);          // high-water mark never shrinks (absent records score as absent)

@@ -391,6 +391,16 @@ finalize_top1_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, const 
     finalize_one(nodes, n_nodes, pods, p, p < n_pods, hint, hint_row_bytes, best, out, P, threadIdx.x & 31);
 }
 
+// Empty cluster image: every requested placement is "no node" (nothing to score; Schedule then ends in "no eligible nodes found", scheduler.go:138-141).
+__global__ void __launch_bounds__(256)
+no_node_fill_kernel(kgwe_placement* __restrict__ out, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    kgwe_placement z{};
+    z.node_idx = KGWE_NO_NODE;
+    out[i] = z;
+}
+
 // K2: one CTA per pod over that pod's row of the score matrix.
 __global__ void __launch_bounds__(256)
 topk_select_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, const kgwe_node_score* __restrict__ scores,

@@ -160,6 +160,15 @@ def test_edge_cases(kg, orc):
     assert dec[0]["node_idx"] == abi.NO_NODE
     s, t = eng.score_batch(pods[:0], 0, want_scores=True, topk=1)
     assert s.shape == (0, 0)
+    # the device entry point on an empty image writes "no node" placements too (not stale memory)
+    import torch
+    d_pods = torch.from_numpy(pods.view(np.uint8).reshape(1, abi.POD_REQ.itemsize)).cuda()
+    for k in (1, 3):
+        d_top = torch.full((k, abi.PLACEMENT.itemsize), 0x5A, dtype=torch.uint8, device="cuda")
+        eng.score_batch_device(d_pods.data_ptr(), 1, None, None, k, d_top.data_ptr())
+        torch.cuda.synchronize()
+        got = d_top.cpu().numpy().view(abi.PLACEMENT).reshape(-1)
+        assert (got["node_idx"] == abi.NO_NODE).all() and (got["total"] == 0).all() and (got["gpu_mask"] == 0).all()
     # ragged nodes: 0..8 GPUs, all-unhealthy, no links
     nodes = np.array([make_node(abi, n_gpus=g) for g in range(9)] + [make_node(abi, unhealthy=range(8)), make_node(abi, links="none")],
                      dtype=abi.NODE_IMAGE)
@@ -230,6 +239,15 @@ def test_incremental_updates_and_ledger(kg, orc):
     s, _ = eng.score_batch(pods, len(nodes), want_scores=True)
     o, _, _ = orc.score_batch(abi, o_nodes, o_led, pods, want_scores=True)
     assert s[:, keep].tobytes() == o[:, keep].tobytes()
+    # a repeated id whose FIRST occurrence finds no node (9 GPUs asked): nothing to overwrite when the second lands
+    twice = pods[10:14].copy()
+    twice["wl_id"][3] = twice["wl_id"][0]
+    twice["gpu_count"][0] = 9
+    dec = eng.schedule_queue(twice)
+    o_dec2, o_led2, _ = orc.schedule_queue(abi, o_nodes, o_led, twice)
+    assert_same_placements(dec, o_dec2)
+    assert dec[0]["node_idx"] == abi.NO_NODE and dec[3]["node_idx"] != abi.NO_NODE
+    assert eng.stats()["n_allocations"] == len(o_led2)
     eng.close()
 
 
@@ -615,6 +633,19 @@ def test_snapshot_and_restore(kg, orc):
         small.restore(blob)                                         # too many nodes for this engine
     with pytest.raises(kg.EngineError):
         fresh.restore(blob[:100])
+    # a corrupted blob (a record claiming 200 GPUs; a ledger entry naming a node far away) is rejected whole,
+    # and the engine keeps the state it had
+    before = fresh.snapshot()
+    bad = bytearray(blob)
+    n_gpus_off = 32 + 2 * 768 + 64 * 8 + 3 * 64 + 5 * 8 + abi.MIG_PROFILES       # header, record 2, up to n_gpus
+    bad[n_gpus_off] = 200
+    with pytest.raises(kg.EngineError):
+        fresh.restore(bytes(bad))
+    bad = bytearray(blob)
+    bad[-8:-4] = (0x7FFFFFFF).to_bytes(4, "little")                                # last ledger entry's node
+    with pytest.raises(kg.EngineError):
+        fresh.restore(bytes(bad))
+    assert fresh.snapshot() == before
     eng.close(); fresh.close(); small.close()
 
 
