@@ -127,14 +127,14 @@ std::string TopologyAwareScheduler::UpsertNode(const NodeTopology& node) {
     std::string err = PackNode(node, &pk);
     if (!err.empty()) return err;
     auto known = node_index_.find(node.NodeName);       // a node that comes back keeps its index (and so its ledger entries, as in the reference)
-    uint32_t idx;
-    if (known == node_index_.end()) {
-        if (node_names_.size() >= max_nodes_) return "cluster image is full";
-        idx = (uint32_t)node_names_.size();
-        node_index_[node.NodeName] = idx; node_names_.push_back(node.NodeName); node_uuids_.emplace_back();
-    } else { idx = known->second; node_names_[idx] = node.NodeName; }
-    node_uuids_[idx] = pk.uuids;
+    const bool fresh = known == node_index_.end();
+    if (fresh && node_names_.size() >= max_nodes_) return "cluster image is full";
+    const uint32_t idx = fresh ? (uint32_t)node_names_.size() : known->second;
+    // the engine first: a record it rejects must not leave a name behind in the tables
     if (kgwe_node_upsert(engine_, idx, &pk.image) != KGWE_OK) return kgwe_last_error(engine_);
+    if (fresh) { node_index_[node.NodeName] = idx; node_names_.push_back(node.NodeName); node_uuids_.emplace_back(); }
+    else node_names_[idx] = node.NodeName;
+    node_uuids_[idx] = pk.uuids;
     return "";
 }
 
@@ -146,11 +146,13 @@ std::string TopologyAwareScheduler::RemoveNode(const std::string& name) {
     return "";
 }
 
-kgwe_pod_req TopologyAwareScheduler::PodReq(const GPUWorkload& w) {
+kgwe_pod_req TopologyAwareScheduler::PodReq(const GPUWorkload& w, bool commits) {
     kgwe_pod_req p; memset(&p, 0, sizeof p);
+    // only calls that record an allocation need a ledger key; score-only calls (ScoreNodes, Filter,
+    // Prioritize) must not grow the UID table with pods that may never be scheduled here
     auto it = wl_id_.find(w.UID);
-    if (it == wl_id_.end()) it = wl_id_.emplace(w.UID, next_wl_++).first;
-    p.wl_id = it->second;
+    if (it == wl_id_.end() && commits) it = wl_id_.emplace(w.UID, next_wl_++).first;
+    p.wl_id = it == wl_id_.end() ? 0 : it->second;
     p.gpu_count = w.Requirements.GPUCount; p.min_memory_gb = w.Requirements.MinMemoryGB;
     p.min_bandwidth_gbps = cfg_.EnableMinBandwidthFilter ? w.Requirements.MinBandwidthGBps : 0.0;
     p.topology_pref = TopologyPreferenceCode(w.Requirements.TopologyPreference);
@@ -198,7 +200,7 @@ Result<std::vector<NodeScore>> TopologyAwareScheduler::ScoreNodes(const GPUWorkl
     Result<std::vector<NodeScore>> r;
     if (!HasTopology()) { r.error = "cluster topology not available"; return r; }
     topk = std::min<uint32_t>(topk, KGWE_MAX_TOPK);
-    const kgwe_pod_req p = PodReq(w);
+    const kgwe_pod_req p = PodReq(w, false);
     std::vector<uint8_t> bm = HintBitmap(hint);
     std::vector<kgwe_placement> out(topk);
     if (kgwe_score_batch(engine_, &p, 1, hint ? bm.data() : nullptr, nullptr, topk, out.data()) != KGWE_OK) { r.error = kgwe_last_error(engine_); return r; }
@@ -210,7 +212,8 @@ Result<SchedulingDecision> TopologyAwareScheduler::Schedule(const GPUWorkload& w
     const auto t0 = std::chrono::steady_clock::now();
     Result<SchedulingDecision> r;
     if (!HasTopology()) { r.error = "cluster topology not available"; return r; }            // scheduler.go:124
-    const kgwe_pod_req p = PodReq(w);
+    const bool known_uid = wl_id_.count(w.UID) != 0;
+    const kgwe_pod_req p = PodReq(w, true);
     std::vector<uint8_t> bm = HintBitmap(hint);
     kgwe_placement pl;
     const int rc = kgwe_schedule_queue(engine_, &p, 1, hint ? bm.data() : nullptr, &pl);
@@ -218,6 +221,7 @@ Result<SchedulingDecision> TopologyAwareScheduler::Schedule(const GPUWorkload& w
     if (rc != KGWE_OK) { r.error = kgwe_last_error(engine_); return r; }
     if (pl.node_idx == KGWE_NO_NODE) {
         UpdateLatency(ms); metrics_.TotalFailed++;
+        if (!known_uid) wl_id_.erase(w.UID);                                                   // nothing was recorded under it
         r.error = "no eligible nodes found for workload " + w.Name;                            // scheduler.go:140
         return r;
     }
@@ -233,7 +237,8 @@ std::vector<Result<SchedulingDecision>> TopologyAwareScheduler::ScheduleBurst(co
     if (ws.empty()) return out;
     if (!HasTopology()) { for (auto& r : out) r.error = "cluster topology not available"; return out; }
     std::vector<kgwe_pod_req> pods; pods.reserve(ws.size());
-    for (auto& w : ws) pods.push_back(PodReq(w));
+    std::set<std::string> fresh_uids;                       // UIDs this burst brought in; forgotten again if none of their tries lands
+    for (auto& w : ws) { if (!wl_id_.count(w.UID)) fresh_uids.insert(w.UID); pods.push_back(PodReq(w, true)); }
     std::vector<kgwe_placement> pls(ws.size());
     if (kgwe_schedule_queue(engine_, pods.data(), (uint32_t)pods.size(), nullptr, pls.data()) != KGWE_OK) {
         for (auto& r : out) r.error = kgwe_last_error(engine_);
@@ -245,7 +250,9 @@ std::vector<Result<SchedulingDecision>> TopologyAwareScheduler::ScheduleBurst(co
         metrics_.TotalScheduled++;
         if (pls[i].topology >= 80) metrics_.TopologyOptimalPlacements++;
         events_.push_back(SchedulingEvent{"Scheduled", ws[i].UID, std::make_shared<SchedulingDecision>(out[i].value), ""});
+        fresh_uids.erase(ws[i].UID);
     }
+    for (auto& uid : fresh_uids) wl_id_.erase(uid);
     return out;
 }
 
@@ -280,7 +287,7 @@ std::string TopologyAwareScheduler::ScoreAll(const GPUWorkload& w, std::vector<k
     kgwe_stats st;
     if (kgwe_get_stats(engine_, &st) != KGWE_OK) return kgwe_last_error(engine_);
     scores->assign(st.n_nodes, kgwe_node_score{});
-    const kgwe_pod_req p = PodReq(w);
+    const kgwe_pod_req p = PodReq(w, false);
     if (st.n_nodes && kgwe_score_batch(engine_, &p, 1, nullptr, scores->data(), 0, nullptr) != KGWE_OK) return kgwe_last_error(engine_);
     return "";
 }
@@ -321,6 +328,7 @@ std::string TopologyAwareScheduler::ReleaseAllocation(const std::string& uid) {
     auto it = wl_id_.find(uid);
     if (it == wl_id_.end() || kgwe_alloc_release(engine_, it->second) != KGWE_OK)
         return "allocation not found for workload " + uid;                                      // scheduler.go:715
+    wl_id_.erase(it);
     events_.push_back(SchedulingEvent{"Released", uid, nullptr, ""});
     return "";
 }

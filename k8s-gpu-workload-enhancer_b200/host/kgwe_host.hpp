@@ -127,7 +127,7 @@ public:
 
 private:
     TopologyAwareScheduler() = default;
-    kgwe_pod_req PodReq(const GPUWorkload& w);
+    kgwe_pod_req PodReq(const GPUWorkload& w, bool commits);
     std::vector<uint8_t> HintBitmap(const PlacementHint* hint) const;
     NodeScore NodeScoreOf(const kgwe_placement& pl) const;
     SchedulingDecision DecisionOf(const GPUWorkload& w, const kgwe_placement& pl) const;

@@ -148,6 +148,22 @@ int main() {
             CHECK(pr[x].Host == cluster[2 * x].NodeName && pr[x].Score == exp && pr[x].Score <= MaxExtenderPriority);
         }
     }
+    // a record the engine rejects leaves no name behind, and the next new node takes the index it would have had
+    {
+        NodeTopology bad = cluster[1]; bad.NodeName = "bad-node";
+        bad.GPUs[0].Topology.PCIeInfo.BandwidthGBps = -5.0;
+        CHECK(!S.UpsertNode(bad).empty() && S.NodeIndex("bad-node") == KGWE_NO_NODE);
+        NodeTopology extra = cluster[1]; extra.NodeName = "extra-node";
+        CHECK(S.UpsertNode(extra).empty() && S.NodeIndex("extra-node") == (uint32_t)N);
+        CHECK(S.RemoveNode("extra-node").empty());
+    }
+    // a released workload can be scheduled again under the same UID (fresh ledger key), and released again
+    {
+        auto again = S.Schedule(jobs[first_placed]);
+        CHECK(again.ok() && again.value.WorkloadUID == jobs[first_placed].UID);
+        CHECK(S.ReleaseAllocation(jobs[first_placed].UID).empty());
+        CHECK(S.ReleaseAllocation(jobs[first_placed].UID) == "allocation not found for workload " + jobs[first_placed].UID);
+    }
     // node delete event
     CHECK(S.RemoveNode(cluster[0].NodeName).empty() && S.NodeIndex(cluster[0].NodeName) == KGWE_NO_NODE);
     CHECK(!S.RemoveNode(cluster[0].NodeName).empty());
