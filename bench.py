@@ -460,6 +460,14 @@ def run_kgwe(args):
                          "note": "achieved = algorithmic bytes (SURVEY 8d); the 7.68 MB node image is L2-resident across the pods of a launch, so real DRAM traffic is ~1.6 GB (the score matrix) and frac > 1 is expected: the kernel is instruction-issue bound (profiles/README.md)"},
             "clocks": clk,
         }
+        lim = out["roofline"]["actual_limits"]
+        if lim and clk.get("sm_mhz"):
+            # the bound that actually holds: warp instructions issued (count per evaluation from the ncu capture x this
+            # run's live launch time) against the issue slots of the device (SMs x 4 schedulers x the SM clock under load)
+            sms = torch.cuda.get_device_properties(0).multi_processor_count
+            issued = lim["warp_instructions_per_evaluation"] * k1_evals / (k1_ms * 1e-3)
+            slots = sms * 4 * clk["sm_mhz"] * 1e6
+            lim["issue_roofline"] = {"bound": "issue", "achieved": issued / 1e9, "peak": slots / 1e9, "unit": "G warp-instructions/s", "frac": issued / slots}
         if lat:
             out["prioritize_latency"] = lat
         if lat_sharded:

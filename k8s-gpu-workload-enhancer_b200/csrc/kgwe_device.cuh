@@ -218,7 +218,8 @@ __device__ __forceinline__ void greedy_chain_fast_k(const NodeFast* nf, int s, i
     key = 0; pay = 0;
     const int4* ip = reinterpret_cast<const int4*>(nf->init);
     int4 a = ip[0], b = ip[1];                         // (the caller has checked that start s is available)
-    int32_t sum = 0; uint32_t order = (uint32_t)s; int m = s;
+    uint32_t sum = 0; uint32_t order = (uint32_t)s; int m = s;      // unsigned: a dead chain may wrap, and must not be UB
+    bool alive = true;
 #pragma unroll
     for (int step = 1; step < K; ++step) {
         const int4* rp = reinterpret_cast<const int4*>(nf->row[m]);
@@ -226,13 +227,16 @@ __device__ __forceinline__ void greedy_chain_fast_k(const NodeFast* nf, int s, i
         a.x += r0.x; a.y += r0.y; a.z += r0.z; a.w += r0.w;
         b.x += r1.x; b.y += r1.y; b.z += r1.z; b.w += r1.w;
         const int32_t best = __vimax3_s32(__vimax3_s32(a.x, a.y, a.z), __vimax3_s32(a.w, b.x, b.y), max(b.z, b.w));
-        if (best <= 7) return;                          // nobody fully connected with a positive aggregate
+        // best <= 7: nobody fully connected with a positive aggregate - the chain is dead.  No branch: dead chains are
+        // rare, and a straight-line body lets the steps be scheduled as one block.  (A dead chain keeps stepping on
+        // whatever m falls out; the running sums stay inside int32: at most 8 terms of FAST_NEG each.)
+        alive &= best > 7;
         m = ~best & 7;                                  // 7 - (best & 7)
-        sum += best;
+        sum += (uint32_t)best;
         order |= (uint32_t)m << (3 * step);
     }
-    const int32_t total = sum >> FAST_SHIFT;
-    if (total > 0) { key = (total << 3) | (7 - s); pay = order; }
+    const int32_t total = (int32_t)sum >> FAST_SHIFT;
+    if (alive && total > 0) { key = (total << 3) | (7 - s); pay = order; }
 }
 
 // The chain from start s for group size k is the first k-1 steps of the chain for size 8, so one
