@@ -140,3 +140,30 @@ def test_contributing_md_snippet_expectation(kg, orc):
         assert int(s[0, 0]["topology"]) >= 80 and int(s[0, 0]["total"]) >= 80
     # docs/architecture.md:353-358 quotes ranges "NVLink 50-100, NUMA 50-90, PCIe 50-80"; the code's fallbacks are
     # 30 / 50 / 40 and NVLink exceeds 100 above 900 GB/s (KAT-3) - the code, not the prose, is what is restated.
+
+
+def test_faithful_equals_indexed_fuzz(kg, orc):
+    """The two oracle builds over the differential fuzzer's input space (tools/fuzz_parity.py: ragged nodes,
+    inactive / zero / fractional / irregular links, MIG, hints, architectures, minimum bandwidth, every
+    preference, counts 0..9, exhaustive flags) at sizes the faithful build finishes in a moment:
+    stateless matrix + top-k, the stateful queue with its final ledger, and gang scheduling."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("fuzz_parity", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "fuzz_parity.py"))
+    fz = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fz)
+    abi = kg.abi
+    kinds = set()
+    for seed in range(1, 81):
+        nodes, pods, led, hint, _, topk, gang_of, kind = fz.make_case(abi, kg.synth, seed, n_lo=8, n_span=40, p_lo=8, p_span=30)
+        kinds.add(kind)
+        a = orc.score_batch(abi, nodes, led, pods, hint=hint, want_scores=True, topk=topk, mode=orc.FAITHFUL)
+        b = orc.score_batch(abi, nodes, led, pods, hint=hint, want_scores=True, topk=topk, mode=orc.INDEXED)
+        assert a[0].tobytes() == b[0].tobytes() and a[1].tobytes() == b[1].tobytes(), f"seed {seed}: stateless"
+        qa = orc.schedule_queue(abi, nodes, led, pods, hint=hint, mode=orc.FAITHFUL)
+        qb = orc.schedule_queue(abi, nodes, led, pods, hint=hint, mode=orc.INDEXED)
+        assert qa[0].tobytes() == qb[0].tobytes(), f"seed {seed}: queue decisions"
+        assert np.sort(qa[1], order="wl_id").tobytes() == np.sort(qb[1], order="wl_id").tobytes(), f"seed {seed}: final ledger"
+        ga = orc.schedule_gangs(abi, nodes, led, pods, gang_of, hint=hint, mode=orc.FAITHFUL)
+        gb = orc.schedule_gangs(abi, nodes, led, pods, gang_of, hint=hint, mode=orc.INDEXED)
+        assert ga[0].tobytes() == gb[0].tobytes(), f"seed {seed}: gang decisions"
+    assert kinds == {0, 1, 2, 3}

@@ -7,12 +7,12 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import __graft_entry__ as entry
 
 
-def one_seed(kg, orc, seed):
-    abi, synth = kg.abi, kg.synth
+def make_case(abi, synth, seed, n_lo=40, n_span=400, p_lo=40, p_span=200):
+    """One random case: (nodes, pods, ledger, hint or None, engine flags, top-k, gang_of, bandwidth kind)."""
     rng = synth.SplitMix64(seed * 7919 + 13)
     u = rng.uniform(16)
-    N = int(40 + u[0] * 400)
-    P = int(40 + u[1] * 200)
+    N = int(n_lo + u[0] * n_span)
+    P = int(p_lo + u[1] * p_span)
     nodes = synth.make_cluster(N, "mixed" if u[2] < 0.8 else "dgx", seed=seed, unhealthy_frac=u[3] * 0.3, inactive_link_frac=u[4] * 0.2,
                                partial_node_frac=u[5] * 0.5, mig_frac=u[6])
     kind = int(u[7] * 4)
@@ -38,10 +38,19 @@ def one_seed(kg, orc, seed):
     led = synth.make_ledger(nodes, u[11] * 0.8, seed=seed)
     hint = synth.make_hint(P, N, u[12] * 0.1, seed=seed) if u[13] < 0.5 else None
     flags = [0, abi.CFG_MEMOISE_GROUPS, abi.CFG_SUBSET_TABLES, abi.CFG_MEMOISE_GROUPS | abi.CFG_SUBSET_TABLES][int(u[14] * 4)]
+    topk = [1, 2, 5, 16][int(u[15] * 4)]
+    sizes = rng.randint(1, 9, P)
+    gang_of = np.repeat(np.arange(P), sizes)[:P].astype(np.uint32)
+    return nodes, pods, led, hint, flags, topk, gang_of, kind
+
+
+def one_seed(kg, orc, seed):
+    abi, synth = kg.abi, kg.synth
+    nodes, pods, led, hint, flags, topk, gang_of, kind = make_case(abi, synth, seed)
+    N, P = len(nodes), len(pods)
     eng = kg.Engine(max_nodes=N, flags=flags)
     eng.upsert_nodes(nodes)
     eng.seed_ledger(led)
-    topk = [1, 2, 5, 16][int(u[15] * 4)]
     s, t = eng.score_batch(pods, N, hint=hint, want_scores=True, topk=topk)
     o, ot, _ = orc.score_batch(abi, nodes, led, pods, hint=hint, want_scores=True, topk=topk, threads=4)
     assert s.tobytes() == o.tobytes(), f"seed {seed}: score matrix differs"
@@ -67,8 +76,6 @@ def one_seed(kg, orc, seed):
     eng = kg.Engine(max_nodes=N, flags=flags)
     eng.upsert_nodes(nodes)
     eng.seed_ledger(led)
-    sizes = rng.randint(1, 9, P)
-    gang_of = np.repeat(np.arange(P), sizes)[:P].astype(np.uint32)
     g = eng.schedule_gangs(pods, gang_of, hint=hint)
     og, ogl = orc.schedule_gangs(abi, nodes, led, pods, gang_of, hint=hint)
     assert g.tobytes() == og.tobytes(), f"seed {seed}: gang decisions differ"
