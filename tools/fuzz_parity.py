@@ -15,7 +15,7 @@ def make_case(abi, synth, seed, n_lo=40, n_span=400, p_lo=40, p_span=200):
     P = int(p_lo + u[1] * p_span)
     nodes = synth.make_cluster(N, "mixed" if u[2] < 0.8 else "dgx", seed=seed, unhealthy_frac=u[3] * 0.3, inactive_link_frac=u[4] * 0.2,
                                partial_node_frac=u[5] * 0.5, mig_frac=u[6])
-    kind = int(u[7] * 4)
+    kind = int(u[7] * 5)
     if kind == 1:      # fractional, asymmetric bandwidths on some nodes (FP64 path)
         frac = rng.uniform(N) < 0.4
         jit = 0.5 + rng.uniform(N * 64).reshape(N, 8, 8)
@@ -29,10 +29,26 @@ def make_case(abi, synth, seed, n_lo=40, n_span=400, p_lo=40, p_span=200):
     nodes["numa"] = rng.randint(-2, 2, N * 8).reshape(N, 8).astype(np.int8)
     nodes["pcie_switch"] = rng.randint(0, 3, N * 8).reshape(N, 8).astype(np.uint8)
     nodes["util"] = np.floor(rng.uniform(N * 8).reshape(N, 8) * 400) / 4.0
+    if kind == 4:      # values at the edges of what an upsert accepts
+        bw_set = np.array([0.0, 1.0, 0.5, 100000.0, 99999.75, 3.0000000001, 1e-300, 899.9999999999999, 900.0])
+        nodes["nvl_bw"] = np.where(nodes["nvl_bw"] > 0, bw_set[rng.randint(0, len(bw_set) - 1, N * 64)].reshape(N, 8, 8), 0.0)
+        pc_set = np.array([0.0, 100000.0, 15.75, 64.0])
+        nodes["pcie_bw"] = pc_set[rng.randint(0, len(pc_set) - 1, N * 8)].reshape(N, 8)
+        ut_set = np.array([-50.0, 0.0, 29.999999999999996, 30.0, 59.99999999999999, 60.0, 1e300, 100.0])
+        nodes["util"] = ut_set[rng.randint(0, len(ut_set) - 1, N * 8)].reshape(N, 8)
+        fb_set = np.array([0, 2**64 - 1, 2**63, 16 * 2**30, 16 * 2**30 - 1, 2**61], dtype=np.uint64)
+        nodes["free_bytes"] = fb_set[rng.randint(0, len(fb_set) - 1, N * 8)].reshape(N, 8)
+        nodes["numa"] = np.array([-128, 127, 0, -1], dtype=np.int8)[rng.randint(0, 3, N * 8)].reshape(N, 8)
+        nodes["pcie_switch"] = np.array([0, 255, 7], dtype=np.uint8)[rng.randint(0, 2, N * 8)].reshape(N, 8)
+        nodes["mig_free"] = np.array([0, 1, 255], dtype=np.uint8)[rng.randint(0, 2, N * abi.MIG_PROFILES)].reshape(N, abi.MIG_PROFILES)
     prefs = rng.uniform(5) + 0.05
     pods = synth.make_pods(P, seed=seed, k_lo=0, k_hi=9, pref_probs=tuple(prefs / prefs.sum()), arch_frac=u[8] * 0.6,
                            minbw_choices=(0.0, 0.0, 200.0, 650.0, 1000.0), mig_frac=u[9] * 0.5)
     pods["min_memory_gb"] = rng.randint(0, 200, P)
+    if kind == 4:
+        pods["min_memory_gb"] = np.array([0, 1, 16, 2**20, 2**19], dtype=np.int64)[rng.randint(0, 4, P)]
+        pods["min_bandwidth_gbps"] = np.array([0.0, 1e-300, 64.0, 99999.75, 1e300])[rng.randint(0, 4, P)]
+        pods["mig_count"] = np.where(pods["mig_profile"] != abi.MIG_NONE, np.array([0, 1, 255, 256, -1])[rng.randint(0, 4, P)], 0)
     exh = rng.uniform(P) < u[10] * 0.5
     pods["flags"] = np.where(exh, abi.POD_EXHAUSTIVE, 0).astype(np.uint8)
     led = synth.make_ledger(nodes, u[11] * 0.8, seed=seed)
