@@ -659,3 +659,7 @@ def test_differential_fuzz_few_seeds(kg, orc):
     spec.loader.exec_module(fz)
     for seed in (101, 102, 103, 104, 105, 106):
         fz.one_seed(kg, orc, seed)
+    # and the stateful life cycle: informer events, ledger calls, queues and scoring interleaved at random on one
+    # engine, mirrored on a plain model that the oracle is given after every step; checkpoint at the end
+    for seed in (201, 202, 203, 204):
+        fz.life_cycle_seed(kg, orc, seed)

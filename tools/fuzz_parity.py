@@ -100,6 +100,102 @@ def one_seed(kg, orc, seed):
     return N, P, kind, flags
 
 
+def life_cycle_seed(kg, orc, seed, n_ops=80):
+    """Random interleaving of informer events (upsert / remove / re-add), ledger calls (commit, overwrite, release)
+    and scoring / scheduling calls on ONE engine, mirrored on a plain model (node array + presence + ledger dict)
+    that is handed to the oracle after every step."""
+    abi, synth = kg.abi, kg.synth
+    rng = synth.SplitMix64(seed * 104729 + 7)
+    N = int(rng.randint(6, 90, 1)[0])
+    nodes = synth.make_cluster(N, "mixed", seed=seed, unhealthy_frac=0.1, inactive_link_frac=0.05, partial_node_frac=0.3, mig_frac=0.3)
+    pool = synth.make_cluster(4 * N, "mixed", seed=seed + 1, unhealthy_frac=0.2, inactive_link_frac=0.1, partial_node_frac=0.4, mig_frac=0.3)
+    present = np.ones(N, dtype=bool)
+    ledger = {}
+    eng = kg.Engine(max_nodes=N + 3)
+    eng.upsert_nodes(nodes)
+    next_wl = [1000]
+
+    def view():          # what the oracle sees: absent records have no GPUs
+        v = nodes.copy()
+        v["n_gpus"][~present] = 0; v["healthy_mask"][~present] = 0
+        led = np.zeros(len(ledger), dtype=abi.ALLOC)
+        for i, (wl, (n, m)) in enumerate(sorted(ledger.items())):
+            led[i]["wl_id"], led[i]["node_idx"], led[i]["gpu_mask"] = wl, n, m
+        return v, led
+
+    def some_pods(n, k_lo):
+        pods = synth.make_pods(n, seed=int(rng.randint(0, 1 << 30, 1)[0]), k_lo=k_lo, k_hi=8, pref_probs=(0.2, 0.3, 0.1, 0.2, 0.2), arch_frac=0.2, mig_frac=0.1)
+        for i in range(n):       # mostly new ids, sometimes one that is already in the ledger (overwrite)
+            if ledger and rng.uniform(1)[0] < 0.2:
+                pods["wl_id"][i] = sorted(ledger)[int(rng.randint(0, len(ledger) - 1, 1)[0])]
+            else:
+                pods["wl_id"][i] = next_wl[0]; next_wl[0] += 1
+        return pods
+
+    for step in range(n_ops):
+        op = int(rng.randint(0, 9, 1)[0])
+        if op == 0:                                   # node refresh / re-add
+            i = int(rng.randint(0, N - 1, 1)[0])
+            nodes[i] = pool[int(rng.randint(0, len(pool) - 1, 1)[0])]
+            eng.upsert_node(i, nodes[i]); present[i] = True
+        elif op == 1:                                 # node delete (or an error for one that is gone)
+            i = int(rng.randint(0, N - 1, 1)[0])
+            if present[i]:
+                eng.remove_node(i); present[i] = False
+            else:
+                try:
+                    eng.remove_node(i); raise AssertionError(f"seed {seed}: removing an absent node succeeded")
+                except kg.EngineError:
+                    pass
+        elif op == 2:                                 # external commit, sometimes over an existing id
+            wl = sorted(ledger)[int(rng.randint(0, len(ledger) - 1, 1)[0])] if (ledger and rng.uniform(1)[0] < 0.3) else next_wl[0]
+            next_wl[0] += 1
+            i, m = int(rng.randint(0, N - 1, 1)[0]), int(rng.randint(1, 255, 1)[0])
+            eng.commit(wl, i, m); ledger[wl] = (i, m)
+        elif op == 3:                                 # release (known or unknown)
+            if ledger and rng.uniform(1)[0] < 0.8:
+                wl = sorted(ledger)[int(rng.randint(0, len(ledger) - 1, 1)[0])]
+                eng.release(wl); del ledger[wl]
+            else:
+                try:
+                    eng.release(999_999_999); raise AssertionError(f"seed {seed}: releasing an unknown workload succeeded")
+                except kg.EngineError:
+                    pass
+        elif op in (4, 5):                            # a short queue with commits
+            pods = some_pods(int(rng.randint(1, 6, 1)[0]), 1)
+            v, led = view()
+            d = eng.schedule_queue(pods)
+            od, oled, _ = orc.schedule_queue(abi, v, led, pods)
+            assert d.tobytes() == od.tobytes(), f"seed {seed} step {step}: queue decisions differ"
+            ledger.clear()
+            for a in oled:
+                ledger[int(a["wl_id"])] = (int(a["node_idx"]), int(a["gpu_mask"]))
+        else:                                         # stateless scoring (matrix + top-3, or the latency path)
+            pods = some_pods(int(rng.randint(1, 12, 1)[0]), 0)
+            v, led = view()
+            if op == 6:
+                _, t = eng.score_batch(pods, N, want_scores=False, topk=1)
+                keep = pods["gpu_count"] >= 1        # a request for 0 GPUs would "fit" the oracle's empty stand-in for an absent node
+                _, ot, _ = orc.score_batch(abi, v, led, pods, want_scores=False, topk=1)
+                assert t[keep].tobytes() == ot[keep].tobytes(), f"seed {seed} step {step}: top-1 differs"
+            else:
+                sc, _ = eng.score_batch(pods, N, want_scores=True)
+                o, _, _ = orc.score_batch(abi, v, led, pods, want_scores=True)
+                assert sc[:, present].tobytes() == o[:, present].tobytes(), f"seed {seed} step {step}: score matrix differs"
+                assert (sc[:, ~present]["flags"] == 0).all(), f"seed {seed} step {step}: an absent node was scored"
+        assert eng.stats()["n_allocations"] == len(ledger), f"seed {seed} step {step}: ledger size"
+    # checkpoint -> fresh engine answers the same
+    blob = eng.snapshot()
+    other = kg.Engine(max_nodes=N + 3)
+    other.restore(blob)
+    pods = some_pods(10, 0)
+    a, _ = eng.score_batch(pods, N, want_scores=True)
+    b, _ = other.score_batch(pods, N, want_scores=True)
+    assert a.tobytes() == b.tobytes(), f"seed {seed}: restored engine differs"
+    eng.close(); other.close()
+    return N, len(ledger), int(present.sum())
+
+
 if __name__ == "__main__":
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 40
     first = int(sys.argv[2]) if len(sys.argv) > 2 else 1
@@ -108,4 +204,6 @@ if __name__ == "__main__":
     for seed in range(first, first + n):
         N, P, kind, flags = one_seed(kg, orc, seed)
         print(f"seed {seed}: ok ({N} nodes, {P} pods, bandwidth kind {kind}, engine flags {flags})", flush=True)
+        N, L, pres = life_cycle_seed(kg, orc, seed)
+        print(f"seed {seed}: life cycle ok ({N} nodes, {pres} present at the end, {L} ledger entries)", flush=True)
     print(f"fuzz_parity: {n} seeds bit-exact")
