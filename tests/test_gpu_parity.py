@@ -663,3 +663,6 @@ def test_differential_fuzz_few_seeds(kg, orc):
     # engine, mirrored on a plain model that the oracle is given after every step; checkpoint at the end
     for seed in (201, 202, 203, 204):
         fz.life_cycle_seed(kg, orc, seed)
+    # and E2 on random MIG tables (any occupancy byte, every profile id, random targets)
+    for seed in (301, 302, 303, 304, 305, 306):
+        fz.mig_seed(kg, orc, seed)

@@ -196,6 +196,31 @@ def life_cycle_seed(kg, orc, seed, n_ops=80):
     return N, len(ledger), int(present.sum())
 
 
+def mig_seed(kg, orc, seed):
+    """E2 on random tables: any occupancy byte (also ones no legal placement sequence produces), every profile id
+    0..12 in the request stream, random target distributions; bin-packing and rebalancing vs the oracle."""
+    abi, synth = kg.abi, kg.synth
+    rng = synth.SplitMix64(seed * 15485863 + 3)
+    G, R = int(rng.randint(1, 700, 1)[0]), int(rng.randint(1, 2500, 1)[0])
+    gpus, profiles = synth.make_mig(G, R, seed=seed, occupancy=float(rng.uniform(1)[0]))
+    if rng.uniform(1)[0] < 0.5:
+        gpus["occ"] = rng.randint(0, 255, G).astype(np.uint8)
+    if rng.uniform(1)[0] < 0.5:
+        profiles = rng.randint(0, 12, R).astype(np.uint8)
+    eng = kg.Engine(max_nodes=1)
+    a, after = eng.mig_pack(gpus, profiles)
+    o, o_after = orc.mig_pack(abi, gpus, profiles)
+    assert a.tobytes() == o.tobytes() and after.tobytes() == o_after.tobytes(), f"seed {seed}: MIG packing differs"
+    t = rng.uniform(10) * (rng.uniform(10) < 0.4)
+    target = t / t.sum() * float(rng.uniform(1)[0]) if t.sum() > 0 else t
+    for tbl in (gpus, after):
+        ops, supply, n = eng.mig_rebalance(tbl, target)
+        o_ops, o_supply, o_n = orc.mig_rebalance(abi, tbl, target)
+        assert n == o_n and ops.tobytes() == o_ops.tobytes() and supply.tolist() == o_supply.tolist(), f"seed {seed}: MIG rebalance differs"
+    eng.close()
+    return G, R
+
+
 if __name__ == "__main__":
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 40
     first = int(sys.argv[2]) if len(sys.argv) > 2 else 1
@@ -206,4 +231,6 @@ if __name__ == "__main__":
         print(f"seed {seed}: ok ({N} nodes, {P} pods, bandwidth kind {kind}, engine flags {flags})", flush=True)
         N, L, pres = life_cycle_seed(kg, orc, seed)
         print(f"seed {seed}: life cycle ok ({N} nodes, {pres} present at the end, {L} ledger entries)", flush=True)
+        G, R = mig_seed(kg, orc, seed)
+        print(f"seed {seed}: MIG ok ({G} GPUs, {R} requests)", flush=True)
     print(f"fuzz_parity: {n} seeds bit-exact")
