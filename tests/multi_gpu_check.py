@@ -21,51 +21,66 @@ def main():
     kg = entry.load_package()
     from oracle import binding as orc
     abi, synth = kg.abi, kg.synth
-    nodes, pods, led = synth.config(3, 0.1)
-    pods = pods[:500]
-    N, P, topk = len(nodes), len(pods), 4
-    lo, hi = kg.sharded.shard_range(N, rank, world)
-    eng = kg.Engine(max_nodes=hi - lo, device=local, node_base=lo)
-    eng.upsert_nodes(nodes[lo:hi])
-    for a in led:
-        if lo <= a["node_idx"] < hi:
-            eng.commit(a["wl_id"], a["node_idx"] - lo, a["gpu_mask"])
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
-    sc = kg.sharded.ShardedScorer(eng, hi - lo, world, dist, stream.cuda_stream)
-    sc.alloc(torch, dev, P, topk, with_matrix=True)
-    d_pods = torch.from_numpy(pods.view(np.uint8).reshape(P, abi.POD_REQ.itemsize)).to(dev)
-    merged = sc.step(d_pods)
-    torch.cuda.synchronize()
-    got = merged.cpu().numpy().view(abi.PLACEMENT).reshape(P, topk)
-    local_scores = sc.d_scores.cpu().numpy().view(abi.NODE_SCORE).reshape(P, hi - lo)
-    o_scores, want, _ = orc.score_batch(abi, nodes, led, pods, want_scores=True, topk=topk, threads=4)
-    ok = got.tobytes() == want.tobytes() and local_scores.tobytes() == np.ascontiguousarray(o_scores[:, lo:hi]).tobytes()
-    # the same batch with the exchange fused into the finalisation kernel (P2P stores), top-1, several steps in a row
-    sc1 = kg.sharded.ShardedScorer(eng, hi - lo, world, dist, stream.cuda_stream, rank=rank)
-    sc1.alloc(torch, dev, P, 1, with_matrix=False)
-    p2p_on = sc1.enable_p2p(torch, dev, P)
-    _, want1, _ = orc.score_batch(abi, nodes, led, pods, want_scores=False, topk=1, threads=4)
-    for it in range(5):
-        m = sc1.step(d_pods)
+
+    def check_case(nodes, pods, led, topk, label):
+        N, P = len(nodes), len(pods)
+        lo, hi = kg.sharded.shard_range(N, rank, world)
+        eng = kg.Engine(max_nodes=hi - lo, device=local, node_base=lo)
+        eng.upsert_nodes(nodes[lo:hi])
+        for a in led:
+            if lo <= a["node_idx"] < hi:
+                eng.commit(a["wl_id"], a["node_idx"] - lo, a["gpu_mask"])
+        sc = kg.sharded.ShardedScorer(eng, hi - lo, world, dist, stream.cuda_stream)
+        sc.alloc(torch, dev, P, topk, with_matrix=True)
+        d_pods = torch.from_numpy(pods.view(np.uint8).reshape(P, abi.POD_REQ.itemsize)).to(dev)
+        merged = sc.step(d_pods)
         torch.cuda.synchronize()
-        got1 = m.cpu().numpy().view(abi.PLACEMENT).reshape(P, 1)
-        ok = ok and got1.tobytes() == want1.tobytes()
-    if rank == 0:
-        print(f"fused P2P exchange: {'on' if p2p_on else 'unavailable (NCCL path used)'}")
-    # stateful queue over the sharded cluster: per-workload all-gather, owner rank commits
-    qpods = pods[:120]
-    got_q = kg.sharded.schedule_queue_sharded(
-        dist, rank, world, (lo, hi), qpods,
-        lambda pod, h: eng.score_batch(pod, hi - lo, want_scores=False, topk=1)[1][0, 0],
-        lambda wl, n, m: eng.commit(wl, n, m), device=dev, torch=torch)
-    want_q, _, _ = orc.schedule_queue(abi, nodes, led, qpods)
-    ok = ok and got_q.tobytes() == want_q.tobytes()
+        got = merged.cpu().numpy().view(abi.PLACEMENT).reshape(P, topk)
+        local_scores = sc.d_scores.cpu().numpy().view(abi.NODE_SCORE).reshape(P, hi - lo)
+        o_scores, want, _ = orc.score_batch(abi, nodes, led, pods, want_scores=True, topk=topk, threads=4)
+        ok = got.tobytes() == want.tobytes() and local_scores.tobytes() == np.ascontiguousarray(o_scores[:, lo:hi]).tobytes()
+        # the same batch with the exchange fused into the finalisation kernel (P2P stores), top-1, several steps in a row
+        sc1 = kg.sharded.ShardedScorer(eng, hi - lo, world, dist, stream.cuda_stream, rank=rank)
+        sc1.alloc(torch, dev, P, 1, with_matrix=False)
+        p2p_on = sc1.enable_p2p(torch, dev, P)
+        _, want1, _ = orc.score_batch(abi, nodes, led, pods, want_scores=False, topk=1, threads=4)
+        for it in range(5):
+            m = sc1.step(d_pods)
+            torch.cuda.synchronize()
+            got1 = m.cpu().numpy().view(abi.PLACEMENT).reshape(P, 1)
+            ok = ok and got1.tobytes() == want1.tobytes()
+        if rank == 0:
+            print(f"fused P2P exchange: {'on' if p2p_on else 'unavailable (NCCL path used)'}")
+        # stateful queue over the sharded cluster: per-workload all-gather, owner rank commits
+        qpods = pods[:120]
+        got_q = kg.sharded.schedule_queue_sharded(
+            dist, rank, world, (lo, hi), qpods,
+            lambda pod, h: eng.score_batch(pod, hi - lo, want_scores=False, topk=1)[1][0, 0],
+            lambda wl, n, m: eng.commit(wl, n, m), device=dev, torch=torch)
+        want_q, _, _ = orc.schedule_queue(abi, nodes, led, qpods)
+        ok = ok and got_q.tobytes() == want_q.tobytes()
+        eng.close()
+        if rank == 0 and not ok:
+            print(f"multi_gpu_check: MISMATCH in case {label}")
+        return ok
+
+    nodes, pods, led = synth.config(3, 0.1)
+    N, P, topk = len(nodes), 500, 4
+    ok = check_case(nodes, pods[:500], led, topk, "config 3 x 0.1")
+    # a few cases from the differential fuzzer's input space (tools/fuzz_parity.py), sharded
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("fuzz_parity", os.path.join(ROOT, "tools", "fuzz_parity.py"))
+    fz = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fz)
+    for seed in (11, 12, 13, 14):
+        f_nodes, f_pods, f_led, _, _, f_topk, _, _ = fz.make_case(abi, synth, seed, n_lo=8 * world, n_span=300)
+        ok = check_case(f_nodes, f_pods, f_led, max(1, f_topk), f"fuzz seed {seed}") and ok
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
         print(f"multi_gpu_check world={world}: {'PARITY OK' if flag.item() else 'MISMATCH'} ({P} pods x {N} nodes, top-{topk})")
-    eng.close()
     dist.destroy_process_group()
     sys.exit(0 if flag.item() else 1)
 
