@@ -282,7 +282,9 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
                     }
                 } else {
                     if (kt && start_ok) greedy_chain_fast(nf, j, kt, key, pay);
-                    fast_group_winner(key, pay, gmask);
+                    // all 32 lanes are here together (the branches into this block are warp-uniform): naming the whole
+                    // warp spares the per-lane mask handling the compiler adds around shuffles with a lane-dependent mask
+                    fast_group_winner(key, pay, 0xffffffffu);
                 }
                 if (j == t) { mykey = key; mypay = pay; }
             }
