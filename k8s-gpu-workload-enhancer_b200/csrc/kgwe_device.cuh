@@ -266,16 +266,17 @@ __device__ __forceinline__ void greedy_chain_fast_all(const NodeFast* nf, int s,
 
 // Precondition for lane s: nf->init[s] >= 0 (start GPU available); callers test it once per node.
 __device__ __forceinline__ void greedy_chain_fast(const NodeFast* nf, int s, int k, int32_t& key, uint32_t& pay) {
-    switch (k) {
-        case 2: greedy_chain_fast_k<2>(nf, s, key, pay); break;
-        case 3: greedy_chain_fast_k<3>(nf, s, key, pay); break;
-        case 4: greedy_chain_fast_k<4>(nf, s, key, pay); break;
-        case 5: greedy_chain_fast_k<5>(nf, s, key, pay); break;
-        case 6: greedy_chain_fast_k<6>(nf, s, key, pay); break;
-        case 7: greedy_chain_fast_k<7>(nf, s, key, pay); break;
-        case 8: greedy_chain_fast_k<8>(nf, s, key, pay); break;
-        default: key = 0; pay = 0;
-    }
+    // a compare tree (two or three tests per size) rather than a switch: the switch became an indexed constant load
+    // plus an indirect branch, with the load's latency in front of every short chain
+    if (k < 5) {
+        if (k < 3) { if (k == 2) greedy_chain_fast_k<2>(nf, s, key, pay); else { key = 0; pay = 0; } }
+        else if (k == 3) greedy_chain_fast_k<3>(nf, s, key, pay);
+        else greedy_chain_fast_k<4>(nf, s, key, pay);
+    } else if (k < 7) {
+        if (k == 5) greedy_chain_fast_k<5>(nf, s, key, pay); else greedy_chain_fast_k<6>(nf, s, key, pay);
+    } else if (k == 7) greedy_chain_fast_k<7>(nf, s, key, pay);
+    else if (k == 8) greedy_chain_fast_k<8>(nf, s, key, pay);
+    else { key = 0; pay = 0; }
 }
 
 // estimateBandwidth, scheduler.go:656-692: mean over pairs i<j (SelectedGPUs order) of GPU
