@@ -185,10 +185,20 @@ __device__ __forceinline__ void take_first_k(uint32_t m, int k, uint32_t& sel, u
         m &= m - 1;
     }
 }
+// GPU mask of a packed list (k fields of 3 bits), without a loop: lanes of a warp hold lists of different
+// lengths, so a loop runs as long as the longest one.  The unused fields are filled with field 0 (a member
+// anyway), the eight fields are spread to nibbles, and each nibble then selects its own byte 1 << v out of
+// the table 0x8040201008040201 with one PRMT per four fields; OR-ing the eight bytes gives the mask.
 __device__ __forceinline__ uint32_t mask_of_order(uint32_t order, int k) {
-    uint32_t sel = 0;
-    for (int i = 0; i < k; ++i) sel |= 1u << ((order >> (3 * i)) & 7);
-    return sel;
+    if (k <= 0) return 0u;
+    const uint32_t used = k >= 8 ? 0x00ffffffu : ((1u << (3 * k)) - 1u);
+    uint32_t x = (order & used) | (((order & 7u) * 0x249249u) & ~used & 0x00ffffffu);
+    x = (x & 0x00000fffu) | ((x & 0x00fff000u) << 4);       // 4 fields per halfword
+    x = (x & 0x003f003fu) | ((x & 0x0fc00fc0u) << 2);       // 2 fields per byte
+    x = (x & 0x07070707u) | ((x & 0x38383838u) << 1);       // 1 field per nibble
+    uint32_t y = __byte_perm(0x08040201u, 0x80402010u, x) | __byte_perm(0x08040201u, 0x80402010u, x >> 16);
+    y |= y >> 16;
+    return (y | (y >> 8)) & 0xffu;
 }
 
 // First min(k, A) available GPUs in index order, from the per-node tables.
