@@ -245,8 +245,10 @@ __device__ __forceinline__ void greedy_chain_fast_k(const NodeFast* nf, int s, i
         sum += (uint32_t)best;
         order |= (uint32_t)m << (3 * step);
     }
-    const int32_t total = (int32_t)sum >> FAST_SHIFT;
-    if (alive && total > 0) { key = (total << 3) | (7 - s); pay = order; }
+    // An alive chain has total > 0 (every step's maximum was above 7, i.e. at least 1 GB/s), and
+    // (sum >> FAST_SHIFT) << 3 is (sum >> 3) with the low three bits cleared.  pay is only read when key > 0.
+    key = alive ? (int32_t)(((sum >> (FAST_SHIFT - 3)) & ~7u) | (uint32_t)(7 - s)) : 0;
+    pay = order;
 }
 
 // The chain from start s for group size k is the first k-1 steps of the chain for size 8, so one

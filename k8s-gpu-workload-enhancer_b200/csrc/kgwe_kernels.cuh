@@ -231,7 +231,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
             for (int kk = 2; kk <= 8; ++kk) {
                 int32_t key = 0; uint32_t pay = 0;
                 if (c.integral && c.A >= kk && (c.avail >> j & 1)) greedy_chain_fast(nf, j, kk, key, pay);
-                fast_group_winner(key, pay, 0xffu << (lane & 24));
+                fast_group_winner(key, pay, 0xffffffffu);          // (all 32 lanes are here)
                 if (j == 0) memo[grp * 8 + (kk - 1)] = make_int2(key, (int)pay);
             }
             __syncwarp();
