@@ -209,6 +209,43 @@ __device__ __forceinline__ void first_k_avail(const NodeCtx& nc, int k, uint32_t
     order = nc.avail_order & (n >= 8 ? 0xffffffu : ((1u << (3 * n)) - 1u));
 }
 
+// Uniform nodes: every ACTIVE link carries the same whole-number bandwidth u >= 1 (any NVSwitch node, any
+// single-generation mesh; the host packer records u in DevNode.pad1, 0 = not uniform).  Then every candidate that is
+// linked to all members has the same aggregate |members| * u, so "largest aggregate, first candidate on ties" is simply
+// "lowest-numbered candidate still linked to all members", and a chain is a walk over bit sets held in registers:
+//   alive = avail & act_in[s];   step: c = lowest bit of alive;  alive &= act_in[c]   (act_in[c] never contains c)
+// with total = u * (1 + 2 + ... + (K-1)) when the walk reaches K members.  Same key / pay as greedy_chain_fast_k.
+__device__ __forceinline__ int node_unit(const DevNode* rec) { return (int)rec->pad1[0] | ((int)rec->pad1[1] << 8) | ((int)rec->pad1[2] << 16); }
+
+template <int K>
+__device__ __forceinline__ void greedy_chain_uniform_k(uint32_t avail, uint64_t colact, int unit, int s, int32_t& key, uint32_t& pay) {
+    const uint32_t lo = (uint32_t)colact, hi = (uint32_t)(colact >> 32);
+    uint32_t alive = avail & __byte_perm(lo, hi, (uint32_t)s);       // byte s of colact = act_in[s]; avail <= 0xff masks the rest
+    uint32_t order = (uint32_t)s;
+    bool ok = true;
+#pragma unroll
+    for (int step = 1; step < K; ++step) {
+        ok &= alive != 0u;
+        const uint32_t c = (uint32_t)(__ffs((int)alive) - 1) & 7u;   // (a dead walk keeps stepping on GPU 7; its key is dropped)
+        order += c << (3 * step);
+        alive &= __byte_perm(lo, hi, c);
+    }
+    key = ok ? (int32_t)((uint32_t)(unit * (K * (K - 1) / 2)) << 3 | (uint32_t)(7 - s)) : 0;
+    pay = order;
+}
+
+__device__ __forceinline__ void greedy_chain_uniform(uint32_t avail, uint64_t colact, int unit, int s, int k, int32_t& key, uint32_t& pay) {
+    if (k < 5) {
+        if (k < 3) { if (k == 2) greedy_chain_uniform_k<2>(avail, colact, unit, s, key, pay); else { key = 0; pay = 0; } }
+        else if (k == 3) greedy_chain_uniform_k<3>(avail, colact, unit, s, key, pay);
+        else greedy_chain_uniform_k<4>(avail, colact, unit, s, key, pay);
+    } else if (k < 7) {
+        if (k == 5) greedy_chain_uniform_k<5>(avail, colact, unit, s, key, pay); else greedy_chain_uniform_k<6>(avail, colact, unit, s, key, pay);
+    } else if (k == 7) greedy_chain_uniform_k<7>(avail, colact, unit, s, key, pay);
+    else if (k == 8) greedy_chain_uniform_k<8>(avail, colact, unit, s, key, pay);
+    else { key = 0; pay = 0; }
+}
+
 // Lane j's build step of NodeFast: row j (what each candidate gains when GPU j joins).
 __device__ __forceinline__ void node_fast_build(NodeFast* nf, const DevNode* rec, const NodeCtx& nc, int j) {
     const uint32_t act = (uint32_t)(nc.colact >> (8 * j)) & 0xffu;

@@ -119,6 +119,24 @@ int fail(kgwe_engine* e, int code, const char* fmt, ...) {
 }
 #define CU(e, call) do { cudaError_t _c = (call); if (_c != cudaSuccess) return fail(e, KGWE_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(_c)); } while (0)
 
+// Uniform bandwidth of a record (greedy_chain_uniform_k, kgwe_device.cuh): the common whole-number bandwidth u >= 1 of
+// all its active links, else 0.  A record without any active link counts as uniform (u = 1: every walk dies at once).
+// Derived from the record itself, kept in pad1 (24 bits; KGWE_MAX_BW_GBPS < 2^17).
+void set_uniform_unit(DevNode& rec) {
+    rec.pad1[0] = rec.pad1[1] = rec.pad1[2] = 0;
+    if (!(rec.flags & NODE_INTEGRAL)) return;
+    uint32_t u = 0;
+    for (int m = 0; m < KGWE_MAX_GPUS; ++m)
+        for (int c = 0; c < KGWE_MAX_GPUS; ++c) {
+            if (c == m || !(rec.act_in[m] >> c & 1)) continue;
+            const uint32_t b = (uint32_t)rec.bw_in[m][bw_slot(m, c)];
+            if (b == 0 || (u && b != u)) return;
+            u = b;
+        }
+    if (u == 0) u = 1;
+    rec.pad1[0] = (uint8_t)u; rec.pad1[1] = (uint8_t)(u >> 8); rec.pad1[2] = (uint8_t)(u >> 16);
+}
+
 // ABI record -> device record: transpose + chunk-swizzle the NVLink matrix (kgwe_device.cuh),
 // transpose the active masks, normalise masks to n_gpus.
 int to_device_record(kgwe_engine* e, const kgwe_node_image& in, DevNode& out) {
@@ -150,6 +168,7 @@ int to_device_record(kgwe_engine* e, const kgwe_node_image& in, DevNode& out) {
     out.mig_enabled_mask = in.mig_enabled_mask & gm; out.mig_has_free_mask = in.mig_has_free_mask & in.mig_enabled_mask & gm;
     out.node_flags = in.node_flags;
     out.flags = NODE_PRESENT | (integral ? NODE_INTEGRAL : 0);
+    set_uniform_unit(out);
     return KGWE_OK;
 }
 
@@ -1051,6 +1070,7 @@ int kgwe_snapshot_load(kgwe_engine* e, const void* buf, uint64_t len) {
     }
     const uint32_t old_n = e->n_nodes;
     memcpy(e->h_nodes, p, (size_t)h.n_nodes * sizeof(DevNode));
+    for (uint32_t i = 0; i < h.n_nodes; ++i) set_uniform_unit(e->h_nodes[i]);      // derived field: never trusted from a blob
     for (uint32_t i = h.n_nodes; i < old_n; ++i) memset(&e->h_nodes[i], 0, sizeof(DevNode));
     e->ledger.clear();
     for (uint64_t i = 0; i < h.n_ledger; ++i) {

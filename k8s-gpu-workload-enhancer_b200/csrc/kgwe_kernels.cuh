@@ -196,13 +196,17 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     const bool node_ok = grp < (int)tile_count;
     const DevNode* rec = tile + grp;
     NodeFast* nf = fast + grp;
-    bool warp_fast;
+    bool warp_fast, warp_uniform;
+    int unit;
     {
         NodeCtx c;
         node_ctx_core(c, rec, node_ok);
         if (want_groups) node_ctx_group_tables(c, rec);
         // integer form of the greedy inputs; usable when all four nodes of the warp are whole-number
         warp_fast = __all_sync(0xffffffffu, c.integral || !c.valid);
+        // and the bit-set walk when all four are uniform (greedy_chain_uniform_k)
+        unit = c.integral ? node_unit(rec) : 0;
+        warp_uniform = __all_sync(0xffffffffu, unit > 0 || !c.valid);
         if (c.integral) node_fast_build(nf, rec, c, j);
         else nf->init[j] = FAST_NEG;
         if (j == 0) ctxs[grp] = c;
@@ -277,11 +281,17 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
                         for (int off = 4; off >= 1; off >>= 1) b = max(b, __shfl_xor_sync(gmask, b, off, 8));
                         key = (int32_t)b;
                     } else if (kt) {
-                        if (start_ok) greedy_chain_fast(nf, j, kt, key, pay);
+                        if (start_ok) {
+                            if (warp_uniform) greedy_chain_uniform(nc.avail, nc.colact, unit, j, kt, key, pay);
+                            else greedy_chain_fast(nf, j, kt, key, pay);
+                        }
                         fast_group_winner(key, pay, gmask);
                     }
                 } else {
-                    if (kt && start_ok) greedy_chain_fast(nf, j, kt, key, pay);
+                    if (kt && start_ok) {
+                        if (warp_uniform) greedy_chain_uniform(nc.avail, nc.colact, unit, j, kt, key, pay);
+                        else greedy_chain_fast(nf, j, kt, key, pay);
+                    }
                     // all 32 lanes are here together (the branches into this block are warp-uniform): naming the whole
                     // warp spares the per-lane mask handling the compiler adds around shuffles with a lane-dependent mask
                     fast_group_winner(key, pay, 0xffffffffu);
