@@ -226,7 +226,7 @@ __device__ __forceinline__ void greedy_chain_uniform_k(uint32_t avail, uint64_t 
 #pragma unroll
     for (int step = 1; step < K; ++step) {
         ok &= alive != 0u;
-        const uint32_t c = (uint32_t)(__ffs((int)alive) - 1) & 7u;   // (a dead walk keeps stepping on GPU 7; its key is dropped)
+        const uint32_t c = (uint32_t)(__ffs((int)alive) - 1);        // 0..7; all ones once the walk is dead (alive == 0 stays 0, key dropped)
         order += c << (3 * step);
         alive &= __byte_perm(lo, hi, c);
     }
