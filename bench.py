@@ -132,6 +132,22 @@ class ClockSampler:
         return out
 
 
+def uniform_nodes(nodes):
+    """How many records take K1's bit-set walk: whole-number bandwidths, all ACTIVE links of the node equal and >= 1
+    (mirrors set_uniform_unit in csrc/kgwe_engine.cu)."""
+    bw = nodes["nvl_bw"]                                      # [N, i, j]: i's link to j
+    bits = (1 << np.arange(8)).astype(np.uint8)
+    ng = np.arange(8)[None, :] < nodes["n_gpus"][:, None]
+    act = ((nodes["nvl_active"] & nodes["nvl_present"])[:, :, None] & bits[None, None, :]) != 0
+    act &= ng[:, :, None] & ng[:, None, :] & ~np.eye(8, dtype=bool)[None]
+    present = ((nodes["nvl_present"][:, :, None] & bits[None, None, :]) != 0) & ng[:, :, None] & ng[:, None, :] & ~np.eye(8, dtype=bool)[None]
+    integral = np.where(present, bw == np.floor(bw), True).all(axis=(1, 2))
+    hi = np.where(act, bw, -np.inf).max(axis=(1, 2))
+    lo = np.where(act, bw, np.inf).min(axis=(1, 2))
+    none = ~act.any(axis=(1, 2))
+    return (integral & (none | ((hi == lo) & (lo >= 1)))).sum()
+
+
 def host_cores():
     try:
         return len(os.sched_getaffinity(0))
@@ -386,7 +402,7 @@ def run_kgwe(args):
         eng2.close()
 
     # ---- E1 exhaustive k-of-8 subset mode and E2 MIG bin-packing (extensions; reported beside the headline) ----
-    exh = mig = memo = None
+    exh = mig = memo = tiers = None
     if world == 1:
         qx = pods.copy()
         qx["flags"] = abi.POD_EXHAUSTIVE
@@ -425,6 +441,31 @@ def run_kgwe(args):
         memo = {"ms_per_step": mms, "candidates_per_sec": (engm.stats()["candidates"] - c0) / 10 / (mms * 1e-3), "evaluations_per_sec": P * n_local / (mms * 1e-3),
                 "note": "greedy winner per (node, GPUCount) found once per node tile and looked up per evaluation; identical results; NOT the headline (brute-force) rate"}
         engm.close()
+        # the numeric tier K1 takes depends on the nodes' link bandwidths; the headline cluster is all "uniform" (every
+        # active link of a node equal: the bit-set walk).  Same workload with the links perturbed, to show the other tiers.
+        tiers = {"headline_cluster": {"uniform_nodes": int(uniform_nodes(nodes)), "nodes": int(N)}}
+        rngt = kg.synth.SplitMix64(77)
+        for tier, make in (("int32", lambda bw: np.where(bw > 0, np.floor(bw * (0.5 + rngt.uniform(bw.size).reshape(bw.shape))), 0.0)),
+                           ("fp64", lambda bw: bw * (0.5 + rngt.uniform(bw.size).reshape(bw.shape)))):
+            nt = nodes.copy()
+            nt["nvl_bw"] = make(nodes["nvl_bw"])
+            engt = kg.Engine(max_nodes=N, device=local_rank)
+            engt.upsert_nodes(nt)
+            engt.seed_ledger(ledger)
+            for _ in range(2):
+                engt.score_batch_device(d_pods.data_ptr(), P, None, scorer.d_scores.data_ptr(), 1, scorer.d_top.data_ptr(), sptr)
+            torch.cuda.synchronize()
+            c0 = engt.stats()["candidates"]
+            reps = 5 if tier == "int32" else 2
+            x0.record(stream)
+            for _ in range(reps):
+                engt.score_batch_device(d_pods.data_ptr(), P, None, scorer.d_scores.data_ptr(), 1, scorer.d_top.data_ptr(), sptr)
+            x1.record(stream)
+            torch.cuda.synchronize()
+            tms = x0.elapsed_time(x1) / reps
+            tiers[tier] = {"ms_per_step": tms, "candidates_per_sec": (engt.stats()["candidates"] - c0) / reps / (tms * 1e-3), "evaluations_per_sec": P * n_local / (tms * 1e-3),
+                           "links": "whole-number, irregular (no common value per node)" if tier == "int32" else "fractional"}
+            engt.close()
         mg, mp = kg.synth.make_mig(10000, 50000)
         a = time.perf_counter()
         asg, mg_after = eng.mig_pack(mg, mp)
@@ -480,6 +521,7 @@ def run_kgwe(args):
             out["mig_pack"] = mig
         if memo:
             out["memoised_group_search"] = memo
+            out["link_tiers"] = tiers
         if not args.no_cpu_baseline and world == 1:
             entry.build_oracle()
             cores = host_cores()
