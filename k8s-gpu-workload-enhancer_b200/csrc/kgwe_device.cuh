@@ -209,16 +209,23 @@ __device__ __forceinline__ void first_k_avail(const NodeCtx& nc, int k, uint32_t
     order = nc.avail_order & (n >= 8 ? 0xffffffu : ((1u << (3 * n)) - 1u));
 }
 
-// Uniform nodes: every ACTIVE link carries the same whole-number bandwidth u >= 1 (any NVSwitch node, any
-// single-generation mesh; the host packer records u in DevNode.pad1, 0 = not uniform).  Then every candidate that is
-// linked to all members has the same aggregate |members| * u, so "largest aggregate, first candidate on ties" is simply
-// "lowest-numbered candidate still linked to all members", and a chain is a walk over bit sets held in registers:
+// Uniform nodes: every ACTIVE link of the node carries the same bandwidth u > 0 - any NVSwitch node, any single-generation
+// mesh, whole-number or not (the host packer records where one such link sits in DevNode.pad1[0]: 0x80 | m << 3 | c,
+// 0x40 = "no active link at all", 0 = not uniform).  Every candidate that is linked to all members then has the SAME
+// aggregate (the same additions of u in the same order, so this holds bit for bit in float64 too), and "largest
+// aggregate, first candidate on ties" is simply "lowest-numbered candidate still linked to all members".  A chain becomes
+// a walk over bit sets held in registers:
 //   alive = avail & act_in[s];   step: c = lowest bit of alive;  alive &= act_in[c]   (act_in[c] never contains c)
-// with total = u * (1 + 2 + ... + (K-1)) when the walk reaches K members.  Same key / pay as greedy_chain_fast_k.
-__device__ __forceinline__ int node_unit(const DevNode* rec) { return (int)rec->pad1[0] | ((int)rec->pad1[1] << 8) | ((int)rec->pad1[2] << 16); }
+// and its total depends on (u, K) only: T[K] = S_1 + ... + S_(K-1) with S_t = S_(t-1) + u, added in that order in float64
+// as the reference does (uniform_totals_build; exact k(k-1)/2 * u for whole numbers).  key = 8 | (7 - s) marks a walk
+// that reached K members (the totals are equal, so the key only ranks the start lanes); pay = join order.
+__device__ __forceinline__ int node_uniform_code(const DevNode* rec) { return rec->pad1[0]; }
+__device__ __forceinline__ double node_uniform_bw(const DevNode* rec, int code) {
+    return (code & 0x80) ? rec->bw_in[(code >> 3) & 7][bw_slot((code >> 3) & 7, code & 7)] : 0.0;
+}
 
 template <int K>
-__device__ __forceinline__ void greedy_chain_uniform_k(uint32_t avail, uint64_t colact, int unit, int s, int32_t& key, uint32_t& pay) {
+__device__ __forceinline__ void greedy_walk_uniform_k(uint32_t avail, uint64_t colact, int s, int32_t& key, uint32_t& pay) {
     const uint32_t lo = (uint32_t)colact, hi = (uint32_t)(colact >> 32);
     uint32_t alive = avail & __byte_perm(lo, hi, (uint32_t)s);       // byte s of colact = act_in[s]; avail <= 0xff masks the rest
     uint32_t order = (uint32_t)s;
@@ -230,20 +237,33 @@ __device__ __forceinline__ void greedy_chain_uniform_k(uint32_t avail, uint64_t 
         order += c << (3 * step);
         alive &= __byte_perm(lo, hi, c);
     }
-    key = ok ? (int32_t)((uint32_t)(unit * (K * (K - 1) / 2)) << 3 | (uint32_t)(7 - s)) : 0;
+    key = ok ? (8 | (7 - s)) : 0;
     pay = order;
 }
 
-__device__ __forceinline__ void greedy_chain_uniform(uint32_t avail, uint64_t colact, int unit, int s, int k, int32_t& key, uint32_t& pay) {
+__device__ __forceinline__ void greedy_walk_uniform(uint32_t avail, uint64_t colact, int s, int k, int32_t& key, uint32_t& pay) {
     if (k < 5) {
-        if (k < 3) { if (k == 2) greedy_chain_uniform_k<2>(avail, colact, unit, s, key, pay); else { key = 0; pay = 0; } }
-        else if (k == 3) greedy_chain_uniform_k<3>(avail, colact, unit, s, key, pay);
-        else greedy_chain_uniform_k<4>(avail, colact, unit, s, key, pay);
+        if (k < 3) { if (k == 2) greedy_walk_uniform_k<2>(avail, colact, s, key, pay); else { key = 0; pay = 0; } }
+        else if (k == 3) greedy_walk_uniform_k<3>(avail, colact, s, key, pay);
+        else greedy_walk_uniform_k<4>(avail, colact, s, key, pay);
     } else if (k < 7) {
-        if (k == 5) greedy_chain_uniform_k<5>(avail, colact, unit, s, key, pay); else greedy_chain_uniform_k<6>(avail, colact, unit, s, key, pay);
-    } else if (k == 7) greedy_chain_uniform_k<7>(avail, colact, unit, s, key, pay);
-    else if (k == 8) greedy_chain_uniform_k<8>(avail, colact, unit, s, key, pay);
+        if (k == 5) greedy_walk_uniform_k<5>(avail, colact, s, key, pay); else greedy_walk_uniform_k<6>(avail, colact, s, key, pay);
+    } else if (k == 7) greedy_walk_uniform_k<7>(avail, colact, s, key, pay);
+    else if (k == 8) greedy_walk_uniform_k<8>(avail, colact, s, key, pay);
     else { key = 0; pay = 0; }
+}
+
+// T[2..8] of a uniform node, kept in the spare 16 bytes at the end of NodeFast rows 0..3 (two doubles per row).
+__device__ __forceinline__ double* uniform_total_slot(NodeFast* nf, int k) {          // 2 <= k <= 8
+    return reinterpret_cast<double*>(&nf->row[(k - 2) >> 1][8]) + ((k - 2) & 1);
+}
+__device__ __forceinline__ void uniform_totals_build(NodeFast* nf, double u) {
+    double S = 0.0, T = 0.0;
+    for (int k = 2; k <= 8; ++k) {
+        S = __dadd_rn(S, u);            // the aggregate of the candidate chosen at step k-1: u added k-1 times from 0.0
+        T = __dadd_rn(T, S);            // findBestNVLinkGroup's running total
+        *uniform_total_slot(nf, k) = T;
+    }
 }
 
 // Lane j's build step of NodeFast: row j (what each candidate gains when GPU j joins).

@@ -119,22 +119,21 @@ int fail(kgwe_engine* e, int code, const char* fmt, ...) {
 }
 #define CU(e, call) do { cudaError_t _c = (call); if (_c != cudaSuccess) return fail(e, KGWE_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(_c)); } while (0)
 
-// Uniform bandwidth of a record (greedy_chain_uniform_k, kgwe_device.cuh): the common whole-number bandwidth u >= 1 of
-// all its active links, else 0.  A record without any active link counts as uniform (u = 1: every walk dies at once).
-// Derived from the record itself, kept in pad1 (24 bits; KGWE_MAX_BW_GBPS < 2^17).
+// Uniform-link code of a record (greedy_walk_uniform_k, kgwe_device.cuh): set when all its ACTIVE links carry the same
+// bandwidth u > 0 (whole-number or not).  pad1[0] = 0x80 | m << 3 | c names one such link (c's link to m) so the kernels
+// can fetch u; 0x40 = the record has no active link at all (every walk dies at once); 0 = not uniform.
+// Derived from the record itself, never taken from outside.
 void set_uniform_unit(DevNode& rec) {
     rec.pad1[0] = rec.pad1[1] = rec.pad1[2] = 0;
-    if (!(rec.flags & NODE_INTEGRAL)) return;
-    uint32_t u = 0;
+    bool any = false; double u = 0.0; int loc = 0;
     for (int m = 0; m < KGWE_MAX_GPUS; ++m)
         for (int c = 0; c < KGWE_MAX_GPUS; ++c) {
             if (c == m || !(rec.act_in[m] >> c & 1)) continue;
-            const uint32_t b = (uint32_t)rec.bw_in[m][bw_slot(m, c)];
-            if (b == 0 || (u && b != u)) return;
-            u = b;
+            const double b = rec.bw_in[m][bw_slot(m, c)];
+            if (!(b > 0.0) || (any && b != u)) return;
+            if (!any) { any = true; u = b; loc = (m << 3) | c; }
         }
-    if (u == 0) u = 1;
-    rec.pad1[0] = (uint8_t)u; rec.pad1[1] = (uint8_t)(u >> 8); rec.pad1[2] = (uint8_t)(u >> 16);
+    rec.pad1[0] = any ? (uint8_t)(0x80 | loc) : (uint8_t)0x40;
 }
 
 // ABI record -> device record: transpose + chunk-swizzle the NVLink matrix (kgwe_device.cuh),

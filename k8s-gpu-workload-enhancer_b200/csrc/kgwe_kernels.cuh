@@ -197,18 +197,18 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     const DevNode* rec = tile + grp;
     NodeFast* nf = fast + grp;
     bool warp_fast, warp_uniform;
-    int unit;
     {
         NodeCtx c;
         node_ctx_core(c, rec, node_ok);
         if (want_groups) node_ctx_group_tables(c, rec);
         // integer form of the greedy inputs; usable when all four nodes of the warp are whole-number
         warp_fast = __all_sync(0xffffffffu, c.integral || !c.valid);
-        // and the bit-set walk when all four are uniform (greedy_chain_uniform_k)
-        unit = c.integral ? node_unit(rec) : 0;
-        warp_uniform = __all_sync(0xffffffffu, unit > 0 || !c.valid);
+        // and the bit-set walk when all four are uniform (greedy_walk_uniform_k); the memoised variant keeps its int32 tables
+        const int ucode = c.valid ? node_uniform_code(rec) : 0;
+        warp_uniform = !MEMO && __all_sync(0xffffffffu, ucode != 0 || !c.valid);
         if (c.integral) node_fast_build(nf, rec, c, j);
         else nf->init[j] = FAST_NEG;
+        if (!MEMO && ucode && j == 0) uniform_totals_build(nf, node_uniform_bw(rec, ucode));
         if (j == 0) ctxs[grp] = c;
         if (TABLES) {
             // E1 subset keys of this node: lane j fills slots j, j+8, ...
@@ -244,7 +244,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     const NodeCtx& nc = ctxs[grp];
     const uint32_t gnode = P.node_base + node;
     const uint32_t gmask = 0xffu << (lane & 24);
-    const bool start_ok = nf->init[j] >= 0;             // this lane's start GPU is available
+    const bool start_ok = (nc.avail >> j) & 1;          // this lane's start GPU is available
     unsigned long long cand = 0;
 
     for (uint32_t p0 = p_begin; p0 < p_end; p0 += 8) {
@@ -256,7 +256,8 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         const bool eligible = live && eval_filter(rec, nc, pod, k);
         const bool wants_group = k >= 2 && is_nvlink_pref(pod);
         const bool exhaustive = wants_group && (pod.flags & KGWE_POD_EXHAUSTIVE);
-        const bool octet = warp_fast && (TABLES || !__any_sync(0xffffffffu, live && exhaustive));
+        const bool any_exh = __any_sync(0xffffffffu, live && exhaustive);
+        const bool octet = (warp_fast && (TABLES || !any_exh)) || (warp_uniform && !any_exh);
         EvalOut o;
         if (octet) {
             // ---- phase A: the group searches, one pod slot at a time ----
@@ -282,14 +283,14 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
                         key = (int32_t)b;
                     } else if (kt) {
                         if (start_ok) {
-                            if (warp_uniform) greedy_chain_uniform(nc.avail, nc.colact, unit, j, kt, key, pay);
+                            if (warp_uniform) greedy_walk_uniform(nc.avail, nc.colact, j, kt, key, pay);
                             else greedy_chain_fast(nf, j, kt, key, pay);
                         }
                         fast_group_winner(key, pay, gmask);
                     }
                 } else {
                     if (kt && start_ok) {
-                        if (warp_uniform) greedy_chain_uniform(nc.avail, nc.colact, unit, j, kt, key, pay);
+                        if (warp_uniform) greedy_walk_uniform(nc.avail, nc.colact, j, kt, key, pay);
                         else greedy_chain_fast(nf, j, kt, key, pay);
                     }
                     // all 32 lanes are here together (the branches into this block are warp-uniform): naming the whole
@@ -300,6 +301,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
             }
             // ---- phase B: lane j finishes pod p0 + j ----
             bool found = mykey > 0; double win_total = (double)(mykey >> 3);
+            if (warp_uniform && found) win_total = *uniform_total_slot(nf, k);      // (found implies 2 <= k <= 8)
             uint32_t ord = mypay, sel = found ? mask_of_order(mypay, k) : 0u, ncand = (uint32_t)nc.A;
             if (TABLES && exhaustive) {
                 win_total = (double)(mykey >> 8);

@@ -166,4 +166,4 @@ def test_faithful_equals_indexed_fuzz(kg, orc):
         ga = orc.schedule_gangs(abi, nodes, led, pods, gang_of, hint=hint, mode=orc.FAITHFUL)
         gb = orc.schedule_gangs(abi, nodes, led, pods, gang_of, hint=hint, mode=orc.INDEXED)
         assert ga[0].tobytes() == gb[0].tobytes(), f"seed {seed}: gang decisions"
-    assert kinds == {0, 1, 2, 3, 4}
+    assert kinds == {0, 1, 2, 3, 4, 5}

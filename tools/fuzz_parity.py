@@ -15,7 +15,7 @@ def make_case(abi, synth, seed, n_lo=40, n_span=400, p_lo=40, p_span=200):
     P = int(p_lo + u[1] * p_span)
     nodes = synth.make_cluster(N, "mixed" if u[2] < 0.8 else "dgx", seed=seed, unhealthy_frac=u[3] * 0.3, inactive_link_frac=u[4] * 0.2,
                                partial_node_frac=u[5] * 0.5, mig_frac=u[6])
-    kind = int(u[7] * 5)
+    kind = int(u[7] * 6)
     if kind == 1:      # fractional, asymmetric bandwidths on some nodes (FP64 path)
         frac = rng.uniform(N) < 0.4
         jit = 0.5 + rng.uniform(N * 64).reshape(N, 8, 8)
@@ -23,6 +23,11 @@ def make_case(abi, synth, seed, n_lo=40, n_span=400, p_lo=40, p_span=200):
     elif kind == 2:    # whole-number but irregular, asymmetric bandwidths (integer path, no common unit)
         jit = rng.randint(1, 2000, N * 64).reshape(N, 8, 8).astype(np.float64)
         nodes["nvl_bw"] = np.where(nodes["nvl_bw"] > 0, jit, 0.0)
+    elif kind == 5:    # one fractional bandwidth per node on most nodes (uniform walk with float64 totals), per-link jitter on the rest
+        per_node = 0.5 + rng.uniform(N)
+        jit = 0.5 + rng.uniform(N * 64).reshape(N, 8, 8)
+        odd = rng.uniform(N) < 0.25
+        nodes["nvl_bw"] = nodes["nvl_bw"] * np.where(odd[:, None, None], jit, per_node[:, None, None])
     elif kind == 3:    # zero-bandwidth links here and there
         z = rng.uniform(N * 64).reshape(N, 8, 8) < 0.15
         nodes["nvl_bw"] = np.where(z, 0.0, nodes["nvl_bw"])
