@@ -158,8 +158,11 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     uint32_t* subset = reinterpret_cast<uint32_t*>(smem + kBase);                       // TABLES only
     uint8_t* smask = smem + kBase + TILE_NODES * 256 * 4;                               // TABLES only
     int2* memo = reinterpret_cast<int2*>(smem + kBase + (TABLES ? SUBSET_SMEM_BYTES : 0));   // MEMO only
-    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem + kBase + (TABLES ? SUBSET_SMEM_BYTES : 0) + (MEMO ? MEMO_SMEM_BYTES : 0));
-    uint64_t* bar = reinterpret_cast<uint64_t*>(keys + pods_per_chunk);
+    // per-pod arg-max of this CTA's tile, as a 32-bit word (TotalScore << 6 | 63 - node-in-tile: a native shared-memory
+    // atomicMax; the 64-bit form is a compare-and-swap spin loop, and all warps of a CTA hit the same 8 pods together).
+    // TotalScore of a kept evaluation is 1 .. 4000 (|weights| <= 1000, kgwe_engine_create), far below 2^25.
+    uint32_t* keys = reinterpret_cast<uint32_t*>(smem + kBase + (TABLES ? SUBSET_SMEM_BYTES : 0) + (MEMO ? MEMO_SMEM_BYTES : 0));
+    uint64_t* bar = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned long long*>(keys) + pods_per_chunk);
 
     const int tid = threadIdx.x, lane = tid & 31, grp = tid >> 3, j = tid & 7;
     const uint32_t tile_first = blockIdx.x * TILE_NODES;
@@ -177,7 +180,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         mbar_expect_tx(bar, bytes);
         tma_bulk_g2s(tile, nodes + tile_first, bytes, bar);
     }
-    if (best) for (uint32_t i = tid; i < pods_per_chunk; i += SCORE_THREADS) keys[i] = 0ull;
+    if (best) for (uint32_t i = tid; i < pods_per_chunk; i += SCORE_THREADS) keys[i] = 0u;
     // NUMA / PCIe group tables are only worth building when the chunk has a pod that asks for them
     bool want_groups = false;
     for (uint32_t p = p_begin + tid; p < p_end; p += SCORE_THREADS) {
@@ -242,7 +245,6 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         }
     }
     const NodeCtx& nc = ctxs[grp];
-    const uint32_t gnode = P.node_base + node;
     const uint32_t gmask = 0xffu << (lane & 24);
     const bool start_ok = (nc.avail >> j) & 1;          // this lane's start GPU is available
     unsigned long long cand = 0;
@@ -267,6 +269,10 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
                 const int2 w = memo[grp * 8 + (k - 1)];
                 mykey = w.x; mypay = (uint32_t)w.y; chain_k = 0;
             }
+            if (warp_uniform && !any_exh) {
+                // uniform nodes: every lane settles its own pod (first_uniform_walk) - no slots, no shuffles
+                if (chain_k) { mykey = first_uniform_walk(nc.avail, nc.colact, k, mypay) ? 8 : 0; chain_k = 0; }
+            } else
 #pragma unroll 1
             for (int t = 0; t < 8; ++t) {
                 const int ct = __shfl_sync(0xffffffffu, chain_k, t, 8);
@@ -318,9 +324,9 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
                 }
             }
             if (best) {
-                unsigned long long key = (live && (o.flags & KGWE_F_KEPT)) ? rank_key(o.total, gnode) : 0ull;
-                unsigned long long k2 = __shfl_xor_sync(0xffffffffu, key, 8);  key = k2 > key ? k2 : key;
-                k2 = __shfl_xor_sync(0xffffffffu, key, 16);                    key = k2 > key ? k2 : key;
+                uint32_t key = (live && (o.flags & KGWE_F_KEPT)) ? (((uint32_t)o.total << 6) | (uint32_t)(63 - grp)) : 0u;
+                key = max(key, __shfl_xor_sync(0xffffffffu, key, 8));
+                key = max(key, __shfl_xor_sync(0xffffffffu, key, 16));
                 if (lane < 8 && key) atomicMax(&keys[p - p_begin], key);
             }
         } else {
@@ -339,9 +345,9 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
                     }
                 }
                 if (best) {
-                    unsigned long long key = (o.flags & KGWE_F_KEPT) ? rank_key(o.total, gnode) : 0ull;
-                    unsigned long long k2 = __shfl_xor_sync(0xffffffffu, key, 8);  key = k2 > key ? k2 : key;
-                    k2 = __shfl_xor_sync(0xffffffffu, key, 16);                    key = k2 > key ? k2 : key;
+                    uint32_t key = (o.flags & KGWE_F_KEPT) ? (((uint32_t)o.total << 6) | (uint32_t)(63 - grp)) : 0u;
+                    key = max(key, __shfl_xor_sync(0xffffffffu, key, 8));
+                    key = max(key, __shfl_xor_sync(0xffffffffu, key, 16));
                     if (lane == 0 && key) atomicMax(&keys[pt - p_begin], key);
                 }
             }
@@ -353,8 +359,10 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     if (lane == 0 && counters && cand) atomicAdd(&counters[1], cand);
     if (best) {
         __syncthreads();
-        for (uint32_t i = tid; i < p_end - p_begin; i += SCORE_THREADS)
-            if (keys[i]) atomicMax(&best[p_begin + i], keys[i]);
+        for (uint32_t i = tid; i < p_end - p_begin; i += SCORE_THREADS) {
+            const uint32_t kk = keys[i];
+            if (kk) atomicMax(&best[p_begin + i], rank_key((int32_t)(kk >> 6), P.node_base + tile_first + (63u - (kk & 63u))));
+        }
     }
     if (tail.out) {
         // latency path (n_pods <= 64): the last CTA to finish turns the keys into placements in the
