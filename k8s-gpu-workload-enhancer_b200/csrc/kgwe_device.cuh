@@ -253,25 +253,23 @@ __device__ __forceinline__ void greedy_walk_uniform(uint32_t avail, uint64_t col
     else { key = 0; pay = 0; }
 }
 
-// One lane, one evaluation: the walks of a uniform node tried from the lowest available start upwards.  All walks that
-// reach k members have the same total and the reference keeps the FIRST start that reaches the best total (strict >,
-// scheduler.go:428-431), so the first walk that completes is its answer and the later starts cannot change it.
-// Returns true with the join order, false when no start reaches k members (k in 2..8).
+// One lane, one evaluation: the walk from the LOWEST available start.  All walks that reach k members have the same total
+// and the reference keeps the first start that reaches the best total (strict >, scheduler.go:428-431), so when this walk
+// completes it is the reference's answer and the other seven starts cannot change it.  When it dies (a link down, a
+// sparse mesh) the caller falls back to the 8-lane search over all starts.  2 <= k <= 8, avail != 0.
 __device__ __forceinline__ bool first_uniform_walk(uint32_t avail, uint64_t colact, int k, uint32_t& order_out) {
     const uint32_t lo = (uint32_t)colact, hi = (uint32_t)(colact >> 32);
-    for (uint32_t starts = avail; starts; starts &= starts - 1u) {
-        const uint32_t s = (uint32_t)(__ffs((int)starts) - 1);
-        uint32_t alive = avail & __byte_perm(lo, hi, s);
-        uint32_t order = s;
-        int step = 1;
-        for (; step < k && alive; ++step) {
-            const uint32_t c = (uint32_t)(__ffs((int)alive) - 1);
-            order += c << (3 * step);
-            alive &= __byte_perm(lo, hi, c);
-        }
-        if (step == k) { order_out = order; return true; }
+    const uint32_t s = (uint32_t)(__ffs((int)avail) - 1);
+    uint32_t alive = avail & __byte_perm(lo, hi, s);
+    uint32_t order = s;
+    int step = 1;
+    for (; step < k && alive; ++step) {
+        const uint32_t c = (uint32_t)(__ffs((int)alive) - 1);
+        order += c << (3 * step);
+        alive &= __byte_perm(lo, hi, c);
     }
-    return false;
+    order_out = order;
+    return step == k;
 }
 
 // T[2..8] of a uniform node, kept in the spare 16 bytes at the end of NodeFast rows 0..3 (two doubles per row).

@@ -269,14 +269,19 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
                 const int2 w = memo[grp * 8 + (k - 1)];
                 mykey = w.x; mypay = (uint32_t)w.y; chain_k = 0;
             }
-            if (warp_uniform && !any_exh) {
-                // uniform nodes: every lane settles its own pod (first_uniform_walk) - no slots, no shuffles
-                if (chain_k) { mykey = first_uniform_walk(nc.avail, nc.colact, k, mypay) ? 8 : 0; chain_k = 0; }
-            } else
+            if (warp_uniform && chain_k && !exhaustive) {
+                // uniform nodes: each lane first tries the walk from its node's lowest available GPU for its own pod; that
+                // settles nearly every evaluation without any cross-lane work (first_uniform_walk)
+                if (first_uniform_walk(nc.avail, nc.colact, k, mypay)) { mykey = 8; chain_k = 0; }
+            }
+            // the 8-lane search, one pod slot at a time, for whatever is left: everything on non-uniform nodes, on uniform
+            // ones only the pods whose first walk died
+            uint32_t pend = __ballot_sync(0xffffffffu, chain_k != 0);
+            pend = (pend | (pend >> 8) | (pend >> 16) | (pend >> 24)) & 0xffu;
 #pragma unroll 1
-            for (int t = 0; t < 8; ++t) {
+            for (; pend; pend &= pend - 1u) {
+                const int t = __ffs((int)pend) - 1;
                 const int ct = __shfl_sync(0xffffffffu, chain_k, t, 8);
-                if (!__any_sync(0xffffffffu, ct != 0)) continue;       // warp-uniform
                 const int kt = ct & 15;
                 int32_t key = 0; uint32_t pay = 0;
                 if (TABLES && __any_sync(0xffffffffu, ct & 16)) {      // some group has an exhaustive pod in this slot
@@ -303,7 +308,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
                     // warp spares the per-lane mask handling the compiler adds around shuffles with a lane-dependent mask
                     fast_group_winner(key, pay, 0xffffffffu);
                 }
-                if (j == t) { mykey = key; mypay = pay; }
+                if (j == t && ct) { mykey = key; mypay = pay; }      // (groups whose pod of this slot is already settled keep their result)
             }
             // ---- phase B: lane j finishes pod p0 + j ----
             bool found = mykey > 0; double win_total = (double)(mykey >> 3);
