@@ -164,7 +164,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     uint32_t* keys = reinterpret_cast<uint32_t*>(smem + kBase + (TABLES ? SUBSET_SMEM_BYTES : 0) + (MEMO ? MEMO_SMEM_BYTES : 0));
     uint64_t* bar = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned long long*>(keys) + pods_per_chunk);
 
-    const int tid = threadIdx.x, lane = tid & 31, grp = tid >> 3, j = tid & 7;
+    const int tid = threadIdx.x, lane = tid & 31, j = tid & 7;
     const uint32_t tile_first = blockIdx.x * TILE_NODES;
     const uint32_t tile_count = min((uint32_t)TILE_NODES, n_nodes - tile_first);
     const uint32_t p_begin = blockIdx.y * pods_per_chunk;
@@ -195,12 +195,17 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     mbar_wait(bar, 0);
     want_groups = __syncthreads_or(want_groups);
 
-    const uint32_t node = tile_first + grp;
-    const bool node_ok = grp < (int)tile_count;
-    const DevNode* rec = tile + grp;
-    NodeFast* nf = fast + grp;
-    bool warp_fast, warp_uniform;
+    // ---- set-up: lane group g of the CTA prepares node g of the tile; quad = the 4 nodes of one warp ----
+    constexpr int QUADS = SCORE_THREADS / 32;
+    __shared__ uint8_t quad_flags[QUADS];           // bit 0: all four nodes whole-number (int32 chains), bit 1: all four uniform (bit-set walks)
+    __shared__ unsigned int next_item;
+    if (tid == 0) next_item = 0;
     {
+        const int grp = tid >> 3;
+        const bool node_ok = grp < (int)tile_count;
+        const DevNode* rec = tile + grp;
+        NodeFast* nf = fast + grp;
+        bool warp_fast, warp_uniform;
         NodeCtx c;
         node_ctx_core(c, rec, node_ok);
         if (want_groups) node_ctx_group_tables(c, rec);
@@ -243,13 +248,31 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
             }
             __syncwarp();
         }
+        if (lane == 0) quad_flags[tid >> 5] = (uint8_t)((warp_fast ? 1 : 0) | (warp_uniform ? 2 : 0));
     }
-    const NodeCtx& nc = ctxs[grp];
+    __syncthreads();            // every warp may now work on any quad's tables
     const uint32_t gmask = 0xffu << (lane & 24);
-    const bool start_ok = (nc.avail >> j) & 1;          // this lane's start GPU is available
     unsigned long long cand = 0;
 
-    for (uint32_t p0 = p_begin; p0 < p_end; p0 += 8) {
+    // Work items = (octet of pods, quad of nodes), handed out through a shared counter in pod-major order: a warp whose
+    // nodes need the 8-lane search more often (links down, sparse meshes) simply takes fewer items, instead of making the
+    // other 15 warps wait for it at the end of the chunk (that wait was a third of all warp time with a fixed split).
+    const uint32_t n_items = ((p_end - p_begin + 7u) / 8u) * QUADS;
+    for (;;) {
+        uint32_t item = 0;
+        if (lane == 0) item = atomicAdd(&next_item, 1u);
+        item = __shfl_sync(0xffffffffu, item, 0);
+        if (item >= n_items) break;
+        const uint32_t p0 = p_begin + (item / QUADS) * 8u;
+        const int quad = (int)(item % QUADS);
+        const int grp = quad * 4 + (lane >> 3);
+        const uint32_t node = tile_first + grp;
+        const bool node_ok = grp < (int)tile_count;
+        const DevNode* rec = tile + grp;
+        NodeFast* nf = fast + grp;
+        const NodeCtx& nc = ctxs[grp];
+        const bool warp_fast = quad_flags[quad] & 1, warp_uniform = quad_flags[quad] & 2;
+        const bool start_ok = (nc.avail >> j) & 1;          // this lane's start GPU is available
         // ---- phase 0: lane j owns pod p0 + j ----
         const uint32_t p = p0 + j;
         const bool live = p < p_end;
@@ -379,7 +402,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         __syncthreads();
         if (ticket == gridDim.x * gridDim.y - 1) {
             __threadfence();
-            finalize_one(nodes, n_nodes, pods, (uint32_t)grp, (uint32_t)grp < n_pods, hint, hint_row_bytes, best, tail.out, P, lane, spods);
+            finalize_one(nodes, n_nodes, pods, (uint32_t)(tid >> 3), (uint32_t)(tid >> 3) < n_pods, hint, hint_row_bytes, best, tail.out, P, lane, spods);
             __threadfence_system();
             __syncthreads();
             if (tid == 0) { *tail.done = 0u; *reinterpret_cast<volatile unsigned int*>(tail.flag) = tail.seq; }
