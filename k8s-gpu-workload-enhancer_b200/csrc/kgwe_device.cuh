@@ -272,16 +272,20 @@ __device__ __forceinline__ bool first_uniform_walk(uint32_t avail, uint64_t cola
     return step == k;
 }
 
-// T[2..8] of a uniform node, kept in the spare 16 bytes at the end of NodeFast rows 0..3 (two doubles per row).
-__device__ __forceinline__ double* uniform_total_slot(NodeFast* nf, int k) {          // 2 <= k <= 8
-    return reinterpret_cast<double*>(&nf->row[(k - 2) >> 1][8]) + ((k - 2) & 1);
+// The NVLink TopologyScore of a uniform node depends on k only: the walk's total is T[k] = S_1 + ... + S_(k-1) with
+// S_t = S_(t-1) + u, added in that order in float64 as the reference does (exact k(k-1)/2 * u for whole numbers), and the
+// score is nvlink_score(T[k]).  Built once per node per CTA, kept as 7 ints in the spare 16 bytes at the end of NodeFast
+// rows 0 and 1, so an evaluation on a uniform node does no floating-point arithmetic at all.
+__device__ __forceinline__ int* uniform_topo_slot(NodeFast* nf, int k) {             // 2 <= k <= 8
+    return &nf->row[(k - 2) >> 2][8 + ((k - 2) & 3)];
 }
-__device__ __forceinline__ void uniform_totals_build(NodeFast* nf, double u) {
+__device__ __forceinline__ int nvlink_score(double total, int k, double norm);
+__device__ __forceinline__ void uniform_topo_build(NodeFast* nf, double u, double norm) {
     double S = 0.0, T = 0.0;
     for (int k = 2; k <= 8; ++k) {
         S = __dadd_rn(S, u);            // the aggregate of the candidate chosen at step k-1: u added k-1 times from 0.0
         T = __dadd_rn(T, S);            // findBestNVLinkGroup's running total
-        *uniform_total_slot(nf, k) = T;
+        *uniform_topo_slot(nf, k) = nvlink_score(T, k, norm);
     }
 }
 
@@ -481,7 +485,7 @@ __device__ __forceinline__ bool eval_filter(const DevNode* rec, const NodeCtx& n
 __device__ __forceinline__ void eval_finish(const DevNode* rec, const NodeCtx& nc, const kgwe_pod_req& pod, const Params& P,
                                             bool hinted, bool eligible, int k,
                                             bool found, double win_total, uint32_t sel, uint32_t order, uint32_t candidates,
-                                            EvalOut& o) {
+                                            EvalOut& o, int topo_known = -1) {
     o.total = o.topo = o.res = o.bal = 0; o.mask = o.order = o.flags = 0; o.candidates = 1;
     if (!eligible) return;
     int topo = 0; int nsel = 0; bool fallback = false;
@@ -493,7 +497,7 @@ __device__ __forceinline__ void eval_finish(const DevNode* rec, const NodeCtx& n
         if (!found) {                    // no fully connected group: scheduler.go:358-365
             topo = 30; fallback = true; first_k_avail(nc, k, sel, order, nsel);
         } else {
-            topo = nvlink_score(win_total, k, P.norm);
+            topo = topo_known >= 0 ? topo_known : nvlink_score(win_total, k, P.norm);
             nsel = k;
         }
     } else if (pod.topology_pref == KGWE_TOPO_SAME_NUMA || pod.topology_pref == KGWE_TOPO_SAME_PCIE_SWITCH) {

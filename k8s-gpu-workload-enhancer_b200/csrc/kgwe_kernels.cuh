@@ -216,7 +216,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         warp_uniform = !MEMO && __all_sync(0xffffffffu, ucode != 0 || !c.valid);
         if (c.integral) node_fast_build(nf, rec, c, j);
         else nf->init[j] = FAST_NEG;
-        if (!MEMO && ucode && j == 0) uniform_totals_build(nf, node_uniform_bw(rec, ucode));
+        if (!MEMO && ucode && j == 0) uniform_topo_build(nf, node_uniform_bw(rec, ucode), P.norm);
         if (j == 0) ctxs[grp] = c;
         if (TABLES) {
             // E1 subset keys of this node: lane j fills slots j, j+8, ...
@@ -335,7 +335,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
             }
             // ---- phase B: lane j finishes pod p0 + j ----
             bool found = mykey > 0; double win_total = (double)(mykey >> 3);
-            if (warp_uniform && found) win_total = *uniform_total_slot(nf, k);      // (found implies 2 <= k <= 8)
+            const int topo_known = (warp_uniform && found && !(TABLES && exhaustive)) ? *uniform_topo_slot(nf, k) : -1;      // (found implies 2 <= k <= 8)
             uint32_t ord = mypay, sel = found ? mask_of_order(mypay, k) : 0u, ncand = (uint32_t)nc.A;
             if (TABLES && exhaustive) {
                 win_total = (double)(mykey >> 8);
@@ -343,7 +343,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
                 ncand = 1; for (int i = 1; i <= k; ++i) ncand = ncand * (uint32_t)(nc.A - k + i) / (uint32_t)i;
             }
             eval_finish(rec, nc, pod, P, live && hint_bit(hint, hint_row_bytes, p, node), eligible, k,
-                        found, win_total, sel, ord, ncand, o);
+                        found, win_total, sel, ord, ncand, o, topo_known);
             if (live && node_ok) {
                 cand += o.candidates;
                 if (out) {
