@@ -3,9 +3,12 @@
 //  score_kernel      K1  stateless Filter+Prioritize: grid = node tiles x pod chunks.  A CTA
 //                        stages one tile of 64 node records (48 KB) into shared memory with a
 //                        single TMA bulk copy (cp.async.bulk + mbarrier), derives the
-//                        pod-independent NodeCtx of its nodes once, then streams its pod chunk:
-//                        8 lanes per (pod,node), 16-byte score records out, per-pod arg-max
-//                        through a shared-memory key table flushed with one atomicMax per pod.
+//                        pod-independent NodeCtx of its nodes once, then works through its pod chunk
+//                        in (8 pods x 4 nodes) items taken from a shared counter: three numeric
+//                        tiers for the NVLink group search (bit-set walks on uniform nodes, int32
+//                        chains on whole-number bandwidths, FP64 otherwise), 16-byte score records
+//                        out, per-pod arg-max through a shared-memory key table flushed with one
+//                        atomicMax per pod.
 //  finalize_top1     K1b turns the arg-max keys into placements (+ EstimatedBandwidth).
 //  topk_select       K2  ranked top-k per pod from the score matrix (canonical order).
 //  topk_merge        K2b merges per-shard ranked lists (multi-GPU, after the all-gather).
@@ -113,8 +116,10 @@ __device__ __forceinline__ void finalize_one(const DevNode* __restrict__ nodes, 
 //
 // Pod loop, "octet" form: the 8 lanes of a group take 8 consecutive pods at a time.
 //   phase 0  lane i loads pod i and runs the Filter for (pod i, this node);
-//   phase A  for each of the 8 pods that needs an NVLink group on this node, the 8 lanes run
-//            the 8 greedy chains (lane = start GPU) and reduce to the winner; lane i keeps pod i's;
+//   phase A  on uniform nodes lane i first tries the bit-set walk from the lowest available GPU for pod i
+//            (first_uniform_walk), which settles almost every evaluation; for each pod still open - all of
+//            them on other nodes - the 8 lanes run the 8 greedy chains (lane = start GPU) and reduce to
+//            the winner; lane i keeps pod i's;
 //   phase B  lane i finishes pod i (topology score, resource, total, flags), stores its 16-byte
 //            NodeScore and joins the per-pod arg-max.
 // So the group search is 8-wide per evaluation while the scalar part of an evaluation is done by
