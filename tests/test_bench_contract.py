@@ -28,3 +28,29 @@ def test_kgwe_arm_refuses_to_run_without_a_gpu():
         return
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1"], capture_output=True, text=True, timeout=300)
     assert r.returncode != 0 and "no CPU fallback" in (r.stderr + r.stdout)
+
+
+def test_uniform_node_count_of_the_bench_line(kg):
+    """bench.py's `link_tiers.headline_cluster.uniform_nodes` (how many records take K1's bit-set walk) on hand-made
+    cases: the synthetic cluster is all uniform (also with links down and ragged nodes), a per-link jitter ends that,
+    a per-node factor does not, a zero-bandwidth active link does."""
+    import importlib.util
+    import numpy as np
+    spec = importlib.util.spec_from_file_location("kgwe_bench", os.path.join(ROOT, "bench.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    synth = kg.synth
+    nodes = synth.make_cluster(200, "mixed", seed=3, inactive_link_frac=0.1, partial_node_frac=0.3)
+    assert b.uniform_nodes(nodes) == 200
+    rng = synth.SplitMix64(1)
+    per_link = nodes.copy()
+    per_link["nvl_bw"] = nodes["nvl_bw"] * (0.5 + rng.uniform(200 * 64).reshape(200, 8, 8))
+    has_two_links = (nodes["nvl_active"] != 0).sum(axis=1) >= 2
+    assert b.uniform_nodes(per_link) == int((~has_two_links).sum())          # nodes with no active link at all stay "uniform"
+    per_node = nodes.copy()
+    per_node["nvl_bw"] = nodes["nvl_bw"] * (0.5 + rng.uniform(200))[:, None, None]
+    assert b.uniform_nodes(per_node) == 200
+    zero = nodes.copy()
+    zero["nvl_bw"][7, 0, 1] = 0.0                                            # GPU 0's (active) link to GPU 1 carries nothing
+    assert (nodes["nvl_active"][7, 0] >> 1) & 1 and nodes["n_gpus"][7] >= 2
+    assert b.uniform_nodes(zero) == 199
