@@ -287,13 +287,15 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         const bool wants_group = k >= 2 && is_nvlink_pref(pod);
         const bool exhaustive = wants_group && (pod.flags & KGWE_POD_EXHAUSTIVE);
         const bool any_exh = __any_sync(0xffffffffu, live && exhaustive);
-        const bool octet = (warp_fast && (TABLES || !any_exh)) || (warp_uniform && !any_exh);
+        // general (fractional, irregular) bandwidths take the same octet loop with FP64 chains and 64-bit keys
+        const bool fp64_chains = !warp_fast && !warp_uniform;
+        const bool octet = (warp_fast && (TABLES || !any_exh)) || !any_exh;
         EvalOut o;
         if (octet) {
             // ---- phase A: the group searches, one pod slot at a time ----
-            int32_t mykey = 0; uint32_t mypay = 0;
+            int32_t mykey = 0; uint32_t mypay = 0, mylow = 0;     // (FP64 chains: mykey:mylow = the bits of the winning total)
             int chain_k = (eligible && wants_group) ? (k | (exhaustive ? 16 : 0)) : 0;
-            if (MEMO && chain_k && !exhaustive) {        // look the greedy winner up instead of searching
+            if (MEMO && warp_fast && chain_k && !exhaustive) {        // look the greedy winner up instead of searching
                 const int2 w = memo[grp * 8 + (k - 1)];
                 mykey = w.x; mypay = (uint32_t)w.y; chain_k = 0;
             }
@@ -311,7 +313,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
                 const int t = __ffs((int)pend) - 1;
                 const int ct = __shfl_sync(0xffffffffu, chain_k, t, 8);
                 const int kt = ct & 15;
-                int32_t key = 0; uint32_t pay = 0;
+                int32_t key = 0; uint32_t pay = 0, word_lo = 0;
                 if (TABLES && __any_sync(0xffffffffu, ct & 16)) {      // some group has an exhaustive pod in this slot
                     if (ct & 16) {
                         const uint32_t* tab = subset + grp * 256;
@@ -327,6 +329,20 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
                         }
                         fast_group_winner(key, pay, gmask);
                     }
+                } else if (fp64_chains) {
+                    // scoreNVLinkTopology in float64 (greedy_chain); winner = strictly largest total, then lowest start
+                    bool ok = false; double total = 0.0; uint32_t mem = 0;
+                    if (kt && start_ok) greedy_chain(rec, nc, j, kt, ok, total, pay, mem);
+                    unsigned long long k64 = (ok && total > 0.0) ? (unsigned long long)__double_as_longlong(total) : 0ull;
+                    uint32_t tie = (uint32_t)j;
+#pragma unroll
+                    for (int off = 4; off >= 1; off >>= 1) {
+                        const unsigned long long okey = __shfl_xor_sync(0xffffffffu, k64, off, 8);
+                        const uint32_t otie = __shfl_xor_sync(0xffffffffu, tie, off, 8);
+                        const uint32_t opay = __shfl_xor_sync(0xffffffffu, pay, off, 8);
+                        if (okey > k64 || (okey == k64 && otie < tie)) { k64 = okey; tie = otie; pay = opay; }
+                    }
+                    key = (int32_t)(k64 >> 32); word_lo = (uint32_t)k64;        // (a positive double: the high word is > 0)
                 } else {
                     if (kt && start_ok) {
                         if (warp_uniform) greedy_walk_uniform(nc.avail, nc.colact, j, kt, key, pay);
@@ -336,10 +352,11 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
                     // warp spares the per-lane mask handling the compiler adds around shuffles with a lane-dependent mask
                     fast_group_winner(key, pay, 0xffffffffu);
                 }
-                if (j == t && ct) { mykey = key; mypay = pay; }      // (groups whose pod of this slot is already settled keep their result)
+                if (j == t && ct) { mykey = key; mypay = pay; mylow = word_lo; }      // (groups whose pod of this slot is already settled keep their result)
             }
             // ---- phase B: lane j finishes pod p0 + j ----
             bool found = mykey > 0; double win_total = (double)(mykey >> 3);
+            if (fp64_chains) { found = (mykey | (int32_t)mylow) != 0; win_total = __longlong_as_double((long long)(((unsigned long long)(uint32_t)mykey << 32) | mylow)); }
             const int topo_known = (warp_uniform && found && !(TABLES && exhaustive)) ? *uniform_topo_slot(nf, k) : -1;      // (found implies 2 <= k <= 8)
             uint32_t ord = mypay, sel = found ? mask_of_order(mypay, k) : 0u, ncand = (uint32_t)nc.A;
             if (TABLES && exhaustive) {

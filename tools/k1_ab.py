@@ -9,6 +9,9 @@ st = torch.cuda.Stream(); torch.cuda.set_stream(st)
 nodes, pods, led = kg.synth.config(3)
 N, P = len(nodes), len(pods)
 flags = int(sys.argv[1]) if len(sys.argv) > 1 else 0
+if len(sys.argv) > 2 and sys.argv[2] == "fp64":       # irregular fractional bandwidths: the FP64 tier
+    r = kg.synth.SplitMix64(77)
+    nodes["nvl_bw"] = nodes["nvl_bw"] * (0.5 + r.uniform(nodes["nvl_bw"].size).reshape(nodes["nvl_bw"].shape))
 eng = kg.Engine(max_nodes=N, flags=flags); eng.upsert_nodes(nodes); eng.seed_ledger(led)
 d_pods = torch.from_numpy(pods.view(np.uint8).reshape(P, 32)).to(dev)
 d_top = torch.empty((P, 32), dtype=torch.uint8, device=dev)
