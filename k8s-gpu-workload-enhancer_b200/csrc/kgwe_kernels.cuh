@@ -125,9 +125,10 @@ __device__ __forceinline__ void finalize_one(const DevNode* __restrict__ nodes, 
 // So the group search is 8-wide per evaluation while the scalar part of an evaluation is done by
 // one lane instead of redundantly by eight.  Stores of one warp instruction: for each i, the 4
 // groups' lanes i write 4 consecutive nodes of pod i = 64 contiguous bytes.
-// Warps with a node whose bandwidths are not whole numbers take the one-pod-per-pass generic path
-// instead, and so do octets containing an exhaustive-mode pod unless the kernel was launched with
-// subset tables (TABLES): then each node also gets, once per tile, the score key of every one of
+// The group search of a quad runs in the cheapest tier its four nodes allow: bit-set walks (all uniform), int32 chains
+// (all whole-number), else FP64 chains with 64-bit winner keys.  Octets containing an exhaustive-mode pod take the
+// one-pod-per-pass generic path instead, unless the kernel was launched with subset tables (TABLES) and the quad's
+// bandwidths are whole numbers: then each node also gets, once per tile, the score key of every one of
 // its 256 GPU subsets (E1: total << 8 | 255 - mask, 0 when the subset is not an available active
 // clique), laid out by popcount, and an exhaustive evaluation is the max over the C(8,k) keys of
 // its k - 8 lanes x <= 9 entries - with the same lowest-mask tie-break.
