@@ -1,6 +1,6 @@
 """Differential fuzzing: random clusters / pod queues with every feature switched on at random, engine vs
 oracle (indexed build), stateless matrix + top-k and the stateful queue, over many seeds.
-  python tools/fuzz_parity.py [n_seeds] [first_seed]"""
+  python tests/fuzz_parity.py [n_seeds] [first_seed]"""
 import os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

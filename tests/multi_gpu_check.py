@@ -69,9 +69,9 @@ def main():
     nodes, pods, led = synth.config(3, 0.1)
     N, P, topk = len(nodes), 500, 4
     ok = check_case(nodes, pods[:500], led, topk, "config 3 x 0.1")
-    # a few cases from the differential fuzzer's input space (tools/fuzz_parity.py), sharded
+    # a few cases from the differential fuzzer's input space (tests/fuzz_parity.py), sharded
     import importlib.util
-    spec = importlib.util.spec_from_file_location("fuzz_parity", os.path.join(ROOT, "tools", "fuzz_parity.py"))
+    spec = importlib.util.spec_from_file_location("fuzz_parity", os.path.join(ROOT, "tests", "fuzz_parity.py"))
     fz = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(fz)
     for seed in (11, 12, 13, 14):

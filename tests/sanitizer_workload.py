@@ -1,6 +1,6 @@
 """Small end-to-end workload for compute-sanitizer runs (memcheck / racecheck): every kernel of the
 engine on config 1 (16 nodes) plus a 300-node mixed cluster, checked against the oracle.
-  compute-sanitizer --tool memcheck python tools/sanitizer_workload.py"""
+  compute-sanitizer --tool memcheck python tests/sanitizer_workload.py"""
 import os
 import sys
 

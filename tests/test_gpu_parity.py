@@ -650,11 +650,11 @@ def test_snapshot_and_restore(kg, orc):
 
 
 def test_differential_fuzz_few_seeds(kg, orc):
-    """tools/fuzz_parity.py for a handful of seeds: every feature at random (ragged nodes, inactive / zero /
+    """tests/fuzz_parity.py for a handful of seeds: every feature at random (ragged nodes, inactive / zero /
     fractional / irregular links, MIG, hints, architectures, min-bandwidth, all preferences, counts 0..9,
     exhaustive flags, both kernel-variant flags), engine vs oracle, stateless + latency path + queue."""
     import importlib.util
-    spec = importlib.util.spec_from_file_location("fuzz_parity", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "fuzz_parity.py"))
+    spec = importlib.util.spec_from_file_location("fuzz_parity", os.path.join(os.path.dirname(os.path.abspath(__file__)), "fuzz_parity.py"))
     fz = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(fz)
     for seed in (101, 102, 103, 104, 105, 106):

@@ -143,12 +143,12 @@ def test_contributing_md_snippet_expectation(kg, orc):
 
 
 def test_faithful_equals_indexed_fuzz(kg, orc):
-    """The two oracle builds over the differential fuzzer's input space (tools/fuzz_parity.py: ragged nodes,
+    """The two oracle builds over the differential fuzzer's input space (tests/fuzz_parity.py: ragged nodes,
     inactive / zero / fractional / irregular links, MIG, hints, architectures, minimum bandwidth, every
     preference, counts 0..9, exhaustive flags) at sizes the faithful build finishes in a moment:
     stateless matrix + top-k, the stateful queue with its final ledger, and gang scheduling."""
     import importlib.util
-    spec = importlib.util.spec_from_file_location("fuzz_parity", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "fuzz_parity.py"))
+    spec = importlib.util.spec_from_file_location("fuzz_parity", os.path.join(os.path.dirname(os.path.abspath(__file__)), "fuzz_parity.py"))
     fz = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(fz)
     abi = kg.abi
