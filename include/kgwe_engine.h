@@ -99,6 +99,14 @@ typedef struct kgwe_config {
  * (pod,node) evaluation looks it up.  Results are identical; throughput figures obtained with it
  * are reported separately from the brute-force rate (the group search is shared between pods). */
 #define KGWE_CFG_MEMOISE_GROUPS 0x2u
+/* By default every available start GPU of a node grows its own group for every (pod,node) evaluation, as
+ * findBestNVLinkGroup does (scheduler.go:389): A candidate groups scored per evaluation.  On a node whose
+ * active links all carry the same bandwidth every group that reaches the requested size has the same total and
+ * the reference keeps the first such start, so the walk from the lowest available start already is the
+ * answer whenever it completes.  With this flag the scoring kernel stops there (and searches all starts only
+ * when that walk dies).  Results are identical; kgwe_stats.candidates then counts the one group actually
+ * grown, kgwe_stats.candidates_resolved still counts A. */
+#define KGWE_CFG_PRUNE_TIED_STARTS 0x4u
 
 /* One node of the topology snapshot: exactly the fields of NodeTopology / GPUDevice the
  * scorer reads (src/discovery/types.go:11-47,116-164,336-366).
@@ -181,7 +189,9 @@ typedef struct kgwe_placement {
 
 typedef struct kgwe_stats {
     uint64_t evaluations;        /* (pod,node) pairs scored since create */
-    uint64_t candidates;         /* GPU subsets scored (counting rule: SURVEY.md 8d) */
+    uint64_t candidates;         /* GPU subsets whose score was actually computed (groups grown, subsets summed; 1 for an
+                                  * evaluation without a group search).  Equals candidates_resolved unless a KGWE_CFG_* flag
+                                  * lets evaluations share or skip parts of the search. */
     uint64_t scheduled;          /* SchedulerMetrics.TotalScheduled */
     uint64_t failed;             /* SchedulerMetrics.TotalFailed */
     uint64_t topology_optimal;   /* TopologyOptimalPlacements (TopologyScore >= 80, scheduler.go:154) */
@@ -193,6 +203,8 @@ typedef struct kgwe_stats {
     uint32_t n_allocations;      /* ledger size */
     double   score_kernel_ms;    /* summed device time of the scoring kernel (K1) launches timed so far (CUDA events on the launching stream) */
     uint64_t score_kernel_timed; /* how many K1 launches that sum covers */
+    uint64_t candidates_resolved;/* candidates by the reference's counting rule: A per NVLink-greedy evaluation with
+                                  * k >= 2 on an eligible node, C(A,k) in exhaustive mode, 1 otherwise - whatever the engine did */
 } kgwe_stats;
 
 typedef struct kgwe_engine kgwe_engine;

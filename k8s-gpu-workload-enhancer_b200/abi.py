@@ -22,6 +22,7 @@ MIG_NAMES = ["1g.5gb", "1g.10gb", "2g.10gb", "2g.20gb", "3g.20gb", "3g.40gb", "4
 POD_EXHAUSTIVE = 0x01
 CFG_SUBSET_TABLES = 0x1
 CFG_MEMOISE_GROUPS = 0x2
+CFG_PRUNE_TIED_STARTS = 0x4
 F_ELIGIBLE, F_KEPT, F_HINT, F_FALLBACK, F_MINBW, F_GANG_ROLLBACK = 0x01, 0x02, 0x04, 0x08, 0x10, 0x20
 MIG_GPU = np.dtype([("occ", "u1"), ("cls", "u1"), ("enabled", "u1"), ("pad", "u1")])
 MIG_ASSIGNMENT = np.dtype([("gpu_idx", "<u4"), ("start", "u1"), ("size", "u1"), ("cost", "u1"), ("profile", "u1")])
@@ -70,7 +71,7 @@ class Stats(C.Structure):
                 ("failed", C.c_uint64), ("topology_optimal", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("last_call_gpu_ms", C.c_double),
                 ("n_nodes", C.c_uint32), ("n_allocations", C.c_uint32),
-                ("score_kernel_ms", C.c_double), ("score_kernel_timed", C.c_uint64)]
+                ("score_kernel_ms", C.c_double), ("score_kernel_timed", C.c_uint64), ("candidates_resolved", C.c_uint64)]
 
 
 def default_config(max_nodes, device=0, node_base=0):

@@ -538,6 +538,7 @@ __device__ __forceinline__ void eval_finish(const DevNode* rec, const NodeCtx& n
     o.mask = sel; o.order = order | ((uint32_t)nsel << 24); o.flags = flags;
 }
 
+#ifdef __CUDACC__      // warp-collective code (8 lanes per evaluation): K1b, K3
 // Winner of the 8 integer chains of a group: key = (total << 3) | (7 - start).  `gmask` names the
 // 8 lanes of the group (or the whole warp when all four groups are known to be here together).
 __device__ __forceinline__ void fast_group_winner(int32_t& key, uint32_t& pay, uint32_t gmask) {
@@ -603,6 +604,8 @@ __device__ __forceinline__ void evaluate(const DevNode* rec, const NodeCtx& nc, 
     }
     eval_finish(rec, nc, pod, P, hinted, eligible, k, found, win_total, sel, order, candidates, o);
 }
+
+#endif  // __CUDACC__
 
 __device__ __forceinline__ kgwe_node_score to_record(const EvalOut& o) {
     kgwe_node_score r;

@@ -23,6 +23,7 @@
 
 #include "kgwe_kernels.cuh"
 #include "kgwe_mig.cuh"
+#include "kgwe_pack.hpp"
 
 using namespace kgwe;
 
@@ -58,6 +59,7 @@ struct PinBuf {
     void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
 };
 
+constexpr int kCounters = 4;      // device counters: [0] evaluations (K3), [1] candidates scored, [2] candidates by the reference's counting rule
 constexpr size_t kScoreScratchBytes = 1ull << 30;   // internal score-matrix chunk (top-k > 1 without out_scores, host copies)
 // Testing knob: KGWE_SCORE_SCRATCH_BYTES shrinks the chunk so the multi-pass path of kgwe_score_batch can be exercised on small inputs.
 size_t score_scratch_bytes() {
@@ -76,6 +78,7 @@ struct kgwe_engine {
     int sm_count = 148;
     int sched_blocks_per_sm = 1;
     int sched_tile_blocks_per_sm = 0;
+    int k1_blocks_per_sm[3] = {4, 2, 1};   // co-resident CTAs of K1's lean / GENERAL / TABLES variants
 
     DevNode* d_nodes = nullptr;       // cluster image in HBM
     DevNode* h_nodes = nullptr;       // pinned mirror (device layout)
@@ -83,6 +86,7 @@ struct kgwe_engine {
     std::vector<uint32_t> dirty;
     uint32_t n_nodes = 0;             // high-water mark of present records
     uint32_t n_present = 0;
+    uint32_t n_nonuniform = 0;        // present records whose active links are not all equal (K1 then needs its GENERAL variant)
     std::unordered_map<uint64_t, LedgerEntry> ledger;
 
     DevBuf<kgwe_pod_req> d_pods;
@@ -91,7 +95,7 @@ struct kgwe_engine {
     DevBuf<unsigned int> d_arrive;          // per-pod arrival counters of the queue kernel, kept all-zero between calls
     DevBuf<kgwe_placement> d_topk;
     DevBuf<kgwe_node_score> d_scores;
-    unsigned long long* d_counters = nullptr;   // [0] evaluations (K3), [1] candidates
+    unsigned long long* d_counters = nullptr;   // kCounters words, see above
     PinBuf<kgwe_pod_req> h_pods;
     PinBuf<kgwe_placement> h_topk;
     PinBuf<uint8_t> h_hint;
@@ -119,75 +123,13 @@ int fail(kgwe_engine* e, int code, const char* fmt, ...) {
 }
 #define CU(e, call) do { cudaError_t _c = (call); if (_c != cudaSuccess) return fail(e, KGWE_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(_c)); } while (0)
 
-// Uniform-link code of a record (greedy_walk_uniform_k, kgwe_device.cuh): set when all its ACTIVE links carry the same
-// bandwidth u > 0 (whole-number or not).  pad1[0] = 0x80 | m << 3 | c names one such link (c's link to m) so the kernels
-// can fetch u; 0x40 = the record has no active link at all (every walk dies at once); 0 = not uniform.
-// Derived from the record itself, never taken from outside.
-void set_uniform_unit(DevNode& rec) {
-    rec.pad1[0] = rec.pad1[1] = rec.pad1[2] = 0;
-    bool any = false; double u = 0.0; int loc = 0;
-    for (int m = 0; m < KGWE_MAX_GPUS; ++m)
-        for (int c = 0; c < KGWE_MAX_GPUS; ++c) {
-            if (c == m || !(rec.act_in[m] >> c & 1)) continue;
-            const double b = rec.bw_in[m][bw_slot(m, c)];
-            if (!(b > 0.0) || (any && b != u)) return;
-            if (!any) { any = true; u = b; loc = (m << 3) | c; }
-        }
-    rec.pad1[0] = any ? (uint8_t)(0x80 | loc) : (uint8_t)0x40;
-}
-
-// ABI record -> device record: transpose + chunk-swizzle the NVLink matrix (kgwe_device.cuh),
-// transpose the active masks, normalise masks to n_gpus.
 int to_device_record(kgwe_engine* e, const kgwe_node_image& in, DevNode& out) {
-    if (in.n_gpus > KGWE_MAX_GPUS) return fail(e, KGWE_ERR_INVALID_ARG, "n_gpus %u > %d", in.n_gpus, KGWE_MAX_GPUS);
-    const int ng = in.n_gpus;
-    const uint8_t gm = (uint8_t)((1u << ng) - 1u);
-    memset(&out, 0, sizeof out);
-    bool integral = true;
-    for (int i = 0; i < ng; ++i) {
-        const uint8_t present = in.nvl_present[i] & gm & (uint8_t)~(1u << i);
-        const uint8_t active = in.nvl_active[i] & present;
-        out.present[i] = present;
-        for (int j = 0; j < ng; ++j) {
-            double bw = (present >> j & 1) ? in.nvl_bw[i][j] : 0.0;
-            if (!(bw >= 0.0) || !(bw <= KGWE_MAX_BW_GBPS)) return fail(e, KGWE_ERR_INVALID_ARG, "nvl_bw[%d][%d]=%g outside [0,%g]", i, j, bw, KGWE_MAX_BW_GBPS);
-            if (bw == 0.0) bw = 0.0;                              // -0.0 -> +0.0
-            if (bw != std::floor(bw)) integral = false;
-            out.bw_in[j][bw_slot(j, i)] = bw;                     // i's link to j
-            if (active >> j & 1) out.act_in[j] |= (uint8_t)(1u << i);
-        }
-        const double pb = in.pcie_bw[i], ut = in.util[i];
-        if (!(pb >= 0.0) || !(pb <= KGWE_MAX_BW_GBPS)) return fail(e, KGWE_ERR_INVALID_ARG, "pcie_bw[%d]=%g outside [0,%g]", i, pb, KGWE_MAX_BW_GBPS);
-        if (!std::isfinite(ut)) return fail(e, KGWE_ERR_INVALID_ARG, "util[%d] is not finite", i);
-        out.pcie_bw[i] = pb; out.util[i] = ut; out.free_bytes[i] = in.free_bytes[i];
-        out.numa[i] = in.numa[i]; out.pcie_switch[i] = in.pcie_switch[i]; out.arch[i] = in.arch[i];
-    }
-    memcpy(out.mig_free, in.mig_free, sizeof out.mig_free);
-    out.n_gpus = (uint8_t)ng; out.healthy_mask = in.healthy_mask & gm;
-    out.mig_enabled_mask = in.mig_enabled_mask & gm; out.mig_has_free_mask = in.mig_has_free_mask & in.mig_enabled_mask & gm;
-    out.node_flags = in.node_flags;
-    out.flags = NODE_PRESENT | (integral ? NODE_INTEGRAL : 0);
-    set_uniform_unit(out);
+    char msg[160];
+    if (kgwe::to_device_record(in, out, msg, sizeof msg) != 0) return fail(e, KGWE_ERR_INVALID_ARG, "%s", msg);
     return KGWE_OK;
 }
 
-void to_abi_record(const DevNode& in, kgwe_node_image& out) {
-    memset(&out, 0, sizeof out);
-    const int ng = in.n_gpus;
-    for (int i = 0; i < ng; ++i) {
-        out.nvl_present[i] = in.present[i];
-        for (int j = 0; j < ng; ++j) {
-            out.nvl_bw[i][j] = in.bw_in[j][bw_slot(j, i)];
-            if (in.act_in[j] >> i & 1) out.nvl_active[i] |= (uint8_t)(1u << j);
-        }
-        out.pcie_bw[i] = in.pcie_bw[i]; out.util[i] = in.util[i]; out.free_bytes[i] = in.free_bytes[i];
-        out.numa[i] = in.numa[i]; out.pcie_switch[i] = in.pcie_switch[i]; out.arch[i] = in.arch[i];
-    }
-    memcpy(out.mig_free, in.mig_free, sizeof out.mig_free);
-    out.n_gpus = in.n_gpus; out.healthy_mask = in.healthy_mask; out.allocated_mask = in.allocated_mask;
-    out.flags = in.flags & NODE_PRESENT; out.n_allocs = in.n_allocs;
-    out.mig_enabled_mask = in.mig_enabled_mask; out.mig_has_free_mask = in.mig_has_free_mask; out.node_flags = in.node_flags;
-}
+inline uint32_t rec_nonuniform(const DevNode& r) { return ((r.flags & NODE_PRESENT) && r.pad1[0] == 0) ? 1u : 0u; }
 
 void mark_dirty(kgwe_engine* e, uint32_t idx) {
     if (!e->dirty_flag[idx]) { e->dirty_flag[idx] = 1; e->dirty.push_back(idx); }
@@ -225,25 +167,67 @@ int validate_pods(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n) {
 uint32_t hint_row_bytes(const kgwe_engine* e) { return (e->n_nodes + 7) / 8; }
 size_t sched_tile_smem_bytes() { return (size_t)TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx) + 64) + 16; }
 
-size_t score_smem_bytes(uint32_t pods_per_chunk, bool tables = false, bool memo = false) {
-    return (size_t)TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx)) + (tables ? SUBSET_SMEM_BYTES : 0) + (memo ? MEMO_SMEM_BYTES : 0) +
-           (size_t)pods_per_chunk * 8 + 16;
+// ---- K1 launch ------------------------------------------------------------------------------------
+// Kernel variant: the lean one when every present record is uniform (all active links of a node equal - any
+// NVSwitch node, any single-generation mesh), GENERAL as soon as one record is not (matrix columns in shared
+// memory), TABLES when exhaustive-mode pods may be in the batch (subset-key columns; implies GENERAL).
+struct K1Plan { bool general, tables; uint32_t mode, chunks, ppc, n_tiles; size_t smem; };
+
+uint32_t k1_mode(const kgwe_engine* e) {
+    return (e->cfg.flags & KGWE_CFG_MEMOISE_GROUPS) ? K1_MODE_MEMO : (e->cfg.flags & KGWE_CFG_PRUNE_TIED_STARTS) ? K1_MODE_PRUNE : K1_MODE_FULL;
 }
 
-// Pod chunks of a K1 launch: whole waves of co-resident CTAs (2 per SM; 1 with subset tables), as few waves
-// as keep the per-CTA arg-max table within bounds - every CTA pays the tile set-up once, so fewer, longer
-// CTAs amortise it better, and whole waves avoid a ragged tail (all CTAs do the same amount of work).
-void plan_pod_chunks(const kgwe_engine* e, uint32_t n_pods, uint32_t n_tiles, bool tables, uint32_t* chunks_out, uint32_t* ppc_out) {
-    const uint32_t slots = (uint32_t)e->sm_count * (tables ? 1u : 2u);
+// Pod chunks: whole waves of co-resident CTAs, as few waves as keep the per-CTA pod tables within bounds - every CTA
+// pays its set-up (node state, pod decode) once, so fewer, longer CTAs amortise it better, and whole waves avoid a
+// ragged tail (all CTAs do the same amount of work).
+K1Plan plan_k1(const kgwe_engine* e, uint32_t n_pods, bool tables) {
+    K1Plan pl;
+    pl.tables = tables || (e->cfg.flags & KGWE_CFG_SUBSET_TABLES);
+    pl.general = pl.tables || e->n_nonuniform > 0;
+    pl.mode = k1_mode(e);
+    pl.n_tiles = (e->n_nodes + K1_TILE - 1) / K1_TILE;
+    const uint32_t max_ppc = pl.tables ? 512u : (uint32_t)MAX_PODS_PER_CHUNK;      // the subset columns leave room for 512 pod records
+    const uint32_t slots = (uint32_t)e->sm_count * (uint32_t)e->k1_blocks_per_sm[pl.tables ? 2 : pl.general ? 1 : 0];
     uint32_t chunks = 1, ppc = n_pods;
-    for (uint32_t waves = 1; waves <= 64; ++waves) {
-        chunks = std::max(1u, std::min(n_pods, slots * waves / n_tiles));
+    for (uint32_t waves = 1; waves <= 256; ++waves) {
+        chunks = std::max(1u, std::min(n_pods, slots * waves / pl.n_tiles));
         ppc = (n_pods + chunks - 1) / chunks;
-        if (ppc <= MAX_PODS_PER_CHUNK && (waves >= 2 || n_pods <= 64)) break;
+        if (ppc <= max_ppc && (waves >= 2 || n_pods <= 64)) break;
     }
-    if (ppc > MAX_PODS_PER_CHUNK) ppc = MAX_PODS_PER_CHUNK;
-    *ppc_out = ppc;
-    *chunks_out = (n_pods + ppc - 1) / ppc;
+    if (ppc > max_ppc) ppc = max_ppc;
+    pl.ppc = ppc;
+    pl.chunks = (n_pods + ppc - 1) / ppc;
+    pl.smem = k1_layout(ppc, pl.general, pl.tables, pl.mode == K1_MODE_MEMO).total;
+    return pl;
+}
+
+// Launch K1 alone: scores into d_scores (nullable), arg-max keys into `best` (nullable).
+int launch_k1(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const uint8_t* d_hint, kgwe_node_score* d_scores,
+              unsigned long long* best, cudaStream_t s, bool tables, const FusedTail& tail, bool timed) {
+    const K1Plan pl = plan_k1(e, n_pods, tables);
+    if (pl.chunks > 65535u) return fail(e, KGWE_ERR_TOO_LARGE, "too many pods in one launch (%u)", n_pods);
+    const dim3 grid(pl.n_tiles, pl.chunks);
+    timed = timed && e->timers_pending < kgwe_engine::kTimers;
+    if (timed) CU(e, cudaEventRecord(e->t0[e->timers_pending], s));
+#define KGWE_LAUNCH_SCORE(G, T) score_kernel<G, T><<<grid, K1_THREADS, pl.smem, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, pl.ppc, d_hint, hint_row_bytes(e), \
+                                                                                    d_scores, best, e->params, e->d_counters, pl.mode, tail)
+    if (pl.tables) KGWE_LAUNCH_SCORE(true, true);
+    else if (pl.general) KGWE_LAUNCH_SCORE(true, false);
+    else KGWE_LAUNCH_SCORE(false, false);
+#undef KGWE_LAUNCH_SCORE
+    CU(e, cudaGetLastError());
+    if (timed) { CU(e, cudaEventRecord(e->t1[e->timers_pending], s)); e->timers_pending++; }
+    e->stats.kernel_launches++;
+    e->stats.evaluations += (uint64_t)n_pods * e->n_present;
+    return KGWE_OK;
+}
+
+// Arg-max key table of the engine for n_pods pods (grown on demand, kept all-zero between calls).
+int ensure_best(kgwe_engine* e, uint32_t n_pods, cudaStream_t s) {
+    const size_t had = e->d_best.cap;
+    CU(e, e->d_best.ensure(n_pods));
+    if (e->d_best.cap != had) CU(e, cudaMemsetAsync(e->d_best.p, 0, e->d_best.cap * sizeof(unsigned long long), s));
+    return KGWE_OK;
 }
 
 // Launch K1 (+K1b / K2) for n_pods pods whose descriptors, hint rows and outputs are in
@@ -267,32 +251,15 @@ int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, co
         }
         return KGWE_OK;
     }
-    const uint32_t n_tiles = (e->n_nodes + TILE_NODES - 1) / TILE_NODES;
-    tables = tables || (e->cfg.flags & KGWE_CFG_SUBSET_TABLES);
-    uint32_t chunks, ppc;
-    plan_pod_chunks(e, n_pods, n_tiles, tables, &chunks, &ppc);
-    if (chunks > 65535u) return fail(e, KGWE_ERR_TOO_LARGE, "too many pods in one launch (%u)", n_pods);
     unsigned long long* best = nullptr;
     if (topk == 1) {
-        const size_t had = e->d_best.cap;
-        CU(e, e->d_best.ensure(n_pods));
-        if (e->d_best.cap != had) CU(e, cudaMemsetAsync(e->d_best.p, 0, e->d_best.cap * sizeof(unsigned long long), s));
+        int rc = ensure_best(e, n_pods, s);
+        if (rc != KGWE_OK) return rc;
         best = e->d_best.p;
     }
-    dim3 grid(n_tiles, chunks);
-    const bool timed = !fused_tail && e->timers_pending < kgwe_engine::kTimers;
-    if (timed) CU(e, cudaEventRecord(e->t0[e->timers_pending], s));
-    const bool memo = e->cfg.flags & KGWE_CFG_MEMOISE_GROUPS;
-    const size_t smem = score_smem_bytes(ppc, tables, memo);
-#define KGWE_LAUNCH_SCORE(T, M) score_kernel<T, M><<<grid, SCORE_THREADS, smem, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e), \
-                                                                                     d_scores, best, e->params, e->d_counters, tail)
-    if (tables) { if (memo) KGWE_LAUNCH_SCORE(true, true); else KGWE_LAUNCH_SCORE(true, false); }
-    else        { if (memo) KGWE_LAUNCH_SCORE(false, true); else KGWE_LAUNCH_SCORE(false, false); }
-#undef KGWE_LAUNCH_SCORE
-    CU(e, cudaGetLastError());
-    if (timed) { CU(e, cudaEventRecord(e->t1[e->timers_pending], s)); e->timers_pending++; }
-    e->stats.kernel_launches++;
-    if (fused_tail) { e->stats.evaluations += (uint64_t)n_pods * e->n_present; return KGWE_OK; }
+    int rc = launch_k1(e, d_pods, n_pods, d_hint, d_scores, best, s, tables, tail, !fused_tail);
+    if (rc != KGWE_OK) return rc;
+    if (fused_tail) return KGWE_OK;
     if (topk == 1) {
         const uint32_t threads = 256, pods_per_block = threads / 8;
         finalize_top1_kernel<<<(n_pods + pods_per_block - 1) / pods_per_block, threads, 0, s>>>(
@@ -304,13 +271,12 @@ int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, co
         CU(e, cudaGetLastError());
         e->stats.kernel_launches++;
     }
-    e->stats.evaluations += (uint64_t)n_pods * e->n_present;
     return KGWE_OK;
 }
 
 int pull_counters(kgwe_engine* e, cudaStream_t s) {
-    CU(e, cudaMemcpyAsync(e->h_counters, e->d_counters, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
-    CU(e, cudaMemsetAsync(e->d_counters, 0, 2 * sizeof(unsigned long long), s));
+    CU(e, cudaMemcpyAsync(e->h_counters, e->d_counters, kCounters * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
+    CU(e, cudaMemsetAsync(e->d_counters, 0, kCounters * sizeof(unsigned long long), s));
     return KGWE_OK;
 }
 
@@ -364,22 +330,31 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
            && cudaEventCreate(&e->ev0) == cudaSuccess && cudaEventCreate(&e->ev1) == cudaSuccess
            && cudaMalloc(&e->d_nodes, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
            && cudaMallocHost(&e->h_nodes, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
-           && cudaMalloc(&e->d_counters, 2 * sizeof(unsigned long long)) == cudaSuccess
-           && cudaMallocHost(&e->h_counters, 2 * sizeof(unsigned long long)) == cudaSuccess
+           && cudaMalloc(&e->d_counters, kCounters * sizeof(unsigned long long)) == cudaSuccess
+           && cudaMallocHost(&e->h_counters, kCounters * sizeof(unsigned long long)) == cudaSuccess
            && cudaMalloc(&e->d_done, sizeof(unsigned int)) == cudaSuccess && cudaMemset(e->d_done, 0, sizeof(unsigned int)) == cudaSuccess
            && cudaMallocHost(&e->h_flag, sizeof(unsigned int)) == cudaSuccess
            && cudaMemset(e->d_nodes, 0, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
-           && cudaMemset(e->d_counters, 0, 2 * sizeof(unsigned long long)) == cudaSuccess;
+           && cudaMemset(e->d_counters, 0, kCounters * sizeof(unsigned long long)) == cudaSuccess;
     if (ok) {
         memset(e->h_nodes, 0, (size_t)cfg->max_nodes * sizeof(DevNode));
-        e->h_counters[0] = e->h_counters[1] = 0; *e->h_flag = 0;
+        for (int i = 0; i < kCounters; ++i) e->h_counters[i] = 0;
+        *e->h_flag = 0;
         e->dirty_flag.assign(cfg->max_nodes, 0);
         cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, cfg->device);
         for (int i = 0; i < kgwe_engine::kTimers && ok; ++i) ok = cudaEventCreate(&e->t0[i]) == cudaSuccess && cudaEventCreate(&e->t1[i]) == cudaSuccess;
-        ok = ok && cudaFuncSetAttribute(score_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK, false, false)) == cudaSuccess
-                && cudaFuncSetAttribute(score_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK, true, false)) == cudaSuccess
-                && cudaFuncSetAttribute(score_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK, false, true)) == cudaSuccess
-                && cudaFuncSetAttribute(score_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)score_smem_bytes(MAX_PODS_PER_CHUNK, true, true)) == cudaSuccess;
+        {
+            const int lean = (int)k1_layout(MAX_PODS_PER_CHUNK, false, false, true).total, gen = (int)k1_layout(MAX_PODS_PER_CHUNK, true, false, true).total,
+                      tab = (int)k1_layout(512, true, true, true).total;
+            ok = ok && cudaFuncSetAttribute(score_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lean) == cudaSuccess
+                    && cudaFuncSetAttribute(score_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, gen) == cudaSuccess
+                    && cudaFuncSetAttribute(score_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab) == cudaSuccess;
+            // co-resident CTAs at a typical chunk size (plan_k1 sizes its waves with these)
+            int b = 0;
+            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<false, false>, K1_THREADS, k1_layout(512, false, false, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[0] = b;
+            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, false>, K1_THREADS, k1_layout(512, true, false, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[1] = b;
+            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, true>, K1_THREADS, k1_layout(512, true, true, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[2] = b;
+        }
         int bps = 0;
         if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, schedule_kernel, SCORE_THREADS, 0) == cudaSuccess && bps > 0) e->sched_blocks_per_sm = bps;
         ok = ok && cudaFuncSetAttribute(schedule_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sched_tile_smem_bytes()) == cudaSuccess;
@@ -429,6 +404,7 @@ int kgwe_nodes_upsert(kgwe_engine* e, uint32_t first, uint32_t count, const kgwe
             for (auto& kv : e->ledger) if (kv.second.node == first + i) { m |= kv.second.mask; n++; }
             rec.allocated_mask = m; rec.n_allocs = n;
         }
+        e->n_nonuniform += rec_nonuniform(rec) - rec_nonuniform(dst);
         dst = rec;
         if (!was) e->n_present++;
         mark_dirty(e, first + i);
@@ -449,6 +425,7 @@ int kgwe_node_remove(kgwe_engine* e, uint32_t idx) {
     // in the ledger (they are keyed by node name there) and simply stop matching any node - until a
     // node comes back under the same index (see kgwe_nodes_upsert).  n_nodes is a high-water mark and
     // does not shrink, so the stride of score matrices and hint rows stays what the host knows.
+    e->n_nonuniform -= rec_nonuniform(dst);
     memset(&dst, 0, sizeof dst);
     e->n_present--;
     mark_dirty(e, idx);
@@ -507,35 +484,16 @@ int kgwe_score_batch_device_p2p(kgwe_engine* e, const kgwe_pod_req* d_pods, uint
     if (n_pods == 0) return KGWE_OK;
     if (e->n_nodes == 0) return fail(e, KGWE_ERR_INVALID_ARG, "the cluster image of this shard is empty");
     // K1 exactly as in launch_score(topk = 1), then the fused finalise + scatter
-    const uint32_t n_tiles = (e->n_nodes + TILE_NODES - 1) / TILE_NODES;
-    const bool tables = e->cfg.flags & KGWE_CFG_SUBSET_TABLES, memo = e->cfg.flags & KGWE_CFG_MEMOISE_GROUPS;
-    uint32_t chunks, ppc;
-    plan_pod_chunks(e, n_pods, n_tiles, tables, &chunks, &ppc);
-    if (chunks > 65535u) return fail(e, KGWE_ERR_TOO_LARGE, "too many pods in one launch (%u)", n_pods);
-    {
-        const size_t had = e->d_best.cap;
-        CU(e, e->d_best.ensure(n_pods));
-        if (e->d_best.cap != had) CU(e, cudaMemsetAsync(e->d_best.p, 0, e->d_best.cap * sizeof(unsigned long long), s));
-    }
+    rc = ensure_best(e, n_pods, s);
+    if (rc != KGWE_OK) return rc;
     unsigned long long* best = e->d_best.p;
-    const dim3 grid(n_tiles, chunks);
-    const size_t smem = score_smem_bytes(ppc, tables, memo);
-    const FusedTail tail{};
-    const bool timed = e->timers_pending < kgwe_engine::kTimers;
-    if (timed) CU(e, cudaEventRecord(e->t0[e->timers_pending], s));
-#define KGWE_LAUNCH_SCORE(T, M) score_kernel<T, M><<<grid, SCORE_THREADS, smem, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e), \
-                                                                                     d_out, best, e->params, e->d_counters, tail)
-    if (tables) { if (memo) KGWE_LAUNCH_SCORE(true, true); else KGWE_LAUNCH_SCORE(true, false); }
-    else        { if (memo) KGWE_LAUNCH_SCORE(false, true); else KGWE_LAUNCH_SCORE(false, false); }
-#undef KGWE_LAUNCH_SCORE
-    CU(e, cudaGetLastError());
-    if (timed) { CU(e, cudaEventRecord(e->t1[e->timers_pending], s)); e->timers_pending++; }
+    rc = launch_k1(e, d_pods, n_pods, d_hint, d_out, best, s, false, FusedTail{}, true);
+    if (rc != KGWE_OK) return rc;
     PeerBufs peers;
     for (uint32_t r = 0; r < 8; ++r) peers.p[r] = r < n_ranks ? reinterpret_cast<kgwe_placement*>(peer_bufs[r]) : nullptr;
     finalize_top1_p2p_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), best, peers, n_ranks, my_rank, e->params);
     CU(e, cudaGetLastError());
-    e->stats.kernel_launches += 2;
-    e->stats.evaluations += (uint64_t)n_pods * e->n_present;
+    e->stats.kernel_launches++;
     return KGWE_OK;
 }
 
@@ -622,7 +580,7 @@ int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, 
         if (rc != KGWE_OK) return rc;
         CU(e, cudaStreamSynchronize(s));
         if (topk) memcpy(out_topk + (size_t)p0 * topk, e->h_topk.p, (size_t)np * topk * sizeof(kgwe_placement));
-        e->stats.candidates += e->h_counters[1];
+        e->stats.candidates += e->h_counters[1]; e->stats.candidates_resolved += e->h_counters[2];
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) == cudaSuccess) gpu_ms += ms;
     }
@@ -719,7 +677,7 @@ static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t 
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) == cudaSuccess) *gpu_ms += ms;
     e->stats.evaluations += e->h_counters[0];
-    e->stats.candidates += e->h_counters[1];
+    e->stats.candidates += e->h_counters[1]; e->stats.candidates_resolved += e->h_counters[2];
     return KGWE_OK;
 }
 
@@ -1077,8 +1035,8 @@ int kgwe_snapshot_load(kgwe_engine* e, const void* buf, uint64_t len) {
         e->ledger[en.wl_id] = LedgerEntry{en.node, (uint8_t)en.mask};
     }
     e->n_nodes = std::max(h.n_nodes, old_n);          // high-water mark never shrinks (absent records score as absent)
-    e->n_present = 0;
-    for (uint32_t i = 0; i < e->n_nodes; ++i) { if (e->h_nodes[i].flags & NODE_PRESENT) e->n_present++; mark_dirty(e, i); }
+    e->n_present = 0; e->n_nonuniform = 0;
+    for (uint32_t i = 0; i < e->n_nodes; ++i) { if (e->h_nodes[i].flags & NODE_PRESENT) e->n_present++; e->n_nonuniform += rec_nonuniform(e->h_nodes[i]); mark_dirty(e, i); }
     return KGWE_OK;
 }
 
@@ -1108,9 +1066,9 @@ int kgwe_get_stats(kgwe_engine* e, kgwe_stats* out) {
     e->timers_pending = 0;
     // fold in candidates counted by asynchronous (device-pointer) calls since the last pull
     if (cudaSetDevice(e->cfg.device) == cudaSuccess && cudaDeviceSynchronize() == cudaSuccess &&
-        cudaMemcpy(e->h_counters, e->d_counters, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost) == cudaSuccess &&
-        cudaMemset(e->d_counters, 0, 2 * sizeof(unsigned long long)) == cudaSuccess) {
-        e->stats.candidates += e->h_counters[1];
+        cudaMemcpy(e->h_counters, e->d_counters, kCounters * sizeof(unsigned long long), cudaMemcpyDeviceToHost) == cudaSuccess &&
+        cudaMemset(e->d_counters, 0, kCounters * sizeof(unsigned long long)) == cudaSuccess) {
+        e->stats.candidates += e->h_counters[1]; e->stats.candidates_resolved += e->h_counters[2];
     }
     *out = e->stats;
     out->n_nodes = e->n_nodes;
@@ -1171,17 +1129,10 @@ extern "C" int kgwe_score_top1_noalloc(kgwe_engine* e, const kgwe_pod_req* d_pod
     if (e->n_nodes == 0) return fail(e, KGWE_ERR_INVALID_ARG, "kgwe_score_top1_noalloc: the cluster image is empty");
     // the table still holds whatever an earlier (possibly failed) call left: clear our slots
     CU(e, cudaMemsetAsync(keys, 0, (size_t)n_pods * sizeof(unsigned long long), s));
-    const uint32_t n_tiles = (e->n_nodes + TILE_NODES - 1) / TILE_NODES;
-    uint32_t chunks = std::max(1u, ((uint32_t)e->sm_count * 8u + n_tiles - 1) / n_tiles);
-    chunks = std::min(chunks, n_pods);
-    uint32_t ppc = std::min<uint32_t>((n_pods + chunks - 1) / chunks, MAX_PODS_PER_CHUNK);
-    chunks = (n_pods + ppc - 1) / ppc;
-    score_kernel<false, false><<<dim3(n_tiles, chunks), SCORE_THREADS, score_smem_bytes(ppc), s>>>(
-        e->d_nodes, e->n_nodes, d_pods, n_pods, ppc, d_hint, hint_row_bytes(e), d_out, keys, e->params, e->d_counters, FusedTail{});
-    CU(e, cudaGetLastError());
+    rc = launch_k1(e, d_pods, n_pods, d_hint, d_out, keys, s, false, FusedTail{}, false);
+    if (rc != KGWE_OK) return rc;
     finalize_top1_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), keys, d_top1, 1, e->params);
     CU(e, cudaGetLastError());
-    e->stats.kernel_launches += 2;
-    e->stats.evaluations += (uint64_t)n_pods * e->n_present;
+    e->stats.kernel_launches++;
     return KGWE_OK;
 }

@@ -1,14 +1,6 @@
 // kgwe_kernels.cuh — the engine's kernels (sm_100a).
 //
-//  score_kernel      K1  stateless Filter+Prioritize: grid = node tiles x pod chunks.  A CTA
-//                        stages one tile of 64 node records (48 KB) into shared memory with a
-//                        single TMA bulk copy (cp.async.bulk + mbarrier), derives the
-//                        pod-independent NodeCtx of its nodes once, then works through its pod chunk
-//                        in (8 pods x 4 nodes) items taken from a shared counter: three numeric
-//                        tiers for the NVLink group search (bit-set walks on uniform nodes, int32
-//                        chains on whole-number bandwidths, FP64 otherwise), 16-byte score records
-//                        out, per-pod arg-max through a shared-memory key table flushed with one
-//                        atomicMax per pod.
+//  score_kernel      K1  stateless Filter+Prioritize, one lane per node: kgwe_score.cuh / kgwe_lane.cuh.
 //  finalize_top1     K1b turns the arg-max keys into placements (+ EstimatedBandwidth).
 //  topk_select       K2  ranked top-k per pod from the score matrix (canonical order).
 //  topk_merge        K2b merges per-shard ranked lists (multi-GPU, after the all-gather).
@@ -22,9 +14,8 @@
 namespace kgwe {
 namespace cg = cooperative_groups;
 
-constexpr int TILE_NODES = 64;                 // nodes per CTA tile
-constexpr int SCORE_THREADS = TILE_NODES * 8;  // 8 lanes per node
-constexpr int MAX_PODS_PER_CHUNK = 1024;       // size of the per-CTA arg-max table
+constexpr int TILE_NODES = 64;                 // K3: nodes per CTA tile
+constexpr int SCORE_THREADS = TILE_NODES * 8;  // K3: 8 lanes per node
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -111,327 +102,9 @@ __device__ __forceinline__ void finalize_one(const DevNode* __restrict__ nodes, 
     }
 }
 
-// ---------------------------------------------------------------------------------------
-// K1.  dynamic smem: [tile: 64 x 768 B][fast: 64 x 288 B][ctx: 64 x NodeCtx][keys: pods_per_chunk x 8 B][mbarrier]
-//
-// Pod loop, "octet" form: the 8 lanes of a group take 8 consecutive pods at a time.
-//   phase 0  lane i loads pod i and runs the Filter for (pod i, this node);
-//   phase A  on uniform nodes lane i first tries the bit-set walk from the lowest available GPU for pod i
-//            (first_uniform_walk), which settles almost every evaluation; for each pod still open - all of
-//            them on other nodes - the 8 lanes run the 8 greedy chains (lane = start GPU) and reduce to
-//            the winner; lane i keeps pod i's;
-//   phase B  lane i finishes pod i (topology score, resource, total, flags), stores its 16-byte
-//            NodeScore and joins the per-pod arg-max.
-// So the group search is 8-wide per evaluation while the scalar part of an evaluation is done by
-// one lane instead of redundantly by eight.  Stores of one warp instruction: for each i, the 4
-// groups' lanes i write 4 consecutive nodes of pod i = 64 contiguous bytes.
-// The group search of a quad runs in the cheapest tier its four nodes allow: bit-set walks (all uniform), int32 chains
-// (all whole-number), else FP64 chains with 64-bit winner keys.  Octets containing an exhaustive-mode pod take the
-// one-pod-per-pass generic path instead, unless the kernel was launched with subset tables (TABLES) and the quad's
-// bandwidths are whole numbers: then each node also gets, once per tile, the score key of every one of
-// its 256 GPU subsets (E1: total << 8 | 255 - mask, 0 when the subset is not an available active
-// clique), laid out by popcount, and an exhaustive evaluation is the max over the C(8,k) keys of
-// its k - 8 lanes x <= 9 entries - with the same lowest-mask tie-break.
-//   extra smem with TABLES: [subset keys: 64 x 256 x 4 B][mask-by-popcount order: 256 B]
-constexpr int SUBSET_SMEM_BYTES = TILE_NODES * 256 * 4 + 256;
-__device__ __forceinline__ int subset_off(int k) {      // first table slot of popcount k: sum_{i<k} C(8,i)
-    return k <= 0 ? 0 : k == 1 ? 1 : k == 2 ? 9 : k == 3 ? 37 : k == 4 ? 93 : k == 5 ? 163 : k == 6 ? 219 : k == 7 ? 247 : k == 8 ? 255 : 256;
-}
-
-// MEMO (engine flag KGWE_CFG_MEMOISE_GROUPS): the greedy winner of a node depends only on the
-// node and on k, so it is computed once per tile for k = 2..8 and every (pod,node) evaluation
-// looks it up instead of re-running the 8 chains.  Same results; reported separately from the
-// brute-force rate because the group search is then shared between pods.
-//   extra smem with MEMO: [winners: 64 nodes x 8 x (key, pay)] = 4 KB
-constexpr int MEMO_SMEM_BYTES = TILE_NODES * 8 * 8;
-// Optional fused finalisation for the latency path: out != nullptr enables it.
-// Up to 4 pod descriptors can travel inside the kernel parameters (n_inline > 0): the kernel then never
-// reads the descriptors over PCIe from pinned host memory, which removes three dependent host-memory
-// round trips from a single-pod call.
-struct FusedTail { kgwe_placement* out; unsigned int* done; unsigned int* flag; unsigned int seq; unsigned int n_inline; kgwe_pod_req inline_pods[4]; };
-template <bool TABLES, bool MEMO>
-__global__ void __launch_bounds__(SCORE_THREADS, TABLES ? 1 : 2)
-score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
-             const kgwe_pod_req* __restrict__ pods, uint32_t n_pods, uint32_t pods_per_chunk,
-             const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
-             kgwe_node_score* __restrict__ out, unsigned long long* __restrict__ best,
-             Params P, unsigned long long* __restrict__ counters, FusedTail tail) {
-    extern __shared__ __align__(128) unsigned char smem[];
-    DevNode* tile = reinterpret_cast<DevNode*>(smem);
-    NodeFast* fast = reinterpret_cast<NodeFast*>(smem + TILE_NODES * sizeof(DevNode));
-    NodeCtx* ctxs = reinterpret_cast<NodeCtx*>(smem + TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast)));
-    constexpr size_t kBase = TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx));
-    uint32_t* subset = reinterpret_cast<uint32_t*>(smem + kBase);                       // TABLES only
-    uint8_t* smask = smem + kBase + TILE_NODES * 256 * 4;                               // TABLES only
-    int2* memo = reinterpret_cast<int2*>(smem + kBase + (TABLES ? SUBSET_SMEM_BYTES : 0));   // MEMO only
-    // per-pod arg-max of this CTA's tile, as a 32-bit word (TotalScore << 6 | 63 - node-in-tile: a native shared-memory
-    // atomicMax; the 64-bit form is a compare-and-swap spin loop, and all warps of a CTA hit the same 8 pods together).
-    // TotalScore of a kept evaluation is 1 .. 4000 (|weights| <= 1000, kgwe_engine_create), far below 2^25.
-    uint32_t* keys = reinterpret_cast<uint32_t*>(smem + kBase + (TABLES ? SUBSET_SMEM_BYTES : 0) + (MEMO ? MEMO_SMEM_BYTES : 0));
-    uint64_t* bar = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned long long*>(keys) + pods_per_chunk);
-
-    const int tid = threadIdx.x, lane = tid & 31, j = tid & 7;
-    const uint32_t tile_first = blockIdx.x * TILE_NODES;
-    const uint32_t tile_count = min((uint32_t)TILE_NODES, n_nodes - tile_first);
-    const uint32_t p_begin = blockIdx.y * pods_per_chunk;
-    const uint32_t p_end = min(n_pods, p_begin + pods_per_chunk);
-
-    __shared__ kgwe_pod_req inline_copy[4];
-    if (tid < (int)tail.n_inline) inline_copy[tid] = tail.inline_pods[tid];
-    const kgwe_pod_req* spods = tail.n_inline ? inline_copy : nullptr;
-    if (tid == 0) mbar_init(bar, 1);
-    __syncthreads();
-    if (tid == 0) {
-        const uint32_t bytes = tile_count * (uint32_t)sizeof(DevNode);
-        mbar_expect_tx(bar, bytes);
-        tma_bulk_g2s(tile, nodes + tile_first, bytes, bar);
-    }
-    if (best) for (uint32_t i = tid; i < pods_per_chunk; i += SCORE_THREADS) keys[i] = 0u;
-    // NUMA / PCIe group tables are only worth building when the chunk has a pod that asks for them
-    bool want_groups = false;
-    for (uint32_t p = p_begin + tid; p < p_end; p += SCORE_THREADS) {
-        const uint8_t pref = spods ? spods[p].topology_pref : __ldg(&pods[p].topology_pref);
-        want_groups |= pref == KGWE_TOPO_SAME_NUMA || pref == KGWE_TOPO_SAME_PCIE_SWITCH;
-    }
-    if (TABLES && tid < 256) {          // slot of mask `tid` in (popcount, value) order
-        int rank = 0;
-        for (int m = 0; m < tid; ++m) rank += __popc(m) == __popc(tid);
-        smask[subset_off(__popc(tid)) + rank] = (uint8_t)tid;
-    }
-    mbar_wait(bar, 0);
-    want_groups = __syncthreads_or(want_groups);
-
-    // ---- set-up: lane group g of the CTA prepares node g of the tile; quad = the 4 nodes of one warp ----
-    constexpr int QUADS = SCORE_THREADS / 32;
-    __shared__ uint8_t quad_flags[QUADS];           // bit 0: all four nodes whole-number (int32 chains), bit 1: all four uniform (bit-set walks)
-    __shared__ unsigned int next_item;
-    if (tid == 0) next_item = 0;
-    {
-        const int grp = tid >> 3;
-        const bool node_ok = grp < (int)tile_count;
-        const DevNode* rec = tile + grp;
-        NodeFast* nf = fast + grp;
-        bool warp_fast, warp_uniform;
-        NodeCtx c;
-        node_ctx_core(c, rec, node_ok);
-        if (want_groups) node_ctx_group_tables(c, rec);
-        // integer form of the greedy inputs; usable when all four nodes of the warp are whole-number
-        warp_fast = __all_sync(0xffffffffu, c.integral || !c.valid);
-        // and the bit-set walk when all four are uniform (greedy_walk_uniform_k); the memoised variant keeps its int32 tables
-        const int ucode = c.valid ? node_uniform_code(rec) : 0;
-        warp_uniform = !MEMO && __all_sync(0xffffffffu, ucode != 0 || !c.valid);
-        if (c.integral) node_fast_build(nf, rec, c, j);
-        else nf->init[j] = FAST_NEG;
-        if (!MEMO && ucode && j == 0) uniform_topo_build(nf, node_uniform_bw(rec, ucode), P.norm);
-        if (j == 0) ctxs[grp] = c;
-        if (TABLES) {
-            // E1 subset keys of this node: lane j fills slots j, j+8, ...
-            uint32_t* tab = subset + grp * 256;
-            for (int r = j; r < 256; r += 8) {
-                const uint32_t mask = smask[r];
-                uint32_t key = 0;
-                if (c.integral && mask && !(mask & ~c.avail)) {
-                    bool ok = true; int total = 0;
-                    for (int m = 0; m < 8; ++m) {
-                        if (!(mask >> m & 1)) continue;
-                        if (mask & ~(1u << m) & ~(uint32_t)((c.colact >> (8 * m)) & 0xff)) ok = false;
-                        for (int i = 0; i < m; ++i) if (mask >> i & 1) total += __double2int_rz(rec->bw_in[i][bw_slot(i, m)]);
-                    }
-                    if (ok && total > 0) key = ((uint32_t)total << 8) | (255u - mask);
-                }
-                tab[r] = key;
-            }
-        }
-        __syncwarp();
-        if (MEMO) {
-            // greedy winners of this node for every group size (all 32 lanes: shuffles inside)
-#pragma unroll 1
-            for (int kk = 2; kk <= 8; ++kk) {
-                int32_t key = 0; uint32_t pay = 0;
-                if (c.integral && c.A >= kk && (c.avail >> j & 1)) greedy_chain_fast(nf, j, kk, key, pay);
-                fast_group_winner(key, pay, 0xffffffffu);          // (all 32 lanes are here)
-                if (j == 0) memo[grp * 8 + (kk - 1)] = make_int2(key, (int)pay);
-            }
-            __syncwarp();
-        }
-        if (lane == 0) quad_flags[tid >> 5] = (uint8_t)((warp_fast ? 1 : 0) | (warp_uniform ? 2 : 0));
-    }
-    __syncthreads();            // every warp may now work on any quad's tables
-    const uint32_t gmask = 0xffu << (lane & 24);
-    unsigned long long cand = 0;
-
-    // Work items = (octet of pods, quad of nodes), handed out through a shared counter in pod-major order: a warp whose
-    // nodes need the 8-lane search more often (links down, sparse meshes) simply takes fewer items, instead of making the
-    // other 15 warps wait for it at the end of the chunk (that wait was a third of all warp time with a fixed split).
-    const uint32_t n_items = ((p_end - p_begin + 7u) / 8u) * QUADS;
-    for (;;) {
-        uint32_t item = 0;
-        if (lane == 0) item = atomicAdd(&next_item, 1u);
-        item = __shfl_sync(0xffffffffu, item, 0);
-        if (item >= n_items) break;
-        const uint32_t p0 = p_begin + (item / QUADS) * 8u;
-        const int quad = (int)(item % QUADS);
-        const int grp = quad * 4 + (lane >> 3);
-        const uint32_t node = tile_first + grp;
-        const bool node_ok = grp < (int)tile_count;
-        const DevNode* rec = tile + grp;
-        NodeFast* nf = fast + grp;
-        const NodeCtx& nc = ctxs[grp];
-        const bool warp_fast = quad_flags[quad] & 1, warp_uniform = quad_flags[quad] & 2;
-        const bool start_ok = (nc.avail >> j) & 1;          // this lane's start GPU is available
-        // ---- phase 0: lane j owns pod p0 + j ----
-        const uint32_t p = p0 + j;
-        const bool live = p < p_end;
-        kgwe_pod_req pod = load_pod2(pods, spods, live ? p : p0);
-        const int k = clamp_k(pod.gpu_count);
-        const bool eligible = live && eval_filter(rec, nc, pod, k);
-        const bool wants_group = k >= 2 && is_nvlink_pref(pod);
-        const bool exhaustive = wants_group && (pod.flags & KGWE_POD_EXHAUSTIVE);
-        const bool any_exh = __any_sync(0xffffffffu, live && exhaustive);
-        // general (fractional, irregular) bandwidths take the same octet loop with FP64 chains and 64-bit keys
-        const bool fp64_chains = !warp_fast && !warp_uniform;
-        const bool octet = (warp_fast && (TABLES || !any_exh)) || !any_exh;
-        EvalOut o;
-        if (octet) {
-            // ---- phase A: the group searches, one pod slot at a time ----
-            int32_t mykey = 0; uint32_t mypay = 0, mylow = 0;     // (FP64 chains: mykey:mylow = the bits of the winning total)
-            int chain_k = (eligible && wants_group) ? (k | (exhaustive ? 16 : 0)) : 0;
-            if (MEMO && warp_fast && chain_k && !exhaustive) {        // look the greedy winner up instead of searching
-                const int2 w = memo[grp * 8 + (k - 1)];
-                mykey = w.x; mypay = (uint32_t)w.y; chain_k = 0;
-            }
-            if (warp_uniform && chain_k && !exhaustive) {
-                // uniform nodes: each lane first tries the walk from its node's lowest available GPU for its own pod; that
-                // settles nearly every evaluation without any cross-lane work (first_uniform_walk)
-                if (first_uniform_walk(nc.avail, nc.colact, k, mypay)) { mykey = 8; chain_k = 0; }
-            }
-            // the 8-lane search, one pod slot at a time, for whatever is left: everything on non-uniform nodes, on uniform
-            // ones only the pods whose first walk died
-            uint32_t pend = __ballot_sync(0xffffffffu, chain_k != 0);
-            pend = (pend | (pend >> 8) | (pend >> 16) | (pend >> 24)) & 0xffu;
-#pragma unroll 1
-            for (; pend; pend &= pend - 1u) {
-                const int t = __ffs((int)pend) - 1;
-                const int ct = __shfl_sync(0xffffffffu, chain_k, t, 8);
-                const int kt = ct & 15;
-                int32_t key = 0; uint32_t pay = 0, word_lo = 0;
-                if (TABLES && __any_sync(0xffffffffu, ct & 16)) {      // some group has an exhaustive pod in this slot
-                    if (ct & 16) {
-                        const uint32_t* tab = subset + grp * 256;
-                        uint32_t b = 0;
-                        for (int r = subset_off(kt) + j; r < subset_off(kt + 1); r += 8) b = max(b, tab[r]);
-#pragma unroll
-                        for (int off = 4; off >= 1; off >>= 1) b = max(b, __shfl_xor_sync(gmask, b, off, 8));
-                        key = (int32_t)b;
-                    } else if (kt) {
-                        if (start_ok) {
-                            if (warp_uniform) greedy_walk_uniform(nc.avail, nc.colact, j, kt, key, pay);
-                            else greedy_chain_fast(nf, j, kt, key, pay);
-                        }
-                        fast_group_winner(key, pay, gmask);
-                    }
-                } else if (fp64_chains) {
-                    // scoreNVLinkTopology in float64 (greedy_chain); winner = strictly largest total, then lowest start
-                    bool ok = false; double total = 0.0; uint32_t mem = 0;
-                    if (kt && start_ok) greedy_chain(rec, nc, j, kt, ok, total, pay, mem);
-                    unsigned long long k64 = (ok && total > 0.0) ? (unsigned long long)__double_as_longlong(total) : 0ull;
-                    uint32_t tie = (uint32_t)j;
-#pragma unroll
-                    for (int off = 4; off >= 1; off >>= 1) {
-                        const unsigned long long okey = __shfl_xor_sync(0xffffffffu, k64, off, 8);
-                        const uint32_t otie = __shfl_xor_sync(0xffffffffu, tie, off, 8);
-                        const uint32_t opay = __shfl_xor_sync(0xffffffffu, pay, off, 8);
-                        if (okey > k64 || (okey == k64 && otie < tie)) { k64 = okey; tie = otie; pay = opay; }
-                    }
-                    key = (int32_t)(k64 >> 32); word_lo = (uint32_t)k64;        // (a positive double: the high word is > 0)
-                } else {
-                    if (kt && start_ok) {
-                        if (warp_uniform) greedy_walk_uniform(nc.avail, nc.colact, j, kt, key, pay);
-                        else greedy_chain_fast(nf, j, kt, key, pay);
-                    }
-                    // all 32 lanes are here together (the branches into this block are warp-uniform): naming the whole
-                    // warp spares the per-lane mask handling the compiler adds around shuffles with a lane-dependent mask
-                    fast_group_winner(key, pay, 0xffffffffu);
-                }
-                if (j == t && ct) { mykey = key; mypay = pay; mylow = word_lo; }      // (groups whose pod of this slot is already settled keep their result)
-            }
-            // ---- phase B: lane j finishes pod p0 + j ----
-            bool found = mykey > 0; double win_total = (double)(mykey >> 3);
-            if (fp64_chains) { found = (mykey | (int32_t)mylow) != 0; win_total = __longlong_as_double((long long)(((unsigned long long)(uint32_t)mykey << 32) | mylow)); }
-            const int topo_known = (warp_uniform && found && !(TABLES && exhaustive)) ? *uniform_topo_slot(nf, k) : -1;      // (found implies 2 <= k <= 8)
-            uint32_t ord = mypay, sel = found ? mask_of_order(mypay, k) : 0u, ncand = (uint32_t)nc.A;
-            if (TABLES && exhaustive) {
-                win_total = (double)(mykey >> 8);
-                take_first_k(255u - ((uint32_t)mykey & 255u), k, sel, ord);
-                ncand = 1; for (int i = 1; i <= k; ++i) ncand = ncand * (uint32_t)(nc.A - k + i) / (uint32_t)i;
-            }
-            eval_finish(rec, nc, pod, P, live && hint_bit(hint, hint_row_bytes, p, node), eligible, k,
-                        found, win_total, sel, ord, ncand, o, topo_known);
-            if (live && node_ok) {
-                cand += o.candidates;
-                if (out) {
-                    const kgwe_node_score r = to_record(o);
-                    *reinterpret_cast<int4*>(out + (size_t)p * n_nodes + node) = *reinterpret_cast<const int4*>(&r);
-                }
-            }
-            if (best) {
-                uint32_t key = (live && (o.flags & KGWE_F_KEPT)) ? (((uint32_t)o.total << 6) | (uint32_t)(63 - grp)) : 0u;
-                key = max(key, __shfl_xor_sync(0xffffffffu, key, 8));
-                key = max(key, __shfl_xor_sync(0xffffffffu, key, 16));
-                if (lane < 8 && key) atomicMax(&keys[p - p_begin], key);
-            }
-        } else {
-            // generic path: one pod per pass, all 8 lanes of a group on the same pod
-            const uint32_t n_here = min(8u, p_end - p0);
-#pragma unroll 1
-            for (uint32_t t = 0; t < n_here; ++t) {
-                const uint32_t pt = p0 + t;
-                const kgwe_pod_req podt = load_pod2(pods, spods, pt);
-                evaluate<true>(rec, nc, podt, P, hint_bit(hint, hint_row_bytes, pt, node), lane, o, nf, warp_fast);
-                if (j == 0 && node_ok) {
-                    cand += o.candidates;
-                    if (out) {
-                        const kgwe_node_score r = to_record(o);
-                        *reinterpret_cast<int4*>(out + (size_t)pt * n_nodes + node) = *reinterpret_cast<const int4*>(&r);
-                    }
-                }
-                if (best) {
-                    uint32_t key = (o.flags & KGWE_F_KEPT) ? (((uint32_t)o.total << 6) | (uint32_t)(63 - grp)) : 0u;
-                    key = max(key, __shfl_xor_sync(0xffffffffu, key, 8));
-                    key = max(key, __shfl_xor_sync(0xffffffffu, key, 16));
-                    if (lane == 0 && key) atomicMax(&keys[pt - p_begin], key);
-                }
-            }
-        }
-    }
-    // candidates counter: one atomic per warp
-#pragma unroll
-    for (int off = 16; off >= 1; off >>= 1) cand += __shfl_xor_sync(0xffffffffu, cand, off);
-    if (lane == 0 && counters && cand) atomicAdd(&counters[1], cand);
-    if (best) {
-        __syncthreads();
-        for (uint32_t i = tid; i < p_end - p_begin; i += SCORE_THREADS) {
-            const uint32_t kk = keys[i];
-            if (kk) atomicMax(&best[p_begin + i], rank_key((int32_t)(kk >> 6), P.node_base + tile_first + (63u - (kk & 63u))));
-        }
-    }
-    if (tail.out) {
-        // latency path (n_pods <= 64): the last CTA to finish turns the keys into placements in the
-        // same launch and raises the host-visible flag (threadfence-reduction pattern)
-        __shared__ unsigned int ticket;
-        __threadfence();
-        __syncthreads();
-        if (tid == 0) ticket = atomicAdd(tail.done, 1u);
-        __syncthreads();
-        if (ticket == gridDim.x * gridDim.y - 1) {
-            __threadfence();
-            finalize_one(nodes, n_nodes, pods, (uint32_t)(tid >> 3), (uint32_t)(tid >> 3) < n_pods, hint, hint_row_bytes, best, tail.out, P, lane, spods);
-            __threadfence_system();
-            __syncthreads();
-            if (tid == 0) { *tail.done = 0u; *reinterpret_cast<volatile unsigned int*>(tail.flag) = tail.seq; }
-        }
-    }
-}
+}  // namespace kgwe
+#include "kgwe_score.cuh"      // K1 (needs load_pod2 / finalize_one above)
+namespace kgwe {
 
 // K1b with the exchange fused in: the placement of (this rank, pod p) is stored into slot `my_rank`
 // of every rank's gather buffer over peer-mapped memory (NVLink P2P stores), replacing the all-gather.
@@ -614,7 +287,7 @@ schedule_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict
     if ((lane & 7) != 0) { cand = 0; evals = 0; }
 #pragma unroll
     for (int off = 16; off >= 8; off >>= 1) { cand += __shfl_xor_sync(0xffffffffu, cand, off); evals += __shfl_xor_sync(0xffffffffu, evals, off); }
-    if (lane == 0 && counters) { if (evals) atomicAdd(&counters[0], evals); if (cand) atomicAdd(&counters[1], cand); }
+    if (lane == 0 && counters) { if (evals) atomicAdd(&counters[0], evals); if (cand) { atomicAdd(&counters[1], cand); atomicAdd(&counters[2], cand); } }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -753,7 +426,8 @@ schedule_tile_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __res
     if (j != 0) { cand = 0; evals = 0; }
 #pragma unroll
     for (int off = 16; off >= 8; off >>= 1) { cand += __shfl_xor_sync(0xffffffffu, cand, off); evals += __shfl_xor_sync(0xffffffffu, evals, off); }
-    if (lane == 0 && counters) { if (evals) atomicAdd(&counters[0], evals); if (cand) atomicAdd(&counters[1], cand); }
+    // (winners come from the owner's per-size table: one candidate looked up per evaluation, A resolved)
+    if (lane == 0 && counters) { if (evals) { atomicAdd(&counters[0], evals); atomicAdd(&counters[1], evals); } if (cand) atomicAdd(&counters[2], cand); }
 }
 
 // EstimatedBandwidth of the queue's decisions (scheduler.go:656-692), one thread per decision.  It

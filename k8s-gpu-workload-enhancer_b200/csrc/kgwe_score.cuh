@@ -1,0 +1,175 @@
+// kgwe_score.cuh — K1, the stateless Filter + Prioritize kernel (scoreNodes for a batch of pods,
+// reference src/scheduler/scheduler.go:182-203 and everything it calls).
+//
+// grid = node tiles (K1_TILE nodes) x pod chunks; ONE LANE = ONE NODE (kgwe_lane.cuh).
+//   set-up   the CTA decodes its pod chunk into 16-byte PodLite records in shared memory; every lane reads
+//            its node's 768-byte record with 128-bit loads, derives the pod-independent state into registers
+//            (LaneNode) and its tables into [entry][lane] columns of shared memory (conflict-free for any
+//            per-lane entry): NVLink score per k of a uniform node, NUMA / PCIe group tables, MIG counts,
+//            and - kernel variants - the int32 / float64 link matrix, the E1 subset keys, memoised winners.
+//   loop     each warp walks the pods of the chunk for its 32 nodes: lane_evaluate (no cross-lane work),
+//            one 16-byte NodeScore store per lane (a warp writes 512 contiguous bytes of the pod's row),
+//            one REDUX.MAX + one shared-memory atomicMax per warp for the per-pod arg-max
+//            (TotalScore << 7 | 127 - node-in-tile), flushed with one global 64-bit atomicMax per pod per CTA.
+// Variants: GENERAL adds the matrix columns (images that hold a node whose active links are not all equal);
+// TABLES adds the E1 subset-key columns (implies GENERAL).  The search mode (all starts / first completed walk /
+// memoised winners) is a launch argument.
+#pragma once
+#include "kgwe_lane.cuh"
+
+namespace kgwe {
+
+constexpr int K1_THREADS = 128;                // 4 warps
+constexpr int K1_TILE = K1_THREADS;            // nodes per CTA: one per lane
+constexpr int MAX_PODS_PER_CHUNK = 1024;       // size of the per-CTA PodLite / arg-max tables
+
+// Optional fused finalisation for the latency path: out != nullptr enables it.
+// Up to 4 pod descriptors can travel inside the kernel parameters (n_inline > 0): the kernel then never
+// reads the descriptors over PCIe from pinned host memory, which removes dependent host-memory round trips
+// from a single-pod call.
+struct FusedTail { kgwe_placement* out; unsigned int* done; unsigned int* flag; unsigned int seq; unsigned int n_inline; kgwe_pod_req inline_pods[4]; };
+
+struct K1Layout { uint32_t pods, keys, topo, grp, mig, memo, mat, subset, slot, total; };
+__host__ __device__ inline K1Layout k1_layout(uint32_t ppc, bool general, bool tables, bool memo) {
+    K1Layout L; uint32_t o = 0;
+    L.pods = o; o += ppc * 16u;
+    L.keys = o; o += ((ppc * 4u) + 15u) & ~15u;
+    L.mat = o; o += general ? 32u * K1_TILE * 16u : 0u;
+    L.memo = o; o += memo ? 7u * K1_TILE * 8u : 0u;
+    L.topo = o; o += 7u * K1_TILE * 4u;
+    L.grp = o; o += 6u * K1_TILE * 4u;
+    L.mig = o; o += 3u * K1_TILE * 4u;
+    L.subset = o; o += tables ? 256u * K1_TILE * 4u : 0u;
+    L.slot = o; o += tables ? 256u : 0u;
+    L.total = o;
+    return L;
+}
+
+template <bool GENERAL, bool TABLES>
+__global__ void __launch_bounds__(K1_THREADS, TABLES ? 1 : (GENERAL ? 2 : 4))
+score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
+             const kgwe_pod_req* __restrict__ pods, uint32_t n_pods, uint32_t pods_per_chunk,
+             const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
+             kgwe_node_score* __restrict__ out, unsigned long long* __restrict__ best,
+             Params P, unsigned long long* __restrict__ counters, uint32_t mode, FusedTail tail) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const K1Layout L = k1_layout(pods_per_chunk, GENERAL, TABLES, mode == K1_MODE_MEMO);
+    PodLite* spod = reinterpret_cast<PodLite*>(smem + L.pods);
+    uint32_t* keys = reinterpret_cast<uint32_t*>(smem + L.keys);
+    uint8_t* slot_of = smem + L.slot;                                          // TABLES only
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint32_t tile_first = blockIdx.x * K1_TILE;
+    const uint32_t p_begin = blockIdx.y * pods_per_chunk;
+    const uint32_t p_end = min(n_pods, p_begin + pods_per_chunk);
+    const uint32_t np = p_end - p_begin;
+
+    __shared__ kgwe_pod_req inline_copy[4];
+    if (tid < (int)tail.n_inline) inline_copy[tid] = tail.inline_pods[tid];
+    const kgwe_pod_req* spods = tail.n_inline ? inline_copy : nullptr;
+    if (tail.n_inline) __syncthreads();
+
+    // ---- set-up 1: pod chunk -> PodLite; arg-max table cleared ----
+    bool want_groups = false;
+    for (uint32_t i = tid; i < np; i += K1_THREADS) {
+        const kgwe_pod_req pod = load_pod2(pods, spods, p_begin + i);
+        const PodLite pl = pod_lite(pod);
+        spod[i] = pl;
+        want_groups |= (pl.cls & (PL_NUMA | PL_PCIE)) != 0;      // the group tables are only worth building when a pod asks for them
+        keys[i] = 0u;
+    }
+    if (TABLES)      // slot of mask m in (popcount, value) order
+        for (int m = tid; m < 256; m += K1_THREADS) {
+            int rank = 0;
+            for (int q = 0; q < m; ++q) rank += __popc(q) == __popc(m);
+            slot_of[m] = (uint8_t)(subset_off(__popc(m)) + rank);
+        }
+    want_groups = __syncthreads_or(want_groups);
+
+    // ---- set-up 2: this lane's node ----
+    const uint32_t node = tile_first + tid;
+    const bool in_range = node < n_nodes;
+    const DevNode* rec = nodes + (in_range ? node : 0);
+    LaneNode ln;
+    LaneTabs tb;
+    tb.stride = K1_TILE;
+    tb.topo = reinterpret_cast<int32_t*>(smem + L.topo) + tid;
+    tb.grp = reinterpret_cast<uint32_t*>(smem + L.grp) + tid;
+    tb.mig = reinterpret_cast<uint32_t*>(smem + L.mig) + tid;
+    tb.memo = reinterpret_cast<int2*>(smem + L.memo) + tid;
+    tb.mat = reinterpret_cast<int4*>(smem + L.mat) + tid;
+    tb.subset = reinterpret_cast<uint32_t*>(smem + L.subset) + tid;
+    {
+        NodeCtx c;
+        node_ctx_core(c, rec, in_range);
+        if (want_groups) node_ctx_group_tables(c, rec);
+        lane_node_init(ln, c, rec, GENERAL);
+        lane_tables_build<GENERAL, TABLES>(ln, c, tb, rec, P.norm, mode, slot_of);
+    }
+    __syncthreads();
+
+    // ---- the pod loop: every warp scores all pods of the chunk against its 32 nodes ----
+    uint32_t cnt_scored = 0, cnt_resolved = 0;
+    kgwe_node_score* outp = out ? out + (size_t)p_begin * n_nodes + node : nullptr;
+    const uint8_t* hintp = hint ? hint + (size_t)p_begin * hint_row_bytes + (node >> 3) : nullptr;
+    PodLite pd = spod[0];
+#pragma unroll 1
+    for (uint32_t i = 0; i < np; ++i) {
+        const PodLite next = spod[i + 1 < np ? i + 1 : i];
+        double min_bw = 0.0;
+        if (pd.cls & PL_MINBW) min_bw = spods ? spods[p_begin + i].min_bandwidth_gbps : __ldg(&pods[p_begin + i].min_bandwidth_gbps);
+        bool hinted = false;
+        if (hintp) { hinted = in_range && ((__ldg(hintp) >> (node & 7)) & 1); hintp += hint_row_bytes; }
+        EvalOut o; uint32_t scored;
+        lane_evaluate<GENERAL, TABLES>(ln, tb, rec, pd, min_bw, hinted, P, mode, o, scored);
+        if (in_range) {
+            cnt_scored += scored; cnt_resolved += o.candidates;
+            if (outp) {
+                const kgwe_node_score r = to_record(o);
+                *reinterpret_cast<int4*>(outp) = *reinterpret_cast<const int4*>(&r);
+            }
+        }
+        if (outp) outp += n_nodes;
+        if (best) {
+            uint32_t key = (o.flags & KGWE_F_KEPT) ? (((uint32_t)o.total << 7) | (uint32_t)(K1_TILE - 1 - tid)) : 0u;
+            key = __reduce_max_sync(0xffffffffu, key);
+            if (lane == 0 && key) atomicMax(&keys[i], key);
+        }
+        pd = next;
+    }
+    // counters: [1] candidates whose score was computed, [2] candidates by the reference's counting rule
+    cnt_scored = __reduce_add_sync(0xffffffffu, cnt_scored);
+    cnt_resolved = __reduce_add_sync(0xffffffffu, cnt_resolved);
+    if (lane == 0 && counters) {
+        if (cnt_scored) atomicAdd(&counters[1], (unsigned long long)cnt_scored);
+        if (cnt_resolved) atomicAdd(&counters[2], (unsigned long long)cnt_resolved);
+    }
+    if (best) {
+        __syncthreads();
+        for (uint32_t i = tid; i < np; i += K1_THREADS) {
+            const uint32_t kk = keys[i];
+            if (kk) atomicMax(&best[p_begin + i], rank_key((int32_t)(kk >> 7), P.node_base + tile_first + ((uint32_t)(K1_TILE - 1) - (kk & 127u))));
+        }
+    }
+    if (tail.out) {
+        // latency path (n_pods <= 32): the last CTA to finish turns the keys into placements in the
+        // same launch and raises the host-visible flag (threadfence-reduction pattern)
+        __shared__ unsigned int ticket;
+        __threadfence();
+        __syncthreads();
+        if (tid == 0) ticket = atomicAdd(tail.done, 1u);
+        __syncthreads();
+        if (ticket == gridDim.x * gridDim.y - 1) {
+            __threadfence();
+            for (uint32_t p0 = 0; p0 < n_pods; p0 += K1_THREADS / 8) {
+                const uint32_t p = p0 + (uint32_t)(tid >> 3);
+                finalize_one(nodes, n_nodes, pods, p, p < n_pods, hint, hint_row_bytes, best, tail.out, P, lane, spods);
+            }
+            __threadfence_system();
+            __syncthreads();
+            if (tid == 0) { *tail.done = 0u; *reinterpret_cast<volatile unsigned int*>(tail.flag) = tail.seq; }
+        }
+    }
+}
+
+}  // namespace kgwe
