@@ -231,7 +231,7 @@ def run_kgwe(args):
         nodes, _, ledger = kg.synth.config(3, args.scale * world)   # same pod burst, `world` times the nodes
     N, P = len(nodes), len(pods)
     lo, hi = rank * N // world, (rank + 1) * N // world        # contiguous node shard of this rank
-    eng = kg.Engine(max_nodes=hi - lo, device=local_rank, node_base=lo)
+    eng = kg.Engine(max_nodes=hi - lo, device=local_rank, node_base=lo, flags=int(os.environ.get("KGWE_BENCH_FLAGS", "0"), 0))
     eng.upsert_nodes(nodes[lo:hi])
     for a in ledger:
         if lo <= a["node_idx"] < hi:

@@ -186,7 +186,7 @@ K1Plan plan_k1(const kgwe_engine* e, uint32_t n_pods, bool tables) {
     pl.general = pl.tables || e->n_nonuniform > 0;
     pl.mode = k1_mode(e);
     pl.n_tiles = (e->n_nodes + K1_TILE - 1) / K1_TILE;
-    const uint32_t max_ppc = pl.tables ? 512u : (uint32_t)MAX_PODS_PER_CHUNK;      // the subset columns leave room for 512 pod records
+    const uint32_t max_ppc = pl.tables ? 256u : (uint32_t)MAX_PODS_PER_CHUNK;      // the subset columns leave room for 256 pods' tables
     const uint32_t slots = (uint32_t)e->sm_count * (uint32_t)e->k1_blocks_per_sm[pl.tables ? 2 : pl.general ? 1 : 0];
     uint32_t chunks = 1, ppc = n_pods;
     for (uint32_t waves = 1; waves <= 256; ++waves) {
@@ -345,7 +345,7 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
         for (int i = 0; i < kgwe_engine::kTimers && ok; ++i) ok = cudaEventCreate(&e->t0[i]) == cudaSuccess && cudaEventCreate(&e->t1[i]) == cudaSuccess;
         {
             const int lean = (int)k1_layout(MAX_PODS_PER_CHUNK, false, false, true).total, gen = (int)k1_layout(MAX_PODS_PER_CHUNK, true, false, true).total,
-                      tab = (int)k1_layout(512, true, true, true).total;
+                      tab = (int)k1_layout(256, true, true, true).total;
             ok = ok && cudaFuncSetAttribute(score_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lean) == cudaSuccess
                     && cudaFuncSetAttribute(score_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, gen) == cudaSuccess
                     && cudaFuncSetAttribute(score_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab) == cudaSuccess;
@@ -353,7 +353,7 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
             int b = 0;
             if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<false, false>, K1_THREADS, k1_layout(512, false, false, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[0] = b;
             if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, false>, K1_THREADS, k1_layout(512, true, false, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[1] = b;
-            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, true>, K1_THREADS, k1_layout(512, true, true, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[2] = b;
+            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, true>, K1_THREADS, k1_layout(256, true, true, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[2] = b;
         }
         int bps = 0;
         if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, schedule_kernel, SCORE_THREADS, 0) == cudaSuccess && bps > 0) e->sched_blocks_per_sm = bps;

@@ -32,30 +32,26 @@ namespace kgwe {
 struct __align__(16) PodLite {
     uint64_t required;     // MinMemoryGB * 2^30 * k (scheduler.go:533), with the wrap-around of the 64-bit form
     int32_t  mig_count;    // MIGRequirements.Count
-    uint8_t  k;            // GPUCount clamped to 0..9; PL_K_NEVER for a negative count (never eligible)
-    uint8_t  cls;          // PL_* bits
-    uint8_t  arch;
-    uint8_t  mig_profile;
+    uint32_t pk;           // k | cls << 8 | arch << 16 | mig_profile << 24
 };
 static_assert(sizeof(PodLite) == 16, "PodLite is one 16-byte shared-memory word");
-constexpr uint8_t PL_NVLINK = 0x01;   // NVLink preference with k >= 2: the group search runs
-constexpr uint8_t PL_NUMA   = 0x02;   // SameNUMA with k >= 2
-constexpr uint8_t PL_PCIE   = 0x04;   // SamePCIeSwitch with k >= 2
-constexpr uint8_t PL_EXH    = 0x08;   // E1 exhaustive subset mode (implies PL_NVLINK)
-constexpr uint8_t PL_MINBW  = 0x10;   // E3 minimum bandwidth > 0 with k >= 2
-constexpr uint8_t PL_ARCH   = 0x20;
-constexpr uint8_t PL_MIG    = 0x40;
-constexpr uint8_t PL_K_NEVER = 15;
+// k = GPUCount clamped to 0..9; PL_K_NEVER for a negative count (never eligible).  cls bits (already shifted):
+constexpr uint32_t PL_NVLINK = 0x0100;   // NVLink preference with k >= 2: the group search runs
+constexpr uint32_t PL_NUMA   = 0x0200;   // SameNUMA with k >= 2
+constexpr uint32_t PL_PCIE   = 0x0400;   // SamePCIeSwitch with k >= 2
+constexpr uint32_t PL_EXH    = 0x0800;   // E1 exhaustive subset mode (implies PL_NVLINK)
+constexpr uint32_t PL_MINBW  = 0x1000;   // E3 minimum bandwidth > 0 with k >= 2
+constexpr uint32_t PL_ARCH   = 0x2000;
+constexpr uint32_t PL_MIG    = 0x4000;
+constexpr uint32_t PL_K_NEVER = 15;
 
 __device__ inline PodLite pod_lite(const kgwe_pod_req& pod) {
     PodLite pl;
     const int k = clamp_k(pod.gpu_count);
-    pl.k = k < 0 ? PL_K_NEVER : (uint8_t)k;
     pl.required = (uint64_t)(uint32_t)pod.min_memory_gb * 1073741824ull * (uint64_t)(uint32_t)k;
     pl.mig_count = pod.mig_count;
-    pl.arch = pod.arch; pl.mig_profile = pod.mig_profile;
     const bool nv = k >= 2 && is_nvlink_pref(pod);
-    uint8_t c = 0;
+    uint32_t c = k < 0 ? PL_K_NEVER : (uint32_t)k;
     if (nv) c |= PL_NVLINK;
     if (nv && (pod.flags & KGWE_POD_EXHAUSTIVE)) c |= PL_EXH;
     if (k >= 2 && pod.topology_pref == KGWE_TOPO_SAME_NUMA) c |= PL_NUMA;
@@ -63,7 +59,7 @@ __device__ inline PodLite pod_lite(const kgwe_pod_req& pod) {
     if (k >= 2 && pod.min_bandwidth_gbps > 0.0) c |= PL_MINBW;
     if (pod.arch != KGWE_ARCH_ANY) c |= PL_ARCH;
     if (pod.mig_profile != KGWE_MIG_NONE) c |= PL_MIG;
-    pl.cls = c;
+    pl.pk = c | ((uint32_t)pod.arch << 16) | ((uint32_t)pod.mig_profile << 24);
     return pl;
 }
 
@@ -142,63 +138,76 @@ __device__ __forceinline__ uint32_t prmt_raw(uint32_t a, uint32_t b, uint32_t se
 }
 
 // ---- uniform tier -----------------------------------------------------------------------------------
-// All eight starts, ascending GPU index (descending reversed position).  A start that is not available has an
-// all-zero row, so its walk dies at once.  A walk with K members is K-1 picks; a dead set stays dead (x & 0),
-// so one test before the last pick decides whether the walk completed.  All completed walks have the same
-// total (uniform_topo_build), and the reference keeps the FIRST start that reaches the best total (strict >,
-// scheduler.go:428-431).  ordR = join order in reversed positions, 3 bits per member.
+// All eight starts.  A start that is not available has an all-zero row, so its walk dies at once.  A walk with K
+// members is K-1 picks; a dead set stays dead (x & 0), so one test before the last pick decides whether the walk
+// completed.  All completed walks have the same total (uniform_topo_build), and the reference keeps the FIRST
+// start that reaches the best total (strict >, scheduler.go:428-431): the starts are walked from GPU 7 down to
+// GPU 0 and every completed walk overwrites the result, so the lowest-numbered completed start is what is left.
+// ordN = join order in reversed positions, one NIBBLE per member (member p in bits [4p, 4p+4)).
 template <int K>
-__device__ __forceinline__ void walk_all(uint32_t rlo, uint32_t rhi, bool& found, uint32_t& ordR) {
-    found = false; ordR = 0;
+__device__ __forceinline__ void walk_all(uint32_t rlo, uint32_t rhi, bool& found, uint32_t& ordN) {
+    found = false; ordN = 0;
 #pragma unroll
-    for (int b0 = 7; b0 >= 0; --b0) {
+    for (int b0 = 0; b0 <= 7; ++b0) {
         uint32_t alive = prmt_raw(b0 < 4 ? rlo : rhi, 0u, 0x4440u | (uint32_t)(b0 & 3));      // byte b0 of the rows, zero-extended
         uint32_t ord = (uint32_t)b0;
 #pragma unroll
         for (int t = 1; t < K - 1; ++t) {
             const uint32_t c = bfind_u32(alive);
-            ord = c * (1u << (3 * t)) + ord;
+            ord = c * (1u << (4 * t)) + ord;
             alive &= prmt_raw(rlo, rhi, c);
         }
         const bool ok = alive != 0u;
         const uint32_t c = bfind_u32(alive);
-        ord = c * (1u << (3 * (K - 1))) + ord;
-        if (ok && !found) { ordR = ord; found = true; }
+        ord = c * (1u << (4 * (K - 1))) + ord;
+        ordN = ok ? ord : ordN;
+        found = found || ok;
     }
 }
 
-__device__ __forceinline__ void walk_all_k(uint32_t rlo, uint32_t rhi, int k, bool& found, uint32_t& ordR) {
+__device__ __forceinline__ void walk_all_k(uint32_t rlo, uint32_t rhi, int k, bool& found, uint32_t& ordN) {
     switch (k) {      // k is the same for the whole warp
-        case 2: walk_all<2>(rlo, rhi, found, ordR); break;
-        case 3: walk_all<3>(rlo, rhi, found, ordR); break;
-        case 4: walk_all<4>(rlo, rhi, found, ordR); break;
-        case 5: walk_all<5>(rlo, rhi, found, ordR); break;
-        case 6: walk_all<6>(rlo, rhi, found, ordR); break;
-        case 7: walk_all<7>(rlo, rhi, found, ordR); break;
-        case 8: walk_all<8>(rlo, rhi, found, ordR); break;
-        default: found = false; ordR = 0; break;
+        case 2: walk_all<2>(rlo, rhi, found, ordN); break;
+        case 3: walk_all<3>(rlo, rhi, found, ordN); break;
+        case 4: walk_all<4>(rlo, rhi, found, ordN); break;
+        case 5: walk_all<5>(rlo, rhi, found, ordN); break;
+        case 6: walk_all<6>(rlo, rhi, found, ordN); break;
+        case 7: walk_all<7>(rlo, rhi, found, ordN); break;
+        case 8: walk_all<8>(rlo, rhi, found, ordN); break;
+        default: found = false; ordN = 0; break;
     }
 }
 
 // KGWE_CFG_PRUNE_TIED_STARTS: only the walk from the lowest available start.  When it completes it is the
 // reference's answer (all completed walks tie, the first start wins); when it dies the caller walks all starts.
-__device__ __forceinline__ bool walk_first(uint32_t avail, uint32_t rlo, uint32_t rhi, int k, uint32_t& ordR) {
+__device__ __forceinline__ bool walk_first(uint32_t avail, uint32_t rlo, uint32_t rhi, int k, uint32_t& ordN) {
     const uint32_t b0 = 7u - (uint32_t)(__ffs((int)avail) - 1);
     uint32_t alive = prmt_raw(rlo, rhi, b0) & 0xffu;
     uint32_t ord = b0;
     int t = 1;
     for (; t < k && alive; ++t) {
         const uint32_t c = bfind_u32(alive);
-        ord |= c << (3 * t);
+        ord |= c << (4 * t);
         alive &= prmt_raw(rlo, rhi, c);
     }
-    ordR = ord;
+    ordN = ord;
     return t == k;
 }
 
-// reversed positions -> GPU indices: 7 - b = b ^ 7 in every 3-bit field
-__device__ __forceinline__ uint32_t order_from_reversed(uint32_t ordR, int k) {
-    return (ordR ^ 0x00ffffffu) & (k >= 8 ? 0x00ffffffu : ((1u << (3 * k)) - 1u));
+// Nibble order in reversed positions -> SelectedGPUs as a set (GPU g at bit g) and as the ABI's packed list
+// (3 bits per member, GPU indices).  k in 2..8.  The set: each nibble selects its byte 1 << (7 - b) out of an
+// 8-byte table with one PRMT per four members; nibbles past k are set to 9, which PRMT reads as "sign of table
+// byte 1" = 0.  The list: 7 - b = b ^ 7, then the nibbles are squeezed to 3-bit fields.
+__device__ __forceinline__ void order_from_nibbles(uint32_t ordN, int k, uint32_t& sel, uint32_t& order) {
+    const uint32_t used = k >= 8 ? 0xffffffffu : ((1u << (4 * k)) - 1u);
+    const uint32_t f = (ordN & used) | (0x99999999u & ~used);
+    uint32_t y = prmt_raw(0x10204080u, 0x01020408u, f) | prmt_raw(0x10204080u, 0x01020408u, f >> 16);
+    y |= y >> 16;
+    sel = (y | (y >> 8)) & 0xffu;
+    uint32_t x = (ordN ^ 0x77777777u) & used;
+    x = (x & 0x07070707u) | ((x >> 1) & 0x38383838u);       // two members per byte
+    x = (x & 0x003f003fu) | ((x >> 2) & 0x0fc00fc0u);       // four per halfword
+    order = (x & 0x00000fffu) | ((x >> 4) & 0x00fff000u);
 }
 
 // ---- int32 tier: the lane's matrix column ---------------------------------------------------------
@@ -369,29 +378,28 @@ constexpr uint32_t K1_MODE_PRUNE = 1;    // KGWE_CFG_PRUNE_TIED_STARTS: uniform 
 constexpr uint32_t K1_MODE_MEMO = 2;     // KGWE_CFG_MEMOISE_GROUPS: winners per (node, k) found once per CTA
 
 // The NVLink group search of one lane for group size k (2..8), not exhaustive.  topo = TopologyScore of the
-// winning group, -1 when no start reaches k members.  scored = groups actually grown.
+// winning group, -1 when no start reaches k members; sel / order = its GPUs.  scored = groups actually grown.
 template <bool GENERAL>
 __device__ __forceinline__ void lane_group_search(const LaneNode& ln, const LaneTabs& tb, const DevNode* rec, int k, double norm,
-                                                  uint32_t mode, int& topo, uint32_t& order, uint32_t& scored) {
-    topo = -1; order = 0; scored = 0;
+                                                  uint32_t mode, int& topo, uint32_t& sel, uint32_t& order, uint32_t& scored) {
+    topo = -1; sel = 0; order = 0; scored = 0;
     if (ln.tier == TIER_UNIFORM) {
-        bool found; uint32_t ordR;
-        if (mode == K1_MODE_PRUNE) {
-            found = walk_first(ln.avail, ln.rlo, ln.rhi, k, ordR); scored = 1;
-            if (!found) { walk_all_k(ln.rlo, ln.rhi, k, found, ordR); scored += (uint32_t)ln.A; }
-        } else { walk_all_k(ln.rlo, ln.rhi, k, found, ordR); scored = (uint32_t)ln.A; }
-        if (found) { topo = tb.topo[(k - 2) * tb.stride]; order = order_from_reversed(ordR, k); }
+        bool found = false, all_starts = true; uint32_t ordN = 0;
+        if (mode == K1_MODE_PRUNE) { found = walk_first(ln.avail, ln.rlo, ln.rhi, k, ordN); scored = 1; all_starts = !found; }
+        if (all_starts) { walk_all_k(ln.rlo, ln.rhi, k, found, ordN); scored += (uint32_t)ln.A; }      // (one inlined copy of the walks in the pod loop)
+        order_from_nibbles(ordN, k, sel, order);
+        if (found) topo = tb.topo[(k - 2) * tb.stride];
     } else if (GENERAL && ln.tier == TIER_INT) {
         int32_t key; uint32_t pay;
         chain_int_all_k(tb.mat, tb.stride, ln.avail, k, key, pay); scored = (uint32_t)ln.A;
-        if (key > 0) { topo = nvlink_score((double)(key >> 3), k, norm); order = pay; }
+        if (key > 0) { topo = nvlink_score((double)(key >> 3), k, norm); order = pay; sel = mask_of_order(pay, k); }
     } else if (ln.tier != TIER_NONE) {
         bool found; double total; uint32_t ord;
         const uint64_t colact = ld_u64(rec->act_in);
         if (GENERAL && ln.tier == TIER_F64) chain_f64_all(tb.mat, tb.stride, ln.avail, colact, k, found, total, ord);
         else chain_f64_all_rec(rec, ln.avail, colact, k, found, total, ord);
         scored = (uint32_t)ln.A;
-        if (found) { topo = nvlink_score(total, k, norm); order = ord; }
+        if (found) { topo = nvlink_score(total, k, norm); order = ord; sel = mask_of_order(ord, k); }
     }
 }
 
@@ -401,36 +409,51 @@ __device__ __forceinline__ bool lane_arch_match(const LaneNode& ln, uint32_t arc
     return ((((x - 0x01010101u) & ~x) | ((y - 0x01010101u) & ~y)) & 0x80808080u) != 0u;      // some byte is zero
 }
 
+// One evaluation's result: the 16-byte NodeScore as four words (all zero when the node is not eligible), the
+// arg-max contribution (TotalScore when the evaluation is kept, else 0), and the two candidate counts.
+struct LaneResult {
+    uint32_t w0, w1, w2, w3;       // total | topology, resource << 16 | balance, gpu_mask << 16, flags << 24 | order
+    uint32_t kept_total;           // TotalScore if KGWE_F_KEPT else 0 (kept implies TotalScore > 0)
+    uint32_t candidates, scored;   // reference-semantic count / subsets whose score this call computed
+};
+
 // isNodeEligible + scoreNode (scheduler.go:206-300) for (this lane's node, pod).  `rec` is the node's record in
-// global memory (read only on rare paths: minimum-bandwidth filter, float64 fall-backs).  o.candidates is the
-// reference-semantic count, scored the number of subsets whose score this call computed.
+// global memory (read only on rare paths: minimum-bandwidth filter, float64 fall-backs).
 template <bool GENERAL, bool TABLES>
 __device__ __forceinline__ void lane_evaluate(const LaneNode& ln, const LaneTabs& tb, const DevNode* rec, const PodLite& pd,
-                                              double min_bw, bool hinted, const Params& P, uint32_t mode, EvalOut& o, uint32_t& scored) {
-    o.total = o.topo = o.res = o.bal = 0; o.mask = o.order = o.flags = 0; o.candidates = 1; scored = 1;
-    const int k = pd.k;
+                                              double min_bw, bool hinted, const Params& P, uint32_t mode, LaneResult& r) {
+    r.w0 = r.w1 = r.w2 = r.w3 = 0u; r.kept_total = 0u; r.candidates = 1u; r.scored = 1u;
+    const uint32_t pk = pd.pk;
+    const int k = (int)(pk & 0xffu);
     bool eligible = ln.valid && ln.A >= k;                                            // scheduler.go:213-216
-    if (pd.cls & PL_ARCH) eligible = eligible && lane_arch_match(ln, pd.arch);        // :219-230
-    if (pd.cls & PL_MIG) {                                                            // :233-238
+    if (pk & PL_ARCH) eligible = eligible && lane_arch_match(ln, (pk >> 16) & 0xffu);  // :219-230
+    if (pk & PL_MIG) {                                                                // :233-238
+        const uint32_t prof = pk >> 24;
         int have = 0;
-        if (pd.mig_profile >= 1 && pd.mig_profile <= KGWE_MIG_PROFILES && ln.valid) {
-            const int idx = pd.mig_profile - 1;
+        if (prof >= 1 && prof <= KGWE_MIG_PROFILES && ln.valid) {
+            const uint32_t idx = prof - 1;
             have = (int)((tb.mig[(idx >> 2) * tb.stride] >> (8 * (idx & 3))) & 0xffu);
         }
         eligible = eligible && have >= pd.mig_count;
     }
     if (!eligible) return;
-    int topo = 0, nsel = 0; bool fallback = false; uint32_t sel = 0, order = 0;
+    int topo; uint32_t sel, order, fb = 0;       // fb: KGWE_F_FALLBACK or 0
+    int nsel = k;
+    // first k available GPUs in index order (k = 1 for k <= 1): the fall-back selection of every arm; kk <= A <= 8 (or A = 0: both are 0)
+    const int kk = k < 1 ? 1 : k;
+#define KGWE_SEL_FIRST ((uint32_t)(ln.avail_prefix >> (8 * (kk - 1))) & 0xffu)
+#define KGWE_ORD_FIRST (ln.avail_order & ((1u << (3 * kk)) - 1u))
     if (k <= 1) {                                                                     // :309-315 (k = 0 lands here too)
-        if (ln.A > 0) { topo = 100; sel = (uint32_t)ln.avail_prefix & 0xffu; order = ln.avail_order & 7u; nsel = 1; }
-    } else if (pd.cls & PL_NVLINK) {                                                  // scoreNVLinkTopology, :336-373
+        const bool any = ln.A > 0;
+        topo = any ? 100 : 0; sel = KGWE_SEL_FIRST; order = KGWE_ORD_FIRST; nsel = any ? 1 : 0;
+    } else if (pk & PL_NVLINK) {                                                      // scoreNVLinkTopology, :336-373
         int found_topo = -1;
-        if (pd.cls & PL_EXH) {
-            o.candidates = binom_small(ln.A, k); scored = o.candidates;
+        if (pk & PL_EXH) {
+            r.candidates = binom_small(ln.A, k); r.scored = r.candidates;
             uint32_t bm = 0; double best = 0.0;
             if (TABLES && ln.integral) {
                 uint32_t key = 0;
-                for (int r = subset_off(k); r < subset_off(k + 1); ++r) key = max(key, tb.subset[r * tb.stride]);
+                for (int q = subset_off(k); q < subset_off(k + 1); ++q) key = max(key, tb.subset[q * tb.stride]);
                 if (key) { best = (double)(key >> 8); bm = 255u - (key & 255u); }
             } else {
                 NodeCtx nc; nc.avail = ln.avail; nc.colact = ld_u64(rec->act_in);
@@ -440,56 +463,61 @@ __device__ __forceinline__ void lane_evaluate(const LaneNode& ln, const LaneTabs
                     if (b > best || (b == best && b > 0.0 && m < bm)) { best = b; bm = m; }
                 }
             }
+            sel = 0; order = 0;
             if (best > 0.0) { found_topo = nvlink_score(best, k, P.norm); take_first_k(bm, k, sel, order); }
         } else {
-            o.candidates = (uint32_t)ln.A;
-            if (mode == K1_MODE_MEMO) { const int2 w = tb.memo[(k - 2) * tb.stride]; found_topo = w.x; order = (uint32_t)w.y; scored = 0; }
-            else lane_group_search<GENERAL>(ln, tb, rec, k, P.norm, mode, found_topo, order, scored);
-            if (found_topo >= 0) sel = mask_of_order(order, k);
+            r.candidates = (uint32_t)ln.A;
+            if (mode == K1_MODE_MEMO) {
+                const int2 w = tb.memo[(k - 2) * tb.stride];
+                found_topo = w.x; order = (uint32_t)w.y & 0xffffffu; sel = (uint32_t)w.y >> 24; r.scored = 0;
+            } else lane_group_search<GENERAL>(ln, tb, rec, k, P.norm, mode, found_topo, sel, order, r.scored);
         }
-        if (found_topo < 0) {                                                         // no fully connected group, :358-365
-            topo = 30; fallback = true;
-            sel = (uint32_t)(ln.avail_prefix >> (8 * (k - 1))) & 0xffu; order = ln.avail_order & ((1u << (3 * k)) - 1u); nsel = k;   // first k available; 2 <= k <= A <= 8
-        } else { topo = found_topo; nsel = k; }
-    } else if (pd.cls & (PL_NUMA | PL_PCIE)) {                                        // :438-513
-        const bool numa = pd.cls & PL_NUMA;
+        const bool found = found_topo >= 0;                                            // else no fully connected group, :358-365
+        topo = found_topo;
+        if (!found) { topo = 30; fb = KGWE_F_FALLBACK; sel = KGWE_SEL_FIRST; order = KGWE_ORD_FIRST; }
+    } else if (pk & (PL_NUMA | PL_PCIE)) {                                            // :438-513
+        const bool numa = pk & PL_NUMA;
         const int base = numa ? 0 : 3;
         const uint64_t pick = (uint64_t)tb.grp[base * tb.stride] | ((uint64_t)tb.grp[(base + 1) * tb.stride] << 32);
         const uint32_t gorder = tb.grp[(base + 2) * tb.stride];
         const uint32_t grp = (uint32_t)((pick >> (8 * (k - 1))) & 0xff);              // 2 <= k <= A <= 8 here
-        if (grp) { topo = numa ? 90 : 80; take_first_k(grp, k, sel, order); nsel = k; }
+        if (grp) { topo = numa ? 90 : 80; take_first_k(grp, k, sel, order); }
         else {
-            topo = numa ? 50 : 40; fallback = true;
-            order = gorder & ((k >= 8) ? 0xffffffu : ((1u << (3 * k)) - 1u));
-            sel = mask_of_order(order, k); nsel = k;
+            topo = numa ? 50 : 40; fb = KGWE_F_FALLBACK;
+            order = gorder & ((1u << (3 * k)) - 1u);
+            sel = mask_of_order(order, k);
         }
     } else {                                                                          // :325-331
-        topo = 50;
-        sel = (uint32_t)(ln.avail_prefix >> (8 * (k - 1))) & 0xffu; order = ln.avail_order & ((1u << (3 * k)) - 1u); nsel = k;
+        topo = 50; sel = KGWE_SEL_FIRST; order = KGWE_ORD_FIRST;
     }
+#undef KGWE_SEL_FIRST
+#undef KGWE_ORD_FIRST
     int res = 0;                                                                      // calculateResourceScore, :516-553
     if (ln.A > 0) {
         res = 50 + (ln.sum_free >= pd.required * 2 ? 25 : (ln.sum_free >= pd.required ? 10 : 0)) + ln.util_bonus;
         res = res > 100 ? 100 : res;
     }
     int total = (topo * P.wt + res * P.wr + ln.balance * P.wb) / 100;                 // :282-286
-    uint32_t flags = KGWE_F_ELIGIBLE;
+    uint32_t flags = KGWE_F_ELIGIBLE | fb;
     if (hinted) { total += P.bonus; flags |= KGWE_F_HINT; }
     bool kept = total > 0;                                                            // :196
-    if (fallback) flags |= KGWE_F_FALLBACK;
-    if ((pd.cls & PL_MINBW) && kept && est_bandwidth(rec, order, nsel) < min_bw) { kept = false; flags |= KGWE_F_MINBW; }      // E3
+    if ((pk & PL_MINBW) && kept && est_bandwidth(rec, order, nsel) < min_bw) { kept = false; flags |= KGWE_F_MINBW; }      // E3
     if (kept) flags |= KGWE_F_KEPT;
-    o.total = total; o.topo = topo; o.res = res; o.bal = ln.balance;
-    o.mask = sel; o.order = order | ((uint32_t)nsel << 24); o.flags = flags;
+    r.w0 = (uint32_t)total;
+    r.w1 = ((uint32_t)topo & 0xffffu) | ((uint32_t)res << 16);
+    r.w2 = (uint32_t)ln.balance | (sel << 16) | (flags << 24);
+    r.w3 = order | ((uint32_t)nsel << 24);
+    r.kept_total = kept ? (uint32_t)total : 0u;
 }
 
-// Memoised winners of this lane's node for k = 2..8 (K1_MODE_MEMO), by the full search.
+// Memoised winners of this lane's node for k = 2..8 (K1_MODE_MEMO), by the full search: (TopologyScore or -1,
+// join order | GPU set << 24).
 template <bool GENERAL>
-__device__ inline void lane_memo_build(const LaneNode& ln, const LaneTabs& tb, const DevNode* rec, double norm) {
+__device__ __noinline__ void lane_memo_build(const LaneNode& ln, const LaneTabs& tb, const DevNode* rec, double norm) {
     for (int k = 2; k <= 8; ++k) {
-        int topo = -1; uint32_t order = 0, sc = 0;
-        if (ln.valid && ln.A >= k) lane_group_search<GENERAL>(ln, tb, rec, k, norm, K1_MODE_FULL, topo, order, sc);
-        tb.memo[(k - 2) * tb.stride] = make_int2(topo, (int)order);
+        int topo = -1; uint32_t sel = 0, order = 0, sc = 0;
+        if (ln.valid && ln.A >= k) lane_group_search<GENERAL>(ln, tb, rec, k, norm, K1_MODE_FULL, topo, sel, order, sc);
+        tb.memo[(k - 2) * tb.stride] = make_int2(topo, (int)(order | (sel << 24)));
     }
 }
 

@@ -32,8 +32,8 @@ struct FusedTail { kgwe_placement* out; unsigned int* done; unsigned int* flag; 
 struct K1Layout { uint32_t pods, keys, topo, grp, mig, memo, mat, subset, slot, total; };
 __host__ __device__ inline K1Layout k1_layout(uint32_t ppc, bool general, bool tables, bool memo) {
     K1Layout L; uint32_t o = 0;
-    L.pods = o; o += ppc * 16u;
-    L.keys = o; o += ((ppc * 4u) + 15u) & ~15u;
+    L.pods = o; o += (ppc + 1u) * 16u;                              // + one slot: the loop prefetches pod i + 1
+    L.keys = o; o += ((ppc * 4u * (K1_THREADS / 32)) + 15u) & ~15u;    // one arg-max row per warp (plain stores, no atomics)
     L.mat = o; o += general ? 32u * K1_TILE * 16u : 0u;
     L.memo = o; o += memo ? 7u * K1_TILE * 8u : 0u;
     L.topo = o; o += 7u * K1_TILE * 4u;
@@ -46,7 +46,7 @@ __host__ __device__ inline K1Layout k1_layout(uint32_t ppc, bool general, bool t
 }
 
 template <bool GENERAL, bool TABLES>
-__global__ void __launch_bounds__(K1_THREADS, TABLES ? 1 : (GENERAL ? 2 : 4))
+__global__ void __launch_bounds__(K1_THREADS, TABLES ? 1 : (GENERAL ? 2 : 5))
 score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
              const kgwe_pod_req* __restrict__ pods, uint32_t n_pods, uint32_t pods_per_chunk,
              const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
@@ -69,14 +69,14 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     const kgwe_pod_req* spods = tail.n_inline ? inline_copy : nullptr;
     if (tail.n_inline) __syncthreads();
 
-    // ---- set-up 1: pod chunk -> PodLite; arg-max table cleared ----
+    // ---- set-up 1: pod chunk -> PodLite ----
     bool want_groups = false;
     for (uint32_t i = tid; i < np; i += K1_THREADS) {
         const kgwe_pod_req pod = load_pod2(pods, spods, p_begin + i);
         const PodLite pl = pod_lite(pod);
         spod[i] = pl;
-        want_groups |= (pl.cls & (PL_NUMA | PL_PCIE)) != 0;      // the group tables are only worth building when a pod asks for them
-        keys[i] = 0u;
+        if (i == np - 1) spod[np] = pl;
+        want_groups |= (pl.pk & (PL_NUMA | PL_PCIE)) != 0;      // the group tables are only worth building when a pod asks for them
     }
     if (TABLES)      // slot of mask m in (popcount, value) order
         for (int m = tid; m < 256; m += K1_THREADS) {
@@ -110,30 +110,37 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
 
     // ---- the pod loop: every warp scores all pods of the chunk against its 32 nodes ----
     uint32_t cnt_scored = 0, cnt_resolved = 0;
-    kgwe_node_score* outp = out ? out + (size_t)p_begin * n_nodes + node : nullptr;
-    const uint8_t* hintp = hint ? hint + (size_t)p_begin * hint_row_bytes + (node >> 3) : nullptr;
+    const bool has_hint = hint != nullptr, has_best = best != nullptr;
+    const uint32_t do_store = (out != nullptr && in_range) ? 1u : 0u, live = in_range ? 0xffffffffu : 0u;
+    int4* outp = reinterpret_cast<int4*>(out) + ((size_t)p_begin * n_nodes + node);              // only dereferenced when do_store
+    const uint8_t* hintp = hint + ((size_t)p_begin * hint_row_bytes + (node >> 3));               // only dereferenced when has_hint && in_range
+    const uint32_t key_low = (uint32_t)(K1_TILE - 1 - tid);
+    uint32_t pod_addr = (uint32_t)__cvta_generic_to_shared(spod);
+    uint32_t key_addr = (uint32_t)__cvta_generic_to_shared(keys) + (uint32_t)(tid >> 5) * pods_per_chunk * 4u;      // this warp's row
     PodLite pd = spod[0];
 #pragma unroll 1
     for (uint32_t i = 0; i < np; ++i) {
-        const PodLite next = spod[i + 1 < np ? i + 1 : i];
-        double min_bw = 0.0;
-        if (pd.cls & PL_MINBW) min_bw = spods ? spods[p_begin + i].min_bandwidth_gbps : __ldg(&pods[p_begin + i].min_bandwidth_gbps);
-        bool hinted = false;
-        if (hintp) { hinted = in_range && ((__ldg(hintp) >> (node & 7)) & 1); hintp += hint_row_bytes; }
-        EvalOut o; uint32_t scored;
-        lane_evaluate<GENERAL, TABLES>(ln, tb, rec, pd, min_bw, hinted, P, mode, o, scored);
-        if (in_range) {
-            cnt_scored += scored; cnt_resolved += o.candidates;
-            if (outp) {
-                const kgwe_node_score r = to_record(o);
-                *reinterpret_cast<int4*>(outp) = *reinterpret_cast<const int4*>(&r);
-            }
+        PodLite next;      // pod i + 1 (slot np repeats the last pod), straight from the shared window
+        {
+            uint32_t a0, a1, a2, a3;
+            pod_addr += 16u;
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(a0), "=r"(a1), "=r"(a2), "=r"(a3) : "r"(pod_addr));
+            next.required = ((uint64_t)a1 << 32) | a0; next.mig_count = (int32_t)a2; next.pk = a3;
         }
-        if (outp) outp += n_nodes;
-        if (best) {
-            uint32_t key = (o.flags & KGWE_F_KEPT) ? (((uint32_t)o.total << 7) | (uint32_t)(K1_TILE - 1 - tid)) : 0u;
-            key = __reduce_max_sync(0xffffffffu, key);
-            if (lane == 0 && key) atomicMax(&keys[i], key);
+        double min_bw = 0.0;
+        if (pd.pk & PL_MINBW) min_bw = spods ? spods[p_begin + i].min_bandwidth_gbps : __ldg(&pods[p_begin + i].min_bandwidth_gbps);
+        bool hinted = false;
+        if (has_hint) { hinted = in_range && ((__ldg(hintp) >> (node & 7)) & 1); hintp += hint_row_bytes; }
+        LaneResult r;
+        lane_evaluate<GENERAL, TABLES>(ln, tb, rec, pd, min_bw, hinted, P, mode, r);
+        cnt_scored += r.scored & live; cnt_resolved += r.candidates & live;
+        if (do_store) *outp = make_int4((int)r.w0, (int)r.w1, (int)r.w2, (int)r.w3);
+        outp += n_nodes;
+        if (has_best) {
+            // kept evaluations have TotalScore > 0, so key > 0 exactly when one of the 32 nodes is kept
+            const uint32_t key = __reduce_max_sync(0xffffffffu, r.kept_total ? ((r.kept_total << 7) | key_low) : 0u);
+            if (lane == 0) asm volatile("st.shared.u32 [%0], %1;" ::"r"(key_addr), "r"(key) : "memory");
+            key_addr += 4u;
         }
         pd = next;
     }
@@ -147,7 +154,9 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     if (best) {
         __syncthreads();
         for (uint32_t i = tid; i < np; i += K1_THREADS) {
-            const uint32_t kk = keys[i];
+            uint32_t kk = keys[i];
+#pragma unroll
+            for (int w = 1; w < K1_THREADS / 32; ++w) kk = max(kk, keys[w * pods_per_chunk + i]);
             if (kk) atomicMax(&best[p_begin + i], rank_key((int32_t)(kk >> 7), P.node_base + tile_first + ((uint32_t)(K1_TILE - 1) - (kk & 127u))));
         }
     }

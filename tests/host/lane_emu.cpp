@@ -15,6 +15,7 @@
 #include <cuda_runtime.h>      // vector types only (int4, double2, make_int4 ...); __device__ expands to nothing under g++
 
 // ---- host stand-ins for the device intrinsics used by kgwe_device.cuh / kgwe_lane.cuh ----
+#define __noinline__ __attribute__((noinline))
 static inline int __popc(unsigned x) { return __builtin_popcount(x); }
 static inline int __ffs(int x) { return __builtin_ffs(x); }
 static inline int __clz(int x) { return x ? __builtin_clz((unsigned)x) : 32; }
@@ -89,13 +90,17 @@ extern "C" int lane_emu_score_batch(const kgwe_config* cfg, const kgwe_node_imag
         else lane_tables_build<false, false>(ln, c, tb, rec, P.norm, mode, slot_of);
         for (uint32_t p = 0; p < n_pods; ++p) {
             const bool hinted = hint && ((hint[(size_t)p * row_bytes + (n >> 3)] >> (n & 7)) & 1);
-            EvalOut o; uint32_t scored = 0;
+            LaneResult r;
             const double min_bw = pods[p].min_bandwidth_gbps;
-            if (tables) lane_evaluate<true, true>(ln, tb, rec, pl[p], min_bw, hinted, P, mode, o, scored);
-            else if (general) lane_evaluate<true, false>(ln, tb, rec, pl[p], min_bw, hinted, P, mode, o, scored);
-            else lane_evaluate<false, false>(ln, tb, rec, pl[p], min_bw, hinted, P, mode, o, scored);
-            out[(size_t)p * n_nodes + n] = to_record(o);
-            scored_sum += scored; resolved_sum += o.candidates;
+            if (tables) lane_evaluate<true, true>(ln, tb, rec, pl[p], min_bw, hinted, P, mode, r);
+            else if (general) lane_evaluate<true, false>(ln, tb, rec, pl[p], min_bw, hinted, P, mode, r);
+            else lane_evaluate<false, false>(ln, tb, rec, pl[p], min_bw, hinted, P, mode, r);
+            const uint32_t w[4] = {r.w0, r.w1, r.w2, r.w3};
+            memcpy(&out[(size_t)p * n_nodes + n], w, 16);
+            // the arg-max contribution must be TotalScore exactly for kept evaluations
+            const kgwe_node_score& rec16 = out[(size_t)p * n_nodes + n];
+            if (((rec16.flags & KGWE_F_KEPT) ? (uint32_t)rec16.total : 0u) != r.kept_total) return -3;
+            scored_sum += r.scored; resolved_sum += r.candidates;
         }
     }
     if (scored_out) *scored_out = scored_sum;
