@@ -5,21 +5,32 @@ Workload (config.workload): configs[2], the 10,000-node x 8-GPU mixed cluster wi
 10,000-pod burst, reference greedy subset scoring (NVLinkOptimal, k ~ U{1..8}), 30% of the
 nodes pre-allocated.  One "step" = one stateless Filter+Prioritize pass of ALL pods over
 ALL nodes (scoreNodes per pod, reference src/scheduler/scheduler.go:182-203) producing the
-full P x N NodeScore matrix in HBM plus the best placement per pod.
+full P x N NodeScore matrix in HBM plus the best placement per pod.  Every available start
+GPU of every node grows its own group for every (pod, node), as findBestNVLinkGroup does
+(:389): `value` counts candidates whose score was computed, nothing shared between pods.
 
   value     device-resident: pods and outputs already in HBM (kgwe_score_batch_device).
-  e2e       the reference-facing C-ABI call kgwe_score_batch with HOST buffers: pod
-            descriptors copied host->device and the per-pod best placement copied
-            device->host inside the timed region, every step.
-  roofline  the scoring kernel (K1) alone: algorithmic bytes (784 B per (pod,node)
-            evaluation) / its CUDA-event duration, vs the measured HBM peak.
+  e2e       1 GPU: the reference-facing C-ABI call kgwe_score_batch with HOST buffers (pod
+            descriptors copied host->device, the per-pod best placement device->host, inside
+            the timed region, every step).  N GPUs: pods from pinned host memory -> device,
+            the sharded step with its exchange, merged placements -> pinned host memory.
+  parity    outside the timed region, every run: the merged placements of every 97th pod and
+            this rank's slice of their score-matrix rows against the CPU oracle (indexed
+            build), and a CRC-32 of ALL merged placements - the same at 1, 2, 4 and 8 GPUs.
+            A mismatch makes the run exit non-zero.
+  roofline  the scoring kernel (K1) alone.  The bound that holds is instruction issue: warp
+            instructions per evaluation (this round's ncu capture) x evaluations / K1's
+            CUDA-event time against SMs x 4 schedulers x the sampled SM clock.  The
+            algorithmic-HBM figure of SURVEY.md 8d (784 B per evaluation) and the real DRAM
+            fraction are carried beside it.
   cpu_baseline / --impl reference
             the faithful CPU restatement of the reference scorer (oracle/, the Go
             toolchain is absent) on a bounded sample of the same workload, all host cores.
 
 N > 1 (torchrun): nodes are sharded by contiguous index range over the ranks (SURVEY.md
-8e), each rank scores all pods against its shard, local top-1 lists are all-gathered over
-NCCL and merged on every rank.  Total work is fixed => "scaling": "strong".
+8e), each rank scores all pods against its shard, local top-1 records are exchanged (P2P
+stores over NVLink, or an NCCL all-gather) and merged on every rank.  Total work is fixed
+=> "scaling": "strong".
 """
 import argparse
 import json
@@ -28,6 +39,7 @@ import subprocess
 import sys
 import tempfile
 import time
+import zlib
 
 import numpy as np
 
@@ -39,6 +51,7 @@ BYTES_PER_EVAL = 784            # 768 B node record read + 16 B NodeScore writte
 METRIC = "placement_candidates_scored_per_sec"
 UNIT = "candidates/s"
 WORKLOAD = "BASELINE configs[2]: 10,000-node x 8-GPU mixed H100/A100/B200 cluster, 10,000-pod burst, greedy k-of-8 subset scoring (NVLinkOptimal, k~U{1..8}), 30% nodes pre-allocated"
+SEARCH = "greedy, every available start GPU grows its group per (pod,node) - the reference's search, nothing shared between pods"
 
 
 def parse():
@@ -49,30 +62,24 @@ def parse():
     ap.add_argument("--impl", default="kgwe", choices=["kgwe", "reference"])
     ap.add_argument("--scale", type=float, default=1.0, help="shrink N and P (testing only; the default is the full config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the side measurements (latency, queue, extensions, other configs)")
     ap.add_argument("--weak", action="store_true", help="weak scaling: 10,000 nodes PER GPU (a larger cluster than the named config; not the default)")
     ap.add_argument("--kernel-only", action="store_true", help="only the device-resident steps (for ncu runs; prints no bench value)")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the bounded cpu_baseline sample")
     return ap.parse_args()
 
 
-def measured_limits(n_gpus, scale):
-    """What actually bounds K1 according to the committed ncu capture (single-GPU full-size workload only)."""
+def shared_config(nodes, pods, ledger):
+    """The part of `config` both arms print, so the driver can see they ran the same workload."""
+    return {"workload": WORKLOAD, "n_nodes": int(len(nodes)), "n_pods": int(len(pods)), "ledger_entries": int(len(ledger)), "search": SEARCH}
+
+
+def profile_facts(n_gpus, scale):
+    """What the committed ncu capture of this round says about K1 (single-GPU full-size workload only)."""
     try:
         t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["score_kernel"]
         if n_gpus == t["n_gpus"] and scale == 1.0:
-            return {k: t[k] for k in ("warp_instructions_per_evaluation", "issue_active_pct", "shared_data_pipe_pct", "alu_pipe_pct", "note")}
-    except Exception:
-        pass
-    return None
-
-
-def measured_traffic(n_gpus, scale):
-    """DRAM bytes per score_kernel launch from the committed ncu --set full capture (profiles/traffic.json),
-    valid for the full-size single-GPU workload only."""
-    try:
-        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["score_kernel"]
-        if n_gpus == t["n_gpus"] and scale == 1.0:
-            return float(t["dram_bytes_per_launch"])
+            return t
     except Exception:
         pass
     return None
@@ -134,7 +141,7 @@ class ClockSampler:
 
 def uniform_nodes(nodes):
     """How many records take K1's bit-set walk: all ACTIVE links of the node carry the same bandwidth > 0
-    (mirrors set_uniform_unit in csrc/kgwe_engine.cu)."""
+    (mirrors set_uniform_unit in csrc/kgwe_pack.hpp)."""
     bw = nodes["nvl_bw"]                                      # [N, i, j]: i's link to j
     bits = (1 << np.arange(8)).astype(np.uint8)
     ng = np.arange(8)[None, :] < nodes["n_gpus"][:, None]
@@ -186,24 +193,36 @@ def run_reference(args):
     for w in range(args.warmup):
         orc.score_batch(kg.abi, nodes, ledger, pods[w * n % len(pods):][:n], want_scores=False, topk=1, mode=orc.FAITHFUL, threads=cores)
     cand = ev = 0
-    secs = 0.0
     t0 = time.time()
     for s in range(args.steps):
         off = (s * n) % max(1, len(pods) - n + 1)
         _, _, c = orc.score_batch(kg.abi, nodes, ledger, pods[off:off + n], want_scores=False, topk=1, mode=orc.FAITHFUL, threads=cores)
-        cand += c["candidates"]; ev += c["evaluations"]; secs += c["seconds"]
+        cand += c["candidates"]; ev += c["evaluations"]
     wall = time.time() - t0
     v = cand / wall
-    sample = f"{n} pods x {len(nodes)} nodes per step ({n * len(nodes)} evaluations), ledger {len(ledger)} entries, {cores} threads"
+    sample = f"{n} pods x {len(nodes)} nodes per step ({n * len(nodes)} evaluations, a bounded sample of the {len(pods)}-pod burst: the metric is a rate), ledger {len(ledger)} entries, {cores} threads"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": wall / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "config": {"workload": WORKLOAD, "n_nodes": len(nodes), "n_pods": len(pods), "sample_per_step": sample},
+        "data": "synthetic", "config": shared_config(nodes, pods, ledger), "sample_per_step": sample,
         "evaluations_per_sec": ev / wall,
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
                          "note": "faithful C++ restatement of scheduler.go:182-707 (Go toolchain absent); likely faster than Go"},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+def timed_device_loop(torch, stream, fn, reps, warm=2):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record(stream)
+    for _ in range(reps):
+        fn()
+    b.record(stream)
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps
 
 
 def run_kgwe(args):
@@ -225,6 +244,7 @@ def run_kgwe(args):
         dist.barrier()
     kg = kg or entry.load_package()
     abi = kg.abi
+    from oracle import binding as orc          # the checker of the parity block / the timed CPU baseline, never the measured path
 
     nodes, pods, ledger = kg.synth.config(3, args.scale)
     if args.weak and world > 1:
@@ -242,7 +262,8 @@ def run_kgwe(args):
     torch.cuda.set_stream(stream)
     sptr = stream.cuda_stream
     assert sptr != 0
-    d_pods = torch.from_numpy(pods.view(np.uint8).reshape(P, abi.POD_REQ.itemsize)).to(dev)
+    h_pods = torch.from_numpy(pods.view(np.uint8).reshape(P, abi.POD_REQ.itemsize).copy()).pin_memory()
+    d_pods = h_pods.to(dev)
     scorer = kg.sharded.ShardedScorer(eng, n_local, world, dist if world > 1 else None, sptr, rank=rank)
     scorer.alloc(torch, dev, P, 1, with_matrix=True)
     exchange = "none (1 GPU)"
@@ -254,7 +275,7 @@ def run_kgwe(args):
             scorer.p2p = None
         exchange = ("P2P stores from the finalisation kernel into every rank's gather buffer (symmetric memory) + one cross-GPU barrier"
                     if scorer.p2p is not None else "NCCL all_gather of the local top-1 lists")
-    d_gather, d_merged = scorer.d_gather, scorer.d_merged
+    d_merged = scorer.d_merged
     flush = torch.empty(160 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
 
     def step_device():
@@ -298,12 +319,11 @@ def run_kgwe(args):
     ms_total = float(t.item())
 
     # whole-job units: every rank scored P pods x its shard
-    cand_local = st1["candidates"] - st0["candidates"]
-    ev_local = st1["evaluations"] - st0["evaluations"]
-    tot = torch.tensor([cand_local, ev_local, st1["kernel_launches"] - st0["kernel_launches"]], dtype=torch.float64, device=dev)
+    tot = torch.tensor([st1["candidates"] - st0["candidates"], st1["evaluations"] - st0["evaluations"], st1["kernel_launches"] - st0["kernel_launches"],
+                        st1["candidates_resolved"] - st0["candidates_resolved"]], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    cand_total, ev_total, launches = (float(x) for x in tot.tolist())
+    cand_total, ev_total, launches, resolved_total = (float(x) for x in tot.tolist())
     # K1 alone (events recorded by the engine on the launching stream, rank 0's shard)
     k1_ms = (st1["score_kernel_ms"] - st0["score_kernel_ms"]) / max(1, st1["score_kernel_timed"] - st0["score_kernel_timed"])
     k1_evals = P * n_local
@@ -313,36 +333,179 @@ def run_kgwe(args):
         eng.close()
         return
 
-    # ---- e2e through the host-buffer C ABI: H2D pods + D2H best placement per pod, every step ----
+    # the L2 flush alone (a bench artefact that does not shrink with the number of GPUs), for ms_per_step_excl_flush
+    flush_ms = timed_device_loop(torch, stream, lambda: flush.zero_(), 50)
+
+    # ---- parity, outside the timed region: sampled pods against the oracle + a digest of ALL merged placements ----
+    torch.cuda.synchronize()
+    merged = d_merged.cpu().numpy().view(abi.PLACEMENT).reshape(P)
+    digest = zlib.crc32(merged.tobytes()) & 0xFFFFFFFF
+    sample = np.arange(0, P, 97)
+    o_scores, o_top, _ = orc.score_batch(abi, nodes, ledger, pods[sample], want_scores=True, topk=1, threads=min(8, host_cores()))
+    mism = int((merged[sample].view(np.uint8).reshape(len(sample), -1) != o_top.reshape(len(sample)).view(np.uint8).reshape(len(sample), -1)).any(axis=1).sum())
+    idx = torch.from_numpy(sample).to(dev)
+    rows = scorer.d_scores.index_select(0, idx).cpu().numpy().view(abi.NODE_SCORE).reshape(len(sample), n_local)
+    want_rows = np.ascontiguousarray(o_scores[:, lo:hi])
+    mism_rows = int((rows.view(np.uint8).reshape(len(sample), -1) != want_rows.view(np.uint8).reshape(len(sample), -1)).any(axis=1).sum())
+    par = torch.tensor([mism, mism_rows], dtype=torch.int64, device=dev)
+    dg = torch.tensor([digest, -digest], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(par, op=dist.ReduceOp.SUM)
+        dist.all_reduce(dg, op=dist.ReduceOp.MAX)                  # max(d) and max(-d) = -min(d)
+    digests_agree = bool(int(dg[0].item()) == -int(dg[1].item()))
+    parity = {"pods_checked": int(len(sample)), "placement_mismatches": int(par[0].item()) // world, "matrix_row_mismatches": int(par[1].item()),
+              "mismatches": int(par[0].item()) // world + int(par[1].item()) + (0 if digests_agree else 1),
+              "digest": f"crc32:{digest:08x}", "digest_of": f"all {P} merged placements (32 B each); identical on every rank: {digests_agree}",
+              "checker": "oracle/ indexed build: merged top-1 of every 97th pod + each rank's slice of those pods' score-matrix rows, byte for byte"}
+
+    # ---- e2e: inputs from HOST memory and the result back on the host, every step ----
     h2d = P * abi.POD_REQ.itemsize
     d2h = P * abi.PLACEMENT.itemsize
-    for _ in range(2):
-        eng.score_batch(pods, n_local, want_scores=False, topk=1)
-    fence()
-    c0 = eng.stats()["candidates"]
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        _, top = eng.score_batch(pods, n_local, want_scores=False, topk=1)
-        if world > 1:
-            g = torch.from_numpy(top.view(np.uint8).reshape(P, 1, abi.PLACEMENT.itemsize)).to(dev, non_blocking=True)
-            dist.all_gather_into_tensor(d_gather, g)
-            eng.topk_merge_device(d_gather.data_ptr(), world, P, 1, d_merged.data_ptr(), sptr)
-            _ = d_merged.cpu()
-    fence()
-    e2e_s = time.perf_counter() - t0
+    if world == 1:
+        for _ in range(2):
+            eng.score_batch(pods, n_local, want_scores=False, topk=1)
+        fence()
+        c0 = eng.stats()["candidates"]
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            _, top = eng.score_batch(pods, n_local, want_scores=False, topk=1)
+        fence()
+        e2e_s = time.perf_counter() - t0
+        e2e_cand = float(eng.stats()["candidates"] - c0)
+        e2e_call = "kgwe_score_batch(host pods, topk=1 -> host placements)"
+        e2e_ok = top.reshape(P).tobytes() == merged.tobytes()
+    else:
+        h_out = torch.empty((P, abi.PLACEMENT.itemsize), dtype=torch.uint8).pin_memory()
+        d_in = torch.empty_like(d_pods)
+
+        def step_e2e():
+            d_in.copy_(h_pods, non_blocking=True)                       # pods from pinned host memory
+            m = scorer.step(d_in)                                        # sharded scoring + exchange + merge, device-resident
+            h_out.copy_(m.view(P, abi.PLACEMENT.itemsize), non_blocking=True)
+            stream.synchronize()                                         # the caller has its placements
+        for _ in range(2):
+            step_e2e()
+        fence()
+        c0 = eng.stats()["candidates"]
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_e2e()
+        fence()
+        e2e_s = time.perf_counter() - t0
+        e2e_cand = float(eng.stats()["candidates"] - c0)
+        e2e_call = "pinned host pods -> device, ShardedScorer.step (kgwe_score_batch_device_p2p + merge), merged placements -> pinned host"
+        e2e_ok = h_out.numpy().tobytes() == merged.tobytes()
     t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-    c = torch.tensor([eng.stats()["candidates"] - c0], dtype=torch.float64, device=dev)
+    c = torch.tensor([e2e_cand], dtype=torch.float64, device=dev)
+    okt = torch.tensor([1 if e2e_ok else 0], device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(c, op=dist.ReduceOp.SUM)
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
     e2e_value = float(c.item()) / float(t.item())
+    if int(okt.item()) == 0:
+        parity["mismatches"] += 1
+        parity["e2e_placements_differ"] = True
 
-    # ---- per-pod Prioritize latency vs node count: one kgwe_score_batch(P=1) C-ABI call per pod (N=1 only) ----
-    lat = None
+    extras = {}
+    if not args.no_extras:
+        extras = side_measurements(args, torch, dist, kg, orc, eng, scorer, stream, dev, local_rank, world, rank, nodes, pods, ledger, lo, hi, d_pods)
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        facts = profile_facts(world, args.scale)
+        algorithmic = k1_evals * BYTES_PER_EVAL / (k1_ms * 1e-3) / 1e9
+        sms = torch.cuda.get_device_properties(0).multi_processor_count
+        roof = {"kernel": "kgwe::score_kernel", "ms_per_launch": k1_ms, "evaluations_per_launch": k1_evals,
+                "hbm_algorithmic": {"bound": "hbm", "achieved": algorithmic, "peak": peak, "unit": "GB/s", "frac": algorithmic / peak, "bytes_per_evaluation": BYTES_PER_EVAL,
+                                    "peak_source": peak_src,
+                                    "note": "SURVEY 8d's figure: 768 B record + 16 B score per evaluation.  The image is read once per CTA and kept in registers, so this is not what memory sees and a value above 1 is expected"}}
+        if facts and clk.get("sm_mhz"):
+            issued = facts["warp_instructions_per_evaluation"] * k1_evals / (k1_ms * 1e-3)
+            slots = sms * 4 * clk["sm_mhz"] * 1e6
+            traffic = float(facts["dram_bytes_per_launch"])
+            roof.update({"bound": "issue", "achieved": issued / 1e9, "peak": slots / 1e9, "unit": "G warp-instructions/s", "frac": issued / slots,
+                         "traffic": traffic, "traffic_unit": "bytes of DRAM read+write per launch (ncu --set full, profiles/traffic.json)",
+                         "dram_actual_frac": traffic / (k1_ms * 1e-3) / 1e9 / peak,
+                         "warp_instructions_per_evaluation": facts["warp_instructions_per_evaluation"], "capture": facts.get("source"),
+                         "pipes": {k: facts[k] for k in ("issue_active_pct", "alu_pipe_pct", "xu_pipe_pct", "fma_pipe_pct", "lsu_pipe_pct") if k in facts},
+                         "note": "the bound that holds: instruction issue (SMs x 4 schedulers x sampled SM clock).  DRAM carries only the score matrix; see dram_actual_frac"})
+        else:
+            roof.update({"bound": "hbm", "achieved": algorithmic, "peak": peak, "unit": "GB/s", "frac": algorithmic / peak, "traffic": None,
+                         "note": "no ncu capture committed for this GPU count / scale: only the algorithmic figure is available"})
+        out = {
+            "metric": METRIC, "value": cand_total / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak" if (args.weak and world > 1) else "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": shared_config(nodes, pods, ledger),
+            "run": {"sharding": f"nodes by contiguous range over {world} rank(s)", "exchange": exchange,
+                    "l2": "160 MiB buffer written between steps (inside the timed region); each step also writes its P x N_local x 16 B score matrix (1.6 GB at 1 GPU, 200 MB at 8), both larger than the 126 MB L2",
+                    "flush_ms_per_step": flush_ms, "ms_per_step_excl_flush": ms_total / args.steps - flush_ms,
+                    "value_excl_flush": cand_total / args.steps / ((ms_total / args.steps - flush_ms) * 1e-3)},
+            "evaluations_per_sec": ev_total / (ms_total * 1e-3),
+            "candidates_per_step": cand_total / args.steps,
+            "candidates_resolved_per_step": resolved_total / args.steps,
+            "counting": "value counts candidates whose score was computed (kgwe_stats.candidates): one group grown per available start GPU per NVLink evaluation, 1 otherwise. "
+                        "candidates_resolved is the reference's counting rule (SURVEY 8d); the two are equal in this mode",
+            "parity": parity,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "call": e2e_call},
+            "gpu_launches": int(launches),
+            "roofline": roof,
+            "clocks": clk,
+        }
+        out.update(extras)
+        if not args.no_cpu_baseline and world == 1:
+            entry.build_oracle()
+            cores = host_cores()
+            r = cpu_reference_rate(kg, nodes, ledger, pods, args.cpu_seconds, cores)
+            out["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": cores, "kind": "port",
+                                   "sample": f"{r['pods']} pods x {N} nodes ({r['pods'] * N} evaluations, {r['seconds']:.1f} s), ledger {len(ledger)} entries",
+                                   "evaluations_per_sec": r["evals_per_s"],
+                                   "note": "faithful C++ restatement of scheduler.go:182-707 (Go toolchain absent); likely faster than Go"}
+            r2 = cpu_reference_rate(kg, nodes, ledger, pods, min(args.cpu_seconds, 5.0), cores, mode=orc.INDEXED)
+            out["cpu_baseline_indexed"] = {"value": r2["value"], "unit": UNIT, "cores": cores, "kind": "port-optimised",
+                                           "sample": f"{r2['pods']} pods x {N} nodes ({r2['seconds']:.1f} s)", "evaluations_per_sec": r2["evals_per_s"],
+                                           "note": "same results on dense arrays and per-node masks (no ledger scans, no string maps): a CPU upper bound, not the reference's algorithmic cost"}
+        print(json.dumps(out))
+    eng.close()
+    bad = parity["mismatches"]
+    if world > 1:
+        dist.destroy_process_group()
+    if bad:
+        sys.exit(3)
+
+
+def side_measurements(args, torch, dist, kg, orc, eng, scorer, stream, dev, local_rank, world, rank, nodes, pods, ledger, lo, hi, d_pods):
+    """Everything reported beside the headline: latency, the other search modes and link tiers, the stateful queue,
+    the extensions, and the other BASELINE configs (timed, with their own parity checks)."""
+    abi = kg.abi
+    N, P, n_local = len(nodes), len(pods), hi - lo
+    sptr = stream.cuda_stream
+    out = {}
+
     if world == 1:
-        def measure(engine, n_here, calls=3000, warm=300):
-            # the raw C-ABI call on preallocated host buffers (no numpy allocation in the timed part)
-            fn, h = engine.lib.kgwe_score_batch, engine.h
+        # ---- Prioritize-shaped e2e: the P x N score matrix back on the host (what the extender's Prioritize verb returns) ----
+        np_pr = min(P, 1000)
+        h_scores = torch.empty((np_pr, n_local, abi.NODE_SCORE.itemsize), dtype=torch.uint8).pin_memory()
+        fn, h = eng.lib.kgwe_score_batch, eng.h
+        pr_pods = np.ascontiguousarray(pods[:np_pr])
+        for _ in range(2):
+            assert fn(h, pr_pods.ctypes.data, np_pr, None, h_scores.data_ptr(), 0, None) == 0
+        c0 = eng.stats()["candidates"]
+        t0 = time.perf_counter()
+        reps = 5
+        for _ in range(reps):
+            assert fn(h, pr_pods.ctypes.data, np_pr, None, h_scores.data_ptr(), 0, None) == 0
+        dt = (time.perf_counter() - t0) / reps
+        d2h_b = np_pr * n_local * abi.NODE_SCORE.itemsize
+        out["e2e_prioritize"] = {"value": (eng.stats()["candidates"] - c0) / reps / dt, "unit": UNIT, "pods": np_pr, "ms_per_call": dt * 1e3,
+                                 "h2d_bytes_per_call": np_pr * abi.POD_REQ.itemsize, "d2h_bytes_per_call": d2h_b, "d2h_gbs": d2h_b / dt / 1e9,
+                                 "call": "kgwe_score_batch(host pods, out_scores = pinned host P x N matrix)",
+                                 "bound": "PCIe: the 16 B/evaluation matrix copy dominates (the kernel part of the same call is ~0.13 ms)"}
+
+        # ---- per-pod Prioritize latency vs node count: one kgwe_score_batch(P=1) C-ABI call per pod ----
+        def measure(engine, n_here, calls=10000, warm=1000):
+            fn, h = engine.lib.kgwe_score_batch, engine.h       # the raw C-ABI call on preallocated host buffers
             outp = np.zeros(1, dtype=abi.PLACEMENT)
             op = outp.ctypes.data
             ptrs = [pods[i:i + 1].ctypes.data for i in range(min(P, 512))]
@@ -355,7 +518,7 @@ def run_kgwe(args):
                 rc = fn(h, q, 1, None, None, 1, op)
                 xs[i] = (time.perf_counter() - a) * 1e6
                 assert rc == 0
-            return {"n_nodes": n_here, "calls": calls, "p50_us": float(np.percentile(xs, 50)), "p99_us": float(np.percentile(xs, 99)), "max_us": float(xs.max())}
+            return {"n_nodes": n_here, "calls": calls, "warmup_calls": warm, "p50_us": float(np.percentile(xs, 50)), "p99_us": float(np.percentile(xs, 99)), "max_us": float(xs.max())}
         lat = [measure(eng, n_local)]
         for n_small in (1000, 16):
             if n_small < N:
@@ -363,11 +526,9 @@ def run_kgwe(args):
                 e3.upsert_nodes(nodes[:n_small])
                 lat.append(measure(e3, n_small))
                 e3.close()
-
-    # ---- the same per-pod Prioritize over the node shards (N > 1): local top-1 on every rank, one 32-byte
-    #      all-gather, identical merge; SURVEY 8e asks whether this beats the 1-GPU latency (it does not at 10k nodes)
-    lat_sharded = None
-    if world > 1:
+        out["prioritize_latency"] = lat
+    else:
+        # the same per-pod Prioritize over the node shards: local top-1 on every rank, one 32-byte all-gather, identical merge
         itp = abi.PLACEMENT.itemsize
         gathered = torch.empty(world * itp, dtype=torch.uint8, device=dev)
         xs = np.empty(600)
@@ -381,164 +542,139 @@ def run_kgwe(args):
             kg.sharded.merge_host(lists, 1)
             if i >= 100:
                 xs[i - 100] = (time.perf_counter() - a) * 1e6
-        lat_sharded = {"n_nodes": N, "ranks": world, "calls": len(xs), "p50_us": float(np.percentile(xs, 50)), "p99_us": float(np.percentile(xs, 99)),
-                       "path": "kgwe_score_batch(P=1) per shard + NCCL all_gather(32 B) + kgwe_topk_merge_host"}
+        out["prioritize_latency_sharded"] = {"n_nodes": N, "ranks": world, "calls": len(xs), "p50_us": float(np.percentile(xs, 50)), "p99_us": float(np.percentile(xs, 99)),
+                                             "path": "kgwe_score_batch(P=1) per shard + NCCL all_gather(32 B) + kgwe_topk_merge_host"}
+        return out
 
-    # ---- stateful Schedule() queue throughput (reported beside the headline; N=1 only) ----
-    sched = None
-    if world == 1:
-        eng2 = kg.Engine(max_nodes=N, device=local_rank)
-        eng2.upsert_nodes(nodes)
-        eng2.seed_ledger(ledger)
-        q = pods[: min(P, 4000)]
-        a = time.perf_counter()
-        dec = eng2.schedule_queue(q)
-        w = time.perf_counter() - a
-        s2 = eng2.stats()
-        sched = {"pods": len(q), "wall_ms": w * 1e3, "gpu_ms": s2["last_call_gpu_ms"], "us_per_pod": s2["last_call_gpu_ms"] * 1e3 / len(q),
-                 "placed": int((dec["node_idx"] != abi.NO_NODE).sum()), "candidates_per_sec": s2["candidates"] / w}
-        eng2.close()
+    def fresh(flags=0, nd=nodes, led=ledger):
+        e = kg.Engine(max_nodes=len(nd), device=local_rank, flags=flags)
+        e.upsert_nodes(nd)
+        e.seed_ledger(led)
+        return e
 
-    # ---- E1 exhaustive k-of-8 subset mode and E2 MIG bin-packing (extensions; reported beside the headline) ----
-    exh = mig = memo = tiers = None
-    if world == 1:
-        qx = pods.copy()
-        qx["flags"] = abi.POD_EXHAUSTIVE
-        d_qx = torch.from_numpy(qx.view(np.uint8).reshape(len(qx), abi.POD_REQ.itemsize)).to(dev)
-        engx = kg.Engine(max_nodes=N, device=local_rank, flags=abi.CFG_SUBSET_TABLES)
-        engx.upsert_nodes(nodes)
-        engx.seed_ledger(ledger)
-        x0, x1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        for _ in range(3):
-            engx.score_batch_device(d_qx.data_ptr(), len(qx), None, scorer.d_scores.data_ptr(), 1, scorer.d_top.data_ptr(), sptr)
+    def device_rate(e, dp, npods, reps):
+        run = lambda: e.score_batch_device(dp.data_ptr(), npods, None, scorer.d_scores.data_ptr(), 1, scorer.d_top.data_ptr(), sptr)
+        for _ in range(2):
+            run()
         torch.cuda.synchronize()
-        c0 = engx.stats()["candidates"]
-        x0.record(stream)
-        for _ in range(5):
-            engx.score_batch_device(d_qx.data_ptr(), len(qx), None, scorer.d_scores.data_ptr(), 1, scorer.d_top.data_ptr(), sptr)
-        x1.record(stream)
-        torch.cuda.synchronize()
-        xms = x0.elapsed_time(x1) / 5
-        exh = {"pods": len(qx), "ms": xms, "candidates_per_sec": (engx.stats()["candidates"] - c0) / 5 / (xms * 1e-3),
-               "evaluations_per_sec": len(qx) * n_local / (xms * 1e-3), "mode": "all C(A,k) subsets per (pod,node), extension E1"}
-        engx.close()
-        # memoised group search (KGWE_CFG_MEMOISE_GROUPS): same workload and outputs as the headline step
-        engm = kg.Engine(max_nodes=N, device=local_rank, flags=abi.CFG_MEMOISE_GROUPS)
-        engm.upsert_nodes(nodes)
-        engm.seed_ledger(ledger)
-        for _ in range(3):
-            engm.score_batch_device(d_pods.data_ptr(), P, None, scorer.d_scores.data_ptr(), 1, scorer.d_top.data_ptr(), sptr)
-        torch.cuda.synchronize()
-        c0 = engm.stats()["candidates"]
-        x0.record(stream)
-        for _ in range(10):
-            engm.score_batch_device(d_pods.data_ptr(), P, None, scorer.d_scores.data_ptr(), 1, scorer.d_top.data_ptr(), sptr)
-        x1.record(stream)
-        torch.cuda.synchronize()
-        mms = x0.elapsed_time(x1) / 10
-        memo = {"ms_per_step": mms, "candidates_per_sec": (engm.stats()["candidates"] - c0) / 10 / (mms * 1e-3), "evaluations_per_sec": P * n_local / (mms * 1e-3),
-                "note": "greedy winner per (node, GPUCount) found once per node tile and looked up per evaluation; identical results; NOT the headline (brute-force) rate"}
-        engm.close()
-        # the numeric tier K1 takes depends on the nodes' link bandwidths; the headline cluster is all "uniform" (every
-        # active link of a node equal: the bit-set walk).  Same workload with the links perturbed, to show the other tiers.
-        tiers = {"headline_cluster": {"uniform_nodes": int(uniform_nodes(nodes)), "nodes": int(N)}}
-        rngt = kg.synth.SplitMix64(77)
-        for tier, make in (("uniform_fractional", lambda bw: bw * (0.5 + rngt.uniform(len(bw)))[:, None, None]),
-                           ("int32", lambda bw: np.where(bw > 0, np.floor(bw * (0.5 + rngt.uniform(bw.size).reshape(bw.shape))), 0.0)),
-                           ("fp64", lambda bw: bw * (0.5 + rngt.uniform(bw.size).reshape(bw.shape)))):
-            nt = nodes.copy()
-            nt["nvl_bw"] = make(nodes["nvl_bw"])
-            engt = kg.Engine(max_nodes=N, device=local_rank)
-            engt.upsert_nodes(nt)
-            engt.seed_ledger(ledger)
-            for _ in range(2):
-                engt.score_batch_device(d_pods.data_ptr(), P, None, scorer.d_scores.data_ptr(), 1, scorer.d_top.data_ptr(), sptr)
-            torch.cuda.synchronize()
-            c0 = engt.stats()["candidates"]
-            reps = 2 if tier == "fp64" else 5
-            x0.record(stream)
-            for _ in range(reps):
-                engt.score_batch_device(d_pods.data_ptr(), P, None, scorer.d_scores.data_ptr(), 1, scorer.d_top.data_ptr(), sptr)
-            x1.record(stream)
-            torch.cuda.synchronize()
-            tms = x0.elapsed_time(x1) / reps
-            tiers[tier] = {"ms_per_step": tms, "candidates_per_sec": (engt.stats()["candidates"] - c0) / reps / (tms * 1e-3), "evaluations_per_sec": P * n_local / (tms * 1e-3),
-                           "links": {"uniform_fractional": "one fractional value per node (bit-set walk, float64 totals)", "int32": "whole-number, irregular (no common value per node)",
-                                     "fp64": "fractional, irregular"}[tier]}
-            engt.close()
-        mg, mp = kg.synth.make_mig(10000, 50000)
-        a = time.perf_counter()
-        asg, mg_after = eng.mig_pack(mg, mp)
-        w = time.perf_counter() - a
-        gms = eng.stats()["last_call_gpu_ms"]
-        a = time.perf_counter()
-        tgt = np.zeros(10); tgt[[1, 3, 5]] = [0.7, 0.2, 0.1]
-        ops, supply, n_ops = eng.mig_rebalance(mg, tgt)
-        w2 = time.perf_counter() - a
-        mig = {"gpus": len(mg), "requests": len(mp), "placed": int((asg["gpu_idx"] != abi.NO_NODE).sum()), "kernel_ms": gms, "wall_ms": w * 1e3,
-               "requests_per_sec": len(mp) / w, "rebalance_wall_ms": w2 * 1e3, "rebalance_ops": int(n_ops),
-               "workload": "BASELINE configs[3]: 10,000 GPUs x all MIG profiles, 50k slice requests + one rebalancing pass (extension E2)"}
+        s0 = e.stats()
+        ms = timed_device_loop(torch, stream, run, reps, warm=0)
+        s1 = e.stats()
+        return {"ms_per_step": ms, "candidates_per_sec": (s1["candidates"] - s0["candidates"]) / reps / (ms * 1e-3),
+                "candidates_resolved_per_sec": (s1["candidates_resolved"] - s0["candidates_resolved"]) / reps / (ms * 1e-3),
+                "evaluations_per_sec": npods * len(nodes) / (ms * 1e-3)}
 
-    if rank == 0:
-        peak, peak_src = peaks()
-        achieved = k1_evals * BYTES_PER_EVAL / (k1_ms * 1e-3) / 1e9
-        out = {
-            "metric": METRIC, "value": cand_total / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-            "warmup": max(3, args.warmup), "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak" if (args.weak and world > 1) else "strong",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "n_nodes": N, "n_pods": P, "ledger_entries": int(len(ledger)), "mode": "greedy (reference parity)",
-                       "sharding": f"nodes by contiguous range over {world} rank(s)", "exchange": exchange,
-                       "l2": "160 MiB buffer written between steps (inside the timed region); each step also writes its P x N_local x 16 B score matrix (1.6 GB at 1 GPU, 200 MB at 8), both larger than the 126 MB L2"},
-            "evaluations_per_sec": ev_total / (ms_total * 1e-3),
-            "candidates_per_step": cand_total / args.steps,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "call": "kgwe_score_batch(host pods, topk=1 -> host placements)"},
-            "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(world, args.scale),
-                         "kernel": "kgwe::score_kernel", "ms_per_launch": k1_ms, "evaluations_per_launch": k1_evals,
-                         "bytes_per_evaluation": BYTES_PER_EVAL, "peak_source": peak_src, "actual_limits": measured_limits(world, args.scale),
-                         "traffic_unit": "bytes of DRAM read+write per launch (ncu, profiles/traffic.json)",
-                         "note": "achieved = algorithmic bytes (SURVEY 8d); the 7.68 MB node image is L2-resident across the pods of a launch, so real DRAM traffic is ~1.6 GB (the score matrix) and frac > 1 is expected: the kernel is instruction-issue bound (profiles/README.md)"},
-            "clocks": clk,
-        }
-        lim = out["roofline"]["actual_limits"]
-        if lim and clk.get("sm_mhz"):
-            # the bound that actually holds: warp instructions issued (count per evaluation from the ncu capture x this
-            # run's live launch time) against the issue slots of the device (SMs x 4 schedulers x the SM clock under load)
-            sms = torch.cuda.get_device_properties(0).multi_processor_count
-            issued = lim["warp_instructions_per_evaluation"] * k1_evals / (k1_ms * 1e-3)
-            slots = sms * 4 * clk["sm_mhz"] * 1e6
-            lim["issue_roofline"] = {"bound": "issue", "achieved": issued / 1e9, "peak": slots / 1e9, "unit": "G warp-instructions/s", "frac": issued / slots}
-        if lat:
-            out["prioritize_latency"] = lat
-        if lat_sharded:
-            out["prioritize_latency_sharded"] = lat_sharded
-        if sched:
-            out["stateful_queue"] = sched
-        if exh:
-            out["exhaustive_mode"] = exh
-        if mig:
-            out["mig_pack"] = mig
-        if memo:
-            out["memoised_group_search"] = memo
-            out["link_tiers"] = tiers
-        if not args.no_cpu_baseline and world == 1:
-            entry.build_oracle()
-            cores = host_cores()
-            r = cpu_reference_rate(kg, nodes, ledger, pods, args.cpu_seconds, cores)
-            out["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": cores, "kind": "port",
-                                   "sample": f"{r['pods']} pods x {N} nodes ({r['pods'] * N} evaluations, {r['seconds']:.1f} s), ledger {len(ledger)} entries",
-                                   "evaluations_per_sec": r["evals_per_s"],
-                                   "note": "faithful C++ restatement of scheduler.go:182-707 (Go toolchain absent); likely faster than Go"}
-            from oracle import binding as orc
-            r2 = cpu_reference_rate(kg, nodes, ledger, pods, min(args.cpu_seconds, 5.0), cores, mode=orc.INDEXED)
-            out["cpu_baseline_indexed"] = {"value": r2["value"], "unit": UNIT, "cores": cores, "kind": "port-optimised",
-                                           "sample": f"{r2['pods']} pods x {N} nodes ({r2['seconds']:.1f} s)", "evaluations_per_sec": r2["evals_per_s"],
-                                           "note": "same results on dense arrays and per-node masks (no ledger scans, no string maps): a CPU upper bound, not the reference's algorithmic cost"}
-        print(json.dumps(out))
-    eng.close()
-    if world > 1:
-        dist.destroy_process_group()
+    # ---- stateful Schedule() queue throughput ----
+    eng2 = fresh()
+    q = pods[: min(P, 4000)]
+    a = time.perf_counter()
+    dec = eng2.schedule_queue(q)
+    w = time.perf_counter() - a
+    s2 = eng2.stats()
+    out["stateful_queue"] = {"pods": len(q), "wall_ms": w * 1e3, "gpu_ms": s2["last_call_gpu_ms"], "us_per_pod": s2["last_call_gpu_ms"] * 1e3 / len(q),
+                             "placed": int((dec["node_idx"] != abi.NO_NODE).sum()), "candidates_resolved_per_sec": s2["candidates_resolved"] / w}
+    eng2.close()
+
+    # ---- the other search modes on the same workload and outputs (reported separately: they share or skip parts of the search) ----
+    for name, flag, note in (("pruned_tied_starts", abi.CFG_PRUNE_TIED_STARTS, "KGWE_CFG_PRUNE_TIED_STARTS: uniform nodes stop at the first completed walk; identical results; candidates counts the groups actually grown"),
+                             ("memoised_group_search", abi.CFG_MEMOISE_GROUPS, "KGWE_CFG_MEMOISE_GROUPS: greedy winner per (node, GPUCount) found once per CTA and looked up per evaluation; identical results; NOT the headline (brute-force) rate")):
+        e = fresh(flag)
+        r = device_rate(e, d_pods, P, 10)
+        r["note"] = note
+        out[name] = r
+        e.close()
+
+    # ---- E1 exhaustive k-of-8 subset mode ----
+    qx = pods.copy()
+    qx["flags"] = abi.POD_EXHAUSTIVE
+    d_qx = torch.from_numpy(qx.view(np.uint8).reshape(len(qx), abi.POD_REQ.itemsize)).to(dev)
+    e = fresh(abi.CFG_SUBSET_TABLES)
+    r = device_rate(e, d_qx, len(qx), 5)
+    r["mode"] = "all C(A,k) subsets per (pod,node), extension E1 (subset keys per node built once per CTA)"
+    out["exhaustive_mode"] = r
+    e.close()
+
+    # ---- the numeric tier K1 takes depends on the nodes' link bandwidths; the headline cluster is all "uniform" ----
+    tiers = {"headline_cluster": {"uniform_nodes": int(uniform_nodes(nodes)), "nodes": int(N)}}
+    rngt = kg.synth.SplitMix64(77)
+    for tier, make in (("uniform_fractional", lambda bw: bw * (0.5 + rngt.uniform(len(bw)))[:, None, None]),
+                       ("int32", lambda bw: np.where(bw > 0, np.floor(bw * (0.5 + rngt.uniform(bw.size).reshape(bw.shape))), 0.0)),
+                       ("fp64", lambda bw: bw * (0.5 + rngt.uniform(bw.size).reshape(bw.shape)))):
+        nt = nodes.copy()
+        nt["nvl_bw"] = make(nodes["nvl_bw"])
+        e = fresh(0, nt)
+        r = device_rate(e, d_pods, P, 2 if tier == "fp64" else 5)
+        r["links"] = {"uniform_fractional": "one fractional value per node (bit-set walks, float64 totals)", "int32": "whole-number, irregular (no common value per node)",
+                      "fp64": "fractional, irregular"}[tier]
+        tiers[tier] = r
+        e.close()
+    out["link_tiers"] = tiers
+
+    # ---- E2 MIG bin-packing (BASELINE configs[3]) ----
+    mg, mp = kg.synth.make_mig(10000, 50000)
+    a = time.perf_counter()
+    asg, mg_after = eng.mig_pack(mg, mp)
+    w = time.perf_counter() - a
+    gms = eng.stats()["last_call_gpu_ms"]
+    a = time.perf_counter()
+    tgt = np.zeros(10); tgt[[1, 3, 5]] = [0.7, 0.2, 0.1]
+    ops, supply, n_ops = eng.mig_rebalance(mg, tgt)
+    w2 = time.perf_counter() - a
+    out["mig_pack"] = {"gpus": len(mg), "requests": len(mp), "placed": int((asg["gpu_idx"] != abi.NO_NODE).sum()), "kernel_ms": gms, "wall_ms": w * 1e3,
+                       "requests_per_sec": len(mp) / w, "rebalance_wall_ms": w2 * 1e3, "rebalance_ops": int(n_ops),
+                       "workload": "BASELINE configs[3]: 10,000 GPUs x all MIG profiles, 50k slice requests + one rebalancing pass (extension E2)"}
+
+    # ---- the other BASELINE configs at their stated size: timed, each with its own parity check ----
+    cfgs = {}
+    n1, p1, l1 = kg.synth.config(1)
+    e = fresh(0, n1, l1)
+    a = time.perf_counter(); s1, t1 = e.score_batch(p1, len(n1), want_scores=True, topk=1); w = time.perf_counter() - a
+    o1, ot1, c1 = orc.score_batch(abi, n1, l1, p1, want_scores=True, topk=1, mode=orc.FAITHFUL)
+    cfgs["configs[0] 16-node DGX, 100 pods"] = {"stateless_call_ms": w * 1e3, "cpu_reference_ms": c1["seconds"] * 1e3, "evaluations": len(n1) * len(p1),
+                                               "parity_mismatches": int(s1.tobytes() != o1.tobytes()) + int(t1.tobytes() != ot1.tobytes())}
+    e.close()
+    n2, p2, l2 = kg.synth.config(2)
+    e = fresh(0, n2, l2)
+    e.score_batch(p2[:8], len(n2), want_scores=True, topk=1)
+    a = time.perf_counter(); s2m, t2 = e.score_batch(p2, len(n2), want_scores=True, topk=1); w = time.perf_counter() - a
+    gms2 = e.stats()["last_call_gpu_ms"]
+    o2, ot2, c2 = orc.score_batch(abi, n2, l2, p2, want_scores=True, topk=1, threads=min(8, host_cores()))
+    a = time.perf_counter(); d2 = e.schedule_queue(p2); wq = time.perf_counter() - a
+    gq2 = e.stats()["last_call_gpu_ms"]
+    od2, _, _ = orc.schedule_queue(abi, n2, l2, p2)
+    cfgs["configs[1] 1,000-node mixed, 1k pods, NVLinkOptimal + minBandwidthGBps"] = {
+        "stateless_call_ms": w * 1e3, "stateless_gpu_ms": gms2, "evaluations": len(n2) * len(p2), "candidates_per_sec_gpu": c2["candidates"] / (gms2 * 1e-3),
+        "filtered_by_min_bandwidth": int(((s2m["flags"] & abi.F_MINBW) != 0).sum()),
+        "stateful_queue_ms": wq * 1e3, "stateful_gpu_ms": gq2, "placed": int((d2["node_idx"] != abi.NO_NODE).sum()),
+        "parity_mismatches": int(s2m.tobytes() != o2.tobytes()) + int(t2.tobytes() != ot2.tobytes()) + int(d2.tobytes() != od2.tobytes()),
+        "parity": "full matrix, top-1 and all stateful decisions vs the oracle (indexed build)"}
+    e.close()
+    n5, p5, l5 = kg.synth.config(5)
+    gang_of = (np.arange(len(p5)) // 8).astype(np.uint32)
+    e = fresh(0, n5, l5)
+    a = time.perf_counter(); g5 = e.schedule_gangs(p5, gang_of); w = time.perf_counter() - a
+    gg5 = e.stats()["last_call_gpu_ms"]
+    placed = g5["node_idx"] != abi.NO_NODE
+    by_gang = placed.reshape(-1, 8)
+    pairs = set()
+    dup = 0
+    for nidx, m in zip(g5["node_idx"][placed].tolist(), g5["gpu_mask"][placed].tolist()):
+        for b in range(8):
+            if m >> b & 1:
+                dup += (nidx, b) in pairs
+                pairs.add((nidx, b))
+    n_first = 40 * 8
+    og5, _ = orc.schedule_gangs(abi, n5, l5, p5[:n_first], gang_of[:n_first])
+    terms = e.placement_terms(g5[:64])
+    cfgs["configs[4] 10,000 nodes, 1,250 gangs x 8 members x 8 GPUs (worldSize 64)"] = {
+        "gang_queue_ms": w * 1e3, "gang_queue_gpu_ms": gg5, "us_per_member": gg5 * 1e3 / len(p5), "members": int(len(p5)), "gangs_placed": int(by_gang.all(axis=1).sum()),
+        "all_or_nothing_violations": int((by_gang.any(axis=1) & ~by_gang.all(axis=1)).sum()), "gpus_handed_out_twice": int(dup),
+        "parity_mismatches": int(g5[:n_first].tobytes() != og5.tobytes()) + int(dup) + int((by_gang.any(axis=1) & ~by_gang.all(axis=1)).sum()),
+        "parity": f"first {n_first // 8} gangs vs the oracle byte for byte; the rest by all-or-nothing and no-GPU-twice",
+        "side_terms_first_placement": {"bisection_gbps": float(terms["bisection_gbps"][0]), "ring_bottleneck_gbps": float(terms["ring_bottleneck_gbps"][0])}}
+    e.close()
+    out["configs"] = cfgs
+    return out
 
 
 def main():

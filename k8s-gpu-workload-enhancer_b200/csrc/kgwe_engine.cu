@@ -78,7 +78,7 @@ struct kgwe_engine {
     int sm_count = 148;
     int sched_blocks_per_sm = 1;
     int sched_tile_blocks_per_sm = 0;
-    int k1_blocks_per_sm[3] = {4, 2, 1};   // co-resident CTAs of K1's lean / GENERAL / TABLES variants
+    int k1_blocks_per_sm[4] = {5, 3, 2, 1};   // co-resident CTAs of K1's lean / GENERAL (int32 columns) / GENERAL (float64 columns) / TABLES variants
 
     DevNode* d_nodes = nullptr;       // cluster image in HBM
     DevNode* h_nodes = nullptr;       // pinned mirror (device layout)
@@ -87,12 +87,14 @@ struct kgwe_engine {
     uint32_t n_nodes = 0;             // high-water mark of present records
     uint32_t n_present = 0;
     uint32_t n_nonuniform = 0;        // present records whose active links are not all equal (K1 then needs its GENERAL variant)
+    uint32_t n_fractional = 0;        // ... of which with a fractional bandwidth (K1 then needs float64 matrix columns)
     std::unordered_map<uint64_t, LedgerEntry> ledger;
 
     DevBuf<kgwe_pod_req> d_pods;
     DevBuf<uint8_t> d_hint;
     DevBuf<unsigned long long> d_best;      // arg-max keys, kept all-zero between calls
     DevBuf<unsigned int> d_arrive;          // per-pod arrival counters of the queue kernel, kept all-zero between calls
+    DevBuf<uint32_t> d_gang;                // gang numbers of the queue's pods (E5)
     DevBuf<kgwe_placement> d_topk;
     DevBuf<kgwe_node_score> d_scores;
     unsigned long long* d_counters = nullptr;   // kCounters words, see above
@@ -130,6 +132,7 @@ int to_device_record(kgwe_engine* e, const kgwe_node_image& in, DevNode& out) {
 }
 
 inline uint32_t rec_nonuniform(const DevNode& r) { return ((r.flags & NODE_PRESENT) && r.pad1[0] == 0) ? 1u : 0u; }
+inline uint32_t rec_fractional(const DevNode& r) { return (rec_nonuniform(r) && !(r.flags & NODE_INTEGRAL)) ? 1u : 0u; }
 
 void mark_dirty(kgwe_engine* e, uint32_t idx) {
     if (!e->dirty_flag[idx]) { e->dirty_flag[idx] = 1; e->dirty.push_back(idx); }
@@ -171,7 +174,7 @@ size_t sched_tile_smem_bytes() { return (size_t)TILE_NODES * (sizeof(DevNode) + 
 // Kernel variant: the lean one when every present record is uniform (all active links of a node equal - any
 // NVSwitch node, any single-generation mesh), GENERAL as soon as one record is not (matrix columns in shared
 // memory), TABLES when exhaustive-mode pods may be in the batch (subset-key columns; implies GENERAL).
-struct K1Plan { bool general, tables; uint32_t mode, chunks, ppc, n_tiles; size_t smem; };
+struct K1Plan { bool general, tables; uint32_t mode, chunks, ppc, n_tiles, mat_units; size_t smem; };
 
 uint32_t k1_mode(const kgwe_engine* e) {
     return (e->cfg.flags & KGWE_CFG_MEMOISE_GROUPS) ? K1_MODE_MEMO : (e->cfg.flags & KGWE_CFG_PRUNE_TIED_STARTS) ? K1_MODE_PRUNE : K1_MODE_FULL;
@@ -184,10 +187,11 @@ K1Plan plan_k1(const kgwe_engine* e, uint32_t n_pods, bool tables) {
     K1Plan pl;
     pl.tables = tables || (e->cfg.flags & KGWE_CFG_SUBSET_TABLES);
     pl.general = pl.tables || e->n_nonuniform > 0;
+    pl.mat_units = !pl.general ? 0u : e->n_fractional > 0 ? 32u : 16u;      // float64 rows only when some non-uniform record has fractional bandwidths
     pl.mode = k1_mode(e);
     pl.n_tiles = (e->n_nodes + K1_TILE - 1) / K1_TILE;
     const uint32_t max_ppc = pl.tables ? 256u : (uint32_t)MAX_PODS_PER_CHUNK;      // the subset columns leave room for 256 pods' tables
-    const uint32_t slots = (uint32_t)e->sm_count * (uint32_t)e->k1_blocks_per_sm[pl.tables ? 2 : pl.general ? 1 : 0];
+    const uint32_t slots = (uint32_t)e->sm_count * (uint32_t)e->k1_blocks_per_sm[pl.tables ? 3 : !pl.general ? 0 : pl.mat_units == 16 ? 1 : 2];
     uint32_t chunks = 1, ppc = n_pods;
     for (uint32_t waves = 1; waves <= 256; ++waves) {
         chunks = std::max(1u, std::min(n_pods, slots * waves / pl.n_tiles));
@@ -197,7 +201,7 @@ K1Plan plan_k1(const kgwe_engine* e, uint32_t n_pods, bool tables) {
     if (ppc > max_ppc) ppc = max_ppc;
     pl.ppc = ppc;
     pl.chunks = (n_pods + ppc - 1) / ppc;
-    pl.smem = k1_layout(ppc, pl.general, pl.tables, pl.mode == K1_MODE_MEMO).total;
+    pl.smem = k1_layout(ppc, pl.mat_units, pl.tables, pl.mode == K1_MODE_MEMO).total;
     return pl;
 }
 
@@ -210,7 +214,7 @@ int launch_k1(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const
     timed = timed && e->timers_pending < kgwe_engine::kTimers;
     if (timed) CU(e, cudaEventRecord(e->t0[e->timers_pending], s));
 #define KGWE_LAUNCH_SCORE(G, T) score_kernel<G, T><<<grid, K1_THREADS, pl.smem, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, pl.ppc, d_hint, hint_row_bytes(e), \
-                                                                                    d_scores, best, e->params, e->d_counters, pl.mode, tail)
+                                                                                    d_scores, best, e->params, e->d_counters, pl.mode, pl.mat_units, tail)
     if (pl.tables) KGWE_LAUNCH_SCORE(true, true);
     else if (pl.general) KGWE_LAUNCH_SCORE(true, false);
     else KGWE_LAUNCH_SCORE(false, false);
@@ -344,16 +348,17 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
         cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, cfg->device);
         for (int i = 0; i < kgwe_engine::kTimers && ok; ++i) ok = cudaEventCreate(&e->t0[i]) == cudaSuccess && cudaEventCreate(&e->t1[i]) == cudaSuccess;
         {
-            const int lean = (int)k1_layout(MAX_PODS_PER_CHUNK, false, false, true).total, gen = (int)k1_layout(MAX_PODS_PER_CHUNK, true, false, true).total,
-                      tab = (int)k1_layout(256, true, true, true).total;
+            const int lean = (int)k1_layout(MAX_PODS_PER_CHUNK, 0, false, true).total, gen = (int)k1_layout(MAX_PODS_PER_CHUNK, 32, false, true).total,
+                      tab = (int)k1_layout(256, 32, true, true).total;
             ok = ok && cudaFuncSetAttribute(score_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lean) == cudaSuccess
                     && cudaFuncSetAttribute(score_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, gen) == cudaSuccess
                     && cudaFuncSetAttribute(score_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab) == cudaSuccess;
             // co-resident CTAs at a typical chunk size (plan_k1 sizes its waves with these)
             int b = 0;
-            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<false, false>, K1_THREADS, k1_layout(512, false, false, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[0] = b;
-            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, false>, K1_THREADS, k1_layout(512, true, false, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[1] = b;
-            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, true>, K1_THREADS, k1_layout(256, true, true, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[2] = b;
+            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<false, false>, K1_THREADS, k1_layout(512, 0, false, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[0] = b;
+            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, false>, K1_THREADS, k1_layout(512, 16, false, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[1] = b;
+            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, false>, K1_THREADS, k1_layout(512, 32, false, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[2] = b;
+            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, true>, K1_THREADS, k1_layout(256, 32, true, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[3] = b;
         }
         int bps = 0;
         if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, schedule_kernel, SCORE_THREADS, 0) == cudaSuccess && bps > 0) e->sched_blocks_per_sm = bps;
@@ -370,7 +375,7 @@ int kgwe_engine_destroy(kgwe_engine* e) {
     if (!e) return KGWE_ERR_INVALID_ARG;
     cudaSetDevice(e->cfg.device);
     if (e->stream) cudaStreamSynchronize(e->stream);
-    e->d_pods.release(); e->d_hint.release(); e->d_best.release(); e->d_arrive.release(); e->d_topk.release(); e->d_scores.release();
+    e->d_pods.release(); e->d_hint.release(); e->d_best.release(); e->d_arrive.release(); e->d_gang.release(); e->d_topk.release(); e->d_scores.release();
     e->h_pods.release(); e->h_topk.release(); e->h_hint.release();
     if (e->d_nodes) cudaFree(e->d_nodes);
     if (e->h_nodes) cudaFreeHost(e->h_nodes);
@@ -405,6 +410,7 @@ int kgwe_nodes_upsert(kgwe_engine* e, uint32_t first, uint32_t count, const kgwe
             rec.allocated_mask = m; rec.n_allocs = n;
         }
         e->n_nonuniform += rec_nonuniform(rec) - rec_nonuniform(dst);
+        e->n_fractional += rec_fractional(rec) - rec_fractional(dst);
         dst = rec;
         if (!was) e->n_present++;
         mark_dirty(e, first + i);
@@ -426,6 +432,7 @@ int kgwe_node_remove(kgwe_engine* e, uint32_t idx) {
     // node comes back under the same index (see kgwe_nodes_upsert).  n_nodes is a high-water mark and
     // does not shrink, so the stride of score matrices and hint rows stays what the host knows.
     e->n_nonuniform -= rec_nonuniform(dst);
+    e->n_fractional -= rec_fractional(dst);
     memset(&dst, 0, sizeof dst);
     e->n_present--;
     mark_dirty(e, idx);
@@ -624,7 +631,14 @@ int kgwe_topk_merge_host(const kgwe_placement* lists, uint32_t n_lists, uint32_t
 
 // Launch the stateful queue kernel (K3) for np pods and wait.  Decisions land in e->h_topk; the
 // DEVICE image then carries every commit of the segment, the host mirror none yet.
-static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t np, const uint8_t* hint_rows, double* gpu_ms) {
+// True when the image fits the tile form of the queue kernel (every node has its own lane group).
+static bool queue_tile_form(const kgwe_engine* e) {
+    const uint32_t n_tiles = (e->n_nodes + TILE_NODES - 1) / TILE_NODES;
+    return n_tiles <= (uint32_t)(e->sm_count * e->sched_tile_blocks_per_sm);
+}
+
+// gang_of (host, np entries, nullable): all-or-nothing gangs decided on the device (tile form only).
+static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t np, const uint8_t* hint_rows, double* gpu_ms, const uint32_t* gang_of = nullptr) {
     cudaStream_t s = e->stream;
     const uint32_t N = e->n_nodes, row = hint_row_bytes(e);
     int rc = flush_dirty(e, s);
@@ -650,17 +664,25 @@ static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t 
         e->stats.h2d_bytes += (uint64_t)np * row;
         d_hint = e->d_hint.p;
     }
+    const uint32_t* d_gang = nullptr;
+    if (gang_of) {
+        CU(e, e->d_gang.ensure(np));
+        CU(e, cudaMemcpyAsync(e->d_gang.p, gang_of, (size_t)np * sizeof(uint32_t), cudaMemcpyHostToDevice, s));      // (pageable source: the runtime stages it before returning)
+        e->stats.h2d_bytes += (uint64_t)np * sizeof(uint32_t);
+        d_gang = e->d_gang.p;
+    }
     // persistent grid: as many CTAs as can be co-resident, no more than there are node tiles
     uint32_t grid = std::min<uint32_t>((uint32_t)(e->sm_count * e->sched_blocks_per_sm), (N + TILE_NODES - 1) / TILE_NODES);
     grid = std::max(grid, 1u);
     DevNode* d_nodes = e->d_nodes; uint32_t n_nodes = N; const kgwe_pod_req* d_pods = e->d_pods.p; uint32_t npods = np; uint32_t rowb = row;
     unsigned long long* best = e->d_best.p; unsigned int* arrive = e->d_arrive.p; kgwe_placement* d_out = e->d_topk.p; Params prm = e->params; unsigned long long* ctr = e->d_counters;
     void* args[] = {&d_nodes, &n_nodes, &d_pods, &npods, &d_hint, &rowb, &best, &arrive, &d_out, &prm, &ctr};
+    void* targs[] = {&d_nodes, &n_nodes, &d_pods, &npods, &d_hint, &rowb, &best, &arrive, &d_out, &prm, &ctr, &d_gang};
     CU(e, cudaEventRecord(e->ev0, s));
     const uint32_t n_tiles = (N + TILE_NODES - 1) / TILE_NODES;
-    if (n_tiles <= (uint32_t)(e->sm_count * e->sched_tile_blocks_per_sm)) {
+    if (queue_tile_form(e)) {
         // every node gets its own lane group: tile form (shared-memory resident tables)
-        CU(e, cudaLaunchCooperativeKernel((const void*)schedule_tile_kernel, dim3(n_tiles), dim3(SCORE_THREADS), args, sched_tile_smem_bytes(), s));
+        CU(e, cudaLaunchCooperativeKernel((const void*)schedule_tile_kernel, dim3(n_tiles), dim3(SCORE_THREADS), targs, sched_tile_smem_bytes(), s));
     } else
     CU(e, cudaLaunchCooperativeKernel((const void*)schedule_kernel, dim3(grid), dim3(SCORE_THREADS), args, 0, s));
     est_bandwidth_kernel<<<(np + 127) / 128, 128, 0, s>>>(e->d_nodes, N, e->cfg.node_base, e->d_topk.p, np);
@@ -775,7 +797,38 @@ int kgwe_schedule_gangs(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pod
         return KGWE_OK;
     }
     const uint32_t row = hint_row_bytes(e);
-    const uint32_t kWindow = 4096;
+    if (queue_tile_form(e) && !getenv("KGWE_GANG_WINDOW")) {      // (the variable also forces the window path below, for tests)
+        // All-or-nothing on the device: the queue kernel itself takes a rejected gang's commits back (schedule_tile_kernel),
+        // so the whole queue is one launch per segment; the host only turns the decisions of rejected gangs into
+        // "no node" (+ KGWE_F_GANG_ROLLBACK for members that had found one) and mirrors the surviving commits.
+        const uint32_t kSegment = 1u << 20;
+        double gms = 0.0;
+        uint32_t q0 = 0;
+        while (q0 < n_pods) {
+            uint32_t q1 = std::min(n_pods, q0 + kSegment);
+            while (q1 < n_pods && gang_of[q1] == gang_of[q1 - 1]) ++q1;
+            const uint32_t np = q1 - q0;
+            rc = run_queue_segment(e, pods + q0, np, hint ? hint + (size_t)q0 * row : nullptr, &gms, gang_of + q0);
+            if (rc != KGWE_OK) return rc;
+            uint32_t g0 = 0;
+            while (g0 < np) {
+                uint32_t g1 = g0 + 1; bool all = e->h_topk.p[g0].node_idx != KGWE_NO_NODE;
+                while (g1 < np && gang_of[q0 + g1] == gang_of[q0 + g0]) { all = all && e->h_topk.p[g1].node_idx != KGWE_NO_NODE; ++g1; }
+                for (uint32_t i = g0; i < g1; ++i) {
+                    const kgwe_placement& d = e->h_topk.p[i];
+                    if (all) { out[q0 + i] = d; apply_commit(e, pods[q0 + i].wl_id, d); }
+                    else { no_node(out[q0 + i], d.node_idx != KGWE_NO_NODE ? KGWE_F_GANG_ROLLBACK : 0); e->stats.failed++; }
+                }
+                g0 = g1;
+            }
+            q0 = q1;
+        }
+        e->stats.last_call_gpu_ms = gms;
+        return KGWE_OK;
+    }
+    // Images too large for the tile form of the queue kernel: speculative windows.
+    // speculative window (pods per queue launch); KGWE_GANG_WINDOW shrinks it so tests can cross many window edges on small inputs
+    static const uint32_t kWindow = [] { const char* v = getenv("KGWE_GANG_WINDOW"); const long x = v ? atol(v) : 0; return x > 0 ? (uint32_t)x : 4096u; }();
     double gpu_ms = 0.0;
     uint32_t p0 = 0;
     while (p0 < n_pods) {
@@ -1035,8 +1088,8 @@ int kgwe_snapshot_load(kgwe_engine* e, const void* buf, uint64_t len) {
         e->ledger[en.wl_id] = LedgerEntry{en.node, (uint8_t)en.mask};
     }
     e->n_nodes = std::max(h.n_nodes, old_n);          // high-water mark never shrinks (absent records score as absent)
-    e->n_present = 0; e->n_nonuniform = 0;
-    for (uint32_t i = 0; i < e->n_nodes; ++i) { if (e->h_nodes[i].flags & NODE_PRESENT) e->n_present++; e->n_nonuniform += rec_nonuniform(e->h_nodes[i]); mark_dirty(e, i); }
+    e->n_present = 0; e->n_nonuniform = 0; e->n_fractional = 0;
+    for (uint32_t i = 0; i < e->n_nodes; ++i) { if (e->h_nodes[i].flags & NODE_PRESENT) e->n_present++; e->n_nonuniform += rec_nonuniform(e->h_nodes[i]); e->n_fractional += rec_fractional(e->h_nodes[i]); mark_dirty(e, i); }
     return KGWE_OK;
 }
 

@@ -337,7 +337,7 @@ __global__ void __launch_bounds__(SCORE_THREADS, 2)
 schedule_tile_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
                      const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
                      unsigned long long* __restrict__ best, unsigned int* __restrict__ arrive, kgwe_placement* __restrict__ out,
-                     Params P, unsigned long long* __restrict__ counters) {
+                     Params P, unsigned long long* __restrict__ counters, const uint32_t* __restrict__ gang_of) {
     extern __shared__ __align__(128) unsigned char smem[];
     DevNode* tile = reinterpret_cast<DevNode*>(smem);
     NodeFast* fast = reinterpret_cast<NodeFast*>(smem + TILE_NODES * sizeof(DevNode));
@@ -371,9 +371,15 @@ schedule_tile_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __res
     bool warp_fast = __all_sync(0xffffffffu, nc.integral || !nc.valid);
     unsigned long long cand = 0, evals = 0;
     kgwe_pod_req pod = load_pod(pods, 0);
+    // E5 gangs (gang_of != nullptr): all-or-nothing per run of equal gang numbers.  Every thread sees every decision, so
+    // "a member of the current gang found no node" is known grid-wide without any extra exchange; a group remembers what
+    // its node committed for the current gang and takes it back when the gang's last member has been decided.
+    bool gang_failed = false; uint32_t gang_mask = 0, gang_commits = 0;
+    uint32_t gang_cur = gang_of ? __ldg(gang_of) : 0u;
 
     for (uint32_t p = 0; p < n_pods; ++p) {
         const kgwe_pod_req next = load_pod(pods, p + 1 < n_pods ? p + 1 : p);      // prefetch
+        const uint32_t gang_next = (gang_of && p + 1 < n_pods) ? __ldg(gang_of + p + 1) : 0xFFFFFFFFu;
         const int k = clamp_k(pod.gpu_count);
         const bool hinted = node_ok && hint_bit(hint, hint_row_bytes, p, node);
         EvalOut o;
@@ -406,14 +412,32 @@ schedule_tile_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __res
         }
         __syncthreads();
         const unsigned long long win = winner;
+        bool changed = false;
         if (win == 0ull) {
             if (blockIdx.x == 0 && tid == 0) store_no_placement(out + p);
+            gang_failed = true;
         } else if (win == mykey) {
             // this group owns the winner: tryScheduleOnNode + recordAllocation (scheduler.go:625-653, 695-707)
             if (j == 0) {
                 store_placement(out + p, P.node_base + node, o, 0.0);     // EstimatedBandwidth is filled in after the queue (est_bandwidth_kernel)
                 rec->allocated_mask = (uint8_t)(rec->allocated_mask | o.mask);
                 rec->n_allocs = rec->n_allocs + 1;
+            }
+            gang_mask |= o.mask; gang_commits += 1;
+            changed = true;
+        }
+        if (gang_of && gang_next != gang_cur) {          // the gang's last member has been decided
+            if (gang_failed && gang_commits) {            // take this node's commits for the gang back
+                if (j == 0) {
+                    rec->allocated_mask = (uint8_t)(rec->allocated_mask & ~gang_mask);
+                    rec->n_allocs = rec->n_allocs - gang_commits;
+                }
+                changed = true;
+            }
+            gang_failed = false; gang_mask = 0; gang_commits = 0; gang_cur = gang_next;
+        }
+        if (changed) {
+            if (j == 0) {
                 nodes[node].allocated_mask = rec->allocated_mask;       // the image in HBM follows
                 nodes[node].n_allocs = rec->n_allocs;
             }

@@ -84,7 +84,8 @@ struct LaneNode {
 
 __device__ __forceinline__ uint32_t rev8(uint32_t x) { return __brev(x) >> 24; }
 
-__device__ inline void lane_node_init(LaneNode& ln, const NodeCtx& c, const DevNode* rec, bool have_columns) {
+// mat_units: 16-byte units of the lane's matrix column - 0 (no column), 16 (int32 rows only), 32 (int32 or float64 rows)
+__device__ inline void lane_node_init(LaneNode& ln, const NodeCtx& c, const DevNode* rec, uint32_t mat_units) {
     ln.avail = c.avail; ln.A = c.A; ln.sum_free = c.sum_free; ln.util_bonus = c.util_bonus; ln.balance = c.balance;
     ln.avail_order = c.avail_order; ln.avail_prefix = c.avail_prefix; ln.valid = c.valid; ln.integral = c.integral;
     uint64_t a8 = c.arch8, rows = 0;
@@ -95,7 +96,7 @@ __device__ inline void lane_node_init(LaneNode& ln, const NodeCtx& c, const DevN
     }
     ln.arch_lo = (uint32_t)a8; ln.arch_hi = (uint32_t)(a8 >> 32);
     ln.rlo = (uint32_t)rows; ln.rhi = (uint32_t)(rows >> 32);
-    ln.tier = !c.valid ? TIER_NONE : node_uniform_code(rec) ? TIER_UNIFORM : !have_columns ? TIER_F64_GLOBAL : c.integral ? TIER_INT : TIER_F64;
+    ln.tier = !c.valid ? TIER_NONE : node_uniform_code(rec) ? TIER_UNIFORM : (c.integral && mat_units >= 16) ? TIER_INT : (!c.integral && mat_units >= 32) ? TIER_F64 : TIER_F64_GLOBAL;
 }
 
 // Per-lane views of the shared-memory tables: entry e of table X is X[e * stride] (stride = lanes per CTA;
@@ -236,7 +237,9 @@ __device__ __forceinline__ void lane_mat_build_f64(const LaneTabs& tb, const Dev
 }
 
 // All available starts, integer chains (see NodeFast / greedy_chain_fast_k): key = (total << 3) | (7 - start) of
-// the best chain that reached K members with total > 0, else 0; pay = its join order.
+// the best chain that reached K members with total > 0, else 0; pay = its join order.  Two starts are grown side by
+// side (independent dependency chains: load -> add -> max tree -> next row), the second one masked when the number
+// of available starts is odd.
 template <int K>
 __device__ __forceinline__ void chain_int_all(const int4* mat, int stride, uint32_t avail, int32_t& key, uint32_t& pay) {
     key = 0; pay = 0;
@@ -244,24 +247,30 @@ __device__ __forceinline__ void chain_int_all(const int4* mat, int stride, uint3
     ia.x = (avail & 1u) ? 7 : FAST_NEG;   ia.y = (avail & 2u) ? 6 : FAST_NEG;   ia.z = (avail & 4u) ? 5 : FAST_NEG;   ia.w = (avail & 8u) ? 4 : FAST_NEG;
     ib.x = (avail & 16u) ? 3 : FAST_NEG;  ib.y = (avail & 32u) ? 2 : FAST_NEG;  ib.z = (avail & 64u) ? 1 : FAST_NEG;  ib.w = (avail & 128u) ? 0 : FAST_NEG;
 #pragma unroll 1
-    for (uint32_t rest = avail; rest; rest &= rest - 1u) {
-        const int s = __ffs((int)rest) - 1;
-        int4 a = ia, b = ib;
-        uint32_t sum = 0, order = (uint32_t)s; int m = s;
-        bool alive = true;
+    for (uint32_t rest = avail; rest;) {
+        const int s0 = __ffs((int)rest) - 1; rest &= rest - 1u;
+        const bool two = rest != 0u;
+        const int s1 = two ? __ffs((int)rest) - 1 : s0; rest &= rest - 1u;
+        int4 a0 = ia, b0 = ib, a1 = ia, b1 = ib;
+        uint32_t sum0 = 0, sum1 = 0, ord0 = (uint32_t)s0, ord1 = (uint32_t)s1; int m0 = s0, m1 = s1;
+        bool alive0 = true, alive1 = two;
 #pragma unroll
         for (int step = 1; step < K; ++step) {
-            const int4 r0 = mat[(2 * m) * stride], r1 = mat[(2 * m + 1) * stride];
-            a.x += r0.x; a.y += r0.y; a.z += r0.z; a.w += r0.w;
-            b.x += r1.x; b.y += r1.y; b.z += r1.z; b.w += r1.w;
-            const int32_t best = __vimax3_s32(__vimax3_s32(a.x, a.y, a.z), __vimax3_s32(a.w, b.x, b.y), max(b.z, b.w));
-            alive &= best > 7;
-            m = ~best & 7;
-            sum += (uint32_t)best;
-            order |= (uint32_t)m << (3 * step);
+            const int4 r0 = mat[(2 * m0) * stride], r1 = mat[(2 * m0 + 1) * stride];
+            const int4 q0 = mat[(2 * m1) * stride], q1 = mat[(2 * m1 + 1) * stride];
+            a0.x += r0.x; a0.y += r0.y; a0.z += r0.z; a0.w += r0.w; b0.x += r1.x; b0.y += r1.y; b0.z += r1.z; b0.w += r1.w;
+            a1.x += q0.x; a1.y += q0.y; a1.z += q0.z; a1.w += q0.w; b1.x += q1.x; b1.y += q1.y; b1.z += q1.z; b1.w += q1.w;
+            const int32_t best0 = __vimax3_s32(__vimax3_s32(a0.x, a0.y, a0.z), __vimax3_s32(a0.w, b0.x, b0.y), max(b0.z, b0.w));
+            const int32_t best1 = __vimax3_s32(__vimax3_s32(a1.x, a1.y, a1.z), __vimax3_s32(a1.w, b1.x, b1.y), max(b1.z, b1.w));
+            alive0 &= best0 > 7; alive1 &= best1 > 7;
+            m0 = ~best0 & 7; m1 = ~best1 & 7;
+            sum0 += (uint32_t)best0; sum1 += (uint32_t)best1;
+            ord0 |= (uint32_t)m0 << (3 * step); ord1 |= (uint32_t)m1 << (3 * step);
         }
-        const int32_t k32 = alive ? (int32_t)(((sum >> (FAST_SHIFT - 3)) & ~7u) | (uint32_t)(7 - s)) : 0;
-        if (k32 > key) { key = k32; pay = order; }
+        const int32_t k0 = alive0 ? (int32_t)(((sum0 >> (FAST_SHIFT - 3)) & ~7u) | (uint32_t)(7 - s0)) : 0;
+        const int32_t k1 = alive1 ? (int32_t)(((sum1 >> (FAST_SHIFT - 3)) & ~7u) | (uint32_t)(7 - s1)) : 0;
+        if (k0 > key) { key = k0; pay = ord0; }
+        if (k1 > key) { key = k1; pay = ord1; }
     }
 }
 __device__ __forceinline__ void chain_int_all_k(const int4* mat, int stride, uint32_t avail, int k, int32_t& key, uint32_t& pay) {
@@ -453,6 +462,7 @@ __device__ __forceinline__ void lane_evaluate(const LaneNode& ln, const LaneTabs
             uint32_t bm = 0; double best = 0.0;
             if (TABLES && ln.integral) {
                 uint32_t key = 0;
+#pragma unroll 4
                 for (int q = subset_off(k); q < subset_off(k + 1); ++q) key = max(key, tb.subset[q * tb.stride]);
                 if (key) { best = (double)(key >> 8); bm = 255u - (key & 255u); }
             } else {
@@ -540,7 +550,7 @@ __device__ inline void lane_tables_build(const LaneNode& ln, const NodeCtx& c, c
     }
     if (GENERAL && ln.valid) {
         if (ln.integral) lane_mat_build_int(tb, rec, c.colact);
-        else lane_mat_build_f64(tb, rec);
+        else if (ln.tier == TIER_F64) lane_mat_build_f64(tb, rec);
     }
     if (TABLES) lane_subset_build(tb, ln, c.colact, slot_of);
     if (mode == K1_MODE_MEMO) lane_memo_build<GENERAL>(ln, tb, rec, norm);

@@ -30,11 +30,12 @@ constexpr int MAX_PODS_PER_CHUNK = 1024;       // size of the per-CTA PodLite / 
 struct FusedTail { kgwe_placement* out; unsigned int* done; unsigned int* flag; unsigned int seq; unsigned int n_inline; kgwe_pod_req inline_pods[4]; };
 
 struct K1Layout { uint32_t pods, keys, topo, grp, mig, memo, mat, subset, slot, total; };
-__host__ __device__ inline K1Layout k1_layout(uint32_t ppc, bool general, bool tables, bool memo) {
+// mat_units: 16-byte units per lane of the matrix columns: 0 (lean variant), 16 (int32 rows), 32 (int32 or float64 rows)
+__host__ __device__ inline K1Layout k1_layout(uint32_t ppc, uint32_t mat_units, bool tables, bool memo) {
     K1Layout L; uint32_t o = 0;
     L.pods = o; o += (ppc + 1u) * 16u;                              // + one slot: the loop prefetches pod i + 1
     L.keys = o; o += ((ppc * 4u * (K1_THREADS / 32)) + 15u) & ~15u;    // one arg-max row per warp (plain stores, no atomics)
-    L.mat = o; o += general ? 32u * K1_TILE * 16u : 0u;
+    L.mat = o; o += mat_units * K1_TILE * 16u;
     L.memo = o; o += memo ? 7u * K1_TILE * 8u : 0u;
     L.topo = o; o += 7u * K1_TILE * 4u;
     L.grp = o; o += 6u * K1_TILE * 4u;
@@ -46,14 +47,14 @@ __host__ __device__ inline K1Layout k1_layout(uint32_t ppc, bool general, bool t
 }
 
 template <bool GENERAL, bool TABLES>
-__global__ void __launch_bounds__(K1_THREADS, TABLES ? 1 : (GENERAL ? 2 : 5))
+__global__ void __launch_bounds__(K1_THREADS, TABLES ? 1 : (GENERAL ? 3 : 5))
 score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
              const kgwe_pod_req* __restrict__ pods, uint32_t n_pods, uint32_t pods_per_chunk,
              const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
              kgwe_node_score* __restrict__ out, unsigned long long* __restrict__ best,
-             Params P, unsigned long long* __restrict__ counters, uint32_t mode, FusedTail tail) {
+             Params P, unsigned long long* __restrict__ counters, uint32_t mode, uint32_t mat_units, FusedTail tail) {
     extern __shared__ __align__(128) unsigned char smem[];
-    const K1Layout L = k1_layout(pods_per_chunk, GENERAL, TABLES, mode == K1_MODE_MEMO);
+    const K1Layout L = k1_layout(pods_per_chunk, GENERAL ? mat_units : 0u, TABLES, mode == K1_MODE_MEMO);
     PodLite* spod = reinterpret_cast<PodLite*>(smem + L.pods);
     uint32_t* keys = reinterpret_cast<uint32_t*>(smem + L.keys);
     uint8_t* slot_of = smem + L.slot;                                          // TABLES only
@@ -103,7 +104,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         NodeCtx c;
         node_ctx_core(c, rec, in_range);
         if (want_groups) node_ctx_group_tables(c, rec);
-        lane_node_init(ln, c, rec, GENERAL);
+        lane_node_init(ln, c, rec, GENERAL ? mat_units : 0u);
         lane_tables_build<GENERAL, TABLES>(ln, c, tb, rec, P.norm, mode, slot_of);
     }
     __syncthreads();

@@ -81,7 +81,7 @@ extern "C" int lane_emu_score_batch(const kgwe_config* cfg, const kgwe_node_imag
         node_ctx_core(c, rec, true);
         node_ctx_group_tables(c, rec);
         LaneNode ln;
-        lane_node_init(ln, c, rec, general != 0);
+        lane_node_init(ln, c, rec, general == 0 ? 0u : (uint32_t)general);
         int32_t topo[7] = {0}; uint32_t grp[6] = {0}, mig[3] = {0}; int2 memo[7]; int4 mat[32]; std::vector<uint32_t> subset(256, 0u);
         memset(memo, 0, sizeof memo); memset(mat, 0, sizeof mat);
         LaneTabs tb{topo, grp, mig, memo, mat, subset.data(), 1};

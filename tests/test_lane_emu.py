@@ -39,7 +39,7 @@ def run_emu(emu, abi, nodes, ledger, pods, hint, general, tables, mode, cfg=None
     return out, sc.value, rs.value
 
 
-VARIANTS = [(False, False), (True, False), (True, True)]
+VARIANTS = [(0, False), (16, False), (32, False), (32, True), (16, True)]      # (matrix units per lane, subset tables)
 
 
 @pytest.mark.parametrize("num,scale", [(1, 1.0), (2, 0.1), (3, 0.02), (5, 0.02)])
@@ -83,5 +83,5 @@ def test_non_default_weights(kg, orc, emu):
         cfg.topology_weight, cfg.resource_weight, cfg.balance_weight, cfg.hint_bonus, cfg.nvlink_norm_gbps = wt, wr, wb, bonus, norm
         hint = kg.synth.make_hint(len(pods), len(nodes), 0.2)
         ref, _, _ = orc.score_batch(abi, nodes, ledger, pods, hint=hint, want_scores=True, cfg=cfg)
-        got, _, _ = run_emu(emu, abi, nodes, ledger, pods, hint, False, False, MODE_FULL, cfg=cfg)
+        got, _, _ = run_emu(emu, abi, nodes, ledger, pods, hint, 0, False, MODE_FULL, cfg=cfg)
         assert got.tobytes() == ref.tobytes()
