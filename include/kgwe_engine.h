@@ -11,12 +11,19 @@
  * Conventions
  *  - Every function returns KGWE_OK (0) or a negative kgwe_status; nothing throws or
  *    aborts across this boundary.  kgwe_last_error() gives the message of the last
- *    failing call on that engine.
+ *    failing call made BY THE CALLING THREAD (kept per thread, so another thread's
+ *    failure cannot replace the text while it is being read).
  *  - All structs are plain old data with fixed-width fields.  Buffers are owned by
  *    the caller; the engine keeps no caller pointer after a call returns (cgo rule).
  *  - The engine owns its device memory and pinned staging.  One mutex per engine
  *    (mirrors `s.mu`, scheduler.go:17) makes every entry point callable from any
  *    thread; each call selects the engine's CUDA device first.
+ *  - The cluster image is double-buffered on the device: node upserts and ledger calls
+ *    only touch a host mirror; the next call that reads the image copies the pending
+ *    records into the image that is NOT being read, on a copy stream, and switches over
+ *    with event dependencies - no entry point synchronises the host with a stream to
+ *    apply updates.  Calls given different cuda_stream arguments are ordered one after
+ *    the other on the device the same way (the engine's scratch buffers are shared).
  *  - There is no CPU fallback: if CUDA is unavailable, kgwe_engine_create fails.
  *  - Canonical order: nodes are visited in ascending node index and
  *    ties on TotalScore resolve to the LOWEST node index; NUMA groups in ascending
@@ -224,9 +231,18 @@ void kgwe_config_default(kgwe_config* cfg);
 int kgwe_node_upsert(kgwe_engine* e, uint32_t local_idx, const kgwe_node_image* img);
 int kgwe_nodes_upsert(kgwe_engine* e, uint32_t first_local_idx, uint32_t count, const kgwe_node_image* imgs);
 int kgwe_node_remove(kgwe_engine* e, uint32_t local_idx);
+/* The same refresh for a node whose GPU LIST changed (a GPU fell off the bus, NVML enumerates in another order): the
+ * ledger names GPUs by their index in the list, the reference by UUID (scheduler.go:586-598), so the host - which knows
+ * the UUIDs - says where each old index went: old_to_new[i] = new index of the GPU that was at index i, -1 if it is gone
+ * (KGWE_MAX_GPUS entries; values must be distinct).  Every ledger entry on the node is moved accordingly before the new
+ * record is applied; an entry whose GPUs all vanished stays in the ledger and still counts as a workload on the node. */
+int kgwe_node_upsert_remap(kgwe_engine* e, uint32_t local_idx, const kgwe_node_image* img, const int8_t* old_to_new);
 
 /* Ledger.  Replaces recordAllocation (scheduler.go:695-707; same wl_id overwrites) and
- * ReleaseAllocation (scheduler.go:710-727; unknown id -> KGWE_ERR_NOT_FOUND). */
+ * ReleaseAllocation (scheduler.go:710-727; unknown id -> KGWE_ERR_NOT_FOUND).  A commit that names a GPU another
+ * workload already holds on that node is refused with KGWE_ERR_CONFLICT and changes nothing (tryScheduleOnNode's
+ * re-check, scheduler.go:634-640); a mask bit at or above the node's n_gpus is KGWE_ERR_INVALID_ARG.  Commits on an
+ * index whose record is absent are kept as they are (the reference's ledger is keyed by node name and outlives nodes). */
 int kgwe_alloc_commit(kgwe_engine* e, uint64_t wl_id, uint32_t local_idx, uint8_t gpu_mask);
 int kgwe_alloc_release(kgwe_engine* e, uint64_t wl_id);
 
@@ -417,6 +433,8 @@ int kgwe_snapshot_load(kgwe_engine* e, const void* buf, uint64_t len);
 /* Read one record back (device -> host) in ABI layout, ledger fields included. */
 int kgwe_node_read(kgwe_engine* e, uint32_t local_idx, kgwe_node_image* out);
 
+/* Counters so far.  Does not synchronise the device: kernels of asynchronous (device-pointer) calls that are still
+ * running show up in a later poll, and so do the K1 timings of launches that have not finished. */
 int kgwe_get_stats(kgwe_engine* e, kgwe_stats* out);
 const char* kgwe_last_error(kgwe_engine* e);
 const char* kgwe_version(void);

@@ -87,7 +87,7 @@ ENGINE_SYMBOLS = [
     "kgwe_version", "kgwe_score_top1_noalloc", "kgwe_topk_merge_host",
     "kgwe_schedule_gangs", "kgwe_placement_terms", "kgwe_mig_pack", "kgwe_mig_rebalance",
     "kgwe_topology_hint_batch", "kgwe_topology_gauges", "kgwe_score_batch_device_p2p",
-    "kgwe_snapshot_size", "kgwe_snapshot_save", "kgwe_snapshot_load",
+    "kgwe_snapshot_size", "kgwe_snapshot_save", "kgwe_snapshot_load", "kgwe_node_upsert_remap",
 ]
 NOALLOC_MAX_PODS = 16384
 
@@ -111,6 +111,7 @@ def load_engine_lib():
     lib.kgwe_config_default.restype = None
     lib.kgwe_node_upsert.argtypes = [vp, u32, vp]
     lib.kgwe_nodes_upsert.argtypes = [vp, u32, u32, vp]
+    lib.kgwe_node_upsert_remap.argtypes = [vp, u32, vp, vp]
     lib.kgwe_node_remove.argtypes = [vp, u32]
     lib.kgwe_alloc_commit.argtypes = [vp, u64, u32, u8]
     lib.kgwe_alloc_release.argtypes = [vp, u64]

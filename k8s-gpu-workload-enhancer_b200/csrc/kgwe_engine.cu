@@ -1,9 +1,11 @@
 // kgwe_engine.cu — host side of the engine and the C ABI of include/kgwe_engine.h.
 //
 // State (replaces TopologyAwareScheduler's fields, reference src/scheduler/scheduler.go:16-39):
-//   * cluster image: DevNode[max_nodes] in HBM + a pinned host mirror; upserts touch the mirror
-//     and a dirty list, and are flushed as coalesced H2D copies before the next scoring call
-//     (incremental, instead of discovery.go:290-319's full rebuild);
+//   * cluster image: TWO DevNode[max_nodes] images in HBM + a pinned host mirror.  Upserts and ledger calls
+//     touch the mirror and two dirty lists (one per image); the next call that reads the image copies the
+//     pending records into the SHADOW image on a copy stream, makes its own stream wait for that copy (an event,
+//     no host synchronisation) and swaps the two (incremental and double-buffered, instead of
+//     discovery.go:290-319's full rebuild): kernels still running on the old image are never written under;
 //   * ledger: wl_id -> (node, gpu mask) on the host; its per-node projection
 //     (allocated_mask, n_allocs) lives inside the node records, which is all the kernels need
 //     (replaces the three full ledger scans per (pod,node) at scheduler.go:587-593, 562-566);
@@ -80,10 +82,21 @@ struct kgwe_engine {
     int sched_tile_blocks_per_sm = 0;
     int k1_blocks_per_sm[4] = {5, 3, 2, 1};   // co-resident CTAs of K1's lean / GENERAL (int32 columns) / GENERAL (float64 columns) / TABLES variants
 
-    DevNode* d_nodes = nullptr;       // cluster image in HBM
-    DevNode* h_nodes = nullptr;       // pinned mirror (device layout)
-    std::vector<uint8_t> dirty_flag;
-    std::vector<uint32_t> dirty;
+    DevNode* d_img[2] = {nullptr, nullptr};   // the two cluster images in HBM
+    int front = 0;                    // the image scoring kernels read; the other one (shadow) receives the next updates
+    DevNode* d_nodes = nullptr;       // == d_img[front]
+    DevNode* h_nodes = nullptr;       // pinned mirror (device layout), authoritative
+    std::vector<uint8_t> dirty_flag[2];       // per image: records that differ from the mirror
+    std::vector<uint32_t> dirty[2];
+    cudaStream_t cstream = nullptr;   // copy stream of the image updates
+    cudaStream_t qstream = nullptr;   // counter read-back of kgwe_get_stats
+    cudaEvent_t ev_copy = nullptr;    // the latest batch of image copies
+    bool copy_pending = false;        // ev_copy may not have completed: the mirror records it reads must not change yet
+    cudaEvent_t ev_use[2] = {nullptr, nullptr};   // after the latest launch that reads image i
+    cudaEvent_t ev_last = nullptr;    // after the latest work of any entry point ...
+    cudaStream_t last_stream = nullptr;       // ... on this stream (the engine's scratch is shared between calls)
+    uint64_t epoch = 0;               // published image versions
+    uint64_t host_evaluations = 0;    // evaluations counted on the host (K1: pods x present records)
     uint32_t n_nodes = 0;             // high-water mark of present records
     uint32_t n_present = 0;
     uint32_t n_nonuniform = 0;        // present records whose active links are not all equal (K1 then needs its GENERAL variant)
@@ -112,15 +125,19 @@ struct kgwe_engine {
     int timers_pending = 0;
 
     kgwe_stats stats;
-    std::string err;
 };
 
 namespace {
 
+// The message of the last failing call is kept per THREAD: kgwe_last_error hands out a pointer, and a message stored in
+// the engine could be replaced (and freed) by another thread's failing call while the first thread still reads it.
+thread_local std::string tl_last_error;
+
 int fail(kgwe_engine* e, int code, const char* fmt, ...) {
     char buf[512];
     va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
-    if (e) e->err = buf;
+    (void)e;
+    tl_last_error = buf;
     return code;
 }
 #define CU(e, call) do { cudaError_t _c = (call); if (_c != cudaSuccess) return fail(e, KGWE_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(_c)); } while (0)
@@ -134,27 +151,55 @@ int to_device_record(kgwe_engine* e, const kgwe_node_image& in, DevNode& out) {
 inline uint32_t rec_nonuniform(const DevNode& r) { return ((r.flags & NODE_PRESENT) && r.pad1[0] == 0) ? 1u : 0u; }
 inline uint32_t rec_fractional(const DevNode& r) { return (rec_nonuniform(r) && !(r.flags & NODE_INTEGRAL)) ? 1u : 0u; }
 
-void mark_dirty(kgwe_engine* e, uint32_t idx) {
-    if (!e->dirty_flag[idx]) { e->dirty_flag[idx] = 1; e->dirty.push_back(idx); }
+void mark_dirty_image(kgwe_engine* e, int img, uint32_t idx) {
+    if (!e->dirty_flag[img][idx]) { e->dirty_flag[img][idx] = 1; e->dirty[img].push_back(idx); }
+}
+// A record of the mirror changed: both images are stale there.
+void mark_dirty(kgwe_engine* e, uint32_t idx) { mark_dirty_image(e, 0, idx); mark_dirty_image(e, 1, idx); }
+// A queue kernel committed on the front image itself and the mirror has followed: only the shadow is stale.
+void mark_dirty_shadow(kgwe_engine* e, uint32_t idx) { mark_dirty_image(e, 1 - e->front, idx); }
+
+// Called before the host changes a record of the pinned mirror: a copy batch may still be reading it.
+void wait_copy(kgwe_engine* e) {
+    if (e->copy_pending) { cudaEventSynchronize(e->ev_copy); e->copy_pending = false; }
 }
 
-// Coalesce dirty records into runs and copy them to the device image.
-int flush_dirty(kgwe_engine* e, cudaStream_t s) {
-    if (e->dirty.empty()) return KGWE_OK;
-    std::sort(e->dirty.begin(), e->dirty.end());
+// Start of every entry point that reads the image on stream s:
+//   - order s after the engine's previous work if that ran on another stream (scratch buffers are shared);
+//   - if the front image is stale, bring the SHADOW image up to date on the copy stream (waiting, on the device, for
+//     kernels that may still read it from the time it was front), let s wait for the copies, and swap.
+// No host synchronisation: the caller's stream only gets event dependencies.
+int publish(kgwe_engine* e, cudaStream_t s) {
+    if (e->last_stream && e->last_stream != s) CU(e, cudaStreamWaitEvent(s, e->ev_last, 0));
+    if (e->dirty[e->front].empty()) return KGWE_OK;
+    const int sh = 1 - e->front;
+    std::vector<uint32_t>& d = e->dirty[sh];
+    CU(e, cudaStreamWaitEvent(e->cstream, e->ev_use[sh], 0));
+    std::sort(d.begin(), d.end());
     size_t i = 0;
-    while (i < e->dirty.size()) {
+    while (i < d.size()) {
         size_t j = i + 1;
-        while (j < e->dirty.size() && e->dirty[j] == e->dirty[j - 1] + 1) ++j;
-        const uint32_t first = e->dirty[i], count = (uint32_t)(j - i);
-        CU(e, cudaMemcpyAsync(e->d_nodes + first, e->h_nodes + first, (size_t)count * sizeof(DevNode), cudaMemcpyHostToDevice, s));
+        while (j < d.size() && d[j] == d[j - 1] + 1) ++j;
+        const uint32_t first = d[i], count = (uint32_t)(j - i);
+        CU(e, cudaMemcpyAsync(e->d_img[sh] + first, e->h_nodes + first, (size_t)count * sizeof(DevNode), cudaMemcpyHostToDevice, e->cstream));
         e->stats.h2d_bytes += (uint64_t)count * sizeof(DevNode);
         i = j;
     }
-    for (uint32_t idx : e->dirty) e->dirty_flag[idx] = 0;
-    e->dirty.clear();
-    // the copies read the pinned mirror; finish them before any later upsert can touch it
-    CU(e, cudaStreamSynchronize(s));
+    for (uint32_t idx : d) e->dirty_flag[sh][idx] = 0;
+    d.clear();
+    CU(e, cudaEventRecord(e->ev_copy, e->cstream));
+    e->copy_pending = true;
+    CU(e, cudaStreamWaitEvent(s, e->ev_copy, 0));
+    e->front = sh; e->d_nodes = e->d_img[sh]; e->epoch++;
+    return KGWE_OK;
+}
+int flush_dirty(kgwe_engine* e, cudaStream_t s) { return publish(e, s); }
+
+// End of every entry point that launched work on s.
+int note_use(kgwe_engine* e, cudaStream_t s) {
+    CU(e, cudaEventRecord(e->ev_use[e->front], s));
+    CU(e, cudaEventRecord(e->ev_last, s));
+    e->last_stream = s;
     return KGWE_OK;
 }
 
@@ -222,6 +267,7 @@ int launch_k1(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const
     CU(e, cudaGetLastError());
     if (timed) { CU(e, cudaEventRecord(e->t1[e->timers_pending], s)); e->timers_pending++; }
     e->stats.kernel_launches++;
+    e->host_evaluations += (uint64_t)n_pods * e->n_present;
     e->stats.evaluations += (uint64_t)n_pods * e->n_present;
     return KGWE_OK;
 }
@@ -278,10 +324,15 @@ int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, co
     return KGWE_OK;
 }
 
+// Device counters are monotonic (never reset): reading them needs no exclusion against running kernels.
 int pull_counters(kgwe_engine* e, cudaStream_t s) {
     CU(e, cudaMemcpyAsync(e->h_counters, e->d_counters, kCounters * sizeof(unsigned long long), cudaMemcpyDeviceToHost, s));
-    CU(e, cudaMemsetAsync(e->d_counters, 0, kCounters * sizeof(unsigned long long), s));
     return KGWE_OK;
+}
+void fold_counters(kgwe_engine* e) {      // after the copy of pull_counters has completed
+    e->stats.evaluations = e->host_evaluations + e->h_counters[0];
+    e->stats.candidates = e->h_counters[1];
+    e->stats.candidates_resolved = e->h_counters[2];
 }
 
 int ledger_apply(kgwe_engine* e, uint64_t wl_id, uint32_t idx, uint8_t mask, bool touch_device) {
@@ -321,6 +372,12 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
     auto bad_w = [](int w) { return w < -1000 || w > 1000; };
     if (bad_w(cfg->topology_weight) || bad_w(cfg->resource_weight) || bad_w(cfg->balance_weight) || bad_w(cfg->hint_bonus)) return KGWE_ERR_INVALID_ARG;
     if (!(cfg->nvlink_norm_gbps >= 400.0) || !(cfg->nvlink_norm_gbps <= 1e6)) return KGWE_ERR_INVALID_ARG;   // keeps TopologyScore inside int16
+    {   // K1 ranks with 32-bit keys (TotalScore << 7 | node-in-tile): with TopologyScore <= 12,550 (links <= 1e5 GB/s at norm >= 400),
+        // Resource / Balance <= 100 and these weights, TotalScore stays below 2^24
+        auto ab = [](long long v) { return v < 0 ? -v : v; };
+        const long long max_total = (12550 * ab(cfg->topology_weight) + 100 * ab(cfg->resource_weight) + 100 * ab(cfg->balance_weight)) / 100 + ab(cfg->hint_bonus);
+        if (max_total >= (1ll << 24)) return KGWE_ERR_INVALID_ARG;
+    }
     *out = nullptr;
     int n_dev = 0;
     if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0 || cfg->device < 0 || cfg->device >= n_dev) return KGWE_ERR_NO_DEVICE;
@@ -332,19 +389,23 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
     memset(&e->stats, 0, sizeof e->stats);
     bool ok = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess
            && cudaEventCreate(&e->ev0) == cudaSuccess && cudaEventCreate(&e->ev1) == cudaSuccess
-           && cudaMalloc(&e->d_nodes, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
+           && cudaMalloc(&e->d_img[0], (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess && cudaMalloc(&e->d_img[1], (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
+           && cudaStreamCreateWithFlags(&e->cstream, cudaStreamNonBlocking) == cudaSuccess && cudaStreamCreateWithFlags(&e->qstream, cudaStreamNonBlocking) == cudaSuccess
+           && cudaEventCreateWithFlags(&e->ev_copy, cudaEventDisableTiming) == cudaSuccess && cudaEventCreateWithFlags(&e->ev_last, cudaEventDisableTiming) == cudaSuccess
+           && cudaEventCreateWithFlags(&e->ev_use[0], cudaEventDisableTiming) == cudaSuccess && cudaEventCreateWithFlags(&e->ev_use[1], cudaEventDisableTiming) == cudaSuccess
            && cudaMallocHost(&e->h_nodes, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
            && cudaMalloc(&e->d_counters, kCounters * sizeof(unsigned long long)) == cudaSuccess
            && cudaMallocHost(&e->h_counters, kCounters * sizeof(unsigned long long)) == cudaSuccess
            && cudaMalloc(&e->d_done, sizeof(unsigned int)) == cudaSuccess && cudaMemset(e->d_done, 0, sizeof(unsigned int)) == cudaSuccess
            && cudaMallocHost(&e->h_flag, sizeof(unsigned int)) == cudaSuccess
-           && cudaMemset(e->d_nodes, 0, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
+           && cudaMemset(e->d_img[0], 0, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess && cudaMemset(e->d_img[1], 0, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
            && cudaMemset(e->d_counters, 0, kCounters * sizeof(unsigned long long)) == cudaSuccess;
     if (ok) {
         memset(e->h_nodes, 0, (size_t)cfg->max_nodes * sizeof(DevNode));
         for (int i = 0; i < kCounters; ++i) e->h_counters[i] = 0;
         *e->h_flag = 0;
-        e->dirty_flag.assign(cfg->max_nodes, 0);
+        e->dirty_flag[0].assign(cfg->max_nodes, 0); e->dirty_flag[1].assign(cfg->max_nodes, 0);
+        e->d_nodes = e->d_img[0];
         cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, cfg->device);
         for (int i = 0; i < kgwe_engine::kTimers && ok; ++i) ok = cudaEventCreate(&e->t0[i]) == cudaSuccess && cudaEventCreate(&e->t1[i]) == cudaSuccess;
         {
@@ -377,7 +438,13 @@ int kgwe_engine_destroy(kgwe_engine* e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     e->d_pods.release(); e->d_hint.release(); e->d_best.release(); e->d_arrive.release(); e->d_gang.release(); e->d_topk.release(); e->d_scores.release();
     e->h_pods.release(); e->h_topk.release(); e->h_hint.release();
-    if (e->d_nodes) cudaFree(e->d_nodes);
+    if (e->cstream) cudaStreamSynchronize(e->cstream);
+    if (e->qstream) cudaStreamSynchronize(e->qstream);
+    for (int i = 0; i < 2; ++i) { if (e->d_img[i]) cudaFree(e->d_img[i]); if (e->ev_use[i]) cudaEventDestroy(e->ev_use[i]); }
+    if (e->ev_copy) cudaEventDestroy(e->ev_copy);
+    if (e->ev_last) cudaEventDestroy(e->ev_last);
+    if (e->cstream) cudaStreamDestroy(e->cstream);
+    if (e->qstream) cudaStreamDestroy(e->qstream);
     if (e->h_nodes) cudaFreeHost(e->h_nodes);
     if (e->d_counters) cudaFree(e->d_counters);
     if (e->h_counters) cudaFreeHost(e->h_counters);
@@ -391,35 +458,75 @@ int kgwe_engine_destroy(kgwe_engine* e) {
     return KGWE_OK;
 }
 
+// Ledger projection of one node from the ledger itself.
+static void recount_node(kgwe_engine* e, uint32_t node) {
+    uint8_t m = 0; uint32_t n = 0;
+    for (auto& kv : e->ledger) if (kv.second.node == node) { m |= kv.second.mask; n++; }
+    e->h_nodes[node].allocated_mask = m; e->h_nodes[node].n_allocs = n;
+}
+
+// One record into the mirror (mutex held).  old_to_new (nullable): the GPU list of the node changed - see kgwe_node_upsert_remap.
+static int upsert_one(kgwe_engine* e, uint32_t idx, const kgwe_node_image& img, const int8_t* old_to_new) {
+    DevNode rec;
+    int rc = to_device_record(e, img, rec);
+    if (rc != KGWE_OK) return rc;
+    if (old_to_new)
+        for (int g = 0; g < KGWE_MAX_GPUS; ++g)
+            if (old_to_new[g] >= (int)rec.n_gpus) return fail(e, KGWE_ERR_INVALID_ARG, "old_to_new[%d] = %d names a GPU the new record does not have (%u GPUs)", g, old_to_new[g], rec.n_gpus);
+    wait_copy(e);
+    DevNode& dst = e->h_nodes[idx];
+    const bool was = dst.flags & 1;
+    if (old_to_new) {
+        // the ledger names GPUs by their index in the OLD list: move every entry of this node to the new indices
+        // (the reference keys allocations by GPU UUID, scheduler.go:586-598, so they follow the GPU, not the slot)
+        for (auto& kv : e->ledger) {
+            if (kv.second.node != idx) continue;
+            uint8_t m = 0;
+            for (int g = 0; g < KGWE_MAX_GPUS; ++g)
+                if ((kv.second.mask >> g & 1) && old_to_new[g] >= 0) m |= (uint8_t)(1u << old_to_new[g]);
+            kv.second.mask = m;              // an entry whose GPUs all vanished still counts as a workload on the node (scheduler.go:561-566)
+        }
+    }
+    e->n_nonuniform += rec_nonuniform(rec) - rec_nonuniform(dst);
+    e->n_fractional += rec_fractional(rec) - rec_fractional(dst);
+    if (was && !old_to_new) { rec.allocated_mask = dst.allocated_mask; rec.n_allocs = dst.n_allocs; dst = rec; }     // ledger-owned fields survive a refresh
+    else {
+        // a node (re)appearing under an index the ledger still names gets its allocations back, as the
+        // reference's name-keyed ledger would match them again (scheduler.go:587-593)
+        dst = rec;
+        recount_node(e, idx);
+    }
+    if (!was) e->n_present++;
+    mark_dirty(e, idx);
+    e->n_nodes = std::max(e->n_nodes, idx + 1);
+    return KGWE_OK;
+}
+
 int kgwe_nodes_upsert(kgwe_engine* e, uint32_t first, uint32_t count, const kgwe_node_image* imgs) {
     if (!e || (!imgs && count)) return KGWE_ERR_INVALID_ARG;
     std::lock_guard<std::mutex> lk(e->mu);
     if ((uint64_t)first + count > e->cfg.max_nodes) return fail(e, KGWE_ERR_OUT_OF_RANGE, "nodes [%u,%u) exceed max_nodes %u", first, first + count, e->cfg.max_nodes);
     for (uint32_t i = 0; i < count; ++i) {
-        DevNode rec;
-        int rc = to_device_record(e, imgs[i], rec);
+        int rc = upsert_one(e, first + i, imgs[i], nullptr);
         if (rc != KGWE_OK) return rc;
-        DevNode& dst = e->h_nodes[first + i];
-        const bool was = dst.flags & 1;
-        if (was) { rec.allocated_mask = dst.allocated_mask; rec.n_allocs = dst.n_allocs; }     // ledger-owned fields survive a refresh
-        else {
-            // a node (re)appearing under an index the ledger still names gets its allocations back, as the
-            // reference's name-keyed ledger would match them again (scheduler.go:587-593)
-            uint8_t m = 0; uint32_t n = 0;
-            for (auto& kv : e->ledger) if (kv.second.node == first + i) { m |= kv.second.mask; n++; }
-            rec.allocated_mask = m; rec.n_allocs = n;
-        }
-        e->n_nonuniform += rec_nonuniform(rec) - rec_nonuniform(dst);
-        e->n_fractional += rec_fractional(rec) - rec_fractional(dst);
-        dst = rec;
-        if (!was) e->n_present++;
-        mark_dirty(e, first + i);
-        e->n_nodes = std::max(e->n_nodes, first + i + 1);
     }
     return KGWE_OK;
 }
 
 int kgwe_node_upsert(kgwe_engine* e, uint32_t idx, const kgwe_node_image* img) { return kgwe_nodes_upsert(e, idx, 1, img); }
+
+int kgwe_node_upsert_remap(kgwe_engine* e, uint32_t idx, const kgwe_node_image* img, const int8_t* old_to_new) {
+    if (!e || !img || !old_to_new) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (idx >= e->cfg.max_nodes) return fail(e, KGWE_ERR_OUT_OF_RANGE, "node %u out of range", idx);
+    uint32_t seen = 0;
+    for (int g = 0; g < KGWE_MAX_GPUS; ++g) {
+        if (old_to_new[g] < 0) continue;
+        if (old_to_new[g] >= KGWE_MAX_GPUS || (seen >> old_to_new[g] & 1)) return fail(e, KGWE_ERR_INVALID_ARG, "old_to_new is not an injective map into 0..%d", KGWE_MAX_GPUS - 1);
+        seen |= 1u << old_to_new[g];
+    }
+    return upsert_one(e, idx, *img, old_to_new);
+}
 
 int kgwe_node_remove(kgwe_engine* e, uint32_t idx) {
     if (!e) return KGWE_ERR_INVALID_ARG;
@@ -431,6 +538,7 @@ int kgwe_node_remove(kgwe_engine* e, uint32_t idx) {
     // in the ledger (they are keyed by node name there) and simply stop matching any node - until a
     // node comes back under the same index (see kgwe_nodes_upsert).  n_nodes is a high-water mark and
     // does not shrink, so the stride of score matrices and hint rows stays what the host knows.
+    wait_copy(e);
     e->n_nonuniform -= rec_nonuniform(dst);
     e->n_fractional -= rec_fractional(dst);
     memset(&dst, 0, sizeof dst);
@@ -443,6 +551,16 @@ int kgwe_alloc_commit(kgwe_engine* e, uint64_t wl_id, uint32_t idx, uint8_t gpu_
     if (!e) return KGWE_ERR_INVALID_ARG;
     std::lock_guard<std::mutex> lk(e->mu);
     if (idx >= e->cfg.max_nodes) return fail(e, KGWE_ERR_OUT_OF_RANGE, "node %u out of range", idx);
+    const DevNode& rec = e->h_nodes[idx];
+    if (rec.flags & NODE_PRESENT) {
+        // tryScheduleOnNode re-checks that none of the selected GPUs is in any allocation (scheduler.go:634-640); the entry
+        // this workload id already holds does not count, recordAllocation replaces it (:699)
+        if (gpu_mask >> rec.n_gpus) return fail(e, KGWE_ERR_INVALID_ARG, "gpu_mask 0x%02x names a GPU node %u does not have (%u GPUs)", gpu_mask, idx, rec.n_gpus);
+        uint8_t others = 0;
+        for (auto& kv : e->ledger) if (kv.second.node == idx && kv.first != wl_id) others |= kv.second.mask;
+        if (others & gpu_mask) return fail(e, KGWE_ERR_CONFLICT, "GPUs 0x%02x of node %u are already allocated", others & gpu_mask, idx);
+    }
+    wait_copy(e);
     return ledger_apply(e, wl_id, idx, gpu_mask, true);
 }
 
@@ -453,10 +571,8 @@ int kgwe_alloc_release(kgwe_engine* e, uint64_t wl_id) {
     if (it == e->ledger.end()) return fail(e, KGWE_ERR_NOT_FOUND, "allocation not found for workload %llu", (unsigned long long)wl_id);
     const uint32_t node = it->second.node;
     e->ledger.erase(it);
-    DevNode& rec = e->h_nodes[node];
-    uint8_t m = 0; uint32_t n = 0;
-    for (auto& kv : e->ledger) if (kv.second.node == node) { m |= kv.second.mask; n++; }
-    rec.allocated_mask = m; rec.n_allocs = n;
+    wait_copy(e);
+    recount_node(e, node);
     mark_dirty(e, node);
     return KGWE_OK;
 }
@@ -476,7 +592,9 @@ int kgwe_score_batch_device(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t
         CU(e, e->d_scores.ensure((size_t)n_pods * e->n_nodes));
         scores = e->d_scores.p;
     }
-    return launch_score(e, d_pods, n_pods, d_hint, scores, topk, d_topk, s);
+    rc = launch_score(e, d_pods, n_pods, d_hint, scores, topk, d_topk, s);
+    if (rc != KGWE_OK) return rc;
+    return note_use(e, s);
 }
 
 int kgwe_score_batch_device_p2p(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const uint8_t* d_hint,
@@ -501,7 +619,7 @@ int kgwe_score_batch_device_p2p(kgwe_engine* e, const kgwe_pod_req* d_pods, uint
     finalize_top1_p2p_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), best, peers, n_ranks, my_rank, e->params);
     CU(e, cudaGetLastError());
     e->stats.kernel_launches++;
-    return KGWE_OK;
+    return note_use(e, s);
 }
 
 int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, const uint8_t* hint,
@@ -537,15 +655,24 @@ int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, 
         // stream now and then so a failed launch cannot spin forever
         volatile unsigned int* flag = e->h_flag;
         const auto t0 = std::chrono::steady_clock::now();
+        const char* trouble = nullptr; cudaError_t q = cudaSuccess;
         for (uint32_t spins = 0; *flag != e->flag_seq; ++spins) {
             if ((spins & 0x3fff) == 0x3fff) {
-                const cudaError_t q = cudaStreamQuery(s);
-                if (q == cudaSuccess) { if (*flag != e->flag_seq) return fail(e, KGWE_ERR_CUDA, "latency path: kernel finished without raising its flag (flag %u, expected %u)", *flag, e->flag_seq); break; }
-                if (q != cudaErrorNotReady) return fail(e, KGWE_ERR_CUDA, "latency path: %s", cudaGetErrorString(q));
-                if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > 5.0)
-                    return fail(e, KGWE_ERR_CUDA, "latency path: no answer from the GPU after 5 s (flag %u, expected %u)", *flag, e->flag_seq);
+                q = cudaStreamQuery(s);
+                if (q == cudaSuccess) { if (*flag != e->flag_seq) trouble = "kernel finished without raising its flag"; break; }
+                if (q != cudaErrorNotReady) { trouble = cudaGetErrorString(q); break; }
+                if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > 5.0) { trouble = "no answer from the GPU after 5 s"; break; }
             }
         }
+        if (trouble) {
+            // leave the ticket counter of the fused tail at zero for the next call, whatever state the launch ended in
+            cudaStreamSynchronize(s);
+            cudaMemsetAsync(e->d_done, 0, sizeof(unsigned int), s);
+            cudaStreamSynchronize(s);
+            cudaGetLastError();
+            return fail(e, KGWE_ERR_CUDA, "latency path: %s (flag %u, expected %u)", trouble, *flag, e->flag_seq);
+        }
+        note_use(e, s);
         memcpy(out_topk, e->h_topk.p, (size_t)n_pods * sizeof(kgwe_placement));
         e->stats.h2d_bytes += (uint64_t)n_pods * sizeof(kgwe_pod_req) + (hint ? (uint64_t)n_pods * row : 0);
         e->stats.d2h_bytes += (uint64_t)n_pods * sizeof(kgwe_placement);
@@ -587,7 +714,7 @@ int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, 
         if (rc != KGWE_OK) return rc;
         CU(e, cudaStreamSynchronize(s));
         if (topk) memcpy(out_topk + (size_t)p0 * topk, e->h_topk.p, (size_t)np * topk * sizeof(kgwe_placement));
-        e->stats.candidates += e->h_counters[1]; e->stats.candidates_resolved += e->h_counters[2];
+        fold_counters(e);
         float ms = 0.f;
         if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) == cudaSuccess) gpu_ms += ms;
     }
@@ -698,8 +825,7 @@ static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t 
     CU(e, cudaStreamSynchronize(s));
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) == cudaSuccess) *gpu_ms += ms;
-    e->stats.evaluations += e->h_counters[0];
-    e->stats.candidates += e->h_counters[1]; e->stats.candidates_resolved += e->h_counters[2];
+    fold_counters(e);
     return KGWE_OK;
 }
 
@@ -708,9 +834,11 @@ static void apply_commit(kgwe_engine* e, uint64_t wl_id, const kgwe_placement& d
     e->stats.scheduled++;
     if (d.topology >= 80) e->stats.topology_optimal++;
     const uint32_t local = d.node_idx - e->cfg.node_base;
+    wait_copy(e);
     DevNode& rec = e->h_nodes[local];
     rec.allocated_mask |= d.gpu_mask; rec.n_allocs++;
     e->ledger[wl_id] = LedgerEntry{local, d.gpu_mask};
+    mark_dirty_shadow(e, local);          // the queue kernel committed on the front image itself; the other image has to follow
 }
 
 static void no_node(kgwe_placement& p, uint8_t flags) { memset(&p, 0, sizeof p); p.node_idx = KGWE_NO_NODE; p.flags = flags; }
@@ -759,12 +887,7 @@ int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pod
             e->ledger.erase(pods[p0 + i].wl_id);
             apply_commit(e, pods[p0 + i].wl_id, d);
             const uint32_t local = d.node_idx - e->cfg.node_base;
-            for (uint32_t nd : {old_node, local}) {
-                uint8_t m = 0; uint32_t n = 0;
-                for (auto& kv : e->ledger) if (kv.second.node == nd) { m |= kv.second.mask; n++; }
-                e->h_nodes[nd].allocated_mask = m; e->h_nodes[nd].n_allocs = n;
-                mark_dirty(e, nd);
-            }
+            for (uint32_t nd : {old_node, local}) { recount_node(e, nd); mark_dirty(e, nd); }
         }
         p0 = p1;
     }
@@ -1079,13 +1202,33 @@ int kgwe_snapshot_load(kgwe_engine* e, const void* buf, uint64_t len) {
         if (en.node >= e->cfg.max_nodes) return fail(e, KGWE_ERR_INVALID_ARG, "snapshot ledger entry names node %u", en.node);
     }
     const uint32_t old_n = e->n_nodes;
+    wait_copy(e);
     memcpy(e->h_nodes, p, (size_t)h.n_nodes * sizeof(DevNode));
-    for (uint32_t i = 0; i < h.n_nodes; ++i) set_uniform_unit(e->h_nodes[i]);      // derived field: never trusted from a blob
     for (uint32_t i = h.n_nodes; i < old_n; ++i) memset(&e->h_nodes[i], 0, sizeof(DevNode));
     e->ledger.clear();
     for (uint64_t i = 0; i < h.n_ledger; ++i) {
         SnapEntry en; memcpy(&en, pl + i * sizeof(SnapEntry), sizeof en);
         e->ledger[en.wl_id] = LedgerEntry{en.node, (uint8_t)en.mask};
+    }
+    // everything that can be derived is derived again, never trusted from a blob: masks cut to n_gpus, the whole-number and
+    // uniform-link flags from the bandwidths, the ledger projection from the blob's own ledger
+    for (uint32_t i = 0; i < h.n_nodes; ++i) {
+        DevNode& r = e->h_nodes[i];
+        if (!(r.flags & NODE_PRESENT)) { memset(&r, 0, sizeof r); continue; }
+        const uint8_t gm = (uint8_t)((1u << r.n_gpus) - 1u);
+        for (int g = 0; g < KGWE_MAX_GPUS; ++g) {
+            r.act_in[g] &= gm; r.present[g] &= gm;
+            if (g >= r.n_gpus) { r.act_in[g] = 0; r.present[g] = 0; }
+            r.act_in[g] &= (uint8_t)~(1u << g); r.present[g] &= (uint8_t)~(1u << g);
+        }
+        r.healthy_mask &= gm; r.mig_enabled_mask &= gm; r.mig_has_free_mask &= r.mig_enabled_mask;
+        r.flags = NODE_PRESENT | (record_is_integral(r) ? NODE_INTEGRAL : 0);
+        set_uniform_unit(r);
+        r.allocated_mask = 0; r.n_allocs = 0;
+    }
+    for (auto& kv : e->ledger) {
+        DevNode& r = e->h_nodes[kv.second.node];
+        if (r.flags & NODE_PRESENT) { r.allocated_mask |= kv.second.mask; r.n_allocs++; }       // (entries naming an absent record wait for the node to come back, see upsert_one)
     }
     e->n_nodes = std::max(h.n_nodes, old_n);          // high-water mark never shrinks (absent records score as absent)
     e->n_present = 0; e->n_nonuniform = 0; e->n_fractional = 0;
@@ -1110,26 +1253,31 @@ int kgwe_node_read(kgwe_engine* e, uint32_t idx, kgwe_node_image* out) {
 int kgwe_get_stats(kgwe_engine* e, kgwe_stats* out) {
     if (!e || !out) return KGWE_ERR_INVALID_ARG;
     std::lock_guard<std::mutex> lk(e->mu);
-    for (int i = 0; i < e->timers_pending; ++i) {       // harvest K1 timings (waits for those launches)
+    // K1 timings of launches that have finished (no waiting: unfinished ones stay for the next poll)
+    int kept = 0;
+    for (int i = 0; i < e->timers_pending; ++i) {
         float ms = 0.f;
-        if (cudaEventSynchronize(e->t1[i]) == cudaSuccess && cudaEventElapsedTime(&ms, e->t0[i], e->t1[i]) == cudaSuccess) {
-            e->stats.score_kernel_ms += ms; e->stats.score_kernel_timed++;
+        if (kept == 0 && cudaEventQuery(e->t1[i]) == cudaSuccess) {
+            if (cudaEventElapsedTime(&ms, e->t0[i], e->t1[i]) == cudaSuccess) { e->stats.score_kernel_ms += ms; e->stats.score_kernel_timed++; }
+        } else {
+            std::swap(e->t0[kept], e->t0[i]); std::swap(e->t1[kept], e->t1[i]); ++kept;
         }
     }
-    e->timers_pending = 0;
-    // fold in candidates counted by asynchronous (device-pointer) calls since the last pull
-    if (cudaSetDevice(e->cfg.device) == cudaSuccess && cudaDeviceSynchronize() == cudaSuccess &&
-        cudaMemcpy(e->h_counters, e->d_counters, kCounters * sizeof(unsigned long long), cudaMemcpyDeviceToHost) == cudaSuccess &&
-        cudaMemset(e->d_counters, 0, kCounters * sizeof(unsigned long long)) == cudaSuccess) {
-        e->stats.candidates += e->h_counters[1]; e->stats.candidates_resolved += e->h_counters[2];
-    }
+    e->timers_pending = kept;
+    // Device counters are monotonic, so they can be read on a stream of their own while kernels run: no device-wide
+    // synchronisation; work still in flight is counted by a later poll.
+    if (cudaSetDevice(e->cfg.device) == cudaSuccess &&
+        cudaMemcpyAsync(e->h_counters, e->d_counters, kCounters * sizeof(unsigned long long), cudaMemcpyDeviceToHost, e->qstream) == cudaSuccess &&
+        cudaStreamSynchronize(e->qstream) == cudaSuccess)
+        fold_counters(e);
+    else cudaGetLastError();
     *out = e->stats;
     out->n_nodes = e->n_nodes;
     out->n_allocations = (uint32_t)e->ledger.size();
     return KGWE_OK;
 }
 
-const char* kgwe_last_error(kgwe_engine* e) { return e ? e->err.c_str() : "null engine"; }
+const char* kgwe_last_error(kgwe_engine* e) { (void)e; return tl_last_error.c_str(); }
 
 }  // extern "C"
 
@@ -1187,5 +1335,5 @@ extern "C" int kgwe_score_top1_noalloc(kgwe_engine* e, const kgwe_pod_req* d_pod
     finalize_top1_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), keys, d_top1, 1, e->params);
     CU(e, cudaGetLastError());
     e->stats.kernel_launches++;
-    return KGWE_OK;
+    return note_use(e, s);
 }

@@ -51,6 +51,13 @@ class Engine:
         img = np.ascontiguousarray(image, dtype=abi.NODE_IMAGE).reshape(1)
         self._check(self.lib.kgwe_node_upsert(self.h, idx, abi.ptr(img)))
 
+    def upsert_node_remap(self, idx, image, old_to_new):
+        """Refresh of a node whose GPU list changed: old_to_new[i] = new index of the GPU formerly at index i, -1 if gone."""
+        img = np.ascontiguousarray(image, dtype=abi.NODE_IMAGE).reshape(1)
+        m = np.full(abi.MAX_GPUS, -1, dtype=np.int8)
+        m[: len(old_to_new)] = old_to_new
+        self._check(self.lib.kgwe_node_upsert_remap(self.h, idx, abi.ptr(img), abi.ptr(m)))
+
     def remove_node(self, idx):
         self._check(self.lib.kgwe_node_remove(self.h, idx))
 

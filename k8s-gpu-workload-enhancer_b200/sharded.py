@@ -32,6 +32,7 @@ class ShardedScorer:
         self.eng, self.n_local, self.world, self.dist, self.sptr, self.rank = engine, n_local, world, dist, stream_ptr, rank
         self.p2p = None            # (symmetric-memory tensor [2, world, P, 32], handle) when the fused exchange is on
         self.step_no = 0
+        self._torch, self._ext = None, None      # torch and the engine's stream as a torch stream (set by alloc)
 
     def enable_p2p(self, torch, dev, n_pods):
         """Fused exchange for top-1 batches: the finalisation kernel stores straight into every rank's
@@ -54,13 +55,24 @@ class ShardedScorer:
     def alloc(self, torch, dev, n_pods, topk, with_matrix=True):
         it = abi.PLACEMENT.itemsize
         self.P, self.topk = n_pods, topk
+        self._torch = torch
+        self._ext = torch.cuda.ExternalStream(self.sptr, device=dev) if self.sptr else None
         self.d_scores = torch.empty((n_pods, self.n_local, abi.NODE_SCORE.itemsize), dtype=torch.uint8, device=dev) if with_matrix else None
         self.d_top = torch.empty((n_pods, topk, it), dtype=torch.uint8, device=dev)
         self.d_gather = torch.empty((self.world, n_pods, topk, it), dtype=torch.uint8, device=dev) if self.world > 1 else None
         self.d_merged = torch.empty((n_pods, topk, it), dtype=torch.uint8, device=dev) if self.world > 1 else self.d_top
 
     def step(self, d_pods, d_hint=None):
-        """One batch: local scoring (+ matrix), all-gather of local top-k, merge.  Asynchronous."""
+        """One batch: local scoring (+ matrix), all-gather of local top-k, merge.  Asynchronous.
+        The engine's kernels run on the stream given at construction; the cross-GPU barrier and the NCCL all-gather
+        run on torch's CURRENT stream, so for the duration of the step that is made the same stream - otherwise
+        P2P stores -> barrier -> merge would only be ordered by luck."""
+        if self.world > 1 and self._ext is not None:
+            with self._torch.cuda.stream(self._ext):
+                return self._step(d_pods, d_hint)
+        return self._step(d_pods, d_hint)
+
+    def _step(self, d_pods, d_hint=None):
         sc = self.d_scores.data_ptr() if self.d_scores is not None else None
         if self.p2p is not None and self.topk == 1 and self.world > 1:
             buf, hdl, ptrs = self.p2p
@@ -80,12 +92,15 @@ class ShardedScorer:
         return self.d_merged
 
 
-def schedule_queue_sharded(dist, rank, world, shard, pods, score_top1, commit, hint=None, device=None, torch=None):
+def schedule_queue_sharded(dist, rank, world, shard, pods, score_top1, commit, hint=None, device=None, torch=None, release=None):
     """Stateful Schedule() over a node-sharded cluster: per workload every rank scores its
     shard (top-1, global node index), ONE small all-gather of the 32-byte placements, the identical merge on
     every rank (score desc, node index asc), and the rank that owns the winning node commits it.
       score_top1(pod_array_of_1, hint_row_or_None) -> PLACEMENT record of this shard's best node
       commit(wl_id, local_node_idx, gpu_mask)
+      release(wl_id)   (optional) drop this rank's entry for wl_id if it has one; called on EVERY rank before the owner
+                       commits, because recordAllocation overwrites by UID (scheduler.go:699) and the workload's
+                       previous entry may live in another shard
     `shard` = (lo, hi) node range of this rank.  Exact, but it pays a collective per workload: for clusters
     that fit one GPU (10k nodes = 7.68 MB) kgwe_schedule_queue on one engine is the fast path."""
     lo, hi = shard
@@ -104,6 +119,9 @@ def schedule_queue_sharded(dist, rank, world, shard, pods, score_top1, commit, h
             lists = local.reshape(1, 1, 1)
         best = merge_host(lists, 1)[0, 0]
         out[i] = best
-        if best["node_idx"] != abi.NO_NODE and lo <= int(best["node_idx"]) < hi:
-            commit(int(pods[i]["wl_id"]), int(best["node_idx"]) - lo, int(best["gpu_mask"]))
+        if best["node_idx"] != abi.NO_NODE:
+            if release is not None:
+                release(int(pods[i]["wl_id"]))
+            if lo <= int(best["node_idx"]) < hi:
+                commit(int(pods[i]["wl_id"]), int(best["node_idx"]) - lo, int(best["gpu_mask"]))
     return out

@@ -156,7 +156,19 @@ def life_cycle_seed(kg, orc, seed, n_ops=80):
             wl = sorted(ledger)[int(rng.randint(0, len(ledger) - 1, 1)[0])] if (ledger and rng.uniform(1)[0] < 0.3) else next_wl[0]
             next_wl[0] += 1
             i, m = int(rng.randint(0, N - 1, 1)[0]), int(rng.randint(1, 255, 1)[0])
-            eng.commit(wl, i, m); ledger[wl] = (i, m)
+            # what the engine must answer: a present node refuses GPUs it does not have and GPUs another workload holds
+            others = 0
+            for w2, (n2, m2) in ledger.items():
+                if n2 == i and w2 != wl:
+                    others |= m2
+            bad = present[i] and ((m >> int(nodes["n_gpus"][i])) != 0 or (others & m) != 0)
+            if bad:
+                try:
+                    eng.commit(wl, i, m); raise AssertionError(f"seed {seed}: a conflicting commit succeeded")
+                except kg.EngineError as ex:
+                    assert ex.code in (-1, -6)
+            else:
+                eng.commit(wl, i, m); ledger[wl] = (i, m)
         elif op == 3:                                 # release (known or unknown)
             if ledger and rng.uniform(1)[0] < 0.8:
                 wl = sorted(ledger)[int(rng.randint(0, len(ledger) - 1, 1)[0])]

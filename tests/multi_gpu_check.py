@@ -54,11 +54,19 @@ def main():
         if rank == 0:
             print(f"fused P2P exchange: {'on' if p2p_on else 'unavailable (NCCL path used)'}")
         # stateful queue over the sharded cluster: per-workload all-gather, owner rank commits
-        qpods = pods[:120]
+        qpods = pods[:120].copy()
+        qpods["wl_id"][90:] = qpods["wl_id"][10:40]      # scheduled again: the previous entry may live on another rank
+
+        def release_if_held(wl):
+            try:
+                eng.release(wl)
+            except kg.EngineError as ex:
+                assert ex.code == -5          # KGWE_ERR_NOT_FOUND: this rank held nothing for it
+
         got_q = kg.sharded.schedule_queue_sharded(
             dist, rank, world, (lo, hi), qpods,
             lambda pod, h: eng.score_batch(pod, hi - lo, want_scores=False, topk=1)[1][0, 0],
-            lambda wl, n, m: eng.commit(wl, n, m), device=dev, torch=torch)
+            lambda wl, n, m: eng.commit(wl, n, m), device=dev, torch=torch, release=release_if_held)
         want_q, _, _ = orc.schedule_queue(abi, nodes, led, qpods)
         ok = ok and got_q.tobytes() == want_q.tobytes()
         eng.close()

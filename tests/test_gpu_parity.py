@@ -227,8 +227,15 @@ def test_incremental_updates_and_ledger(kg, orc):
         eng.release(first["wl_id"])
     assert ei.value.code == -5 and "allocation not found" in str(ei.value)
     led2 = led[1:].copy()
-    eng.commit(led2[0]["wl_id"], 5, 0x81)                      # overwrite: moves to node 5
-    led2[0]["node_idx"], led2[0]["gpu_mask"] = 5, 0x81
+    taken5 = int(np.bitwise_or.reduce(led2["gpu_mask"][1:][led2["node_idx"][1:] == 5], initial=0))
+    free5 = [g for g in range(int(nodes[5]["n_gpus"])) if not taken5 >> g & 1]
+    move = (1 << free5[0]) | (1 << free5[-1])
+    if taken5:
+        with pytest.raises(kg.EngineError) as ei:              # a GPU another workload holds: refused (scheduler.go:634-640)
+            eng.commit(led2[0]["wl_id"], 5, move | (taken5 & -taken5))
+        assert ei.value.code == -6
+    eng.commit(led2[0]["wl_id"], 5, move)                      # overwrite: moves to node 5
+    led2[0]["node_idx"], led2[0]["gpu_mask"] = 5, move
     s, _ = eng.score_batch(pods, len(nodes), want_scores=True)
     o, _, _ = orc.score_batch(abi, o_nodes, led2, pods, want_scores=True)
     assert s[:, keep].tobytes() == o[:, keep].tobytes()
@@ -538,7 +545,8 @@ def test_concurrent_callers_share_one_engine(kg, orc):
     pods = pods[:40]
     eng = engine_for(kg, nodes, led)
     _, base, _ = orc.score_batch(abi, nodes, led, pods, want_scores=False, topk=1)
-    led2 = np.concatenate([led, ledger_of(abi, [(77_000_001, 0, 0xFF)])])
+    spare = int(np.setdiff1d(np.arange(len(nodes)), led["node_idx"])[0])        # a node the ledger does not touch (a commit on taken GPUs is refused)
+    led2 = np.concatenate([led, ledger_of(abi, [(77_000_001, spare, 0xFF)])])
     _, alt, _ = orc.score_batch(abi, nodes, led2, pods, want_scores=False, topk=1)
     errors = []
 
@@ -554,7 +562,7 @@ def test_concurrent_callers_share_one_engine(kg, orc):
     def writer():
         try:
             for _ in range(60):
-                eng.commit(77_000_001, 0, 0xFF)
+                eng.commit(77_000_001, spare, 0xFF)
                 eng.release(77_000_001)
         except Exception as ex:           # noqa: BLE001
             errors.append(repr(ex))

@@ -54,7 +54,8 @@ def _queue_worker(rank, world, port, q):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     abi, synth = kg.abi, kg.synth
     nodes, pods, led = synth.config(1)                     # 16 nodes: pods compete for the same nodes across shards
-    pods = pods[:60]
+    pods = pods[:60].copy()
+    pods["wl_id"][40:] = pods["wl_id"][5:25]               # workloads scheduled again: the old entry may sit in the OTHER shard
     lo, hi = kg.sharded.shard_range(len(nodes), rank, world)
     state = {"led": [tuple(x) for x in led[(led["node_idx"] >= lo) & (led["node_idx"] < hi)][["wl_id", "node_idx", "gpu_mask"]].tolist()]}
     cfg = abi.default_config(hi - lo, node_base=lo)
@@ -69,7 +70,10 @@ def _queue_worker(rank, world, port, q):
     def commit(wl, local_node, mask):
         state["led"].append((wl, local_node, mask))
 
-    got = kg.sharded.schedule_queue_sharded(dist, rank, world, (lo, hi), pods, score_top1, commit, torch=torch)
+    def release(wl):
+        state["led"] = [x for x in state["led"] if x[0] != wl]
+
+    got = kg.sharded.schedule_queue_sharded(dist, rank, world, (lo, hi), pods, score_top1, commit, torch=torch, release=release)
     want, _, _ = orc.schedule_queue(abi, nodes, led, pods)
     ok = got.tobytes() == want.tobytes()
     dist.barrier()
