@@ -273,8 +273,10 @@ def run_kgwe(args):
         dist.all_reduce(agree, op=dist.ReduceOp.MIN)          # all ranks or none
         if int(agree.item()) == 0:
             scorer.p2p = None
-        exchange = ("P2P stores from the finalisation kernel into every rank's gather buffer (symmetric memory) + one cross-GPU barrier"
-                    if scorer.p2p is not None else "NCCL all_gather of the local top-1 lists")
+        scorer.use_barrier = os.environ.get("KGWE_EXCHANGE_BARRIER", "0") == "1"
+        exchange = ("NCCL all_gather of the local top-1 lists" if scorer.p2p is None else
+                    "P2P stores from the finalisation kernel into every rank's gather buffer (symmetric memory) + one cross-GPU barrier" if (scorer.use_barrier or scorer.flags is None) else
+                    "kgwe_score_merge_p2p: the finalisation kernel stores its records and then its flag into every rank's symmetric memory over NVLink; the merge kernel waits for the flags on the device (no collective, no barrier launch)")
     d_merged = scorer.d_merged
     flush = torch.empty(160 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
 

@@ -311,6 +311,20 @@ int kgwe_score_batch_device_p2p(kgwe_engine* e, const kgwe_pod_req* d_pods, uint
                                 const uint8_t* d_hint_bitmap, kgwe_node_score* d_out_scores,
                                 const uint64_t* peer_gather_bufs, uint32_t n_ranks, uint32_t my_rank, void* cuda_stream);
 
+/* The whole node-sharded top-1 step in one call, with no collective and no separate cross-GPU barrier launch:
+ * K1 on this rank's shard, the finalisation kernel stores this rank's placement of every pod into slot `my_rank` of EVERY
+ * rank's gather buffer over peer-mapped memory and then raises this rank's flag on every rank, and a merge kernel waits
+ * (on the device) until all ranks' flags on THIS rank have reached `epoch` before it merges into d_merged.
+ *   peer_gather_bufs[r]  address, on rank r, of a buffer of 2 x n_ranks x n_pods placements (two slots, used alternately)
+ *   peer_flag_bufs[r]    address, on rank r, of n_ranks + 1 uint32, zero before the first call (the last word is set
+ *                        to 1 by a merge kernel that gave up waiting for a rank)
+ *   epoch                1, 2, 3 ... : the same value on every rank for the same step, one higher each step
+ * Host arrays of n_ranks device addresses (e.g. the buffer_ptrs of torch symmetric-memory allocations).  All ranks must
+ * make the same sequence of calls.  Otherwise as kgwe_score_batch_device(..., topk = 1). */
+int kgwe_score_merge_p2p(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const uint8_t* d_hint_bitmap,
+                         kgwe_node_score* d_out_scores, const uint64_t* peer_gather_bufs, const uint64_t* peer_flag_bufs,
+                         uint32_t n_ranks, uint32_t my_rank, uint32_t epoch, kgwe_placement* d_merged, void* cuda_stream);
+
 /* Merge R ranked lists per pod (layout [r][p][topk], device memory) into one
  * [p][topk] list in canonical order (score desc, node index asc).  This is the merge
  * every rank runs after the all-gather of local top-k lists. */

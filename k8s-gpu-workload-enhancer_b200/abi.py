@@ -87,7 +87,7 @@ ENGINE_SYMBOLS = [
     "kgwe_version", "kgwe_score_top1_noalloc", "kgwe_topk_merge_host",
     "kgwe_schedule_gangs", "kgwe_placement_terms", "kgwe_mig_pack", "kgwe_mig_rebalance",
     "kgwe_topology_hint_batch", "kgwe_topology_gauges", "kgwe_score_batch_device_p2p",
-    "kgwe_snapshot_size", "kgwe_snapshot_save", "kgwe_snapshot_load", "kgwe_node_upsert_remap",
+    "kgwe_snapshot_size", "kgwe_snapshot_save", "kgwe_snapshot_load", "kgwe_node_upsert_remap", "kgwe_score_merge_p2p",
 ]
 NOALLOC_MAX_PODS = 16384
 
@@ -122,6 +122,7 @@ def load_engine_lib():
     lib.kgwe_snapshot_save.argtypes = [vp, vp, u64, C.POINTER(u64)]
     lib.kgwe_snapshot_load.argtypes = [vp, vp, u64]
     lib.kgwe_score_batch_device_p2p.argtypes = [vp, vp, u32, vp, vp, vp, u32, u32, vp]
+    lib.kgwe_score_merge_p2p.argtypes = [vp, vp, u32, vp, vp, vp, vp, u32, u32, u32, vp, vp]
     lib.kgwe_topology_hint_batch.argtypes = [vp, vp, u32, vp]
     lib.kgwe_topology_gauges.argtypes = [vp, vp, u32]
     lib.kgwe_mig_pack.argtypes = [vp, vp, u32, vp, u32, vp]

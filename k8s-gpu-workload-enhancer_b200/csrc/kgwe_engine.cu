@@ -115,7 +115,7 @@ struct kgwe_engine {
     PinBuf<kgwe_placement> h_topk;
     PinBuf<uint8_t> h_hint;
     unsigned long long* h_counters = nullptr;
-    unsigned int* d_done = nullptr;           // latency path: CTA completion ticket
+    unsigned int* d_done = nullptr;           // [0] latency path: CTA completion ticket; [1] the same for the fused P2P finalisation
     unsigned int* h_flag = nullptr;           // latency path: pinned word the kernel sets to flag_seq when the placements are written
     unsigned int flag_seq = 0;
 
@@ -313,7 +313,7 @@ int launch_score(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, co
     if (topk == 1) {
         const uint32_t threads = 256, pods_per_block = threads / 8;
         finalize_top1_kernel<<<(n_pods + pods_per_block - 1) / pods_per_block, threads, 0, s>>>(
-            e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), best, d_topk, 1, e->params);
+            e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), d_scores, best, d_topk, 1, e->params);
         CU(e, cudaGetLastError());
         e->stats.kernel_launches++;
     } else if (topk > 1) {
@@ -396,7 +396,7 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
            && cudaMallocHost(&e->h_nodes, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
            && cudaMalloc(&e->d_counters, kCounters * sizeof(unsigned long long)) == cudaSuccess
            && cudaMallocHost(&e->h_counters, kCounters * sizeof(unsigned long long)) == cudaSuccess
-           && cudaMalloc(&e->d_done, sizeof(unsigned int)) == cudaSuccess && cudaMemset(e->d_done, 0, sizeof(unsigned int)) == cudaSuccess
+           && cudaMalloc(&e->d_done, 2 * sizeof(unsigned int)) == cudaSuccess && cudaMemset(e->d_done, 0, 2 * sizeof(unsigned int)) == cudaSuccess
            && cudaMallocHost(&e->h_flag, sizeof(unsigned int)) == cudaSuccess
            && cudaMemset(e->d_img[0], 0, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess && cudaMemset(e->d_img[1], 0, (size_t)cfg->max_nodes * sizeof(DevNode)) == cudaSuccess
            && cudaMemset(e->d_counters, 0, kCounters * sizeof(unsigned long long)) == cudaSuccess;
@@ -616,9 +616,45 @@ int kgwe_score_batch_device_p2p(kgwe_engine* e, const kgwe_pod_req* d_pods, uint
     if (rc != KGWE_OK) return rc;
     PeerBufs peers;
     for (uint32_t r = 0; r < 8; ++r) peers.p[r] = r < n_ranks ? reinterpret_cast<kgwe_placement*>(peer_bufs[r]) : nullptr;
-    finalize_top1_p2p_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), best, peers, n_ranks, my_rank, e->params);
+    finalize_top1_p2p_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), d_out, best, peers, n_ranks, my_rank, e->params,
+                                                                PeerFlags{}, 0u, nullptr);
     CU(e, cudaGetLastError());
     e->stats.kernel_launches++;
+    return note_use(e, s);
+}
+
+int kgwe_score_merge_p2p(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const uint8_t* d_hint, kgwe_node_score* d_out,
+                         const uint64_t* peer_bufs, const uint64_t* peer_flags, uint32_t n_ranks, uint32_t my_rank, uint32_t epoch,
+                         kgwe_placement* d_merged, void* cuda_stream) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (!peer_bufs || !peer_flags || !d_merged || n_ranks < 2 || n_ranks > 8 || my_rank >= n_ranks || epoch == 0 || (n_pods && !d_pods))
+        return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments (2..8 ranks, epoch >= 1)");
+    CU(e, cudaSetDevice(e->cfg.device));
+    cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : e->stream;
+    int rc = publish(e, s);
+    if (rc != KGWE_OK) return rc;
+    if (n_pods == 0) return KGWE_OK;
+    if (e->n_nodes == 0) return fail(e, KGWE_ERR_INVALID_ARG, "the cluster image of this shard is empty");
+    rc = ensure_best(e, n_pods, s);
+    if (rc != KGWE_OK) return rc;
+    unsigned long long* best = e->d_best.p;
+    rc = launch_k1(e, d_pods, n_pods, d_hint, d_out, best, s, false, FusedTail{}, true);
+    if (rc != KGWE_OK) return rc;
+    // double-buffered record slots: a rank one step ahead writes the other slot (its step after that cannot start
+    // before it has seen this rank's flag of the step in between, i.e. after this rank's merge of the current one)
+    const size_t slot_off = (size_t)(epoch & 1u) * n_ranks * n_pods;
+    PeerBufs peers; PeerFlags flags;
+    for (uint32_t r = 0; r < 8; ++r) {
+        peers.p[r] = r < n_ranks ? reinterpret_cast<kgwe_placement*>(peer_bufs[r]) + slot_off : nullptr;
+        flags.f[r] = r < n_ranks ? reinterpret_cast<uint32_t*>(peer_flags[r]) : nullptr;
+    }
+    finalize_top1_p2p_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), d_out, best, peers, n_ranks, my_rank, e->params,
+                                                                flags, epoch, e->d_done + 1);
+    CU(e, cudaGetLastError());
+    merge_top1_wait_kernel<<<(n_pods + 127) / 128, 128, 0, s>>>(peers.p[my_rank], flags.f[my_rank], n_ranks, epoch, n_pods, d_merged);
+    CU(e, cudaGetLastError());
+    e->stats.kernel_launches += 2;
     return note_use(e, s);
 }
 
@@ -1332,7 +1368,7 @@ extern "C" int kgwe_score_top1_noalloc(kgwe_engine* e, const kgwe_pod_req* d_pod
     CU(e, cudaMemsetAsync(keys, 0, (size_t)n_pods * sizeof(unsigned long long), s));
     rc = launch_k1(e, d_pods, n_pods, d_hint, d_out, keys, s, false, FusedTail{}, false);
     if (rc != KGWE_OK) return rc;
-    finalize_top1_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), keys, d_top1, 1, e->params);
+    finalize_top1_kernel<<<(n_pods + 31) / 32, 256, 0, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, d_hint, hint_row_bytes(e), d_out, keys, d_top1, 1, e->params);
     CU(e, cudaGetLastError());
     e->stats.kernel_launches++;
     return note_use(e, s);

@@ -79,22 +79,32 @@ __device__ __forceinline__ void store_no_placement(kgwe_placement* dst) {
     *dst = pl;
 }
 
-// K1b: one 8-lane group per pod.  Re-evaluates the winning (pod,node) to recover its GPU
-// list, adds EstimatedBandwidth, and clears the key slot for the next call.
+// K1b: one 8-lane group per pod.  Turns the arg-max key into a placement: the winner's NodeScore comes from the
+// score matrix when the call produced one (scores != nullptr), else the winning (pod,node) is evaluated again; adds
+// EstimatedBandwidth, and clears the key slot for the next call.
 __device__ __forceinline__ void finalize_one(const DevNode* __restrict__ nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods,
                                              uint32_t p, bool live, const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
                                              unsigned long long* best, kgwe_placement* out, const Params& P, int lane,
-                                             const kgwe_pod_req* spods = nullptr) {
+                                             const kgwe_pod_req* spods = nullptr, const kgwe_node_score* scores = nullptr) {
     unsigned long long key = live ? *reinterpret_cast<volatile unsigned long long*>(&best[p]) : 0ull;
     const uint32_t node = key ? key_node(key) - P.node_base : 0;
-    kgwe_pod_req pod;
-    if (live) pod = load_pod2(pods, spods, p); else { pod = kgwe_pod_req{}; }
     const DevNode* rec = nodes + node;
-    NodeCtx nc;
-    node_ctx_core(nc, rec, live && key != 0ull && node < n_nodes);
-    if (pod.topology_pref == KGWE_TOPO_SAME_NUMA || pod.topology_pref == KGWE_TOPO_SAME_PCIE_SWITCH) node_ctx_group_tables(nc, rec);
     EvalOut o;
-    evaluate<false>(rec, nc, pod, P, live && hint_bit(hint, hint_row_bytes, p, node), lane, o);
+    if (scores) {            // (uniform over the launch)
+        o.total = o.topo = o.res = o.bal = 0; o.mask = o.order = o.flags = 0; o.candidates = 0;
+        if (live && key != 0ull && node < n_nodes) {
+            const int4 v = *reinterpret_cast<const int4*>(scores + (size_t)p * n_nodes + node);
+            o.total = v.x; o.topo = (int)(int16_t)(v.y & 0xffff); o.res = (int)(int16_t)((uint32_t)v.y >> 16);
+            o.bal = (int)(int16_t)(v.z & 0xffff); o.mask = ((uint32_t)v.z >> 16) & 0xffu; o.flags = (uint32_t)v.z >> 24; o.order = (uint32_t)v.w;
+        }
+    } else {
+        kgwe_pod_req pod;
+        if (live) pod = load_pod2(pods, spods, p); else { pod = kgwe_pod_req{}; }
+        NodeCtx nc;
+        node_ctx_core(nc, rec, live && key != 0ull && node < n_nodes);
+        if (pod.topology_pref == KGWE_TOPO_SAME_NUMA || pod.topology_pref == KGWE_TOPO_SAME_PCIE_SWITCH) node_ctx_group_tables(nc, rec);
+        evaluate<false>(rec, nc, pod, P, live && hint_bit(hint, hint_row_bytes, p, node), lane, o);
+    }
     if (live && (lane & 7) == 0) {
         if (key == 0ull) store_no_placement(out + p);
         else store_placement(out + p, P.node_base + node, o, est_bandwidth(rec, o.order, (int)((o.order >> 24) & 15)));
@@ -108,16 +118,21 @@ namespace kgwe {
 
 // K1b with the exchange fused in: the placement of (this rank, pod p) is stored into slot `my_rank`
 // of every rank's gather buffer over peer-mapped memory (NVLink P2P stores), replacing the all-gather.
+// With flags (kgwe_score_merge_p2p): the last CTA to finish then tells every rank "my records of step `epoch` have
+// landed" by writing the epoch into slot my_rank of that rank's flag array (system-scope fences on both sides of the
+// CTA count order the record stores before the flag), so no separate cross-GPU barrier launch is needed.
 struct PeerBufs { kgwe_placement* p[8]; };
+struct PeerFlags { uint32_t* f[8]; };
 __global__ void __launch_bounds__(256)
 finalize_top1_p2p_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
-                         const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
-                         unsigned long long* __restrict__ best, PeerBufs peers, uint32_t n_ranks, uint32_t my_rank, Params P) {
+                         const uint8_t* __restrict__ hint, uint32_t hint_row_bytes, const kgwe_node_score* __restrict__ scores,
+                         unsigned long long* __restrict__ best, PeerBufs peers, uint32_t n_ranks, uint32_t my_rank, Params P,
+                         PeerFlags flags, uint32_t epoch, unsigned int* __restrict__ ctas_done) {
     const uint32_t p = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
     const bool live = p < n_pods;
     // compute into this rank's own buffer first, then replicate the 32-byte record to the peers
     kgwe_placement* mine = peers.p[my_rank] + (size_t)my_rank * n_pods;
-    finalize_one(nodes, n_nodes, pods, p, live, hint, hint_row_bytes, best, mine, P, threadIdx.x & 31);
+    finalize_one(nodes, n_nodes, pods, p, live, hint, hint_row_bytes, best, mine, P, threadIdx.x & 31, nullptr, scores);
     if (live && (threadIdx.x & 7) == 0) {
         const int4* src = reinterpret_cast<const int4*>(mine + p);
         const int4 a = src[0], b = src[1];
@@ -127,14 +142,60 @@ finalize_top1_p2p_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, co
             dst[0] = a; dst[1] = b;
         }
     }
+    if (ctas_done) {
+        __shared__ unsigned int ticket;
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) ticket = atomicAdd(ctas_done, 1u);
+        __syncthreads();
+        if (ticket == gridDim.x - 1 && threadIdx.x < n_ranks) {
+            __threadfence_system();
+            if (threadIdx.x == 0) *ctas_done = 0u;
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flags.f[threadIdx.x] + my_rank), "r"(epoch) : "memory");
+        }
+    }
+}
+
+// The merge after that exchange: waits until every rank's flag in THIS rank's flag array has reached `epoch` (acquire
+// loads; the flags only grow), then merges the R top-1 records of each pod (score desc, node index asc).  A rank that never
+// shows up within ~4e9 cycles makes the kernel give up and raise my_flags[n_ranks] instead of spinning for ever.
+__global__ void __launch_bounds__(128)
+merge_top1_wait_kernel(const kgwe_placement* __restrict__ lists, uint32_t* my_flags, uint32_t n_ranks, uint32_t epoch, uint32_t n_pods,
+                       kgwe_placement* __restrict__ out) {
+    if (threadIdx.x < n_ranks) {
+        const long long t0 = clock64();
+        uint32_t v;
+        for (;;) {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(my_flags + threadIdx.x) : "memory");
+            if ((int32_t)(v - epoch) >= 0) break;
+            if (clock64() - t0 > 4000000000ll) { my_flags[n_ranks] = 1u; break; }
+        }
+    }
+    __syncthreads();
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_pods) return;
+    int br = -1; int32_t bt = 0; uint32_t bn = 0;
+    for (uint32_t r = 0; r < n_ranks; ++r) {
+        const kgwe_placement* c = lists + (size_t)r * n_pods + p;
+        const uint32_t cn = c->node_idx;
+        if (cn == KGWE_NO_NODE) continue;
+        const int32_t ct = c->total;
+        if (br < 0 || ct > bt || (ct == bt && cn < bn)) { br = (int)r; bt = ct; bn = cn; }
+    }
+    if (br < 0) store_no_placement(out + p);
+    else {
+        const int4* src = reinterpret_cast<const int4*>(lists + (size_t)br * n_pods + p);
+        int4* dst = reinterpret_cast<int4*>(out + p);
+        dst[0] = src[0]; dst[1] = src[1];
+    }
 }
 
 __global__ void __launch_bounds__(256)
 finalize_top1_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
-                     const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
+                     const uint8_t* __restrict__ hint, uint32_t hint_row_bytes, const kgwe_node_score* __restrict__ scores,
                      unsigned long long* __restrict__ best, kgwe_placement* __restrict__ out, uint32_t out_stride, Params P) {
     const uint32_t p = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
-    finalize_one(nodes, n_nodes, pods, p, p < n_pods, hint, hint_row_bytes, best, out, P, threadIdx.x & 31);
+    finalize_one(nodes, n_nodes, pods, p, p < n_pods, hint, hint_row_bytes, best, out, P, threadIdx.x & 31, nullptr, scores);
 }
 
 // Empty cluster image: every requested placement is "no node" (nothing to score; Schedule then ends in "no eligible nodes found", scheduler.go:138-141).

@@ -104,6 +104,12 @@ class Engine:
         arr = (C.c_uint64 * len(peer_ptrs))(*[int(x) for x in peer_ptrs])
         self._check(self.lib.kgwe_score_batch_device_p2p(self.h, d_pods, n_pods, d_hint, d_scores, arr, len(peer_ptrs), my_rank, stream))
 
+    def score_merge_p2p(self, d_pods, n_pods, d_hint, d_scores, peer_ptrs, flag_ptrs, my_rank, epoch, d_merged, stream=None):
+        """The whole sharded top-1 step: K1, finalise + P2P scatter + flag, wait + merge (kgwe_score_merge_p2p)."""
+        a = (C.c_uint64 * len(peer_ptrs))(*[int(x) for x in peer_ptrs])
+        f = (C.c_uint64 * len(flag_ptrs))(*[int(x) for x in flag_ptrs])
+        self._check(self.lib.kgwe_score_merge_p2p(self.h, d_pods, n_pods, d_hint, d_scores, a, f, len(peer_ptrs), my_rank, epoch, d_merged, stream))
+
     def topk_merge_device(self, d_lists, n_lists, n_pods, topk, d_out, stream=None):
         self._check(self.lib.kgwe_topk_merge_device(self.h, d_lists, n_lists, n_pods, topk, d_out, stream))
 

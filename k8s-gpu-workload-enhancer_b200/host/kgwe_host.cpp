@@ -130,8 +130,21 @@ std::string TopologyAwareScheduler::UpsertNode(const NodeTopology& node) {
     const bool fresh = known == node_index_.end();
     if (fresh && node_names_.size() >= max_nodes_) return "cluster image is full";
     const uint32_t idx = fresh ? (uint32_t)node_names_.size() : known->second;
-    // the engine first: a record it rejects must not leave a name behind in the tables
-    if (kgwe_node_upsert(engine_, idx, &pk.image) != KGWE_OK) return kgwe_last_error(engine_);
+    // the engine first: a record it rejects must not leave a name behind in the tables.  The reference keys allocations by
+    // GPU UUID (scheduler.go:586-598), the engine by index in the node's GPU list: when a refresh changes that list (a GPU
+    // fell off the bus, NVML enumerates in another order) the ledger entries of the node follow their GPUs.
+    bool same_list = fresh || node_uuids_[idx].empty() || node_uuids_[idx] == pk.uuids;
+    if (same_list) {
+        if (kgwe_node_upsert(engine_, idx, &pk.image) != KGWE_OK) return kgwe_last_error(engine_);
+    } else {
+        int8_t old_to_new[KGWE_MAX_GPUS];
+        for (int g = 0; g < KGWE_MAX_GPUS; ++g) {
+            old_to_new[g] = -1;
+            if (g >= (int)node_uuids_[idx].size()) continue;
+            for (size_t q = 0; q < pk.uuids.size(); ++q) if (pk.uuids[q] == node_uuids_[idx][g]) old_to_new[g] = (int8_t)q;
+        }
+        if (kgwe_node_upsert_remap(engine_, idx, &pk.image, old_to_new) != KGWE_OK) return kgwe_last_error(engine_);
+    }
     if (fresh) { node_index_[node.NodeName] = idx; node_names_.push_back(node.NodeName); node_uuids_.emplace_back(); }
     else node_names_[idx] = node.NodeName;
     node_uuids_[idx] = pk.uuids;

@@ -33,6 +33,8 @@ class ShardedScorer:
         self.p2p = None            # (symmetric-memory tensor [2, world, P, 32], handle) when the fused exchange is on
         self.step_no = 0
         self._torch, self._ext = None, None      # torch and the engine's stream as a torch stream (set by alloc)
+        self.flags = None          # symmetric-memory flag words of the barrier-free exchange
+        self.use_barrier = False   # True: the older form (finalise + P2P stores, symmetric-memory barrier, merge)
 
     def enable_p2p(self, torch, dev, n_pods):
         """Fused exchange for top-1 batches: the finalisation kernel stores straight into every rank's
@@ -47,6 +49,14 @@ class ShardedScorer:
             if len(ptrs) != self.world:
                 return False
             self.p2p = (buf, hdl, ptrs)
+            # flags of the barrier-free exchange (kgwe_score_merge_p2p): one word per rank + one "gave up" word
+            fl = symm_mem.empty((self.world + 1,), dtype=torch.int32, device=dev)
+            fl.zero_()
+            fh = symm_mem.rendezvous(fl, self.dist.group.WORLD)
+            fptrs = [int(p) for p in fh.buffer_ptrs]
+            torch.cuda.synchronize()
+            self.dist.barrier()                     # every rank's flags are zero before anyone raises one
+            self.flags = (fl, fh, fptrs) if len(fptrs) == self.world else None
             return True
         except Exception:          # noqa: BLE001 - any failure: keep the NCCL path
             self.p2p = None
@@ -74,6 +84,12 @@ class ShardedScorer:
 
     def _step(self, d_pods, d_hint=None):
         sc = self.d_scores.data_ptr() if self.d_scores is not None else None
+        if self.p2p is not None and self.flags is not None and self.topk == 1 and self.world > 1 and not self.use_barrier:
+            buf, hdl, ptrs = self.p2p
+            self.step_no += 1
+            self.eng.score_merge_p2p(d_pods.data_ptr(), self.P, d_hint.data_ptr() if d_hint is not None else None, sc,
+                                     ptrs, self.flags[2], self.rank, self.step_no, self.d_merged.data_ptr(), self.sptr)
+            return self.d_merged
         if self.p2p is not None and self.topk == 1 and self.world > 1:
             buf, hdl, ptrs = self.p2p
             slot = self.step_no & 1

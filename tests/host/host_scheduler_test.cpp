@@ -164,6 +164,37 @@ int main() {
         CHECK(S.ReleaseAllocation(jobs[first_placed].UID).empty());
         CHECK(S.ReleaseAllocation(jobs[first_placed].UID) == "allocation not found for workload " + jobs[first_placed].UID);
     }
+    // a refresh that re-orders a node's GPU list: allocations are keyed by UUID in the reference (scheduler.go:586-598),
+    // so the GPUs a workload holds stay taken wherever they now sit in the list
+    {
+        auto made2 = TopologyAwareScheduler::New(SchedulerConfig{}, 4);
+        CHECK(made2.ok());
+        auto& T = *made2.value;
+        uint64_t rng = 99;
+        NodeTopology n = fixture::make_node(0, 0, rng);
+        for (auto& g : n.GPUs) { g.HealthStatus = "Healthy"; for (auto& kv : g.Topology.NVLinkConnections) kv.second.IsActive = true; }
+        CHECK(T.UpsertNode(n).empty());
+        GPUWorkload w; w.Name = "holder"; w.UID = "uid-holder"; w.Requirements.GPUCount = 3; w.Requirements.MinMemoryGB = 1; w.Requirements.TopologyPreference = "NVLinkOptimal";
+        auto d = T.Schedule(w);
+        CHECK(d.ok() && d.value.SelectedGPUs.size() == 3);
+        const std::vector<std::string> held = d.value.SelectedGPUs;
+        NodeTopology r = n;
+        std::reverse(r.GPUs.begin(), r.GPUs.end());                      // NVML enumerates the other way round after a driver restart
+        r.GPUs.erase(r.GPUs.begin() + 7);                                 // ... and the GPU formerly at index 0 is gone
+        for (size_t g = 0; g < r.GPUs.size(); ++g) r.GPUs[g].Index = (int)g;
+        CHECK(T.UpsertNode(r).empty());
+        GPUWorkload all; all.Name = "rest"; all.UID = "uid-rest"; all.Requirements.GPUCount = 5; all.Requirements.MinMemoryGB = 1; all.Requirements.TopologyPreference = "None";
+        auto d2 = T.Schedule(all);
+        // 7 GPUs left, of which the holder still has those of its three that survived
+        int survived = 0; for (auto& u : held) if (u != fixture::uuid(0, 0)) ++survived;
+        if (7 - survived >= 5) {
+            CHECK(d2.ok());
+            for (auto& u : d2.value.SelectedGPUs) CHECK(std::find(held.begin(), held.end(), u) == held.end());
+        } else CHECK(!d2.ok());
+        CHECK(T.ReleaseAllocation("uid-holder").empty());
+        GPUWorkload big; big.Name = "big"; big.UID = "uid-big"; big.Requirements.GPUCount = 7 - (d2.ok() ? 5 : 0); big.Requirements.MinMemoryGB = 1; big.Requirements.TopologyPreference = "None";
+        CHECK(T.Schedule(big).ok());                                       // everything the holder had is free again
+    }
     // node delete event
     CHECK(S.RemoveNode(cluster[0].NodeName).empty() && S.NodeIndex(cluster[0].NodeName) == KGWE_NO_NODE);
     CHECK(!S.RemoveNode(cluster[0].NodeName).empty());

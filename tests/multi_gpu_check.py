@@ -46,16 +46,29 @@ def main():
         sc1.alloc(torch, dev, P, 1, with_matrix=False)
         p2p_on = sc1.enable_p2p(torch, dev, P)
         _, want1, _ = orc.score_batch(abi, nodes, led, pods, want_scores=False, topk=1, threads=4)
-        for it in range(5):
+        for form in ("flags", "barrier"):
+            # "flags": kgwe_score_merge_p2p (records + flag stores over NVLink, the merge kernel waits on the device);
+            # "barrier": finalise + P2P stores, symmetric-memory barrier, merge
+            sc1.use_barrier = form == "barrier"
+            for it in range(5):
+                m = sc1.step(d_pods)
+                torch.cuda.synchronize()
+                got1 = m.cpu().numpy().view(abi.PLACEMENT).reshape(P, 1)
+                ok = ok and got1.tobytes() == want1.tobytes()
+            if sc1.flags is not None:
+                ok = ok and int(sc1.flags[0][world].item()) == 0          # no merge kernel gave up waiting
+        # back-to-back steps without a host synchronisation in between (a rank may run ahead of the others by a step)
+        sc1.use_barrier = False
+        for it in range(12):
             m = sc1.step(d_pods)
-            torch.cuda.synchronize()
-            got1 = m.cpu().numpy().view(abi.PLACEMENT).reshape(P, 1)
-            ok = ok and got1.tobytes() == want1.tobytes()
+        torch.cuda.synchronize()
+        ok = ok and m.cpu().numpy().view(abi.PLACEMENT).reshape(P, 1).tobytes() == want1.tobytes()
         if rank == 0:
             print(f"fused P2P exchange: {'on' if p2p_on else 'unavailable (NCCL path used)'}")
         # stateful queue over the sharded cluster: per-workload all-gather, owner rank commits
         qpods = pods[:120].copy()
-        qpods["wl_id"][90:] = qpods["wl_id"][10:40]      # scheduled again: the previous entry may live on another rank
+        nq = len(qpods)
+        qpods["wl_id"][nq - nq // 4:] = qpods["wl_id"][nq // 10: nq // 10 + nq // 4]      # scheduled again: the previous entry may live on another rank
 
         def release_if_held(wl):
             try:
