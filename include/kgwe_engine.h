@@ -399,9 +399,26 @@ int kgwe_mig_pack(kgwe_engine* e, kgwe_mig_gpu* gpus, uint32_t n_gpus, const uin
  *     per instance - 40 GB-class GPUs first, then 80 GB-class, each by profile, GPU index, start -
  *     and the resulting free-instance supply per profile.  *n_ops is the number of ops the plan
  *     has; only the first ops_cap are written. */
-typedef struct kgwe_mig_op { uint32_t gpu_idx; uint8_t profile, start, size, pad; } kgwe_mig_op;
+typedef struct kgwe_mig_op { uint32_t gpu_idx; uint8_t profile, start, size, pad; } kgwe_mig_op;      /* pad: KGWE_MIG_OP_* (always CREATE from kgwe_mig_rebalance) */
 int kgwe_mig_rebalance(kgwe_engine* e, const kgwe_mig_gpu* gpus, uint32_t n_gpus, const double* target /*[10]*/,
                        kgwe_mig_op* ops, uint32_t ops_cap, uint32_t* n_ops, uint32_t* supply /*[10]*/);
+
+/*   - reconfiguration pass (the reference sketches it: Rebalance compares usage against strategy and reconfigures when
+ *     AllowDynamicReconfig is set, src/sharing/mig_controller.go:480-504 - its body is empty).  Here a GPU is described by
+ *     the instances that EXIST on it and the ones IN USE, as bit sets over the 14 legal placements
+ *     (bits 0..6: 1g at slice 0..6; 7..9: 2g at 0,2,4; 10..11: 3g at 0,4; 12: 4g at 0; 13: 7g), in_use a subset of created.
+ *     A GPU is reconfigurable when it is enabled and nothing on it is in use; running instances are never touched.
+ *     The reconfigurable GPUs of each class are split among that class's profiles by the same rule as kgwe_mig_rebalance
+ *     (shares of target[], largest remainders, GPUs in index order).  A GPU given geometry q ends up with exactly the
+ *     instances of q at all its legal starts: for it the pass emits a DESTROY op for every existing instance that is not
+ *     one of those (ascending placement bit) and then a CREATE op for every missing one (ascending start) - a GPU that
+ *     already has the wanted layout emits nothing.  Ops come out by class, profile, GPU index.  supply[p] counts the free
+ *     instances of profile p after the pass (reconfigured GPUs, plus the existing free instances of GPUs left alone). */
+typedef struct kgwe_mig_gpu_state { uint16_t created; uint16_t in_use; uint8_t cls; uint8_t enabled; uint8_t pad[2]; } kgwe_mig_gpu_state;
+#define KGWE_MIG_OP_CREATE  0      /* kgwe_mig_op.pad: what the op does */
+#define KGWE_MIG_OP_DESTROY 1
+int kgwe_mig_reconfigure(kgwe_engine* e, const kgwe_mig_gpu_state* gpus, uint32_t n_gpus, const double* target /*[10]*/,
+                         kgwe_mig_op* ops, uint32_t ops_cap, uint32_t* n_ops, uint32_t* supply /*[10]*/);
 
 /* DiscoveryService.GetTopologyHint (src/discovery/discovery.go:222-247) - the reference's second
  * node-parallel scorer, over the same image ("next" row 8f.3).  Per request: every node is scored

@@ -26,7 +26,9 @@ CFG_PRUNE_TIED_STARTS = 0x4
 F_ELIGIBLE, F_KEPT, F_HINT, F_FALLBACK, F_MINBW, F_GANG_ROLLBACK = 0x01, 0x02, 0x04, 0x08, 0x10, 0x20
 MIG_GPU = np.dtype([("occ", "u1"), ("cls", "u1"), ("enabled", "u1"), ("pad", "u1")])
 MIG_ASSIGNMENT = np.dtype([("gpu_idx", "<u4"), ("start", "u1"), ("size", "u1"), ("cost", "u1"), ("profile", "u1")])
-MIG_OP = np.dtype([("gpu_idx", "<u4"), ("profile", "u1"), ("start", "u1"), ("size", "u1"), ("pad", "u1")])
+MIG_OP = np.dtype([("gpu_idx", "<u4"), ("profile", "u1"), ("start", "u1"), ("size", "u1"), ("pad", "u1")])      # pad: MIG_OP_CREATE / MIG_OP_DESTROY
+MIG_GPU_STATE = np.dtype([("created", "<u2"), ("in_use", "<u2"), ("cls", "u1"), ("enabled", "u1"), ("pad", "u1", (2,))])
+MIG_OP_CREATE, MIG_OP_DESTROY = 0, 1
 SIDE_TERMS = np.dtype([("bisection_gbps", "<f8"), ("ring_bottleneck_gbps", "<f8")])
 
 NODE_IMAGE = np.dtype([
@@ -87,7 +89,7 @@ ENGINE_SYMBOLS = [
     "kgwe_version", "kgwe_score_top1_noalloc", "kgwe_topk_merge_host",
     "kgwe_schedule_gangs", "kgwe_placement_terms", "kgwe_mig_pack", "kgwe_mig_rebalance",
     "kgwe_topology_hint_batch", "kgwe_topology_gauges", "kgwe_score_batch_device_p2p",
-    "kgwe_snapshot_size", "kgwe_snapshot_save", "kgwe_snapshot_load", "kgwe_node_upsert_remap", "kgwe_score_merge_p2p",
+    "kgwe_snapshot_size", "kgwe_snapshot_save", "kgwe_snapshot_load", "kgwe_node_upsert_remap", "kgwe_score_merge_p2p", "kgwe_mig_reconfigure",
 ]
 NOALLOC_MAX_PODS = 16384
 
@@ -127,6 +129,7 @@ def load_engine_lib():
     lib.kgwe_topology_gauges.argtypes = [vp, vp, u32]
     lib.kgwe_mig_pack.argtypes = [vp, vp, u32, vp, u32, vp]
     lib.kgwe_mig_rebalance.argtypes = [vp, vp, u32, vp, vp, u32, C.POINTER(u32), vp]
+    lib.kgwe_mig_reconfigure.argtypes = [vp, vp, u32, vp, vp, u32, C.POINTER(u32), vp]
     lib.kgwe_schedule_gangs.argtypes = [vp, vp, u32, vp, vp, vp]
     lib.kgwe_placement_terms.argtypes = [vp, vp, u32, vp]
     lib.kgwe_topk_merge_host.argtypes = [vp, u32, u32, u32, vp]

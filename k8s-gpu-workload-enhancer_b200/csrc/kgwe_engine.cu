@@ -1110,8 +1110,12 @@ int kgwe_mig_pack(kgwe_engine* e, kgwe_mig_gpu* gpus, uint32_t n_gpus, const uin
         for (uint32_t i = 0; i < n_reqs; ++i) { memset(&out[i], 0, sizeof out[i]); out[i].gpu_idx = KGWE_NO_NODE; out[i].profile = profiles[i]; }
         return KGWE_OK;
     }
-    const size_t smem = (size_t)MIG_GEOS * 256 + 36 * 4 + 10 * (size_t)MIG_THREADS * 4 + (size_t)MIG_THREADS * 2 + 2 * (size_t)n_gpus;
-    if (smem > 220 * 1024 || n_gpus >= (1u << 24)) return fail(e, KGWE_ERR_TOO_LARGE, "kgwe_mig_pack: %u GPUs exceed the single-CTA table (max ~85k per call; shard by GPU)", n_gpus);
+    // tables up to MIG_TREE_MAX_GPUS: the tournament-tree kernel (one shared-memory read per request); larger ones: the
+    // scan form (per-thread cached keys, block-wide min), up to what one CTA's shared memory holds
+    const bool tree = n_gpus <= MIG_TREE_MAX_GPUS && mig_tree_smem(n_gpus) <= 220 * 1024;
+    const size_t smem = tree ? mig_tree_smem(n_gpus)
+                             : (size_t)MIG_GEOS * 256 + 36 * 4 + 10 * (size_t)MIG_THREADS * 4 + (size_t)MIG_THREADS * 2 + 2 * (size_t)n_gpus;
+    if (smem > 220 * 1024 || n_gpus >= (1u << 24)) return fail(e, KGWE_ERR_TOO_LARGE, "kgwe_mig_pack: %u GPUs exceed the single-CTA table (max ~85k per call; split the table by GPU pool)", n_gpus);
     CU(e, cudaSetDevice(e->cfg.device));
     cudaStream_t s = e->stream;
     static_assert(sizeof(kgwe_mig_gpu) == 4 && sizeof(kgwe_mig_assignment) == 8 && sizeof(kgwe_mig_op) == 8, "MIG ABI sizes");
@@ -1121,10 +1125,12 @@ int kgwe_mig_pack(kgwe_engine* e, kgwe_mig_gpu* gpus, uint32_t n_gpus, const uin
     CU(e, e->d_hint.ensure(total)); CU(e, e->h_hint.ensure(total));
     memcpy(e->h_hint.p, gpus, bytes_g); memcpy(e->h_hint.p + off_p, profiles, n_reqs);
     CU(e, cudaMemcpyAsync(e->d_hint.p, e->h_hint.p, off_p + n_reqs, cudaMemcpyHostToDevice, s));
-    CU(e, cudaFuncSetAttribute(mig_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(e, cudaFuncSetAttribute(tree ? (const void*)mig_pack_tree_kernel : (const void*)mig_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CU(e, cudaEventRecord(e->ev0, s));
-    mig_pack_kernel<<<1, MIG_THREADS, smem, s>>>(reinterpret_cast<kgwe_mig_gpu*>(e->d_hint.p), n_gpus, e->d_hint.p + off_p, n_reqs,
-                                                 reinterpret_cast<kgwe_mig_assignment*>(e->d_hint.p + off_o));
+    if (tree) mig_pack_tree_kernel<<<1, MIGT_THREADS, smem, s>>>(reinterpret_cast<kgwe_mig_gpu*>(e->d_hint.p), n_gpus, e->d_hint.p + off_p, n_reqs,
+                                                                 reinterpret_cast<kgwe_mig_assignment*>(e->d_hint.p + off_o));
+    else mig_pack_kernel<<<1, MIG_THREADS, smem, s>>>(reinterpret_cast<kgwe_mig_gpu*>(e->d_hint.p), n_gpus, e->d_hint.p + off_p, n_reqs,
+                                                      reinterpret_cast<kgwe_mig_assignment*>(e->d_hint.p + off_o));
     CU(e, cudaGetLastError());
     CU(e, cudaEventRecord(e->ev1, s));
     e->stats.kernel_launches++;
@@ -1171,6 +1177,56 @@ int kgwe_mig_rebalance(kgwe_engine* e, const kgwe_mig_gpu* gpus, uint32_t n_gpus
         mig_emit_kernel<<<(n_gpus + 255) / 256, 256, 0, s>>>(reinterpret_cast<const kgwe_mig_gpu*>(e->d_hint.p), n_gpus, d_rank, plan,
                                                             reinterpret_cast<kgwe_mig_op*>(e->d_hint.p + off_o), ops_cap);
         CU(e, cudaGetLastError());
+        CU(e, cudaMemcpyAsync(e->h_hint.p + off_o, e->d_hint.p + off_o, (size_t)n_write * sizeof(kgwe_mig_op), cudaMemcpyDeviceToHost, s));
+        CU(e, cudaStreamSynchronize(s));
+        memcpy(ops, e->h_hint.p + off_o, (size_t)n_write * sizeof(kgwe_mig_op));
+    }
+    e->stats.kernel_launches += 2;
+    return KGWE_OK;
+}
+
+int kgwe_mig_reconfigure(kgwe_engine* e, const kgwe_mig_gpu_state* gpus, uint32_t n_gpus, const double* target,
+                         kgwe_mig_op* ops, uint32_t ops_cap, uint32_t* n_ops, uint32_t* supply) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if ((n_gpus && !gpus) || !target || !n_ops || !supply || (ops_cap && !ops)) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    double sum = 0.0;
+    for (int p = 0; p < KGWE_MIG_PROFILES; ++p) { if (!(target[p] >= 0.0)) return fail(e, KGWE_ERR_INVALID_ARG, "target[%d] must be >= 0", p); sum += target[p]; }
+    if (sum > 1.01) return fail(e, KGWE_ERR_INVALID_ARG, "profile distribution exceeds 100%%");      // mig_controller.go:263-270
+    for (uint32_t g = 0; g < n_gpus; ++g)
+        if ((gpus[g].in_use & ~gpus[g].created) || (gpus[g].created >> 14)) return fail(e, KGWE_ERR_INVALID_ARG, "GPU %u: in_use must be a subset of created, both within the 14 legal placements", g);
+    *n_ops = 0; for (int p = 0; p < KGWE_MIG_PROFILES; ++p) supply[p] = 0;
+    if (n_gpus == 0) return KGWE_OK;
+    CU(e, cudaSetDevice(e->cfg.device));
+    cudaStream_t s = e->stream;
+    static_assert(sizeof(kgwe_mig_gpu_state) == 8, "MIG ABI sizes");
+    const size_t bytes_g = (size_t)n_gpus * sizeof(kgwe_mig_gpu_state);
+    const size_t off_r = (bytes_g + 255) & ~(size_t)255, off_c = off_r + (size_t)n_gpus * 4, off_o = (off_c + 64 + 255) & ~(size_t)255;
+    const size_t total = off_o + (size_t)ops_cap * sizeof(kgwe_mig_op);
+    CU(e, e->d_hint.ensure(total)); CU(e, e->h_hint.ensure(total));
+    memcpy(e->h_hint.p, gpus, bytes_g);
+    CU(e, cudaMemcpyAsync(e->d_hint.p, e->h_hint.p, bytes_g, cudaMemcpyHostToDevice, s));
+    const kgwe_mig_gpu_state* d_g = reinterpret_cast<const kgwe_mig_gpu_state*>(e->d_hint.p);
+    uint32_t* d_rank = reinterpret_cast<uint32_t*>(e->d_hint.p + off_r);
+    uint32_t* d_cnt = reinterpret_cast<uint32_t*>(e->d_hint.p + off_c);        // [0..1] reconfigurable per class, [2] ops, [4..13] supply
+    mig_state_rank_kernel<<<1, 1024, 0, s>>>(d_g, n_gpus, d_rank, d_cnt);
+    CU(e, cudaGetLastError());
+    CU(e, cudaMemcpyAsync(e->h_hint.p + off_c, d_cnt, 8, cudaMemcpyDeviceToHost, s));
+    CU(e, cudaStreamSynchronize(s));
+    uint32_t counts[2];
+    memcpy(counts, e->h_hint.p + off_c, 8);
+    MigRanks plan;
+    mig_split(counts, target, plan);
+    mig_reconf_kernel<<<1, 1024, 0, s>>>(d_g, n_gpus, d_rank, plan, reinterpret_cast<kgwe_mig_op*>(e->d_hint.p + off_o), ops_cap, d_cnt + 2, d_cnt + 4);
+    CU(e, cudaGetLastError());
+    CU(e, cudaMemcpyAsync(e->h_hint.p + off_c, d_cnt, 64, cudaMemcpyDeviceToHost, s));
+    CU(e, cudaStreamSynchronize(s));
+    uint32_t res[16];
+    memcpy(res, e->h_hint.p + off_c, 64);
+    *n_ops = res[2];
+    for (int p = 0; p < KGWE_MIG_PROFILES; ++p) supply[p] = res[4 + p];
+    const uint32_t n_write = std::min(*n_ops, ops_cap);
+    if (n_write) {
         CU(e, cudaMemcpyAsync(e->h_hint.p + off_o, e->d_hint.p + off_o, (size_t)n_write * sizeof(kgwe_mig_op), cudaMemcpyDeviceToHost, s));
         CU(e, cudaStreamSynchronize(s));
         memcpy(ops, e->h_hint.p + off_o, (size_t)n_write * sizeof(kgwe_mig_op));

@@ -106,6 +106,114 @@ mig_pack_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uint8_t*
     for (uint32_t g = tid; g < n_gpus; g += MIG_THREADS) gpus[g].occ = (uint8_t)(state[g] & 0xff);
 }
 
+// K4, tournament-tree form (tables of up to MIG_TREE_MAX_GPUS GPUs): requests are inherently sequential - each one must see
+// the commits before it - so what counts is the length of the per-request dependency chain, not the width of the machine.
+// Per (class, geometry) a 32-ary min tree over the GPUs keeps the best placement key of every group of 32 GPUs, of every
+// group of 32 groups, and at the root: a request is ONE shared-memory read of its root, and its commit only has to repair
+// the path above the one GPU that changed - three warp-wide REDUX.MIN steps per tree, the five trees of the GPU's class
+// repaired by five warps side by side.  Leaves are one byte per (geometry, GPU): class << 7 | cost << 3 | start, 0x7F = no fit.
+constexpr int MIGT_THREADS = 160;                  // five warps: warp w repairs the tree of geometry w
+constexpr uint32_t MIG_TREE_MAX_GPUS = 24576;      // 3 levels of 32 cover 32,768; shared memory (8.3 B per GPU) sets this lower
+constexpr uint32_t MIG_KEY_NONE = 0xFFFFFFFFu;
+__host__ __device__ inline size_t mig_tree_smem(uint32_t n_gpus) {
+    const size_t n_pad = (n_gpus + 31) & ~31u, n1 = n_pad / 32, n2 = (n1 + 31) / 32;
+    return MIG_GEOS * 256 + 2 * n_pad + MIG_GEOS * n_pad + 10 * 4 * (n1 + n2 * 32 + 1) + 1024 + 64;
+}
+__device__ __forceinline__ uint32_t mig_leaf_key(uint32_t leaf, uint32_t cls, uint32_t g) {
+    return ((leaf >> 7) == cls && (leaf & 0x7Fu) != 0x7Fu) ? ((((leaf >> 3) & 0xFu) << 27) | (g << 3) | (leaf & 7u)) : MIG_KEY_NONE;
+}
+__global__ void __launch_bounds__(MIGT_THREADS, 1)
+mig_pack_tree_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uint8_t* __restrict__ profiles, uint32_t n_reqs,
+                     kgwe_mig_assignment* __restrict__ out) {
+    extern __shared__ __align__(16) unsigned char msm[];
+    const uint32_t n_pad = (n_gpus + 31u) & ~31u, n1 = n_pad / 32u, n2 = (n1 + 31u) / 32u;
+    uint32_t* L1 = reinterpret_cast<uint32_t*>(msm);                        // [10][n1]
+    uint32_t* L2 = L1 + 10 * n1;                                            // [10][n2 * 32] (padded with MIG_KEY_NONE)
+    uint32_t* root = L2 + 10 * n2 * 32;                                     // [10] (+ pad)
+    uint16_t* state = reinterpret_cast<uint16_t*>(root + 16);               // [n_pad]: (enabled | cls << 1) << 8 | occ
+    uint8_t* leaf = reinterpret_cast<uint8_t*>(state + n_pad);              // [5][n_pad]
+    uint8_t* lut = leaf + MIG_GEOS * n_pad;                                 // [5][256]
+    uint8_t* req_stage = lut + MIG_GEOS * 256;                              // [1024]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < MIG_GEOS * 256; i += MIGT_THREADS) lut[i] = (uint8_t)mig_best((uint32_t)(i & 255), i >> 8);
+    __syncthreads();
+    for (uint32_t g = tid; g < n_pad; g += MIGT_THREADS) {
+        uint32_t st = 0;
+        if (g < n_gpus) { const kgwe_mig_gpu v = gpus[g]; st = (((v.enabled ? 1u : 0u) | ((v.cls & 1u) << 1)) << 8) | v.occ; }
+        state[g] = (uint16_t)st;
+        for (int q = 0; q < MIG_GEOS; ++q) {
+            const uint32_t b = (st >> 8 & 1u) ? lut[q * 256 + (st & 0xffu)] : 0xFFu;
+            leaf[q * n_pad + g] = (uint8_t)((((st >> 9) & 1u) << 7) | (b == 0xFFu ? 0x7Fu : b));
+        }
+    }
+    for (uint32_t i = tid; i < 10 * n2 * 32; i += MIGT_THREADS) L2[i] = MIG_KEY_NONE;
+    __syncthreads();
+    // level 1: tree t = cls * 5 + geometry, node i = min over GPUs 32 i .. 32 i + 31
+    for (uint32_t w = warp; w < 10 * n1; w += MIGT_THREADS / 32) {
+        const uint32_t t = w / n1, i = w % n1, g = i * 32 + lane;
+        const uint32_t k = __reduce_min_sync(0xffffffffu, mig_leaf_key(leaf[(t % 5) * n_pad + g], t / 5, g));
+        if (lane == 0) L1[t * n1 + i] = k;
+    }
+    __syncthreads();
+    for (uint32_t w = warp; w < 10 * n2; w += MIGT_THREADS / 32) {
+        const uint32_t t = w / n2, i = w % n2, j = i * 32 + lane;
+        const uint32_t k = __reduce_min_sync(0xffffffffu, j < n1 ? L1[t * n1 + j] : MIG_KEY_NONE);
+        if (lane == 0) L2[t * n2 * 32 + i] = k;
+    }
+    __syncthreads();
+    for (uint32_t t = warp; t < 10; t += MIGT_THREADS / 32) {
+        const uint32_t k = __reduce_min_sync(0xffffffffu, L2[t * n2 * 32 + lane]);        // n2 <= 32
+        if (lane == 0) root[t] = k;
+    }
+    __syncthreads();
+    for (uint32_t r = 0; r < n_reqs; ++r) {
+        if ((r & 1023u) == 0) {                       // refill the staged profiles (every request ends in a barrier, so nobody still reads the old ones)
+            for (uint32_t i = tid; i < 1024u && r + i < n_reqs; i += MIGT_THREADS) req_stage[i] = profiles[r + i];
+            __syncthreads();
+        }
+        const int profile = req_stage[r & 1023u];
+        const bool known = profile >= 1 && profile <= KGWE_MIG_PROFILES;
+        const int geo = known ? mig_geo(profile) : 0, cls = known ? mig_cls(profile) : 0;
+        const uint32_t key = known ? root[cls * 5 + geo] : MIG_KEY_NONE;
+        if (key == MIG_KEY_NONE) {                    // nothing fits: nothing changes
+            if (tid == 0) { kgwe_mig_assignment a; a.gpu_idx = KGWE_NO_NODE; a.start = a.size = a.cost = 0; a.profile = (uint8_t)profile; out[r] = a; }
+            __syncthreads();                          // (warps stay in step: a warp running ahead into the next commit would change a root under a slower one)
+            continue;
+        }
+        const uint32_t g = (key >> 3) & 0xFFFFFFu, start = key & 7u, size = (uint32_t)mig_size(geo);
+        volatile uint16_t* vstate = state;
+        const uint32_t st_new = (uint32_t)vstate[g] | (((1u << size) - 1u) << start);        // (idempotent: whoever reads the old or the new word derives the same)
+        if (tid == 0) {
+            vstate[g] = (uint16_t)st_new;
+            kgwe_mig_assignment a;
+            a.gpu_idx = g; a.start = (uint8_t)start; a.size = (uint8_t)size; a.cost = (uint8_t)(key >> 27); a.profile = (uint8_t)profile;
+            out[r] = a;
+        }
+        // warp w repairs the tree of (cls, geometry w): the GPU's leaf, its group of 32, that group's group, the root
+        {
+            const uint32_t t = (uint32_t)cls * 5u + (uint32_t)warp;
+            if (lane == 0) {
+                const uint32_t b = lut[warp * 256 + (st_new & 0xffu)];
+                leaf[warp * n_pad + g] = (uint8_t)(((uint32_t)cls << 7) | (b == 0xFFu ? 0x7Fu : b));
+            }
+            __syncwarp();
+            const uint32_t i1 = g >> 5, gl = (g & ~31u) + lane;
+            const uint32_t k1 = __reduce_min_sync(0xffffffffu, mig_leaf_key(leaf[warp * n_pad + gl], (uint32_t)cls, gl));
+            if (lane == 0) L1[t * n1 + i1] = k1;
+            __syncwarp();
+            const uint32_t i2 = i1 >> 5, j = (i1 & ~31u) + lane;
+            const uint32_t k2 = __reduce_min_sync(0xffffffffu, j < n1 ? L1[t * n1 + j] : MIG_KEY_NONE);
+            if (lane == 0) L2[t * n2 * 32 + i2] = k2;
+            __syncwarp();
+            const uint32_t k3 = __reduce_min_sync(0xffffffffu, L2[t * n2 * 32 + lane]);
+            if (lane == 0) root[t] = k3;
+        }
+        __syncthreads();                              // the next request reads the repaired roots
+    }
+    __syncthreads();
+    for (uint32_t g = tid; g < n_gpus; g += MIGT_THREADS) gpus[g].occ = (uint8_t)(state[g] & 0xff);
+}
+
 // Rebalance, device part 1: exclusive rank of every idle GPU (enabled, occ == 0) within its class,
 // in index order.  One CTA, chunked ballot/shuffle scan.
 __global__ void __launch_bounds__(1024, 1)
@@ -171,6 +279,151 @@ mig_emit_kernel(const kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const ui
                 op.gpu_idx = g; op.profile = (uint8_t)(2 * q + 1 + c); op.start = (uint8_t)mig_start(q, i); op.size = (uint8_t)mig_size(q); op.pad = 0;
                 ops[at + i] = op;
             }
+    }
+}
+
+// ---- reconfiguration pass with destroy ops (kgwe_mig_reconfigure) -----------------------------------------
+// Placement bit b of the 14 legal placements <-> (geometry, start index).
+__host__ __device__ inline int mig_bit_geo(int b) { return b < 7 ? 0 : b < 10 ? 1 : b < 12 ? 2 : b == 12 ? 3 : 4; }
+__host__ __device__ inline int mig_bit_first(int geo) { return geo == 0 ? 0 : geo == 1 ? 7 : geo == 2 ? 10 : geo == 3 ? 12 : 13; }
+__host__ __device__ inline uint32_t mig_geo_bits(int geo) { return ((1u << mig_nstarts(geo)) - 1u) << mig_bit_first(geo); }
+
+// Part 1: exclusive rank of every reconfigurable GPU (enabled, nothing in use) within its class, in index order.
+__global__ void __launch_bounds__(1024, 1)
+mig_state_rank_kernel(const kgwe_mig_gpu_state* __restrict__ gpus, uint32_t n_gpus, uint32_t* __restrict__ rank, uint32_t* __restrict__ counts) {
+    __shared__ uint32_t wsum[2][32];
+    __shared__ uint32_t tot[2], carry[2];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid < 2) carry[tid] = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < n_gpus; base += 1024) {
+        const uint32_t g = base + tid;
+        int c = -1;
+        if (g < n_gpus) { const kgwe_mig_gpu_state v = gpus[g]; if (v.enabled && v.in_use == 0) c = v.cls & 1; }
+        uint32_t pre[2];
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const uint32_t b = __ballot_sync(0xffffffffu, c == k);
+            pre[k] = __popc(b & ((1u << lane) - 1u));
+            if (lane == 0) wsum[k][warp] = __popc(b);
+        }
+        __syncthreads();
+        if (warp == 0) {
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const uint32_t v = wsum[k][lane]; uint32_t x = v;
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) { const uint32_t o = __shfl_up_sync(0xffffffffu, x, off); if (lane >= off) x += o; }
+                wsum[k][lane] = x - v;
+                if (lane == 31) tot[k] = x;
+            }
+        }
+        __syncthreads();
+        if (g < n_gpus) rank[g] = c < 0 ? 0xFFFFFFFFu : carry[c] + wsum[c][warp] + pre[c];
+        __syncthreads();
+        if (tid < 2) carry[tid] += tot[tid];
+        __syncthreads();
+    }
+    if (tid < 2) counts[tid] = carry[tid];
+}
+
+// Part 2, one launch per (class, geometry) in output order would serialise; instead ONE CTA walks the table once per
+// (class, geometry) pair in output order - ten chunked scans over the op counts of the GPUs assigned to that pair - and
+// every GPU writes its own ops at the offset the scan gives it.  Also counts the supply.
+struct MigRanks { uint32_t first_rank[2][MIG_GEOS + 1]; };
+__global__ void __launch_bounds__(1024, 1)
+mig_reconf_kernel(const kgwe_mig_gpu_state* __restrict__ gpus, uint32_t n_gpus, const uint32_t* __restrict__ rank, MigRanks plan,
+                  kgwe_mig_op* __restrict__ ops, uint32_t ops_cap, uint32_t* __restrict__ n_ops_out, uint32_t* __restrict__ supply_out) {
+    __shared__ uint32_t wsum[32];
+    __shared__ uint32_t carry, tot;
+    __shared__ uint32_t supply[KGWE_MIG_PROFILES];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) carry = 0;
+    if (tid < KGWE_MIG_PROFILES) supply[tid] = 0;
+    __syncthreads();
+    // free instances of the GPUs that are left alone
+    for (uint32_t g = tid; g < n_gpus; g += 1024) {
+        const kgwe_mig_gpu_state v = gpus[g];
+        if (!v.enabled || v.in_use == 0) continue;
+        uint32_t fr = (uint32_t)v.created & ~(uint32_t)v.in_use & 0x3FFFu;
+        while (fr) { const int b = __ffs((int)fr) - 1; fr &= fr - 1u; atomicAdd(&supply[2 * mig_bit_geo(b) + (v.cls & 1)], 1u); }
+    }
+    for (int c = 0; c < 2; ++c)
+        for (int q = 0; q < MIG_GEOS; ++q) {
+            const uint32_t r0 = plan.first_rank[c][q], r1 = plan.first_rank[c][q + 1];
+            if (r1 == r0) continue;
+            if (tid == 0) atomicAdd(&supply[2 * q + c], (r1 - r0) * (uint32_t)mig_nstarts(q));
+            const uint32_t want = mig_geo_bits(q);
+            for (uint32_t base = 0; base < n_gpus; base += 1024) {
+                const uint32_t g = base + tid;
+                uint32_t cnt = 0, have = 0;
+                bool mine = false;
+                if (g < n_gpus) {
+                    const uint32_t r = rank[g];
+                    const kgwe_mig_gpu_state v = gpus[g];
+                    mine = r != 0xFFFFFFFFu && (v.cls & 1) == c && r >= r0 && r < r1;
+                    have = (uint32_t)v.created & 0x3FFFu;
+                    if (mine) cnt = __popc(have & ~want) + __popc(want & ~have);
+                }
+                uint32_t x = cnt;
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) { const uint32_t o = __shfl_up_sync(0xffffffffu, x, off); if (lane >= off) x += o; }
+                if (lane == 31) wsum[warp] = x;
+                __syncthreads();
+                if (warp == 0) {
+                    const uint32_t v = wsum[lane]; uint32_t y = v;
+#pragma unroll
+                    for (int off = 1; off < 32; off <<= 1) { const uint32_t o = __shfl_up_sync(0xffffffffu, y, off); if (lane >= off) y += o; }
+                    wsum[lane] = y - v;
+                    if (lane == 31) tot = y;
+                }
+                __syncthreads();
+                if (mine && cnt) {
+                    uint32_t at = carry + wsum[warp] + (x - cnt);
+                    for (uint32_t d = have & ~want; d; d &= d - 1u, ++at) {
+                        const int b = __ffs((int)d) - 1, gq = mig_bit_geo(b);
+                        if (at < ops_cap) { kgwe_mig_op op; op.gpu_idx = g; op.profile = (uint8_t)(2 * gq + 1 + c); op.start = (uint8_t)mig_start(gq, b - mig_bit_first(gq)); op.size = (uint8_t)mig_size(gq); op.pad = KGWE_MIG_OP_DESTROY; ops[at] = op; }
+                    }
+                    for (uint32_t m = want & ~have; m; m &= m - 1u, ++at) {
+                        const int b = __ffs((int)m) - 1;
+                        if (at < ops_cap) { kgwe_mig_op op; op.gpu_idx = g; op.profile = (uint8_t)(2 * q + 1 + c); op.start = (uint8_t)mig_start(q, b - mig_bit_first(q)); op.size = (uint8_t)mig_size(q); op.pad = KGWE_MIG_OP_CREATE; ops[at] = op; }
+                    }
+                }
+                __syncthreads();
+                if (tid == 0) carry += tot;
+                __syncthreads();
+            }
+        }
+    __syncthreads();
+    if (tid == 0) *n_ops_out = carry;
+    if (tid < KGWE_MIG_PROFILES) supply_out[tid] = supply[tid];
+}
+
+// GPUs per (class, geometry) from the targets: floor of the shares, the remainder to the largest fractional parts, ties to
+// the lowest profile id.  counts[c] GPUs of class c are to be split.
+inline void mig_split(const uint32_t counts[2], const double* target, MigRanks& plan) {
+    for (int c = 0; c < 2; ++c) {
+        double S = 0.0;
+        for (int q = 0; q < MIG_GEOS; ++q) { const double t = target[2 * q + c]; if (t > 0.0) S += t; }
+        uint32_t n[MIG_GEOS] = {0, 0, 0, 0, 0}; double frac[MIG_GEOS] = {0, 0, 0, 0, 0};
+        if (S > 0.0 && counts[c] > 0) {
+            uint32_t used = 0;
+            for (int q = 0; q < MIG_GEOS; ++q) {
+                const double t = target[2 * q + c];
+                if (!(t > 0.0)) continue;
+                const double share = (t / S) * (double)counts[c];
+                n[q] = (uint32_t)share; frac[q] = share - (double)n[q]; used += n[q];
+            }
+            for (uint32_t left = counts[c] - used; left > 0; --left) {
+                int bq = -1;
+                for (int q = 0; q < MIG_GEOS; ++q) if (target[2 * q + c] > 0.0 && (bq < 0 || frac[q] > frac[bq])) bq = q;
+                if (bq < 0) break;
+                n[bq]++; frac[bq] = -1.0;
+            }
+        }
+        uint32_t r = 0;
+        for (int q = 0; q < MIG_GEOS; ++q) { plan.first_rank[c][q] = r; r += n[q]; }
+        plan.first_rank[c][MIG_GEOS] = r;
     }
 }
 

@@ -158,6 +158,17 @@ class Engine:
         self._check(self.lib.kgwe_mig_rebalance(self.h, abi.ptr(gpus), len(gpus), abi.ptr(target), abi.ptr(ops), cap, C.byref(n), abi.ptr(supply)))
         return ops[: min(n.value, cap)].copy(), supply, n.value
 
+    def mig_reconfigure(self, gpus, target, ops_cap=None):
+        """E2: reconfigure GPUs with nothing in use toward `target`, with destroy and create ops.  Returns (ops, supply[10], n_ops)."""
+        gpus = np.ascontiguousarray(gpus, dtype=abi.MIG_GPU_STATE)
+        target = np.ascontiguousarray(target, dtype=np.float64)
+        cap = ops_cap if ops_cap is not None else 21 * len(gpus)
+        ops = np.zeros(cap, dtype=abi.MIG_OP)
+        supply = np.zeros(10, dtype=np.uint32)
+        n = C.c_uint32(0)
+        self._check(self.lib.kgwe_mig_reconfigure(self.h, abi.ptr(gpus), len(gpus), abi.ptr(target), abi.ptr(ops), cap, C.byref(n), abi.ptr(supply)))
+        return ops[: min(n.value, cap)].copy(), supply, n.value
+
     def topology_hints(self, reqs):
         """DiscoveryService.GetTopologyHint for each request (discovery.go:222-247)."""
         reqs = np.ascontiguousarray(reqs, dtype=abi.HINT_REQ)

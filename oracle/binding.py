@@ -32,6 +32,7 @@ def lib():
         _lib.kgwe_oracle_topology_gauges.argtypes = [vp, u32, vp]
         _lib.kgwe_oracle_mig_pack.argtypes = [vp, u32, vp, u32, vp]
         _lib.kgwe_oracle_mig_rebalance.argtypes = [vp, u32, vp, vp, u32, C.POINTER(u32), vp]
+        _lib.kgwe_oracle_mig_reconfigure.argtypes = [vp, u32, vp, vp, u32, C.POINTER(u32), vp]
         _lib.kgwe_oracle_schedule_gangs.argtypes = [vp, vp, u32, vp, u32, vp, u32, vp, vp, vp, vp, C.POINTER(u32), C.c_int]
         _lib.kgwe_oracle_placement_terms.argtypes = [vp, vp, u32, vp, u32, vp]
         _lib.kgwe_oracle_schedule_queue.argtypes = [vp, vp, u32, vp, u32, vp, u32, vp, vp, vp, C.POINTER(u32), C.c_int, C.POINTER(Counters)]
@@ -131,6 +132,19 @@ def mig_rebalance(abi, gpus, target, ops_cap=None):
     supply = np.zeros(10, dtype=np.uint32)
     n = C.c_uint32(0)
     rc = lib().kgwe_oracle_mig_rebalance(_p(gpus), len(gpus), _p(target), _p(ops), cap, C.byref(n), _p(supply))
+    if rc != 0:
+        raise RuntimeError(f"oracle error {rc}")
+    return ops[: min(n.value, cap)].copy(), supply, n.value
+
+
+def mig_reconfigure(abi, gpus, target, ops_cap=None):
+    gpus = np.ascontiguousarray(gpus, dtype=abi.MIG_GPU_STATE)
+    target = np.ascontiguousarray(target, dtype=np.float64)
+    cap = ops_cap if ops_cap is not None else 21 * len(gpus)
+    ops = np.zeros(cap, dtype=abi.MIG_OP)
+    supply = np.zeros(10, dtype=np.uint32)
+    n = C.c_uint32(0)
+    rc = lib().kgwe_oracle_mig_reconfigure(_p(gpus), len(gpus), _p(target), _p(ops), cap, C.byref(n), _p(supply))
     if rc != 0:
         raise RuntimeError(f"oracle error {rc}")
     return ops[: min(n.value, cap)].copy(), supply, n.value

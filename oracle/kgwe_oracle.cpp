@@ -942,39 +942,90 @@ extern "C" int kgwe_oracle_mig_pack(kgwe_mig_gpu* gpus, uint32_t n_gpus, const u
     return KGWE_OK;
 }
 
+namespace mig {
+// How many GPUs each geometry of class c gets out of `count`: shares of the positive targets of that class, rounded down,
+// the GPUs left over handed out one each in order of decreasing fractional part (ties: lower geometry first).  Written
+// from the spec in include/kgwe_engine.h with a sort, on purpose differently from the engine's host code.
+std::vector<uint32_t> split(uint32_t count, const double* target, int c) {
+    std::vector<uint32_t> n(5, 0);
+    double total = 0.0;
+    for (int q = 0; q < 5; ++q) if (target[2 * q + c] > 0.0) total += target[2 * q + c];
+    if (!(total > 0.0) || count == 0) return n;
+    struct Rem { double frac; int q; };
+    std::vector<Rem> rems;
+    uint32_t given = 0;
+    for (int q = 0; q < 5; ++q) {
+        if (!(target[2 * q + c] > 0.0)) continue;
+        const double share = (target[2 * q + c] / total) * (double)count;
+        n[q] = (uint32_t)share;
+        given += n[q];
+        rems.push_back({share - (double)n[q], q});
+    }
+    std::stable_sort(rems.begin(), rems.end(), [](const Rem& a, const Rem& b) { return a.frac > b.frac; });      // stable: ties keep geometry order
+    for (size_t i = 0; i < rems.size() && given < count; ++i, ++given) n[rems[i].q]++;
+    return n;
+}
+const int kStarts[5] = {7, 3, 2, 1, 1}, kStride[5] = {1, 2, 4, 0, 0};
+}  // namespace mig
+
 extern "C" int kgwe_oracle_mig_rebalance(const kgwe_mig_gpu* gpus, uint32_t n_gpus, const double* target,
                                          kgwe_mig_op* ops, uint32_t ops_cap, uint32_t* n_ops, uint32_t* supply) {
     if ((n_gpus && !gpus) || !target || !n_ops || !supply) return KGWE_ERR_INVALID_ARG;
-    const int kStarts[5] = {7, 3, 2, 1, 1}, kStride[5] = {1, 2, 4, 0, 0};
     std::vector<kgwe_mig_op> all;
     for (int p = 0; p < KGWE_MIG_PROFILES; ++p) supply[p] = 0;
     for (int c = 0; c < 2; ++c) {
         std::vector<uint32_t> idle;
         for (uint32_t g = 0; g < n_gpus; ++g) if (gpus[g].enabled && gpus[g].occ == 0 && (gpus[g].cls & 1) == c) idle.push_back(g);
-        double S = 0.0;
-        for (int q = 0; q < 5; ++q) if (target[2 * q + c] > 0.0) S += target[2 * q + c];
-        if (!(S > 0.0) || idle.empty()) continue;
-        uint32_t n[5] = {0, 0, 0, 0, 0}; double frac[5] = {0, 0, 0, 0, 0}; uint32_t used = 0;
-        for (int q = 0; q < 5; ++q) {
-            const double t = target[2 * q + c];
-            if (!(t > 0.0)) continue;
-            const double share = (t / S) * (double)idle.size();
-            n[q] = (uint32_t)share; frac[q] = share - (double)n[q]; used += n[q];
-        }
-        for (uint32_t left = (uint32_t)idle.size() - used; left > 0; --left) {
-            int bq = -1;
-            for (int q = 0; q < 5; ++q) if (target[2 * q + c] > 0.0 && (bq < 0 || frac[q] > frac[bq])) bq = q;
-            if (bq < 0) break;
-            n[bq]++; frac[bq] = -1.0;
-        }
+        const std::vector<uint32_t> n = mig::split((uint32_t)idle.size(), target, c);
         size_t at = 0;
         for (int q = 0; q < 5; ++q)
             for (uint32_t i = 0; i < n[q]; ++i, ++at)
-                for (int sidx = 0; sidx < kStarts[q]; ++sidx) {
+                for (int sidx = 0; sidx < mig::kStarts[q]; ++sidx) {
                     kgwe_mig_op op; memset(&op, 0, sizeof op);
-                    op.gpu_idx = idle[at]; op.profile = (uint8_t)(2 * q + 1 + c); op.start = (uint8_t)(sidx * kStride[q]); op.size = (uint8_t)mig::kSize[q];
+                    op.gpu_idx = idle[at]; op.profile = (uint8_t)(2 * q + 1 + c); op.start = (uint8_t)(sidx * mig::kStride[q]); op.size = (uint8_t)mig::kSize[q];
                     all.push_back(op); supply[2 * q + c]++;
                 }
+    }
+    *n_ops = (uint32_t)all.size();
+    for (uint32_t i = 0; i < all.size() && i < ops_cap; ++i) ops[i] = all[i];
+    return KGWE_OK;
+}
+
+// The reconfiguration pass with destroy ops (spec: kgwe_mig_reconfigure in include/kgwe_engine.h), by plain loops over the
+// 14 legal placements in bit order.
+extern "C" int kgwe_oracle_mig_reconfigure(const kgwe_mig_gpu_state* gpus, uint32_t n_gpus, const double* target,
+                                           kgwe_mig_op* ops, uint32_t ops_cap, uint32_t* n_ops, uint32_t* supply) {
+    if ((n_gpus && !gpus) || !target || !n_ops || !supply) return KGWE_ERR_INVALID_ARG;
+    const std::vector<mig::Placement> legal = mig::legal();          // index = placement bit
+    std::vector<kgwe_mig_op> all;
+    for (int p = 0; p < KGWE_MIG_PROFILES; ++p) supply[p] = 0;
+    for (uint32_t g = 0; g < n_gpus; ++g) {                          // GPUs with something running keep what they have
+        if (!gpus[g].enabled || gpus[g].in_use == 0) continue;
+        for (int b = 0; b < 14; ++b)
+            if ((gpus[g].created >> b & 1) && !(gpus[g].in_use >> b & 1)) supply[2 * legal[b].geo + (gpus[g].cls & 1)]++;
+    }
+    for (int c = 0; c < 2; ++c) {
+        std::vector<uint32_t> free_gpus;
+        for (uint32_t g = 0; g < n_gpus; ++g) if (gpus[g].enabled && gpus[g].in_use == 0 && (gpus[g].cls & 1) == c) free_gpus.push_back(g);
+        const std::vector<uint32_t> n = mig::split((uint32_t)free_gpus.size(), target, c);
+        size_t at = 0;
+        for (int q = 0; q < 5; ++q)
+            for (uint32_t i = 0; i < n[q]; ++i, ++at) {
+                const uint32_t g = free_gpus[at];
+                for (int b = 0; b < 14; ++b)                         // whatever exists and is not wanted goes
+                    if ((gpus[g].created >> b & 1) && legal[b].geo != q) {
+                        kgwe_mig_op op; memset(&op, 0, sizeof op);
+                        op.gpu_idx = g; op.profile = (uint8_t)(2 * legal[b].geo + 1 + c); op.start = (uint8_t)legal[b].start; op.size = (uint8_t)legal[b].size; op.pad = KGWE_MIG_OP_DESTROY;
+                        all.push_back(op);
+                    }
+                for (int b = 0; b < 14; ++b)                         // whatever is wanted and does not exist yet comes
+                    if (legal[b].geo == q && !(gpus[g].created >> b & 1)) {
+                        kgwe_mig_op op; memset(&op, 0, sizeof op);
+                        op.gpu_idx = g; op.profile = (uint8_t)(2 * q + 1 + c); op.start = (uint8_t)legal[b].start; op.size = (uint8_t)legal[b].size; op.pad = KGWE_MIG_OP_CREATE;
+                        all.push_back(op);
+                    }
+                supply[2 * q + c] += (uint32_t)mig::kStarts[q];
+            }
     }
     *n_ops = (uint32_t)all.size();
     for (uint32_t i = 0; i < all.size() && i < ops_cap; ++i) ops[i] = all[i];

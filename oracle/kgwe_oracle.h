@@ -83,6 +83,8 @@ int kgwe_oracle_topology_gauges(const kgwe_node_image* nodes, uint32_t n_nodes, 
 int kgwe_oracle_mig_pack(kgwe_mig_gpu* gpus, uint32_t n_gpus, const uint8_t* profiles, uint32_t n_reqs, kgwe_mig_assignment* out);
 int kgwe_oracle_mig_rebalance(const kgwe_mig_gpu* gpus, uint32_t n_gpus, const double* target,
                               kgwe_mig_op* ops, uint32_t ops_cap, uint32_t* n_ops, uint32_t* supply);
+int kgwe_oracle_mig_reconfigure(const kgwe_mig_gpu_state* gpus, uint32_t n_gpus, const double* target,
+                                kgwe_mig_op* ops, uint32_t ops_cap, uint32_t* n_ops, uint32_t* supply);
 
 #ifdef __cplusplus
 }

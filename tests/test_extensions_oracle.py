@@ -97,6 +97,31 @@ def test_mig_rebalance_known_answers(kg, orc):
     assert not (ops["gpu_idx"] >= 10).any()
 
 
+def test_mig_reconfigure_known_answers(kg, orc):
+    """The reconfiguration pass with destroy ops, worked by hand.  Placement bits: 0..6 = 1g at slice 0..6, 7..9 = 2g at
+    0/2/4, 10..11 = 3g at 0/4, 12 = 4g, 13 = 7g.  Five 80 GB-class GPUs (class 1), target 1g.10gb : 3g.40gb = 1 : 1."""
+    abi = kg.abi
+    g = np.zeros(5, dtype=abi.MIG_GPU_STATE)
+    g["cls"], g["enabled"] = 1, 1
+    g["created"][0] = 0b0000000_1111111                 # GPU 0: seven 1g instances, none in use - already what 1g wants
+    g["created"][1] = (1 << 7) | (1 << 10)               # GPU 1: a 2g at 0 and a 3g at 0 (an impossible mix on real hardware; the pass only reads bits)
+    g["created"][2] = 1 << 13; g["in_use"][2] = 1 << 13   # GPU 2: its 7g instance is running: left alone
+    g["created"][3] = 0                                  # GPU 3: nothing yet
+    g["created"][4] = (1 << 11) | (1 << 0) | (1 << 8); g["in_use"][4] = 1 << 0      # GPU 4: a 1g running -> left alone; its free 3g and 2g count as supply
+    target = np.zeros(10); target[1] = 0.5; target[5] = 0.5
+    ops, supply, n = orc.mig_reconfigure(abi, g, target)
+    # reconfigurable: GPUs 0, 1, 3 -> shares 1.5 / 1.5: one each, the third to the lower profile (tie) -> 1g gets GPUs 0, 1; 3g gets GPU 3
+    want = []
+    # GPU 0 (1g): nothing to do.  GPU 1 (1g): destroy 2g@0 (bit 7) and 3g@0 (bit 10), create 1g at 0..6
+    want += [(1, 4, 0, 2, 1), (1, 6, 0, 4, 1)] + [(1, 2, s, 1, 0) for s in range(7)]
+    # GPU 3 (3g): create 3g at 0 and 4
+    want += [(3, 6, 0, 4, 0), (3, 6, 4, 4, 0)]
+    got = [(int(o["gpu_idx"]), int(o["profile"]), int(o["start"]), int(o["size"]), int(o["pad"])) for o in ops]
+    assert n == len(want) and got == want
+    # supply: 1g.10gb: 2 GPUs x 7; 3g.40gb: GPU 3's two + GPU 4's free one; 2g.20gb: GPU 4's free one
+    assert supply.tolist() == [0, 14, 0, 1, 0, 3, 0, 0, 0, 0]
+
+
 def test_topology_hint_known_answers(kg, orc):
     """GetTopologyHint (discovery.go:222-247, 378-488), hand-derived: base 50, +30 linked group, +10 same NUMA,
     +5 per selected GPU of the wanted architecture; availability = healthy and (free MIG instance | util < 90)."""

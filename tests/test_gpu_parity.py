@@ -452,6 +452,36 @@ def test_mig_pack_and_rebalance_extension(kg, orc):
     eng.close()
 
 
+def test_mig_large_table_and_reconfigure(kg, orc):
+    """E2: a table too large for the tournament-tree kernel takes the scan form of the packer (vs the oracle); the
+    reconfiguration pass with destroy ops vs its plain-loop oracle on random instance layouts, config 4's size included."""
+    abi, synth = kg.abi, kg.synth
+    eng = kg.Engine(max_nodes=1)
+    gpus, profiles = synth.make_mig(26000, 1200, seed=31)
+    a, after = eng.mig_pack(gpus, profiles)
+    o, o_after = orc.mig_pack(abi, gpus, profiles)
+    assert a.tobytes() == o.tobytes() and after.tobytes() == o_after.tobytes()
+    rng = synth.SplitMix64(5)
+    for n in (1, 37, 1024, 1025, 10000):
+        st = np.zeros(n, dtype=abi.MIG_GPU_STATE)
+        st["cls"] = rng.randint(0, 1, n); st["enabled"] = (rng.uniform(n) > 0.05).astype(np.uint8)
+        st["created"] = (rng.randint(0, (1 << 14) - 1, n) & rng.randint(0, (1 << 14) - 1, n)).astype(np.uint16)
+        busy = rng.uniform(n) < 0.4
+        st["in_use"] = np.where(busy, st["created"] & rng.randint(0, (1 << 14) - 1, n).astype(np.uint16), 0).astype(np.uint16)
+        t = rng.uniform(10) * (rng.uniform(10) < 0.5)
+        target = t / t.sum() * 0.9 if t.sum() > 0 else t
+        ops, supply, n_ops = eng.mig_reconfigure(st, target)
+        o_ops, o_supply, o_n = orc.mig_reconfigure(abi, st, target)
+        assert n_ops == o_n and supply.tolist() == o_supply.tolist(), n
+        assert ops.tobytes() == o_ops.tobytes(), n
+        ops2, _, n2 = eng.mig_reconfigure(st, target, ops_cap=5)            # a short op buffer still reports the full plan
+        assert n2 == o_n and ops2.tobytes() == o_ops[:5].tobytes()
+    bad = np.zeros(1, dtype=abi.MIG_GPU_STATE); bad["in_use"] = 1
+    with pytest.raises(kg.EngineError):
+        eng.mig_reconfigure(bad, np.zeros(10))
+    eng.close()
+
+
 def test_latency_path_small_batches(kg, orc):
     """Per-pod Prioritize calls (<= 32 pods, top-1 only) take the zero-copy single-launch path:
     pods of different preferences side by side (lane groups of one warp on different branches),
