@@ -107,20 +107,25 @@ mig_pack_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uint8_t*
 }
 
 // K4, tournament-tree form (tables of up to MIG_TREE_MAX_GPUS GPUs): requests are inherently sequential - each one must see
-// the commits before it - so what counts is the length of the per-request dependency chain, not the width of the machine.
-// Per (class, geometry) a 32-ary min tree over the GPUs keeps the best placement key of every group of 32 GPUs, of every
-// group of 32 groups, and at the root: a request is ONE shared-memory read of its root, and its commit only has to repair
-// the path above the one GPU that changed - three warp-wide REDUX.MIN steps per tree, the five trees of the GPU's class
-// repaired by five warps side by side.  Leaves are one byte per (geometry, GPU): class << 7 | cost << 3 | start, 0x7F = no fit.
+// the commits before it - and ONE CTA serves them, so what counts is the length of the per-request instruction chain (a warp
+// issues in order), not the width of the machine.  Per (class, geometry) a 32-ary min tree over the GPUs keeps the best
+// placement key of every group of 32 GPUs, of every group of 32 groups, and at the root: a request is ONE shared-memory read
+// of its root, and its commit only repairs the path above the one GPU that changed - three warp-wide REDUX.MIN per tree, one
+// value per lane and level, the five trees of the GPU's class repaired by five warps side by side.  The three rows a warp
+// needs are loaded up front (their addresses only depend on the GPU); each level's fresh minimum replaces the stale entry of
+// the next row in a register.  The key carries the winner's occupancy (cost << 27 | gpu << 11 | occ << 3 | start), so the
+// commit needs no look-up of the GPU's state.  Leaves: one byte per (geometry, GPU), class << 7 | cost << 3 | start, 0x7F = no fit.
+// (A two-level tree with several values per lane was measured slower - 20 vs 12 ms for 50,000 requests on 10,000 GPUs: the
+// extra per-lane instructions cost more than the REDUX they save.)
 constexpr int MIGT_THREADS = 160;                  // five warps: warp w repairs the tree of geometry w
 constexpr uint32_t MIG_TREE_MAX_GPUS = 24576;      // 3 levels of 32 cover 32,768; shared memory (8.3 B per GPU) sets this lower
 constexpr uint32_t MIG_KEY_NONE = 0xFFFFFFFFu;
 __host__ __device__ inline size_t mig_tree_smem(uint32_t n_gpus) {
     const size_t n_pad = (n_gpus + 31) & ~31u, n1 = n_pad / 32, n2 = (n1 + 31) / 32;
-    return MIG_GEOS * 256 + 2 * n_pad + MIG_GEOS * n_pad + 10 * 4 * (n1 + n2 * 32 + 1) + 1024 + 64;
+    return MIG_GEOS * 256 + 2 * n_pad + MIG_GEOS * n_pad + 10 * 4 * (n1 + n2 * 32 + 1) + 1024 + 128;
 }
-__device__ __forceinline__ uint32_t mig_leaf_key(uint32_t leaf, uint32_t cls, uint32_t g) {
-    return ((leaf >> 7) == cls && (leaf & 0x7Fu) != 0x7Fu) ? ((((leaf >> 3) & 0xFu) << 27) | (g << 3) | (leaf & 7u)) : MIG_KEY_NONE;
+__device__ __forceinline__ uint32_t mig_leaf_key(uint32_t leaf, uint32_t cls, uint32_t g, uint32_t occ) {
+    return ((leaf >> 7) == cls && (leaf & 0x7Fu) != 0x7Fu) ? ((((leaf >> 3) & 0xFu) << 27) | (g << 11) | ((occ & 0xffu) << 3) | (leaf & 7u)) : MIG_KEY_NONE;
 }
 __global__ void __launch_bounds__(MIGT_THREADS, 1)
 mig_pack_tree_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uint8_t* __restrict__ profiles, uint32_t n_reqs,
@@ -128,8 +133,8 @@ mig_pack_tree_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uin
     extern __shared__ __align__(16) unsigned char msm[];
     const uint32_t n_pad = (n_gpus + 31u) & ~31u, n1 = n_pad / 32u, n2 = (n1 + 31u) / 32u;
     uint32_t* L1 = reinterpret_cast<uint32_t*>(msm);                        // [10][n1]
-    uint32_t* L2 = L1 + 10 * n1;                                            // [10][n2 * 32] (padded with MIG_KEY_NONE)
-    uint32_t* root = L2 + 10 * n2 * 32;                                     // [10] (+ pad)
+    uint32_t* L2 = L1 + 10 * n1;                                            // [10][32] (padded with MIG_KEY_NONE; n2 <= 32)
+    uint32_t* root = L2 + 10 * 32;                                          // [10] (+ pad)
     uint16_t* state = reinterpret_cast<uint16_t*>(root + 16);               // [n_pad]: (enabled | cls << 1) << 8 | occ
     uint8_t* leaf = reinterpret_cast<uint8_t*>(state + n_pad);              // [5][n_pad]
     uint8_t* lut = leaf + MIG_GEOS * n_pad;                                 // [5][256]
@@ -146,71 +151,65 @@ mig_pack_tree_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uin
             leaf[q * n_pad + g] = (uint8_t)((((st >> 9) & 1u) << 7) | (b == 0xFFu ? 0x7Fu : b));
         }
     }
-    for (uint32_t i = tid; i < 10 * n2 * 32; i += MIGT_THREADS) L2[i] = MIG_KEY_NONE;
+    for (uint32_t i = tid; i < 10 * 32; i += MIGT_THREADS) L2[i] = MIG_KEY_NONE;
     __syncthreads();
     // level 1: tree t = cls * 5 + geometry, node i = min over GPUs 32 i .. 32 i + 31
     for (uint32_t w = warp; w < 10 * n1; w += MIGT_THREADS / 32) {
         const uint32_t t = w / n1, i = w % n1, g = i * 32 + lane;
-        const uint32_t k = __reduce_min_sync(0xffffffffu, mig_leaf_key(leaf[(t % 5) * n_pad + g], t / 5, g));
+        const uint32_t k = __reduce_min_sync(0xffffffffu, mig_leaf_key(leaf[(t % 5) * n_pad + g], t / 5, g, state[g]));
         if (lane == 0) L1[t * n1 + i] = k;
     }
     __syncthreads();
     for (uint32_t w = warp; w < 10 * n2; w += MIGT_THREADS / 32) {
         const uint32_t t = w / n2, i = w % n2, j = i * 32 + lane;
         const uint32_t k = __reduce_min_sync(0xffffffffu, j < n1 ? L1[t * n1 + j] : MIG_KEY_NONE);
-        if (lane == 0) L2[t * n2 * 32 + i] = k;
+        if (lane == 0) L2[t * 32 + i] = k;
     }
     __syncthreads();
     for (uint32_t t = warp; t < 10; t += MIGT_THREADS / 32) {
-        const uint32_t k = __reduce_min_sync(0xffffffffu, L2[t * n2 * 32 + lane]);        // n2 <= 32
+        const uint32_t k = __reduce_min_sync(0xffffffffu, L2[t * 32 + lane]);
         if (lane == 0) root[t] = k;
     }
+    for (uint32_t i = tid; i < 1024u && i < n_reqs; i += MIGT_THREADS) req_stage[i] = profiles[i];
     __syncthreads();
+    int profile = n_reqs ? req_stage[0] : 0;
     for (uint32_t r = 0; r < n_reqs; ++r) {
-        if ((r & 1023u) == 0) {                       // refill the staged profiles (every request ends in a barrier, so nobody still reads the old ones)
-            for (uint32_t i = tid; i < 1024u && r + i < n_reqs; i += MIGT_THREADS) req_stage[i] = profiles[r + i];
-            __syncthreads();
-        }
-        const int profile = req_stage[r & 1023u];
+        const int profile_next = req_stage[(r + 1u) & 1023u];      // the next request's profile is fetched now, off the critical path
         const bool known = profile >= 1 && profile <= KGWE_MIG_PROFILES;
         const int geo = known ? mig_geo(profile) : 0, cls = known ? mig_cls(profile) : 0;
         const uint32_t key = known ? root[cls * 5 + geo] : MIG_KEY_NONE;
         if (key == MIG_KEY_NONE) {                    // nothing fits: nothing changes
             if (tid == 0) { kgwe_mig_assignment a; a.gpu_idx = KGWE_NO_NODE; a.start = a.size = a.cost = 0; a.profile = (uint8_t)profile; out[r] = a; }
-            __syncthreads();                          // (warps stay in step: a warp running ahead into the next commit would change a root under a slower one)
-            continue;
-        }
-        const uint32_t g = (key >> 3) & 0xFFFFFFu, start = key & 7u, size = (uint32_t)mig_size(geo);
-        volatile uint16_t* vstate = state;
-        const uint32_t st_new = (uint32_t)vstate[g] | (((1u << size) - 1u) << start);        // (idempotent: whoever reads the old or the new word derives the same)
-        if (tid == 0) {
-            vstate[g] = (uint16_t)st_new;
-            kgwe_mig_assignment a;
-            a.gpu_idx = g; a.start = (uint8_t)start; a.size = (uint8_t)size; a.cost = (uint8_t)(key >> 27); a.profile = (uint8_t)profile;
-            out[r] = a;
-        }
-        // warp w repairs the tree of (cls, geometry w): the GPU's leaf, its group of 32, that group's group, the root
-        {
+        } else {
+            const uint32_t g = (key >> 11) & 0xFFFFu, start = key & 7u, size = (uint32_t)mig_size(geo);
+            const uint32_t occ_new = ((key >> 3) & 0xffu) | (((1u << size) - 1u) << start);
+            const uint32_t b = lut[warp * 256 + occ_new];
             const uint32_t t = (uint32_t)cls * 5u + (uint32_t)warp;
-            if (lane == 0) {
-                const uint32_t b = lut[warp * 256 + (st_new & 0xffu)];
-                leaf[warp * n_pad + g] = (uint8_t)(((uint32_t)cls << 7) | (b == 0xFFu ? 0x7Fu : b));
+            const uint32_t i1 = g >> 5, i2 = i1 >> 5, gl = (g & ~31u) + lane, j = (i1 & ~31u) + lane;
+            const uint32_t leaf_old = leaf[warp * n_pad + gl];
+            const uint32_t st_old = state[gl];
+            const uint32_t row1 = j < n1 ? L1[t * n1 + j] : MIG_KEY_NONE;
+            const uint32_t row2 = L2[t * 32 + lane];
+            if (tid == 0) {
+                kgwe_mig_assignment a;
+                a.gpu_idx = g; a.start = (uint8_t)start; a.size = (uint8_t)size; a.cost = (uint8_t)(key >> 27); a.profile = (uint8_t)profile;
+                out[r] = a;
             }
-            __syncwarp();
-            const uint32_t i1 = g >> 5, gl = (g & ~31u) + lane;
-            const uint32_t k1 = __reduce_min_sync(0xffffffffu, mig_leaf_key(leaf[warp * n_pad + gl], (uint32_t)cls, gl));
-            if (lane == 0) L1[t * n1 + i1] = k1;
-            __syncwarp();
-            const uint32_t i2 = i1 >> 5, j = (i1 & ~31u) + lane;
-            const uint32_t k2 = __reduce_min_sync(0xffffffffu, j < n1 ? L1[t * n1 + j] : MIG_KEY_NONE);
-            if (lane == 0) L2[t * n2 * 32 + i2] = k2;
-            __syncwarp();
-            const uint32_t k3 = __reduce_min_sync(0xffffffffu, L2[t * n2 * 32 + lane]);
-            if (lane == 0) root[t] = k3;
+            const uint32_t leaf_new = ((uint32_t)cls << 7) | (b == 0xFFu ? 0x7Fu : b);
+            const uint32_t k1 = __reduce_min_sync(0xffffffffu, mig_leaf_key(gl == g ? leaf_new : leaf_old, (uint32_t)cls, gl, gl == g ? occ_new : st_old));
+            const uint32_t k2 = __reduce_min_sync(0xffffffffu, j == i1 ? k1 : row1);
+            const uint32_t k3 = __reduce_min_sync(0xffffffffu, (uint32_t)lane == i2 ? k2 : row2);
+            if (lane == 0) { leaf[warp * n_pad + g] = (uint8_t)leaf_new; L1[t * n1 + i1] = k1; L2[t * 32 + i2] = k2; root[t] = k3; if (warp == 0) state[g] = (uint16_t)(0x100u | ((uint32_t)cls << 9) | occ_new); }
         }
-        __syncthreads();                              // the next request reads the repaired roots
+        // every 512 requests the half of the ring consumed last is refilled with the profiles 512..1023 requests ahead (the
+        // loads are issued by all threads at once; a per-request refill would put a global load in front of every barrier)
+        if ((r & 511u) == 511u && r + 513u < n_reqs) {
+            const uint32_t first = r + 513u;
+            for (uint32_t i = tid; i < 512u && first + i < n_reqs; i += MIGT_THREADS) req_stage[(first + i) & 1023u] = profiles[first + i];
+        }
+        __syncthreads();                              // warps stay in step; the next request reads the repaired roots
+        profile = profile_next;
     }
-    __syncthreads();
     for (uint32_t g = tid; g < n_gpus; g += MIGT_THREADS) gpus[g].occ = (uint8_t)(state[g] & 0xff);
 }
 
