@@ -44,6 +44,7 @@ extern "C" {
 #define KGWE_MAX_TOPK      16
 #define KGWE_NO_NODE       0xFFFFFFFFu
 #define KGWE_MAX_BW_GBPS   100000.0   /* upsert rejects bandwidths outside [0, this] or non-finite */
+#define KGWE_LATENCY_BUCKETS 10  /* upper edges in microseconds: 10 25 50 100 250 500 1000 2500 5000 +Inf */
 
 typedef enum kgwe_status {
     KGWE_OK                =  0,
@@ -212,6 +213,15 @@ typedef struct kgwe_stats {
     uint64_t score_kernel_timed; /* how many K1 launches that sum covers */
     uint64_t candidates_resolved;/* candidates by the reference's counting rule: A per NVLink-greedy evaluation with
                                   * k >= 2 on an eligible node, C(A,k) in exhaustive mode, 1 otherwise - whatever the engine did */
+    /* Scheduling-latency histogram, the engine-side source of the reference's kgwe_scheduling_latency_ms
+     * (src/monitoring/prometheus_exporter.go:258-263, read by the Grafana p99 panel, deploy/monitoring/grafana-dashboard.json:191).
+     * Same bucket edges as there - 10, 25, 50, 100, 250, 500, 1000, 2500, 5000, +Inf - but in MICROSECONDS: a call here takes
+     * tens of microseconds, the reference's millisecond buckets would put everything into the first one.  Counts are per
+     * bucket (not cumulative).  Observed: the wall time of every kgwe_score_batch call (one observation per call), and for
+     * kgwe_schedule_queue / kgwe_schedule_gangs the call's wall time divided by its workloads, once per workload. */
+    uint64_t latency_us_bucket[KGWE_LATENCY_BUCKETS];
+    uint64_t latency_count;
+    double   latency_sum_us;
 } kgwe_stats;
 
 typedef struct kgwe_engine kgwe_engine;

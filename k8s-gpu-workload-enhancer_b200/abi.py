@@ -73,7 +73,11 @@ class Stats(C.Structure):
                 ("failed", C.c_uint64), ("topology_optimal", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("last_call_gpu_ms", C.c_double),
                 ("n_nodes", C.c_uint32), ("n_allocations", C.c_uint32),
-                ("score_kernel_ms", C.c_double), ("score_kernel_timed", C.c_uint64), ("candidates_resolved", C.c_uint64)]
+                ("score_kernel_ms", C.c_double), ("score_kernel_timed", C.c_uint64), ("candidates_resolved", C.c_uint64),
+                ("latency_us_bucket", C.c_uint64 * 10), ("latency_count", C.c_uint64), ("latency_sum_us", C.c_double)]
+
+
+LATENCY_BUCKET_EDGES_US = [10, 25, 50, 100, 250, 500, 1000, 2500, 5000, float("inf")]
 
 
 def default_config(max_nodes, device=0, node_base=0):

@@ -213,6 +213,22 @@ int validate_pods(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n) {
 }
 
 uint32_t hint_row_bytes(const kgwe_engine* e) { return (e->n_nodes + 7) / 8; }
+
+// Latency histogram of kgwe_stats: `n` observations of `us` microseconds each.
+void observe_latency(kgwe_engine* e, double us, uint64_t n) {
+    static const double edges[KGWE_LATENCY_BUCKETS - 1] = {10, 25, 50, 100, 250, 500, 1000, 2500, 5000};
+    int b = 0;
+    while (b < KGWE_LATENCY_BUCKETS - 1 && us > edges[b]) ++b;
+    e->stats.latency_us_bucket[b] += n; e->stats.latency_count += n; e->stats.latency_sum_us += us * (double)n;
+}
+struct CallTimer {
+    kgwe_engine* e; uint64_t n; std::chrono::steady_clock::time_point t0;
+    CallTimer(kgwe_engine* e_, uint64_t n_) : e(e_), n(n_), t0(std::chrono::steady_clock::now()) {}
+    void done(bool per_item) {
+        const double us = std::chrono::duration<double, std::micro>(std::chrono::steady_clock::now() - t0).count();
+        if (n) observe_latency(e, per_item ? us / (double)n : us, per_item ? n : 1);
+    }
+};
 size_t sched_tile_smem_bytes() { return (size_t)TILE_NODES * (sizeof(DevNode) + sizeof(NodeFast) + sizeof(NodeCtx) + 64) + 16; }
 
 // ---- K1 launch ------------------------------------------------------------------------------------
@@ -663,6 +679,7 @@ int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, 
     if (!e) return KGWE_ERR_INVALID_ARG;
     std::lock_guard<std::mutex> lk(e->mu);
     if (topk > KGWE_MAX_TOPK || (topk && !out_topk) || (n_pods && !pods)) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    CallTimer timer(e, n_pods);
     int rc = validate_pods(e, pods, n_pods);
     if (rc != KGWE_OK) return rc;
     CU(e, cudaSetDevice(e->cfg.device));
@@ -712,6 +729,7 @@ int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, 
         memcpy(out_topk, e->h_topk.p, (size_t)n_pods * sizeof(kgwe_placement));
         e->stats.h2d_bytes += (uint64_t)n_pods * sizeof(kgwe_pod_req) + (hint ? (uint64_t)n_pods * row : 0);
         e->stats.d2h_bytes += (uint64_t)n_pods * sizeof(kgwe_placement);
+        timer.done(false);
         return KGWE_OK;
     }
     // pods per pass bounded by the score-matrix scratch
@@ -755,6 +773,7 @@ int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, 
         if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) == cudaSuccess) gpu_ms += ms;
     }
     e->stats.last_call_gpu_ms = gpu_ms;
+    timer.done(false);
     return KGWE_OK;
 }
 
@@ -883,6 +902,7 @@ int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pod
     if (!e) return KGWE_ERR_INVALID_ARG;
     std::lock_guard<std::mutex> lk(e->mu);
     if ((n_pods && !pods) || (n_pods && !out)) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    CallTimer timer(e, n_pods);
     int rc = validate_pods(e, pods, n_pods);
     if (rc != KGWE_OK) return rc;
     CU(e, cudaSetDevice(e->cfg.device));
@@ -928,6 +948,7 @@ int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pod
         p0 = p1;
     }
     e->stats.last_call_gpu_ms = gpu_ms;
+    timer.done(true);
     return KGWE_OK;
 }
 
@@ -939,6 +960,7 @@ int kgwe_schedule_gangs(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pod
     if (!e) return KGWE_ERR_INVALID_ARG;
     std::lock_guard<std::mutex> lk(e->mu);
     if (n_pods && (!pods || !out || !gang_of)) return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments");
+    CallTimer timer(e, n_pods);
     int rc = validate_pods(e, pods, n_pods);
     if (rc != KGWE_OK) return rc;
     {
@@ -983,6 +1005,7 @@ int kgwe_schedule_gangs(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pod
             q0 = q1;
         }
         e->stats.last_call_gpu_ms = gms;
+        timer.done(true);
         return KGWE_OK;
     }
     // Images too large for the tile form of the queue kernel: speculative windows.
@@ -1012,6 +1035,7 @@ int kgwe_schedule_gangs(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pod
         p0 += gend;
     }
     e->stats.last_call_gpu_ms = gpu_ms;
+    timer.done(true);
     return KGWE_OK;
 }
 

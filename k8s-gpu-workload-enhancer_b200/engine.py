@@ -198,7 +198,20 @@ class Engine:
     def stats(self):
         s = abi.Stats()
         self._check(self.lib.kgwe_get_stats(self.h, C.byref(s)))
-        return {name: getattr(s, name) for name, _ in abi.Stats._fields_}
+        d = {name: getattr(s, name) for name, _ in abi.Stats._fields_}
+        d["latency_us_bucket"] = list(d["latency_us_bucket"])
+        return d
+
+    def latency_quantile(self, q):
+        """Upper bucket edge (microseconds) below which a fraction q of the observed calls fell - what
+        histogram_quantile() of the Grafana p99 panel reads off the same buckets."""
+        st = self.stats()
+        need, seen = q * st["latency_count"], 0
+        for edge, n in zip(abi.LATENCY_BUCKET_EDGES_US, st["latency_us_bucket"]):
+            seen += n
+            if seen >= need and st["latency_count"]:
+                return edge
+        return None
 
 
 def unpack_order(order):

@@ -287,6 +287,58 @@ Result<TopologyHint> TopologyAwareScheduler::GetTopologyHint(const HintRequireme
     return r;
 }
 
+Result<SchedulingDecision> TopologyAwareScheduler::Bind(const GPUWorkload& w, const std::string& nodeName) {
+    const auto t0 = std::chrono::steady_clock::now();
+    Result<SchedulingDecision> r;
+    if (!HasTopology()) { r.error = "cluster topology not available"; return r; }
+    const uint32_t idx = NodeIndex(nodeName);
+    if (idx == KGWE_NO_NODE) { r.error = "node " + nodeName + " is not in the GPU topology snapshot"; return r; }
+    kgwe_stats st;
+    if (kgwe_get_stats(engine_, &st) != KGWE_OK) { r.error = kgwe_last_error(engine_); return r; }
+    std::vector<kgwe_node_score> sc(st.n_nodes);
+    std::vector<kgwe_placement> top(KGWE_MAX_TOPK);
+    const bool known_uid = wl_id_.count(w.UID) != 0;
+    const kgwe_pod_req p = PodReq(w, true);
+    auto forget = [&] { if (!known_uid) wl_id_.erase(w.UID); };
+    if (kgwe_score_batch(engine_, &p, 1, nullptr, sc.data(), KGWE_MAX_TOPK, top.data()) != KGWE_OK) { forget(); r.error = kgwe_last_error(engine_); return r; }
+    if (idx >= sc.size() || !(sc[idx].flags & KGWE_F_KEPT)) {
+        forget(); metrics_.TotalFailed++;
+        r.error = "failed to schedule workload " + w.Name + " after trying all nodes";          // scheduler.go:178 (the one node it was asked to try)
+        return r;
+    }
+    if (kgwe_alloc_commit(engine_, p.wl_id, idx, sc[idx].gpu_mask) != KGWE_OK) { forget(); metrics_.TotalFailed++; r.error = kgwe_last_error(engine_); return r; }
+    kgwe_placement pl; memset(&pl, 0, sizeof pl);
+    pl.node_idx = idx; pl.total = sc[idx].total; pl.topology = sc[idx].topology; pl.resource = sc[idx].resource; pl.balance = sc[idx].balance;
+    pl.gpu_mask = sc[idx].gpu_mask; pl.flags = sc[idx].flags; pl.order = sc[idx].order;
+    for (auto& t : top) if (t.node_idx == idx) pl.est_bandwidth_gbps = t.est_bandwidth_gbps;    // (known when the node is among the best 16)
+    r.value = DecisionOf(w, pl);
+    UpdateLatency(std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count());
+    metrics_.TotalScheduled++;
+    if (pl.topology >= 80) metrics_.TopologyOptimalPlacements++;
+    events_.push_back(SchedulingEvent{"Scheduled", w.UID, std::make_shared<SchedulingDecision>(r.value), ""});
+    return r;
+}
+
+std::string TopologyAwareScheduler::MetricsText() {
+    kgwe_stats st;
+    if (kgwe_get_stats(engine_, &st) != KGWE_OK) return "# kgwe_get_stats failed\n";
+    static const char* edges[KGWE_LATENCY_BUCKETS] = {"10", "25", "50", "100", "250", "500", "1000", "2500", "5000", "+Inf"};
+    std::string o;
+    char b[256];
+    o += "# HELP kgwe_scheduling_latency_us Histogram of engine call latency in microseconds (the reference's kgwe_scheduling_latency_ms buckets, scaled)\n# TYPE kgwe_scheduling_latency_us histogram\n";
+    uint64_t cum = 0;
+    for (int i = 0; i < KGWE_LATENCY_BUCKETS; ++i) { cum += st.latency_us_bucket[i]; snprintf(b, sizeof b, "kgwe_scheduling_latency_us_bucket{le=\"%s\"} %llu\n", edges[i], (unsigned long long)cum); o += b; }
+    snprintf(b, sizeof b, "kgwe_scheduling_latency_us_sum %.3f\nkgwe_scheduling_latency_us_count %llu\n", st.latency_sum_us, (unsigned long long)st.latency_count); o += b;
+    auto counter = [&](const char* name, const char* help, long long v) { snprintf(b, sizeof b, "# HELP %s %s\n# TYPE %s counter\n%s %lld\n", name, help, name, name, v); o += b; };
+    counter("kgwe_scheduling_attempts_total", "Total number of scheduling attempts", (long long)(metrics_.TotalScheduled + metrics_.TotalFailed));
+    counter("kgwe_scheduling_successes_total", "Total number of successful schedulings", (long long)metrics_.TotalScheduled);
+    counter("kgwe_scheduling_failures_total", "Total number of scheduling failures", (long long)metrics_.TotalFailed);
+    counter("kgwe_topology_optimal_placements_total", "Placements with TopologyScore >= 80", (long long)metrics_.TopologyOptimalPlacements);
+    counter("kgwe_engine_evaluations_total", "(pod, node) pairs scored by the engine", (long long)st.evaluations);
+    counter("kgwe_engine_candidates_total", "GPU subsets whose score the engine computed", (long long)st.candidates);
+    return o;
+}
+
 Result<std::map<std::string, int>> TopologyAwareScheduler::TopologyScores() {
     Result<std::map<std::string, int>> r;
     std::vector<int32_t> v(node_names_.size());

@@ -77,7 +77,7 @@ struct TopologyHint { std::string PreferredNode; std::vector<std::string> Prefer
 // kube-scheduler extender wire types (k8s.io/kube-scheduler/extender/v1: ExtenderFilterResult, HostPriority,
 // MaxExtenderPriority = 10).  The reference only CONFIGURES an extender (verbs filter / prioritize,
 // deploy/helm/kgwe/templates/scheduler-configmap.yaml:61-79) and ships no handler; these are the payloads
-// such handlers would fill from the engine ("next" row 8f.2), without the HTTP/JSON transport.
+// such handlers fill from the engine ("next" row 8f.2); the HTTP/JSON transport around them is kgwe_extender.hpp.
 struct ExtenderFilterResult { std::vector<std::string> NodeNames; std::map<std::string, std::string> FailedNodes; std::string Error; };
 struct HostPriority { std::string Host; int64_t Score = 0; };
 constexpr int64_t MaxExtenderPriority = 10;
@@ -118,6 +118,13 @@ public:
     // prioritize: TotalScore clamped to 0..100 and scaled to 0..MaxExtenderPriority.
     ExtenderFilterResult Filter(const GPUWorkload& workload, const std::vector<std::string>& nodeNames);
     std::vector<HostPriority> Prioritize(const GPUWorkload& workload, const std::vector<std::string>& nodeNames);
+    // The extender's bind verb for one pod: score it once more, and if `nodeName` still keeps it, record the GPUs the scorer
+    // selects there in the ledger (kgwe_alloc_commit refuses GPUs another workload took in the meantime,
+    // tryScheduleOnNode's re-check, scheduler.go:634-640).  Errors: the reference's strings where it has one.
+    Result<SchedulingDecision> Bind(const GPUWorkload& workload, const std::string& nodeName);
+    // Prometheus exposition text of the scheduler counters (prometheus_exporter.go:258-290 names) and of the engine's latency
+    // histogram (kgwe_stats.latency_us_bucket: the reference's bucket edges, in microseconds).
+    std::string MetricsText();
     Result<std::map<std::string, int>> TopologyScores();
     SchedulerMetrics GetMetrics() const { return metrics_; }            // scheduler.go:793
     std::deque<SchedulingEvent>& Events() { return events_; }           // scheduler.go:800 (a queue instead of a channel)

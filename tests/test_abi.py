@@ -23,7 +23,7 @@ def test_struct_layouts(kg):
     abi = kg.abi
     assert abi.NODE_IMAGE.itemsize == 768 and abi.NODE_IMAGE.fields["n_allocs"][1] == 760
     assert abi.POD_REQ.itemsize == 32 and abi.NODE_SCORE.itemsize == 16 and abi.PLACEMENT.itemsize == 32
-    assert C.sizeof(abi.Config) == 48 and C.sizeof(abi.Stats) == 104
+    assert C.sizeof(abi.Config) == 48 and C.sizeof(abi.Stats) == 200
     cfg = abi.Config()
     kg.abi.load_engine_lib().kgwe_config_default(C.byref(cfg))
     assert (cfg.struct_size, cfg.topology_weight, cfg.resource_weight, cfg.balance_weight, cfg.hint_bonus) == (48, 40, 35, 25, 10)

@@ -217,3 +217,19 @@ def test_error_messages_are_per_thread(kg):
     a.start(); b.start(); a.join(); b.join()
     assert all("node 1 not present" in m for m in seen["a"]) and all("node 99 out of range" in m for m in seen["b"])
     eng.close()
+
+
+def test_latency_histogram(kg):
+    """kgwe_stats carries the reference's scheduling-latency histogram (prometheus_exporter.go:258-263 bucket edges, in
+    microseconds): one observation per kgwe_score_batch call, one per workload of a queue call."""
+    abi = kg.abi
+    nodes, pods, led = kg.synth.config(1)
+    eng = engine_for(kg, nodes, led)
+    for i in range(200):
+        eng.score_batch(pods[i % 50:i % 50 + 1], len(nodes), want_scores=False, topk=1)
+    eng.schedule_queue(pods[:40])
+    st = eng.stats()
+    assert st["latency_count"] == 240 and sum(st["latency_us_bucket"]) == 240
+    assert st["latency_sum_us"] > 0 and st["latency_us_bucket"][-1] < 5                  # next to nothing beyond 5 ms
+    assert eng.latency_quantile(0.99) <= 250 and eng.latency_quantile(0.5) <= 100        # the p99 panel's reading of these buckets
+    eng.close()
