@@ -278,7 +278,7 @@ def run_kgwe(args):
                     "P2P stores from the finalisation kernel into every rank's gather buffer (symmetric memory) + one cross-GPU barrier" if (scorer.use_barrier or scorer.flags is None) else
                     "kgwe_score_merge_p2p: the finalisation kernel stores its records and then its flag into every rank's symmetric memory over NVLink; the merge kernel waits for the flags on the device (no collective, no barrier launch)")
     d_merged = scorer.d_merged
-    flush = torch.empty(160 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
+    flush = torch.empty(128 << 20, dtype=torch.uint8, device=dev)     # 134 MB > the 126 MB L2
 
     def step_device():
         flush.zero_()                                                    # L2 flush between steps
@@ -441,7 +441,7 @@ def run_kgwe(args):
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": shared_config(nodes, pods, ledger),
             "run": {"sharding": f"nodes by contiguous range over {world} rank(s)", "exchange": exchange,
-                    "l2": "160 MiB buffer written between steps (inside the timed region); each step also writes its P x N_local x 16 B score matrix (1.6 GB at 1 GPU, 200 MB at 8), both larger than the 126 MB L2",
+                    "l2": "128 MiB (134 MB) buffer written between steps (inside the timed region); each step also writes its P x N_local x 16 B score matrix (1.6 GB at 1 GPU, 200 MB at 8), both larger than the 126 MB L2",
                     "flush_ms_per_step": flush_ms, "ms_per_step_excl_flush": ms_total / args.steps - flush_ms,
                     "value_excl_flush": cand_total / args.steps / ((ms_total / args.steps - flush_ms) * 1e-3)},
             "evaluations_per_sec": ev_total / (ms_total * 1e-3),

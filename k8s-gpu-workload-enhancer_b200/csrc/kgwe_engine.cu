@@ -257,7 +257,7 @@ K1Plan plan_k1(const kgwe_engine* e, uint32_t n_pods, bool tables) {
     for (uint32_t waves = 1; waves <= 256; ++waves) {
         chunks = std::max(1u, std::min(n_pods, slots * waves / pl.n_tiles));
         ppc = (n_pods + chunks - 1) / chunks;
-        if (ppc <= max_ppc && (waves >= 2 || n_pods <= 64)) break;
+        if (ppc <= max_ppc) break;      // (one wave is fine: all CTAs of a launch do the same amount of work)
     }
     if (ppc > max_ppc) ppc = max_ppc;
     pl.ppc = ppc;

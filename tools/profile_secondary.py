@@ -1,6 +1,6 @@
 """Small driver for ncu captures of the secondary kernels: the stateful queue (K3, tile form) and the
 MIG bin-packing kernel (E2) on the BASELINE-sized inputs.  Run plain first, then under ncu:
-  ncu --set full --clock-control none -k regex:'schedule_tile_kernel|mig_pack_kernel' -c 2 -o out python tools/profile_secondary.py"""
+  ncu --set full --clock-control none -k regex:'schedule_tile_kernel|mig_pack_tree_kernel' -c 2 -o out python tools/profile_secondary.py"""
 import os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
