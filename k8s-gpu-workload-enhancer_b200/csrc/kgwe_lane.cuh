@@ -107,7 +107,7 @@ struct LaneTabs {
     uint32_t* mig;       // [3]  mig_free[0..9] as bytes
     int2*     memo;      // [7]  memoised winner per k: (TopologyScore or -1, join order)
     int4*     mat;       // [32] 16-byte units: int32 rows (unit 2m + half) or float64 rows (unit 4m + q)
-    uint32_t* subset;    // [256] E1 subset keys by (popcount, mask) slot
+    uint32_t* subset;    // [SUBSET_UNITS] 16-byte units of E1 subset keys (the pointer is to the lane's first unit)
     int       stride;
 };
 
@@ -339,16 +339,24 @@ __device__ inline void chain_f64_all_rec(const DevNode* rec, uint32_t avail, uin
 }
 
 // ---- E1 exhaustive subsets ------------------------------------------------------------------------
-__device__ __forceinline__ int subset_off(int k) {      // first table slot of popcount k: sum_{i<k} C(8,i)
-    return k <= 0 ? 0 : k == 1 ? 1 : k == 2 ? 9 : k == 3 ? 37 : k == 4 ? 93 : k == 5 ? 163 : k == 6 ? 219 : k == 7 ? 247 : k == 8 ? 255 : 256;
+// Subset keys of a node sit in (popcount, mask) order, every popcount class padded with zero keys to a multiple of four
+// entries, four entries to a 16-byte unit, units laid out [unit][lane]: an evaluation for group size k reads the units of
+// class k with conflict-free 128-bit loads.
+constexpr int SUBSET_ENTRIES = 264;               // 4 + 8 + 28 + 56 + 72 + 56 + 28 + 8 + 4
+constexpr int SUBSET_UNITS = SUBSET_ENTRIES / 4;
+__host__ __device__ inline int subset_off(int k) {      // first entry of popcount class k (a multiple of 4)
+    return k <= 0 ? 0 : k == 1 ? 4 : k == 2 ? 12 : k == 3 ? 40 : k == 4 ? 96 : k == 5 ? 168 : k == 6 ? 224 : k == 7 ? 252 : k == 8 ? 260 : 264;
 }
+// entry e of this lane's column, as a 32-bit word
+__device__ __forceinline__ uint32_t& subset_entry(uint32_t* col, int S, int e) { return col[((e >> 2) * S) * 4 + (e & 3)]; }
 // Subset keys of an integral node: key(mask) = total << 8 | 255 - mask when mask is an available clique on ACTIVE
 // links (both directions of every pair) with total > 0, else 0; total = sum over pairs i < j of bw(j -> i).
 // Built by subset extension: mask = rest + its highest GPU t adds sum_{i in rest} bw(t -> i).  slot_of[mask] is
-// the (popcount, mask)-ordered slot.  First pass leaves (total << 1 | valid) in the slots, the second pass keys.
-__device__ inline void lane_subset_build(const LaneTabs& tb, const LaneNode& ln, uint64_t colact, const uint8_t* slot_of) {
+// the entry of the mask.  First pass leaves (total << 1 | valid) in the entries, the second pass keys.
+__device__ inline void lane_subset_build(const LaneTabs& tb, const LaneNode& ln, uint64_t colact, const uint16_t* slot_of) {
     const int S = tb.stride;
-    if (!ln.integral || !ln.valid) { for (int r = 0; r < 256; ++r) tb.subset[r * S] = 0u; return; }
+    for (int u = 0; u < SUBSET_UNITS; ++u) reinterpret_cast<uint4*>(tb.subset)[u * S] = make_uint4(0u, 0u, 0u, 0u);
+    if (!ln.integral || !ln.valid) return;
     const int* mi = reinterpret_cast<const int*>(tb.mat);
     uint32_t sym[8];       // GPUs with an active link to t AND from t
     for (int t = 0; t < 8; ++t) {
@@ -356,11 +364,11 @@ __device__ inline void lane_subset_build(const LaneTabs& tb, const LaneNode& ln,
         for (int i = 0; i < 8; ++i) if ((uint32_t)(colact >> (8 * i)) >> t & 1u) out_t |= 1u << i;
         sym[t] = (uint32_t)(colact >> (8 * t)) & 0xffu & out_t;
     }
-    tb.subset[slot_of[0] * S] = 1u;                                   // empty set: total 0, valid
+    subset_entry(tb.subset, S, slot_of[0]) = 1u;                       // empty set: total 0, valid
     for (uint32_t mask = 1; mask < 256; ++mask) {
         const int t = 31 - __clz((int)mask);
         const uint32_t rest = mask & ~(1u << t);
-        const uint32_t pr = tb.subset[slot_of[rest] * S];
+        const uint32_t pr = subset_entry(tb.subset, S, slot_of[rest]);
         uint32_t ok = (pr & 1u) && !(rest & ~sym[t]) && (ln.avail >> t & 1u);
         uint32_t tot = pr >> 1;
         if (ok)
@@ -369,16 +377,19 @@ __device__ inline void lane_subset_build(const LaneTabs& tb, const LaneNode& ln,
                 // unit 2i + (t >> 2), component t & 3: 64 * bw(t -> i) (active, so not FAST_NEG)
                 tot += (uint32_t)(mi[((2 * i + (t >> 2)) * S) * 4 + (t & 3)] >> FAST_SHIFT);
             }
-        tb.subset[slot_of[mask] * S] = ok ? ((tot << 1) | 1u) : 0u;
+        subset_entry(tb.subset, S, slot_of[mask]) = ok ? ((tot << 1) | 1u) : 0u;
     }
     for (uint32_t mask = 0; mask < 256; ++mask) {
-        const uint32_t v = tb.subset[slot_of[mask] * S];
-        tb.subset[slot_of[mask] * S] = ((v & 1u) && (v >> 1) > 0u) ? (((v >> 1) << 8) | (255u - mask)) : 0u;
+        uint32_t& e = subset_entry(tb.subset, S, slot_of[mask]);
+        const uint32_t v = e;
+        e = ((v & 1u) && (v >> 1) > 0u) ? (((v >> 1) << 8) | (255u - mask)) : 0u;
     }
 }
+// C(A, k) for 0 <= k <= A <= 8: Pascal's triangle, row A in one 64-bit word, 7 bits per entry (the largest is 70).
 __device__ __forceinline__ uint32_t binom_small(int A, int k) {
-    uint32_t c = 1; for (int i = 1; i <= k; ++i) c = c * (uint32_t)(A - k + i) / (uint32_t)i;
-    return c;
+    uint64_t row = 1, prev = 1;                               // row 0
+    for (int a = 1; a <= A; ++a) { row = prev + (prev << 7); prev = row; }      // row a = row a-1 + (row a-1 shifted by one entry); no carries: entries < 128
+    return (uint32_t)(row >> (7 * k)) & 0x7fu;
 }
 
 // ---- the evaluation ---------------------------------------------------------------------------------
@@ -462,8 +473,12 @@ __device__ __forceinline__ void lane_evaluate(const LaneNode& ln, const LaneTabs
             uint32_t bm = 0; double best = 0.0;
             if (TABLES && ln.integral) {
                 uint32_t key = 0;
-#pragma unroll 4
-                for (int q = subset_off(k); q < subset_off(k + 1); ++q) key = max(key, tb.subset[q * tb.stride]);
+                const uint4* units = reinterpret_cast<const uint4*>(tb.subset);
+#pragma unroll 2
+                for (int u = subset_off(k) >> 2; u < (subset_off(k + 1) >> 2); ++u) {
+                    const uint4 v = units[u * tb.stride];
+                    key = max(max(key, max(v.x, v.y)), max(v.z, v.w));
+                }
                 if (key) { best = (double)(key >> 8); bm = 255u - (key & 255u); }
             } else {
                 NodeCtx nc; nc.avail = ln.avail; nc.colact = ld_u64(rec->act_in);
@@ -534,7 +549,7 @@ __device__ __noinline__ void lane_memo_build(const LaneNode& ln, const LaneTabs&
 // Everything a lane keeps about its node beyond LaneNode: tables in the shared-memory columns.
 template <bool GENERAL, bool TABLES>
 __device__ inline void lane_tables_build(const LaneNode& ln, const NodeCtx& c, const LaneTabs& tb, const DevNode* rec, double norm,
-                                         uint32_t mode, const uint8_t* slot_of) {
+                                         uint32_t mode, const uint16_t* slot_of) {
     const int S = tb.stride;
     if (ln.tier == TIER_UNIFORM) {                       // uniform_topo_build, into the lane's column
         const double u = node_uniform_bw(rec, node_uniform_code(rec));

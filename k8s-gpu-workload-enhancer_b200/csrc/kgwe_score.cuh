@@ -40,8 +40,8 @@ __host__ __device__ inline K1Layout k1_layout(uint32_t ppc, uint32_t mat_units, 
     L.topo = o; o += 7u * K1_TILE * 4u;
     L.grp = o; o += 6u * K1_TILE * 4u;
     L.mig = o; o += 3u * K1_TILE * 4u;
-    L.subset = o; o += tables ? 256u * K1_TILE * 4u : 0u;
-    L.slot = o; o += tables ? 256u : 0u;
+    L.subset = o; o += tables ? (uint32_t)SUBSET_UNITS * K1_TILE * 16u : 0u;
+    L.slot = o; o += tables ? 512u : 0u;
     L.total = o;
     return L;
 }
@@ -57,7 +57,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     const K1Layout L = k1_layout(pods_per_chunk, GENERAL ? mat_units : 0u, TABLES, mode == K1_MODE_MEMO);
     PodLite* spod = reinterpret_cast<PodLite*>(smem + L.pods);
     uint32_t* keys = reinterpret_cast<uint32_t*>(smem + L.keys);
-    uint8_t* slot_of = smem + L.slot;                                          // TABLES only
+    uint16_t* slot_of = reinterpret_cast<uint16_t*>(smem + L.slot);             // TABLES only: entry of each mask
 
     const int tid = threadIdx.x, lane = tid & 31;
     const uint32_t tile_first = blockIdx.x * K1_TILE;
@@ -83,7 +83,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         for (int m = tid; m < 256; m += K1_THREADS) {
             int rank = 0;
             for (int q = 0; q < m; ++q) rank += __popc(q) == __popc(m);
-            slot_of[m] = (uint8_t)(subset_off(__popc(m)) + rank);
+            slot_of[m] = (uint16_t)(subset_off(__popc(m)) + rank);
         }
     want_groups = __syncthreads_or(want_groups);
 
@@ -99,7 +99,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     tb.mig = reinterpret_cast<uint32_t*>(smem + L.mig) + tid;
     tb.memo = reinterpret_cast<int2*>(smem + L.memo) + tid;
     tb.mat = reinterpret_cast<int4*>(smem + L.mat) + tid;
-    tb.subset = reinterpret_cast<uint32_t*>(smem + L.subset) + tid;
+    tb.subset = reinterpret_cast<uint32_t*>(smem + L.subset) + 4 * tid;
     {
         NodeCtx c;
         node_ctx_core(c, rec, in_range);

@@ -66,11 +66,11 @@ extern "C" int lane_emu_score_batch(const kgwe_config* cfg, const kgwe_node_imag
     }
     const Params P{cfg->topology_weight, cfg->resource_weight, cfg->balance_weight, cfg->hint_bonus, cfg->nvlink_norm_gbps, cfg->node_base};
     const uint32_t row_bytes = (n_nodes + 7) / 8;
-    uint8_t slot_of[256];
+    uint16_t slot_of[256];
     for (int m = 0; m < 256; ++m) {
         int rank = 0;
         for (int q = 0; q < m; ++q) rank += __popc(q) == __popc(m);
-        slot_of[m] = (uint8_t)(subset_off(__popc(m)) + rank);
+        slot_of[m] = (uint16_t)(subset_off(__popc(m)) + rank);
     }
     std::vector<PodLite> pl(n_pods);
     for (uint32_t p = 0; p < n_pods; ++p) pl[p] = pod_lite(pods[p]);
@@ -82,7 +82,7 @@ extern "C" int lane_emu_score_batch(const kgwe_config* cfg, const kgwe_node_imag
         node_ctx_group_tables(c, rec);
         LaneNode ln;
         lane_node_init(ln, c, rec, general == 0 ? 0u : (uint32_t)general);
-        int32_t topo[7] = {0}; uint32_t grp[6] = {0}, mig[3] = {0}; int2 memo[7]; int4 mat[32]; std::vector<uint32_t> subset(256, 0u);
+        int32_t topo[7] = {0}; uint32_t grp[6] = {0}, mig[3] = {0}; int2 memo[7]; int4 mat[32]; std::vector<uint32_t> subset(SUBSET_ENTRIES, 0u);
         memset(memo, 0, sizeof memo); memset(mat, 0, sizeof mat);
         LaneTabs tb{topo, grp, mig, memo, mat, subset.data(), 1};
         if (tables) lane_tables_build<true, true>(ln, c, tb, rec, P.norm, mode, slot_of);
