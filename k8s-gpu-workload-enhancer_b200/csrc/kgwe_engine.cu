@@ -25,6 +25,7 @@
 
 #include "kgwe_kernels.cuh"
 #include "kgwe_mig.cuh"
+#include "kgwe_queue.cuh"
 #include "kgwe_pack.hpp"
 
 using namespace kgwe;
@@ -80,6 +81,8 @@ struct kgwe_engine {
     int sm_count = 148;
     int sched_blocks_per_sm = 1;
     int sched_tile_blocks_per_sm = 0;
+    int qc_max_ctas = 0;              // largest cluster the cluster form of the queue kernel can be launched with here (0: none)
+    long long max_total = 0;          // bound on |TotalScore| from the weights
     int k1_blocks_per_sm[4] = {5, 3, 2, 1};   // co-resident CTAs of K1's lean / GENERAL (int32 columns) / GENERAL (float64 columns) / TABLES variants
 
     DevNode* d_img[2] = {nullptr, nullptr};   // the two cluster images in HBM
@@ -442,6 +445,25 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
         ok = ok && cudaFuncSetAttribute(schedule_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sched_tile_smem_bytes()) == cudaSuccess;
         bps = 0;
         if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, schedule_tile_kernel, SCORE_THREADS, sched_tile_smem_bytes()) == cudaSuccess && bps > 0) e->sched_tile_blocks_per_sm = bps;
+    }
+    if (ok) {   // the cluster form of the queue kernel (kgwe_queue.cuh): the largest cluster this device schedules, 16 CTAs if it can
+        auto ab = [](long long v) { return v < 0 ? -v : v; };
+        e->max_total = (12550 * ab(cfg->topology_weight) + 100 * ab(cfg->resource_weight) + 100 * ab(cfg->balance_weight)) / 100 + ab(cfg->hint_bonus);
+        const int smem = (int)qc_layout(QC_MAX_THREADS).total;
+        const char* form = getenv("KGWE_QUEUE_FORM");      // "tile" keeps the grid-wide kernels (A/B runs, tests)
+        if (!(form && !strcmp(form, "tile")) && cudaFuncSetAttribute(schedule_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) == cudaSuccess) {
+            cudaFuncSetAttribute(schedule_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            for (int c = QC_MAX_CTAS; c >= 1 && !e->qc_max_ctas; c >>= 1) {
+                cudaLaunchConfig_t lc = {};
+                lc.gridDim = dim3(c); lc.blockDim = dim3(QC_MAX_THREADS); lc.dynamicSmemBytes = smem;
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = c; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+                lc.attrs = at; lc.numAttrs = 1;
+                int n = 0;
+                if (cudaOccupancyMaxActiveClusters(&n, schedule_cluster_kernel, &lc) == cudaSuccess && n >= 1) e->qc_max_ctas = c;
+            }
+        }
+        cudaGetLastError();
     }
     if (!ok) { cudaGetLastError(); kgwe_engine_destroy(e); return KGWE_ERR_CUDA; }
     *out = e;
@@ -819,7 +841,12 @@ static bool queue_tile_form(const kgwe_engine* e) {
     return n_tiles <= (uint32_t)(e->sm_count * e->sched_tile_blocks_per_sm);
 }
 
-// gang_of (host, np entries, nullable): all-or-nothing gangs decided on the device (tile form only).
+// True when the image fits the cluster form (one lane per node inside one thread-block cluster, kgwe_queue.cuh).
+static bool queue_cluster_form(const kgwe_engine* e) {
+    return e->qc_max_ctas > 0 && e->n_nodes <= (uint32_t)e->qc_max_ctas * (uint32_t)QC_MAX_THREADS && e->max_total < (1ll << (32 - QC_NODE_BITS));
+}
+
+// gang_of (host, np entries, nullable): all-or-nothing gangs decided on the device (cluster and tile forms only).
 static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t np, const uint8_t* hint_rows, double* gpu_ms, const uint32_t* gang_of = nullptr) {
     cudaStream_t s = e->stream;
     const uint32_t N = e->n_nodes, row = hint_row_bytes(e);
@@ -862,7 +889,18 @@ static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t 
     void* targs[] = {&d_nodes, &n_nodes, &d_pods, &npods, &d_hint, &rowb, &best, &arrive, &d_out, &prm, &ctr, &d_gang};
     CU(e, cudaEventRecord(e->ev0, s));
     const uint32_t n_tiles = (N + TILE_NODES - 1) / TILE_NODES;
-    if (queue_tile_form(e)) {
+    if (queue_cluster_form(e)) {
+        // the whole image inside one cluster: about 128 nodes per CTA until the cluster is full, then more lanes per CTA
+        uint32_t ctas = 1;
+        while (ctas < (uint32_t)e->qc_max_ctas && ctas * 128u < N) ctas <<= 1;
+        const uint32_t threads = std::max(32u, ((N + ctas - 1) / ctas + 31u) & ~31u);
+        cudaLaunchConfig_t lc = {};
+        lc.gridDim = dim3(ctas); lc.blockDim = dim3(threads); lc.dynamicSmemBytes = qc_layout(threads).total; lc.stream = s;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = ctas; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        lc.attrs = at; lc.numAttrs = 1;
+        CU(e, cudaLaunchKernelEx(&lc, schedule_cluster_kernel, d_nodes, n_nodes, d_pods, npods, d_hint, rowb, d_out, prm, ctr, d_gang));
+    } else if (queue_tile_form(e)) {
         // every node gets its own lane group: tile form (shared-memory resident tables)
         CU(e, cudaLaunchCooperativeKernel((const void*)schedule_tile_kernel, dim3(n_tiles), dim3(SCORE_THREADS), targs, sched_tile_smem_bytes(), s));
     } else
@@ -978,7 +1016,7 @@ int kgwe_schedule_gangs(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pod
         return KGWE_OK;
     }
     const uint32_t row = hint_row_bytes(e);
-    if (queue_tile_form(e) && !getenv("KGWE_GANG_WINDOW")) {      // (the variable also forces the window path below, for tests)
+    if ((queue_cluster_form(e) || queue_tile_form(e)) && !getenv("KGWE_GANG_WINDOW")) {      // (the variable also forces the window path below, for tests)
         // All-or-nothing on the device: the queue kernel itself takes a rejected gang's commits back (schedule_tile_kernel),
         // so the whole queue is one launch per segment; the host only turns the decisions of rejected gangs into
         // "no node" (+ KGWE_F_GANG_ROLLBACK for members that had found one) and mirrors the surviving commits.

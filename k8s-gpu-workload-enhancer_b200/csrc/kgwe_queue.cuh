@@ -1,0 +1,294 @@
+// kgwe_queue.cuh — K3c, the stateful queue (Schedule for a queue of workloads with a commit after each one,
+// reference src/scheduler/scheduler.go:114-179, 625-653, 695-707) inside ONE thread-block cluster.
+//
+// The queue is a dependent chain - workload p + 1 must see workload p's commit - so what bounds it is the latency
+// of one grid-wide arg-max per workload, not throughput.  schedule_tile_kernel (kgwe_kernels.cuh) spreads the nodes
+// over all SMs and pays two or three L2 round trips per workload for that arg-max.  Here the whole image sits in
+// one cluster of up to 16 CTAs (ONE LANE = ONE NODE, state in registers and [entry][lane] shared-memory columns as
+// in K1, kgwe_lane.cuh), and the arg-max goes through distributed shared memory:
+//   every lane evaluates the workload on its node; REDUX.MAX per warp; one bar.sync; warp 0 folds the warp keys
+//   and stores the CTA's key into slot [rank] of EVERY CTA of the cluster (st.shared::cluster); one cluster
+//   barrier (arrive.release / wait.acquire); every thread reads the <= 16 keys of its own CTA and knows the winner.
+//   The lane that owns the winning node writes the decision, commits in the image and refreshes its own state.
+// Keys are TotalScore << 14 | (16383 - node): largest score, lowest node index on ties (the canonical order).
+// The greedy winners per group size are memoised per lane and filled lazily: a commit only invalidates the owner's
+// memo, and the next evaluation that needs an entry runs the full search of findBestNVLinkGroup (:376-435) for
+// that size alone.
+// Nodes of every link tier are served: the memo fill of a non-uniform node runs the float64 chains on the record
+// itself (the lane variant without matrix columns), which a commit-bound queue can afford.
+// Form limits (the engine falls back to schedule_tile_kernel otherwise): n_nodes <= cluster size x QC_MAX_THREADS
+// (10,240 with 16 CTAs), TotalScore < 2^18.
+#pragma once
+#include "kgwe_lane.cuh"
+
+namespace kgwe {
+
+constexpr int QC_MAX_THREADS = 640;        // 20 warps; 296 bytes of shared-memory columns per lane
+constexpr int QC_MAX_CTAS = 16;            // non-portable cluster size, opt-in at launch
+constexpr int QC_WINDOW = 256;             // pod descriptors staged per refill
+constexpr uint32_t QC_NODE_BITS = 14;
+constexpr uint32_t QC_MAX_NODES = 1u << QC_NODE_BITS;
+
+// Per-lane columns of 8-byte entries that a commit never changes (entry e of a lane at st[e * stride]).
+constexpr int QS_UTIL = 0;       // [8] Utilization.GPUPercent per GPU (double)
+constexpr int QS_FREE = 8;       // [8] Memory.FreeBytes per GPU
+constexpr int QS_ROWS = 16;      // adjacency rows of the greedy graph, reversed bit order (LaneNode::rlo/rhi before the restriction to available GPUs)
+constexpr int QS_ARCH = 17;      // arch[0..7]
+constexpr int QS_NUMA = 18;      // numa[0..7]
+constexpr int QS_PCIE = 19;      // pcie_switch[0..7]
+constexpr int QS_BAL = 20;       // BalanceScore for 0..7 allocations on the node, one byte each (0 from n_gpus allocations on)
+constexpr int QS_MISC = 21;      // healthy_mask | n_gpus (<= 8) << 8 | tier << 16 | valid << 24 | integral << 25
+constexpr int QS_ENTRIES = 22;
+
+struct QcLayout { uint32_t pods, minbw, gang, stat, topo, grp, mig, memo, wkeys, ckeys, total; };
+__host__ __device__ inline QcLayout qc_layout(uint32_t threads) {
+    QcLayout L; uint32_t o = 0;
+    L.pods = o; o += QC_WINDOW * 16u;
+    L.minbw = o; o += QC_WINDOW * 8u;
+    L.gang = o; o += (QC_WINDOW + 1u) * 4u; o = (o + 15u) & ~15u;      // + the first gang number of the next window
+    L.stat = o; o += (uint32_t)QS_ENTRIES * threads * 8u;
+    L.memo = o; o += 7u * threads * 8u;
+    L.topo = o; o += 7u * threads * 4u;
+    L.grp = o; o += 6u * threads * 4u;
+    L.mig = o; o += 3u * threads * 4u;
+    L.wkeys = o; o += 32u * 4u;
+    L.ckeys = o; o += 2u * QC_MAX_CTAS * 4u;
+    L.total = o;
+    return L;
+}
+
+__device__ __forceinline__ uint32_t qc_cta_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ uint32_t qc_map_to_cta(uint32_t smem_addr, uint32_t rank) {
+    uint32_t r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank)); return r;
+}
+__device__ __forceinline__ void qc_store_remote(uint32_t cluster_addr, uint32_t v) {
+    asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(cluster_addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void qc_cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void qc_cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+
+// bit i of the low nibble of x -> byte i all ones
+__device__ __forceinline__ uint32_t qc_expand4(uint32_t x) { return (((x & 0xfu) * 0x00204081u) & 0x01010101u) * 0xffu; }
+
+// The static columns of this lane's node (once, at set-up).
+__device__ inline void qc_static_build(uint64_t* st, int S, const DevNode* rec, const NodeCtx& c, uint32_t tier) {
+    uint32_t ng = c.valid ? rec->n_gpus : 0; ng = ng > 8 ? 8 : ng;
+    uint64_t rows = 0, bal = 0;
+    for (int g = 0; g < 8; ++g) {
+        st[(QS_UTIL + g) * S] = (uint64_t)__double_as_longlong(c.valid ? rec->util[g] : 0.0);
+        st[(QS_FREE + g) * S] = c.valid ? rec->free_bytes[g] : 0ull;
+        rows |= (uint64_t)rev8((uint32_t)(c.colact >> (8 * g)) & 0xffu) << (8 * (7 - g));
+        if (ng > 0) {       // calculateBalanceScore (scheduler.go:556-578) with g allocations on the node
+            const double usage = __ddiv_rn((double)g, (double)ng);
+            const int s = __double2int_rz(__dmul_rn(100.0, __dsub_rn(1.0, usage)));
+            bal |= (uint64_t)(s > 0 ? s : 0) << (8 * g);
+        }
+    }
+    st[QS_ROWS * S] = rows; st[QS_ARCH * S] = c.arch8; st[QS_BAL * S] = bal;
+    st[QS_NUMA * S] = c.valid ? ld_u64(rec->numa) : 0ull; st[QS_PCIE * S] = c.valid ? ld_u64(rec->pcie_switch) : 0ull;
+    st[QS_MISC * S] = (uint64_t)((c.valid ? (uint32_t)rec->healthy_mask : 0u) | (ng << 8) | (tier << 16) | ((c.valid ? 1u : 0u) << 24) | ((c.integral ? 1u : 0u) << 25));
+}
+
+// The lane's pod-independent state (node_ctx_core + lane_node_init) from the static columns and the node's current
+// allocations: what the owner of a winning node runs after its commit, on the critical path of the queue, so it
+// reads shared memory only and divides nothing.  The utilisation bonus compares the ordered sum with 30 * A and
+// 60 * A instead of the mean with 30 and 60: for A <= 8 both thresholds times A are exact doubles whose spacing
+// exceeds A half-ulps of the threshold, so no sum below the product has a quotient that rounds up to the threshold.
+__device__ __forceinline__ void qc_state(LaneNode& ln, const uint64_t* st, int S, uint32_t allocated, uint32_t n_allocs) {
+    const uint32_t misc = (uint32_t)st[QS_MISC * S];
+    const uint32_t ng = (misc >> 8) & 0xffu;
+    ln.valid = (misc >> 24) & 1u; ln.integral = (misc >> 25) & 1u; ln.tier = (misc >> 16) & 0xffu;
+    const uint32_t avail = (misc & 0xffu) & ~allocated & ((1u << ng) - 1u);       // misc = 0 for an absent record
+    ln.avail = avail; ln.A = __popc(avail);
+    uint64_t sum = 0; double usum = 0.0;
+#pragma unroll
+    for (int g = 0; g < 8; ++g)
+        if (avail >> g & 1) { sum += st[(QS_FREE + g) * S]; usum = __dadd_rn(usum, __longlong_as_double((long long)st[(QS_UTIL + g) * S])); }
+    ln.sum_free = sum;
+    const double a = (double)ln.A;
+    ln.util_bonus = ln.A > 0 ? (usum < __dmul_rn(30.0, a) ? 25 : (usum < __dmul_rn(60.0, a) ? 10 : 0)) : 0;
+    ln.balance = n_allocs < 8u ? (int)((st[QS_BAL * S] >> (8 * n_allocs)) & 0xffu) : 0;
+    const uint32_t availR = rev8(avail);
+    const uint64_t rows = st[QS_ROWS * S], arch = st[QS_ARCH * S];
+    ln.rlo = (uint32_t)rows & (availR * 0x01010101u) & qc_expand4(availR);
+    ln.rhi = (uint32_t)(rows >> 32) & (availR * 0x01010101u) & qc_expand4(availR >> 4);
+    ln.arch_lo = (uint32_t)arch & qc_expand4(avail);
+    ln.arch_hi = (uint32_t)(arch >> 32) & qc_expand4(avail >> 4);
+    ln.avail_prefix = 0; ln.avail_order = 0;
+    uint32_t m = avail, acc = 0; int i = 0;
+    while (m) {
+        const int b = __ffs((int)m) - 1;
+        acc |= 1u << b; ln.avail_order |= (uint32_t)b << (3 * i); ln.avail_prefix |= (uint64_t)acc << (8 * i);
+        m &= m - 1; ++i;
+    }
+}
+
+// Lazily filled per-lane tables (by value: the lane state stays in registers across the call).
+__device__ __noinline__ uint32_t qc_memo_fill(uint32_t avail, uint32_t rlo, uint32_t rhi, uint32_t tier, int2* memo, const int32_t* topo_tab, int S,
+                                             const DevNode* rec, int k, double norm) {
+    LaneNode ln; ln.avail = avail; ln.A = __popc(avail); ln.rlo = rlo; ln.rhi = rhi; ln.tier = tier; ln.valid = true;
+    LaneTabs tb; tb.topo = const_cast<int32_t*>(topo_tab); tb.stride = S; tb.mat = nullptr;
+    int topo = -1; uint32_t sel = 0, order = 0, sc = 0;
+    lane_group_search<false>(ln, tb, rec, k, norm, K1_MODE_FULL, topo, sel, order, sc);
+    memo[(k - 2) * S] = make_int2(topo, (int)(order | (sel << 24)));
+    return sc;
+}
+__device__ __noinline__ void qc_groups_fill(uint32_t avail, const uint64_t* st, uint32_t* grp, int S) {
+    uint64_t np = 0, pp = 0; uint32_t no = 0, po = 0;
+    if (((uint32_t)st[QS_MISC * S] >> 24) & 1u) {
+        group_tables(st[QS_NUMA * S], true, avail, np, no);
+        group_tables(st[QS_PCIE * S], false, avail, pp, po);
+    }
+    grp[0] = (uint32_t)np; grp[S] = (uint32_t)(np >> 32); grp[2 * S] = no;
+    grp[3 * S] = (uint32_t)pp; grp[4 * S] = (uint32_t)(pp >> 32); grp[5 * S] = po;
+}
+
+__global__ void __launch_bounds__(QC_MAX_THREADS, 1)
+schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
+                        const uint8_t* __restrict__ hint, uint32_t hint_row_bytes, kgwe_placement* __restrict__ out,
+                        Params P, unsigned long long* __restrict__ counters, const uint32_t* __restrict__ gang_of) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int T = (int)blockDim.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, n_warps = T >> 5;
+    const uint32_t C = gridDim.x, rank = qc_cta_rank();
+    const QcLayout L = qc_layout((uint32_t)T);
+    PodLite* spod = reinterpret_cast<PodLite*>(smem + L.pods);
+    double* sminbw = reinterpret_cast<double*>(smem + L.minbw);
+    uint32_t* sgang = reinterpret_cast<uint32_t*>(smem + L.gang);
+    uint32_t* wkeys = reinterpret_cast<uint32_t*>(smem + L.wkeys);
+    uint32_t* ckeys = reinterpret_cast<uint32_t*>(smem + L.ckeys);
+    uint64_t* st = reinterpret_cast<uint64_t*>(smem + L.stat) + tid;
+
+    const uint32_t node = rank * (uint32_t)T + (uint32_t)tid;
+    const bool in_range = node < n_nodes;
+    DevNode* rec = nodes + (in_range ? node : 0);
+    LaneNode ln;
+    LaneTabs tb;
+    tb.stride = T;
+    tb.topo = reinterpret_cast<int32_t*>(smem + L.topo) + tid;
+    tb.grp = reinterpret_cast<uint32_t*>(smem + L.grp) + tid;
+    tb.mig = reinterpret_cast<uint32_t*>(smem + L.mig) + tid;
+    tb.memo = reinterpret_cast<int2*>(smem + L.memo) + tid;
+    tb.mat = nullptr; tb.subset = nullptr;
+    if (tid < 2 * QC_MAX_CTAS) ckeys[tid] = 0u;
+    uint32_t allocated = 0, n_allocs = 0;       // this node's ledger projection (scheduler.go:587-593, 562-566), mirrored in the image on every change
+    {
+        NodeCtx c;
+        node_ctx_core(c, rec, in_range);
+        lane_node_init(ln, c, rec, 0u);
+        lane_tables_build<false, false>(ln, c, tb, rec, P.norm, K1_MODE_FULL, nullptr);      // NVLink score per k, MIG counts
+        qc_static_build(st, T, rec, c, ln.tier);
+        if (c.valid) { allocated = rec->allocated_mask; n_allocs = rec->n_allocs; }
+    }
+    qc_state(ln, st, T, allocated, n_allocs);
+    uint32_t memo_ok = 0;        // bit k - 2: the memoised winner for group size k is current
+    bool groups_ok = false;      // the NUMA / PCIe group tables are current
+    __syncwarp();
+    qc_cluster_arrive(); qc_cluster_wait();      // every CTA's key slots are initialised before anybody stores into them
+
+    const uint32_t key_low = (QC_MAX_NODES - 1u) - node;
+    const uint32_t my_slot = smem_u32(ckeys) + rank * 4u;
+    uint32_t cnt_scored = 0, cnt_resolved = 0, cnt_evals = 0;
+    // E5 gangs: see schedule_tile_kernel - every thread sees every decision; a lane remembers what its node committed
+    // for the current gang and takes it back when the gang's last member has been decided and one of them found no node.
+    bool gang_failed = false; uint32_t gang_mask = 0, gang_commits = 0;
+    uint32_t hint_byte = (hint && in_range) ? __ldg(hint + (node >> 3)) : 0u;
+
+    for (uint32_t p = 0; p < n_pods; ++p) {
+        const uint32_t wi = p & (QC_WINDOW - 1);
+        if (wi == 0) {      // stage the next window of pod descriptors
+            __syncthreads();
+            const uint32_t cnt = min((uint32_t)QC_WINDOW, n_pods - p);
+            for (uint32_t i = tid; i <= cnt; i += T) {
+                if (i < cnt) {
+                    const kgwe_pod_req pod = load_pod(pods, p + i);
+                    spod[i] = pod_lite(pod); sminbw[i] = pod.min_bandwidth_gbps;
+                }
+                sgang[i] = (gang_of && p + i < n_pods) ? __ldg(gang_of + p + i) : 0xFFFFFFFFu;
+            }
+            __syncthreads();
+        }
+        const PodLite pd = spod[wi];
+        const bool hinted = (hint_byte >> (node & 7)) & 1u;
+        if (hint && in_range && p + 1 < n_pods) hint_byte = __ldg(hint + (size_t)(p + 1) * hint_row_bytes + (node >> 3));      // next pod's bit, off the critical path
+        double min_bw = 0.0;
+        if (pd.pk & PL_MINBW) min_bw = sminbw[wi];
+        const int k = (int)(pd.pk & 0xffu);
+        if ((pd.pk & (PL_NVLINK | PL_EXH)) == PL_NVLINK) {      // warp-uniform
+            if (ln.valid && ln.A >= k && !(memo_ok >> (k - 2) & 1u)) {
+                cnt_scored += qc_memo_fill(ln.avail, ln.rlo, ln.rhi, ln.tier, tb.memo, tb.topo, T, rec, k, P.norm);
+                memo_ok |= 1u << (k - 2);
+            }
+            __syncwarp();
+        } else if (pd.pk & (PL_NUMA | PL_PCIE)) {
+            if (ln.valid && ln.A >= k && !groups_ok) { qc_groups_fill(ln.avail, st, tb.grp, T); groups_ok = true; }
+            __syncwarp();
+        }
+        LaneResult r;
+        lane_evaluate<false, false>(ln, tb, rec, pd, min_bw, hinted, P, K1_MODE_MEMO, r);
+        if (in_range) { cnt_evals += 1; cnt_resolved += r.candidates; cnt_scored += r.scored; }
+        const uint32_t mykey = r.kept_total ? ((r.kept_total << QC_NODE_BITS) | key_low) : 0u;
+        const uint32_t wkey = __reduce_max_sync(0xffffffffu, mykey);
+        if (lane == 0) wkeys[warp] = wkey;
+        __syncthreads();
+        const uint32_t par = (p & 1u) * QC_MAX_CTAS;
+        if (warp == 0) {
+            const uint32_t ckey = __reduce_max_sync(0xffffffffu, lane < n_warps ? wkeys[lane] : 0u);
+            if ((uint32_t)lane < C) qc_store_remote(qc_map_to_cta(my_slot + par * 4u, (uint32_t)lane), ckey);
+            __syncwarp();
+        }
+        qc_cluster_arrive(); qc_cluster_wait();
+        uint32_t win;
+        {
+            const uint4* ck = reinterpret_cast<const uint4*>(ckeys + par);
+            const uint4 a = ck[0], b = ck[1], c = ck[2], d = ck[3];
+            win = max(max(max(a.x, a.y), max(a.z, a.w)), max(max(b.x, b.y), max(b.z, b.w)));
+            win = max(win, max(max(max(c.x, c.y), max(c.z, c.w)), max(max(d.x, d.y), max(d.z, d.w))));
+        }
+        bool changed = false;
+        if (win == 0u) {
+            if (rank == 0 && tid == 0) {
+                kgwe_placement pl;
+                pl.node_idx = KGWE_NO_NODE; pl.total = 0; pl.topology = pl.resource = pl.balance = 0; pl.gpu_mask = 0; pl.flags = 0;
+                pl.order = 0; pl.reserved = 0; pl.est_bandwidth_gbps = 0.0;
+                out[p] = pl;
+            }
+            gang_failed = true;
+        } else if (win == mykey) {
+            // this lane owns the winner: tryScheduleOnNode + recordAllocation (scheduler.go:625-653, 695-707)
+            const uint32_t mask = (r.w2 >> 16) & 0xffu;
+            kgwe_placement pl;
+            pl.node_idx = P.node_base + node; pl.total = (int32_t)r.w0; pl.topology = (int16_t)(r.w1 & 0xffffu); pl.resource = (int16_t)(r.w1 >> 16);
+            pl.balance = (int16_t)(r.w2 & 0xffffu); pl.gpu_mask = (uint8_t)mask; pl.flags = (uint8_t)(r.w2 >> 24); pl.order = r.w3;
+            pl.reserved = 0; pl.est_bandwidth_gbps = 0.0;      // EstimatedBandwidth is filled in after the queue (est_bandwidth_kernel)
+            out[p] = pl;
+            allocated |= mask; n_allocs += 1;
+            gang_mask |= mask; gang_commits += 1;
+            changed = true;
+        }
+        if (gang_of && sgang[wi + 1] != sgang[wi]) {      // the gang's last member has been decided
+            if (gang_failed && gang_commits) {             // take this node's commits for the gang back
+                allocated &= ~gang_mask; n_allocs -= gang_commits;
+                changed = true;
+            }
+            gang_failed = false; gang_mask = 0; gang_commits = 0;
+        }
+        if (changed) {
+            qc_state(ln, st, T, allocated, n_allocs);
+            memo_ok = 0; groups_ok = false;
+            rec->allocated_mask = (uint8_t)allocated;      // the image in HBM follows
+            rec->n_allocs = n_allocs;
+        }
+        __syncwarp();
+    }
+    cnt_scored = __reduce_add_sync(0xffffffffu, cnt_scored);
+    cnt_resolved = __reduce_add_sync(0xffffffffu, cnt_resolved);
+    cnt_evals = __reduce_add_sync(0xffffffffu, cnt_evals);
+    if (lane == 0 && counters) {
+        if (cnt_evals) atomicAdd(&counters[0], (unsigned long long)cnt_evals);
+        if (cnt_scored) atomicAdd(&counters[1], (unsigned long long)cnt_scored);
+        if (cnt_resolved) atomicAdd(&counters[2], (unsigned long long)cnt_resolved);
+    }
+    qc_cluster_arrive(); qc_cluster_wait();      // nobody leaves while a peer may still store into its shared memory
+}
+
+}  // namespace kgwe
