@@ -62,7 +62,7 @@ struct PinBuf {
     void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
 };
 
-constexpr int kCounters = 4;      // device counters: [0] evaluations (K3), [1] candidates scored, [2] candidates by the reference's counting rule
+constexpr int kCounters = 4;      // device counters: [0] evaluations (K3), [1] candidates scored, [2] candidates by the reference's counting rule, [3] watchdog trips of the cluster queue kernel
 constexpr size_t kScoreScratchBytes = 1ull << 30;   // internal score-matrix chunk (top-k > 1 without out_scores, host copies)
 // Testing knob: KGWE_SCORE_SCRATCH_BYTES shrinks the chunk so the multi-pass path of kgwe_score_batch can be exercised on small inputs.
 size_t score_scratch_bytes() {
@@ -83,6 +83,7 @@ struct kgwe_engine {
     int sched_tile_blocks_per_sm = 0;
     int qc_max_ctas = 0;              // largest cluster the cluster form of the queue kernel can be launched with here (0: none)
     long long max_total = 0;          // bound on |TotalScore| from the weights
+    unsigned long long watchdog_seen = 0;     // h_counters[3] at the end of the previous queue call
     int k1_blocks_per_sm[4] = {5, 3, 2, 1};   // co-resident CTAs of K1's lean / GENERAL (int32 columns) / GENERAL (float64 columns) / TABLES variants
 
     DevNode* d_img[2] = {nullptr, nullptr};   // the two cluster images in HBM
@@ -919,6 +920,10 @@ static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t 
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, e->ev0, e->ev1) == cudaSuccess) *gpu_ms += ms;
     fold_counters(e);
+    if (e->h_counters[3] != e->watchdog_seen) {
+        e->watchdog_seen = e->h_counters[3];
+        return fail(e, KGWE_ERR_CUDA, "queue kernel: the exchange between the CTAs of the cluster timed out; decisions of this call are invalid");
+    }
     return KGWE_OK;
 }
 

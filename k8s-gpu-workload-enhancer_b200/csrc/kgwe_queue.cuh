@@ -7,8 +7,9 @@
 // one cluster of up to 16 CTAs (ONE LANE = ONE NODE, state in registers and [entry][lane] shared-memory columns as
 // in K1, kgwe_lane.cuh), and the arg-max goes through distributed shared memory:
 //   every lane evaluates the workload on its node; REDUX.MAX per warp; one bar.sync; warp 0 folds the warp keys
-//   and stores the CTA's key into slot [rank] of EVERY CTA of the cluster (st.shared::cluster); one cluster
-//   barrier (arrive.release / wait.acquire); every thread reads the <= 16 keys of its own CTA and knows the winner.
+//   and stores the CTA's key into slot [rank] of EVERY CTA of the cluster with st.async, which also completes 4
+//   bytes of the receiving CTA's mbarrier; every thread waits for its own CTA's mbarrier phase (<= 16 keys have
+//   landed), reads the keys and knows the winner.  No fence and no cluster-wide barrier inside the loop.
 //   The lane that owns the winning node writes the decision, commits in the image and refreshes its own state.
 // Keys are TotalScore << 14 | (16383 - node): largest score, lowest node index on ties (the canonical order).
 // The greedy winners per group size are memoised per lane and filled lazily: a commit only invalidates the owner's
@@ -19,6 +20,7 @@
 // Form limits (the engine falls back to schedule_tile_kernel otherwise): n_nodes <= cluster size x QC_MAX_THREADS
 // (10,240 with 16 CTAs), TotalScore < 2^18.
 #pragma once
+#include "kgwe_kernels.cuh"
 #include "kgwe_lane.cuh"
 
 namespace kgwe {
@@ -40,7 +42,7 @@ constexpr int QS_BAL = 20;       // BalanceScore for 0..7 allocations on the nod
 constexpr int QS_MISC = 21;      // healthy_mask | n_gpus (<= 8) << 8 | tier << 16 | valid << 24 | integral << 25
 constexpr int QS_ENTRIES = 22;
 
-struct QcLayout { uint32_t pods, minbw, gang, stat, topo, grp, mig, memo, wkeys, ckeys, total; };
+struct QcLayout { uint32_t pods, minbw, gang, stat, topo, grp, mig, memo, wkeys, ckeys, bars, total; };
 __host__ __device__ inline QcLayout qc_layout(uint32_t threads) {
     QcLayout L; uint32_t o = 0;
     L.pods = o; o += QC_WINDOW * 16u;
@@ -53,6 +55,7 @@ __host__ __device__ inline QcLayout qc_layout(uint32_t threads) {
     L.mig = o; o += 3u * threads * 4u;
     L.wkeys = o; o += 32u * 4u;
     L.ckeys = o; o += 2u * QC_MAX_CTAS * 4u;
+    L.bars = o; o += 2u * 8u;
     L.total = o;
     return L;
 }
@@ -61,11 +64,24 @@ __device__ __forceinline__ uint32_t qc_cta_rank() { uint32_t r; asm volatile("mo
 __device__ __forceinline__ uint32_t qc_map_to_cta(uint32_t smem_addr, uint32_t rank) {
     uint32_t r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank)); return r;
 }
-__device__ __forceinline__ void qc_store_remote(uint32_t cluster_addr, uint32_t v) {
-    asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(cluster_addr), "r"(v) : "memory");
+// One 32-bit store into another CTA's shared memory that also signals that CTA's mbarrier (complete_tx of 4 bytes):
+// the data is visible to whoever observes the phase of the mbarrier complete - no fence, no cluster-wide barrier.
+__device__ __forceinline__ void qc_store_signal(uint32_t cluster_addr, uint32_t v, uint32_t cluster_mbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.u32 [%0], %1, [%2];" ::"r"(cluster_addr), "r"(v), "r"(cluster_mbar) : "memory");
 }
 __device__ __forceinline__ void qc_cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
 __device__ __forceinline__ void qc_cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+// Wait for `phase` of a local mbarrier whose transactions come from other CTAs.  Bounded: a protocol fault must not hang the
+// GPU; the caller reports a trip through the watchdog counter.
+__device__ __forceinline__ bool qc_wait_phase(uint32_t mbar, uint32_t phase) {
+    for (uint32_t it = 0; it < (1u << 22); ++it) {
+        uint32_t done;
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(mbar), "r"(phase) : "memory");
+        if (done) return true;
+    }
+    return false;
+}
 
 // bit i of the low nibble of x -> byte i all ones
 __device__ __forceinline__ uint32_t qc_expand4(uint32_t x) { return (((x & 0xfu) * 0x00204081u) & 0x01010101u) * 0xffu; }
@@ -170,6 +186,12 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
     tb.memo = reinterpret_cast<int2*>(smem + L.memo) + tid;
     tb.mat = nullptr; tb.subset = nullptr;
     if (tid < 2 * QC_MAX_CTAS) ckeys[tid] = 0u;
+    const uint32_t bars = smem_u32(smem + L.bars);      // two mbarriers: the keys of even / odd workloads
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bars));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bars + 8u));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     uint32_t allocated = 0, n_allocs = 0;       // this node's ledger projection (scheduler.go:587-593, 562-566), mirrored in the image on every change
     {
         NodeCtx c;
@@ -230,13 +252,14 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
         const uint32_t wkey = __reduce_max_sync(0xffffffffu, mykey);
         if (lane == 0) wkeys[warp] = wkey;
         __syncthreads();
-        const uint32_t par = (p & 1u) * QC_MAX_CTAS;
+        const uint32_t par = (p & 1u) * QC_MAX_CTAS, bar = bars + (p & 1u) * 8u;
         if (warp == 0) {
             const uint32_t ckey = __reduce_max_sync(0xffffffffu, lane < n_warps ? wkeys[lane] : 0u);
-            if ((uint32_t)lane < C) qc_store_remote(qc_map_to_cta(my_slot + par * 4u, (uint32_t)lane), ckey);
+            if (lane == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(C * 4u) : "memory");
+            if ((uint32_t)lane < C) qc_store_signal(qc_map_to_cta(my_slot + par * 4u, (uint32_t)lane), ckey, qc_map_to_cta(bar, (uint32_t)lane));
             __syncwarp();
         }
-        qc_cluster_arrive(); qc_cluster_wait();
+        if (!qc_wait_phase(bar, (p >> 1) & 1u)) { if (counters) atomicAdd(&counters[3], 1ull); break; }      // (every thread of the cluster times out alike)
         uint32_t win;
         {
             const uint4* ck = reinterpret_cast<const uint4*>(ckeys + par);
