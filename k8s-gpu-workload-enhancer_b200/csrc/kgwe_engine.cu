@@ -452,8 +452,13 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
         e->max_total = (12550 * ab(cfg->topology_weight) + 100 * ab(cfg->resource_weight) + 100 * ab(cfg->balance_weight)) / 100 + ab(cfg->hint_bonus);
         const int smem = (int)qc_layout(QC_MAX_THREADS).total;
         const char* form = getenv("KGWE_QUEUE_FORM");      // "tile" keeps the grid-wide kernels (A/B runs, tests)
-        if (!(form && !strcmp(form, "tile")) && cudaFuncSetAttribute(schedule_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) == cudaSuccess) {
-            cudaFuncSetAttribute(schedule_cluster_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        std::vector<uint64_t> pf(256); std::vector<uint32_t> od(256);
+        qc_first_tables(pf.data(), od.data());
+        if (!(form && !strcmp(form, "tile")) && cudaFuncSetAttribute(schedule_cluster_kernel<QC_MAX_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) == cudaSuccess
+            && cudaFuncSetAttribute(schedule_cluster_kernel<QC_SMALL_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qc_layout(QC_SMALL_THREADS).total) == cudaSuccess
+            && cudaMemcpyToSymbol(qc_prefix_lut, pf.data(), 256 * sizeof(uint64_t)) == cudaSuccess && cudaMemcpyToSymbol(qc_order_lut, od.data(), 256 * sizeof(uint32_t)) == cudaSuccess) {
+            cudaFuncSetAttribute(schedule_cluster_kernel<QC_MAX_THREADS>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            cudaFuncSetAttribute(schedule_cluster_kernel<QC_SMALL_THREADS>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
             for (int c = QC_MAX_CTAS; c >= 1 && !e->qc_max_ctas; c >>= 1) {
                 cudaLaunchConfig_t lc = {};
                 lc.gridDim = dim3(c); lc.blockDim = dim3(QC_MAX_THREADS); lc.dynamicSmemBytes = smem;
@@ -461,7 +466,7 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
                 at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = c; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
                 lc.attrs = at; lc.numAttrs = 1;
                 int n = 0;
-                if (cudaOccupancyMaxActiveClusters(&n, schedule_cluster_kernel, &lc) == cudaSuccess && n >= 1) e->qc_max_ctas = c;
+                if (cudaOccupancyMaxActiveClusters(&n, schedule_cluster_kernel<QC_MAX_THREADS>, &lc) == cudaSuccess && n >= 1) e->qc_max_ctas = c;
             }
         }
         cudaGetLastError();
@@ -891,16 +896,17 @@ static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t 
     CU(e, cudaEventRecord(e->ev0, s));
     const uint32_t n_tiles = (N + TILE_NODES - 1) / TILE_NODES;
     if (queue_cluster_form(e)) {
-        // the whole image inside one cluster: about 128 nodes per CTA until the cluster is full, then more lanes per CTA
+        // the whole image inside one cluster: 128 lanes per CTA while 16 such CTAs hold it, else 640
+        const uint32_t threads = N <= (uint32_t)e->qc_max_ctas * (uint32_t)QC_SMALL_THREADS ? (uint32_t)QC_SMALL_THREADS : (uint32_t)QC_MAX_THREADS;
         uint32_t ctas = 1;
-        while (ctas < (uint32_t)e->qc_max_ctas && ctas * 128u < N) ctas <<= 1;
-        const uint32_t threads = std::max(32u, ((N + ctas - 1) / ctas + 31u) & ~31u);
+        while (ctas < (uint32_t)e->qc_max_ctas && ctas * threads < N) ctas <<= 1;
         cudaLaunchConfig_t lc = {};
         lc.gridDim = dim3(ctas); lc.blockDim = dim3(threads); lc.dynamicSmemBytes = qc_layout(threads).total; lc.stream = s;
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = ctas; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         lc.attrs = at; lc.numAttrs = 1;
-        CU(e, cudaLaunchKernelEx(&lc, schedule_cluster_kernel, d_nodes, n_nodes, d_pods, npods, d_hint, rowb, d_out, prm, ctr, d_gang));
+        if (threads == (uint32_t)QC_SMALL_THREADS) CU(e, cudaLaunchKernelEx(&lc, schedule_cluster_kernel<QC_SMALL_THREADS>, d_nodes, n_nodes, d_pods, npods, d_hint, rowb, d_out, prm, ctr, d_gang));
+        else CU(e, cudaLaunchKernelEx(&lc, schedule_cluster_kernel<QC_MAX_THREADS>, d_nodes, n_nodes, d_pods, npods, d_hint, rowb, d_out, prm, ctr, d_gang));
     } else if (queue_tile_form(e)) {
         // every node gets its own lane group: tile form (shared-memory resident tables)
         CU(e, cudaLaunchCooperativeKernel((const void*)schedule_tile_kernel, dim3(n_tiles), dim3(SCORE_THREADS), targs, sched_tile_smem_bytes(), s));

@@ -26,6 +26,7 @@
 namespace kgwe {
 
 constexpr int QC_MAX_THREADS = 640;        // 20 warps; 296 bytes of shared-memory columns per lane
+constexpr int QC_SMALL_THREADS = 128;      // the form for images of up to 16 x 128 nodes: fewer warps per scheduler, shorter passes
 constexpr int QC_MAX_CTAS = 16;            // non-portable cluster size, opt-in at launch
 constexpr int QC_WINDOW = 256;             // pod descriptors staged per refill
 constexpr uint32_t QC_NODE_BITS = 14;
@@ -83,6 +84,19 @@ __device__ __forceinline__ bool qc_wait_phase(uint32_t mbar, uint32_t phase) {
     return false;
 }
 
+// avail (8-bit set) -> avail_prefix (byte i: the first i + 1 members as a set) and avail_order (members in index order, 3 bits each):
+// NodeCtx::avail_prefix / avail_order (node_ctx_core) as a table, filled by the engine at start-up (qc_first_tables).
+__constant__ uint64_t qc_prefix_lut[256];
+__constant__ uint32_t qc_order_lut[256];
+inline void qc_first_tables(uint64_t* prefix, uint32_t* order) {
+    for (uint32_t avail = 0; avail < 256; ++avail) {
+        uint64_t pf = 0; uint32_t od = 0, acc = 0; int i = 0;
+        for (uint32_t b = 0; b < 8; ++b)
+            if (avail >> b & 1u) { acc |= 1u << b; od |= b << (3 * i); pf |= (uint64_t)acc << (8 * i); ++i; }
+        prefix[avail] = pf; order[avail] = od;
+    }
+}
+
 // bit i of the low nibble of x -> byte i all ones
 __device__ __forceinline__ uint32_t qc_expand4(uint32_t x) { return (((x & 0xfu) * 0x00204081u) & 0x01010101u) * 0xffu; }
 
@@ -130,13 +144,7 @@ __device__ __forceinline__ void qc_state(LaneNode& ln, const uint64_t* st, int S
     ln.rhi = (uint32_t)(rows >> 32) & (availR * 0x01010101u) & qc_expand4(availR >> 4);
     ln.arch_lo = (uint32_t)arch & qc_expand4(avail);
     ln.arch_hi = (uint32_t)(arch >> 32) & qc_expand4(avail >> 4);
-    ln.avail_prefix = 0; ln.avail_order = 0;
-    uint32_t m = avail, acc = 0; int i = 0;
-    while (m) {
-        const int b = __ffs((int)m) - 1;
-        acc |= 1u << b; ln.avail_order |= (uint32_t)b << (3 * i); ln.avail_prefix |= (uint64_t)acc << (8 * i);
-        m &= m - 1; ++i;
-    }
+    ln.avail_prefix = qc_prefix_lut[avail]; ln.avail_order = qc_order_lut[avail];
 }
 
 // Lazily filled per-lane tables (by value: the lane state stays in registers across the call).
@@ -145,7 +153,7 @@ __device__ __noinline__ uint32_t qc_memo_fill(uint32_t avail, uint32_t rlo, uint
     LaneNode ln; ln.avail = avail; ln.A = __popc(avail); ln.rlo = rlo; ln.rhi = rhi; ln.tier = tier; ln.valid = true;
     LaneTabs tb; tb.topo = const_cast<int32_t*>(topo_tab); tb.stride = S; tb.mat = nullptr;
     int topo = -1; uint32_t sel = 0, order = 0, sc = 0;
-    lane_group_search<false>(ln, tb, rec, k, norm, K1_MODE_FULL, topo, sel, order, sc);
+    lane_group_search<false>(ln, tb, rec, k, norm, K1_MODE_PRUNE, topo, sel, order, sc);      // (a uniform node's first completed walk is the winner)
     memo[(k - 2) * S] = make_int2(topo, (int)(order | (sel << 24)));
     return sc;
 }
@@ -159,12 +167,14 @@ __device__ __noinline__ void qc_groups_fill(uint32_t avail, const uint64_t* st, 
     grp[3 * S] = (uint32_t)pp; grp[4 * S] = (uint32_t)(pp >> 32); grp[5 * S] = po;
 }
 
-__global__ void __launch_bounds__(QC_MAX_THREADS, 1)
+template <int T>
+__global__ void __launch_bounds__(T, 1)
 schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
                         const uint8_t* __restrict__ hint, uint32_t hint_row_bytes, kgwe_placement* __restrict__ out,
                         Params P, unsigned long long* __restrict__ counters, const uint32_t* __restrict__ gang_of) {
     extern __shared__ __align__(128) unsigned char smem[];
-    const int T = (int)blockDim.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, n_warps = T >> 5;
+    constexpr int n_warps = T >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t C = gridDim.x, rank = qc_cta_rank();
     const QcLayout L = qc_layout((uint32_t)T);
     PodLite* spod = reinterpret_cast<PodLite*>(smem + L.pods);
