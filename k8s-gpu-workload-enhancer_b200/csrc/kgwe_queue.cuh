@@ -7,9 +7,10 @@
 // one cluster of up to 16 CTAs (ONE LANE = ONE NODE, state in registers and [entry][lane] shared-memory columns as
 // in K1, kgwe_lane.cuh), and the arg-max goes through distributed shared memory:
 //   every lane evaluates the workload on its node; REDUX.MAX per warp; one bar.sync; warp 0 folds the warp keys
-//   and stores the CTA's key into slot [rank] of EVERY CTA of the cluster with st.async, which also completes 4
-//   bytes of the receiving CTA's mbarrier; every thread waits for its own CTA's mbarrier phase (<= 16 keys have
-//   landed), reads the keys and knows the winner.  No fence and no cluster-wide barrier inside the loop.
+//   and sends the CTA's key to EVERY CTA of the cluster as a remote atomic max (red.async on shared::cluster) that
+//   also completes 4 bytes of the receiving CTA's mbarrier; one lane per warp waits for its own CTA's mbarrier
+//   phase (all <= 16 keys have landed) and every thread reads the one word that now holds the winner's key.
+//   No fence and no cluster-wide barrier inside the loop.
 //   The lane that owns the winning node writes the decision, commits in the image and refreshes its own state.
 // Keys are TotalScore << 14 | (16383 - node): largest score, lowest node index on ties (the canonical order).
 // The greedy winners per group size are memoised per lane and filled lazily: a commit only invalidates the owner's
@@ -65,10 +66,10 @@ __device__ __forceinline__ uint32_t qc_cta_rank() { uint32_t r; asm volatile("mo
 __device__ __forceinline__ uint32_t qc_map_to_cta(uint32_t smem_addr, uint32_t rank) {
     uint32_t r; asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank)); return r;
 }
-// One 32-bit store into another CTA's shared memory that also signals that CTA's mbarrier (complete_tx of 4 bytes):
-// the data is visible to whoever observes the phase of the mbarrier complete - no fence, no cluster-wide barrier.
-__device__ __forceinline__ void qc_store_signal(uint32_t cluster_addr, uint32_t v, uint32_t cluster_mbar) {
-    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.u32 [%0], %1, [%2];" ::"r"(cluster_addr), "r"(v), "r"(cluster_mbar) : "memory");
+// One 32-bit atomic max on a word of another CTA's shared memory that also signals that CTA's mbarrier (complete_tx of
+// 4 bytes): the update is visible to whoever observes the phase of the mbarrier complete - no fence, no cluster-wide barrier.
+__device__ __forceinline__ void qc_max_signal(uint32_t cluster_addr, uint32_t v, uint32_t cluster_mbar) {
+    asm volatile("red.async.relaxed.cluster.mbarrier::complete_tx::bytes.shared::cluster.max.u32 [%0], %1, [%2];" ::"r"(cluster_addr), "r"(v), "r"(cluster_mbar) : "memory");
 }
 __device__ __forceinline__ void qc_cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
 __device__ __forceinline__ void qc_cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
@@ -77,7 +78,7 @@ __device__ __forceinline__ void qc_cluster_wait() { asm volatile("barrier.cluste
 __device__ __forceinline__ bool qc_wait_phase(uint32_t mbar, uint32_t phase) {
     for (uint32_t it = 0; it < (1u << 22); ++it) {
         uint32_t done;
-        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
                      : "=r"(done) : "r"(mbar), "r"(phase) : "memory");
         if (done) return true;
     }
@@ -171,7 +172,7 @@ template <int T>
 __global__ void __launch_bounds__(T, 1)
 schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
                         const uint8_t* __restrict__ hint, uint32_t hint_row_bytes, kgwe_placement* __restrict__ out,
-                        Params P, unsigned long long* __restrict__ counters, const uint32_t* __restrict__ gang_of) {
+                        Params P, unsigned long long* __restrict__ counters, const uint32_t* __restrict__ gang_of, uint32_t dbg) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr int n_warps = T >> 5;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -218,13 +219,14 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
     qc_cluster_arrive(); qc_cluster_wait();      // every CTA's key slots are initialised before anybody stores into them
 
     const uint32_t key_low = (QC_MAX_NODES - 1u) - node;
-    const uint32_t my_slot = smem_u32(ckeys) + rank * 4u;
+    const uint32_t ckeys_a = smem_u32(ckeys);
     uint32_t cnt_scored = 0, cnt_resolved = 0, cnt_evals = 0;
     // E5 gangs: see schedule_tile_kernel - every thread sees every decision; a lane remembers what its node committed
     // for the current gang and takes it back when the gang's last member has been decided and one of them found no node.
     bool gang_failed = false; uint32_t gang_mask = 0, gang_commits = 0;
     uint32_t hint_byte = (hint && in_range) ? __ldg(hint + (node >> 3)) : 0u;
 
+    LaneResult r;
     for (uint32_t p = 0; p < n_pods; ++p) {
         const uint32_t wi = p & (QC_WINDOW - 1);
         if (wi == 0) {      // stage the next window of pod descriptors
@@ -246,7 +248,7 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
         if (pd.pk & PL_MINBW) min_bw = sminbw[wi];
         const int k = (int)(pd.pk & 0xffu);
         if ((pd.pk & (PL_NVLINK | PL_EXH)) == PL_NVLINK) {      // warp-uniform
-            if (ln.valid && ln.A >= k && !(memo_ok >> (k - 2) & 1u)) {
+            if (!(dbg & 4u) && ln.valid && ln.A >= k && !(memo_ok >> (k - 2) & 1u)) {
                 cnt_scored += qc_memo_fill(ln.avail, ln.rlo, ln.rhi, ln.tier, tb.memo, tb.topo, T, rec, k, P.norm);
                 memo_ok |= 1u << (k - 2);
             }
@@ -255,28 +257,31 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
             if (ln.valid && ln.A >= k && !groups_ok) { qc_groups_fill(ln.avail, st, tb.grp, T); groups_ok = true; }
             __syncwarp();
         }
-        LaneResult r;
-        lane_evaluate<false, false>(ln, tb, rec, pd, min_bw, hinted, P, K1_MODE_MEMO, r);
+        if (!(dbg & 1u) || p == 0) lane_evaluate<false, false>(ln, tb, rec, pd, min_bw, hinted, P, K1_MODE_MEMO, r);
         if (in_range) { cnt_evals += 1; cnt_resolved += r.candidates; cnt_scored += r.scored; }
         const uint32_t mykey = r.kept_total ? ((r.kept_total << QC_NODE_BITS) | key_low) : 0u;
         const uint32_t wkey = __reduce_max_sync(0xffffffffu, mykey);
         if (lane == 0) wkeys[warp] = wkey;
         __syncthreads();
-        const uint32_t par = (p & 1u) * QC_MAX_CTAS, bar = bars + (p & 1u) * 8u;
+        // slot p mod 4 of every CTA receives the arg-max of the cluster for workload p: each CTA's key arrives as a remote
+        // atomic max that also completes 4 bytes of the receiver's mbarrier.  The slot of workload p + 2 is cleared here,
+        // two exchanges before its first remote update can arrive and one after its last reader moved on.
+        const uint32_t slot = ckeys_a + (p & 3u) * 4u, bar = bars + (p & 1u) * 8u;
         if (warp == 0) {
             const uint32_t ckey = __reduce_max_sync(0xffffffffu, lane < n_warps ? wkeys[lane] : 0u);
-            if (lane == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(C * 4u) : "memory");
-            if ((uint32_t)lane < C) qc_store_signal(qc_map_to_cta(my_slot + par * 4u, (uint32_t)lane), ckey, qc_map_to_cta(bar, (uint32_t)lane));
-            __syncwarp();
+            if (lane == 0) {
+                asm volatile("st.shared.u32 [%0], %1;" ::"r"(ckeys_a + ((p + 2u) & 3u) * 4u), "r"(0u) : "memory");
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(C * 4u) : "memory");
+            }
+            if ((uint32_t)lane < C) qc_max_signal(qc_map_to_cta(slot, (uint32_t)lane), ckey, qc_map_to_cta(bar, (uint32_t)lane));
         }
-        if (!qc_wait_phase(bar, (p >> 1) & 1u)) { if (counters) atomicAdd(&counters[3], 1ull); break; }      // (every thread of the cluster times out alike)
+        __syncwarp();
+        bool arrived = true;
+        if (lane == 0) arrived = qc_wait_phase(bar, (p >> 1) & 1u);
+        arrived = __shfl_sync(0xffffffffu, arrived, 0);
+        if (!arrived) { if (lane == 0 && counters) atomicAdd(&counters[3], 1ull); break; }      // (every warp of the cluster times out alike)
         uint32_t win;
-        {
-            const uint4* ck = reinterpret_cast<const uint4*>(ckeys + par);
-            const uint4 a = ck[0], b = ck[1], c = ck[2], d = ck[3];
-            win = max(max(max(a.x, a.y), max(a.z, a.w)), max(max(b.x, b.y), max(b.z, b.w)));
-            win = max(win, max(max(max(c.x, c.y), max(c.z, c.w)), max(max(d.x, d.y), max(d.z, d.w))));
-        }
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(win) : "r"(slot) : "memory");
         bool changed = false;
         if (win == 0u) {
             if (rank == 0 && tid == 0) {
@@ -306,7 +311,7 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
             gang_failed = false; gang_mask = 0; gang_commits = 0;
         }
         if (changed) {
-            qc_state(ln, st, T, allocated, n_allocs);
+            if (!(dbg & 2u)) qc_state(ln, st, T, allocated, n_allocs);
             memo_ok = 0; groups_ok = false;
             rec->allocated_mask = (uint8_t)allocated;      // the image in HBM follows
             rec->n_allocs = n_allocs;
