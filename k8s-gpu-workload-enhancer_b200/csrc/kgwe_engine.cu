@@ -897,7 +897,6 @@ static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t 
     const uint32_t n_tiles = (N + TILE_NODES - 1) / TILE_NODES;
     if (queue_cluster_form(e)) {
         // the whole image inside one cluster: 128 lanes per CTA while 16 such CTAs hold it, else 640
-        const uint32_t dbgf = getenv("KGWE_QC_DBG") ? (uint32_t)atoi(getenv("KGWE_QC_DBG")) : 0u;
         const uint32_t threads = N <= (uint32_t)e->qc_max_ctas * (uint32_t)QC_SMALL_THREADS ? (uint32_t)QC_SMALL_THREADS : (uint32_t)QC_MAX_THREADS;
         uint32_t ctas = 1;
         while (ctas < (uint32_t)e->qc_max_ctas && ctas * threads < N) ctas <<= 1;
@@ -906,8 +905,8 @@ static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t 
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = ctas; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         lc.attrs = at; lc.numAttrs = 1;
-        if (threads == (uint32_t)QC_SMALL_THREADS) CU(e, cudaLaunchKernelEx(&lc, schedule_cluster_kernel<QC_SMALL_THREADS>, d_nodes, n_nodes, d_pods, npods, d_hint, rowb, d_out, prm, ctr, d_gang, dbgf));
-        else CU(e, cudaLaunchKernelEx(&lc, schedule_cluster_kernel<QC_MAX_THREADS>, d_nodes, n_nodes, d_pods, npods, d_hint, rowb, d_out, prm, ctr, d_gang, dbgf));
+        if (threads == (uint32_t)QC_SMALL_THREADS) CU(e, cudaLaunchKernelEx(&lc, schedule_cluster_kernel<QC_SMALL_THREADS>, d_nodes, n_nodes, d_pods, npods, d_hint, rowb, d_out, prm, ctr, d_gang));
+        else CU(e, cudaLaunchKernelEx(&lc, schedule_cluster_kernel<QC_MAX_THREADS>, d_nodes, n_nodes, d_pods, npods, d_hint, rowb, d_out, prm, ctr, d_gang));
     } else if (queue_tile_form(e)) {
         // every node gets its own lane group: tile form (shared-memory resident tables)
         CU(e, cudaLaunchCooperativeKernel((const void*)schedule_tile_kernel, dim3(n_tiles), dim3(SCORE_THREADS), targs, sched_tile_smem_bytes(), s));

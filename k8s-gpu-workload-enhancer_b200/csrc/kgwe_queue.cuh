@@ -172,7 +172,7 @@ template <int T>
 __global__ void __launch_bounds__(T, 1)
 schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
                         const uint8_t* __restrict__ hint, uint32_t hint_row_bytes, kgwe_placement* __restrict__ out,
-                        Params P, unsigned long long* __restrict__ counters, const uint32_t* __restrict__ gang_of, uint32_t dbg) {
+                        Params P, unsigned long long* __restrict__ counters, const uint32_t* __restrict__ gang_of) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr int n_warps = T >> 5;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -226,7 +226,6 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
     bool gang_failed = false; uint32_t gang_mask = 0, gang_commits = 0;
     uint32_t hint_byte = (hint && in_range) ? __ldg(hint + (node >> 3)) : 0u;
 
-    LaneResult r;
     for (uint32_t p = 0; p < n_pods; ++p) {
         const uint32_t wi = p & (QC_WINDOW - 1);
         if (wi == 0) {      // stage the next window of pod descriptors
@@ -248,7 +247,7 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
         if (pd.pk & PL_MINBW) min_bw = sminbw[wi];
         const int k = (int)(pd.pk & 0xffu);
         if ((pd.pk & (PL_NVLINK | PL_EXH)) == PL_NVLINK) {      // warp-uniform
-            if (!(dbg & 4u) && ln.valid && ln.A >= k && !(memo_ok >> (k - 2) & 1u)) {
+            if (ln.valid && ln.A >= k && !(memo_ok >> (k - 2) & 1u)) {
                 cnt_scored += qc_memo_fill(ln.avail, ln.rlo, ln.rhi, ln.tier, tb.memo, tb.topo, T, rec, k, P.norm);
                 memo_ok |= 1u << (k - 2);
             }
@@ -257,7 +256,8 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
             if (ln.valid && ln.A >= k && !groups_ok) { qc_groups_fill(ln.avail, st, tb.grp, T); groups_ok = true; }
             __syncwarp();
         }
-        if (!(dbg & 1u) || p == 0) lane_evaluate<false, false>(ln, tb, rec, pd, min_bw, hinted, P, K1_MODE_MEMO, r);
+        LaneResult r;
+        lane_evaluate<false, false>(ln, tb, rec, pd, min_bw, hinted, P, K1_MODE_MEMO, r);
         if (in_range) { cnt_evals += 1; cnt_resolved += r.candidates; cnt_scored += r.scored; }
         const uint32_t mykey = r.kept_total ? ((r.kept_total << QC_NODE_BITS) | key_low) : 0u;
         const uint32_t wkey = __reduce_max_sync(0xffffffffu, mykey);
@@ -311,7 +311,7 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
             gang_failed = false; gang_mask = 0; gang_commits = 0;
         }
         if (changed) {
-            if (!(dbg & 2u)) qc_state(ln, st, T, allocated, n_allocs);
+            qc_state(ln, st, T, allocated, n_allocs);
             memo_ok = 0; groups_ok = false;
             rec->allocated_mask = (uint8_t)allocated;      // the image in HBM follows
             rec->n_allocs = n_allocs;

@@ -112,11 +112,12 @@ def test_config5_full_size_gangs(kg, orc):
     eng.close()
 
 
-@pytest.mark.parametrize("path", ["device-side roll-back", "speculative windows"])
+@pytest.mark.parametrize("path", ["device-side roll-back", "device-side roll-back, grid-wide kernel", "speculative windows"])
 def test_gangs_fill_the_cluster(kg, orc, path):
     """The regime configs[4] ends in - most gangs rejected once the cluster is full - on a cluster small enough for
     the oracle to run the whole queue.  Two paths: the queue kernel taking rejected gangs back itself (what
-    kgwe_schedule_gangs does whenever the image fits the tile form), and the host-side speculative windows used for
+    kgwe_schedule_gangs does whenever the image fits the cluster form or the tile form of the queue kernel - both are run),
+    and the host-side speculative windows used for
     larger images, forced here and cut to 64 pods so the queue crosses dozens of window edges, each with rejected
     gangs to undo (a fresh process: the variable is read once)."""
     code = r'''
@@ -145,7 +146,44 @@ print("OK")
 ''' % ROOT
     env = dict(os.environ)
     env.pop("KGWE_GANG_WINDOW", None)
+    env.pop("KGWE_QUEUE_FORM", None)
+    if path.endswith("grid-wide kernel"):
+        env["KGWE_QUEUE_FORM"] = "tile"
     if path == "speculative windows":
         env["KGWE_GANG_WINDOW"] = "64"
     r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0 and "OK" in r.stdout, r.stdout[-1500:] + r.stderr[-1500:]
+
+
+@pytest.mark.parametrize("n_nodes,n_pods", [(16, 300), (1000, 1500), (2100, 1500), (10000, 3000)])
+def test_queue_kernel_forms_agree(kg, orc, n_nodes, n_pods):
+    """The stateful queue has two device forms: inside one thread-block cluster (kgwe_queue.cuh; 128 lanes per CTA up to
+    2,048 nodes, 640 up to 10,240) and grid-wide (schedule_tile_kernel).  Both must give the oracle's decisions, with and
+    without hints and minimum bandwidths, and leave the same image and counters behind (KGWE_QUEUE_FORM is read when an
+    engine is created)."""
+    abi = kg.abi
+    nodes = kg.synth.make_cluster(n_nodes, "mixed", seed=21)
+    pods = kg.synth.make_pods(n_pods, seed=22)
+    pods["min_bandwidth_gbps"][::7] = 300.0
+    led = kg.synth.make_ledger(nodes, 0.25, seed=23)
+    hint = kg.synth.make_hint(n_pods, n_nodes, 0.01, seed=24)
+    got = {}
+    old = os.environ.pop("KGWE_QUEUE_FORM", None)
+    try:
+        for form in ("cluster", "tile"):
+            os.environ["KGWE_QUEUE_FORM"] = form
+            eng = engine_for(kg, nodes, led)
+            d1 = eng.schedule_queue(pods[: n_pods // 2], hint[: n_pods // 2])
+            d2 = eng.schedule_queue(pods[n_pods // 2:])
+            st = eng.stats()
+            probe, _ = eng.score_batch(pods[:8], n_nodes, want_scores=True)
+            got[form] = (d1.tobytes(), d2.tobytes(), probe.tobytes(), st["evaluations"], st["candidates_resolved"], st["n_allocations"])
+            eng.close()
+    finally:
+        os.environ.pop("KGWE_QUEUE_FORM", None)
+        if old is not None:
+            os.environ["KGWE_QUEUE_FORM"] = old
+    assert got["cluster"] == got["tile"]
+    n_check = n_pods // 2 if n_nodes <= 2100 else 150      # the oracle's sequential queue is slow on 10k nodes
+    o_dec = orc.schedule_queue(abi, nodes, led, pods[:n_check], hint[:n_check])[0]
+    assert got["cluster"][0][: n_check * abi.PLACEMENT.itemsize] == o_dec.tobytes()
