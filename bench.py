@@ -574,8 +574,19 @@ def side_measurements(args, torch, dist, kg, orc, eng, scorer, stream, dev, loca
     w = time.perf_counter() - a
     s2 = eng2.stats()
     out["stateful_queue"] = {"pods": len(q), "wall_ms": w * 1e3, "gpu_ms": s2["last_call_gpu_ms"], "us_per_pod": s2["last_call_gpu_ms"] * 1e3 / len(q),
-                             "placed": int((dec["node_idx"] != abi.NO_NODE).sum()), "candidates_resolved_per_sec": s2["candidates_resolved"] / w}
+                             "placed": int((dec["node_idx"] != abi.NO_NODE).sum()), "candidates_resolved_per_sec": s2["candidates_resolved"] / w,
+                             "kernel": "one thread-block cluster (kgwe_queue.cuh) while the image has at most 10,240 nodes, else grid-wide (schedule_tile_kernel)"}
     eng2.close()
+    if not os.environ.get("KGWE_QUEUE_FORM"):      # the grid-wide form on the same queue, for comparison (the variable is read at engine creation)
+        os.environ["KGWE_QUEUE_FORM"] = "tile"
+        try:
+            eng2 = fresh()
+            dec_t = eng2.schedule_queue(q)
+            out["stateful_queue"]["grid_wide_form_us_per_pod"] = eng2.stats()["last_call_gpu_ms"] * 1e3 / len(q)
+            out["stateful_queue"]["forms_agree"] = bool(dec_t.tobytes() == dec.tobytes())
+            eng2.close()
+        finally:
+            del os.environ["KGWE_QUEUE_FORM"]
 
     # ---- the other search modes on the same workload and outputs (reported separately: they share or skip parts of the search) ----
     for name, flag, note in (("pruned_tied_starts", abi.CFG_PRUNE_TIED_STARTS, "KGWE_CFG_PRUNE_TIED_STARTS: uniform nodes stop at the first completed walk; identical results; candidates counts the groups actually grown"),
