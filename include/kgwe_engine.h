@@ -39,6 +39,7 @@
 extern "C" {
 #endif
 
+#define KGWE_ABI_VERSION   3     /* bumped whenever an entry point or a struct of this header changes; kgwe_version() ends in "abi <n>" */
 #define KGWE_MAX_GPUS      8     /* GPUs per node record (all BASELINE configs use 8) */
 #define KGWE_MIG_PROFILES  10    /* CRD whitelist, src/sharing/mig_controller.go:273-284 */
 #define KGWE_MAX_TOPK      16

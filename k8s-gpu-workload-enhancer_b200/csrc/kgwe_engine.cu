@@ -377,7 +377,9 @@ int ledger_apply(kgwe_engine* e, uint64_t wl_id, uint32_t idx, uint8_t mask, boo
 
 extern "C" {
 
-const char* kgwe_version(void) { return "kgwe-b200 0.1 (sm_100a)"; }
+#define KGWE_STR2(x) #x
+#define KGWE_STR(x) KGWE_STR2(x)
+const char* kgwe_version(void) { return "kgwe-b200 0.2 (sm_100a) abi " KGWE_STR(KGWE_ABI_VERSION); }
 
 void kgwe_config_default(kgwe_config* c) {
     if (!c) return;

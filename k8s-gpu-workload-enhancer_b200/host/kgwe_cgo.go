@@ -5,6 +5,9 @@
 // absent, here and on the GPU box).  It is kept as a thin 1:1 mapping over include/kgwe_engine.h
 // so that it can be reviewed by reading; the same entry points, call for call, are exercised by
 // the C++ mirror next to this file (kgwe_host.cpp, tests/host/) and by the ctypes binding.
+// Last checked against include/kgwe_engine.h at KGWE_ABI_VERSION 3 (kgwe_node_upsert_remap,
+// KGWE_ERR_CONFLICT from kgwe_alloc_commit, candidates_resolved and the latency histogram in
+// kgwe_stats); init() below refuses to run against any other revision.
 //
 // Wiring inside the reference (src/scheduler/scheduler.go):
 //   NewTopologyAwareScheduler  -> also newGPUEngine(config, maxNodes)
@@ -35,6 +38,14 @@ import (
 
 	"github.com/nvidia/kgwe/src/discovery"
 )
+
+const abiChecked = 3 // the KGWE_ABI_VERSION this file mirrors
+
+func init() {
+	if C.KGWE_ABI_VERSION != abiChecked || C.sizeof_kgwe_stats != 200 {
+		panic(fmt.Sprintf("kgwe_cgo.go mirrors ABI %d of kgwe_engine.h, the header is at %d (%s)", abiChecked, int(C.KGWE_ABI_VERSION), C.GoString(C.kgwe_version())))
+	}
+}
 
 var migNames = []string{"1g.5gb", "1g.10gb", "2g.10gb", "2g.20gb", "3g.20gb", "3g.40gb", "4g.20gb", "4g.40gb", "7g.40gb", "7g.80gb"}
 
@@ -211,16 +222,38 @@ func (e *gpuEngine) upsertNode(n *discovery.NodeTopology) error {
 					continue
 				}
 				img.mig_has_free_mask |= 1 << uint(i)
-				if p := migCode(inst.Profile.Name); p >= 1 && p <= C.KGWE_MIG_PROFILES && img.mig_free[p-1] < 255 {
+				if p := migCode(inst.Profile.Name); p >= 1 && p <= C.KGWE_MIG_PROFILES {
+					if img.mig_free[p-1] == 255 { // one byte per profile in the record: refuse, do not clamp
+						return fmt.Errorf("node %s: more than 255 free MIG instances of profile %s", n.NodeName, inst.Profile.Name)
+					}
 					img.mig_free[p-1]++ // scheduler.go:606-622
 				}
 			}
 		}
 	}
-	e.nodeUUIDs[idx] = uuids
-	if rc := C.kgwe_node_upsert(e.h, C.uint32_t(idx), &img); rc != C.KGWE_OK {
+	// The reference keys allocations by GPU UUID (scheduler.go:587-593), so a refresh that enumerates the node's GPUs in
+	// another order keeps them; the engine's ledger holds index masks, so it is told where each old index went.
+	var oldToNew [C.KGWE_MAX_GPUS]C.int8_t
+	moved := false
+	for g := range oldToNew {
+		oldToNew[g] = -1
+		if g < len(e.nodeUUIDs[idx]) {
+			if q, ok := gpuOf[e.nodeUUIDs[idx][g]]; ok {
+				oldToNew[g] = C.int8_t(q)
+			}
+			moved = moved || int(oldToNew[g]) != g
+		}
+	}
+	var rc C.int
+	if ok && moved {
+		rc = C.kgwe_node_upsert_remap(e.h, C.uint32_t(idx), &img, &oldToNew[0])
+	} else {
+		rc = C.kgwe_node_upsert(e.h, C.uint32_t(idx), &img)
+	}
+	if rc != C.KGWE_OK {
 		return e.err(rc)
 	}
+	e.nodeUUIDs[idx] = uuids
 	return nil
 }
 
@@ -399,4 +432,54 @@ func (e *gpuEngine) release(uid string) error {
 		return fmt.Errorf("allocation not found for workload %s", uid) // scheduler.go:715
 	}
 	return nil
+}
+
+// bind: the extender's bind verb for one pod (deploy/helm/kgwe/templates/scheduler-configmap.yaml:64): score the pod
+// once more, and if nodeName still keeps it, record the GPUs the scorer selects there.  kgwe_alloc_commit refuses GPUs
+// another workload took in the meantime (KGWE_ERR_CONFLICT), which is tryScheduleOnNode's re-check (scheduler.go:634-640).
+func (e *gpuEngine) bind(w *GPUWorkload, nodeName string) (*SchedulingDecision, error) {
+	e.mu.Lock()
+	defer e.mu.Unlock()
+	idx, ok := e.nodeIdx[nodeName]
+	if !ok {
+		return nil, fmt.Errorf("node %s not found", nodeName)
+	}
+	n := len(e.nodeName)
+	req := e.podReq(w)
+	scores := make([]C.kgwe_node_score, n)
+	if rc := C.kgwe_score_batch(e.h, &req, 1, nil, &scores[0], C.uint32_t(n), 0, nil); rc != C.KGWE_OK {
+		return nil, e.err(rc)
+	}
+	s := scores[idx]
+	if s.flags&C.KGWE_F_KEPT == 0 {
+		return nil, fmt.Errorf("failed to schedule on any eligible node") // scheduler.go:178
+	}
+	switch rc := C.kgwe_alloc_commit(e.h, C.uint64_t(e.idOf(w.UID)), C.uint32_t(idx), s.gpu_mask); rc {
+	case C.KGWE_OK:
+	case C.KGWE_ERR_CONFLICT:
+		return nil, fmt.Errorf("GPU already allocated on node %s", nodeName)
+	default:
+		return nil, e.err(rc)
+	}
+	pl := C.kgwe_placement{node_idx: C.uint32_t(idx), total: s.total, topology: s.topology, resource: s.resource, balance: s.balance, gpu_mask: s.gpu_mask, flags: s.flags, order: s.order}
+	ns := e.nodeScoreOf(pl)
+	return &SchedulingDecision{WorkloadUID: w.UID, SelectedNode: ns.NodeName, SelectedGPUs: ns.SelectedGPUs, Score: ns.TotalScore, Reasons: ns.Reasons}, nil
+}
+
+// schedulerMetrics: GetMetrics (scheduler.go:793) plus the engine's own counters.  The latency histogram has the bucket
+// edges of src/monitoring/prometheus_exporter.go:262 read as MICROSECONDS (10 us ... 5 ms, +Inf).
+func (e *gpuEngine) schedulerMetrics() (SchedulerMetrics, [C.KGWE_LATENCY_BUCKETS]uint64, error) {
+	var st C.kgwe_stats
+	var buckets [C.KGWE_LATENCY_BUCKETS]uint64
+	if rc := C.kgwe_get_stats(e.h, &st); rc != C.KGWE_OK {
+		return SchedulerMetrics{}, buckets, e.err(rc)
+	}
+	for i := range buckets {
+		buckets[i] = uint64(st.latency_us_bucket[i])
+	}
+	m := SchedulerMetrics{TotalScheduled: int64(st.scheduled), TotalFailed: int64(st.failed), TopologyOptimalPlacements: int64(st.topology_optimal)}
+	if st.latency_count > 0 {
+		m.AverageLatencyMs = float64(st.latency_sum_us) / float64(st.latency_count) / 1000.0
+	}
+	return m, buckets, nil
 }
