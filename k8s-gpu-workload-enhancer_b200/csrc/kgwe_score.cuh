@@ -112,7 +112,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     // ---- the pod loop: every warp scores all pods of the chunk against its 32 nodes ----
     uint32_t cnt_scored = 0, cnt_resolved = 0;
     const bool has_hint = hint != nullptr, has_best = best != nullptr;
-    const uint32_t do_store = (out != nullptr && in_range) ? 1u : 0u, live = in_range ? 0xffffffffu : 0u;
+    const uint32_t do_store = (out != nullptr && in_range) ? 1u : 0u;
     int4* outp = reinterpret_cast<int4*>(out) + ((size_t)p_begin * n_nodes + node);              // only dereferenced when do_store
     const uint8_t* hintp = hint + ((size_t)p_begin * hint_row_bytes + (node >> 3));               // only dereferenced when has_hint && in_range
     const uint32_t key_low = (uint32_t)(K1_TILE - 1 - tid);
@@ -134,7 +134,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         if (has_hint) { hinted = in_range && ((__ldg(hintp) >> (node & 7)) & 1); hintp += hint_row_bytes; }
         LaneResult r;
         lane_evaluate<GENERAL, TABLES>(ln, tb, rec, pd, min_bw, hinted, P, mode, r);
-        cnt_scored += r.scored & live; cnt_resolved += r.candidates & live;
+        cnt_scored += r.scored; cnt_resolved += r.candidates;
         if (do_store) *outp = make_int4((int)r.w0, (int)r.w1, (int)r.w2, (int)r.w3);
         outp += n_nodes;
         if (has_best) {
@@ -146,6 +146,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         pd = next;
     }
     // counters: [1] candidates whose score was computed, [2] candidates by the reference's counting rule
+    if (!in_range) { cnt_scored = 0; cnt_resolved = 0; }      // (lanes past the image counted 1 + 1 per pod: nothing of the image)
     cnt_scored = __reduce_add_sync(0xffffffffu, cnt_scored);
     cnt_resolved = __reduce_add_sync(0xffffffffu, cnt_resolved);
     if (lane == 0 && counters) {
