@@ -43,6 +43,7 @@ using std::max;
 using std::min;
 
 #include "../../k8s-gpu-workload-enhancer_b200/csrc/kgwe_lane.cuh"
+#include "../../k8s-gpu-workload-enhancer_b200/csrc/kgwe_queue_state.cuh"
 #include "../../k8s-gpu-workload-enhancer_b200/csrc/kgwe_pack.hpp"
 #include "../../oracle/kgwe_oracle.h"
 
@@ -106,4 +107,38 @@ extern "C" int lane_emu_score_batch(const kgwe_config* cfg, const kgwe_node_imag
     if (scored_out) *scored_out = scored_sum;
     if (resolved_out) *resolved_out = resolved_sum;
     return 0;
+}
+
+// The cluster queue kernel's owner refresh (qc_state on the static columns, kgwe_queue_state.cuh) against the set-up path
+// every other kernel uses (node_ctx_core + lane_node_init on the record): for every node and every (allocated_mask,
+// n_allocs) in `allocs` (pairs of mask, count) all LaneNode fields must agree.  Returns the number of disagreements
+// (-1: a record was refused by the packer).
+extern "C" long long lane_emu_queue_state_check(const kgwe_node_image* nodes, uint32_t n_nodes, const uint32_t* allocs, uint32_t n_allocs_cases) {
+    qc_first_tables(qc_prefix_lut, qc_order_lut);
+    long long bad = 0;
+    char msg[160];
+    for (uint32_t n = 0; n < n_nodes; ++n) {
+        DevNode rec;
+        if (to_device_record(nodes[n], rec, msg, sizeof msg) != 0) return -1;
+        const bool present = nodes[n].flags & 1;
+        if (!present) memset(&rec, 0, sizeof rec);
+        NodeCtx c0; node_ctx_core(c0, &rec, true);
+        LaneNode l0; lane_node_init(l0, c0, &rec, 0u);
+        uint64_t st[QS_ENTRIES];
+        qc_static_build(st, 1, &rec, c0, l0.tier);
+        for (uint32_t i = 0; i < n_allocs_cases; ++i) {
+            DevNode r2 = rec;
+            if (present) { r2.allocated_mask = (uint8_t)allocs[2 * i]; r2.n_allocs = allocs[2 * i + 1]; }
+            NodeCtx c; node_ctx_core(c, &r2, true);
+            LaneNode want; lane_node_init(want, c, &r2, 0u);
+            LaneNode got; memset(&got, 0, sizeof got);
+            qc_state(got, st, 1, present ? r2.allocated_mask : 0u, present ? r2.n_allocs : 0u);
+            const bool same = got.avail == want.avail && got.A == want.A && got.rlo == want.rlo && got.rhi == want.rhi && got.sum_free == want.sum_free
+                           && got.util_bonus == want.util_bonus && got.balance == want.balance && got.arch_lo == want.arch_lo && got.arch_hi == want.arch_hi
+                           && got.avail_order == want.avail_order && got.avail_prefix == want.avail_prefix && got.tier == want.tier
+                           && got.valid == want.valid && got.integral == want.integral;
+            bad += same ? 0 : 1;
+        }
+    }
+    return bad;
 }

@@ -20,6 +20,8 @@ def emu():
     lib = C.CDLL(os.path.join(HERE, "host", "liblane_emu.so"))
     vp, u32 = C.c_void_p, C.c_uint32
     lib.lane_emu_score_batch.argtypes = [vp, vp, u32, vp, u32, vp, u32, vp, vp, C.c_int, C.c_int, u32, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+    lib.lane_emu_queue_state_check.argtypes = [vp, u32, vp, u32]
+    lib.lane_emu_queue_state_check.restype = C.c_longlong
     return lib
 
 
@@ -85,3 +87,35 @@ def test_non_default_weights(kg, orc, emu):
         ref, _, _ = orc.score_batch(abi, nodes, ledger, pods, hint=hint, want_scores=True, cfg=cfg)
         got, _, _ = run_emu(emu, abi, nodes, ledger, pods, hint, 0, False, MODE_FULL, cfg=cfg)
         assert got.tobytes() == ref.tobytes()
+
+
+def test_queue_kernel_state_refresh(kg, emu):
+    """The owner lane of the cluster queue kernel re-derives its node's state after a commit from shared-memory columns,
+    without a division (kgwe_queue_state.cuh: the utilisation bonus compares the ordered sum with 30 A and 60 A).  That must
+    equal node_ctx_core + lane_node_init on the record for EVERY allocation state: all 256 masks x several counts, on
+    clusters that include ragged nodes, unhealthy GPUs, MIG, and utilisations chosen to sit on and next to the 30 / 60
+    thresholds of the mean (scheduler.go:540-550) and at the edges of what an upsert accepts."""
+    abi = kg.abi
+    nodes = np.concatenate([kg.synth.make_cluster(40, "mixed", seed=3), kg.synth.config(1)[0]])
+    rng = np.random.default_rng(5)
+    edge = nodes[:24].copy()
+    for i in range(len(edge)):
+        g = int(edge["n_gpus"][i])
+        kind = i % 6
+        if kind == 0:   # means exactly on the thresholds for some subsets
+            edge["util"][i, :g] = rng.choice([30.0, 60.0, 29.999999999999996, 30.000000000000004, 59.99999999999999, 60.00000000000001], g)
+        elif kind == 1:  # sums that hit 30 A / 60 A only through rounding
+            edge["util"][i, :g] = rng.choice([10.0, 20.0, 40.0, 50.0, 70.0, 80.0, 0.1, 0.2, 59.9, 29.9, 30.1, 60.1], g)
+        elif kind == 2:
+            edge["util"][i, :g] = rng.choice([-50.0, 0.0, 1e300, 5e-324, 1e-300, 100.0], g)
+        elif kind == 3:
+            edge["util"][i, :g] = 30.0 + (rng.integers(-3, 4, g) * np.spacing(30.0))
+        elif kind == 4:
+            edge["util"][i, :g] = 60.0 + (rng.integers(-3, 4, g) * np.spacing(60.0))
+        else:
+            edge["util"][i, :g] = rng.uniform(0.0, 100.0, g)
+        edge["free_bytes"][i, :g] = rng.choice(np.array([0, 1, 2**63, 2**64 - 1, 80 * 2**30], dtype=np.uint64), g)
+    nodes = np.ascontiguousarray(np.concatenate([nodes, edge]), dtype=abi.NODE_IMAGE)
+    cases = np.array([(m, c) for m in range(256) for c in (0, 1, 3, 7, 8, 9, 200, 2**32 - 1)], dtype=np.uint32)
+    bad = emu.lane_emu_queue_state_check(nodes.ctypes.data, len(nodes), cases.ctypes.data, len(cases))
+    assert bad == 0
