@@ -33,7 +33,7 @@ constexpr int QC_WINDOW = 256;             // pod descriptors staged per refill
 constexpr uint32_t QC_NODE_BITS = 14;
 constexpr uint32_t QC_MAX_NODES = 1u << QC_NODE_BITS;
 
-struct QcLayout { uint32_t pods, minbw, gang, stat, topo, grp, mig, memo, wkeys, ckeys, bars, total; };
+struct QcLayout { uint32_t pods, minbw, gang, stat, topo, grp, mig, memo, wkeys, ckeys, bars, spec, total; };
 __host__ __device__ inline QcLayout qc_layout(uint32_t threads) {
     QcLayout L; uint32_t o = 0;
     L.pods = o; o += QC_WINDOW * 16u;
@@ -44,9 +44,10 @@ __host__ __device__ inline QcLayout qc_layout(uint32_t threads) {
     L.topo = o; o += 7u * threads * 4u;
     L.grp = o; o += 6u * threads * 4u;
     L.mig = o; o += 3u * threads * 4u;
-    L.wkeys = o; o += 32u * 4u;
+    L.wkeys = o; o += 2u * 32u * 4u;                                   // warp keys of even / odd workloads
     L.ckeys = o; o += 2u * QC_MAX_CTAS * 4u;
     L.bars = o; o += 2u * 8u;
+    L.spec = o; o += 16u * 4u;                                        // the CTA's best lane parks its would-be state here
     L.total = o;
     return L;
 }
@@ -109,6 +110,7 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
     uint32_t* sgang = reinterpret_cast<uint32_t*>(smem + L.gang);
     uint32_t* wkeys = reinterpret_cast<uint32_t*>(smem + L.wkeys);
     uint32_t* ckeys = reinterpret_cast<uint32_t*>(smem + L.ckeys);
+    volatile uint32_t* spec = reinterpret_cast<volatile uint32_t*>(smem + L.spec);
     uint64_t* st = reinterpret_cast<uint64_t*>(smem + L.stat) + tid;
 
     const uint32_t node = rank * (uint32_t)T + (uint32_t)tid;
@@ -187,19 +189,30 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
         if (in_range) { cnt_evals += 1; cnt_resolved += r.candidates; cnt_scored += r.scored; }
         const uint32_t mykey = r.kept_total ? ((r.kept_total << QC_NODE_BITS) | key_low) : 0u;
         const uint32_t wkey = __reduce_max_sync(0xffffffffu, mykey);
-        if (lane == 0) wkeys[warp] = wkey;
+        uint32_t* wk = wkeys + (p & 1u) * 32u;
+        if (lane == 0) wk[warp] = wkey;
         __syncthreads();
+        const uint32_t ckey = __reduce_max_sync(0xffffffffu, lane < n_warps ? wk[lane] : 0u);      // the CTA's best key, in every warp
         // slot p mod 4 of every CTA receives the arg-max of the cluster for workload p: each CTA's key arrives as a remote
         // atomic max that also completes 4 bytes of the receiver's mbarrier.  The slot of workload p + 2 is cleared here,
         // two exchanges before its first remote update can arrive and one after its last reader moved on.
         const uint32_t slot = ckeys_a + (p & 3u) * 4u, bar = bars + (p & 1u) * 8u;
         if (warp == 0) {
-            const uint32_t ckey = __reduce_max_sync(0xffffffffu, lane < n_warps ? wkeys[lane] : 0u);
             if (lane == 0) {
                 asm volatile("st.shared.u32 [%0], %1;" ::"r"(ckeys_a + ((p + 2u) & 3u) * 4u), "r"(0u) : "memory");
                 asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(C * 4u) : "memory");
             }
             if ((uint32_t)lane < C) qc_max_signal(qc_map_to_cta(slot, (uint32_t)lane), ckey, qc_map_to_cta(bar, (uint32_t)lane));
+        }
+        // While the keys travel: the lane that holds the CTA's best key is the only one of this CTA that can win, so it
+        // works out the state its node would have after the commit and parks it; if it wins it only has to pick it up.
+        const bool candidate = mykey != 0u && mykey == ckey;
+        if (candidate) {
+            LaneNode nx;
+            qc_state(nx, st, T, allocated | ((r.w2 >> 16) & 0xffu), n_allocs + 1u);
+            spec[0] = nx.avail; spec[1] = (uint32_t)nx.A; spec[2] = nx.rlo; spec[3] = nx.rhi;
+            spec[4] = (uint32_t)nx.sum_free; spec[5] = (uint32_t)(nx.sum_free >> 32); spec[6] = (uint32_t)nx.util_bonus; spec[7] = (uint32_t)nx.balance;
+            spec[8] = nx.arch_lo; spec[9] = nx.arch_hi; spec[10] = nx.avail_order; spec[11] = (uint32_t)nx.avail_prefix; spec[12] = (uint32_t)(nx.avail_prefix >> 32);
         }
         __syncwarp();
         bool arrived = true;
@@ -208,7 +221,6 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
         if (!arrived) { if (lane == 0 && counters) atomicAdd(&counters[3], 1ull); break; }      // (every warp of the cluster times out alike)
         uint32_t win;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(win) : "r"(slot) : "memory");
-        bool changed = false;
         if (win == 0u) {
             if (rank == 0 && tid == 0) {
                 kgwe_placement pl;
@@ -227,20 +239,23 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
             out[p] = pl;
             allocated |= mask; n_allocs += 1;
             gang_mask |= mask; gang_commits += 1;
-            changed = true;
+            // the state parked above (tier, valid, integral never change)
+            ln.avail = spec[0]; ln.A = (int)spec[1]; ln.rlo = spec[2]; ln.rhi = spec[3];
+            ln.sum_free = (uint64_t)spec[4] | ((uint64_t)spec[5] << 32); ln.util_bonus = (int)spec[6]; ln.balance = (int)spec[7];
+            ln.arch_lo = spec[8]; ln.arch_hi = spec[9]; ln.avail_order = spec[10]; ln.avail_prefix = (uint64_t)spec[11] | ((uint64_t)spec[12] << 32);
+            memo_ok = 0; groups_ok = false;
+            rec->allocated_mask = (uint8_t)allocated;      // the image in HBM follows
+            rec->n_allocs = n_allocs;
         }
         if (gang_of && sgang[wi + 1] != sgang[wi]) {      // the gang's last member has been decided
             if (gang_failed && gang_commits) {             // take this node's commits for the gang back
                 allocated &= ~gang_mask; n_allocs -= gang_commits;
-                changed = true;
+                qc_state(ln, st, T, allocated, n_allocs);
+                memo_ok = 0; groups_ok = false;
+                rec->allocated_mask = (uint8_t)allocated;
+                rec->n_allocs = n_allocs;
             }
             gang_failed = false; gang_mask = 0; gang_commits = 0;
-        }
-        if (changed) {
-            qc_state(ln, st, T, allocated, n_allocs);
-            memo_ok = 0; groups_ok = false;
-            rec->allocated_mask = (uint8_t)allocated;      // the image in HBM follows
-            rec->n_allocs = n_allocs;
         }
         __syncwarp();
     }
