@@ -196,9 +196,13 @@ mig_pack_tree_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uin
                 out[r] = a;
             }
             const uint32_t leaf_new = ((uint32_t)cls << 7) | (b == 0xFFu ? 0x7Fu : b);
+            // the three levels of the repaired path: the minima of the rest of each row do not depend on the level below,
+            // so the three warp reductions are issued together and only two scalar minima are left on the dependent chain
+            const uint32_t rest1 = __reduce_min_sync(0xffffffffu, j == i1 ? MIG_KEY_NONE : row1);
+            const uint32_t rest2 = __reduce_min_sync(0xffffffffu, (uint32_t)lane == i2 ? MIG_KEY_NONE : row2);
             const uint32_t k1 = __reduce_min_sync(0xffffffffu, mig_leaf_key(gl == g ? leaf_new : leaf_old, (uint32_t)cls, gl, gl == g ? occ_new : st_old));
-            const uint32_t k2 = __reduce_min_sync(0xffffffffu, j == i1 ? k1 : row1);
-            const uint32_t k3 = __reduce_min_sync(0xffffffffu, (uint32_t)lane == i2 ? k2 : row2);
+            const uint32_t k2 = min(k1, rest1);
+            const uint32_t k3 = min(k2, rest2);
             if (lane == 0) { leaf[warp * n_pad + g] = (uint8_t)leaf_new; L1[t * n1 + i1] = k1; L2[t * 32 + i2] = k2; root[t] = k3; if (warp == 0) state[g] = (uint16_t)(0x100u | ((uint32_t)cls << 9) | occ_new); }
         }
         // every 512 requests the half of the ring consumed last is refilled with the profiles 512..1023 requests ahead (the
