@@ -921,11 +921,16 @@ static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t 
         CU(e, cudaLaunchCooperativeKernel((const void*)schedule_tile_kernel, dim3(n_tiles), dim3(SCORE_THREADS), targs, sched_tile_smem_bytes(), s));
     } else
     CU(e, cudaLaunchCooperativeKernel((const void*)schedule_kernel, dim3(grid), dim3(SCORE_THREADS), args, 0, s));
-    est_bandwidth_kernel<<<(np + 127) / 128, 128, 0, s>>>(e->d_nodes, N, e->cfg.node_base, e->d_topk.p, np);
-    CU(e, cudaGetLastError());
-    e->stats.kernel_launches += 2;
-    CU(e, cudaMemsetAsync(e->d_best.p, 0, (size_t)np * sizeof(unsigned long long), s));
-    CU(e, cudaMemsetAsync(e->d_arrive.p, 0, (size_t)np * sizeof(unsigned int), s));
+    if (queue_cluster_form(e)) {      // (the cluster form fills in EstimatedBandwidth itself and uses neither key table nor arrival counters)
+        CU(e, cudaGetLastError());
+        e->stats.kernel_launches += 1;
+    } else {
+        est_bandwidth_kernel<<<(np + 127) / 128, 128, 0, s>>>(e->d_nodes, N, e->cfg.node_base, e->d_topk.p, np);
+        CU(e, cudaGetLastError());
+        e->stats.kernel_launches += 2;
+        CU(e, cudaMemsetAsync(e->d_best.p, 0, (size_t)np * sizeof(unsigned long long), s));
+        CU(e, cudaMemsetAsync(e->d_arrive.p, 0, (size_t)np * sizeof(unsigned int), s));
+    }
     CU(e, cudaEventRecord(e->ev1, s));
     CU(e, cudaMemcpyAsync(e->h_topk.p, e->d_topk.p, (size_t)np * sizeof(kgwe_placement), cudaMemcpyDeviceToHost, s));
     e->stats.d2h_bytes += (uint64_t)np * sizeof(kgwe_placement);

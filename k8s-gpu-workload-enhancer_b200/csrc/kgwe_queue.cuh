@@ -267,7 +267,16 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
         if (cnt_scored) atomicAdd(&counters[1], (unsigned long long)cnt_scored);
         if (cnt_resolved) atomicAdd(&counters[2], (unsigned long long)cnt_resolved);
     }
-    qc_cluster_arrive(); qc_cluster_wait();      // nobody leaves while a peer may still store into its shared memory
+    qc_cluster_arrive(); qc_cluster_wait();      // nobody leaves while a peer may still store into its shared memory; every decision is visible
+    // EstimatedBandwidth of the decisions (scheduler.go:656-692): it depends only on link data that commits never change, so
+    // it stays off the per-workload path and one CTA fills it in for the whole queue here.
+    if (rank == 0)
+        for (uint32_t p = (uint32_t)tid; p < n_pods; p += (uint32_t)T) {
+            const uint32_t nd = out[p].node_idx;
+            if (nd == KGWE_NO_NODE || nd - P.node_base >= n_nodes) continue;
+            const uint32_t order = out[p].order;
+            out[p].est_bandwidth_gbps = est_bandwidth(nodes + (nd - P.node_base), order, (int)((order >> 24) & 15));
+        }
 }
 
 }  // namespace kgwe
