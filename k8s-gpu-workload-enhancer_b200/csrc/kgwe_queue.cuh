@@ -11,11 +11,14 @@
 //   also completes 4 bytes of the receiving CTA's mbarrier; one lane per warp waits for its own CTA's mbarrier
 //   phase (all <= 16 keys have landed) and every thread reads the one word that now holds the winner's key.
 //   No fence and no cluster-wide barrier inside the loop.
-//   The lane that owns the winning node writes the decision, commits in the image and refreshes its own state.
+//   (the same wait CUTLASS uses for data that arrives with complete_tx: default acquire at CTA scope).
+//   The lane that owns the winning node writes the decision and commits in the image; the state its node has after
+//   the commit was worked out, while the keys were travelling, by the one lane of each CTA that could win.
 // Keys are TotalScore << 14 | (16383 - node): largest score, lowest node index on ties (the canonical order).
 // The greedy winners per group size are memoised per lane and filled lazily: a commit only invalidates the owner's
-// memo, and the next evaluation that needs an entry runs the full search of findBestNVLinkGroup (:376-435) for
-// that size alone.
+// memo, and the next evaluation that needs an entry runs the search of findBestNVLinkGroup (:376-435) for that size
+// alone (on a uniform node the first completed walk, else all starts: every completed walk ties and the first wins).
+// EstimatedBandwidth (:656-692) is filled in for all decisions by one CTA after the loop.
 // Nodes of every link tier are served: the memo fill of a non-uniform node runs the float64 chains on the record
 // itself (the lane variant without matrix columns), which a commit-bound queue can afford.
 // Form limits (the engine falls back to schedule_tile_kernel otherwise): n_nodes <= cluster size x QC_MAX_THREADS
