@@ -546,6 +546,38 @@ def side_measurements(args, torch, dist, kg, orc, eng, scorer, stream, dev, loca
                 xs[i - 100] = (time.perf_counter() - a) * 1e6
         out["prioritize_latency_sharded"] = {"n_nodes": N, "ranks": world, "calls": len(xs), "p50_us": float(np.percentile(xs, 50)), "p99_us": float(np.percentile(xs, 99)),
                                              "path": "kgwe_score_batch(P=1) per shard + NCCL all_gather(32 B) + kgwe_topk_merge_host"}
+        # ... and through the device-resident exchange: pinned pod -> device, kgwe_score_merge_p2p (score, finalise into every rank's
+        # buffer + flags, wait + merge), merged placement -> pinned host
+        one = kg.sharded.ShardedScorer(eng, n_local, world, dist, stream.cuda_stream, rank=rank)
+        one.alloc(torch, dev, 1, 1, with_matrix=False)
+        ok1 = one.enable_p2p(torch, dev, 1) if scorer.p2p is not None else False
+        agree1 = torch.tensor([1 if (ok1 and one.flags is not None) else 0], device=dev)
+        dist.all_reduce(agree1, op=dist.ReduceOp.MIN)
+        if int(agree1.item()) == 1:
+            h_one = torch.empty((1, abi.POD_REQ.itemsize), dtype=torch.uint8).pin_memory()
+            d_one = torch.empty((1, abi.POD_REQ.itemsize), dtype=torch.uint8, device=dev)
+            h_res = torch.empty((1, itp), dtype=torch.uint8).pin_memory()
+            src = pods.view(np.uint8).reshape(P, abi.POD_REQ.itemsize)
+            same = True
+            for i in range(700):
+                dist.barrier()
+                a = time.perf_counter()
+                h_one.numpy()[0] = src[i % P]
+                d_one.copy_(h_one, non_blocking=True)
+                m = one.step(d_one)
+                h_res.copy_(m.view(1, itp), non_blocking=True)
+                stream.synchronize()
+                if i >= 100:
+                    xs[i - 100] = (time.perf_counter() - a) * 1e6
+                if i < 16:      # the same answer as the host-merged path
+                    _, t1 = eng.score_batch(pods[i % P:i % P + 1], n_local, want_scores=False, topk=1)
+                    mine = torch.from_numpy(t1.view(np.uint8).reshape(itp)).to(dev)
+                    dist.all_gather_into_tensor(gathered, mine)
+                    ref = kg.sharded.merge_host(gathered.cpu().numpy().view(abi.PLACEMENT).reshape(world, 1, 1), 1)
+                    same = same and ref.tobytes() == h_res.numpy().tobytes()
+            out["prioritize_latency_sharded_device_exchange"] = {"n_nodes": N, "ranks": world, "calls": len(xs), "p50_us": float(np.percentile(xs, 50)), "p99_us": float(np.percentile(xs, 99)),
+                                                                 "agrees_with_host_merge": bool(same),
+                                                                 "path": "pinned pod -> device, kgwe_score_merge_p2p(P=1) (flags over NVLink, no collective), merged placement -> pinned host"}
         return out
 
     def fresh(flags=0, nd=nodes, led=ledger):
