@@ -529,6 +529,25 @@ def side_measurements(args, torch, dist, kg, orc, eng, scorer, stream, dev, loca
                 lat.append(measure(e3, n_small))
                 e3.close()
         out["prioritize_latency"] = lat
+        # one Schedule() per call (kgwe_schedule_queue with ONE workload: score on the latency path, pick, record the allocation;
+        # the next call publishes the changed record): the reference's entry point, scheduler.go:114-179
+        e4 = kg.Engine(max_nodes=N, device=local_rank)
+        e4.upsert_nodes(nodes); e4.seed_ledger(ledger)
+        fnq, h4 = e4.lib.kgwe_schedule_queue, e4.h
+        outq = np.zeros(1, dtype=abi.PLACEMENT)
+        calls = min(3000, P - 200)
+        ptrs = [pods[i:i + 1].ctypes.data for i in range(200 + calls)]      # every workload UID once
+        for i in range(200):
+            fnq(h4, ptrs[i], 1, None, outq.ctypes.data)
+        xs = np.empty(calls)
+        for i in range(calls):
+            a = time.perf_counter()
+            rc = fnq(h4, ptrs[200 + i], 1, None, outq.ctypes.data)
+            xs[i] = (time.perf_counter() - a) * 1e6
+            assert rc == 0
+        out["schedule_latency"] = {"n_nodes": N, "calls": calls, "warmup_calls": 200, "p50_us": float(np.percentile(xs, 50)), "p99_us": float(np.percentile(xs, 99)), "max_us": float(xs.max()),
+                                   "call": "kgwe_schedule_queue(1 workload): Schedule() with its commit, one call per workload"}
+        e4.close()
     else:
         # the same per-pod Prioritize over the node shards: local top-1 on every rank, one 32-byte all-gather, identical merge
         itp = abi.PLACEMENT.itemsize

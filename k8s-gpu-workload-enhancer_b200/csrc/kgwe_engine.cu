@@ -711,6 +711,48 @@ int kgwe_score_merge_p2p(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_
     return note_use(e, s);
 }
 
+// Latency path (per-pod Prioritize, and Schedule of a single workload): no copy operations at all.  Pod descriptors, hint rows
+// and placements live in pinned host memory, which the kernel reads and writes directly over PCIe (unified addressing; up to
+// four descriptors travel in the kernel parameters): ONE launch, the last CTA to finish turns the keys into placements and
+// raises a flag in pinned memory that the host spins on.  n_pods <= 32.
+static int latency_top1(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, const uint8_t* hint, kgwe_placement* out_topk, cudaStream_t s) {
+    const uint32_t row = hint_row_bytes(e);
+    int rc;
+    CU(e, e->h_pods.ensure(32)); CU(e, e->h_topk.ensure(32));
+    if (hint) CU(e, e->h_hint.ensure((size_t)32 * row));
+    memcpy(e->h_pods.p, pods, (size_t)n_pods * sizeof(kgwe_pod_req));
+    if (hint) memcpy(e->h_hint.p, hint, (size_t)n_pods * row);
+    rc = launch_score(e, e->h_pods.p, n_pods, hint ? e->h_hint.p : nullptr, nullptr, 1, e->h_topk.p, s, false, true);
+    if (rc != KGWE_OK) return rc;
+    // wait for the kernel's flag in pinned memory instead of a stream synchronisation; look at the
+    // stream now and then so a failed launch cannot spin forever
+    volatile unsigned int* flag = e->h_flag;
+    const auto t0 = std::chrono::steady_clock::now();
+    const char* trouble = nullptr; cudaError_t q = cudaSuccess;
+    for (uint32_t spins = 0; *flag != e->flag_seq; ++spins) {
+        if ((spins & 0x3fff) == 0x3fff) {
+            q = cudaStreamQuery(s);
+            if (q == cudaSuccess) { if (*flag != e->flag_seq) trouble = "kernel finished without raising its flag"; break; }
+            if (q != cudaErrorNotReady) { trouble = cudaGetErrorString(q); break; }
+            if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > 5.0) { trouble = "no answer from the GPU after 5 s"; break; }
+        }
+    }
+    if (trouble) {
+        // leave the ticket counter of the fused tail at zero for the next call, whatever state the launch ended in
+        cudaStreamSynchronize(s);
+        cudaMemsetAsync(e->d_done, 0, sizeof(unsigned int), s);
+        cudaStreamSynchronize(s);
+        cudaGetLastError();
+        return fail(e, KGWE_ERR_CUDA, "latency path: %s (flag %u, expected %u)", trouble, *flag, e->flag_seq);
+    }
+    rc = note_use(e, s);
+    if (rc != KGWE_OK) return rc;
+    memcpy(out_topk, e->h_topk.p, (size_t)n_pods * sizeof(kgwe_placement));
+    e->stats.h2d_bytes += (uint64_t)n_pods * sizeof(kgwe_pod_req) + (hint ? (uint64_t)n_pods * row : 0);
+    e->stats.d2h_bytes += (uint64_t)n_pods * sizeof(kgwe_placement);
+    return KGWE_OK;
+}
+
 int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, const uint8_t* hint,
                      kgwe_node_score* out_scores, uint32_t topk, kgwe_placement* out_topk) {
     if (!e) return KGWE_ERR_INVALID_ARG;
@@ -732,40 +774,8 @@ int kgwe_score_batch(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, 
     const uint32_t row = hint_row_bytes(e);
     const bool need_matrix = out_scores || topk > 1;
     if (!need_matrix && topk == 1 && n_pods <= 32 && !(e->cfg.flags & KGWE_CFG_SUBSET_TABLES)) {
-        // Latency path (per-pod Prioritize): no copy operations at all.  Pod descriptors, hint rows and
-        // placements live in pinned host memory, which the kernels read and write directly over PCIe
-        // (unified addressing): two launches and one stream synchronisation per call.
-        CU(e, e->h_pods.ensure(32)); CU(e, e->h_topk.ensure(32));
-        if (hint) CU(e, e->h_hint.ensure((size_t)32 * row));
-        memcpy(e->h_pods.p, pods, (size_t)n_pods * sizeof(kgwe_pod_req));
-        if (hint) memcpy(e->h_hint.p, hint, (size_t)n_pods * row);
-        rc = launch_score(e, e->h_pods.p, n_pods, hint ? e->h_hint.p : nullptr, nullptr, 1, e->h_topk.p, s, false, true);
+        rc = latency_top1(e, pods, n_pods, hint, out_topk, s);
         if (rc != KGWE_OK) return rc;
-        // wait for the kernel's flag in pinned memory instead of a stream synchronisation; look at the
-        // stream now and then so a failed launch cannot spin forever
-        volatile unsigned int* flag = e->h_flag;
-        const auto t0 = std::chrono::steady_clock::now();
-        const char* trouble = nullptr; cudaError_t q = cudaSuccess;
-        for (uint32_t spins = 0; *flag != e->flag_seq; ++spins) {
-            if ((spins & 0x3fff) == 0x3fff) {
-                q = cudaStreamQuery(s);
-                if (q == cudaSuccess) { if (*flag != e->flag_seq) trouble = "kernel finished without raising its flag"; break; }
-                if (q != cudaErrorNotReady) { trouble = cudaGetErrorString(q); break; }
-                if (std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count() > 5.0) { trouble = "no answer from the GPU after 5 s"; break; }
-            }
-        }
-        if (trouble) {
-            // leave the ticket counter of the fused tail at zero for the next call, whatever state the launch ended in
-            cudaStreamSynchronize(s);
-            cudaMemsetAsync(e->d_done, 0, sizeof(unsigned int), s);
-            cudaStreamSynchronize(s);
-            cudaGetLastError();
-            return fail(e, KGWE_ERR_CUDA, "latency path: %s (flag %u, expected %u)", trouble, *flag, e->flag_seq);
-        }
-        note_use(e, s);
-        memcpy(out_topk, e->h_topk.p, (size_t)n_pods * sizeof(kgwe_placement));
-        e->stats.h2d_bytes += (uint64_t)n_pods * sizeof(kgwe_pod_req) + (hint ? (uint64_t)n_pods * row : 0);
-        e->stats.d2h_bytes += (uint64_t)n_pods * sizeof(kgwe_placement);
         timer.done(false);
         return KGWE_OK;
     }
@@ -972,6 +982,26 @@ int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pod
     if (n_pods == 0) return KGWE_OK;
     if (e->n_nodes == 0) {
         for (uint32_t i = 0; i < n_pods; ++i) { no_node(out[i], 0); e->stats.failed++; }
+        return KGWE_OK;
+    }
+    if (n_pods == 1 && !(e->cfg.flags & KGWE_CFG_SUBSET_TABLES)) {
+        // One Schedule() call (scheduler.go:114-179): score on the latency path (one launch, no copies), then record the
+        // allocation on the host exactly as kgwe_alloc_commit would - the same UID overwrites its previous entry AFTER the
+        // workload was scored against it (:699) - and let the next call publish the changed record(s).
+        cudaStream_t s1 = e->stream;
+        rc = flush_dirty(e, s1);
+        if (rc != KGWE_OK) return rc;
+        rc = latency_top1(e, pods, 1, hint, out, s1);
+        if (rc != KGWE_OK) return rc;
+        if (out[0].node_idx == KGWE_NO_NODE) e->stats.failed++;
+        else {
+            e->stats.scheduled++;
+            if (out[0].topology >= 80) e->stats.topology_optimal++;
+            wait_copy(e);
+            ledger_apply(e, pods[0].wl_id, out[0].node_idx - e->cfg.node_base, out[0].gpu_mask, true);
+        }
+        e->stats.last_call_gpu_ms = 0.0;
+        timer.done(true);
         return KGWE_OK;
     }
     const uint32_t row = hint_row_bytes(e);
