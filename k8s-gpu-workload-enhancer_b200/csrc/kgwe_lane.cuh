@@ -535,11 +535,25 @@ __device__ __forceinline__ void lane_evaluate(const LaneNode& ln, const LaneTabs
     r.kept_total = kept ? (uint32_t)total : 0u;
 }
 
-// Memoised winners of this lane's node for k = 2..8 (K1_MODE_MEMO), by the full search: (TopologyScore or -1,
+// What the pods of a chunk need from the per-node tables (a bit set, OR-ed over the chunk): bit k (2..8) = an NVLink pod with
+// GPUCount k (NVLink score of the uniform node / memoised winner for that k), NEED_GROUPS = a SameNUMA / SamePCIeSwitch pod,
+// NEED_MIG = a pod with MIG requirements.  A single-pod call builds one table entry instead of seven.
+constexpr uint32_t NEED_GROUPS = 1u << 9, NEED_MIG = 1u << 10, NEED_ALL = 0xffffffffu;
+__device__ __forceinline__ uint32_t pod_needs(const PodLite& pl) {
+    uint32_t n = 0;
+    const uint32_t k = pl.pk & 0xffu;
+    if ((pl.pk & PL_NVLINK) && k >= 2u && k <= 8u) n |= 1u << k;
+    if (pl.pk & (PL_NUMA | PL_PCIE)) n |= NEED_GROUPS;
+    if (pl.pk & PL_MIG) n |= NEED_MIG;
+    return n;
+}
+
+// Memoised winners of this lane's node for the needed k in 2..8 (K1_MODE_MEMO), by the full search: (TopologyScore or -1,
 // join order | GPU set << 24).
 template <bool GENERAL>
-__device__ __noinline__ void lane_memo_build(const LaneNode& ln, const LaneTabs& tb, const DevNode* rec, double norm) {
+__device__ __noinline__ void lane_memo_build(const LaneNode& ln, const LaneTabs& tb, const DevNode* rec, double norm, uint32_t needs) {
     for (int k = 2; k <= 8; ++k) {
+        if (!(needs >> k & 1u)) continue;
         int topo = -1; uint32_t sel = 0, order = 0, sc = 0;
         if (ln.valid && ln.A >= k) lane_group_search<GENERAL>(ln, tb, rec, k, norm, K1_MODE_FULL, topo, sel, order, sc);
         tb.memo[(k - 2) * tb.stride] = make_int2(topo, (int)(order | (sel << 24)));
@@ -549,16 +563,21 @@ __device__ __noinline__ void lane_memo_build(const LaneNode& ln, const LaneTabs&
 // Everything a lane keeps about its node beyond LaneNode: tables in the shared-memory columns.
 template <bool GENERAL, bool TABLES>
 __device__ inline void lane_tables_build(const LaneNode& ln, const NodeCtx& c, const LaneTabs& tb, const DevNode* rec, double norm,
-                                         uint32_t mode, const uint16_t* slot_of) {
+                                         uint32_t mode, const uint16_t* slot_of, uint32_t needs = NEED_ALL) {
     const int S = tb.stride;
     if (ln.tier == TIER_UNIFORM) {                       // uniform_topo_build, into the lane's column
         const double u = node_uniform_bw(rec, node_uniform_code(rec));
         double Sm = 0.0, T = 0.0;
-        for (int k = 2; k <= 8; ++k) { Sm = __dadd_rn(Sm, u); T = __dadd_rn(T, Sm); tb.topo[(k - 2) * S] = nvlink_score(T, k, norm); }
+        for (int k = 2; k <= 8; ++k) {
+            Sm = __dadd_rn(Sm, u); T = __dadd_rn(T, Sm);
+            if (needs >> k & 1u) tb.topo[(k - 2) * S] = nvlink_score(T, k, norm);
+        }
     }
-    tb.grp[0] = (uint32_t)c.numa_pick; tb.grp[S] = (uint32_t)(c.numa_pick >> 32); tb.grp[2 * S] = c.numa_order;
-    tb.grp[3 * S] = (uint32_t)c.pcie_pick; tb.grp[4 * S] = (uint32_t)(c.pcie_pick >> 32); tb.grp[5 * S] = c.pcie_order;
-    if (ln.valid) {
+    if (needs & NEED_GROUPS) {
+        tb.grp[0] = (uint32_t)c.numa_pick; tb.grp[S] = (uint32_t)(c.numa_pick >> 32); tb.grp[2 * S] = c.numa_order;
+        tb.grp[3 * S] = (uint32_t)c.pcie_pick; tb.grp[4 * S] = (uint32_t)(c.pcie_pick >> 32); tb.grp[5 * S] = c.pcie_order;
+    }
+    if (ln.valid && (needs & NEED_MIG)) {
         uint32_t w[3] = {0, 0, 0};
         for (int i = 0; i < KGWE_MIG_PROFILES; ++i) w[i >> 2] |= (uint32_t)rec->mig_free[i] << (8 * (i & 3));
         tb.mig[0] = w[0]; tb.mig[S] = w[1]; tb.mig[2 * S] = w[2];
@@ -568,7 +587,7 @@ __device__ inline void lane_tables_build(const LaneNode& ln, const NodeCtx& c, c
         else if (ln.tier == TIER_F64) lane_mat_build_f64(tb, rec);
     }
     if (TABLES) lane_subset_build(tb, ln, c.colact, slot_of);
-    if (mode == K1_MODE_MEMO) lane_memo_build<GENERAL>(ln, tb, rec, norm);
+    if (mode == K1_MODE_MEMO) lane_memo_build<GENERAL>(ln, tb, rec, norm, needs);
 }
 
 }  // namespace kgwe

@@ -68,16 +68,18 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     __shared__ kgwe_pod_req inline_copy[4];
     if (tid < (int)tail.n_inline) inline_copy[tid] = tail.inline_pods[tid];
     const kgwe_pod_req* spods = tail.n_inline ? inline_copy : nullptr;
-    if (tail.n_inline) __syncthreads();
 
-    // ---- set-up 1: pod chunk -> PodLite ----
-    bool want_groups = false;
+    // ---- set-up 1: pod chunk -> PodLite, and what the chunk needs from the per-node tables ----
+    __shared__ uint32_t cta_needs;
+    if (tid == 0) cta_needs = 0u;
+    __syncthreads();
+    uint32_t needs = 0;
     for (uint32_t i = tid; i < np; i += K1_THREADS) {
         const kgwe_pod_req pod = load_pod2(pods, spods, p_begin + i);
         const PodLite pl = pod_lite(pod);
         spod[i] = pl;
         if (i == np - 1) spod[np] = pl;
-        want_groups |= (pl.pk & (PL_NUMA | PL_PCIE)) != 0;      // the group tables are only worth building when a pod asks for them
+        needs |= pod_needs(pl);
     }
     if (TABLES)      // slot of mask m in (popcount, value) order
         for (int m = tid; m < 256; m += K1_THREADS) {
@@ -85,7 +87,11 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
             for (int q = 0; q < m; ++q) rank += __popc(q) == __popc(m);
             slot_of[m] = (uint16_t)(subset_off(__popc(m)) + rank);
         }
-    want_groups = __syncthreads_or(want_groups);
+    needs = __reduce_or_sync(0xffffffffu, needs);
+    if (lane == 0 && needs) atomicOr(&cta_needs, needs);
+    __syncthreads();
+    needs = cta_needs;
+    const bool want_groups = (needs & NEED_GROUPS) != 0u;
 
     // ---- set-up 2: this lane's node ----
     const uint32_t node = tile_first + tid;
@@ -105,7 +111,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         node_ctx_core(c, rec, in_range);
         if (want_groups) node_ctx_group_tables(c, rec);
         lane_node_init(ln, c, rec, GENERAL ? mat_units : 0u);
-        lane_tables_build<GENERAL, TABLES>(ln, c, tb, rec, P.norm, mode, slot_of);
+        lane_tables_build<GENERAL, TABLES>(ln, c, tb, rec, P.norm, mode, slot_of, needs);
     }
     __syncthreads();
 
