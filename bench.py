@@ -594,6 +594,34 @@ def side_measurements(args, torch, dist, kg, orc, eng, scorer, stream, dev, loca
                     dist.all_gather_into_tensor(gathered, mine)
                     ref = kg.sharded.merge_host(gathered.cpu().numpy().view(abi.PLACEMENT).reshape(world, 1, 1), 1)
                     same = same and ref.tobytes() == h_res.numpy().tobytes()
+            # the stateful queue over the node shards, exchanged on the device (kgwe_schedule_queue_p2p): one 64-bit word per workload
+            # and rank through peer-mapped memory, the owner of the winning node commits
+            try:
+                eq = kg.Engine(max_nodes=n_local, device=local_rank, node_base=lo)
+                eq.upsert_nodes(nodes[lo:hi])
+                for a_ in ledger:
+                    if lo <= a_["node_idx"] < hi:
+                        eq.commit(a_["wl_id"], a_["node_idx"] - lo, a_["gpu_mask"])
+                sq = kg.sharded.ShardedQueue(eq, world, rank, dist, torch, dev)
+                nq = min(P, 4000)
+                sq.schedule(pods[:64])
+                dist.barrier()
+                a = time.perf_counter()
+                mine_q = sq.schedule(pods[64:64 + nq])
+                wq = time.perf_counter() - a
+                gq = eq.stats()["last_call_gpu_ms"]
+                allq = sq.merged(mine_q)
+                o_q = orc.schedule_queue(abi, nodes, ledger, pods[:64 + 200])[0][64:] if rank == 0 else None
+                tq = torch.tensor([gq], dtype=torch.float64, device=dev)
+                dist.all_reduce(tq, op=dist.ReduceOp.MAX)
+                out["stateful_queue_sharded_device_exchange"] = {
+                    "pods": nq, "ranks": world, "gpu_ms_max_over_ranks": float(tq.item()), "us_per_pod": float(tq.item()) * 1e3 / nq, "wall_ms_rank0": wq * 1e3,
+                    "placed": int((allq["node_idx"] != abi.NO_NODE).sum()),
+                    "first_200_equal_the_oracle": bool(o_q is not None and allq[:200].tobytes() == o_q.tobytes()),
+                    "call": "kgwe_schedule_queue_p2p on every rank: the queue kernels exchange score and node through peer-mapped memory per workload"}
+                eq.close()
+            except Exception as ex:      # noqa: BLE001 - reported, never fatal for the bench line
+                out["stateful_queue_sharded_device_exchange"] = {"unavailable": repr(ex)[:200]}
             out["prioritize_latency_sharded_device_exchange"] = {"n_nodes": N, "ranks": world, "calls": len(xs), "p50_us": float(np.percentile(xs, 50)), "p99_us": float(np.percentile(xs, 99)),
                                                                  "agrees_with_host_merge": bool(same),
                                                                  "path": "pinned pod -> device, kgwe_score_merge_p2p(P=1) (flags over NVLink, no collective), merged placement -> pinned host"}

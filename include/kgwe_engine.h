@@ -39,7 +39,7 @@
 extern "C" {
 #endif
 
-#define KGWE_ABI_VERSION   3     /* bumped whenever an entry point or a struct of this header changes; kgwe_version() ends in "abi <n>" */
+#define KGWE_ABI_VERSION   4     /* bumped whenever an entry point or a struct of this header changes; kgwe_version() ends in "abi <n>" */
 #define KGWE_MAX_GPUS      8     /* GPUs per node record (all BASELINE configs use 8) */
 #define KGWE_MIG_PROFILES  10    /* CRD whitelist, src/sharing/mig_controller.go:273-284 */
 #define KGWE_MAX_TOPK      16
@@ -354,6 +354,22 @@ int kgwe_topk_merge_host(const kgwe_placement* lists, uint32_t n_lists, uint32_t
  * "no eligible nodes found for workload" (scheduler.go:140). */
 int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods,
                         const uint8_t* hint_bitmap, kgwe_placement* out);
+
+/* The same queue over a node-sharded cluster, on the device ("the owner rank applies the commit"; no
+ * counterpart in the reference, whose scheduler is one process).  Every rank - one engine, one GPU, one shard with its
+ * kgwe_config.node_base - makes this call with the SAME workloads at about the same time.  Per workload each rank's queue
+ * kernel finds its shard's best node, the ranks exchange one 64-bit word (score and global node index) through peer-mapped
+ * memory, and the rank that owns the overall winner commits it: out[i] holds the decision on that rank and
+ * node_idx = KGWE_NO_NODE on the others (and on all of them when no node in the cluster takes the workload).
+ *   peer_recv_bufs[r]  address, on rank r, of n_ranks x 4 uint64, zero before the first call (host array of n_ranks device
+ *                      addresses, e.g. the buffer_ptrs of a torch symmetric-memory allocation)
+ *   seq_base           number of workloads all earlier calls on these buffers have scheduled, modulo 2^24 - 1: the same on
+ *                      every rank
+ * Limits: 2..8 ranks, a shard of at most 10,240 nodes, global node indices below 2^22, workload ids not yet in any rank's
+ * ledger (kgwe_alloc_release first).  A rank whose peers do not answer within about ten seconds fails with KGWE_ERR_CUDA. */
+int kgwe_schedule_queue_p2p(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, const uint8_t* hint_bitmap,
+                            const uint64_t* peer_recv_bufs, uint32_t n_ranks, uint32_t my_rank, uint32_t seq_base,
+                            kgwe_placement* out);
 
 /* EXTENSION E5 - gang scheduling (GangSchedulingGroup exists only as a type in the reference,
  * src/scheduler/types.go:415-444; Schedule places a workload's GPUs on ONE node, so an FSDP

@@ -94,6 +94,7 @@ ENGINE_SYMBOLS = [
     "kgwe_schedule_gangs", "kgwe_placement_terms", "kgwe_mig_pack", "kgwe_mig_rebalance",
     "kgwe_topology_hint_batch", "kgwe_topology_gauges", "kgwe_score_batch_device_p2p",
     "kgwe_snapshot_size", "kgwe_snapshot_save", "kgwe_snapshot_load", "kgwe_node_upsert_remap", "kgwe_score_merge_p2p", "kgwe_mig_reconfigure",
+    "kgwe_schedule_queue_p2p",
 ]
 NOALLOC_MAX_PODS = 16384
 
@@ -139,6 +140,7 @@ def load_engine_lib():
     lib.kgwe_topk_merge_host.argtypes = [vp, u32, u32, u32, vp]
     lib.kgwe_topk_merge_device.argtypes = [vp, vp, u32, u32, u32, vp, vp]
     lib.kgwe_schedule_queue.argtypes = [vp, vp, u32, vp, vp]
+    lib.kgwe_schedule_queue_p2p.argtypes = [vp, vp, u32, vp, vp, u32, u32, u32, vp]
     lib.kgwe_node_read.argtypes = [vp, u32, vp]
     lib.kgwe_get_stats.argtypes = [vp, C.POINTER(Stats)]
     lib.kgwe_last_error.argtypes = [vp]

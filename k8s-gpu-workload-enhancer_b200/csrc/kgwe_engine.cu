@@ -463,11 +463,15 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
         const char* form = getenv("KGWE_QUEUE_FORM");      // "tile" keeps the grid-wide kernels (A/B runs, tests)
         std::vector<uint64_t> pf(256); std::vector<uint32_t> od(256);
         qc_first_tables(pf.data(), od.data());
-        if (!(form && !strcmp(form, "tile")) && cudaFuncSetAttribute(schedule_cluster_kernel<QC_MAX_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) == cudaSuccess
-            && cudaFuncSetAttribute(schedule_cluster_kernel<QC_SMALL_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qc_layout(QC_SMALL_THREADS).total) == cudaSuccess
+        if (!(form && !strcmp(form, "tile")) && cudaFuncSetAttribute(schedule_cluster_kernel<QC_MAX_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) == cudaSuccess
+            && cudaFuncSetAttribute(schedule_cluster_kernel<QC_MAX_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) == cudaSuccess
+            && cudaFuncSetAttribute(schedule_cluster_kernel<QC_SMALL_THREADS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qc_layout(QC_SMALL_THREADS).total) == cudaSuccess
+            && cudaFuncSetAttribute(schedule_cluster_kernel<QC_SMALL_THREADS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)qc_layout(QC_SMALL_THREADS).total) == cudaSuccess
             && cudaMemcpyToSymbol(qc_prefix_lut, pf.data(), 256 * sizeof(uint64_t)) == cudaSuccess && cudaMemcpyToSymbol(qc_order_lut, od.data(), 256 * sizeof(uint32_t)) == cudaSuccess) {
-            cudaFuncSetAttribute(schedule_cluster_kernel<QC_MAX_THREADS>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-            cudaFuncSetAttribute(schedule_cluster_kernel<QC_SMALL_THREADS>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            cudaFuncSetAttribute(schedule_cluster_kernel<QC_MAX_THREADS, false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            cudaFuncSetAttribute(schedule_cluster_kernel<QC_SMALL_THREADS, false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            cudaFuncSetAttribute(schedule_cluster_kernel<QC_MAX_THREADS, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            cudaFuncSetAttribute(schedule_cluster_kernel<QC_SMALL_THREADS, true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
             for (int c = QC_MAX_CTAS; c >= 1 && !e->qc_max_ctas; c >>= 1) {
                 cudaLaunchConfig_t lc = {};
                 lc.gridDim = dim3(c); lc.blockDim = dim3(QC_MAX_THREADS); lc.dynamicSmemBytes = smem;
@@ -475,7 +479,7 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
                 at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = c; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
                 lc.attrs = at; lc.numAttrs = 1;
                 int n = 0;
-                if (cudaOccupancyMaxActiveClusters(&n, schedule_cluster_kernel<QC_MAX_THREADS>, &lc) == cudaSuccess && n >= 1) e->qc_max_ctas = c;
+                if (cudaOccupancyMaxActiveClusters(&n, schedule_cluster_kernel<QC_MAX_THREADS, true>, &lc) == cudaSuccess && n >= 1) e->qc_max_ctas = c;
             }
         }
         cudaGetLastError();
@@ -872,7 +876,8 @@ static bool queue_cluster_form(const kgwe_engine* e) {
 }
 
 // gang_of (host, np entries, nullable): all-or-nothing gangs decided on the device (cluster and tile forms only).
-static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t np, const uint8_t* hint_rows, double* gpu_ms, const uint32_t* gang_of = nullptr) {
+static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t np, const uint8_t* hint_rows, double* gpu_ms, const uint32_t* gang_of = nullptr,
+                             const QcPeers* peers = nullptr) {
     cudaStream_t s = e->stream;
     const uint32_t N = e->n_nodes, row = hint_row_bytes(e);
     int rc = flush_dirty(e, s);
@@ -924,8 +929,12 @@ static int run_queue_segment(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t 
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = ctas; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         lc.attrs = at; lc.numAttrs = 1;
-        if (threads == (uint32_t)QC_SMALL_THREADS) CU(e, cudaLaunchKernelEx(&lc, schedule_cluster_kernel<QC_SMALL_THREADS>, d_nodes, n_nodes, d_pods, npods, d_hint, rowb, d_out, prm, ctr, d_gang));
-        else CU(e, cudaLaunchKernelEx(&lc, schedule_cluster_kernel<QC_MAX_THREADS>, d_nodes, n_nodes, d_pods, npods, d_hint, rowb, d_out, prm, ctr, d_gang));
+        const QcPeers pq = peers ? *peers : QcPeers{};
+        if (peers) {
+            if (threads == (uint32_t)QC_SMALL_THREADS) CU(e, cudaLaunchKernelEx(&lc, schedule_cluster_kernel<QC_SMALL_THREADS, true>, d_nodes, n_nodes, d_pods, npods, d_hint, rowb, d_out, prm, ctr, d_gang, pq));
+            else CU(e, cudaLaunchKernelEx(&lc, schedule_cluster_kernel<QC_MAX_THREADS, true>, d_nodes, n_nodes, d_pods, npods, d_hint, rowb, d_out, prm, ctr, d_gang, pq));
+        } else if (threads == (uint32_t)QC_SMALL_THREADS) CU(e, cudaLaunchKernelEx(&lc, schedule_cluster_kernel<QC_SMALL_THREADS, false>, d_nodes, n_nodes, d_pods, npods, d_hint, rowb, d_out, prm, ctr, d_gang, pq));
+        else CU(e, cudaLaunchKernelEx(&lc, schedule_cluster_kernel<QC_MAX_THREADS, false>, d_nodes, n_nodes, d_pods, npods, d_hint, rowb, d_out, prm, ctr, d_gang, pq));
     } else if (queue_tile_form(e)) {
         // every node gets its own lane group: tile form (shared-memory resident tables)
         CU(e, cudaLaunchCooperativeKernel((const void*)schedule_tile_kernel, dim3(n_tiles), dim3(SCORE_THREADS), targs, sched_tile_smem_bytes(), s));
@@ -1039,6 +1048,47 @@ int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pod
             for (uint32_t nd : {old_node, local}) { recount_node(e, nd); mark_dirty(e, nd); }
         }
         p0 = p1;
+    }
+    e->stats.last_call_gpu_ms = gpu_ms;
+    timer.done(true);
+    return KGWE_OK;
+}
+
+// The stateful queue over a node-sharded cluster, on the device: every rank (one engine = one GPU = one shard) makes this
+// call with the same workloads; the queue kernels of the ranks exchange one 64-bit word per workload through peer-mapped
+// memory (kgwe_queue.cuh) and the rank that owns the winning node commits it.
+int kgwe_schedule_queue_p2p(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, const uint8_t* hint,
+                            const uint64_t* peer_recv_bufs, uint32_t n_ranks, uint32_t my_rank, uint32_t seq_base, kgwe_placement* out) {
+    if (!e) return KGWE_ERR_INVALID_ARG;
+    std::lock_guard<std::mutex> lk(e->mu);
+    if (!peer_recv_bufs || n_ranks < 2 || n_ranks > 8 || my_rank >= n_ranks || seq_base >= QC_SEQ_MOD || (n_pods && (!pods || !out)) || n_pods > (1u << 20))
+        return fail(e, KGWE_ERR_INVALID_ARG, "bad arguments (2..8 ranks, seq_base < 2^24 - 1, at most 2^20 workloads per call)");
+    CallTimer timer(e, n_pods);
+    int rc = validate_pods(e, pods, n_pods);
+    if (rc != KGWE_OK) return rc;
+    {
+        std::unordered_map<uint64_t, int> seen;
+        for (uint32_t i = 0; i < n_pods; ++i) {
+            if (e->ledger.count(pods[i].wl_id) || seen.count(pods[i].wl_id)) return fail(e, KGWE_ERR_INVALID_ARG, "pod %u: workload id already scheduled (release it on every rank first)", i);
+            seen[pods[i].wl_id] = 1;
+        }
+    }
+    CU(e, cudaSetDevice(e->cfg.device));
+    if (n_pods == 0) return KGWE_OK;
+    if (e->n_nodes == 0) return fail(e, KGWE_ERR_INVALID_ARG, "the cluster image of this shard is empty");
+    if (!queue_cluster_form(e) || e->max_total >= (1ll << 17) || (uint64_t)e->cfg.node_base + e->n_nodes > (1ull << 22))
+        return fail(e, KGWE_ERR_TOO_LARGE, "the sharded queue needs a shard of at most %u nodes, TotalScore below 2^17 and global node indices below 2^22",
+                    (unsigned)(e->qc_max_ctas * QC_MAX_THREADS));
+    QcPeers pq{};
+    for (uint32_t r = 0; r < n_ranks; ++r) pq.recv[r] = reinterpret_cast<unsigned long long*>(peer_recv_bufs[r]);
+    pq.n_ranks = n_ranks; pq.my_rank = my_rank; pq.seq_base = seq_base;
+    double gpu_ms = 0.0;
+    rc = run_queue_segment(e, pods, n_pods, hint, &gpu_ms, nullptr, &pq);
+    if (rc != KGWE_OK) return rc;
+    for (uint32_t i = 0; i < n_pods; ++i) {
+        const kgwe_placement& d = e->h_topk.p[i];
+        out[i] = d;
+        if (d.node_idx != KGWE_NO_NODE) apply_commit(e, pods[i].wl_id, d);      // (a workload placed on another rank, or nowhere, leaves this shard as it was)
     }
     e->stats.last_call_gpu_ms = gpu_ms;
     timer.done(true);

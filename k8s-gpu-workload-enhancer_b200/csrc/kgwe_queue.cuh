@@ -49,7 +49,7 @@ __host__ __device__ inline QcLayout qc_layout(uint32_t threads) {
     L.mig = o; o += 3u * threads * 4u;
     L.wkeys = o; o += 2u * 32u * 4u;                                   // warp keys of even / odd workloads
     L.ckeys = o; o += 2u * QC_MAX_CTAS * 4u;
-    L.bars = o; o += 2u * 8u;
+    L.bars = o; o += 4u * 8u;                                         // keys of even / odd workloads: inside the cluster, between the ranks
     L.spec = o; o += 16u * 4u;                                        // the CTA's best lane parks its would-be state here
     L.total = o;
     return L;
@@ -64,6 +64,29 @@ __device__ __forceinline__ uint32_t qc_map_to_cta(uint32_t smem_addr, uint32_t r
 __device__ __forceinline__ void qc_max_signal(uint32_t cluster_addr, uint32_t v, uint32_t cluster_mbar) {
     asm volatile("red.async.relaxed.cluster.mbarrier::complete_tx::bytes.shared::cluster.max.u32 [%0], %1, [%2];" ::"r"(cluster_addr), "r"(v), "r"(cluster_mbar) : "memory");
 }
+// One 32-bit store into another CTA's shared memory that completes 4 bytes of that CTA's mbarrier.
+__device__ __forceinline__ void qc_store_signal(uint32_t cluster_addr, uint32_t v, uint32_t cluster_mbar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.u32 [%0], %1, [%2];" ::"r"(cluster_addr), "r"(v), "r"(cluster_mbar) : "memory");
+}
+
+// Node-sharded queue (kgwe_schedule_queue_p2p): every rank runs this kernel on its shard of the cluster, one rank per
+// GPU, and after the arg-max inside its cluster the ranks exchange ONE 64-bit word per workload through peer-mapped
+// memory: tag << 40 | TotalScore << 22 | (2^22 - 1 - global node), written with a single 64-bit system-scope store into slot
+// [sender][tag & 3] of every peer's receive array and polled there until the tag is the expected one (relaxed accesses: the
+// word is the whole message, no other data rides on it).
+// tag = the workload's sequence number (1 .. 2^24 - 1, running on across calls, the same on every rank): a slot only ever
+// sees increasing tags, so a stale word cannot be taken for a fresh one, and a rank can be at most one workload ahead
+// of a peer (it needs that peer's word to go on), so four slots per sender are more than enough.
+struct QcPeers {
+    unsigned long long* recv[8];   // recv[r]: the receive array of rank r ([n_ranks][4] 64-bit words, zero before the first call)
+    uint32_t n_ranks, my_rank;
+    uint32_t seq_base;             // sequence number of this call's first workload, 0 .. 2^24 - 2
+    uint32_t pad;
+};
+constexpr uint32_t QC_PLACED_ELSEWHERE = 0x80000000u;   // what the cluster is told when another rank's node won
+constexpr uint32_t QC_EXCHANGE_FAILED = 0xFFFFFFFFu;    // ... when a peer's word did not arrive in time
+constexpr uint32_t QC_SEQ_MOD = 0xFFFFFFu;
+
 __device__ __forceinline__ void qc_cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
 __device__ __forceinline__ void qc_cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 // Wait for `phase` of a local mbarrier whose transactions come from other CTAs.  Bounded: a protocol fault must not hang the
@@ -98,11 +121,11 @@ __device__ __noinline__ void qc_groups_fill(uint32_t avail, const uint64_t* st, 
     grp[3 * S] = (uint32_t)pp; grp[4 * S] = (uint32_t)(pp >> 32); grp[5 * S] = po;
 }
 
-template <int T>
+template <int T, bool PEERS>
 __global__ void __launch_bounds__(T, 1)
 schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __restrict__ pods, uint32_t n_pods,
                         const uint8_t* __restrict__ hint, uint32_t hint_row_bytes, kgwe_placement* __restrict__ out,
-                        Params P, unsigned long long* __restrict__ counters, const uint32_t* __restrict__ gang_of) {
+                        Params P, unsigned long long* __restrict__ counters, const uint32_t* __restrict__ gang_of, QcPeers PQ) {
     extern __shared__ __align__(128) unsigned char smem[];
     constexpr int n_warps = T >> 5;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -132,6 +155,8 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bars));
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bars + 8u));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bars + 16u));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bars + 24u));
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     uint32_t allocated = 0, n_allocs = 0;       // this node's ledger projection (scheduler.go:587-593, 562-566), mirrored in the image on every change
@@ -224,14 +249,52 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
         if (!arrived) { if (lane == 0 && counters) atomicAdd(&counters[3], 1ull); break; }      // (every warp of the cluster times out alike)
         uint32_t win;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(win) : "r"(slot) : "memory");
-        if (win == 0u) {
+        if (PEERS) {
+            // `win` is this rank's best.  Warp 0 of CTA 0 speaks for the rank: lane r sends the rank's word to rank r and waits
+            // for rank r's; the outcome goes to every CTA of the cluster the way the keys did (st.async + mbarrier).
+            const uint32_t gslot = ckeys_a + 64u + (p & 3u) * 4u, gbar = bars + 16u + (p & 1u) * 8u;
+            if (tid == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(gbar), "r"(4u) : "memory");
+            if (rank == 0 && tid < 32) {
+                const uint32_t tag = (PQ.seq_base + p) % QC_SEQ_MOD + 1u;
+                const uint32_t gnode = P.node_base + ((QC_MAX_NODES - 1u) - (win & (QC_MAX_NODES - 1u)));
+                const unsigned long long own = win ? (((unsigned long long)(win >> QC_NODE_BITS) << 22) | (unsigned long long)(0x3FFFFFu - gnode)) : 0ull;
+                unsigned long long best = own;
+                bool ok = true;
+                if ((uint32_t)lane < PQ.n_ranks && (uint32_t)lane != PQ.my_rank) {
+                    const unsigned long long word = ((unsigned long long)tag << 40) | own;
+                    unsigned long long* dst = PQ.recv[lane] + (PQ.my_rank * 4u + (tag & 3u));
+                    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(dst), "l"(word) : "memory");      // (the word is the whole message: nothing to release)
+                    const unsigned long long* src = PQ.recv[PQ.my_rank] + ((uint32_t)lane * 4u + (tag & 3u));
+                    unsigned long long v = 0;
+                    const long long t0 = clock64();
+                    for (;;) {
+                        asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(src) : "memory");
+                        if ((uint32_t)(v >> 40) == tag) break;
+                        if (clock64() - t0 > 20000000000ll) { ok = false; break; }      // ~10 s: a rank is gone
+                    }
+                    best = v & 0xFFFFFFFFFFull;
+                }
+#pragma unroll
+                for (int off = 16; off >= 1; off >>= 1) { const unsigned long long o = __shfl_xor_sync(0xffffffffu, best, off); best = o > best ? o : best; }
+                ok = __all_sync(0xffffffffu, ok);
+                const uint32_t gw = !ok ? QC_EXCHANGE_FAILED : best == 0ull ? 0u : best == own ? win : QC_PLACED_ELSEWHERE;
+                if ((uint32_t)lane < C) qc_store_signal(qc_map_to_cta(gslot, (uint32_t)lane), gw, qc_map_to_cta(gbar, (uint32_t)lane));
+            }
+            __syncwarp();
+            arrived = true;
+            if (lane == 0) arrived = qc_wait_phase(gbar, (p >> 1) & 1u);
+            arrived = __shfl_sync(0xffffffffu, arrived, 0);
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(win) : "r"(gslot) : "memory");
+            if (!arrived || win == QC_EXCHANGE_FAILED) { if (lane == 0 && counters) atomicAdd(&counters[3], 1ull); break; }
+        }
+        if (win == 0u || (PEERS && win == QC_PLACED_ELSEWHERE)) {
             if (rank == 0 && tid == 0) {
                 kgwe_placement pl;
                 pl.node_idx = KGWE_NO_NODE; pl.total = 0; pl.topology = pl.resource = pl.balance = 0; pl.gpu_mask = 0; pl.flags = 0;
                 pl.order = 0; pl.reserved = 0; pl.est_bandwidth_gbps = 0.0;
                 out[p] = pl;
             }
-            gang_failed = true;
+            if (win == 0u) gang_failed = true;
         } else if (win == mykey) {
             // this lane owns the winner: tryScheduleOnNode + recordAllocation (scheduler.go:625-653, 695-707)
             const uint32_t mask = (r.w2 >> 16) & 0xffu;

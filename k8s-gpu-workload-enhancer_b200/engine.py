@@ -122,6 +122,17 @@ class Engine:
         self._check(self.lib.kgwe_schedule_queue(self.h, abi.ptr(pods), len(pods), abi.ptr(hint), abi.ptr(out)))
         return out
 
+    def schedule_queue_p2p(self, pods, recv_ptrs, my_rank, seq_base, hint=None):
+        """The stateful queue over a node-sharded cluster, exchanged on the device (kgwe_schedule_queue_p2p): every rank calls this
+        with the same pods; the result holds the decisions whose node this rank owns, NO_NODE elsewhere."""
+        pods = np.ascontiguousarray(pods, dtype=abi.POD_REQ)
+        out = np.zeros(len(pods), dtype=abi.PLACEMENT)
+        if hint is not None:
+            hint = np.ascontiguousarray(hint, dtype=np.uint8)
+        a = (C.c_uint64 * len(recv_ptrs))(*[int(x) for x in recv_ptrs])
+        self._check(self.lib.kgwe_schedule_queue_p2p(self.h, abi.ptr(pods), len(pods), abi.ptr(hint), a, len(recv_ptrs), my_rank, seq_base, abi.ptr(out)))
+        return out
+
     def schedule_gangs(self, pods, gang_of, hint=None):
         """E5: all-or-nothing gangs (members consecutive, gang_of non-decreasing)."""
         pods = np.ascontiguousarray(pods, dtype=abi.POD_REQ)

@@ -5,9 +5,10 @@
 // absent, here and on the GPU box).  It is kept as a thin 1:1 mapping over include/kgwe_engine.h
 // so that it can be reviewed by reading; the same entry points, call for call, are exercised by
 // the C++ mirror next to this file (kgwe_host.cpp, tests/host/) and by the ctypes binding.
-// Last checked against include/kgwe_engine.h at KGWE_ABI_VERSION 3 (kgwe_node_upsert_remap,
+// Last checked against include/kgwe_engine.h at KGWE_ABI_VERSION 4 (kgwe_node_upsert_remap,
 // KGWE_ERR_CONFLICT from kgwe_alloc_commit, candidates_resolved and the latency histogram in
-// kgwe_stats); init() below refuses to run against any other revision.
+// kgwe_stats; version 4 only added the multi-GPU kgwe_schedule_queue_p2p, not bound here); init() below refuses to run
+// against any other revision.
 //
 // Wiring inside the reference (src/scheduler/scheduler.go):
 //   NewTopologyAwareScheduler  -> also newGPUEngine(config, maxNodes)
@@ -39,7 +40,7 @@ import (
 	"github.com/nvidia/kgwe/src/discovery"
 )
 
-const abiChecked = 3 // the KGWE_ABI_VERSION this file mirrors
+const abiChecked = 4 // the KGWE_ABI_VERSION this file mirrors
 
 func init() {
 	if C.KGWE_ABI_VERSION != abiChecked || C.sizeof_kgwe_stats != 200 {

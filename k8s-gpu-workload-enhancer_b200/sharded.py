@@ -108,6 +108,48 @@ class ShardedScorer:
         return self.d_merged
 
 
+class ShardedQueue:
+    """The stateful queue (Schedule with a commit per workload) over a node-sharded cluster, exchanged on the device:
+    one engine per rank holds a shard; every rank calls schedule() with the same workloads; the queue kernels of the ranks
+    exchange one 64-bit word per workload through symmetric (peer-mapped) memory and the owner of the winning node commits.
+    No collective and no host round trip per workload (schedule_queue_sharded below is the host-driven form)."""
+    SEQ_MOD = 0xFFFFFF
+
+    def __init__(self, engine, world, rank, dist, torch, dev):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.eng, self.world, self.rank, self.dist, self.torch, self.dev = engine, world, rank, dist, torch, dev
+        self.recv = symm_mem.empty((world * 4,), dtype=torch.int64, device=dev)
+        self.recv.zero_()
+        self.hdl = symm_mem.rendezvous(self.recv, dist.group.WORLD)
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        if len(self.ptrs) != world:
+            raise RuntimeError("symmetric memory: not every rank is reachable")
+        torch.cuda.synchronize()
+        dist.barrier()                 # every rank's receive words are zero before anyone sends
+        self.seq = 0
+
+    def schedule(self, pods, hint=None):
+        """Decisions whose node this rank owns (NO_NODE for the others)."""
+        out = self.eng.schedule_queue_p2p(pods, self.ptrs, self.rank, self.seq, hint)
+        self.seq = (self.seq + len(pods)) % self.SEQ_MOD
+        return out
+
+    def merged(self, local):
+        """All ranks' decisions put together (one all-gather of the result arrays; for tests and reports)."""
+        torch = self.torch
+        it = abi.PLACEMENT.itemsize
+        mine = torch.from_numpy(local.view(np.uint8).reshape(-1).copy()).to(self.dev)
+        allr = torch.empty(self.world * mine.numel(), dtype=torch.uint8, device=self.dev)
+        self.dist.all_gather_into_tensor(allr, mine)
+        parts = allr.cpu().numpy().view(abi.PLACEMENT).reshape(self.world, len(local))
+        out = parts[0].copy()
+        for r in range(1, self.world):
+            take = parts[r]["node_idx"] != abi.NO_NODE
+            assert not (take & (out["node_idx"] != abi.NO_NODE)).any(), "two ranks claim the same workload"
+            out[take] = parts[r][take]
+        return out
+
+
 def schedule_queue_sharded(dist, rank, world, shard, pods, score_top1, commit, hint=None, device=None, torch=None, release=None):
     """Stateful Schedule() over a node-sharded cluster: per workload every rank scores its
     shard (top-1, global node index), ONE small all-gather of the 32-byte placements, the identical merge on

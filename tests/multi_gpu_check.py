@@ -83,6 +83,32 @@ def main():
         want_q, _, _ = orc.schedule_queue(abi, nodes, led, qpods)
         ok = ok and got_q.tobytes() == want_q.tobytes()
         eng.close()
+        # the same queue exchanged on the device (kgwe_schedule_queue_p2p): fresh engines, two calls (the sequence numbers run
+        # on), hints on the first; workload ids must be new, so the repeated tail of qpods is left out
+        if p2p_on:
+            eng2 = kg.Engine(max_nodes=hi - lo, device=local, node_base=lo)
+            eng2.upsert_nodes(nodes[lo:hi])
+            for a in led:
+                if lo <= a["node_idx"] < hi:
+                    eng2.commit(a["wl_id"], a["node_idx"] - lo, a["gpu_mask"])
+            sq = kg.sharded.ShardedQueue(eng2, world, rank, dist, torch, dev)
+            held = set(int(x) for x in led["wl_id"])
+            keep, seen_ids = [], set()
+            for i, w in enumerate(pods["wl_id"]):
+                if int(w) not in held and int(w) not in seen_ids:
+                    keep.append(i); seen_ids.add(int(w))
+            fresh = pods[np.array(keep, dtype=np.int64)] if keep else pods[:0]
+            half = len(fresh) // 2
+            hq = synth.make_hint(half, N, 0.02, seed=77)
+            local_hint = np.packbits(np.unpackbits(hq, axis=1, bitorder="little")[:, lo:hi], axis=1, bitorder="little")
+            got1 = sq.merged(sq.schedule(fresh[:half], local_hint))
+            got2 = sq.merged(sq.schedule(fresh[half:]))
+            want12, _, _ = orc.schedule_queue(abi, nodes, led, fresh, np.concatenate([hq, np.zeros((len(fresh) - half, hq.shape[1]), np.uint8)]))
+            same = np.concatenate([got1, got2]).tobytes() == want12.tobytes()
+            if rank == 0 and not same:
+                print(f"multi_gpu_check: device-exchanged queue differs in case {label}")
+            ok = ok and same
+            eng2.close()
         if rank == 0 and not ok:
             print(f"multi_gpu_check: MISMATCH in case {label}")
         return ok
