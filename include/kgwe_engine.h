@@ -365,8 +365,10 @@ int kgwe_schedule_queue(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pod
  *                      addresses, e.g. the buffer_ptrs of a torch symmetric-memory allocation)
  *   seq_base           number of workloads all earlier calls on these buffers have scheduled, modulo 2^24 - 1: the same on
  *                      every rank
- * Limits: 2..8 ranks, a shard of at most 10,240 nodes, global node indices below 2^22, workload ids not yet in any rank's
- * ledger (kgwe_alloc_release first).  A rank whose peers do not answer within about ten seconds fails with KGWE_ERR_CUDA. */
+ * Limits: 2..8 ranks, ONE RANK PER GPU (each rank's kernel waits on the device for the other ranks' kernels, which must
+ * therefore be running at the same time), a shard of at most 10,240 nodes, global node indices below 2^22, workload ids not
+ * yet in any rank's ledger (kgwe_alloc_release first).  A rank whose peers do not answer within about ten seconds fails
+ * with KGWE_ERR_CUDA. */
 int kgwe_schedule_queue_p2p(kgwe_engine* e, const kgwe_pod_req* pods, uint32_t n_pods, const uint8_t* hint_bitmap,
                             const uint64_t* peer_recv_bufs, uint32_t n_ranks, uint32_t my_rank, uint32_t seq_base,
                             kgwe_placement* out);
