@@ -105,6 +105,31 @@ def one_seed(kg, orc, seed):
     return N, P, kind, flags
 
 
+def permute_node(abi, node, new_of_old, n_new):
+    """The same node with its GPU list re-ordered / shortened: the GPU at old index i moves to new_of_old[i] (-1: gone)."""
+    out = np.zeros(1, dtype=abi.NODE_IMAGE)[0]
+    for name in ("mig_free", "node_flags", "flags"):
+        out[name] = node[name]
+    out["n_gpus"] = n_new
+    for i, a in enumerate(new_of_old):
+        if a < 0:
+            continue
+        for name in ("pcie_bw", "free_bytes", "util", "numa", "pcie_switch", "arch"):
+            out[name][a] = node[name][i]
+        for bit_name in ("healthy_mask", "mig_enabled_mask", "mig_has_free_mask"):
+            if int(node[bit_name]) >> i & 1:
+                out[bit_name] |= 1 << a
+        for j, b in enumerate(new_of_old):
+            if b < 0:
+                continue
+            out["nvl_bw"][a][b] = node["nvl_bw"][i][j]
+            if int(node["nvl_present"][i]) >> j & 1:
+                out["nvl_present"][a] |= 1 << b
+            if int(node["nvl_active"][i]) >> j & 1:
+                out["nvl_active"][a] |= 1 << b
+    return out
+
+
 def life_cycle_seed(kg, orc, seed, n_ops=80):
     """Random interleaving of informer events (upsert / remove / re-add), ledger calls (commit, overwrite, release)
     and scoring / scheduling calls on ONE engine, mirrored on a plain model (node array + presence + ledger dict)
@@ -139,7 +164,29 @@ def life_cycle_seed(kg, orc, seed, n_ops=80):
 
     for step in range(n_ops):
         op = int(rng.randint(0, 9, 1)[0])
-        if op == 0:                                   # node refresh / re-add
+        if op == 0 and rng.uniform(1)[0] < 0.35 and present.any():
+            # a refresh that re-enumerates a node's GPUs (and sometimes loses one): the reference keys allocations by GPU UUID
+            # (scheduler.go:586-598), the engine by index, so the refresh carries the old -> new map and the ledger moves with it
+            i = int(np.flatnonzero(present)[int(rng.randint(0, int(present.sum()) - 1, 1)[0])])
+            g = int(nodes["n_gpus"][i])
+            if g >= 2:
+                order = list(np.argsort(rng.uniform(g)))                     # new position of every old index
+                lost = int(rng.randint(0, g - 1, 1)[0]) if rng.uniform(1)[0] < 0.4 else -1
+                new_of_old, nxt = [-1] * 8, 0
+                for old_idx in sorted(range(g), key=lambda q: order[q]):
+                    if old_idx == lost:
+                        continue
+                    new_of_old[old_idx] = nxt; nxt += 1
+                nodes[i] = permute_node(abi, nodes[i], new_of_old, nxt)
+                eng.upsert_node_remap(i, nodes[i], new_of_old)
+                for wl, (n2, m2) in list(ledger.items()):
+                    if n2 == i:
+                        m_new = 0
+                        for b in range(8):
+                            if m2 >> b & 1 and new_of_old[b] >= 0:
+                                m_new |= 1 << new_of_old[b]
+                        ledger[wl] = (i, m_new)                          # (an entry whose GPUs all vanished stays and still counts)
+        elif op == 0:                                 # node refresh / re-add
             i = int(rng.randint(0, N - 1, 1)[0])
             nodes[i] = pool[int(rng.randint(0, len(pool) - 1, 1)[0])]
             eng.upsert_node(i, nodes[i]); present[i] = True

@@ -49,28 +49,11 @@ def test_commit_refuses_gpus_that_are_taken(kg, orc):
 
 
 def _permute_node(abi, node, new_of_old, n_new):
-    """The same node with its GPU list re-ordered / shortened: GPU at old index i moves to new_of_old[i] (-1: gone)."""
-    out = np.zeros(1, dtype=abi.NODE_IMAGE)[0]
-    for name in ("mig_free", "node_flags", "flags"):
-        out[name] = node[name]
-    out["n_gpus"] = n_new
-    for i, a in enumerate(new_of_old):
-        if a < 0:
-            continue
-        for name in ("pcie_bw", "free_bytes", "util", "numa", "pcie_switch", "arch"):
-            out[name][a] = node[name][i]
-        for bit_name in ("healthy_mask", "mig_enabled_mask", "mig_has_free_mask"):
-            if int(node[bit_name]) >> i & 1:
-                out[bit_name] |= 1 << a
-        for j, b in enumerate(new_of_old):
-            if b < 0:
-                continue
-            out["nvl_bw"][a][b] = node["nvl_bw"][i][j]
-            if int(node["nvl_present"][i]) >> j & 1:
-                out["nvl_present"][a] |= 1 << b
-            if int(node["nvl_active"][i]) >> j & 1:
-                out["nvl_active"][a] |= 1 << b
-    return out
+    import importlib.util, os      # the fuzzer's life-cycle mode uses the same helper
+    spec = importlib.util.spec_from_file_location("fuzz_parity", os.path.join(os.path.dirname(os.path.abspath(__file__)), "fuzz_parity.py"))
+    fz = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fz)
+    return fz.permute_node(abi, node, new_of_old, n_new)
 
 
 def test_refresh_that_reorders_gpus_moves_the_allocations(kg, orc):
