@@ -1294,7 +1294,7 @@ int kgwe_mig_pack(kgwe_engine* e, kgwe_mig_gpu* gpus, uint32_t n_gpus, const uin
     CU(e, cudaMemcpyAsync(e->d_hint.p, e->h_hint.p, off_p + n_reqs, cudaMemcpyHostToDevice, s));
     CU(e, cudaFuncSetAttribute(tree ? (const void*)mig_pack_tree_kernel : (const void*)mig_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CU(e, cudaEventRecord(e->ev0, s));
-    if (tree) mig_pack_tree_kernel<<<1, MIGT_THREADS, smem, s>>>(reinterpret_cast<kgwe_mig_gpu*>(e->d_hint.p), n_gpus, e->d_hint.p + off_p, n_reqs,
+    if (tree) mig_pack_tree_kernel<<<2, MIGT_THREADS, smem, s>>>(reinterpret_cast<kgwe_mig_gpu*>(e->d_hint.p), n_gpus, e->d_hint.p + off_p, n_reqs,
                                                                  reinterpret_cast<kgwe_mig_assignment*>(e->d_hint.p + off_o));
     else mig_pack_kernel<<<1, MIG_THREADS, smem, s>>>(reinterpret_cast<kgwe_mig_gpu*>(e->d_hint.p), n_gpus, e->d_hint.p + off_p, n_reqs,
                                                       reinterpret_cast<kgwe_mig_assignment*>(e->d_hint.p + off_o));

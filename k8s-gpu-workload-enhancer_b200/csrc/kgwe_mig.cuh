@@ -106,8 +106,8 @@ mig_pack_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uint8_t*
     for (uint32_t g = tid; g < n_gpus; g += MIG_THREADS) gpus[g].occ = (uint8_t)(state[g] & 0xff);
 }
 
-// K4, tournament-tree form (tables of up to MIG_TREE_MAX_GPUS GPUs): requests are inherently sequential - each one must see
-// the commits before it - and ONE CTA serves them, so what counts is the length of the per-request instruction chain (a warp
+// K4, tournament-tree form (tables of up to MIG_TREE_MAX_GPUS GPUs): requests of one GPU class are inherently sequential - each one
+// must see the commits before it - and ONE CTA per class serves them, so what counts is the length of the per-request instruction chain (a warp
 // issues in order), not the width of the machine.  Per (class, geometry) a 32-ary min tree over the GPUs keeps the best
 // placement key of every group of 32 GPUs, of every group of 32 groups, and at the root: a request is ONE shared-memory read
 // of its root, and its commit only repairs the path above the one GPU that changed - three warp-wide REDUX.MIN per tree, one
@@ -140,6 +140,10 @@ mig_pack_tree_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uin
     uint8_t* lut = leaf + MIG_GEOS * n_pad;                                 // [5][256]
     uint8_t* req_stage = lut + MIG_GEOS * 256;                              // [1024]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // Two CTAs, one per GPU class: a request only ever touches GPUs (and trees) of its profile's class, so the two classes are
+    // independent request streams.  Each CTA walks the whole stream, serves the requests of its class in order and steps over the
+    // others without a barrier (CTA 0 also answers requests with an unknown profile).
+    const uint32_t my_cls = blockIdx.x;
     for (int i = tid; i < MIG_GEOS * 256; i += MIGT_THREADS) lut[i] = (uint8_t)mig_best((uint32_t)(i & 255), i >> 8);
     __syncthreads();
     for (uint32_t g = tid; g < n_pad; g += MIGT_THREADS) {
@@ -154,19 +158,19 @@ mig_pack_tree_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uin
     for (uint32_t i = tid; i < 10 * 32; i += MIGT_THREADS) L2[i] = MIG_KEY_NONE;
     __syncthreads();
     // level 1: tree t = cls * 5 + geometry, node i = min over GPUs 32 i .. 32 i + 31
-    for (uint32_t w = warp; w < 10 * n1; w += MIGT_THREADS / 32) {
-        const uint32_t t = w / n1, i = w % n1, g = i * 32 + lane;
+    for (uint32_t w = warp; w < 5 * n1; w += MIGT_THREADS / 32) {
+        const uint32_t t = my_cls * 5u + w / n1, i = w % n1, g = i * 32 + lane;
         const uint32_t k = __reduce_min_sync(0xffffffffu, mig_leaf_key(leaf[(t % 5) * n_pad + g], t / 5, g, state[g]));
         if (lane == 0) L1[t * n1 + i] = k;
     }
     __syncthreads();
-    for (uint32_t w = warp; w < 10 * n2; w += MIGT_THREADS / 32) {
-        const uint32_t t = w / n2, i = w % n2, j = i * 32 + lane;
+    for (uint32_t w = warp; w < 5 * n2; w += MIGT_THREADS / 32) {
+        const uint32_t t = my_cls * 5u + w / n2, i = w % n2, j = i * 32 + lane;
         const uint32_t k = __reduce_min_sync(0xffffffffu, j < n1 ? L1[t * n1 + j] : MIG_KEY_NONE);
         if (lane == 0) L2[t * 32 + i] = k;
     }
     __syncthreads();
-    for (uint32_t t = warp; t < 10; t += MIGT_THREADS / 32) {
+    for (uint32_t t = my_cls * 5u + warp; t < my_cls * 5u + 5u; t += MIGT_THREADS / 32) {
         const uint32_t k = __reduce_min_sync(0xffffffffu, L2[t * 32 + lane]);
         if (lane == 0) root[t] = k;
     }
@@ -177,8 +181,12 @@ mig_pack_tree_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uin
         const int profile_next = req_stage[(r + 1u) & 1023u];      // the next request's profile is fetched now, off the critical path
         const bool known = profile >= 1 && profile <= KGWE_MIG_PROFILES;
         const int geo = known ? mig_geo(profile) : 0, cls = known ? mig_cls(profile) : 0;
-        const uint32_t key = known ? root[cls * 5 + geo] : MIG_KEY_NONE;
-        if (key == MIG_KEY_NONE) {                    // nothing fits: nothing changes
+        const bool mine = known ? ((uint32_t)cls == my_cls) : (my_cls == 0u);
+        const bool refill = (r & 511u) == 511u && r + 513u < n_reqs;
+        if (!mine && !refill) { profile = profile_next; continue; }      // the other class's request: nothing of this CTA's changes
+        const uint32_t key = (known && mine) ? root[cls * 5 + geo] : MIG_KEY_NONE;
+        if (!mine) {
+        } else if (key == MIG_KEY_NONE) {                    // nothing fits: nothing changes
             if (tid == 0) { kgwe_mig_assignment a; a.gpu_idx = KGWE_NO_NODE; a.start = a.size = a.cost = 0; a.profile = (uint8_t)profile; out[r] = a; }
         } else {
             const uint32_t g = (key >> 11) & 0xFFFFu, start = key & 7u, size = (uint32_t)mig_size(geo);
@@ -207,14 +215,15 @@ mig_pack_tree_kernel(kgwe_mig_gpu* __restrict__ gpus, uint32_t n_gpus, const uin
         }
         // every 512 requests the half of the ring consumed last is refilled with the profiles 512..1023 requests ahead (the
         // loads are issued by all threads at once; a per-request refill would put a global load in front of every barrier)
-        if ((r & 511u) == 511u && r + 513u < n_reqs) {
+        if (refill) {
             const uint32_t first = r + 513u;
             for (uint32_t i = tid; i < 512u && first + i < n_reqs; i += MIGT_THREADS) req_stage[(first + i) & 1023u] = profiles[first + i];
         }
         __syncthreads();                              // warps stay in step; the next request reads the repaired roots
         profile = profile_next;
     }
-    for (uint32_t g = tid; g < n_gpus; g += MIGT_THREADS) gpus[g].occ = (uint8_t)(state[g] & 0xff);
+    for (uint32_t g = tid; g < n_gpus; g += MIGT_THREADS)
+        if (((state[g] >> 9) & 1u) == my_cls) gpus[g].occ = (uint8_t)(state[g] & 0xff);      // (this CTA's class: the other CTA never touched these)
 }
 
 // Rebalance, device part 1: exclusive rank of every idle GPU (enabled, occ == 0) within its class,
