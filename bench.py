@@ -278,7 +278,7 @@ def run_kgwe(args):
                     "P2P stores from the finalisation kernel into every rank's gather buffer (symmetric memory) + one cross-GPU barrier" if (scorer.use_barrier or scorer.flags is None) else
                     "kgwe_score_merge_p2p: the finalisation kernel stores its records and then its flag into every rank's symmetric memory over NVLink; the merge kernel waits for the flags on the device (no collective, no barrier launch)")
     d_merged = scorer.d_merged
-    flush = torch.empty(128 << 20, dtype=torch.uint8, device=dev)     # 134 MB > the 126 MB L2
+    flush = torch.empty((128 << 20) // 4, dtype=torch.int32, device=dev)     # 134 MB > the 126 MB L2 (32-bit elements: the fill kernel writes it in 21 us, as bytes in 37)
 
     def step_device():
         flush.zero_()                                                    # L2 flush between steps
