@@ -151,7 +151,7 @@ schedule_cluster_kernel(DevNode* nodes, uint32_t n_nodes, const kgwe_pod_req* __
     tb.memo = reinterpret_cast<int2*>(smem + L.memo) + tid;
     tb.mat = nullptr; tb.subset = nullptr;
     if (tid < 2 * QC_MAX_CTAS) ckeys[tid] = 0u;
-    const uint32_t bars = smem_u32(smem + L.bars);      // two mbarriers: the keys of even / odd workloads
+    const uint32_t bars = smem_u32(smem + L.bars);      // four mbarriers: the keys of even / odd workloads inside the cluster, the outcome of the exchange between the ranks (PEERS)
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bars));
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bars + 8u));
