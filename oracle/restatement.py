@@ -1,7 +1,8 @@
 """oracle/restatement.py — TEST INFRASTRUCTURE (nothing under k8s-gpu-workload-enhancer_b200/ imports it).
 
-A third restatement of the reference's Filter / Prioritize / Schedule path, written from
-/root/reference/src/scheduler/scheduler.go:114-707 on its own - not from oracle/kgwe_oracle.cpp and not from the
+A third restatement of the reference's Filter / Prioritize / Schedule path (and, below, of DiscoveryService.GetTopologyHint,
+src/discovery/discovery.go:222-247, 378-541, and of the exporter's per-node gauge, src/monitoring/prometheus_exporter.go:
+517-539), written from /root/reference/src/scheduler/scheduler.go:114-707 on its own - not from oracle/kgwe_oracle.cpp and not from the
 kernels - in plain Python with the reference's own data shapes: GPU objects with UUID strings, per-call adjacency
 dicts, a dict ledger scanned per node.  tests/test_restatements_agree.py runs it against both builds of the C++
 oracle on small random clusters; three texts that agree make a transcription slip in any one of them visible.
@@ -29,7 +30,9 @@ class GPU:
     numa_node: int
     switch_id: int                     # interned PCIe switch id ("" -> "default" happens in the packer)
     pcie_bandwidth: float
-    nvlink: dict = field(default_factory=dict)      # peer uuid -> (BandwidthGBps, IsActive)
+    nvlink: dict = field(default_factory=dict)      # peer uuid -> (BandwidthGBps, IsActive), in ascending peer index (the canonical map order)
+    mig_enabled: bool = False
+    mig_has_free: bool = False                      # some MIG instance of the GPU is not in use
 
 
 @dataclass
@@ -38,6 +41,7 @@ class Node:
     index: int
     gpus: list
     mig_free: list                     # free instances per profile over the node's MIG-enabled GPUs (getMIGAvailability's count)
+    nvswitch_present: bool = False
 
 
 @dataclass
@@ -265,8 +269,8 @@ def nodes_from_images(images):
                     links[f"n{n}g{p}"] = (float(im["nvl_bw"][g][p]), bool(int(im["nvl_active"][g]) >> p & 1))
             gpus.append(GPU(f"n{n}g{g}", int(im["arch"][g]), int(im["free_bytes"][g]), float(im["util"][g]),
                             bool(int(im["healthy_mask"]) >> g & 1), int(im["numa"][g]), int(im["pcie_switch"][g]),
-                            float(im["pcie_bw"][g]), links))
-        nodes.append(Node(f"node{n}", n, gpus, [int(x) for x in im["mig_free"]]))
+                            float(im["pcie_bw"][g]), links, bool(int(im["mig_enabled_mask"]) >> g & 1), bool(int(im["mig_has_free_mask"]) >> g & 1)))
+        nodes.append(Node(f"node{n}", n, gpus, [int(x) for x in im["mig_free"]], bool(int(im["node_flags"]) & 1)))
     return nodes
 
 
@@ -283,3 +287,126 @@ def seed_ledger(sched, ledger):
 
 def gpu_indices(selected):
     return [int(u.split("g")[1]) for u in selected]
+
+
+# ---- DiscoveryService.GetTopologyHint (src/discovery/discovery.go:222-247, 378-541) --------------------------------
+@dataclass
+class HintRequirements:
+    count: int
+    min_memory_gb: int
+    prefer_nvlink: bool
+    prefer_same_numa: bool
+    architecture: int                  # 0 = ""
+
+
+class Discovery:
+    def __init__(self, nodes):
+        self.nodes = nodes
+
+    # discovery.go:436-460
+    @staticmethod
+    def get_available_gpus(node):
+        available = []
+        for g in node.gpus:
+            if g.healthy:
+                if g.mig_enabled:
+                    if g.mig_has_free:
+                        available.append(g)
+                elif g.gpu_percent < 90:
+                    available.append(g)
+        return available
+
+    # discovery.go:462-488 (the peers of a GPU in ascending index: the canonical order of the map iteration at :468)
+    @staticmethod
+    def find_nvlink_groups(gpus, size):
+        groups = []
+        for g in gpus:
+            group = [g.uuid]
+            for peer_uuid in g.nvlink:
+                if len(group) >= size:
+                    break
+                for peer in gpus:
+                    if peer.uuid == peer_uuid:
+                        group.append(peer_uuid)
+                        break
+            if len(group) >= size:
+                groups.append(group[:size])
+        return groups
+
+    # discovery.go:490-504
+    @staticmethod
+    def are_on_same_numa(node, uuids):
+        numa = -2
+        for u in uuids:
+            for g in node.gpus:
+                if g.uuid == u:
+                    if numa == -2:
+                        numa = g.numa_node
+                    elif numa != g.numa_node:
+                        return False
+        return True
+
+    # discovery.go:506-541
+    @staticmethod
+    def estimate_bandwidth(node, uuids):
+        if len(uuids) < 2:
+            return 0.0
+        total, count = 0.0, 0
+        for i, u1 in enumerate(uuids):
+            for j, u2 in enumerate(uuids):
+                if i >= j:
+                    continue
+                for g in node.gpus:
+                    if g.uuid == u1:
+                        total += g.nvlink[u2][0] if u2 in g.nvlink else g.pcie_bandwidth
+                        count += 1
+                        break
+        return 0.0 if count == 0 else total / float(count)
+
+    # discovery.go:378-434
+    def score_node_for_requirements(self, node, req):
+        available = self.get_available_gpus(node)
+        if len(available) < req.count:
+            return 0, []
+        filtered = [g for g in available if int(g.free_bytes // (1024 * 1024 * 1024)) >= req.min_memory_gb]
+        if len(filtered) < req.count:
+            return 0, []
+        score, selected = 50, []
+        if req.count > 1 and req.prefer_nvlink:
+            groups = self.find_nvlink_groups(filtered, req.count)
+            if groups:
+                score += 30
+                selected = groups[0]
+        if not selected:
+            selected = [g.uuid for g in filtered[:max(req.count, 0)]]
+        if req.prefer_same_numa and self.are_on_same_numa(node, selected):
+            score += 10
+        if req.architecture != 0:
+            for u in selected:
+                for g in node.gpus:
+                    if g.uuid == u and g.architecture == req.architecture:
+                        score += 5
+        return score, selected
+
+    # discovery.go:222-247: (node index, score, GPU uuids, bandwidth estimate) or None ("no suitable placement found")
+    def get_topology_hint(self, req):
+        best = None
+        best_score = 0
+        for node in self.nodes:
+            score, gpus = self.score_node_for_requirements(node, req)
+            if score > best_score:
+                best_score = score
+                best = (node.index, score, gpus, self.estimate_bandwidth(node, gpus))
+        return best
+
+
+# PrometheusExporter.calculateTopologyScore (src/monitoring/prometheus_exporter.go:517-539)
+def exporter_topology_score(node):
+    if not node.gpus:
+        return 0
+    score = 50
+    if node.nvswitch_present:
+        score += 30
+    if sum(len(g.nvlink) for g in node.gpus) > 0:
+        score += 20
+    return min(100, score)

@@ -98,3 +98,27 @@ def test_stateful_queue(kg, orc, seed):
                (best.node.index, best.total, best.topology, best.resource, best.balance, rs.gpu_indices(best.selected)), f"seed {seed} pod {p}"
         assert abs(float(d["est_bandwidth_gbps"]) - bw) <= 1e-9 * max(1.0, abs(bw))
     assert len(sched.allocations) == len(led_after)
+
+
+@pytest.mark.parametrize("seed", range(201, 221))
+def test_topology_hint_and_gauge(kg, orc, seed):
+    """DiscoveryService.GetTopologyHint (discovery.go:222-247, 378-541) and the exporter's per-node gauge
+    (prometheus_exporter.go:517-539): the C++ oracle against the Python restatement."""
+    abi = kg.abi
+    nodes, _, _, _ = _case(kg, seed)
+    reqs = kg.synth.make_hint_reqs(40, seed=seed)
+    want = orc.topology_hints(abi, nodes, reqs)
+    objs = rs.nodes_from_images(nodes)
+    disc = rs.Discovery(objs)
+    for i, rq in enumerate(reqs):
+        h = disc.get_topology_hint(rs.HintRequirements(int(rq["count"]), int(rq["min_memory_gb"]), bool(rq["prefer_nvlink"]), bool(rq["prefer_same_numa"]), int(rq["arch"])))
+        w = want[i]
+        if h is None:
+            assert int(w["node_idx"]) == abi.NO_NODE and int(w["score"]) == 0, f"seed {seed} request {i}"
+            continue
+        n = (int(w["order"]) >> 24) & 15
+        order = [(int(w["order"]) >> (3 * j)) & 7 for j in range(n)]
+        assert (int(w["node_idx"]), int(w["score"]), order) == (h[0], h[1], rs.gpu_indices(h[2])), f"seed {seed} request {i}"
+        assert abs(float(w["bandwidth_estimate"]) - h[3]) <= 1e-9 * max(1.0, abs(h[3]))
+    gauges = orc.topology_gauges(abi, nodes)
+    assert [int(x) for x in gauges] == [rs.exporter_topology_score(n) for n in objs]
