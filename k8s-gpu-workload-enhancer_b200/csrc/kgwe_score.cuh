@@ -47,7 +47,7 @@ __host__ __device__ inline K1Layout k1_layout(uint32_t ppc, uint32_t mat_units, 
 }
 
 template <bool GENERAL, bool TABLES>
-__global__ void __launch_bounds__(K1_THREADS, TABLES ? 1 : (GENERAL ? 3 : 5))
+__global__ void __launch_bounds__(K1_THREADS, TABLES ? 1 : (GENERAL ? 4 : 5))
 score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
              const kgwe_pod_req* __restrict__ pods, uint32_t n_pods, uint32_t pods_per_chunk,
              const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
