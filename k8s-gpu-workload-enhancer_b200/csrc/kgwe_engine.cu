@@ -239,7 +239,7 @@ size_t sched_tile_smem_bytes() { return (size_t)TILE_NODES * (sizeof(DevNode) + 
 // Kernel variant: the lean one when every present record is uniform (all active links of a node equal - any
 // NVSwitch node, any single-generation mesh), GENERAL as soon as one record is not (matrix columns in shared
 // memory), TABLES when exhaustive-mode pods may be in the batch (subset-key columns; implies GENERAL).
-struct K1Plan { bool general, tables; uint32_t mode, chunks, ppc, n_tiles, mat_units; size_t smem; };
+struct K1Plan { bool general, tables; uint32_t mode, chunks, ppc, n_tiles, mat_units, groups; size_t smem; };
 
 uint32_t k1_mode(const kgwe_engine* e) {
     return (e->cfg.flags & KGWE_CFG_MEMOISE_GROUPS) ? K1_MODE_MEMO : (e->cfg.flags & KGWE_CFG_PRUNE_TIED_STARTS) ? K1_MODE_PRUNE : K1_MODE_FULL;
@@ -249,12 +249,15 @@ uint32_t k1_mode(const kgwe_engine* e) {
 // chunks amortise it better, but CTAs differ in cost (absent or full nodes finish early) and several shorter waves even
 // that out: measured on the headline workload, chunks of about 270 pods are the best trade at every shard size
 // (1.30 -> 1.24 ms at 10,000 nodes with four waves; a 1,250-node shard keeps its single wave of 136-pod chunks).
-K1Plan plan_k1(const kgwe_engine* e, uint32_t n_pods, bool tables) {
+K1Plan plan_k1(const kgwe_engine* e, uint32_t n_pods, bool tables, bool fused_tail = false) {
     K1Plan pl;
     pl.tables = tables || (e->cfg.flags & KGWE_CFG_SUBSET_TABLES);
     pl.general = pl.tables || e->n_nonuniform > 0;
     pl.mat_units = !pl.general ? 0u : e->n_fractional > 0 ? 32u : 16u;      // float64 rows only when some non-uniform record has fractional bandwidths
     pl.mode = k1_mode(e);
+    // the variants with big per-node tables run two warp groups per CTA that share them (kgwe_score.cuh); not on the latency path,
+    // whose in-kernel finalisation is written for one group
+    pl.groups = ((pl.tables || pl.mat_units == 32u) && !fused_tail) ? (uint32_t)K1_MAX_GROUPS : 1u;
     pl.n_tiles = (e->n_nodes + K1_TILE - 1) / K1_TILE;
     const uint32_t max_ppc = pl.tables ? 256u : (uint32_t)MAX_PODS_PER_CHUNK;      // the subset columns leave room for 256 pods' tables
     const uint32_t slots = (uint32_t)e->sm_count * (uint32_t)e->k1_blocks_per_sm[pl.tables ? 3 : !pl.general ? 0 : pl.mat_units == 16 ? 1 : 2];
@@ -263,7 +266,7 @@ K1Plan plan_k1(const kgwe_engine* e, uint32_t n_pods, bool tables) {
     if (!pl.tables) {      // (the subset-table variant has the heaviest set-up: it keeps the longest chunks it can hold)
         const uint32_t one_wave_chunks = std::max(1u, std::min(n_pods, slots / pl.n_tiles));
         const uint32_t one_wave_ppc = (n_pods + one_wave_chunks - 1) / one_wave_chunks;
-        first_waves = std::max(1u, (one_wave_ppc + 135u) / 270u);
+        first_waves = std::max(1u, (one_wave_ppc + 135u * pl.groups) / (270u * pl.groups));
     }
     for (uint32_t waves = first_waves; waves <= 256; ++waves) {
         chunks = std::max(1u, std::min(n_pods, slots * waves / pl.n_tiles));
@@ -273,19 +276,19 @@ K1Plan plan_k1(const kgwe_engine* e, uint32_t n_pods, bool tables) {
     if (ppc > max_ppc) ppc = max_ppc;
     pl.ppc = ppc;
     pl.chunks = (n_pods + ppc - 1) / ppc;
-    pl.smem = k1_layout(ppc, pl.mat_units, pl.tables, pl.mode == K1_MODE_MEMO).total;
+    pl.smem = k1_layout(ppc, pl.mat_units, pl.tables, pl.mode == K1_MODE_MEMO, pl.groups).total;
     return pl;
 }
 
 // Launch K1 alone: scores into d_scores (nullable), arg-max keys into `best` (nullable).
 int launch_k1(kgwe_engine* e, const kgwe_pod_req* d_pods, uint32_t n_pods, const uint8_t* d_hint, kgwe_node_score* d_scores,
               unsigned long long* best, cudaStream_t s, bool tables, const FusedTail& tail, bool timed) {
-    const K1Plan pl = plan_k1(e, n_pods, tables);
+    const K1Plan pl = plan_k1(e, n_pods, tables, tail.out != nullptr);
     if (pl.chunks > 65535u) return fail(e, KGWE_ERR_TOO_LARGE, "too many pods in one launch (%u)", n_pods);
     const dim3 grid(pl.n_tiles, pl.chunks);
     timed = timed && e->timers_pending < kgwe_engine::kTimers;
     if (timed) CU(e, cudaEventRecord(e->t0[e->timers_pending], s));
-#define KGWE_LAUNCH_SCORE(G, T) score_kernel<G, T><<<grid, K1_THREADS, pl.smem, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, pl.ppc, d_hint, hint_row_bytes(e), \
+#define KGWE_LAUNCH_SCORE(G, T) score_kernel<G, T><<<grid, K1_THREADS * pl.groups, pl.smem, s>>>(e->d_nodes, e->n_nodes, d_pods, n_pods, pl.ppc, d_hint, hint_row_bytes(e), \
                                                                                     d_scores, best, e->params, e->d_counters, pl.mode, pl.mat_units, tail)
     if (pl.tables) KGWE_LAUNCH_SCORE(true, true);
     else if (pl.general) KGWE_LAUNCH_SCORE(true, false);
@@ -438,8 +441,8 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
         cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, cfg->device);
         for (int i = 0; i < kgwe_engine::kTimers && ok; ++i) ok = cudaEventCreate(&e->t0[i]) == cudaSuccess && cudaEventCreate(&e->t1[i]) == cudaSuccess;
         {
-            const int lean = (int)k1_layout(MAX_PODS_PER_CHUNK, 0, false, true).total, gen = (int)k1_layout(MAX_PODS_PER_CHUNK, 32, false, true).total,
-                      tab = (int)k1_layout(256, 32, true, true).total;
+            const int lean = (int)k1_layout(MAX_PODS_PER_CHUNK, 0, false, true).total, gen = (int)k1_layout(MAX_PODS_PER_CHUNK, 32, false, true, K1_MAX_GROUPS).total,
+                      tab = (int)k1_layout(256, 32, true, true, K1_MAX_GROUPS).total;
             ok = ok && cudaFuncSetAttribute(score_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lean) == cudaSuccess
                     && cudaFuncSetAttribute(score_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, gen) == cudaSuccess
                     && cudaFuncSetAttribute(score_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab) == cudaSuccess;
@@ -447,8 +450,8 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
             int b = 0;
             if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<false, false>, K1_THREADS, k1_layout(512, 0, false, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[0] = b;
             if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, false>, K1_THREADS, k1_layout(512, 16, false, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[1] = b;
-            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, false>, K1_THREADS, k1_layout(512, 32, false, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[2] = b;
-            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, true>, K1_THREADS, k1_layout(256, 32, true, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[3] = b;
+            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, false>, K1_THREADS * K1_MAX_GROUPS, k1_layout(540, 32, false, false, K1_MAX_GROUPS).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[2] = b;
+            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, true>, K1_THREADS * K1_MAX_GROUPS, k1_layout(256, 32, true, false, K1_MAX_GROUPS).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[3] = b;
         }
         int bps = 0;
         if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, schedule_kernel, SCORE_THREADS, 0) == cudaSuccess && bps > 0) e->sched_blocks_per_sm = bps;

@@ -31,10 +31,11 @@ struct FusedTail { kgwe_placement* out; unsigned int* done; unsigned int* flag; 
 
 struct K1Layout { uint32_t pods, keys, topo, grp, mig, memo, mat, subset, slot, total; };
 // mat_units: 16-byte units per lane of the matrix columns: 0 (lean variant), 16 (int32 rows), 32 (int32 or float64 rows)
-__host__ __device__ inline K1Layout k1_layout(uint32_t ppc, uint32_t mat_units, bool tables, bool memo) {
+// groups: warp groups of K1_TILE lanes per CTA that share the node tables and split the pod chunk (1 or 2)
+__host__ __device__ inline K1Layout k1_layout(uint32_t ppc, uint32_t mat_units, bool tables, bool memo, uint32_t groups = 1) {
     K1Layout L; uint32_t o = 0;
     L.pods = o; o += (ppc + 1u) * 16u;                              // + one slot: the loop prefetches pod i + 1
-    L.keys = o; o += ((ppc * 4u * (K1_THREADS / 32)) + 15u) & ~15u;    // one arg-max row per warp (plain stores, no atomics)
+    L.keys = o; o += ((ppc * 4u * (K1_THREADS / 32) * groups) + 15u) & ~15u;    // one arg-max row per warp (plain stores, no atomics)
     L.mat = o; o += mat_units * K1_TILE * 16u;
     L.memo = o; o += memo ? 7u * K1_TILE * 8u : 0u;
     L.topo = o; o += 7u * K1_TILE * 4u;
@@ -46,20 +47,28 @@ __host__ __device__ inline K1Layout k1_layout(uint32_t ppc, uint32_t mat_units, 
     return L;
 }
 
+// The variants with big per-node tables (float64 matrix columns, subset keys) fit few CTAs per SM, i.e. few warps to hide the
+// latency of their dependent chains.  They are launched with TWO warp groups of K1_TILE lanes per CTA: both groups own the same
+// 128 nodes and share their tables (built once, by group 0), and each takes half of the CTA's pod chunk.
+constexpr int K1_MAX_GROUPS = 2;
 template <bool GENERAL, bool TABLES>
-__global__ void __launch_bounds__(K1_THREADS, TABLES ? 1 : (GENERAL ? 4 : 5))
+__global__ void __launch_bounds__(GENERAL ? K1_THREADS * K1_MAX_GROUPS : K1_THREADS, TABLES ? 1 : (GENERAL ? 2 : 5))
 score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
              const kgwe_pod_req* __restrict__ pods, uint32_t n_pods, uint32_t pods_per_chunk,
              const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
              kgwe_node_score* __restrict__ out, unsigned long long* __restrict__ best,
              Params P, unsigned long long* __restrict__ counters, uint32_t mode, uint32_t mat_units, FusedTail tail) {
     extern __shared__ __align__(128) unsigned char smem[];
-    const K1Layout L = k1_layout(pods_per_chunk, GENERAL ? mat_units : 0u, TABLES, mode == K1_MODE_MEMO);
+    const uint32_t n_groups = GENERAL ? (blockDim.x / K1_TILE) : 1u;
+    const K1Layout L = k1_layout(pods_per_chunk, GENERAL ? mat_units : 0u, TABLES, mode == K1_MODE_MEMO, n_groups);
     PodLite* spod = reinterpret_cast<PodLite*>(smem + L.pods);
     uint32_t* keys = reinterpret_cast<uint32_t*>(smem + L.keys);
     uint16_t* slot_of = reinterpret_cast<uint16_t*>(smem + L.slot);             // TABLES only: entry of each mask
 
     const int tid = threadIdx.x, lane = tid & 31;
+    const int ltid = GENERAL ? (tid & (K1_TILE - 1)) : tid;            // the lane's node within the tile
+    const uint32_t grp = GENERAL ? (uint32_t)tid / K1_TILE : 0u;      // its warp group
+    const uint32_t n_threads = GENERAL ? blockDim.x : (uint32_t)K1_THREADS;
     const uint32_t tile_first = blockIdx.x * K1_TILE;
     const uint32_t p_begin = blockIdx.y * pods_per_chunk;
     const uint32_t p_end = min(n_pods, p_begin + pods_per_chunk);
@@ -74,7 +83,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     if (tid == 0) cta_needs = 0u;
     __syncthreads();
     uint32_t needs = 0;
-    for (uint32_t i = tid; i < np; i += K1_THREADS) {
+    for (uint32_t i = tid; i < np; i += n_threads) {
         const kgwe_pod_req pod = load_pod2(pods, spods, p_begin + i);
         const PodLite pl = pod_lite(pod);
         spod[i] = pl;
@@ -82,7 +91,7 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
         needs |= pod_needs(pl);
     }
     if (TABLES)      // slot of mask m in (popcount, value) order
-        for (int m = tid; m < 256; m += K1_THREADS) {
+        for (int m = tid; m < 256; m += (int)n_threads) {
             int rank = 0;
             for (int q = 0; q < m; ++q) rank += __popc(q) == __popc(m);
             slot_of[m] = (uint16_t)(subset_off(__popc(m)) + rank);
@@ -94,24 +103,24 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     const bool want_groups = (needs & NEED_GROUPS) != 0u;
 
     // ---- set-up 2: this lane's node ----
-    const uint32_t node = tile_first + tid;
+    const uint32_t node = tile_first + (uint32_t)ltid;
     const bool in_range = node < n_nodes;
     const DevNode* rec = nodes + (in_range ? node : 0);
     LaneNode ln;
     LaneTabs tb;
     tb.stride = K1_TILE;
-    tb.topo = reinterpret_cast<int32_t*>(smem + L.topo) + tid;
-    tb.grp = reinterpret_cast<uint32_t*>(smem + L.grp) + tid;
-    tb.mig = reinterpret_cast<uint32_t*>(smem + L.mig) + tid;
-    tb.memo = reinterpret_cast<int2*>(smem + L.memo) + tid;
-    tb.mat = reinterpret_cast<int4*>(smem + L.mat) + tid;
-    tb.subset = reinterpret_cast<uint32_t*>(smem + L.subset) + 4 * tid;
+    tb.topo = reinterpret_cast<int32_t*>(smem + L.topo) + ltid;
+    tb.grp = reinterpret_cast<uint32_t*>(smem + L.grp) + ltid;
+    tb.mig = reinterpret_cast<uint32_t*>(smem + L.mig) + ltid;
+    tb.memo = reinterpret_cast<int2*>(smem + L.memo) + ltid;
+    tb.mat = reinterpret_cast<int4*>(smem + L.mat) + ltid;
+    tb.subset = reinterpret_cast<uint32_t*>(smem + L.subset) + 4 * ltid;
     {
         NodeCtx c;
         node_ctx_core(c, rec, in_range);
         if (want_groups) node_ctx_group_tables(c, rec);
         lane_node_init(ln, c, rec, GENERAL ? mat_units : 0u);
-        lane_tables_build<GENERAL, TABLES>(ln, c, tb, rec, P.norm, mode, slot_of, needs);
+        if (grp == 0) lane_tables_build<GENERAL, TABLES>(ln, c, tb, rec, P.norm, mode, slot_of, needs);      // (the groups share the tables)
     }
     __syncthreads();
 
@@ -119,14 +128,17 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     uint32_t cnt_scored = 0, cnt_resolved = 0;
     const bool has_hint = hint != nullptr, has_best = best != nullptr;
     const uint32_t do_store = (out != nullptr && in_range) ? 1u : 0u;
-    int4* outp = reinterpret_cast<int4*>(out) + ((size_t)p_begin * n_nodes + node);              // only dereferenced when do_store
-    const uint8_t* hintp = hint + ((size_t)p_begin * hint_row_bytes + (node >> 3));               // only dereferenced when has_hint && in_range
-    const uint32_t key_low = (uint32_t)(K1_TILE - 1 - tid);
-    uint32_t pod_addr = (uint32_t)__cvta_generic_to_shared(spod);
-    uint32_t key_addr = (uint32_t)__cvta_generic_to_shared(keys) + (uint32_t)(tid >> 5) * pods_per_chunk * 4u;      // this warp's row
-    PodLite pd = spod[0];
+    // this group's part of the chunk
+    const uint32_t sub = (np + n_groups - 1u) / n_groups;
+    const uint32_t g_begin = min(np, grp * sub), g_end = min(np, g_begin + sub);
+    int4* outp = reinterpret_cast<int4*>(out) + ((size_t)(p_begin + g_begin) * n_nodes + node);              // only dereferenced when do_store
+    const uint8_t* hintp = hint + ((size_t)(p_begin + g_begin) * hint_row_bytes + (node >> 3));               // only dereferenced when has_hint && in_range
+    const uint32_t key_low = (uint32_t)(K1_TILE - 1 - ltid);
+    uint32_t pod_addr = (uint32_t)__cvta_generic_to_shared(spod) + g_begin * 16u;
+    uint32_t key_addr = (uint32_t)__cvta_generic_to_shared(keys) + ((uint32_t)(tid >> 5) * pods_per_chunk + g_begin) * 4u;      // this warp's row
+    PodLite pd = spod[g_begin];
 #pragma unroll 1
-    for (uint32_t i = 0; i < np; ++i) {
+    for (uint32_t i = g_begin; i < g_end; ++i) {
         PodLite next;      // pod i + 1 (slot np repeats the last pod), straight from the shared window
         {
             uint32_t a0, a1, a2, a3;
@@ -161,10 +173,11 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     }
     if (best) {
         __syncthreads();
-        for (uint32_t i = tid; i < np; i += K1_THREADS) {
-            uint32_t kk = keys[i];
+        for (uint32_t i = tid; i < np; i += n_threads) {
+            const uint32_t w0 = (i / sub) * (K1_THREADS / 32);          // the four warps of the group that scored pod i
+            uint32_t kk = keys[w0 * pods_per_chunk + i];
 #pragma unroll
-            for (int w = 1; w < K1_THREADS / 32; ++w) kk = max(kk, keys[w * pods_per_chunk + i]);
+            for (int w = 1; w < K1_THREADS / 32; ++w) kk = max(kk, keys[(w0 + w) * pods_per_chunk + i]);
             if (kk) atomicMax(&best[p_begin + i], rank_key((int32_t)(kk >> 7), P.node_base + tile_first + ((uint32_t)(K1_TILE - 1) - (kk & 127u))));
         }
     }
