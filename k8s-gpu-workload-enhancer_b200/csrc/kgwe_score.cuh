@@ -52,7 +52,7 @@ __host__ __device__ inline K1Layout k1_layout(uint32_t ppc, uint32_t mat_units, 
 // 128 nodes and share their tables (built once, by group 0), and each takes half of the CTA's pod chunk.
 constexpr int K1_MAX_GROUPS = 2;
 template <bool GENERAL, bool TABLES>
-__global__ void __launch_bounds__(GENERAL ? K1_THREADS * K1_MAX_GROUPS : K1_THREADS, TABLES ? 1 : (GENERAL ? 2 : 5))
+__global__ void __launch_bounds__(TABLES ? K1_THREADS * 4 : GENERAL ? K1_THREADS * K1_MAX_GROUPS : K1_THREADS, TABLES ? 1 : (GENERAL ? 2 : 5))
 score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
              const kgwe_pod_req* __restrict__ pods, uint32_t n_pods, uint32_t pods_per_chunk,
              const uint8_t* __restrict__ hint, uint32_t hint_row_bytes,
