@@ -259,7 +259,7 @@ K1Plan plan_k1(const kgwe_engine* e, uint32_t n_pods, bool tables, bool fused_ta
     // whose in-kernel finalisation is written for one group
     pl.groups = ((pl.tables || pl.mat_units == 32u) && !fused_tail) ? (pl.tables ? 4u : (uint32_t)K1_MAX_GROUPS) : 1u;
     pl.n_tiles = (e->n_nodes + K1_TILE - 1) / K1_TILE;
-    const uint32_t max_ppc = pl.tables ? (pl.groups == 4u ? 160u : 256u) : (uint32_t)MAX_PODS_PER_CHUNK;      // the subset columns leave little room for the pods' tables
+    const uint32_t max_ppc = pl.tables ? 384u : (uint32_t)MAX_PODS_PER_CHUNK;      // the subset columns leave little room for the pods' tables
     const uint32_t slots = (uint32_t)e->sm_count * (uint32_t)e->k1_blocks_per_sm[pl.tables ? 3 : !pl.general ? 0 : pl.mat_units == 16 ? 1 : 2];
     uint32_t chunks = 1, ppc = n_pods;
     uint32_t first_waves = 1;
@@ -442,7 +442,7 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
         for (int i = 0; i < kgwe_engine::kTimers && ok; ++i) ok = cudaEventCreate(&e->t0[i]) == cudaSuccess && cudaEventCreate(&e->t1[i]) == cudaSuccess;
         {
             const int lean = (int)k1_layout(MAX_PODS_PER_CHUNK, 0, false, true).total, gen = (int)k1_layout(MAX_PODS_PER_CHUNK, 32, false, true, K1_MAX_GROUPS).total,
-                      tab = (int)k1_layout(160, 32, true, true, 4).total;
+                      tab = (int)k1_layout(384, 32, true, true, 4).total;
             ok = ok && cudaFuncSetAttribute(score_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, lean) == cudaSuccess
                     && cudaFuncSetAttribute(score_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, gen) == cudaSuccess
                     && cudaFuncSetAttribute(score_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, tab) == cudaSuccess;
@@ -451,7 +451,7 @@ int kgwe_engine_create(const kgwe_config* cfg, kgwe_engine** out) {
             if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<false, false>, K1_THREADS, k1_layout(512, 0, false, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[0] = b;
             if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, false>, K1_THREADS, k1_layout(512, 16, false, false).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[1] = b;
             if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, false>, K1_THREADS * K1_MAX_GROUPS, k1_layout(540, 32, false, false, K1_MAX_GROUPS).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[2] = b;
-            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, true>, K1_THREADS * 4, k1_layout(160, 32, true, false, 4).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[3] = b;
+            if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, score_kernel<true, true>, K1_THREADS * 4, k1_layout(384, 32, true, false, 4).total) == cudaSuccess && b > 0) e->k1_blocks_per_sm[3] = b;
         }
         int bps = 0;
         if (ok && cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, schedule_kernel, SCORE_THREADS, 0) == cudaSuccess && bps > 0) e->sched_blocks_per_sm = bps;

@@ -35,7 +35,7 @@ struct K1Layout { uint32_t pods, keys, topo, grp, mig, memo, mat, subset, slot, 
 __host__ __device__ inline K1Layout k1_layout(uint32_t ppc, uint32_t mat_units, bool tables, bool memo, uint32_t groups = 1) {
     K1Layout L; uint32_t o = 0;
     L.pods = o; o += (ppc + 1u) * 16u;                              // + one slot: the loop prefetches pod i + 1
-    L.keys = o; o += ((ppc * 4u * (K1_THREADS / 32) * groups) + 15u) & ~15u;    // one arg-max row per warp (plain stores, no atomics)
+    L.keys = o; o += ((((ppc + groups - 1u) / groups) * 4u * (K1_THREADS / 32) * groups) + 15u) & ~15u;    // one arg-max row per warp over its group's share of the chunk (plain stores, no atomics)
     L.mat = o; o += mat_units * K1_TILE * 16u;
     L.memo = o; o += memo ? 7u * K1_TILE * 8u : 0u;
     L.topo = o; o += 7u * K1_TILE * 4u;
@@ -135,7 +135,8 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     const uint8_t* hintp = hint + ((size_t)(p_begin + g_begin) * hint_row_bytes + (node >> 3));               // only dereferenced when has_hint && in_range
     const uint32_t key_low = (uint32_t)(K1_TILE - 1 - ltid);
     uint32_t pod_addr = (uint32_t)__cvta_generic_to_shared(spod) + g_begin * 16u;
-    uint32_t key_addr = (uint32_t)__cvta_generic_to_shared(keys) + ((uint32_t)(tid >> 5) * pods_per_chunk + g_begin) * 4u;      // this warp's row
+    const uint32_t row_len = (pods_per_chunk + n_groups - 1u) / n_groups;                                      // a warp's row covers its group's share
+    uint32_t key_addr = (uint32_t)__cvta_generic_to_shared(keys) + (uint32_t)(tid >> 5) * row_len * 4u;      // this warp's row, entry 0 = pod g_begin
     PodLite pd = spod[g_begin];
 #pragma unroll 1
     for (uint32_t i = g_begin; i < g_end; ++i) {
@@ -174,10 +175,10 @@ score_kernel(const DevNode* __restrict__ nodes, uint32_t n_nodes,
     if (best) {
         __syncthreads();
         for (uint32_t i = tid; i < np; i += n_threads) {
-            const uint32_t w0 = (i / sub) * (K1_THREADS / 32);          // the four warps of the group that scored pod i
-            uint32_t kk = keys[w0 * pods_per_chunk + i];
+            const uint32_t g = i / sub, w0 = g * (K1_THREADS / 32), j = i - g * sub;      // the four warps of the group that scored pod i
+            uint32_t kk = keys[w0 * row_len + j];
 #pragma unroll
-            for (int w = 1; w < K1_THREADS / 32; ++w) kk = max(kk, keys[(w0 + w) * pods_per_chunk + i]);
+            for (int w = 1; w < K1_THREADS / 32; ++w) kk = max(kk, keys[(w0 + w) * row_len + j]);
             if (kk) atomicMax(&best[p_begin + i], rank_key((int32_t)(kk >> 7), P.node_base + tile_first + ((uint32_t)(K1_TILE - 1) - (kk & 127u))));
         }
     }
